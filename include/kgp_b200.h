@@ -1,0 +1,127 @@
+/* kgp_b200.h -- C ABI of the B200-native GP inference engine.
+ *
+ * This is the drop-in boundary for the ONE hot path of alshedivat/keras-gp: the GP
+ * engine behind kgp.backend (nlZ, dnlZ, dnlZ/dX, predict for infExact / infGrid).
+ * In the reference that path is a chain  Python -> oct2py -> Octave -> GPML .m code
+ * (kgp/backend/gpml.py:13-31 command strings, kgp/backend/engines.py:72-99).  There
+ * is no FFI in the reference to mirror, so each entry point cites the command
+ * string / .m function it replaces.  Plain pointers and sizes only; no torch types.
+ *
+ * Conventions: all reals are FP64 (the reference up-casts everything,
+ * kgp/backend/engines.py:84-88).  Matrices are row-major (NumPy C order).  Pointers
+ * are HOST pointers when the function name ends in _host, DEVICE pointers when it
+ * ends in _dev.  Every call returns a kgp_status; kgp_last_error() gives text.
+ * One context = one CUDA device + one stream + its workspaces; calls on a context
+ * are blocking at return and must not be issued concurrently.
+ */
+#ifndef KGP_B200_H
+#define KGP_B200_H
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct kgp_ctx kgp_ctx;
+
+typedef enum {
+  KGP_OK = 0,
+  KGP_BAD_ARG = 1,
+  KGP_CUDA_ERR = 2,
+  KGP_NOT_PD = 3,            /* Octave: "chol: input matrix must be positive definite" */
+  KGP_CG_NOT_CONVERGED = 4,  /* GPML/cov/apx.m:277 error('Not converged ...') */
+  KGP_NO_GRID = 5,           /* infGrid called before update_grid / xg */
+  KGP_NO_DATA = 6
+} kgp_status;
+
+/* data slots = the Octave workspace variables X_tr/y_tr, X_tst, X_val, X_tmp
+ * (kgp/backend/gpml.py:152-158) */
+enum { KGP_SLOT_TR = 0, KGP_SLOT_TST = 1, KGP_SLOT_VAL = 2, KGP_SLOT_TMP = 3, KGP_NUM_SLOTS = 4 };
+
+enum { KGP_INF_EXACT = 0, KGP_INF_GRID = 1 };                 /* infExact | infGrid */
+enum { KGP_COV_SEISO = 0, KGP_COV_SEARD = 1, KGP_COV_SM = 2 }; /* covSEiso | covSEard | covSM */
+/* mean function: bit mask, summed in this order (meanSum of the set bits) */
+enum { KGP_MEAN_ZERO = 0, KGP_MEAN_LINEAR = 1, KGP_MEAN_CONST = 2 };
+
+/* GPML `opt` struct fields that reach this path (GPML/cov/apx.m:118-130) */
+typedef struct {
+  double cg_tol;          /* default 1e-6 */
+  int    cg_maxit;        /* default min(n,20); <=0 selects the default */
+  int    ldB2_cheby;      /* 0: Fiedler bound (default), 1: Chebyshev-Hutchinson */
+  int    ldB2_cheby_hutch;   /* probes m, default 10 */
+  int    ldB2_cheby_degree;  /* degree d, default 15 */
+  int    ldB2_cheby_maxit;   /* power/Lanczos iterations for emax, default 50 */
+  uint64_t ldB2_cheby_seed;  /* probe seed (intent of apx.m:130) */
+  int    ard_reference_form; /* 1: dcovSEard.m:7 quirk (divide every dim by ell_1^2) */
+} kgp_opt;
+
+/* per-call statistics of the last kgp_eval / kgp_dlik_dx / kgp_predict */
+typedef struct {
+  double ms_total;        /* device time of the last call (CUDA events) */
+  double ms_kbuild, ms_potrf, ms_inverse, ms_reduce, ms_solve;   /* exact path phases */
+  double ms_gemm;         /* time inside dgemm_nt_kernel launches only (events around them; 0 unless profiling on) */
+  double gemm_flops;      /* algorithmic flops issued to dgemm_nt_kernel in the last call */
+  long   gemm_launches, kernel_launches;
+  int    cg_iters; double cg_relres;   /* grid path */
+  int    potrf_info;      /* 0 or 1-based index of the failing pivot */
+  long   n, np;           /* problem size and padded size */
+} kgp_stats;
+
+/* lifetime ------------------------------------------------------------------- */
+int  kgp_ctx_create(int device, kgp_ctx** out);
+int  kgp_ctx_destroy(kgp_ctx* ctx);
+const char* kgp_last_error(kgp_ctx* ctx);
+const char* kgp_version(void);
+void kgp_opt_default(kgp_opt* opt);
+int  kgp_set_profiling(kgp_ctx* ctx, int on);   /* on: time GEMM launches separately (adds syncs) */
+
+/* data: replaces eng.push('X_<set>',X) / push('y_<set>',y)  (kgp/backend/gpml.py:152-158) */
+int kgp_set_data_host(kgp_ctx* ctx, int slot, const double* X, long n, int D, const double* y /* may be NULL */);
+int kgp_set_data_dev (kgp_ctx* ctx, int slot, const double* X, long n, int D, const double* y /* may be NULL */);
+
+/* model: replaces configure()'s push('hyp',hyp) / push('opt',opt) and the cov/mean/inf
+ * strings (kgp/backend/gpml.py:76-150).  hyp_cov in GPML order ([log ell..., log sf]);
+ * for infGrid the per-dimension blocks are concatenated (column-major read of the
+ * tiled array, GPML/cov/apxGrid.m:230-231). */
+int kgp_set_model(kgp_ctx* ctx, int inf_kind, int cov_kind, int sm_Q, int mean_mask,
+                  const double* hyp_cov, int n_cov, double hyp_lik,
+                  const double* hyp_mean, int n_mean, const kgp_opt* opt /* may be NULL */);
+
+/* evaluate: replaces "[nlZ dnlZ post] = gp(hyp, inf, mean, cov, lik, X, y)"
+ * (kgp/backend/gpml.py:16-18; GPML/gp.m:111-126 -> infGaussLik.m:19-33).
+ * want: 0 = nlZ only, 1 = + dnlZ, 2 = + dnlZ/dX kept on the device for kgp_dlik_dx.
+ * dnlZ_host receives [cov..., lik, mean...] (minimize.m:173-186 unwrap order). */
+int kgp_eval(kgp_ctx* ctx, int slot, int want, double* nlZ_host, double* dnlZ_host);
+
+/* input gradient: replaces "dlik_dx = dlik(hyp, mean, cov, lik, dcov, X, y)"
+ * (kgp/backend/gpml.py:26-28; kgp/backend/utils/dlikExact.m:9-25, dlikGrid.m:8-40).
+ * out is n x D row-major.  Re-uses the factorisation of a preceding kgp_eval(...,2)
+ * on the same slot/model, otherwise runs the inference itself like the reference. */
+int kgp_dlik_dx_host(kgp_ctx* ctx, int slot, double* out);
+int kgp_dlik_dx_dev (kgp_ctx* ctx, int slot, double* out);
+
+/* predict: replaces "[ymu ys2 fmu fs2] = gp(hyp, inf, mean, cov, lik, X_tr, y_tr, X_tst)"
+ * (kgp/backend/gpml.py:19-25; GPML/gp.m:128-181; GPML/inf/infGrid.m:131-145).
+ * Uses slot TR as training data; any output pointer may be NULL. */
+int kgp_predict_host(kgp_ctx* ctx, const double* Xs, long ns,
+                     double* ymu, double* ys2, double* fmu, double* fs2);
+
+/* grid: replaces "xg = covGrid('create', X, eq, k)" (kgp/backend/gpml.py:29-31;
+ * GPML/cov/apxGrid.m:389-416) and push('xg', ...) (kgp/backend/gpml.py:125-126). */
+int kgp_grid_create(kgp_ctx* ctx, int slot, int eq, double k);
+int kgp_grid_set_host(kgp_ctx* ctx, int n_axes, const int* axis_len, const double* axes_concat);
+int kgp_grid_get_host(kgp_ctx* ctx, int* n_axes, int* axis_len /* >= 16 ints */, double* axes_concat /* may be NULL */);
+
+/* posterior pieces for tests / callers that want them (host copies) */
+int kgp_get_alpha_host(kgp_ctx* ctx, double* alpha /* n */);
+
+int kgp_last_stats(kgp_ctx* ctx, kgp_stats* out);
+
+/* measurement helpers (bench.py): FP64 DMMA issue-rate micro-benchmark and a timed
+ * dgemm_nt launch on synthetic operands; both return TFLOP/s. */
+int kgp_bench_dmma_peak(kgp_ctx* ctx, int iters, double* tflops);
+int kgp_bench_dgemm(kgp_ctx* ctx, int n, int k, int reps, double* tflops, double* ms);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

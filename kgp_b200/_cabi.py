@@ -1,0 +1,202 @@
+"""ctypes binding of libkgp_b200.so (C ABI in include/kgp_b200.h).
+
+Replaces the reference's engine layer (kgp/backend/engines.py:7-99: push / pull /
+eval through oct2py).  There is no CPU fallback: if the library or a CUDA device is
+missing, importing works but creating a context raises.
+"""
+import ctypes as C
+import os
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, 'libkgp_b200.so')
+
+OK, BAD_ARG, CUDA_ERR, NOT_PD, CG_NOT_CONVERGED, NO_GRID, NO_DATA = range(7)
+SLOTS = {'tr': 0, 'tst': 1, 'val': 2, 'tmp': 3}
+INF = {'infExact': 0, 'infGrid': 1}
+COV = {'covSEiso': 0, 'covSEard': 1, 'covSM': 2}
+
+
+class KgpOpt(C.Structure):
+    _fields_ = [('cg_tol', C.c_double), ('cg_maxit', C.c_int), ('ldB2_cheby', C.c_int),
+                ('ldB2_cheby_hutch', C.c_int), ('ldB2_cheby_degree', C.c_int),
+                ('ldB2_cheby_maxit', C.c_int), ('ldB2_cheby_seed', C.c_uint64),
+                ('ard_reference_form', C.c_int)]
+
+
+class KgpStats(C.Structure):
+    _fields_ = [('ms_total', C.c_double), ('ms_kbuild', C.c_double), ('ms_potrf', C.c_double),
+                ('ms_inverse', C.c_double), ('ms_reduce', C.c_double), ('ms_solve', C.c_double),
+                ('ms_gemm', C.c_double), ('gemm_flops', C.c_double), ('gemm_launches', C.c_long),
+                ('kernel_launches', C.c_long), ('cg_iters', C.c_int), ('cg_relres', C.c_double),
+                ('potrf_info', C.c_int), ('n', C.c_long), ('np', C.c_long)]
+
+    def as_dict(self):
+        return {k: getattr(self, k) for k, _ in self._fields_}
+
+
+class KgpError(RuntimeError):
+    def __init__(self, code, msg):
+        super().__init__('kgp_b200 error %d: %s' % (code, msg))
+        self.code = code
+
+
+_lib = None
+_DP = C.POINTER(C.c_double)
+
+# name -> (restype, argtypes); every symbol include/kgp_b200.h declares
+SIGNATURES = {
+    'kgp_ctx_create': (C.c_int, [C.c_int, C.POINTER(C.c_void_p)]),
+    'kgp_ctx_destroy': (C.c_int, [C.c_void_p]),
+    'kgp_last_error': (C.c_char_p, [C.c_void_p]),
+    'kgp_version': (C.c_char_p, []),
+    'kgp_opt_default': (None, [C.POINTER(KgpOpt)]),
+    'kgp_set_profiling': (C.c_int, [C.c_void_p, C.c_int]),
+    'kgp_set_data_host': (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_long, C.c_int, C.c_void_p]),
+    'kgp_set_data_dev': (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_long, C.c_int, C.c_void_p]),
+    'kgp_set_model': (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_int,
+                                C.c_double, C.c_void_p, C.c_int, C.POINTER(KgpOpt)]),
+    'kgp_eval': (C.c_int, [C.c_void_p, C.c_int, C.c_int, _DP, C.c_void_p]),
+    'kgp_dlik_dx_host': (C.c_int, [C.c_void_p, C.c_int, C.c_void_p]),
+    'kgp_dlik_dx_dev': (C.c_int, [C.c_void_p, C.c_int, C.c_void_p]),
+    'kgp_predict_host': (C.c_int, [C.c_void_p, C.c_void_p, C.c_long, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
+    'kgp_grid_create': (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_double]),
+    'kgp_grid_set_host': (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]),
+    'kgp_grid_get_host': (C.c_int, [C.c_void_p, C.POINTER(C.c_int), C.c_void_p, C.c_void_p]),
+    'kgp_get_alpha_host': (C.c_int, [C.c_void_p, C.c_void_p]),
+    'kgp_last_stats': (C.c_int, [C.c_void_p, C.POINTER(KgpStats)]),
+    'kgp_bench_dmma_peak': (C.c_int, [C.c_void_p, C.c_int, _DP]),
+    'kgp_bench_dgemm': (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, _DP, _DP]),
+}
+
+
+def lib():
+    """Load the shared library (built by __graft_entry__.build / csrc/Makefile)."""
+    global _lib
+    if _lib is None:
+        if not os.path.isfile(LIB_PATH):
+            raise ImportError('libkgp_b200.so not built: run `python -c "import __graft_entry__ as g; g.build()"`')
+        l = C.CDLL(LIB_PATH)
+        for name, (res, args) in SIGNATURES.items():
+            fn = getattr(l, name)
+            fn.restype = res
+            fn.argtypes = args
+        _lib = l
+    return _lib
+
+
+def _ptr(a):
+    return None if a is None else a.ctypes.data_as(C.c_void_p)
+
+
+def f64(a, shape=None):
+    a = np.ascontiguousarray(a, dtype=np.float64)      # float32 -> float64 like engines.py:84-88
+    if shape is not None:
+        a = a.reshape(shape)
+    return a
+
+
+class Context(object):
+    """One engine context = one CUDA device, stream and workspace set."""
+
+    def __init__(self, device=0):
+        self._l = lib()
+        h = C.c_void_p()
+        rc = self._l.kgp_ctx_create(int(device), C.byref(h))
+        if rc != OK:
+            raise KgpError(rc, 'cannot create a CUDA context on device %d (no GPU / driver?) -- '
+                               'this engine has no CPU path' % device)
+        self._h = h
+
+    def close(self):
+        if getattr(self, '_h', None):
+            self._l.kgp_ctx_destroy(self._h)
+            self._h = None
+
+    __del__ = close
+
+    def _chk(self, rc):
+        if rc != OK:
+            raise KgpError(rc, self._l.kgp_last_error(self._h).decode())
+
+    def set_data(self, slot, X, y=None):
+        X = f64(X)
+        if X.ndim == 1:
+            X = X[:, None]
+        n, D = X.shape
+        yy = None if y is None else f64(y, (-1,))
+        if yy is not None and yy.size != n:
+            raise ValueError('X and y disagree: %d vs %d rows' % (n, yy.size))
+        self._chk(self._l.kgp_set_data_host(self._h, slot, _ptr(X), n, D, _ptr(yy)))
+
+    def set_data_dev(self, slot, X_ptr, n, D, y_ptr=None):
+        self._chk(self._l.kgp_set_data_dev(self._h, slot, C.c_void_p(X_ptr), n, D,
+                                           C.c_void_p(y_ptr) if y_ptr else None))
+
+    def set_model(self, inf, cov, hyp_cov, hyp_lik, hyp_mean=(), mean_mask=0, sm_Q=0, opt=None):
+        hc = f64(hyp_cov, (-1,)); hm = f64(hyp_mean, (-1,))
+        o = KgpOpt(); self._l.kgp_opt_default(C.byref(o))
+        for k, v in (opt or {}).items():
+            if hasattr(o, k):
+                setattr(o, k, type(getattr(o, k))(v))
+        self._chk(self._l.kgp_set_model(self._h, INF[inf], COV[cov], int(sm_Q), int(mean_mask), _ptr(hc), hc.size,
+                                        float(hyp_lik), _ptr(hm), hm.size, C.byref(o)))
+
+    def eval(self, slot, want, n_hyp):
+        nlZ = C.c_double()
+        g = np.zeros(max(n_hyp, 1))
+        self._chk(self._l.kgp_eval(self._h, slot, want, C.byref(nlZ), _ptr(g) if want else None))
+        return nlZ.value, g[:n_hyp]
+
+    def dlik_dx(self, slot, n, D):
+        out = np.empty((n, D))
+        self._chk(self._l.kgp_dlik_dx_host(self._h, slot, _ptr(out)))
+        return out
+
+    def predict(self, Xs, want_var=True):
+        Xs = f64(Xs)
+        if Xs.ndim == 1:
+            Xs = Xs[:, None]
+        ns = Xs.shape[0]
+        ymu = np.empty(ns); ys2 = np.empty(ns) if want_var else None
+        self._chk(self._l.kgp_predict_host(self._h, _ptr(Xs), ns, _ptr(ymu), _ptr(ys2), None, None))
+        return ymu, ys2
+
+    def alpha(self, n):
+        a = np.empty(n)
+        self._chk(self._l.kgp_get_alpha_host(self._h, _ptr(a)))
+        return a
+
+    def grid_create(self, slot, eq, k):
+        self._chk(self._l.kgp_grid_create(self._h, slot, int(eq), float(k)))
+
+    def grid_set(self, axes):
+        axes = [f64(a, (-1,)) for a in axes]
+        lens = np.array([a.size for a in axes], dtype=np.int32)
+        cat = np.concatenate(axes)
+        self._chk(self._l.kgp_grid_set_host(self._h, len(axes), _ptr(lens), _ptr(cat)))
+
+    def grid_get(self):
+        na = C.c_int(); lens = np.zeros(16, dtype=np.int32)
+        self._chk(self._l.kgp_grid_get_host(self._h, C.byref(na), _ptr(lens), None))
+        cat = np.empty(int(lens[:na.value].sum()))
+        self._chk(self._l.kgp_grid_get_host(self._h, C.byref(na), _ptr(lens), _ptr(cat)))
+        out, o = [], 0
+        for a in range(na.value):
+            out.append(cat[o:o + lens[a]].copy()); o += lens[a]
+        return out
+
+    def stats(self):
+        s = KgpStats()
+        self._chk(self._l.kgp_last_stats(self._h, C.byref(s)))
+        return s.as_dict()
+
+    def bench_dmma_peak(self, iters=20000):
+        t = C.c_double()
+        self._chk(self._l.kgp_bench_dmma_peak(self._h, iters, C.byref(t)))
+        return t.value
+
+    def bench_dgemm(self, n=8192, k=8192, reps=3):
+        t = C.c_double(); ms = C.c_double()
+        self._chk(self._l.kgp_bench_dgemm(self._h, n, k, reps, C.byref(t), C.byref(ms)))
+        return t.value, ms.value

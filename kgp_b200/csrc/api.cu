@@ -1,0 +1,252 @@
+// C ABI of libkgp_b200.so (declared in include/kgp_b200.h).
+#include "ctx.h"
+#include "dgemm_nt.cuh"
+#include <string.h>
+#include <math.h>
+#include <new>
+
+namespace kgp {
+int exact_init(kgp_ctx* c);
+int exact_eval(kgp_ctx* c, int slot, int want, double* nlZ, double* dnlZ);
+int exact_dlik(kgp_ctx* c, int slot, double* out, bool out_is_dev);
+int exact_alpha(kgp_ctx* c, double* out);
+int exact_predict(kgp_ctx* c, const double* Xs, long ns, double* ymu, double* ys2, double* fmu, double* fs2);
+int grid_eval(kgp_ctx* c, int slot, int want, double* nlZ, double* dnlZ);
+int grid_dlik(kgp_ctx* c, int slot, double* out, bool out_is_dev);
+int grid_alpha(kgp_ctx* c, double* out);
+int grid_predict(kgp_ctx* c, const double* Xs, long ns, double* ymu, double* ys2, double* fmu, double* fs2);
+int grid_create(kgp_ctx* c, int slot, int eq, double k);
+void grid_free(kgp_ctx* c);
+
+// FP64 DMMA issue-rate micro-benchmark: 8 warps/SMSP-worth of independent DMMA chains
+__global__ void dmma_peak_kernel(double* out, int iters) {
+  double c[16][2];
+#pragma unroll
+  for (int i = 0; i < 16; ++i) { c[i][0] = 0.0; c[i][1] = 0.0; }
+  double a = 1.0 + threadIdx.x * 1e-9, b = 1.0 - threadIdx.x * 1e-9;
+  for (int it = 0; it < iters; ++it) {
+#pragma unroll
+    for (int i = 0; i < 16; ++i) dmma884(c[i][0], c[i][1], a, b);
+  }
+  double s = 0.0;
+#pragma unroll
+  for (int i = 0; i < 16; ++i) s += c[i][0] + c[i][1];
+  if (s == 123.456) out[0] = s;
+}
+__global__ void fill_kernel(double* p, long n, double scale) {
+  long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) p[i] = scale * (double)((i * 2654435761u) % 1024) / 1024.0;
+}
+}  // namespace kgp
+
+using namespace kgp;
+
+extern "C" {
+
+const char* kgp_version(void) { return "kgp_b200 0.1 (sm_100a)"; }
+
+void kgp_opt_default(kgp_opt* o) {
+  memset(o, 0, sizeof *o);
+  o->cg_tol = 1e-6; o->cg_maxit = 0; o->ldB2_cheby = 0; o->ldB2_cheby_hutch = 10;
+  o->ldB2_cheby_degree = 15; o->ldB2_cheby_maxit = 50; o->ldB2_cheby_seed = 0; o->ard_reference_form = 0;
+}
+
+int kgp_ctx_create(int device, kgp_ctx** out) {
+  if (!out) return KGP_BAD_ARG;
+  *out = nullptr;
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev <= 0) return KGP_CUDA_ERR;   // no CPU fallback
+  if (device < 0 || device >= ndev) return KGP_BAD_ARG;
+  if (cudaSetDevice(device) != cudaSuccess) return KGP_CUDA_ERR;
+  kgp_ctx* c = new (std::nothrow) kgp_ctx();
+  if (!c) return KGP_CUDA_ERR;
+  c->device = device;
+  kgp_opt_default(&c->model.opt);
+  memset(&c->stats, 0, sizeof c->stats);
+  if (cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) != cudaSuccess) { delete c; return KGP_CUDA_ERR; }
+  for (int i = 0; i < 16; ++i) cudaEventCreate(&c->ev[i]);
+  int rc = exact_init(c);
+  if (rc) { fprintf(stderr, "kgp_ctx_create: %s\n", c->err.c_str()); delete c; return rc; }
+  *out = c;
+  return KGP_OK;
+}
+
+int kgp_ctx_destroy(kgp_ctx* c) {
+  if (!c) return KGP_OK;
+  cudaSetDevice(c->device);
+  cudaStreamSynchronize(c->stream);
+  grid_free(c);
+  DevBuf* bufs[] = {&c->M, &c->W2, &c->Dws, &c->xs, &c->s, &c->mu, &c->inv_ell, &c->ym, &c->alpha, &c->tvec,
+                    &c->parts, &c->rows, &c->scal, &c->hypm, &c->dX, &c->fac, &c->pred_K, &c->pred_x, &c->pred_s,
+                    &c->pred_a, &c->pred_b, &c->pred_out, &c->pred_X};
+  for (DevBuf* b : bufs) b->release();
+  for (auto& s : c->slots) { s.X.release(); s.y.release(); }
+  if (c->d_info) cudaFree(c->d_info);
+  for (int i = 0; i < 16; ++i) cudaEventDestroy(c->ev[i]);
+  cudaStreamDestroy(c->stream);
+  delete c;
+  return KGP_OK;
+}
+
+const char* kgp_last_error(kgp_ctx* c) { return c ? c->err.c_str() : "null context"; }
+int kgp_set_profiling(kgp_ctx* c, int on) { if (!c) return KGP_BAD_ARG; c->profiling = on; return KGP_OK; }
+
+static int set_data(kgp_ctx* c, int slot, const double* X, long n, int D, const double* y, cudaMemcpyKind kind) {
+  if (!c) return KGP_BAD_ARG;
+  if (slot < 0 || slot >= KGP_NUM_SLOTS) return c->fail(KGP_BAD_ARG, "bad slot %d", slot);
+  if (!X || n <= 0 || D <= 0) return c->fail(KGP_BAD_ARG, "bad data shape n=%ld D=%d", n, D);
+  cudaSetDevice(c->device);
+  Slot& S = c->slots[slot];
+  KGP_CUDA(c, S.X.ensure((size_t)n * D * 8));
+  KGP_CUDA(c, cudaMemcpyAsync(S.X.p, X, (size_t)n * D * 8, kind, c->stream));
+  if (y) {
+    KGP_CUDA(c, S.y.ensure((size_t)n * 8));
+    KGP_CUDA(c, cudaMemcpyAsync(S.y.p, y, (size_t)n * 8, kind, c->stream));
+    S.has_y = true;
+  } else if (S.n != n) S.has_y = false;     // a stale y of another length cannot be used
+  S.n = n; S.D = D; S.version++;
+  KGP_CUDA(c, cudaStreamSynchronize(c->stream));
+  return KGP_OK;
+}
+int kgp_set_data_host(kgp_ctx* c, int slot, const double* X, long n, int D, const double* y) {
+  return set_data(c, slot, X, n, D, y, cudaMemcpyHostToDevice);
+}
+int kgp_set_data_dev(kgp_ctx* c, int slot, const double* X, long n, int D, const double* y) {
+  return set_data(c, slot, X, n, D, y, cudaMemcpyDeviceToDevice);
+}
+
+int kgp_set_model(kgp_ctx* c, int inf_kind, int cov_kind, int sm_Q, int mean_mask, const double* hyp_cov, int n_cov,
+                  double hyp_lik, const double* hyp_mean, int n_mean, const kgp_opt* opt) {
+  if (!c) return KGP_BAD_ARG;
+  if (inf_kind != KGP_INF_EXACT && inf_kind != KGP_INF_GRID) return c->fail(KGP_BAD_ARG, "unknown inference method %d", inf_kind);
+  if (cov_kind < KGP_COV_SEISO || cov_kind > KGP_COV_SM) return c->fail(KGP_BAD_ARG, "unknown covariance %d", cov_kind);
+  if (inf_kind == KGP_INF_EXACT && cov_kind == KGP_COV_SM) return c->fail(KGP_BAD_ARG, "covSM is supported on the infGrid path only");
+  if (n_cov < 0 || n_mean < 0 || (n_cov && !hyp_cov) || (n_mean && !hyp_mean)) return c->fail(KGP_BAD_ARG, "bad hyp arrays");
+  if (mean_mask & ~3) return c->fail(KGP_BAD_ARG, "unknown mean mask %d", mean_mask);
+  Model& m = c->model;
+  m.inf_kind = inf_kind; m.cov_kind = cov_kind; m.sm_Q = sm_Q; m.mean_mask = mean_mask;
+  m.hyp_cov.assign(hyp_cov, hyp_cov + n_cov); m.hyp_mean.assign(hyp_mean, hyp_mean + n_mean); m.hyp_lik = hyp_lik;
+  if (opt) m.opt = *opt;
+  m.set = true; m.version++;
+  return KGP_OK;
+}
+
+static int check_ready(kgp_ctx* c, int slot, bool need_y) {
+  if (!c) return KGP_BAD_ARG;
+  if (slot < 0 || slot >= KGP_NUM_SLOTS) return c->fail(KGP_BAD_ARG, "bad slot %d", slot);
+  if (!c->model.set) return c->fail(KGP_NO_DATA, "model not configured");
+  if (c->slots[slot].n <= 0) return c->fail(KGP_NO_DATA, "data slot %d is empty", slot);
+  if (need_y && !c->slots[slot].has_y) return c->fail(KGP_NO_DATA, "data slot %d has no targets y", slot);
+  cudaSetDevice(c->device);
+  return KGP_OK;
+}
+
+int kgp_eval(kgp_ctx* c, int slot, int want, double* nlZ, double* dnlZ) {
+  int rc = check_ready(c, slot, true); if (rc) return rc;
+  if (want < 0 || want > 2) return c->fail(KGP_BAD_ARG, "want must be 0, 1 or 2");
+  return c->model.inf_kind == KGP_INF_EXACT ? exact_eval(c, slot, want, nlZ, dnlZ) : grid_eval(c, slot, want, nlZ, dnlZ);
+}
+int kgp_dlik_dx_host(kgp_ctx* c, int slot, double* out) {
+  int rc = check_ready(c, slot, true); if (rc) return rc;
+  if (!out) return c->fail(KGP_BAD_ARG, "null output");
+  return c->model.inf_kind == KGP_INF_EXACT ? exact_dlik(c, slot, out, false) : grid_dlik(c, slot, out, false);
+}
+int kgp_dlik_dx_dev(kgp_ctx* c, int slot, double* out) {
+  int rc = check_ready(c, slot, true); if (rc) return rc;
+  if (!out) return c->fail(KGP_BAD_ARG, "null output");
+  return c->model.inf_kind == KGP_INF_EXACT ? exact_dlik(c, slot, out, true) : grid_dlik(c, slot, out, true);
+}
+int kgp_predict_host(kgp_ctx* c, const double* Xs, long ns, double* ymu, double* ys2, double* fmu, double* fs2) {
+  int rc = check_ready(c, KGP_SLOT_TR, true); if (rc) return rc;
+  if (!Xs || ns <= 0) return c->fail(KGP_BAD_ARG, "bad test inputs");
+  return c->model.inf_kind == KGP_INF_EXACT ? exact_predict(c, Xs, ns, ymu, ys2, fmu, fs2)
+                                            : grid_predict(c, Xs, ns, ymu, ys2, fmu, fs2);
+}
+int kgp_get_alpha_host(kgp_ctx* c, double* alpha) {
+  if (!c || !alpha) return KGP_BAD_ARG;
+  cudaSetDevice(c->device);
+  return c->model.inf_kind == KGP_INF_EXACT ? exact_alpha(c, alpha) : grid_alpha(c, alpha);
+}
+
+int kgp_grid_create(kgp_ctx* c, int slot, int eq, double k) {
+  if (!c) return KGP_BAD_ARG;
+  if (slot < 0 || slot >= KGP_NUM_SLOTS || c->slots[slot].n <= 0) return c->fail(KGP_NO_DATA, "data slot %d is empty", slot);
+  cudaSetDevice(c->device);
+  return grid_create(c, slot, eq, k);
+}
+int kgp_grid_set_host(kgp_ctx* c, int n_axes, const int* axis_len, const double* axes) {
+  if (!c || n_axes <= 0 || n_axes > 16 || !axis_len || !axes) return c ? c->fail(KGP_BAD_ARG, "bad grid") : KGP_BAD_ARG;
+  c->grid.axes.clear();
+  long o = 0;
+  for (int a = 0; a < n_axes; ++a) {
+    if (axis_len[a] < 4) return c->fail(KGP_BAD_ARG, "grid axis %d needs >= 4 points", a);
+    c->grid.axes.emplace_back(axes + o, axes + o + axis_len[a]); o += axis_len[a];
+  }
+  c->grid.set = true; c->grid.version++;
+  return KGP_OK;
+}
+int kgp_grid_get_host(kgp_ctx* c, int* n_axes, int* axis_len, double* axes) {
+  if (!c || !n_axes) return KGP_BAD_ARG;
+  if (!c->grid.set) return c->fail(KGP_NO_GRID, "no grid: call update_grid or pass grid_kwargs['xg']");
+  *n_axes = (int)c->grid.axes.size();
+  long o = 0;
+  for (size_t a = 0; a < c->grid.axes.size(); ++a) {
+    if (axis_len) axis_len[a] = (int)c->grid.axes[a].size();
+    if (axes) memcpy(axes + o, c->grid.axes[a].data(), c->grid.axes[a].size() * 8);
+    o += (long)c->grid.axes[a].size();
+  }
+  return KGP_OK;
+}
+
+int kgp_last_stats(kgp_ctx* c, kgp_stats* out) {
+  if (!c || !out) return KGP_BAD_ARG;
+  *out = c->stats; return KGP_OK;
+}
+
+int kgp_bench_dmma_peak(kgp_ctx* c, int iters, double* tflops) {
+  if (!c || !tflops) return KGP_BAD_ARG;
+  cudaSetDevice(c->device);
+  cudaDeviceProp p; KGP_CUDA(c, cudaGetDeviceProperties(&p, c->device));
+  KGP_CUDA(c, c->scal.ensure(256 * 8));
+  const int blocks = p.multiProcessorCount * 2, threads = 512;
+  dmma_peak_kernel<<<blocks, threads, 0, c->stream>>>(c->scal.d(), 16);
+  double best = 0.0;
+  for (int rep = 0; rep < 5; ++rep) {
+    cudaEventRecord(c->ev[8], c->stream);
+    dmma_peak_kernel<<<blocks, threads, 0, c->stream>>>(c->scal.d(), iters);
+    cudaEventRecord(c->ev[9], c->stream);
+    KGP_CUDA(c, cudaStreamSynchronize(c->stream));
+    float ms = 0; cudaEventElapsedTime(&ms, c->ev[8], c->ev[9]);
+    double fl = (double)blocks * (threads / 32) * (double)iters * 16.0 * 512.0;   // 8x8x4 MACs = 512 flop
+    double tf = fl / (ms * 1e-3) / 1e12;
+    if (tf > best) best = tf;
+  }
+  *tflops = best;
+  return KGP_OK;
+}
+
+int kgp_bench_dgemm(kgp_ctx* c, int n, int k, int reps, double* tflops, double* ms_out) {
+  if (!c || n % 128 || k % 16 || n <= 0 || k <= 0) return c ? c->fail(KGP_BAD_ARG, "n%%128, k%%16 required") : KGP_BAD_ARG;
+  cudaSetDevice(c->device);
+  DevBuf A, B, C;
+  KGP_CUDA(c, A.ensure((size_t)n * k * 8)); KGP_CUDA(c, B.ensure((size_t)n * k * 8)); KGP_CUDA(c, C.ensure((size_t)n * n * 8));
+  fill_kernel<<<(unsigned)(((long)n * k + 255) / 256), 256, 0, c->stream>>>(A.d(), (long)n * k, 1.0);
+  fill_kernel<<<(unsigned)(((long)n * k + 255) / 256), 256, 0, c->stream>>>(B.d(), (long)n * k, 0.5);
+  GemmArgs g; memset(&g, 0, sizeof g);
+  g.A = A.d(); g.lda = k; g.B = B.d(); g.ldb = k; g.C = C.d(); g.ldc = n; g.ntm = g.ntn = n / 128;
+  g.kbeg = 0; g.kend = k; g.shape = GEMM_FULL; g.ktri = KTRI_NONE; g.alpha = 1.0; g.beta = 0.0; g.nb = NB;
+  gemm_launch(g, c->stream);
+  cudaEventRecord(c->ev[8], c->stream);
+  for (int r = 0; r < reps; ++r) gemm_launch(g, c->stream);
+  cudaEventRecord(c->ev[9], c->stream);
+  KGP_CUDA(c, cudaStreamSynchronize(c->stream));
+  KGP_CUDA(c, cudaGetLastError());
+  float ms = 0; cudaEventElapsedTime(&ms, c->ev[8], c->ev[9]);
+  ms /= reps;
+  if (ms_out) *ms_out = ms;
+  if (tflops) *tflops = 2.0 * n * (double)n * k / (ms * 1e-3) / 1e12;
+  A.release(); B.release(); C.release();
+  return KGP_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,80 @@
+// Engine context: device buffers + model state.  One per kgp_ctx (C ABI).
+#pragma once
+#include <cuda_runtime.h>
+#include <string>
+#include <vector>
+#include <stdarg.h>
+#include <stdio.h>
+#include "../../include/kgp_b200.h"
+
+namespace kgp {
+
+struct DevBuf {
+  void* p = nullptr; size_t bytes = 0;
+  cudaError_t ensure(size_t need) {
+    if (need <= bytes) return cudaSuccess;
+    if (p) cudaFree(p);
+    p = nullptr; bytes = 0;
+    cudaError_t e = cudaMalloc(&p, need);
+    if (e == cudaSuccess) bytes = need;
+    return e;
+  }
+  void release() { if (p) cudaFree(p); p = nullptr; bytes = 0; }
+  double* d() const { return (double*)p; }
+};
+
+struct Slot {
+  DevBuf X, y; long n = 0; int D = 0; bool has_y = false;
+  unsigned long version = 0;
+};
+
+struct Model {
+  int inf_kind = KGP_INF_EXACT, cov_kind = KGP_COV_SEISO, sm_Q = 0, mean_mask = 0;
+  std::vector<double> hyp_cov, hyp_mean; double hyp_lik = 0.0;
+  kgp_opt opt; bool set = false;
+  unsigned long version = 0;
+};
+
+struct Grid {
+  std::vector<std::vector<double>> axes;   // xg{d} = equispaced axis values
+  bool set = false; unsigned long version = 0;
+};
+
+constexpr int NB = 512;     // outer block width of the blocked factorisations
+
+}  // namespace kgp
+
+struct kgp_ctx {
+  int device = 0;
+  cudaStream_t stream = nullptr;
+  cudaEvent_t ev[16];
+  std::string err;
+  kgp::Slot slots[KGP_NUM_SLOTS];
+  kgp::Model model;
+  kgp::Grid grid;
+  kgp_stats stats;
+  int profiling = 0;
+
+  // exact-path device state
+  kgp::DevBuf M, W2, Dws;             // L (lower) | Z upper -> full B^{-1} | diagonal nb-blocks of B^{-1}
+  kgp::DevBuf xs, s, mu, inv_ell, ym, alpha, tvec, parts, rows, scal, hypm, dX, fac;
+  kgp::DevBuf pred_K, pred_x, pred_s, pred_a, pred_b, pred_out, pred_X;
+  int* d_info = nullptr;
+  long np = 0; int Dp = 0;
+  // what the factorisation state corresponds to
+  unsigned long st_slot_ver = 0, st_model_ver = 0; int st_slot = -1; int st_level = -1;  // -1 none, 0 L+alpha, 2 +dX
+  double st_nlZ = 0.0; std::vector<double> st_dnlZ;
+  // grid-path state lives in grid.cu (opaque)
+  void* gridstate = nullptr;
+
+  int fail(int code, const char* fmt, ...) {
+    char buf[512]; va_list ap; va_start(ap, fmt); vsnprintf(buf, sizeof buf, fmt, ap); va_end(ap);
+    err = buf; return code;
+  }
+};
+
+#define KGP_CUDA(ctx, call)                                                              \
+  do { cudaError_t e__ = (call);                                                         \
+       if (e__ != cudaSuccess)                                                           \
+         return (ctx)->fail(KGP_CUDA_ERR, "%s:%d %s: %s", __FILE__, __LINE__, #call, cudaGetErrorString(e__)); \
+  } while (0)

@@ -1,0 +1,351 @@
+// Host orchestration of the exact-GP path on one B200.
+//
+// What the reference does per evaluation (GPML/inf/infGaussLik.m:19-33 with
+// GPML/cov/apx.m:141-173): K, L = chol(I + K/sn2), Q = B^{-1} by two n-RHS
+// triangular solves, alpha, nlZ, dnlZ; then dlikExact.m re-runs it all for dnlZ/dX.
+// Here: one blocked FP64 Cholesky, one triangular inverse Z = L^{-T}, one product
+// B^{-1} = Z Z^T (n^3 flops in total instead of 7n^3/3), all O(n^3) work in
+// dgemm_nt_kernel (DMMA), and ONE fused O(n^2) pass for every gradient.
+//
+// Storage (row-major, order np = n rounded up to 128, identity padding):
+//   M  : lower triangle = B, then L (kept: prediction solves with it)
+//   W2 : upper triangle = Z = L^{-T} (so that every GEMM operand is K-contiguous),
+//        then the full symmetric B^{-1}
+//   Dws: the diagonal NB x NB blocks of B^{-1} while W2's diagonal blocks still hold Z
+#include "ctx.h"
+#include "exact_kernels2.cuh"
+#include <math.h>
+#include <string.h>
+
+namespace kgp {
+
+static inline void count_gemm(kgp_ctx* c, const GemmArgs& g) {
+  c->stats.gemm_launches++; c->stats.kernel_launches++;
+  double f = 0.0;
+  for (int tm = 0; tm < g.ntm; ++tm) {
+    int ntn = (g.shape == GEMM_LOWER) ? (tm + 1 < g.ntn ? tm + 1 : g.ntn) : g.ntn;
+    int kb = g.kbeg + (g.ktri == KTRI_FROM_M0 ? tm * 128 : 0);
+    f += 2.0 * 128.0 * 128.0 * (double)(g.kend - kb) * ntn;
+  }
+  c->stats.gemm_flops += f;
+}
+static inline void gemm(kgp_ctx* c, const GemmArgs& g) {
+  if (g.ntm <= 0 || g.ntn <= 0) return;
+  count_gemm(c, g);
+  gemm_launch(g, c->stream);
+}
+static inline GemmArgs mkgemm(const double* A, long lda, const double* B, long ldb, double* C, long ldc,
+                              int ntm, int ntn, int kbeg, int kend, int shape, int ktri, double alpha, double beta) {
+  GemmArgs g; memset(&g, 0, sizeof g);
+  g.A = A; g.lda = lda; g.B = B; g.ldb = ldb; g.C = C; g.ldc = ldc; g.ntm = ntm; g.ntn = ntn;
+  g.kbeg = kbeg; g.kend = kend; g.shape = shape; g.ktri = ktri; g.alpha = alpha; g.beta = beta;
+  g.Cdiag = nullptr; g.nb = NB; g.cdiag_only = 0;
+  return g;
+}
+
+// X (mrows x w, leading dim ldx) <- X * Lblk^{-T}, Lblk lower w x w (w multiple of 128, <= NB)
+static void trsm_block(kgp_ctx* c, double* X, long ldx, long mrows, const double* Lblk, long ldl, int w) {
+  const int nc = w / 128;
+  for (int cb = 0; cb < nc; ++cb) {
+    trsm128_rows_kernel<<<(unsigned)(mrows / 128), TR_THREADS, TR_SMEM, c->stream>>>(
+        X + cb * 128, ldx, mrows, Lblk + (long)cb * 128 * ldl + cb * 128, ldl);
+    c->stats.kernel_launches++;
+    if (cb + 1 < nc)
+      gemm(c, mkgemm(X + cb * 128, ldx, Lblk + (long)(cb + 1) * 128 * ldl + cb * 128, ldl,
+                     X + (cb + 1) * 128, ldx, (int)(mrows / 128), nc - cb - 1, 0, 128, GEMM_FULL, KTRI_NONE, -1.0, 1.0));
+  }
+}
+
+// blocked right-looking Cholesky of the lower triangle of M (two levels: NB / 128)
+static void potrf(kgp_ctx* c) {
+  double* M = c->M.d(); const long ld = c->np, np = c->np;
+  for (long k0 = 0; k0 < np; k0 += NB) {
+    const int w = (int)((np - k0 < NB) ? np - k0 : NB);
+    for (int cb = 0; cb < w / 128; ++cb) {
+      const long j = k0 + cb * 128, r0 = j + 128, mrows = np - r0;
+      potrf_diag128_kernel<<<1, PD_THREADS, PD_SMEM, c->stream>>>(M + j * ld + j, ld, (int)j, c->d_info);
+      c->stats.kernel_launches++;
+      if (mrows > 0) {
+        trsm128_rows_kernel<<<(unsigned)(mrows / 128), TR_THREADS, TR_SMEM, c->stream>>>(
+            M + r0 * ld + j, ld, mrows, M + j * ld + j, ld);
+        c->stats.kernel_launches++;
+        const long ncols = k0 + w - r0;
+        if (ncols > 0)
+          gemm(c, mkgemm(M + r0 * ld + j, ld, M + r0 * ld + j, ld, M + r0 * ld + r0, ld,
+                         (int)(mrows / 128), (int)(ncols / 128), 0, 128, GEMM_LOWER, KTRI_NONE, -1.0, 1.0));
+      }
+    }
+    const long r0 = k0 + w, mt = (np - r0) / 128;
+    if (mt > 0)
+      gemm(c, mkgemm(M + r0 * ld + k0, ld, M + r0 * ld + k0, ld, M + r0 * ld + r0, ld,
+                     (int)mt, (int)mt, 0, w, GEMM_LOWER, KTRI_NONE, -1.0, 1.0));
+  }
+}
+
+// Z = L^{-T} into the upper triangle of W2, block column by block column
+static void zsweep(kgp_ctx* c) {
+  const double* M = c->M.d(); double* W = c->W2.d(); const long ld = c->np, np = c->np;
+  for (long k0 = 0; k0 < np; k0 += NB) {
+    const int w = (int)((np - k0 < NB) ? np - k0 : NB);
+    if (k0 > 0)
+      gemm(c, mkgemm(W, ld, M + k0 * ld, ld, W + k0, ld, (int)(k0 / 128), w / 128, 0, (int)k0,
+                     GEMM_FULL, KTRI_FROM_M0, -1.0, 0.0));
+    set_identity_kernel<<<(unsigned)(((long)w * w + 255) / 256), 256, 0, c->stream>>>(W + k0 * ld + k0, ld, w);
+    c->stats.kernel_launches++;
+    trsm_block(c, W + k0, ld, k0 + w, M + k0 * ld + k0, ld, w);
+  }
+}
+
+// B^{-1} = Z Z^T : off-diagonal NB-blocks into W2's lower triangle, diagonal blocks into Dws
+static void zzt(kgp_ctx* c) {
+  double* W = c->W2.d(); const long ld = c->np; const int nt = (int)(c->np / 128);
+  GemmArgs g = mkgemm(W, ld, W, ld, W, ld, nt, nt, 0, (int)c->np, GEMM_LOWER, KTRI_FROM_M0, 1.0, 0.0);
+  g.Cdiag = c->Dws.d(); g.nb = NB; g.cdiag_only = 0;
+  gemm(c, g);
+  dim3 grid((unsigned)(c->np / 32), (unsigned)(c->np / 32)), blk(32, 8);
+  mirror_finalize_kernel<<<grid, blk, 0, c->stream>>>(W, ld, c->np, c->Dws.d(), NB);
+  c->stats.kernel_launches++;
+}
+
+static int pick_dp(int D) { return D <= 4 ? 4 : D <= 8 ? 8 : D <= 16 ? 16 : 32; }
+
+template <int DP>
+static void launch_reduce(kgp_ctx* c, long n, double sf2, double inv_sn2, int nsplit, int per) {
+  dim3 grid((unsigned)(c->np / 128), (unsigned)nsplit);
+  reduce_grad_kernel<DP><<<grid, 128, 0, c->stream>>>(c->W2.d(), c->np, n, c->np, c->xs.d(), c->alpha.d(),
+                                                     sf2, inv_sn2, per, c->parts.d());
+}
+
+static int ensure_exact_buffers(kgp_ctx* c, long n, int D) {
+  const long np = ((n + 127) / 128) * 128;
+  const int Dp = pick_dp(D);
+  c->np = np; c->Dp = Dp;
+  KGP_CUDA(c, c->M.ensure((size_t)np * np * 8));
+  KGP_CUDA(c, c->W2.ensure((size_t)np * np * 8));
+  KGP_CUDA(c, c->Dws.ensure((size_t)np * NB * 8));
+  KGP_CUDA(c, c->xs.ensure((size_t)np * Dp * 8));
+  KGP_CUDA(c, c->s.ensure((size_t)np * 8));
+  KGP_CUDA(c, c->mu.ensure(64 * 8));
+  KGP_CUDA(c, c->inv_ell.ensure(64 * 8));
+  KGP_CUDA(c, c->fac.ensure(64 * 8));
+  KGP_CUDA(c, c->hypm.ensure(128 * 8));
+  KGP_CUDA(c, c->ym.ensure((size_t)np * 8));
+  KGP_CUDA(c, c->alpha.ensure((size_t)np * 8));
+  KGP_CUDA(c, c->tvec.ensure((size_t)np * 8));
+  KGP_CUDA(c, c->scal.ensure(256 * 8));
+  KGP_CUDA(c, c->rows.ensure((size_t)np * (Dp + 3) * 8));
+  KGP_CUDA(c, c->dX.ensure((size_t)n * D * 8));
+  if (!c->d_info) KGP_CUDA(c, cudaMalloc(&c->d_info, sizeof(int)));
+  return KGP_OK;
+}
+
+static float ev_ms(cudaEvent_t a, cudaEvent_t b) { float ms = 0; cudaEventElapsedTime(&ms, a, b); return ms; }
+
+// ---------------------------------------------------------------------------
+int exact_eval(kgp_ctx* c, int slot, int want, double* nlZ_out, double* dnlZ_out) {
+  Slot& S = c->slots[slot]; Model& m = c->model;
+  const long n = S.n; const int D = S.D;
+  if (D > 32) return c->fail(KGP_BAD_ARG, "exact path supports input_dim <= 32 (got %d)", D);
+  const bool ard = m.cov_kind == KGP_COV_SEARD;
+  const int nl = ard ? D : 1;
+  if ((int)m.hyp_cov.size() != nl + 1) return c->fail(KGP_BAD_ARG, "Wrong number of hyperparameters (cov): got %d, need %d", (int)m.hyp_cov.size(), nl + 1);
+  const int nmean = ((m.mean_mask & 1) ? D : 0) + ((m.mean_mask & 2) ? 1 : 0);
+  if ((int)m.hyp_mean.size() != nmean) return c->fail(KGP_BAD_ARG, "Number of mean function hyperparameters disagree with mean function");
+  int rc = ensure_exact_buffers(c, n, D); if (rc) return rc;
+  const long np = c->np; const int Dp = c->Dp;
+  cudaStream_t st = c->stream;
+  memset(&c->stats, 0, sizeof c->stats); c->stats.n = n; c->stats.np = np;
+  c->st_level = -1;
+
+  const double sn2 = exp(2.0 * m.hyp_lik), sf2 = exp(2.0 * m.hyp_cov[nl]);
+  double h_inv_ell[64], h_fac[64];
+  for (int d = 0; d < D; ++d) {
+    double ell = exp(m.hyp_cov[ard ? d : 0]);
+    h_inv_ell[d] = 1.0 / ell;
+    h_fac[d] = (ard && m.opt.ard_reference_form) ? ell / exp(2.0 * m.hyp_cov[0]) : 1.0 / ell;
+  }
+  KGP_CUDA(c, cudaMemcpyAsync(c->inv_ell.p, h_inv_ell, D * 8, cudaMemcpyHostToDevice, st));
+  KGP_CUDA(c, cudaMemcpyAsync(c->fac.p, h_fac, D * 8, cudaMemcpyHostToDevice, st));
+  if (nmean) KGP_CUDA(c, cudaMemcpyAsync(c->hypm.p, m.hyp_mean.data(), nmean * 8, cudaMemcpyHostToDevice, st));
+  int big = 1 << 30;
+  KGP_CUDA(c, cudaMemcpyAsync(c->d_info, &big, sizeof(int), cudaMemcpyHostToDevice, st));
+
+  cudaEventRecord(c->ev[0], st);
+  col_mean_kernel<<<D, 1024, 0, st>>>(S.X.d(), n, D, c->mu.d());
+  scale_x_kernel<<<(unsigned)((np + 255) / 256), 256, 0, st>>>(S.X.d(), n, D, c->mu.d(), c->inv_ell.d(), c->xs.d(), c->s.d(), np, Dp);
+  resid_mean_kernel<<<(unsigned)((np + 255) / 256), 256, 0, st>>>(S.X.d(), S.has_y ? S.y.d() : nullptr, n, D, m.mean_mask, c->hypm.d(), c->ym.d(), np);
+  {
+    dim3 grid((unsigned)(np / 128), (unsigned)(np / 128));
+    kbuild_kernel<<<grid, KB_THREADS, kbuild_smem(Dp), st>>>(c->xs.d(), c->s.d(), n, c->xs.d(), c->s.d(), n, Dp,
+                                                            sf2 / sn2, 1, 1, c->M.d(), np);
+  }
+  c->stats.kernel_launches += 4;
+  cudaEventRecord(c->ev[1], st);
+  potrf(c);
+  logdet_kernel<<<1, 1024, 0, st>>>(c->M.d(), np, n, c->scal.d() + 100);
+  c->stats.kernel_launches++;
+  cudaEventRecord(c->ev[2], st);
+  zsweep(c);
+  cudaEventRecord(c->ev[3], st);
+  {  // alpha = B^{-1} ym / sn2 = Z (Z^T ym) / sn2
+    const int nch = (int)((np + 511) / 512);
+    KGP_CUDA(c, c->parts.ensure((size_t)nch * np * 8));
+    dim3 grid((unsigned)(np / 128), (unsigned)nch);
+    gemv_t_upper_kernel<<<grid, 128, 0, st>>>(c->W2.d(), np, np, c->ym.d(), c->parts.d());
+    sum_parts_kernel<<<(unsigned)((np + 255) / 256), 256, 0, st>>>(c->parts.d(), np, nch, 1.0, c->tvec.d());
+    gemv_n_upper_kernel<<<(unsigned)((np + 7) / 8), 256, 0, st>>>(c->W2.d(), np, np, c->tvec.d(), 1.0 / sn2, c->alpha.d());
+    dot_kernel<<<1, 1024, 0, st>>>(c->ym.d(), c->alpha.d(), n, c->scal.d() + 101);
+    c->stats.kernel_launches += 4;
+  }
+  cudaEventRecord(c->ev[4], st);
+  int nsc = 0;
+  if (want >= 1) {
+    zzt(c);
+    cudaEventRecord(c->ev[5], st);
+    const int ntr = (int)(np / 128), nt32 = (int)(np / 32);
+    int nsplit = (1184 + ntr - 1) / ntr; if (nsplit < 1) nsplit = 1; if (nsplit > nt32) nsplit = nt32;
+    const int per = (nt32 + nsplit - 1) / nsplit; nsplit = (nt32 + per - 1) / per;
+    KGP_CUDA(c, c->parts.ensure((size_t)nsplit * np * (Dp + 3) * 8));
+    switch (Dp) {
+      case 4: launch_reduce<4>(c, n, sf2, 1.0 / sn2, nsplit, per); break;
+      case 8: launch_reduce<8>(c, n, sf2, 1.0 / sn2, nsplit, per); break;
+      case 16: launch_reduce<16>(c, n, sf2, 1.0 / sn2, nsplit, per); break;
+      default: launch_reduce<32>(c, n, sf2, 1.0 / sn2, nsplit, per); break;
+    }
+    const long tot = np * (Dp + 3);
+    reduce_rows_kernel<<<(unsigned)((tot + 255) / 256), 256, 0, st>>>(c->parts.d(), np, nsplit, Dp + 3, c->rows.d());
+    grad_scalars_kernel<<<1, 1024, 0, st>>>(c->rows.d(), n, Dp, c->xs.d(), c->alpha.d(), c->scal.d());
+    dx_from_rows_kernel<<<(unsigned)((n * D + 255) / 256), 256, 0, st>>>(c->rows.d(), n, D, Dp, c->fac.d(), c->dX.d());
+    if (nmean) mean_grad_kernel<<<D + 1, 1024, 0, st>>>(S.X.d(), c->alpha.d(), n, D, c->scal.d() + 110);
+    c->stats.kernel_launches += 4 + (nmean ? 1 : 0);
+    nsc = 4 + Dp;
+    cudaEventRecord(c->ev[6], st);
+  }
+  double h[256];
+  KGP_CUDA(c, cudaMemcpyAsync(h, c->scal.p, 256 * 8, cudaMemcpyDeviceToHost, st));
+  int info = 0;
+  KGP_CUDA(c, cudaMemcpyAsync(&info, c->d_info, sizeof(int), cudaMemcpyDeviceToHost, st));
+  cudaEventRecord(c->ev[7], st);
+  KGP_CUDA(c, cudaStreamSynchronize(st));
+  KGP_CUDA(c, cudaGetLastError());
+  c->stats.ms_kbuild = ev_ms(c->ev[0], c->ev[1]);
+  c->stats.ms_potrf = ev_ms(c->ev[1], c->ev[2]);
+  c->stats.ms_inverse = ev_ms(c->ev[2], c->ev[3]) + (want >= 1 ? ev_ms(c->ev[4], c->ev[5]) : 0.f);
+  c->stats.ms_solve = ev_ms(c->ev[3], c->ev[4]);
+  c->stats.ms_reduce = want >= 1 ? ev_ms(c->ev[5], c->ev[6]) : 0.f;
+  c->stats.ms_total = ev_ms(c->ev[0], c->ev[7]);
+  if (info != (1 << 30)) {
+    c->stats.potrf_info = info;
+    return c->fail(KGP_NOT_PD, "chol: input matrix must be positive definite (pivot %d)", info);
+  }
+  const double ldB2 = h[100], yta = h[101];
+  const double nlZ = yta / 2.0 + ldB2 + (double)n * log(2.0 * M_PI * sn2) / 2.0;     // infGaussLik.m:29
+  if (nlZ_out) *nlZ_out = nlZ;
+  c->st_nlZ = nlZ; c->st_dnlZ.clear();
+  if (want >= 1) {
+    (void)nsc;
+    std::vector<double> g;
+    if (ard) for (int d = 0; d < D; ++d) g.push_back(h[4 + d]);
+    else g.push_back(0.5 * h[1]);
+    g.push_back(h[0]);                                                     // d/d log sf
+    g.push_back(-sn2 * h[3] - h[2] / sn2 + (double)n);                     // infGaussLik.m:32
+    if (m.mean_mask & 1) for (int d = 0; d < D; ++d) g.push_back(h[110 + d]);
+    if (m.mean_mask & 2) g.push_back(h[110 + D]);
+    c->st_dnlZ = g;
+    if (dnlZ_out) memcpy(dnlZ_out, g.data(), g.size() * 8);
+  }
+  c->st_slot = slot; c->st_slot_ver = S.version; c->st_model_ver = m.version;
+  c->st_level = want >= 1 ? 2 : 0;
+  return KGP_OK;
+}
+
+static bool state_valid(kgp_ctx* c, int slot, int level) {
+  return c->st_level >= level && c->st_slot == slot && c->st_slot_ver == c->slots[slot].version &&
+         c->st_model_ver == c->model.version;
+}
+
+int exact_dlik(kgp_ctx* c, int slot, double* out, bool out_is_dev) {
+  if (!state_valid(c, slot, 2)) {
+    int rc = exact_eval(c, slot, 2, nullptr, nullptr);
+    if (rc) return rc;
+  }
+  Slot& S = c->slots[slot];
+  KGP_CUDA(c, cudaMemcpyAsync(out, c->dX.p, (size_t)S.n * S.D * 8,
+                              out_is_dev ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost, c->stream));
+  KGP_CUDA(c, cudaStreamSynchronize(c->stream));
+  return KGP_OK;
+}
+
+int exact_alpha(kgp_ctx* c, double* out) {
+  if (c->st_level < 0) return c->fail(KGP_NO_DATA, "no posterior computed yet");
+  KGP_CUDA(c, cudaMemcpy(out, c->alpha.p, (size_t)c->slots[c->st_slot].n * 8, cudaMemcpyDeviceToHost));
+  return KGP_OK;
+}
+
+// gp.m:128-181 for infExact: batches of <=1024 test points
+int exact_predict(kgp_ctx* c, const double* Xs, long ns, double* ymu, double* ys2, double* fmu, double* fs2) {
+  const int slot = KGP_SLOT_TR;
+  if (!state_valid(c, slot, 0)) {
+    int rc = exact_eval(c, slot, 0, nullptr, nullptr);
+    if (rc) return rc;
+  }
+  Slot& S = c->slots[slot]; Model& m = c->model;
+  const long n = S.n, np = c->np; const int D = S.D, Dp = c->Dp;
+  const bool ard = m.cov_kind == KGP_COV_SEARD; const int nl = ard ? D : 1;
+  const double sn2 = exp(2.0 * m.hyp_lik), sf2 = exp(2.0 * m.hyp_cov[nl]);
+  const bool want_var = ys2 || fs2;
+  cudaStream_t st = c->stream;
+  const long BATCH = 1024;
+  KGP_CUDA(c, c->pred_K.ensure((size_t)BATCH * np * 8));
+  KGP_CUDA(c, c->pred_X.ensure((size_t)BATCH * D * 8));
+  KGP_CUDA(c, c->pred_x.ensure((size_t)BATCH * Dp * 8));
+  KGP_CUDA(c, c->pred_s.ensure((size_t)BATCH * 8));
+  KGP_CUDA(c, c->pred_a.ensure((size_t)BATCH * 8));
+  KGP_CUDA(c, c->pred_b.ensure((size_t)BATCH * 8));
+  KGP_CUDA(c, c->pred_out.ensure((size_t)BATCH * 4 * 8));
+  std::vector<double> h(BATCH * 4);
+  for (long s0 = 0; s0 < ns; s0 += BATCH) {
+    const long nsb = (ns - s0 < BATCH) ? ns - s0 : BATCH, nsp = ((nsb + 127) / 128) * 128;
+    KGP_CUDA(c, cudaMemcpyAsync(c->pred_X.p, Xs + s0 * D, (size_t)nsb * D * 8, cudaMemcpyHostToDevice, st));
+    scale_x_kernel<<<(unsigned)((nsp + 255) / 256), 256, 0, st>>>(c->pred_X.d(), nsb, D, c->mu.d(), c->inv_ell.d(),
+                                                                  c->pred_x.d(), c->pred_s.d(), nsp, Dp);
+    dim3 grid((unsigned)(np / 128), (unsigned)(nsp / 128));
+    kbuild_kernel<<<grid, KB_THREADS, kbuild_smem(Dp), st>>>(c->pred_x.d(), c->pred_s.d(), nsb, c->xs.d(), c->s.d(), n,
+                                                            Dp, sf2, 0, 0, c->pred_K.d(), np);
+    gemv_rows_kernel<<<(unsigned)((nsp + 7) / 8), 256, 0, st>>>(c->pred_K.d(), np, nsp, np, c->alpha.d(), c->pred_a.d());
+    if (want_var) {
+      double* X = c->pred_K.d(); const double* M = c->M.d();
+      for (long k0 = 0; k0 < np; k0 += NB) {
+        const int w = (int)((np - k0 < NB) ? np - k0 : NB);
+        trsm_block(c, X + k0, np, nsp, M + k0 * np + k0, np, w);
+        const long rest = np - k0 - w;
+        if (rest > 0)
+          gemm(c, mkgemm(X + k0, np, M + (k0 + w) * np + k0, np, X + k0 + w, np, (int)(nsp / 128), (int)(rest / 128),
+                         0, w, GEMM_FULL, KTRI_NONE, -1.0, 1.0));
+      }
+      rowsumsq_kernel<<<(unsigned)((nsp + 7) / 8), 256, 0, st>>>(X, np, nsp, np, c->pred_b.d());
+      scale_matrix_kernel<<<(unsigned)((nsp + 255) / 256), 256, 0, st>>>(c->pred_b.d(), 1, nsp, 1, 1.0 / sn2);
+    }
+    double* o = c->pred_out.d();
+    predict_finish_kernel<<<(unsigned)((nsb + 255) / 256), 256, 0, st>>>(c->pred_X.d(), nsb, D, m.mean_mask, c->hypm.d(),
+        c->pred_a.d(), c->pred_b.d(), sf2, sn2, want_var ? 1 : 0, o, o + BATCH, o + 2 * BATCH, o + 3 * BATCH);
+    KGP_CUDA(c, cudaMemcpyAsync(h.data(), o, (size_t)BATCH * 4 * 8, cudaMemcpyDeviceToHost, st));
+    KGP_CUDA(c, cudaStreamSynchronize(st));
+    KGP_CUDA(c, cudaGetLastError());
+    if (ymu) memcpy(ymu + s0, h.data(), nsb * 8);
+    if (ys2) memcpy(ys2 + s0, h.data() + BATCH, nsb * 8);
+    if (fmu) memcpy(fmu + s0, h.data() + 2 * BATCH, nsb * 8);
+    if (fs2) memcpy(fs2 + s0, h.data() + 3 * BATCH, nsb * 8);
+  }
+  return KGP_OK;
+}
+
+int exact_init(kgp_ctx* c) {
+  KGP_CUDA(c, gemm_init());
+  KGP_CUDA(c, cudaFuncSetAttribute(potrf_diag128_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, PD_SMEM));
+  KGP_CUDA(c, cudaFuncSetAttribute(trsm128_rows_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, TR_SMEM));
+  KGP_CUDA(c, cudaFuncSetAttribute(kbuild_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kbuild_smem(32)));
+  return KGP_OK;
+}
+
+}  // namespace kgp

@@ -1,0 +1,254 @@
+// Device kernels of the exact-GP path (infExact).  Reference arithmetic being
+// reproduced: GPML/cov/covMaha.m:125-154 (centred squared distances, clamp),
+// covSE.m:23 / covScale.m:74 (K = sf^2 exp(-D2/2)), GPML/cov/apx.m:160-166
+// (chol, log-det, inverse), GPML/inf/infGaussLik.m:25-32 (alpha, nlZ, dnlZ),
+// kgp/backend/utils/dlikExact.m:19-25 (input gradient), GPML/gp.m:151-164 (predict).
+#pragma once
+#include "dgemm_nt.cuh"
+#include <math.h>
+
+namespace kgp {
+
+// ---------------------------------------------------------------------------
+// small deterministic reductions
+// ---------------------------------------------------------------------------
+__device__ __forceinline__ double warp_sum(double v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+// block-wide sum, result valid in thread 0 (and broadcast through smem to all)
+__device__ __forceinline__ double block_sum(double v, double* sh /* >= 32 doubles */) {
+  int lane = threadIdx.x & 31, w = threadIdx.x >> 5, nw = (blockDim.x + 31) >> 5;
+  v = warp_sum(v);
+  __syncthreads();
+  if (lane == 0) sh[w] = v;
+  __syncthreads();
+  double r = 0.0;
+  if (w == 0) {
+    r = lane < nw ? sh[lane] : 0.0;
+    r = warp_sum(r);
+    if (lane == 0) sh[0] = r;
+  }
+  __syncthreads();
+  return sh[0];
+}
+
+// column means of X (n x D): one CTA per column   [covMaha.m:138 mu = mean(x,1)]
+__global__ void col_mean_kernel(const double* __restrict__ X, long n, int D, double* __restrict__ mu) {
+  __shared__ double sh[32];
+  int d = blockIdx.x;
+  double a = 0.0;
+  for (long i = threadIdx.x; i < n; i += blockDim.x) a += X[i * D + d];
+  double t = block_sum(a, sh);
+  if (threadIdx.x == 0) mu[d] = t / (double)n;
+}
+
+// xs[i][d] = (x[i][d]-mu[d]) * inv_ell[d]  (zero padded to np x Dp);  s[i] = sum_d xs^2
+__global__ void scale_x_kernel(const double* __restrict__ X, long n, int D, const double* __restrict__ mu,
+                               const double* __restrict__ inv_ell, double* __restrict__ xs,
+                               double* __restrict__ s, long np, int Dp) {
+  long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= np) return;
+  double acc = 0.0;
+  for (int d = 0; d < Dp; ++d) {
+    double v = 0.0;
+    if (i < n && d < D) v = (X[i * D + d] - mu[d]) * inv_ell[d];
+    xs[i * Dp + d] = v;
+    acc += v * v;
+  }
+  s[i] = acc;
+}
+
+// ym = y - m(x), m = meanSum{meanLinear, meanConst} selected by mask  (meanSum.m:13-37)
+__global__ void resid_mean_kernel(const double* __restrict__ X, const double* __restrict__ y, long n, int D,
+                                  int mean_mask, const double* __restrict__ hyp_mean, double* __restrict__ ym,
+                                  long np) {
+  long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= np) return;
+  if (i >= n) { ym[i] = 0.0; return; }
+  double m = 0.0; int o = 0;
+  if (mean_mask & 1) { for (int d = 0; d < D; ++d) m += X[i * D + d] * hyp_mean[d]; o = D; }
+  if (mean_mask & 2) m += hyp_mean[o];
+  ym[i] = (y ? y[i] : 0.0) - m;
+}
+
+// ---------------------------------------------------------------------------
+// kernel-matrix tiles:  out[i][j] = scale*exp(-max(s_i+s_j-2 xs_i.xs_j,0)/2) (+1 on the diagonal)
+// rows/cols beyond nR/nC (padding) give the identity pattern.  The Gram part runs
+// on the FP64 tensor pipe (DMMA.8x8x4 over Dp/4 k-steps).
+// ---------------------------------------------------------------------------
+constexpr int KB_THREADS = 256;
+__global__ void __launch_bounds__(KB_THREADS) kbuild_kernel(
+    const double* __restrict__ xr, const double* __restrict__ sr, long nR,
+    const double* __restrict__ xc, const double* __restrict__ sc, long nC,
+    int Dp, double scale, int diag_add, int lower_only, double* __restrict__ out, long ld) {
+  const int tn = blockIdx.x, tm = blockIdx.y;
+  if (lower_only && tn > tm) return;
+  extern __shared__ __align__(16) double sm[];
+  const int ldx = ((Dp + 11) / 16) * 16 + 4;          // ldx % 16 == 4 -> conflict-free LDS.64 fragments
+  double* sxr = sm; double* sxc = sm + 128 * ldx;
+  double* ssr = sxc + 128 * ldx; double* ssc = ssr + 128;
+  const long i0 = (long)tm * 128, j0 = (long)tn * 128;
+  for (int q = threadIdx.x; q < 128 * Dp; q += KB_THREADS) {
+    int r = q / Dp, d = q % Dp;
+    sxr[r * ldx + d] = xr[(i0 + r) * Dp + d];
+    sxc[r * ldx + d] = xc[(j0 + r) * Dp + d];
+  }
+  if (threadIdx.x < 128) ssr[threadIdx.x] = sr[i0 + threadIdx.x];
+  else ssc[threadIdx.x - 128] = sc[j0 + threadIdx.x - 128];
+  __syncthreads();
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, gq = lane >> 2, tq = lane & 3;
+  double acc[2][16][2];
+#pragma unroll
+  for (int a = 0; a < 2; ++a)
+#pragma unroll
+    for (int b = 0; b < 16; ++b) acc[a][b][0] = acc[a][b][1] = 0.0;
+  for (int k = 0; k < Dp; k += 4) {
+    double af[2];
+#pragma unroll
+    for (int a = 0; a < 2; ++a) af[a] = sxr[(warp * 16 + a * 8 + gq) * ldx + k + tq];
+#pragma unroll
+    for (int b = 0; b < 16; ++b) {
+      double bf = sxc[(b * 8 + gq) * ldx + k + tq];
+#pragma unroll
+      for (int a = 0; a < 2; ++a) dmma884(acc[a][b][0], acc[a][b][1], af[a], bf);
+    }
+  }
+#pragma unroll
+  for (int a = 0; a < 2; ++a) {
+    int rl = warp * 16 + a * 8 + gq;
+    long gi = i0 + rl;
+    double si = ssr[rl];
+#pragma unroll
+    for (int b = 0; b < 16; ++b) {
+      double2 v;
+#pragma unroll
+      for (int h = 0; h < 2; ++h) {
+        int cl = b * 8 + tq * 2 + h;
+        long gj = j0 + cl;
+        double val;
+        if (gi < nR && gj < nC) {
+          double d2 = fmax(si + ssc[cl] - 2.0 * acc[a][b][h], 0.0);     // covMaha.m:150
+          val = scale * exp(-0.5 * d2);
+        } else val = 0.0;
+        if (diag_add && gi == gj) val += 1.0;
+        if (h == 0) v.x = val; else v.y = val;
+      }
+      *reinterpret_cast<double2*>(out + gi * ld + j0 + b * 8 + tq * 2) = v;
+    }
+  }
+}
+inline size_t kbuild_smem(int Dp) { int ldx = ((Dp + 11) / 16) * 16 + 4; return (size_t)(2 * 128 * ldx + 256) * 8; }
+
+// ---------------------------------------------------------------------------
+// Cholesky of one 128x128 diagonal block in shared memory (lower, row-major).
+// info: 1-based global index of the first non-positive pivot (atomicMin), else unchanged.
+// ---------------------------------------------------------------------------
+constexpr int PD_THREADS = 512;
+constexpr int PD_LD = 129;
+constexpr int PD_SMEM = 128 * PD_LD * 8;
+__global__ void __launch_bounds__(PD_THREADS) potrf_diag128_kernel(double* __restrict__ A, long ld, int j0, int* info) {
+  extern __shared__ __align__(16) double a[];
+  const int tid = threadIdx.x;
+  for (int q = tid; q < 128 * 128; q += PD_THREADS) {
+    int r = q >> 7, c = q & 127;
+    a[r * PD_LD + c] = A[(long)r * ld + c];
+  }
+  for (int k = 0; k < 128; ++k) {
+    __syncthreads();
+    double d = a[k * PD_LD + k];
+    if (!(d > 0.0)) {
+      if (tid == 0) atomicMin(info, j0 + k + 1);
+      d = nan("");
+    }
+    double dk = sqrt(d);
+    for (int i = k + 1 + tid; i < 128; i += PD_THREADS) a[i * PD_LD + k] = a[i * PD_LD + k] / dk;
+    __syncthreads();
+    if (tid == 0) a[k * PD_LD + k] = dk;
+    const int m = 127 - k;
+    for (int q = tid; q < m * m; q += PD_THREADS) {
+      int i = k + 1 + q / m, j = k + 1 + q % m;
+      if (j <= i) a[i * PD_LD + j] -= a[i * PD_LD + k] * a[j * PD_LD + k];
+    }
+  }
+  __syncthreads();
+  for (int q = tid; q < 128 * 128; q += PD_THREADS) {
+    int r = q >> 7, c = q & 127;
+    if (c <= r) A[(long)r * ld + c] = a[r * PD_LD + c];
+  }
+}
+
+// ---------------------------------------------------------------------------
+// X <- X * L^{-T} for a 128x128 lower-triangular L (true forward substitution per
+// row; never an explicit inverse).  One warp owns 8 rows; the row values live in
+// the DMMA C-fragment layout so that solved micro-blocks feed later DMMA updates
+// straight from registers (k-permutation: step h uses columns 2t+h).
+// ---------------------------------------------------------------------------
+constexpr int TR_THREADS = 512;                 // 16 warps x 8 rows = 128 rows per CTA
+constexpr int TR_LDL = 136;                     // % 16 == 8 -> conflict-free LDS.128 B fragments
+constexpr int TR_SMEM = 128 * TR_LDL * 8;
+__global__ void __launch_bounds__(TR_THREADS, 1) trsm128_rows_kernel(
+    double* __restrict__ X, long ldx, long nrows, const double* __restrict__ L, long ldl) {
+  extern __shared__ __align__(16) double Ls[];
+  for (int q = threadIdx.x; q < 128 * 64; q += TR_THREADS) {
+    int r = q >> 6, c2 = (q & 63) * 2;
+    double2 v = make_double2(0.0, 0.0);
+    if (c2 <= r) v = *reinterpret_cast<const double2*>(L + (long)r * ldl + c2);
+    *reinterpret_cast<double2*>(Ls + r * TR_LDL + c2) = v;
+  }
+  __syncthreads();
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, gq = lane >> 2, tq = lane & 3;
+  const long row = (long)blockIdx.x * 128 + warp * 8 + gq;
+  if ((long)blockIdx.x * 128 + warp * 8 >= nrows) return;
+  double* xp = X + row * ldx + tq * 2;
+  double x[16][2];
+#pragma unroll
+  for (int cb = 0; cb < 16; ++cb) {
+    double2 v = *reinterpret_cast<const double2*>(xp + cb * 8);
+    x[cb][0] = v.x; x[cb][1] = v.y;
+  }
+#pragma unroll
+  for (int cb = 0; cb < 16; ++cb) {
+    double c0 = x[cb][0], c1 = x[cb][1];
+#pragma unroll
+    for (int p = 0; p < cb; ++p) {
+      double2 l = *reinterpret_cast<const double2*>(Ls + (cb * 8 + gq) * TR_LDL + p * 8 + tq * 2);
+      dmma884(c0, c1, -x[p][0], l.x);
+      dmma884(c0, c1, -x[p][1], l.y);
+    }
+    const double* Ld = Ls + (cb * 8) * TR_LDL + cb * 8;
+#pragma unroll
+    for (int c = 0; c < 8; ++c) {
+      double v = __shfl_sync(0xffffffffu, (c & 1) ? c1 : c0, (lane & ~3) | (c >> 1));
+      double xc = v / Ld[c * TR_LDL + c];
+      if (2 * tq > c) c0 -= xc * Ld[(2 * tq) * TR_LDL + c];
+      if (2 * tq + 1 > c) c1 -= xc * Ld[(2 * tq + 1) * TR_LDL + c];
+      if (2 * tq == c) c0 = xc;
+      if (2 * tq + 1 == c) c1 = xc;
+    }
+    x[cb][0] = c0; x[cb][1] = c1;
+  }
+#pragma unroll
+  for (int cb = 0; cb < 16; ++cb)
+    *reinterpret_cast<double2*>(xp + cb * 8) = make_double2(x[cb][0], x[cb][1]);
+}
+
+// w x w block <- identity
+__global__ void set_identity_kernel(double* __restrict__ A, long ld, int w) {
+  long q = (long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (q >= (long)w * w) return;
+  int r = (int)(q / w), c = (int)(q % w);
+  A[(long)r * ld + c] = (r == c) ? 1.0 : 0.0;
+}
+
+// sum_i log(L_ii), i < n  (apx.m:161); single CTA, deterministic
+__global__ void logdet_kernel(const double* __restrict__ L, long ld, long n, double* __restrict__ out) {
+  __shared__ double sh[32];
+  double a = 0.0;
+  for (long i = threadIdx.x; i < n; i += blockDim.x) a += log(L[i * ld + i]);
+  double t = block_sum(a, sh);
+  if (threadIdx.x == 0) out[0] = t;
+}
+
+}  // namespace kgp
