@@ -1,0 +1,257 @@
+#!/usr/bin/env python
+"""bench.py -- GP nlZ + full-gradient evaluations per second (BASELINE.json metric).
+
+A *step* is one pass of the hot path over one synthetic batch: one exact-GP
+evaluation [nlZ, dnlZ] plus dnlZ/dX -- what `train` + `get_dlik_dx` consume per
+function evaluation.  Workload at N=1: BASELINE.json configs[1],
+"mlp_kin40k" scale-up: exact GP, covSEard, n=40 000, d=8, FP64, on one B200.
+
+  python bench.py [--gpus N --steps K --warmup W] [--n 40000]      # this engine
+  python bench.py --impl reference ...                             # CPU arm (oracle port)
+
+N>1 (torchrun): the exact path is not yet sharded across GPUs in this round; every
+rank runs an independent GP of the same size (one GP per output, the way the
+reference runs one Octave process per GP layer, kgp/layers.py:63) -> weak scaling.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+import numpy as np
+
+
+def synth_c2(n, D=8, seed=43):
+    """kin40k-shaped synthetic inputs, standardised targets."""
+    rng = np.random.RandomState(seed)
+    X = rng.randn(n, D)
+    y = np.sin(X[:, 0] * X[:, 1]) + X[:, 2] ** 2 - X[:, 3] + 0.5 * np.cos(X.sum(1))
+    y = (y - y.mean()) / y.std() + 0.1 * rng.randn(n)
+    hyp = {'cov': np.concatenate([np.log(2.0) * np.ones(D), [0.0]]), 'lik': float(np.log(0.1)), 'mean': np.zeros(0)}
+    return X, y, hyp
+
+
+class ClockSampler(threading.Thread):
+    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md recipe)."""
+    Q = ('clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,'
+         'clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,'
+         'clocks_event_reasons.sw_power_cap')
+
+    def __init__(self, gpu_index):
+        super().__init__(daemon=True)
+        self.gpu = gpu_index; self.samples = []; self.stop_flag = False
+
+    def run(self):
+        while not self.stop_flag:
+            try:
+                out = subprocess.check_output(['nvidia-smi', '-i', str(self.gpu), '--query-gpu=' + self.Q,
+                                               '--format=csv,noheader,nounits'], timeout=5).decode().strip()
+                self.samples.append([t.strip() for t in out.split(',')])
+            except Exception:
+                pass
+            time.sleep(0.2)
+
+    def summary(self):
+        if not self.samples:
+            return {'sm_mhz': None, 'sm_max_mhz': None, 'reasons': ['nvidia-smi unavailable']}
+        sm = sorted(float(s[0]) for s in self.samples)
+        names = ['hw_slowdown', 'hw_thermal_slowdown', 'sw_thermal_slowdown', 'sw_power_cap']
+        reasons = [nm for k, nm in enumerate(names) if any(s[3 + k].lower().startswith('active') for s in self.samples)]
+        return {'sm_mhz': sm[len(sm) // 2], 'sm_max_mhz': float(self.samples[0][1]),
+                'power_w_max': max(float(s[2]) for s in self.samples), 'reasons': reasons, 'samples': len(sm)}
+
+
+def cpu_eval_seconds(n_s, D=8, reps=1):
+    """Oracle (CPU FP64 restatement of the GPML path) on a bounded sample: one evaluation =
+    gp() [nlZ, dnlZ] + dlikExact (which re-runs the inference, dlikExact.m:14)."""
+    sys.path.insert(0, os.path.join(ROOT, 'oracle'))
+    import gpml_exact as orc
+    X, y, hyp = synth_c2(n_s, D)
+    best = float('inf')
+    for _ in range(reps):
+        t0 = time.perf_counter()
+        orc.inf_exact(hyp, ['meanZero'], 'ard', X, y, want_grad=True)
+        orc.dlik_exact(hyp, ['meanZero'], 'ard', X, y)
+        best = min(best, time.perf_counter() - t0)
+    return best
+
+
+def cpu_threads():
+    try:
+        from threadpoolctl import threadpool_info
+        return max([p.get('num_threads', 1) for p in threadpool_info()] + [1])
+    except Exception:
+        return os.cpu_count() or 1
+
+
+def run_reference(args, rank, world):
+    if rank != 0:
+        return
+    n, n_s = args.n, args.cpu_sample_n
+    for _ in range(args.warmup):
+        cpu_eval_seconds(n_s)
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        cpu_eval_seconds(n_s)
+    per = (time.perf_counter() - t0) / max(args.steps, 1)
+    scale = (n / float(n_s)) ** 3
+    val = 1.0 / (per * scale)
+    sample = ('one step = oracle gp()+dlikExact at n=%d (d=8, covSEard); evals/s at n=%d obtained by n^3 '
+              'extrapolation (x%.1f)' % (n_s, n, scale))
+    line = {'impl': 'reference', 'metric': 'gp_nlZ_grad_evals_per_sec', 'value': val, 'unit': 'evals/s',
+            'n_gpus': args.gpus, 'steps': args.steps, 'warmup': args.warmup, 'ms_per_step': per * scale * 1e3,
+            'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f64', 'data': 'synthetic',
+            'config': {'workload': 'exact GP covSEard infExact n=%d d=8 (BASELINE configs[1])' % n,
+                       'note': 'reference GPML/Octave unavailable on this box; CPU arm = NumPy/SciPy port (oracle/)'},
+            'cpu_baseline': {'value': val, 'unit': 'evals/s', 'cores': cpu_threads(), 'kind': 'port', 'sample': sample},
+            'e2e': {'value': val, 'unit': 'evals/s', 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0}}
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument('--gpus', type=int, default=1)
+    ap.add_argument('--steps', type=int, default=5)
+    ap.add_argument('--warmup', type=int, default=3)
+    ap.add_argument('--impl', default='b200')
+    ap.add_argument('--n', type=int, default=40000)
+    ap.add_argument('--cpu-sample-n', type=int, default=4096)
+    ap.add_argument('--no-cpu', action='store_true', help='skip the cpu_baseline leg')
+    args = ap.parse_args()
+    rank = int(os.environ.get('RANK', 0)); world = int(os.environ.get('WORLD_SIZE', 1))
+    local = int(os.environ.get('LOCAL_RANK', 0))
+
+    if args.impl == 'reference':
+        run_reference(args, rank, world)
+        return
+
+    import torch
+    import torch.distributed as dist
+    import __graft_entry__ as g
+    if not os.path.isfile(os.path.join(ROOT, 'kgp_b200', 'libkgp_b200.so')):
+        g.build()
+    from kgp_b200 import B200GP
+    if world > 1:
+        os.environ.setdefault('MASTER_ADDR', '127.0.0.1')
+        torch.cuda.set_device(local)
+        dist.init_process_group('nccl', device_id=torch.device('cuda', local))
+
+    n, D = args.n, 8
+    X, y, hyp = synth_c2(n, D, seed=43 + rank)
+    gp = B200GP(engine_kwargs={'device': local})
+    gp.configure(D, {'lik': hyp['lik'], 'mean': [], 'cov': hyp['cov'][:, None].copy()}, {}, 'infExact', 'meanZero',
+                 'covSEard', 'likGauss', 'dlikExact', verbose=0)
+    gp.update_data('tr', X, y[:, None])
+    eng = gp.eng
+    nh = D + 2
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- device-resident timing (value) -----------------------------------------------------
+    for _ in range(args.warmup):
+        eng.eval(0, 2, nh)
+    eng.set_profiling(True)
+    sampler = ClockSampler(local); sampler.start()
+    barrier()
+    dev_ms = 0.0; gemm_ms = 0.0; gemm_fl = 0.0; gemm_l = 0; launches = 0
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        nlZ, grad = eng.eval(0, 2, nh)                 # blocking; device time from CUDA events inside
+        st = eng.stats()
+        dev_ms += st['ms_total']; gemm_ms += st['ms_gemm']; gemm_fl += st['gemm_flops']
+        gemm_l += st['gemm_launches']; launches += st['kernel_launches']
+    barrier()
+    wall = time.perf_counter() - t0
+    sampler.stop_flag = True; sampler.join(timeout=3)
+    eng.set_profiling(False)
+    t = torch.tensor([dev_ms], dtype=torch.float64, device='cuda')
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    dev_ms_max = float(t.item())
+    ms_per_step = dev_ms_max / args.steps
+    value = world * 1e3 / ms_per_step
+
+    # ---- end to end through the public API with host buffers -------------------------------
+    Xh = torch.from_numpy(X).pin_memory().numpy(); yh = torch.from_numpy(y[:, None].copy()).pin_memory().numpy()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        gp.update_data('tr', Xh, yh)                  # H2D of this step's inputs
+        nl = gp.evaluate('tr')                        # nlZ (+ dnlZ, dX cached on device)
+        dX = gp.get_dlik_dx('tr')                     # D2H n x D
+    barrier()
+    e2e_s = time.perf_counter() - t0
+    t = torch.tensor([e2e_s], dtype=torch.float64, device='cuda')
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    e2e_val = world * args.steps / float(t.item())
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    # ---- roofline of the dominant kernel (dgemm_nt_kernel, FP64 DMMA) -----------------------
+    peak_tf = eng.bench_dmma_peak(20000)
+    try:
+        a = torch.randn(8192, 8192, dtype=torch.float64, device='cuda')
+        torch.matmul(a, a); torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(True), torch.cuda.Event(True)
+        e0.record(); torch.matmul(a, a); torch.matmul(a, a); e1.record(); torch.cuda.synchronize()
+        cublas_tf = 2 * 2 * 8192.0 ** 3 / (e0.elapsed_time(e1) * 1e-3) / 1e12
+        del a
+    except Exception:
+        cublas_tf = None
+    achieved = gemm_fl / (gemm_ms * 1e-3) / 1e12 if gemm_ms > 0 else None
+    traffic = None
+    tp = os.path.join(ROOT, 'profiles', 'r01_dgemm_traffic.json')
+    if os.path.isfile(tp):
+        try:
+            traffic = json.load(open(tp)).get('dram_bytes_per_launch')
+        except Exception:
+            traffic = None
+    roofline = {'bound': 'tensor', 'kernel': 'dgemm_nt_kernel (FP64 DMMA.8x8x4)', 'achieved': achieved, 'peak': peak_tf,
+                'unit': 'TFLOP/s', 'frac': (achieved / peak_tf) if achieved else None, 'traffic': traffic,
+                'peak_source': 'FP64 DMMA issue-rate microbenchmark run in this process (MEASURED_PEAKS.json has no FP64 entry)',
+                'cublas_dgemm_8192_tflops': cublas_tf,
+                'flops_per_launch': gemm_fl / max(gemm_l, 1), 'ms_per_launch': gemm_ms / max(gemm_l, 1),
+                'launches_per_step': gemm_l / args.steps, 'share_of_step': gemm_ms / dev_ms if dev_ms else None,
+                'whole_eval_tflops': gemm_fl / (dev_ms * 1e-3) / 1e12}
+
+    cpu = None
+    if not args.no_cpu:
+        n_s = args.cpu_sample_n
+        sec = cpu_eval_seconds(n_s)
+        scale = (n / float(n_s)) ** 3
+        cpu = {'value': 1.0 / (sec * scale), 'unit': 'evals/s', 'cores': cpu_threads(), 'kind': 'port',
+               'sample': 'oracle gp()+dlikExact once at n=%d: %.2f s; n^3-extrapolated x%.1f to n=%d' % (n_s, sec, scale, n)}
+
+    line = {'metric': 'gp_nlZ_grad_evals_per_sec', 'value': value, 'unit': 'evals/s', 'n_gpus': world,
+            'steps': args.steps, 'warmup': args.warmup, 'ms_per_step': ms_per_step, 'higher_is_better': True,
+            'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f64', 'data': 'synthetic',
+            'config': {'workload': 'exact GP covSEard infExact n=%d d=%d (BASELINE configs[1] mlp_kin40k scale-up): '
+                                   'nlZ + dnlZ + dnlZ/dX per step' % (n, D),
+                       'l2': 'inputs larger than L2 (two %.1f GB matrices per step)' % (n * n * 8 / 1e9),
+                       'parallelism': 'one independent GP per GPU (no collective)' if world > 1 else 'single GPU',
+                       'wall_s_timed_region': wall},
+            'roofline': roofline, 'cpu_baseline': cpu,
+            'e2e': {'value': e2e_val, 'unit': 'evals/s', 'h2d_bytes_per_step': int(X.nbytes + y.nbytes),
+                    'd2h_bytes_per_step': int(n * D * 8 + 8)},
+            'gpu_launches': int(launches), 'clocks': sampler.summary(),
+            'parity_probe': {'nlZ': nlZ, 'nlZ_e2e': nl}}
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == '__main__':
+    main()

@@ -186,6 +186,9 @@ class Context(object):
             out.append(cat[o:o + lens[a]].copy()); o += lens[a]
         return out
 
+    def set_profiling(self, on):
+        self._chk(self._l.kgp_set_profiling(self._h, int(bool(on))))
+
     def stats(self):
         s = KgpStats()
         self._chk(self._l.kgp_last_stats(self._h, C.byref(s)))

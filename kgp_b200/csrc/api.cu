@@ -83,6 +83,7 @@ int kgp_ctx_destroy(kgp_ctx* c) {
   for (auto& s : c->slots) { s.X.release(); s.y.release(); }
   if (c->d_info) cudaFree(c->d_info);
   for (int i = 0; i < 16; ++i) cudaEventDestroy(c->ev[i]);
+  for (cudaEvent_t e : c->gev) cudaEventDestroy(e);
   cudaStreamDestroy(c->stream);
   delete c;
   return KGP_OK;

@@ -32,7 +32,21 @@ static inline void count_gemm(kgp_ctx* c, const GemmArgs& g) {
 static inline void gemm(kgp_ctx* c, const GemmArgs& g) {
   if (g.ntm <= 0 || g.ntn <= 0) return;
   count_gemm(c, g);
-  gemm_launch(g, c->stream);
+  if (c->profiling) {
+    if (c->gev_used + 2 > c->gev.size()) {
+      size_t old = c->gev.size(); c->gev.resize(old + 256);
+      for (size_t i = old; i < c->gev.size(); ++i) cudaEventCreate(&c->gev[i]);
+    }
+    cudaEventRecord(c->gev[c->gev_used], c->stream);
+    gemm_launch(g, c->stream);
+    cudaEventRecord(c->gev[c->gev_used + 1], c->stream);
+    c->gev_used += 2;
+  } else gemm_launch(g, c->stream);
+}
+static void gemm_prof_collect(kgp_ctx* c) {
+  double ms = 0.0;
+  for (size_t i = 0; i + 1 < c->gev_used; i += 2) { float t = 0; cudaEventElapsedTime(&t, c->gev[i], c->gev[i + 1]); ms += t; }
+  c->stats.ms_gemm = ms; c->gev_used = 0;
 }
 static inline GemmArgs mkgemm(const double* A, long lda, const double* B, long ldb, double* C, long ldc,
                               int ntm, int ntn, int kbeg, int kend, int shape, int ktri, double alpha, double beta) {
@@ -228,6 +242,7 @@ int exact_eval(kgp_ctx* c, int slot, int want, double* nlZ_out, double* dnlZ_out
   cudaEventRecord(c->ev[7], st);
   KGP_CUDA(c, cudaStreamSynchronize(st));
   KGP_CUDA(c, cudaGetLastError());
+  if (c->profiling) gemm_prof_collect(c);
   c->stats.ms_kbuild = ev_ms(c->ev[0], c->ev[1]);
   c->stats.ms_potrf = ev_ms(c->ev[1], c->ev[2]);
   c->stats.ms_inverse = ev_ms(c->ev[2], c->ev[3]) + (want >= 1 ? ev_ms(c->ev[4], c->ev[5]) : 0.f);
