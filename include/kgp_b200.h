@@ -119,7 +119,8 @@ int kgp_last_stats(kgp_ctx* ctx, kgp_stats* out);
 /* measurement helpers (bench.py): FP64 DMMA issue-rate micro-benchmark and a timed
  * dgemm_nt launch on synthetic operands; both return TFLOP/s. */
 int kgp_bench_dmma_peak(kgp_ctx* ctx, int iters, double* tflops);
-int kgp_bench_dgemm(kgp_ctx* ctx, int n, int k, int reps, double* tflops, double* ms);
+int kgp_bench_dgemm(kgp_ctx* ctx, int n, int k, int reps, double* tflops, double* ms);   /* C = A B^T */
+int kgp_bench_syrk (kgp_ctx* ctx, int n, int k, int reps, double* tflops, double* ms);   /* C -= A A^T, lower tiles */
 
 #ifdef __cplusplus
 }

@@ -67,6 +67,7 @@ SIGNATURES = {
     'kgp_last_stats': (C.c_int, [C.c_void_p, C.POINTER(KgpStats)]),
     'kgp_bench_dmma_peak': (C.c_int, [C.c_void_p, C.c_int, _DP]),
     'kgp_bench_dgemm': (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, _DP, _DP]),
+    'kgp_bench_syrk': (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, _DP, _DP]),
 }
 
 
@@ -199,7 +200,7 @@ class Context(object):
         self._chk(self._l.kgp_bench_dmma_peak(self._h, iters, C.byref(t)))
         return t.value
 
-    def bench_dgemm(self, n=8192, k=8192, reps=3):
+    def bench_dgemm(self, n=8192, k=8192, reps=3, syrk=False):
         t = C.c_double(); ms = C.c_double()
-        self._chk(self._l.kgp_bench_dgemm(self._h, n, k, reps, C.byref(t), C.byref(ms)))
+        self._chk((self._l.kgp_bench_syrk if syrk else self._l.kgp_bench_dgemm)(self._h, n, k, reps, C.byref(t), C.byref(ms)))
         return t.value, ms.value

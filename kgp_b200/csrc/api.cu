@@ -226,16 +226,18 @@ int kgp_bench_dmma_peak(kgp_ctx* c, int iters, double* tflops) {
   return KGP_OK;
 }
 
-int kgp_bench_dgemm(kgp_ctx* c, int n, int k, int reps, double* tflops, double* ms_out) {
+static int bench_gemm_impl(kgp_ctx* c, int n, int k, int reps, int syrk, double* tflops, double* ms_out) {
   if (!c || n % 128 || k % 16 || n <= 0 || k <= 0) return c ? c->fail(KGP_BAD_ARG, "n%%128, k%%16 required") : KGP_BAD_ARG;
   cudaSetDevice(c->device);
   DevBuf A, B, C;
   KGP_CUDA(c, A.ensure((size_t)n * k * 8)); KGP_CUDA(c, B.ensure((size_t)n * k * 8)); KGP_CUDA(c, C.ensure((size_t)n * n * 8));
   fill_kernel<<<(unsigned)(((long)n * k + 255) / 256), 256, 0, c->stream>>>(A.d(), (long)n * k, 1.0);
   fill_kernel<<<(unsigned)(((long)n * k + 255) / 256), 256, 0, c->stream>>>(B.d(), (long)n * k, 0.5);
+  KGP_CUDA(c, cudaMemsetAsync(C.p, 0, (size_t)n * n * 8, c->stream));
   GemmArgs g; memset(&g, 0, sizeof g);
-  g.A = A.d(); g.lda = k; g.B = B.d(); g.ldb = k; g.C = C.d(); g.ldc = n; g.ntm = g.ntn = n / 128;
-  g.kbeg = 0; g.kend = k; g.shape = GEMM_FULL; g.ktri = KTRI_NONE; g.alpha = 1.0; g.beta = 0.0; g.nb = NB;
+  g.A = A.d(); g.lda = k; g.B = syrk ? A.d() : B.d(); g.ldb = k; g.C = C.d(); g.ldc = n; g.ntm = g.ntn = n / 128;
+  g.kbeg = 0; g.kend = k; g.shape = syrk ? GEMM_LOWER : GEMM_FULL; g.ktri = KTRI_NONE;
+  g.alpha = syrk ? -1.0 : 1.0; g.beta = syrk ? 1.0 : 0.0; g.nb = NB;
   gemm_launch(g, c->stream);
   cudaEventRecord(c->ev[8], c->stream);
   for (int r = 0; r < reps; ++r) gemm_launch(g, c->stream);
@@ -245,9 +247,17 @@ int kgp_bench_dgemm(kgp_ctx* c, int n, int k, int reps, double* tflops, double* 
   float ms = 0; cudaEventElapsedTime(&ms, c->ev[8], c->ev[9]);
   ms /= reps;
   if (ms_out) *ms_out = ms;
-  if (tflops) *tflops = 2.0 * n * (double)n * k / (ms * 1e-3) / 1e12;
+  double nt = (double)n / 128;
+  double tiles = syrk ? nt * (nt + 1) / 2 : nt * nt;
+  if (tflops) *tflops = 2.0 * 128 * 128 * tiles * k / (ms * 1e-3) / 1e12;
   A.release(); B.release(); C.release();
   return KGP_OK;
+}
+int kgp_bench_dgemm(kgp_ctx* c, int n, int k, int reps, double* tflops, double* ms_out) {
+  return bench_gemm_impl(c, n, k, reps, 0, tflops, ms_out);
+}
+int kgp_bench_syrk(kgp_ctx* c, int n, int k, int reps, double* tflops, double* ms_out) {
+  return bench_gemm_impl(c, n, k, reps, 1, tflops, ms_out);
 }
 
 }  // extern "C"

@@ -23,12 +23,14 @@
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <stdlib.h>
 
 namespace kgp {
 
 enum : int { GEMM_FULL = 0, GEMM_LOWER = 1 };
 enum : int { KTRI_NONE = 0, KTRI_FROM_M0 = 1 };
 
+constexpr int GEMM_MAX_BANDS = 160;     // 160 bands x 8 rows x 128 = order 163 840
 struct GemmArgs {
   const double* A; long lda;   // A[m][k], row m at A + m*lda
   const double* B; long ldb;   // B[n][k]
@@ -40,10 +42,18 @@ struct GemmArgs {
   double alpha, beta;
   // optional redirect of C tiles that fall in a diagonal nb x nb block (ZZ^T step):
   double* Cdiag; int nb;       // if Cdiag && (m0/nb == n0/nb): C tile -> Cdiag[blk][m0%nb.., n0%nb..], ld = nb
-  int cdiag_only;              // 1: only those tiles; -1: only the others; 0: all
+  int cdiag_only;              // (repurposed) 1: prefetch the C tile into L2 at tile start
+  int nbands; int band_base[GEMM_MAX_BANDS];   // LOWER shape: tile index at which each band of 8 tile-rows starts
 };
 
-constexpr int GEMM_BM = 128, GEMM_BN = 128, GEMM_BK = 16, GEMM_STAGES = 4;
+#ifndef KGP_GEMM_BK
+#define KGP_GEMM_BK 32
+#endif
+#ifndef KGP_GEMM_STAGES
+#define KGP_GEMM_STAGES 3
+#endif
+constexpr int GEMM_BM = 128, GEMM_BN = 128, GEMM_BK = KGP_GEMM_BK, GEMM_STAGES = KGP_GEMM_STAGES;
+constexpr int GEMM_KSTEPS = GEMM_BK / 4, GEMM_CHUNKS = GEMM_BK / 2;   // k4-steps / 16-byte chunks per row per stage
 constexpr int GEMM_THREADS = 256;
 constexpr int GEMM_STAGE_DOUBLES = (GEMM_BM + GEMM_BN) * GEMM_BK;           // 4096
 constexpr int GEMM_SMEM_BYTES = GEMM_STAGES * GEMM_STAGE_DOUBLES * 8;       // 131072
@@ -70,137 +80,225 @@ inline long gemm_num_tiles(const GemmArgs& g) {
   return t;
 }
 
+// Tile rasterisation: tiles are issued in bands of GEMM_BAND tile-rows, column-major inside a
+// band, so that the ~148 concurrently resident CTAs share a handful of A row-panels and walk the
+// B row-panels together (L2 working set ~ (8+19) panels instead of ~150).  Bands go top to
+// bottom, which also issues the longest tiles first when the K range is triangular.
+constexpr int GEMM_BAND = 8;
 __device__ __forceinline__ void gemm_tile_coords(const GemmArgs& g, long idx, int& tm, int& tn) {
-  if (g.shape == GEMM_FULL) { tm = (int)(idx / g.ntn); tn = (int)(idx % g.ntn); return; }
-  // rows tm < ntn hold tm+1 tiles, later rows hold ntn tiles
-  long tri = (long)g.ntn * (g.ntn + 1) / 2;
-  if (idx < tri) {
-    int r = (int)((sqrt(8.0 * (double)idx + 1.0) - 1.0) * 0.5);
-    while ((long)(r + 1) * (r + 2) / 2 <= idx) ++r;
-    while ((long)r * (r + 1) / 2 > idx) --r;
-    tm = r; tn = (int)(idx - (long)r * (r + 1) / 2);
-  } else {
-    long rem = idx - tri;
-    tm = g.ntn + (int)(rem / g.ntn); tn = (int)(rem % g.ntn);
+  if (g.shape == GEMM_FULL) {
+    const long per_band = (long)GEMM_BAND * g.ntn;
+    const int b = (int)(idx / per_band);
+    const long r = idx - (long)b * per_band;
+    const int rows = (g.ntm - b * GEMM_BAND < GEMM_BAND) ? g.ntm - b * GEMM_BAND : GEMM_BAND;
+    tn = (int)(r / rows); tm = b * GEMM_BAND + (int)(r % rows);
+    return;
   }
+  // LOWER: row tm holds min(tm+1, ntn) tiles; band_base[] (host-built) = tiles before each band
+  int lo = 0, hi = g.nbands - 1;
+  while (lo < hi) {                       // last band with band_base <= idx
+    int mid = (lo + hi + 1) >> 1;
+    if (g.band_base[mid] <= idx) lo = mid; else hi = mid - 1;
+  }
+  const int b = lo; const long base = g.band_base[b];
+  const int r0 = b * GEMM_BAND;
+  const int rows = (g.ntm - r0 < GEMM_BAND) ? g.ntm - r0 : GEMM_BAND;
+  long r = idx - base;
+  const int rect = (r0 < g.ntn) ? r0 : g.ntn;          // columns shared by every row of the band
+  if (r < (long)rect * rows) { tn = (int)(r / rows); tm = r0 + (int)(r % rows); return; }
+  r -= (long)rect * rows;
+  for (int c = rect; c < g.ntn; ++c) {                  // triangular part: column c holds rows >= c
+    const int first = (c > r0) ? c : r0;
+    const int cnt = r0 + rows - first;
+    if (cnt <= 0) break;
+    if (r < cnt) { tn = c; tm = first + (int)r; return; }
+    r -= cnt;
+  }
+  tm = r0; tn = 0;   // unreachable
 }
 
-__global__ void __launch_bounds__(GEMM_THREADS, 1) dgemm_nt_kernel(const GemmArgs g) {
-  extern __shared__ __align__(16) double smem[];
-  int tm, tn;
-  gemm_tile_coords(g, blockIdx.x, tm, tn);
-  const int m0 = tm * GEMM_BM, n0 = tn * GEMM_BN;
-
-  double* Cp = g.C; long ldc = g.ldc;
-  bool in_diag = false;
-  if (g.Cdiag) {
-    in_diag = (m0 / g.nb) == (n0 / g.nb);
-    if (g.cdiag_only == 1 && !in_diag) return;
-    if (g.cdiag_only == -1 && in_diag) return;
+// One work item of the persistent loop: tile coordinates, K range and operand pointers.
+struct GemmTile {
+  int m0, n0, nk; bool in_diag;
+  const double* Ag; const double* Bg;
+};
+__device__ __forceinline__ bool gemm_fetch_tile(const GemmArgs& g, long idx, long ntiles, GemmTile& t) {
+  for (; idx < ntiles; idx += gridDim.x) {     // (cdiag_only filters are not used with skipping here)
+    int tm, tn;
+    gemm_tile_coords(g, idx, tm, tn);
+    t.m0 = tm * GEMM_BM; t.n0 = tn * GEMM_BN;
+    t.in_diag = g.Cdiag && (t.m0 / g.nb) == (t.n0 / g.nb);
+    const int kbeg = g.kbeg + (g.ktri == KTRI_FROM_M0 ? t.m0 : 0);
+    t.nk = (g.kend - kbeg) / GEMM_BK;
+    t.Ag = g.A + (long)t.m0 * g.lda + kbeg;
+    t.Bg = g.B + (long)t.n0 * g.ldb + kbeg;
+    return true;
   }
+  return false;
+}
+
+// Persistent kernel: one CTA per SM walks tiles blockIdx.x, +gridDim.x, ...  The cp.async ring
+// runs ahead ACROSS tile boundaries (the load cursor is up to 3 k-steps ahead of the compute
+// cursor), so the pipeline fill of the next tile overlaps the epilogue of the current one.
+__global__ void __launch_bounds__(GEMM_THREADS, 1) dgemm_nt_kernel(const GemmArgs g, const long ntiles) {
+  extern __shared__ __align__(16) double smem[];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int wm = warp >> 2, wn = warp & 3;        // 2 x 4 warps
   const int gq = lane >> 2, tq = lane & 3;
 
-  int kbeg = g.kbeg + (g.ktri == KTRI_FROM_M0 ? m0 : 0);
-  const int nk = (g.kend - kbeg) / GEMM_BK;
-
-  double acc[8][4][2];
+  // --- load cursor
+  GemmTile lt; long lidx = blockIdx.x; int lkt = 0;
+  bool lvalid = gemm_fetch_tile(g, lidx, ntiles, lt);
+  auto load_next = [&](int stage) {
+    if (lvalid) {
+      double* sA = smem + stage * GEMM_STAGE_DOUBLES;
+      double* sB = sA + GEMM_BM * GEMM_BK;
+      const long koff = (long)lkt * GEMM_BK;
 #pragma unroll
-  for (int i = 0; i < 8; ++i)
-#pragma unroll
-    for (int j = 0; j < 4; ++j) acc[i][j][0] = acc[i][j][1] = 0.0;
-
-  // --- global->shared copy mapping: 1024 16-byte chunks per operand per stage, 4 per thread
-  const double* Ag = g.A + (long)m0 * g.lda + kbeg;
-  const double* Bg = g.B + (long)n0 * g.ldb + kbeg;
-  auto load_stage = [&](int stage, int kt) {
-    double* sA = smem + stage * GEMM_STAGE_DOUBLES;
-    double* sB = sA + GEMM_BM * GEMM_BK;
-    const long koff = (long)kt * GEMM_BK;
-#pragma unroll
-    for (int i = 0; i < 4; ++i) {
-      int q = tid + i * GEMM_THREADS;
-      int row = q >> 3, ch = q & 7;
-      int so = ((ch >> 2) * 128 + row) * 8 + (ch & 3) * 2;
-      cp_async16(sA + so, Ag + (long)row * g.lda + koff + ch * 2);
-      cp_async16(sB + so, Bg + (long)row * g.ldb + koff + ch * 2);
+      for (int i = 0; i < (GEMM_BM * GEMM_CHUNKS) / GEMM_THREADS; ++i) {
+        int q = tid + i * GEMM_THREADS;
+        int row = q / GEMM_CHUNKS, ch = q % GEMM_CHUNKS;
+        int so = ((ch >> 1) * 128 + row) * 4 + (ch & 1) * 2;     // [k4-step][row][4]
+        cp_async16(sA + so, lt.Ag + (long)row * g.lda + koff + ch * 2);
+        cp_async16(sB + so, lt.Bg + (long)row * g.ldb + koff + ch * 2);
+      }
+      if (++lkt == lt.nk) { lkt = 0; lidx += gridDim.x; lvalid = gemm_fetch_tile(g, lidx, ntiles, lt); }
     }
-  };
-
-#pragma unroll
-  for (int s = 0; s < GEMM_STAGES - 1; ++s) {
-    if (s < nk) load_stage(s, s);
     cp_async_commit();
-  }
+  };
+#pragma unroll
+  for (int s = 0; s < GEMM_STAGES - 1; ++s) load_next(s);
 
-  for (int kt = 0; kt < nk; ++kt) {
-    cp_async_wait<GEMM_STAGES - 2>();
-    __syncthreads();
-    {
-      int nxt = kt + GEMM_STAGES - 1;
-      if (nxt < nk) load_stage(nxt % GEMM_STAGES, nxt);
-      cp_async_commit();
-    }
-    const double* sA = smem + (kt % GEMM_STAGES) * GEMM_STAGE_DOUBLES;
+  // --- compute cursor.  Fragments are double-buffered in registers at k4-step granularity: the
+  // LDS.64 of step s+1 are issued before the 32 DMMAs of step s, and the block barrier sits before
+  // the LAST step of a stage (where the first fragments of the next stage are fetched), so the
+  // tensor pipe always has a full step of DMMAs queued while a warp waits.
+  double fa[2][8], fb[2][4];
+  auto lds = [&](int buf, const double* sA, int step) {
     const double* sB = sA + GEMM_BM * GEMM_BK;
 #pragma unroll
-    for (int slab = 0; slab < 2; ++slab) {
-      double2 af[8], bf[4];
+    for (int i = 0; i < 8; ++i) fa[buf][i] = sA[(step * 128 + wm * 64 + i * 8 + gq) * 4 + tq];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) fb[buf][j] = sB[(step * 128 + wn * 32 + j * 8 + gq) * 4 + tq];
+  };
+  GemmTile ct; int it = 0;
+  cp_async_wait<GEMM_STAGES - 2>();
+  __syncthreads();
+  lds(0, smem, 0);
+  for (long cidx = blockIdx.x; gemm_fetch_tile(g, cidx, ntiles, ct); cidx += gridDim.x) {
+    double* Cp; long ldc; long crow0, ccol0;
+    if (ct.in_diag) {
+      int blk = ct.m0 / g.nb;
+      Cp = g.Cdiag + (long)blk * g.nb * g.nb; ldc = g.nb;
+      crow0 = ct.m0 - blk * g.nb; ccol0 = ct.n0 - blk * g.nb;
+    } else { Cp = g.C; ldc = g.ldc; crow0 = ct.m0; ccol0 = ct.n0; }
+    const double alpha = g.alpha, beta = g.beta;
+    const bool last_tile = cidx + gridDim.x >= ntiles;
+    if (beta != 0.0 && g.cdiag_only) {   // pull the C tile towards L2 while the main loop runs
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        int line = tid * 4 + i;
+        const double* pp = Cp + (crow0 + (line >> 3)) * ldc + ccol0 + (line & 7) * 16;
+        asm volatile("prefetch.global.L2 [%0];" ::"l"(pp));
+      }
+    }
+    double acc[8][4][2];
+#pragma unroll
+    for (int i = 0; i < 8; ++i)
+#pragma unroll
+      for (int j = 0; j < 4; ++j) acc[i][j][0] = acc[i][j][1] = 0.0;
+
+    for (int kt = 0; kt < ct.nk; ++kt, ++it) {
+      const double* sA = smem + (it % GEMM_STAGES) * GEMM_STAGE_DOUBLES;
+#pragma unroll
+      for (int step = 0; step < GEMM_KSTEPS; ++step) {
+        const int cur = step & 1;
+        if (step < GEMM_KSTEPS - 1) {
+          lds(cur ^ 1, sA, step + 1);
+#pragma unroll
+          for (int i = 0; i < 8; ++i)
+#pragma unroll
+            for (int j = 0; j < 4; ++j) dmma884(acc[i][j][0], acc[i][j][1], fa[cur][i], fb[cur][j]);
+        } else {
+          // stage boundary: barrier, then half of this step's DMMAs are issued BEFORE the cp.async /
+          // LDS bookkeeping so the tensor pipe has work queued while the warp does address math
+          cp_async_wait<GEMM_STAGES - 3>();
+          __syncthreads();
+#pragma unroll
+          for (int i = 0; i < 4; ++i)
+#pragma unroll
+            for (int j = 0; j < 4; ++j) dmma884(acc[i][j][0], acc[i][j][1], fa[cur][i], fb[cur][j]);
+          load_next((it + GEMM_STAGES - 1) % GEMM_STAGES);
+          if (!(last_tile && kt + 1 == ct.nk))
+            lds(cur ^ 1, smem + ((it + 1) % GEMM_STAGES) * GEMM_STAGE_DOUBLES, 0);
+#pragma unroll
+          for (int i = 4; i < 8; ++i)
+#pragma unroll
+            for (int j = 0; j < 4; ++j) dmma884(acc[i][j][0], acc[i][j][1], fa[cur][i], fb[cur][j]);
+        }
+      }
+    }
+
+    // --- epilogue (registers -> global; shared memory is not touched, the ring keeps filling)
+    double* cbase = Cp + (crow0 + wm * 64 + gq) * ldc + ccol0 + wn * 32 + tq * 2;
+    if (beta != 0.0) {
+      // read-modify-write: batch the loads (16 x 16 B in flight per thread) before any store, otherwise
+      // possible aliasing makes the compiler serialise 32 DRAM round trips per thread
+#pragma unroll
+      for (int ih = 0; ih < 2; ++ih) {
+        double2 cv[4][4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+#pragma unroll
+          for (int j = 0; j < 4; ++j)
+            cv[i][j] = __ldcg(reinterpret_cast<const double2*>(cbase + (long)(ih * 4 + i) * 8 * ldc + j * 8));
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            double2 v;
+            v.x = beta * cv[i][j].x + alpha * acc[ih * 4 + i][j][0];
+            v.y = beta * cv[i][j].y + alpha * acc[ih * 4 + i][j][1];
+            *reinterpret_cast<double2*>(cbase + (long)(ih * 4 + i) * 8 * ldc + j * 8) = v;
+          }
+      }
+    } else {
 #pragma unroll
       for (int i = 0; i < 8; ++i)
-        af[i] = *reinterpret_cast<const double2*>(sA + (slab * 128 + wm * 64 + i * 8 + gq) * 8 + tq * 2);
 #pragma unroll
-      for (int j = 0; j < 4; ++j)
-        bf[j] = *reinterpret_cast<const double2*>(sB + (slab * 128 + wn * 32 + j * 8 + gq) * 8 + tq * 2);
-#pragma unroll
-      for (int i = 0; i < 8; ++i)
-#pragma unroll
-        for (int j = 0; j < 4; ++j) dmma884(acc[i][j][0], acc[i][j][1], af[i].x, bf[j].x);
-#pragma unroll
-      for (int i = 0; i < 8; ++i)
-#pragma unroll
-        for (int j = 0; j < 4; ++j) dmma884(acc[i][j][0], acc[i][j][1], af[i].y, bf[j].y);
+        for (int j = 0; j < 4; ++j)
+          *reinterpret_cast<double2*>(cbase + (long)i * 8 * ldc + j * 8) =
+              make_double2(alpha * acc[i][j][0], alpha * acc[i][j][1]);
     }
   }
   cp_async_wait<0>();
-
-  // --- epilogue
-  long crow0, ccol0;
-  if (in_diag) {
-    int blk = m0 / g.nb;
-    Cp = g.Cdiag + (long)blk * g.nb * g.nb; ldc = g.nb;
-    crow0 = m0 - blk * g.nb; ccol0 = n0 - blk * g.nb;
-  } else { crow0 = m0; ccol0 = n0; }
-  const double alpha = g.alpha, beta = g.beta;
-#pragma unroll
-  for (int i = 0; i < 8; ++i) {
-    long r = crow0 + wm * 64 + i * 8 + gq;
-#pragma unroll
-    for (int j = 0; j < 4; ++j) {
-      long c = ccol0 + wn * 32 + j * 8 + tq * 2;
-      double2* p = reinterpret_cast<double2*>(Cp + r * ldc + c);
-      double2 v;
-      if (beta != 0.0) {
-        v = *p;
-        v.x = beta * v.x + alpha * acc[i][j][0];
-        v.y = beta * v.y + alpha * acc[i][j][1];
-      } else {
-        v.x = alpha * acc[i][j][0]; v.y = alpha * acc[i][j][1];
-      }
-      *p = v;
-    }
-  }
 }
 
+static int g_gemm_num_sms = 148;
+static int g_gemm_persist = 1, g_gemm_prefetch_c = 1;   // tuning knobs (env KGP_GEMM_PERSIST / KGP_GEMM_PREFETCHC)
 inline cudaError_t gemm_init() {
+  int dev = 0; cudaGetDevice(&dev);
+  cudaDeviceGetAttribute(&g_gemm_num_sms, cudaDevAttrMultiProcessorCount, dev);
+  if (const char* e = getenv("KGP_GEMM_PERSIST")) g_gemm_persist = atoi(e);
+  if (const char* e = getenv("KGP_GEMM_PREFETCHC")) g_gemm_prefetch_c = atoi(e);
   return cudaFuncSetAttribute(dgemm_nt_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, GEMM_SMEM_BYTES);
 }
 
-inline void gemm_launch(const GemmArgs& g, cudaStream_t st) {
+inline void gemm_launch(const GemmArgs& g_in, cudaStream_t st) {
+  GemmArgs g = g_in;
   long nt = gemm_num_tiles(g);
+  if (g.shape == GEMM_LOWER) {
+    long base = 0; int nb_ = 0;
+    for (int r0 = 0; r0 < g.ntm && nb_ < GEMM_MAX_BANDS; r0 += 8) {
+      g.band_base[nb_++] = (int)base;
+      for (int r = r0; r < r0 + 8 && r < g.ntm; ++r) base += (r + 1 < g.ntn) ? r + 1 : g.ntn;
+    }
+    g.nbands = nb_;
+  }
   if (nt <= 0 || g.kend <= g.kbeg) return;
-  dgemm_nt_kernel<<<(unsigned)nt, GEMM_THREADS, GEMM_SMEM_BYTES, st>>>(g);
+  long grid = (g_gemm_persist && nt > g_gemm_num_sms) ? g_gemm_num_sms : nt;
+  g.cdiag_only = g_gemm_prefetch_c;
+  dgemm_nt_kernel<<<(unsigned)grid, GEMM_THREADS, GEMM_SMEM_BYTES, st>>>(g, nt);
 }
 
 }  // namespace kgp
