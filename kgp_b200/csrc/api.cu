@@ -209,7 +209,10 @@ int kgp_bench_dmma_peak(kgp_ctx* c, int iters, double* tflops) {
   cudaSetDevice(c->device);
   cudaDeviceProp p; KGP_CUDA(c, cudaGetDeviceProperties(&p, c->device));
   KGP_CUDA(c, c->scal.ensure(256 * 8));
-  const int blocks = p.multiProcessorCount * 2, threads = 512;
+  int bps = 2, threads = 512;      // default: 32 warps per SM; env overrides are for occupancy experiments
+  if (const char* e = getenv("KGP_PEAK_BLOCKS_PER_SM")) bps = atoi(e);
+  if (const char* e = getenv("KGP_PEAK_THREADS")) threads = atoi(e);
+  const int blocks = p.multiProcessorCount * bps;
   dmma_peak_kernel<<<blocks, threads, 0, c->stream>>>(c->scal.d(), 16);
   double best = 0.0;
   for (int rep = 0; rep < 5; ++rep) {

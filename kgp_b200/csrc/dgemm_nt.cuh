@@ -47,10 +47,13 @@ struct GemmArgs {
 };
 
 #ifndef KGP_GEMM_BK
-#define KGP_GEMM_BK 32
+#define KGP_GEMM_BK 16
 #endif
 #ifndef KGP_GEMM_STAGES
-#define KGP_GEMM_STAGES 3
+#define KGP_GEMM_STAGES 4
+#endif
+#ifndef KGP_GEMM_SPLIT
+#define KGP_GEMM_SPLIT 1
 #endif
 constexpr int GEMM_BM = 128, GEMM_BN = 128, GEMM_BK = KGP_GEMM_BK, GEMM_STAGES = KGP_GEMM_STAGES;
 constexpr int GEMM_KSTEPS = GEMM_BK / 4, GEMM_CHUNKS = GEMM_BK / 2;   // k4-steps / 16-byte chunks per row per stage
@@ -224,15 +227,17 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) dgemm_nt_kernel(const GemmArg
           // LDS bookkeeping so the tensor pipe has work queued while the warp does address math
           cp_async_wait<GEMM_STAGES - 3>();
           __syncthreads();
+#if KGP_GEMM_SPLIT
 #pragma unroll
           for (int i = 0; i < 4; ++i)
 #pragma unroll
             for (int j = 0; j < 4; ++j) dmma884(acc[i][j][0], acc[i][j][1], fa[cur][i], fb[cur][j]);
+#endif
           load_next((it + GEMM_STAGES - 1) % GEMM_STAGES);
           if (!(last_tile && kt + 1 == ct.nk))
             lds(cur ^ 1, smem + ((it + 1) % GEMM_STAGES) * GEMM_STAGE_DOUBLES, 0);
 #pragma unroll
-          for (int i = 4; i < 8; ++i)
+          for (int i = (KGP_GEMM_SPLIT ? 4 : 0); i < 8; ++i)
 #pragma unroll
             for (int j = 0; j < 4; ++j) dmma884(acc[i][j][0], acc[i][j][1], fa[cur][i], fb[cur][j]);
         }
