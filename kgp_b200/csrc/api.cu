@@ -17,6 +17,7 @@ int grid_alpha(kgp_ctx* c, double* out);
 int grid_predict(kgp_ctx* c, const double* Xs, long ns, double* ymu, double* ys2, double* fmu, double* fs2);
 int grid_create(kgp_ctx* c, int slot, int eq, double k);
 void grid_free(kgp_ctx* c);
+int grid_init(kgp_ctx* c);
 
 // FP64 DMMA issue-rate micro-benchmark: 8 warps/SMSP-worth of independent DMMA chains
 __global__ void dmma_peak_kernel(double* out, int iters) {
@@ -66,6 +67,7 @@ int kgp_ctx_create(int device, kgp_ctx** out) {
   if (cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) != cudaSuccess) { delete c; return KGP_CUDA_ERR; }
   for (int i = 0; i < 16; ++i) cudaEventCreate(&c->ev[i]);
   int rc = exact_init(c);
+  if (!rc) rc = grid_init(c);
   if (rc) { fprintf(stderr, "kgp_ctx_create: %s\n", c->err.c_str()); delete c; return rc; }
   *out = c;
   return KGP_OK;

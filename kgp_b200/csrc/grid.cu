@@ -1,10 +1,429 @@
-// KISS-GP / MSGP (infGrid) path -- placeholder until the grid kernels land.
+// Host orchestration of the KISS-GP / MSGP (infGrid) path on one B200.
+//
+// Reference flow (GPML/inf/infGrid.m:53-89 -> infGaussLik.m:19-33 -> apx.m:116-138,218-244):
+// interpolation matrix Mx, Kronecker grid covariance Kg, alpha by un-preconditioned CG on
+// B = I + sW Mx Kg Mx' sW, Fiedler log-det bound from the factor eigenvalues, hyper-derivatives
+// by dirder, input gradient by deriv_x.  Here Mx is never formed (weights recomputed per pass),
+// the whole CG iteration is device-resident (scalars, convergence flag and iteration count live
+// in device memory; the host only polls the flag every few iterations).
 #include "ctx.h"
+#include "grid_kernels3.cuh"
+#include <math.h>
+#include <string.h>
+#include <algorithm>
+
 namespace kgp {
-int grid_eval(kgp_ctx* c, int, int, double*, double*) { return c->fail(KGP_BAD_ARG, "infGrid path not built yet"); }
-int grid_dlik(kgp_ctx* c, int, double*, bool) { return c->fail(KGP_BAD_ARG, "infGrid path not built yet"); }
-int grid_alpha(kgp_ctx* c, double*) { return c->fail(KGP_BAD_ARG, "infGrid path not built yet"); }
-int grid_predict(kgp_ctx* c, const double*, long, double*, double*, double*, double*) { return c->fail(KGP_BAD_ARG, "infGrid path not built yet"); }
-int grid_create(kgp_ctx* c, int, int, double) { return c->fail(KGP_BAD_ARG, "infGrid path not built yet"); }
-void grid_free(kgp_ctx*) {}
+
+struct GridState {
+  DevBuf axes, Kf, Vf, Af, ee, eoff, de, zv, Qm, Pm, g0, g1, tgrid, beta;
+  DevBuf x, r, d, z, ym, partA, partB, S, hyp, hypm, dX, dhyp, out, sortk, sorti, keep, dmean;
+  int p = 0; int ng[GRID_MAXP] = {0}; long N = 0;
+  long koff[GRID_MAXP] = {0};            // offsets of factor i inside Kf / Vf
+  int eoff_h[GRID_MAXP] = {0};
+  unsigned long grid_ver = 0;
+  // cached posterior
+  unsigned long st_slot_ver = 0, st_model_ver = 0, st_grid_ver = 0; int st_slot = -1, st_level = -1;
+  double prior_var = 0.0;
+};
+
+static GridState* gs(kgp_ctx* c) {
+  if (!c->gridstate) c->gridstate = new GridState();
+  return (GridState*)c->gridstate;
 }
+void grid_free(kgp_ctx* c) {
+  if (!c->gridstate) return;
+  GridState* g = (GridState*)c->gridstate;
+  DevBuf* bufs[] = {&g->axes, &g->Kf, &g->Vf, &g->Af, &g->ee, &g->eoff, &g->de, &g->zv, &g->Qm, &g->Pm, &g->g0, &g->g1,
+                    &g->tgrid, &g->beta, &g->x, &g->r, &g->d, &g->z, &g->ym, &g->partA, &g->partB, &g->S, &g->hyp,
+                    &g->hypm, &g->dX, &g->dhyp, &g->out, &g->sortk, &g->sorti, &g->keep, &g->dmean};
+  for (DevBuf* b : bufs) b->release();
+  delete g; c->gridstate = nullptr;
+}
+
+static int nblocks_for(long n) { long b = (n + 255) / 256; return (int)std::min<long>(std::max<long>(b, 1), 1184); }
+
+// upload axes, fill the descriptor
+static int grid_setup(kgp_ctx* c, GridState* g, GridDesc& G) {
+  if (!c->grid.set) return c->fail(KGP_NO_GRID, "no grid: call update_grid or pass grid_kwargs['xg']");
+  const int p = (int)c->grid.axes.size();
+  if (p > GRID_MAXP) return c->fail(KGP_BAD_ARG, "at most %d grid dimensions", GRID_MAXP);
+  long tot = 0; for (auto& a : c->grid.axes) tot += (long)a.size();
+  if (g->grid_ver != c->grid.version || g->p != p) {
+    KGP_CUDA(c, g->axes.ensure(tot * 8));
+    long o = 0;
+    for (int d = 0; d < p; ++d) {
+      KGP_CUDA(c, cudaMemcpyAsync(g->axes.d() + o, c->grid.axes[d].data(), c->grid.axes[d].size() * 8,
+                                  cudaMemcpyHostToDevice, c->stream));
+      o += (long)c->grid.axes[d].size();
+    }
+    g->grid_ver = c->grid.version;
+  }
+  memset(&G, 0, sizeof G);
+  G.p = p; g->p = p; long o = 0, N = 1, ko = 0; int eo = 0;
+  for (int d = 0; d < p; ++d) {
+    const std::vector<double>& a = c->grid.axes[d];
+    G.ng[d] = (int)a.size(); G.stride[d] = N; N *= G.ng[d];
+    G.ax[d] = g->axes.d() + o; o += (long)a.size();
+    G.s0[d] = a[0]; G.ds[d] = a[1] - a[0];
+    G.range[d] = *std::max_element(a.begin(), a.end()) - *std::min_element(a.begin(), a.end());
+    g->ng[d] = G.ng[d]; g->koff[d] = ko; ko += (long)G.ng[d] * G.ng[d]; g->eoff_h[d] = eo; eo += G.ng[d];
+  }
+  G.N = N; g->N = N;
+  return KGP_OK;
+}
+
+template <typename F> static void for_p(int p, F&& f) {
+  switch (p) { case 1: f(std::integral_constant<int, 1>()); break; case 2: f(std::integral_constant<int, 2>()); break;
+               case 3: f(std::integral_constant<int, 3>()); break; default: f(std::integral_constant<int, 4>()); }
+}
+
+// g_out = Mx' (scale .* v)
+static void scatter(kgp_ctx* c, const GridDesc& G, const double* X, long n, int D, const double* v, double scale, double* gout) {
+  cudaMemsetAsync(gout, 0, G.N * 8, c->stream);
+  const int use_smem = (G.N * 8 <= 96 * 1024) ? 1 : 0;
+  const int blocks = use_smem ? (int)std::min<long>((n + 255) / 256, 296) : nblocks_for(n);
+  for_p(G.p, [&](auto P) {
+    interp_scatter_kernel<decltype(P)::value><<<blocks, 256, use_smem ? G.N * 8 : 0, c->stream>>>(G, X, n, D, v, scale, gout, use_smem);
+  });
+  c->stats.kernel_launches += 2;
+}
+// out = (K_p kron ... kron K_1) in ; skip = mode to leave out (-1: none).  Returns the buffer holding the result.
+static double* kron_apply(kgp_ctx* c, GridState* g, const GridDesc& G, double* in, double* tmp, int skip) {
+  double* src = in; double* dst = tmp;
+  for (int d = 0; d < G.p; ++d) {
+    if (d == skip) continue;
+    long inner = G.stride[d], outer = G.N / (inner * G.ng[d]);
+    mode_product_kernel<<<(unsigned)((G.N + 255) / 256), 256, 0, c->stream>>>(g->Kf.d() + g->koff[d], G.ng[d], src, dst, inner, outer);
+    c->stats.kernel_launches++;
+    std::swap(src, dst);
+  }
+  return src;
+}
+
+static int factor_nhyp(const Model& m) { return m.cov_kind == KGP_COV_SM ? 3 * m.sm_Q : 2; }
+
+static int ensure_grid_buffers(kgp_ctx* c, GridState* g, const GridDesc& G, long n, int D, int nhyp) {
+  long ksz = 0; int esz = 0, ngmax = 0;
+  for (int d = 0; d < G.p; ++d) { ksz += (long)G.ng[d] * G.ng[d]; esz += G.ng[d]; ngmax = std::max(ngmax, G.ng[d]); }
+  KGP_CUDA(c, g->Kf.ensure(ksz * 8)); KGP_CUDA(c, g->Vf.ensure(ksz * 8)); KGP_CUDA(c, g->Af.ensure(ksz * 8));
+  KGP_CUDA(c, g->ee.ensure(esz * 8)); KGP_CUDA(c, g->eoff.ensure(GRID_MAXP * 4));
+  KGP_CUDA(c, g->de.ensure(G.N * 8)); KGP_CUDA(c, g->zv.ensure(ngmax * 8));
+  KGP_CUDA(c, g->Qm.ensure((long)ngmax * ngmax * 8)); KGP_CUDA(c, g->Pm.ensure((long)ngmax * ngmax * 8));
+  KGP_CUDA(c, g->g0.ensure(G.N * 8)); KGP_CUDA(c, g->g1.ensure(G.N * 8));
+  KGP_CUDA(c, g->tgrid.ensure(G.N * 8)); KGP_CUDA(c, g->beta.ensure(G.N * 8));
+  DevBuf* vecs[] = {&g->x, &g->r, &g->d, &g->z, &g->ym};
+  for (DevBuf* b : vecs) KGP_CUDA(c, b->ensure(n * 8));
+  KGP_CUDA(c, g->partA.ensure(2048 * 8)); KGP_CUDA(c, g->partB.ensure(2048 * 8));
+  KGP_CUDA(c, g->S.ensure(64 * 8)); KGP_CUDA(c, g->hyp.ensure(std::max(nhyp, 1) * 8));
+  KGP_CUDA(c, g->hypm.ensure(128 * 8)); KGP_CUDA(c, g->dmean.ensure(64 * 8));
+  KGP_CUDA(c, g->dX.ensure(n * D * 8)); KGP_CUDA(c, g->dhyp.ensure((std::max(nhyp, 1) + 128) * 8));
+  KGP_CUDA(c, g->out.ensure(64 * 8));
+  return KGP_OK;
+}
+
+static double axis_mean(const std::vector<double>& a) { double s = 0; for (double v : a) s += v; return s / (double)a.size(); }
+
+// alpha = sW .* CG(B, sW .* ym)   (apx.m:219-222,281-302); result in g->x (scaled into alpha at the end)
+static int cg_solve(kgp_ctx* c, GridState* g, const GridDesc& G, const double* X, long n, int D, double sw,
+                    double tol, int maxit) {
+  cudaStream_t st = c->stream;
+  const int nb = nblocks_for(n);
+  cg_init_kernel<<<nb, 256, 0, st>>>(g->ym.d(), sw, n, g->x.d(), g->r.d(), g->d.d(), g->partA.d());
+  cg_init_scalars_kernel<<<1, 256, 0, st>>>(g->partA.d(), nb, tol, g->S.d());
+  c->stats.kernel_launches += 2;
+  double hS[CG_NSCAL];
+  int iter = 2, parity = 0; bool done = false;
+  KGP_CUDA(c, cudaMemcpyAsync(hS, g->S.p, sizeof hS, cudaMemcpyDeviceToHost, st));
+  KGP_CUDA(c, cudaStreamSynchronize(st));
+  done = hS[CG_DONE] != 0.0;
+  const int CHECK = 16;
+  while (!done && iter <= maxit) {
+    const int upto = std::min(maxit, iter + CHECK - 1);
+    for (; iter <= upto; ++iter) {
+      scatter(c, G, X, n, D, g->d.d(), sw, g->g0.d());                       // Mx' (sW d)
+      double* u = kron_apply(c, g, G, g->g0.d(), g->g1.d(), -1);             // Kg ...
+      for_p(G.p, [&](auto P) {                                               // z = sW Mx u + d ; d.z
+        interp_gather_bz_kernel<decltype(P)::value><<<nb, 256, 0, st>>>(G, X, n, D, u, sw, g->d.d(), g->z.d(), g->partA.d());
+      });
+      cg_update1_kernel<<<nb, 256, 0, st>>>(n, g->partA.d(), nb, g->S.d(), parity, g->x.d(), g->r.d(), g->d.d(), g->z.d(), g->partB.d());
+      cg_update2_kernel<<<nb, 256, 0, st>>>(n, g->partB.d(), nb, g->S.d(), parity, tol, iter, g->r.d(), g->d.d());
+      c->stats.kernel_launches += 3;
+      parity ^= 1;
+    }
+    KGP_CUDA(c, cudaMemcpyAsync(hS, g->S.p, sizeof hS, cudaMemcpyDeviceToHost, st));
+    KGP_CUDA(c, cudaStreamSynchronize(st));
+    done = hS[CG_DONE] != 0.0;
+  }
+  KGP_CUDA(c, cudaGetLastError());
+  c->stats.cg_iters = (int)hS[CG_ITER]; c->stats.cg_relres = hS[CG_RELRES];
+  if (!done)
+    return c->fail(KGP_CG_NOT_CONVERGED, "Not converged after %d iterations, r=%1.2e", (int)hS[CG_ITER], hS[CG_RELRES]);
+  return KGP_OK;
+}
+
+static bool gstate_valid(kgp_ctx* c, GridState* g, int slot, int level) {
+  return g->st_level >= level && g->st_slot == slot && g->st_slot_ver == c->slots[slot].version &&
+         g->st_model_ver == c->model.version && g->st_grid_ver == c->grid.version;
+}
+
+int grid_eval(kgp_ctx* c, int slot, int want, double* nlZ_out, double* dnlZ_out) {
+  GridState* g = gs(c); Slot& S = c->slots[slot]; Model& m = c->model;
+  const long n = S.n; const int D = S.D;
+  if (m.cov_kind != KGP_COV_SEISO && m.cov_kind != KGP_COV_SM) return c->fail(KGP_BAD_ARG, "infGrid supports covSEiso / covSM factors");
+  if (m.opt.ldB2_cheby) return c->fail(KGP_BAD_ARG, "opt.ldB2_cheby (Chebyshev log-det) is not built yet; Fiedler bound only");
+  GridDesc G; int rc = grid_setup(c, g, G); if (rc) return rc;
+  if (G.p != D) return c->fail(KGP_BAD_ARG, "Grid and data dimension are different.");
+  const int nh = factor_nhyp(m), nhyp = nh * G.p;
+  if ((int)m.hyp_cov.size() != nhyp) return c->fail(KGP_BAD_ARG, "Number of cov function hyperparameters disagree with cov function");
+  const int nmean = ((m.mean_mask & 1) ? D : 0) + ((m.mean_mask & 2) ? 1 : 0);
+  if ((int)m.hyp_mean.size() != nmean) return c->fail(KGP_BAD_ARG, "Number of mean function hyperparameters disagree with mean function");
+  rc = ensure_grid_buffers(c, g, G, n, D, nhyp); if (rc) return rc;
+  cudaStream_t st = c->stream;
+  memset(&c->stats, 0, sizeof c->stats); c->stats.n = n; c->stats.np = G.N;
+  g->st_level = -1;
+  const double sn2 = exp(2.0 * m.hyp_lik), sw = 1.0 / sqrt(sn2), w = 1.0 / sn2;
+  const int kind = m.cov_kind == KGP_COV_SM ? 2 : 0, Q = m.sm_Q;
+
+  cudaEventRecord(c->ev[0], st);
+  KGP_CUDA(c, cudaMemcpyAsync(g->hyp.p, m.hyp_cov.data(), nhyp * 8, cudaMemcpyHostToDevice, st));
+  if (nmean) KGP_CUDA(c, cudaMemcpyAsync(g->hypm.p, m.hyp_mean.data(), nmean * 8, cudaMemcpyHostToDevice, st));
+  KGP_CUDA(c, cudaMemcpyAsync(g->eoff.p, g->eoff_h, GRID_MAXP * 4, cudaMemcpyHostToDevice, st));
+  double prior = 1.0;
+  for (int d = 0; d < G.p; ++d) {
+    const double am = axis_mean(c->grid.axes[d]);
+    const long nn = (long)G.ng[d] * G.ng[d];
+    factor_build_kernel<<<(unsigned)((nn + 255) / 256), 256, 0, st>>>(kind, Q, g->hyp.d() + d * nh, G.ax[d], G.ng[d], am, g->Kf.d() + g->koff[d]);
+    KGP_CUDA(c, cudaMemcpyAsync(g->Af.d() + g->koff[d], g->Kf.d() + g->koff[d], nn * 8, cudaMemcpyDeviceToDevice, st));
+    const size_t need = 2 * nn * 8;
+    const int use_smem = need <= 190 * 1024;
+    jacobi_eig_kernel<<<1, EIG_THREADS, use_smem ? need : 0, st>>>(g->Af.d() + g->koff[d], g->Vf.d() + g->koff[d],
+                                                                  g->ee.d() + g->eoff_h[d], G.ng[d], use_smem, 40);
+    c->stats.kernel_launches += 2;
+    if (kind == 0) prior *= exp(2.0 * m.hyp_cov[d * nh + 1]);
+    else { double sws = 0; for (int q = 0; q < Q; ++q) sws += exp(m.hyp_cov[d * nh + q]); prior *= sws; }
+  }
+  g->prior_var = prior;
+  resid_mean_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(S.X.d(), S.has_y ? S.y.d() : nullptr, n, D, m.mean_mask, g->hypm.d(), g->ym.d(), n);
+  c->stats.kernel_launches++;
+  cudaEventRecord(c->ev[1], st);
+
+  int maxit = m.opt.cg_maxit > 0 ? m.opt.cg_maxit : (int)std::min<long>(n, 20);
+  rc = cg_solve(c, g, G, S.X.d(), n, D, sw, m.opt.cg_tol, maxit);
+  if (rc) return rc;
+  axpy_scale_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(n, sw, g->x.d(), g->x.d());      // alpha = sW q
+  dot_kernel<<<1, 1024, 0, st>>>(g->ym.d(), g->x.d(), n, g->out.d() + 0);
+  dot_kernel<<<1, 1024, 0, st>>>(g->x.d(), g->x.d(), n, g->out.d() + 1);
+  cudaEventRecord(c->ev[2], st);
+
+  // Fiedler bound (apx.m:236-240,312-318)
+  const unsigned char* keep = nullptr;
+  if (n < G.N) {
+    long Npad = 1; while (Npad < G.N) Npad <<= 1;
+    KGP_CUDA(c, g->sortk.ensure(Npad * 8)); KGP_CUDA(c, g->sorti.ensure(Npad * 4)); KGP_CUDA(c, g->keep.ensure(G.N));
+    kron_eig_kernel<<<(unsigned)((Npad + 255) / 256), 256, 0, st>>>(G, g->ee.d(), (const int*)g->eoff.p, g->sortk.d(), (int*)g->sorti.p, Npad);
+    for (long k = 2; k <= Npad; k <<= 1)
+      for (long j = k >> 1; j > 0; j >>= 1) {
+        bitonic_stage_kernel<<<(unsigned)((Npad + 255) / 256), 256, 0, st>>>(g->sortk.d(), (int*)g->sorti.p, Npad, j, k);
+        c->stats.kernel_launches++;
+      }
+    KGP_CUDA(c, cudaMemsetAsync(g->keep.p, 0, G.N, st));
+    mark_keep_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>((const int*)g->sorti.p, n, G.N, (unsigned char*)g->keep.p);
+    keep = (const unsigned char*)g->keep.p;
+  }
+  const int fb = nblocks_for(G.N);
+  fiedler_kernel<<<fb, 256, 0, st>>>(G, g->ee.d(), (const int*)g->eoff.p, (double)n / (double)G.N, w, keep, g->de.d(), g->partA.d(), g->partB.d());
+  sum_small_kernel<<<1, 256, 0, st>>>(g->partA.d(), fb, g->out.d() + 2);
+  sum_small_kernel<<<1, 256, 0, st>>>(g->partB.d(), fb, g->out.d() + 3);
+  c->stats.kernel_launches += 6;
+
+  // beta = Kg Mx' alpha (needed by predict and deriv_x); T = Mx' alpha kept for dirder
+  scatter(c, G, S.X.d(), n, D, g->x.d(), 1.0, g->tgrid.d());
+  KGP_CUDA(c, cudaMemcpyAsync(g->g0.p, g->tgrid.p, G.N * 8, cudaMemcpyDeviceToDevice, st));
+  {
+    double* b = kron_apply(c, g, G, g->g0.d(), g->g1.d(), -1);
+    KGP_CUDA(c, cudaMemcpyAsync(g->beta.p, b, G.N * 8, cudaMemcpyDeviceToDevice, st));
+  }
+  if (want >= 1) {
+    for (int d = 0; d < G.p; ++d) {
+      const double am = axis_mean(c->grid.axes[d]);
+      const long nn = (long)G.ng[d] * G.ng[d];
+      // Fiedler part: dK_d( V diag(z) V' )
+      fiedler_z_kernel<<<G.ng[d], 256, 0, st>>>(G, d, g->ee.d(), (const int*)g->eoff.p, g->de.d(), g->zv.d());
+      vdv_kernel<<<(unsigned)((nn + 255) / 256), 256, 0, st>>>(g->Vf.d() + g->koff[d], g->zv.d(), G.ng[d], g->Qm.d());
+      factor_dirder_kernel<<<nh, 256, 0, st>>>(kind, Q, g->hyp.d() + d * nh, G.ax[d], G.ng[d], am, g->Qm.d(), 1.0, g->dhyp.d() + d * nh, 0);
+      // data-fit part: -1/2 dK_d( P ),  P = shp(v) shp(T)',  v = T with every other factor applied
+      KGP_CUDA(c, cudaMemcpyAsync(g->g0.p, g->tgrid.p, G.N * 8, cudaMemcpyDeviceToDevice, st));
+      double* v = kron_apply(c, g, G, g->g0.d(), g->g1.d(), d);
+      const long inner = G.stride[d], outer = G.N / (inner * G.ng[d]);
+      dim3 gg(G.ng[d], G.ng[d]);
+      mode_gram_kernel<<<gg, 128, 0, st>>>(v, g->tgrid.d(), G.ng[d], inner, outer, g->Pm.d());
+      factor_dirder_kernel<<<nh, 256, 0, st>>>(kind, Q, g->hyp.d() + d * nh, G.ax[d], G.ng[d], am, g->Pm.d(), -0.5, g->dhyp.d() + d * nh, 1);
+      c->stats.kernel_launches += 5;
+    }
+    if (nmean) { mean_grad_kernel<<<D + 1, 1024, 0, st>>>(S.X.d(), g->x.d(), n, D, g->dhyp.d() + nhyp); c->stats.kernel_launches++; }
+  }
+  if (want >= 2) {
+    const double* dmean = nullptr;
+    if (m.mean_mask & 1) { KGP_CUDA(c, cudaMemcpyAsync(g->dmean.p, m.hyp_mean.data(), D * 8, cudaMemcpyHostToDevice, st)); dmean = g->dmean.d(); }
+    for_p(G.p, [&](auto P) {
+      interp_dx_kernel<decltype(P)::value><<<(unsigned)((n + 255) / 256), 256, 0, st>>>(G, S.X.d(), n, D, g->beta.d(), g->x.d(), dmean, g->dX.d());
+    });
+    c->stats.kernel_launches++;
+  }
+  cudaEventRecord(c->ev[3], st);
+  double ho[8]; std::vector<double> hd(nhyp + D + 2);
+  KGP_CUDA(c, cudaMemcpyAsync(ho, g->out.p, 4 * 8, cudaMemcpyDeviceToHost, st));
+  if (want >= 1) KGP_CUDA(c, cudaMemcpyAsync(hd.data(), g->dhyp.p, (nhyp + D + 1) * 8, cudaMemcpyDeviceToHost, st));
+  KGP_CUDA(c, cudaStreamSynchronize(st));
+  KGP_CUDA(c, cudaGetLastError());
+  float ms = 0;
+  cudaEventElapsedTime(&ms, c->ev[0], c->ev[3]); c->stats.ms_total = ms;
+  cudaEventElapsedTime(&ms, c->ev[0], c->ev[1]); c->stats.ms_kbuild = ms;
+  cudaEventElapsedTime(&ms, c->ev[1], c->ev[2]); c->stats.ms_solve = ms;
+  cudaEventElapsedTime(&ms, c->ev[2], c->ev[3]); c->stats.ms_reduce = ms;
+  const double yta = ho[0], ata = ho[1], ldB2 = ho[2], sdW = ho[3];
+  const double nlZ = yta / 2.0 + ldB2 + (double)n * log(2.0 * M_PI * sn2) / 2.0;
+  if (nlZ_out) *nlZ_out = nlZ;
+  if (want >= 1 && dnlZ_out) {
+    int o = 0;
+    for (int i = 0; i < nhyp; ++i) dnlZ_out[o++] = hd[i];
+    dnlZ_out[o++] = -sn2 * ata - 2.0 * sdW / sn2 + (double)n;          // infGaussLik.m:32
+    if (m.mean_mask & 1) for (int d = 0; d < D; ++d) dnlZ_out[o++] = hd[nhyp + d];
+    if (m.mean_mask & 2) dnlZ_out[o++] = hd[nhyp + D];
+  }
+  g->st_slot = slot; g->st_slot_ver = S.version; g->st_model_ver = m.version; g->st_grid_ver = c->grid.version;
+  g->st_level = want >= 2 ? 2 : 0;
+  return KGP_OK;
+}
+
+int grid_dlik(kgp_ctx* c, int slot, double* out, bool out_is_dev) {
+  GridState* g = gs(c);
+  if (!gstate_valid(c, g, slot, 2)) {
+    int rc = grid_eval(c, slot, 2, nullptr, nullptr);     // like dlikGrid.m:29-36: the inference is re-run
+    if (rc) return rc;
+  }
+  Slot& S = c->slots[slot];
+  KGP_CUDA(c, cudaMemcpyAsync(out, g->dX.p, (size_t)S.n * S.D * 8, out_is_dev ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost, c->stream));
+  KGP_CUDA(c, cudaStreamSynchronize(c->stream));
+  return KGP_OK;
+}
+
+int grid_alpha(kgp_ctx* c, double* out) {
+  GridState* g = gs(c);
+  if (g->st_level < 0) return c->fail(KGP_NO_DATA, "no posterior computed yet");
+  KGP_CUDA(c, cudaMemcpy(out, g->x.p, (size_t)c->slots[g->st_slot].n * 8, cudaMemcpyDeviceToHost));
+  return KGP_OK;
+}
+
+// post.predict (infGrid.m:135-145): fmu = ms + Ms (Kg Mx' alpha); fs2 = prior variance (vg = 0)
+int grid_predict(kgp_ctx* c, const double* Xs, long ns, double* ymu, double* ys2, double* fmu, double* fs2) {
+  GridState* g = gs(c);
+  const int slot = KGP_SLOT_TR;
+  if (!gstate_valid(c, g, slot, 0)) {
+    int rc = grid_eval(c, slot, 1, nullptr, nullptr);     // gpml.py:22-25 always asks for dnlZ as well
+    if (rc) return rc;
+  }
+  GridDesc G; int rc = grid_setup(c, g, G); if (rc) return rc;
+  Model& m = c->model; const int D = c->slots[slot].D;
+  const double sn2 = exp(2.0 * m.hyp_lik);
+  cudaStream_t st = c->stream;
+  KGP_CUDA(c, c->pred_X.ensure((size_t)ns * D * 8)); KGP_CUDA(c, c->pred_a.ensure((size_t)ns * 8));
+  KGP_CUDA(c, c->pred_b.ensure((size_t)ns * 8));
+  KGP_CUDA(c, cudaMemcpyAsync(c->pred_X.p, Xs, (size_t)ns * D * 8, cudaMemcpyHostToDevice, st));
+  resid_mean_kernel<<<(unsigned)((ns + 255) / 256), 256, 0, st>>>(c->pred_X.d(), nullptr, ns, D, m.mean_mask, g->hypm.d(), c->pred_b.d(), ns);   // = -ms
+  for_p(G.p, [&](auto P) {
+    interp_gather_bz_kernel<decltype(P)::value><<<nblocks_for(ns), 256, 0, st>>>(G, c->pred_X.d(), ns, D, g->beta.d(), 1.0, nullptr, c->pred_a.d(), nullptr);
+  });
+  std::vector<double> a(ns), b(ns);
+  KGP_CUDA(c, cudaMemcpyAsync(a.data(), c->pred_a.p, ns * 8, cudaMemcpyDeviceToHost, st));
+  KGP_CUDA(c, cudaMemcpyAsync(b.data(), c->pred_b.p, ns * 8, cudaMemcpyDeviceToHost, st));
+  KGP_CUDA(c, cudaStreamSynchronize(st));
+  KGP_CUDA(c, cudaGetLastError());
+  const double v = fmax(g->prior_var, 0.0);
+  for (long i = 0; i < ns; ++i) {
+    const double f = a[i] - b[i];
+    if (fmu) fmu[i] = f; if (ymu) ymu[i] = f;
+    if (fs2) fs2[i] = v; if (ys2) ys2[i] = v + sn2;
+  }
+  return KGP_OK;
+}
+
+// ---- covGrid('create', X, eq, k)   (apxGrid.m:389-416) ------------------------------------------
+__global__ void col_minmax_kernel(const double* __restrict__ X, long n, int D, int col, double* __restrict__ out) {
+  __shared__ double smin[32], smax[32];
+  double lo = INFINITY, hi = -INFINITY;
+  for (long i = threadIdx.x; i < n; i += blockDim.x) { double v = X[i * D + col]; lo = fmin(lo, v); hi = fmax(hi, v); }
+  for (int o = 16; o > 0; o >>= 1) { lo = fmin(lo, __shfl_xor_sync(0xffffffffu, lo, o)); hi = fmax(hi, __shfl_xor_sync(0xffffffffu, hi, o)); }
+  if ((threadIdx.x & 31) == 0) { smin[threadIdx.x >> 5] = lo; smax[threadIdx.x >> 5] = hi; }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    for (int w = 1; w < (int)(blockDim.x >> 5); ++w) { lo = fmin(lo, smin[w]); hi = fmax(hi, smax[w]); }
+    out[0] = lo; out[1] = hi;
+  }
+}
+__global__ void col_gather_kernel(const double* __restrict__ X, long n, int D, int col, double* __restrict__ key,
+                                  int* __restrict__ idx, long Npad) {
+  long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= Npad) return;
+  key[i] = (i < n) ? X[i * D + col] : -INFINITY; idx[i] = (int)i;
+}
+__global__ void count_unique_kernel(const double* __restrict__ key, long n, unsigned long long* __restrict__ cnt) {
+  long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  if (i == 0 || key[i] != key[i - 1]) atomicAdd(cnt, 1ULL);     // integer count: order-independent
+}
+
+int grid_create(kgp_ctx* c, int slot, int eq, double k) {
+  if (!eq) return c->fail(KGP_BAD_ARG, "covGrid('create') with eq=0 needs kmeans (statistics package); only eq=1 is built");
+  GridState* g = gs(c); Slot& S = c->slots[slot];
+  const long n = S.n; const int D = S.D;
+  if (D > GRID_MAXP) return c->fail(KGP_BAD_ARG, "at most %d grid dimensions", GRID_MAXP);
+  cudaStream_t st = c->stream;
+  KGP_CUDA(c, g->out.ensure(64 * 8));
+  std::vector<std::vector<double>> axes;
+  for (int j = 0; j < D; ++j) {
+    double mm[2];
+    col_minmax_kernel<<<1, 1024, 0, st>>>(S.X.d(), n, D, j, g->out.d());
+    KGP_CUDA(c, cudaMemcpyAsync(mm, g->out.p, 16, cudaMemcpyDeviceToHost, st));
+    KGP_CUDA(c, cudaStreamSynchronize(st));
+    if (!(mm[1] > mm[0])) return c->fail(KGP_BAD_ARG, "Two few unique points.");
+    long ngj;
+    if (k >= 0.0 && k <= 1.0) {                       // fraction of the unique values (apxGrid.m:402-403)
+      long Npad = 1; while (Npad < n) Npad <<= 1;
+      KGP_CUDA(c, g->sortk.ensure(Npad * 8)); KGP_CUDA(c, g->sorti.ensure(Npad * 4));
+      col_gather_kernel<<<(unsigned)((Npad + 255) / 256), 256, 0, st>>>(S.X.d(), n, D, j, g->sortk.d(), (int*)g->sorti.p, Npad);
+      for (long kk = 2; kk <= Npad; kk <<= 1)
+        for (long jj = kk >> 1; jj > 0; jj >>= 1)
+          bitonic_stage_kernel<<<(unsigned)((Npad + 255) / 256), 256, 0, st>>>(g->sortk.d(), (int*)g->sorti.p, Npad, jj, kk);
+      unsigned long long* cnt = (unsigned long long*)(g->out.d() + 8);
+      KGP_CUDA(c, cudaMemsetAsync(cnt, 0, 8, st));
+      count_unique_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(g->sortk.d(), n, cnt);
+      unsigned long long hc = 0;
+      KGP_CUDA(c, cudaMemcpyAsync(&hc, cnt, 8, cudaMemcpyDeviceToHost, st));
+      KGP_CUDA(c, cudaStreamSynchronize(st));
+      ngj = (long)ceil(k * (double)hc);
+    } else ngj = (long)k;
+    if (ngj < 1) return c->fail(KGP_BAD_ARG, "bad grid size k=%g", k);
+    const double du = (mm[1] - mm[0]) / (double)ngj, b0 = mm[0] - 5.0 * du, b1 = mm[1] + 5.0 * du;
+    const long np_ = std::max<long>(ngj, 5);
+    std::vector<double> ax(np_);                      // Octave linspace: base + i*delta, last point exact
+    const double delta = (b1 - b0) / (double)(np_ - 1);
+    for (long i = 0; i < np_; ++i) ax[i] = b0 + (double)i * delta;
+    ax[np_ - 1] = b1;
+    axes.push_back(ax);
+  }
+  KGP_CUDA(c, cudaGetLastError());
+  c->grid.axes = axes; c->grid.set = true; c->grid.version++;
+  return KGP_OK;
+}
+
+int grid_init(kgp_ctx* c) {
+  KGP_CUDA(c, cudaFuncSetAttribute(jacobi_eig_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 190 * 1024));
+  KGP_CUDA(c, cudaFuncSetAttribute(interp_scatter_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024));
+  KGP_CUDA(c, cudaFuncSetAttribute(interp_scatter_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024));
+  KGP_CUDA(c, cudaFuncSetAttribute(interp_scatter_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024));
+  KGP_CUDA(c, cudaFuncSetAttribute(interp_scatter_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024));
+  return KGP_OK;
+}
+
+}  // namespace kgp

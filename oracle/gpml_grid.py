@@ -1,0 +1,428 @@
+"""CPU FP64 oracle for the KISS-GP / MSGP (infGrid) path -- TEST INFRASTRUCTURE ONLY.
+
+NumPy/SciPy restatement of the reference's grid inference; parity checker for the
+CUDA engine and timed CPU baseline.  Nothing under kgp_b200/ may import it.
+
+Reference restated (GPML/ = kgp/backend/gpml/ of alshedivat/keras-gp):
+  grid creation      GPML/cov/apxGrid.m:389-416 (creategrid, eq=1 only)
+  interpolation      GPML/cov/apxGrid.m:440-490 (interpgrid), 495-523 (eqinterp), 527-539 (kcub/dkcub)
+  Kronecker MVM      GPML/cov/apxGrid.m:302-329 (kronmvm), dense factors (plain numeric axes)
+  CG                 GPML/cov/apx.m:275-302 (conjgrad/linsolve), 218-226 (ldB2_grid)
+  Fiedler log-det    GPML/cov/apxGrid.m:571-588 (eigkron), GPML/cov/apx.m:312-318, 246-269
+  Chebyshev log-det  GPML/cov/apx.m:336-391 (probes and emax are explicit inputs)
+  hyper-derivatives  GPML/cov/apxGrid.m:631-652 (dirder), GPML/cov/apx.m:271-273
+  inference          GPML/inf/infGrid.m:53-89,131-145, GPML/inf/infGaussLik.m:19-33
+  factor kernels     covSEiso on a 1-D axis (covMaha/covSE/covScale), GPML/cov/covSM.m:124-156
+  input gradient     kgp/backend/utils/dlikGrid.m:8-40, deriv_x.m:4-26
+
+Parity status: "parity unpinned" -- the reference holds no numeric value for infGrid
+anywhere; this restatement is checked by self-consistency (finite differences,
+explicit Kronecker products, dense solves) in tests/test_oracle_grid.py.
+"""
+import numpy as np
+import scipy.sparse as sp
+
+from gpml_exact import mean_eval
+
+
+# ----------------------------------------------------------------------------
+# grid creation (apxGrid.m:389-416), eq = 1
+# ----------------------------------------------------------------------------
+def creategrid(x, eq=1, k=1.0):
+    x = np.asarray(x, dtype=np.float64)
+    if x.ndim == 1:
+        x = x[:, None]
+    assert eq, 'only equispaced grids (eq=1): eq=0 needs kmeans from the statistics package'
+    xg = []
+    for j in range(x.shape[1]):
+        u = np.unique(x[:, j])
+        if u.size < 2:
+            raise ValueError('Two few unique points.')
+        if 0 <= k <= 1:
+            ngj = int(np.ceil(k * u.size))
+        else:
+            ngj = int(k)
+        du = (u[-1] - u[0]) / ngj
+        xg.append(np.linspace(u[0] - 5 * du, u[-1] + 5 * du, max(ngj, 5)))
+    return xg
+
+
+# ----------------------------------------------------------------------------
+# cubic convolution interpolation (apxGrid.m:495-539)
+# ----------------------------------------------------------------------------
+def kcub(x):
+    x = np.abs(x)
+    y = np.zeros_like(x)
+    q = x <= 1
+    y[q] = ((1.5 * x[q] - 2.5) * x[q]) * x[q] + 1
+    q = (1 < x) & (x <= 2)
+    y[q] = ((-0.5 * x[q] + 2.5) * x[q] - 4) * x[q] + 2
+    return y
+
+
+def dkcub(x):
+    y = np.sign(x); x = np.abs(x)
+    q = x <= 1
+    y[q] = y[q] * (4.5 * x[q] - 5.0) * x[q]
+    q = (1 < x) & (x <= 2)
+    y[q] = y[q] * ((-1.5 * x[q] + 5.0) * x[q] - 4.0)
+    y[x > 2] = 0
+    return y
+
+
+def eqinterp(s, t):
+    """J (nt,4) 0-based node indices, C (nt,4) weights, dC (nt,4) derivative weights * (ns-1)."""
+    s = np.asarray(s, dtype=np.float64); t = np.asarray(t, dtype=np.float64)
+    it = np.array([-2, -1, 0, 1]); nc = 4
+    ds = s[1] - s[0]; ns = s.size
+    assert ns >= nc
+    j = np.floor((t - s[0]) / ds) + 1
+    w = (t - s[0]) / ds - j + 1
+    j = j - it[nc - 1]
+    C = np.zeros((t.size, nc)); dC = np.zeros((t.size, nc))
+    for i in range(nc):
+        C[:, i] = kcub(w + it[nc - 1 - i])
+        dC[:, i] = dkcub(w + it[nc - 1 - i]) * (ns - 1)
+    idx = np.where(j < nc + it[0])[0]                     # lower boundary (:515-518)
+    C[idx] = 0; dC[idx] = 0
+    if idx.size:
+        jid = np.argmin(np.abs(s[None, :nc] - t[idx, None]), axis=1)
+        C[idx, jid] = 1
+    j[idx] = 1
+    v = ns - nc + 1
+    idx = np.where(j > v)[0]                              # upper boundary (:519-522)
+    C[idx] = 0; dC[idx] = 0
+    if idx.size:
+        jid = np.argmin(np.abs(s[None, ns - nc:] - t[idx, None]), axis=1)
+        C[idx, jid] = 1
+    j[idx] = v
+    J = (j[:, None] + np.arange(nc)[None, :] - 1).astype(np.int64)   # 0-based
+    return J, C, dC
+
+
+def interpgrid(xg, x, want_deriv=False):
+    """Sparse Mx (n x N) and optionally dMx[i]; grid linear index has the first axis fastest."""
+    x = np.asarray(x, dtype=np.float64)
+    if x.ndim == 1:
+        x = x[:, None]
+    n, p = x.shape
+    ng = [a.size for a in xg]; N = int(np.prod(ng))
+    J = np.zeros((n, 1), dtype=np.int64); C = np.ones((n, 1))
+    dC = [np.ones((n, 1)) for _ in range(p)]
+    s = 1
+    for i in range(p):
+        Ji, Ci, dCi = eqinterp(xg[i], x[:, i])
+        J = (J[:, :, None] + s * Ji[:, None, :]).reshape(n, -1)
+        C = (C[:, :, None] * Ci[:, None, :]).reshape(n, -1)
+        for jd in range(p):
+            dC[jd] = (dC[jd][:, :, None] * (dCi if jd == i else Ci)[:, None, :]).reshape(n, -1)
+        s *= ng[i]
+    I = np.repeat(np.arange(n)[:, None], C.shape[1], axis=1)
+    Mx = sp.csr_matrix((C.ravel(), (I.ravel(), J.ravel())), shape=(n, N))
+    if not want_deriv:
+        return Mx
+    dMx = [sp.csr_matrix((d.ravel(), (I.ravel(), J.ravel())), shape=(n, N)) for d in dC]
+    return Mx, dMx
+
+
+# ----------------------------------------------------------------------------
+# 1-D factor kernels on a grid axis and their directional derivatives
+# ----------------------------------------------------------------------------
+def factor_nhyp(kind, Q=0):
+    return 2 if kind == 'covSEiso' else 3 * Q
+
+
+def factor_cov(kind, hyp, ax, Q=0):
+    """returns K (ng x ng) and dK(R) -> d tr(R'K)/dhyp   (R need not be symmetric)."""
+    hyp = np.asarray(hyp, dtype=np.float64).reshape(-1)
+    ax = np.asarray(ax, dtype=np.float64)
+    if kind == 'covSEiso':
+        ell, sf2 = np.exp(hyp[0]), np.exp(2 * hyp[1])
+        xc = (ax - ax.mean()) / ell                       # covMaha.m:138-143 centring
+        sq = xc * xc
+        D2 = np.maximum(sq[:, None] + (sq[None, :] - 2.0 * np.outer(xc, xc)), 0.0)
+        K0 = np.exp(-D2 / 2.0)
+        K = sf2 * K0
+
+        def dK(R):
+            return np.array([np.sum(R * K * D2), 2.0 * np.sum(R * K)])   # covMaha.m:104, covScale.m:87-93
+        return K, dK
+    if kind == 'covSM':                                   # covSM.m:124-156, D=1
+        w = np.exp(hyp[:Q]); m = np.exp(hyp[Q:2 * Q]); v = np.exp(2 * hyp[2 * Q:3 * Q])
+        T = 2 * np.pi * (ax[:, None] - ax[None, :])
+        E = np.exp(-0.5 * (T * T)[:, :, None] * v[None, None, :])
+        Tm = T[:, :, None] * m[None, None, :]
+        H = E * np.cos(Tm)
+        K = H @ w
+
+        def dK(R):
+            dw = np.einsum('ij,ijq->q', R, H) * w
+            dm = -np.einsum('ij,ijq,ij->q', R, E * np.sin(Tm), T) * w * m
+            dv = -np.einsum('ij,ijq,ij->q', R, H, T * T) * w * v
+            return np.concatenate([dw, dm, dv])
+        return K, dK
+    raise ValueError(kind)
+
+
+def factor_diag(kind, hyp, Q=0):
+    """k(x,x) of one factor (covGrid 'diag' mode, apxGrid.m:239-249)."""
+    hyp = np.asarray(hyp, dtype=np.float64).reshape(-1)
+    return np.exp(2 * hyp[1]) if kind == 'covSEiso' else np.exp(hyp[:Q]).sum()
+
+
+def split_hyp(kind, hyp_cov, p, Q=0):
+    nh = factor_nhyp(kind, Q)
+    hyp_cov = np.asarray(hyp_cov, dtype=np.float64).reshape(-1)
+    assert hyp_cov.size == nh * p, 'Number of cov function hyperparameters disagree with cov function'
+    return [hyp_cov[i * nh:(i + 1) * nh] for i in range(p)]
+
+
+def kronmvm(Ks, v):
+    """(K_p kron ... kron K_1) v for v (N,) or (N,m); first axis fastest (apxGrid.m:302-329)."""
+    v = np.asarray(v, dtype=np.float64)
+    one = v.ndim == 1
+    if one:
+        v = v[:, None]
+    m = v.shape[1]
+    ng = [K.shape[0] for K in Ks]
+    t = v.T.reshape([m] + ng[::-1])                       # axes: rhs, dim p, ..., dim 1
+    for i, K in enumerate(Ks):
+        axn = t.ndim - 1 - i
+        t = np.moveaxis(np.tensordot(K, t, axes=([1], [axn])), 0, axn)
+    out = t.reshape(m, -1).T
+    return out[:, 0] if one else out
+
+
+# ----------------------------------------------------------------------------
+# conjugate gradients (apx.m:281-302)
+# ----------------------------------------------------------------------------
+def conjgrad(A, b, tol=1e-10, maxit=None):
+    b = np.asarray(b, dtype=np.float64)
+    one = b.ndim == 1
+    if one:
+        b = b[:, None]
+    if maxit is None:
+        maxit = min(b.shape[0], 20)
+    x = np.zeros_like(b)
+    r = b - A(x); r2 = (r * r).sum(0); r2new = r2.copy()
+    nb = np.sqrt((b * b).sum(0)); flag = 0; it = 1
+    with np.errstate(all='ignore'):
+        relres = np.sqrt(r2) / nb
+    todo = relres >= tol
+    if not todo.any():
+        return (x[:, 0] if one else x), 1, relres, it
+    r = r[:, todo]; d = r.copy()
+    for it in range(2, int(maxit) + 1):
+        z = A(d)
+        a = r2[todo] / (d * z).sum(0)
+        x[:, todo] += a[None, :] * d
+        r = r - a[None, :] * z
+        r2new[todo] = (r * r).sum(0)
+        relres = np.sqrt(r2new) / nb
+        cnv = relres[todo] < tol; todo = relres >= tol
+        d = d[:, ~cnv]; r = r[:, ~cnv]
+        if not todo.any():
+            flag = 1
+            break
+        bb = r2new / r2
+        d = r + bb[todo][None, :] * d
+        r2 = r2new.copy()
+    return (x[:, 0] if one else x), flag, relres, it
+
+
+class CGNotConverged(Exception):
+    pass
+
+
+# ----------------------------------------------------------------------------
+# Fiedler log-det bound and its derivatives (apxGrid.m:571-588, apx.m:246-269,312-318)
+# ----------------------------------------------------------------------------
+def eigkron(Ks):
+    V, ee = [], []
+    for K in Ks:
+        ej, Vj = np.linalg.eigh((K + K.T) / 2.0)
+        V.append(Vj); ee.append(np.maximum(ej, 0.0))
+    e = np.ones(1)
+    for ej in ee:
+        e = np.kron(ej, e)
+    return V, ee, e
+
+
+def logdet_fiedler(E, W):
+    ie = np.argsort(-E, kind='stable'); iw = np.argsort(-W, kind='stable')
+    Es, Ws = E[ie], W[iw]
+    N, n = E.size, W.size
+    k = n / N * Es
+    k = np.concatenate([k, np.zeros(n - N)]) if n > N else k[:n]
+    kw1 = k * Ws + 1.0
+    ub = np.log(kw1).sum() / 2.0
+    dW = np.zeros(n); dW[iw] = k / (2.0 * kw1)
+    m = min(n, N)
+    dE = np.zeros(N); dE[ie[:m]] = Ws[:m] / (N * 2.0 / n * kw1[:m])
+    return ub, dE, dW
+
+
+def fiedler_dhyp(Ks, dKs, V, ee, de):
+    """dhyp_i = dK_i( V_i diag(z_i) V_i' ),  z_i = de contracted with the other factors' eigenvalues."""
+    ng = [K.shape[0] for K in Ks]; p = len(Ks)
+    out = []
+    for i in range(p):
+        z = de.reshape(ng[::-1])                          # axes: dim p ... dim 1
+        for j in range(p):
+            if j != i:
+                axn = z.ndim - 1 - j
+                z = np.moveaxis(np.tensordot(ee[j][None, :], z, axes=([1], [axn])), 0, axn)
+        z = z.reshape(-1)
+        Q = (V[i] * z[None, :]) @ V[i].T
+        out.append(dKs[i](Q))
+    return np.concatenate(out)
+
+
+def dirder(Ks, dKs, Mx, a, b):
+    """d (a' Mx Kg Mx' b) / d hyp   (apxGrid.m:631-652), dense factors."""
+    ng = [K.shape[0] for K in Ks]; p = len(Ks)
+    Mta = Mx.T @ a; Mtb = Mx.T @ b
+    out = []
+    for i in range(p):
+        v = Mta.reshape(ng[::-1])
+        for j in range(p):
+            if j != i:
+                axn = v.ndim - 1 - j
+                v = np.moveaxis(np.tensordot(Ks[j], v, axes=([1], [axn])), 0, axn)
+        axi = len(ng) - 1 - i
+        A = np.moveaxis(v, axi, 0).reshape(ng[i], -1)
+        B = np.moveaxis(Mtb.reshape(ng[::-1]), axi, 0).reshape(ng[i], -1)
+        out.append(dKs[i](A @ B.T))
+    return np.concatenate(out)
+
+
+# ----------------------------------------------------------------------------
+# Chebyshev-Hutchinson log-det (apx.m:336-391); probes V (n x m) and emax are inputs
+# ----------------------------------------------------------------------------
+def logdet_sample(W, Kmvm, dK, V, d, emax, want_deriv=True):
+    sW = np.sqrt(W); n = W.size; emin = 1.0; m = V.shape[1]
+    B0 = lambda x: x + sW[:, None] * Kmvm(sW[:, None] * x) if x.ndim == 2 else x + sW * Kmvm(sW * x)
+    a = emin + emax; dl = 1 - emax / a; ldB2 = n * np.log(a) / 2.0
+    sf = 2.0 / a / (1 - 2 * dl)
+    B = lambda x: sf * B0(x) - 1.0 / (1 - 2 * dl) * x
+    xk = np.cos(np.pi * (np.arange(d + 1) + 0.5) / (d + 1))
+    fk = np.log(((1 - 2 * dl) / 2.0) * xk + 0.5)
+    Tk = np.ones((d + 1, d + 1)); Tk[:, 1] = xk
+    for i in range(2, d + 1):
+        Tk[:, i] = 2 * xk * Tk[:, i - 1] - Tk[:, i - 2]
+    c = 2.0 / (d + 1) * (Tk.T @ fk); c[0] /= 2
+    p1 = np.zeros(d + 1); p1[0] = 1; p2 = np.zeros(d + 1); p2[1] = 1
+    p = c[0] * p1 + c[1] * p2
+    for i in range(2, d + 1):
+        p3 = np.concatenate([[0.0], 2 * p2[:d]]) - p1
+        p = p + c[i] * p3; p1, p2 = p2, p3
+    dhyp = 0.0; dWv = np.zeros(n)
+    for i in range(m):
+        v = V[:, i]
+        Bv = np.zeros((n, d + 1)); Bv[:, 0] = v
+        for j in range(d):
+            Bv[:, j + 1] = B(Bv[:, j])
+        ldB2 += (v @ Bv @ p) / (2.0 * m)
+        if not want_deriv:
+            continue
+        sWBv = sW[:, None] * Bv
+        for j in range(1, d + 1):
+            for k in range(1, int(np.ceil(j / 2)) + 1):
+                akj = sf * p[j] / m
+                if k == int(np.ceil(j / 2)) and j % 2 == 1:
+                    akj /= 2
+                dhyp = dhyp + akj * dK(sWBv[:, j - k], sWBv[:, k - 1])
+        u = Bv / sW[:, None]; w = Kmvm(sWBv)
+        for j in range(1, d + 1):
+            dWj = (u[:, j - 1::-1][:, :j] * w[:, :j] + w[:, j - 1::-1][:, :j] * u[:, :j]).sum(1)
+            dWv += sf * p[j] / (4.0 * m) * dWj
+    return ldB2, dhyp, dWv
+
+
+# ----------------------------------------------------------------------------
+# infGrid with likGauss (infGrid.m:53-89 -> infGaussLik.m:19-33 -> apx.m grid branch)
+# ----------------------------------------------------------------------------
+def inf_grid(hyp, mean, kind, xg, x, y, opt=None, Q=0, want_grad=True, cheby=None):
+    """returns post {alpha, Kalpha (grid vector), cg_iter, cg_relres}, nlZ, dnlZ {cov, lik, mean}.
+
+    opt: cg_tol (1e-6), cg_maxit (min(n,20)).  cheby = dict(V=..., d=..., emax=...) selects the
+    Chebyshev estimator with injected probes (opt.ldB2_cheby), else the Fiedler bound."""
+    opt = opt or {}
+    x = np.asarray(x, dtype=np.float64)
+    if x.ndim == 1:
+        x = x[:, None]
+    y = np.asarray(y, dtype=np.float64).reshape(-1)
+    n, D = x.shape; p = len(xg)
+    assert p == D, 'Grid and data dimension are different.'
+    tol = opt.get('cg_tol', 1e-6); maxit = opt.get('cg_maxit', min(n, 20))
+    hs = split_hyp(kind, hyp['cov'], p, Q)
+    fac = [factor_cov(kind, hs[i], xg[i], Q) for i in range(p)]
+    Ks = [f[0] for f in fac]; dKs = [f[1] for f in fac]
+    Mx = interpgrid(xg, x)
+    MxT = Mx.T.tocsr()
+    m, dm = mean_eval(mean, hyp.get('mean', []), x)
+    sn2 = np.exp(2.0 * float(hyp['lik'])); W = np.full(n, 1.0 / sn2); sW = np.sqrt(W)
+    Kmvm = lambda v: Mx @ kronmvm(Ks, MxT @ v)
+
+    def mvmB(v):
+        return (sW[:, None] * Kmvm(sW[:, None] * v) + v) if v.ndim == 2 else sW * Kmvm(sW * v) + v
+
+    def solveKiW(r):
+        q, flag, relres, it = conjgrad(mvmB, sW * r, tol, maxit)
+        if not flag:
+            raise CGNotConverged('Not converged after %d iterations, r=%1.2e' % (it, np.max(relres)))
+        solveKiW.iters, solveKiW.relres = it, float(np.max(relres))
+        return sW * q
+
+    dK_ab = lambda a, b: dirder(Ks, dKs, Mx, a, b)
+    if cheby is None:
+        V, ee, e = eigkron(Ks)
+        ldB2, de, dW = logdet_fiedler(e, W)
+        de = de * (e > 0)
+        dhyp_cov = fiedler_dhyp(Ks, dKs, V, ee, de) if want_grad else None
+    else:
+        ldB2, dhyp_cov, dW = logdet_sample(W, Kmvm, dK_ab, cheby['V'], cheby['d'], cheby['emax'], want_grad)
+    alpha = solveKiW(y - m)
+    post = {'alpha': alpha, 'Kalpha': kronmvm(Ks, MxT @ alpha), 'cg_iter': solveKiW.iters,
+            'cg_relres': solveKiW.relres, 'ldB2': ldB2}
+    nlZ = (y - m) @ alpha / 2.0 + ldB2 + n * np.log(2 * np.pi * sn2) / 2.0
+    if not want_grad:
+        return post, nlZ, None
+    dnlZ = {'cov': dhyp_cov - dK_ab(alpha, alpha) / 2.0,               # apx.m:271-272
+            'mean': -dm(alpha),
+            'lik': -sn2 * (alpha @ alpha) - 2.0 * dW.sum() / sn2 + n}
+    return post, nlZ, dnlZ
+
+
+def dlik_grid(hyp, mean, kind, xg, x, y, opt=None, Q=0, h=1e-5):
+    """dnlZ/dX (n x D): dlikGrid.m:8-40 -> deriv_x.m:4-26 (no projection)."""
+    x = np.asarray(x, dtype=np.float64)
+    if x.ndim == 1:
+        x = x[:, None]
+    post, _, _ = inf_grid(hyp, mean, kind, xg, x, y, opt, Q, want_grad=False)
+    alpha = post['alpha']
+    _, dM = interpgrid(xg, x, want_deriv=True)
+    beta = post['Kalpha']
+    cols = []
+    for i in range(x.shape[1]):
+        wi = xg[i].max() - xg[i].min()
+        xm = x.copy(); xm[:, i] -= h
+        xp = x.copy(); xp[:, i] += h            # reference: -h then +2h (deriv_x.m:16-19)
+        dmi = (mean_eval(mean, hyp.get('mean', []), xp)[0] - mean_eval(mean, hyp.get('mean', []), xm)[0]) / (2 * h)
+        cols.append(-alpha * (dmi + dM[i] @ beta / wi))
+    return np.stack(cols, axis=1)
+
+
+def predict_grid(hyp, mean, kind, xg, post, xs, Q=0):
+    """[fmu fs2 ymu ys2] = post.predict(xs)  (infGrid.m:135-145; vg = 0 unless opt.pred_var)."""
+    xs = np.asarray(xs, dtype=np.float64)
+    if xs.ndim == 1:
+        xs = xs[:, None]
+    Ms = interpgrid(xg, xs)
+    ms, _ = mean_eval(mean, hyp.get('mean', []), xs)
+    fmu = ms + Ms @ post['Kalpha']
+    hs = split_hyp(kind, hyp['cov'], len(xg), Q)
+    ks = np.prod([factor_diag(kind, h_, Q) for h_ in hs]) * np.ones(xs.shape[0])
+    fs2 = np.maximum(ks - 0.0, 0.0)
+    sn2 = np.exp(2.0 * float(hyp['lik']))
+    return fmu, fs2, fmu.copy(), fs2 + sn2

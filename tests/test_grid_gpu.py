@@ -1,0 +1,161 @@
+"""GPU parity tests of the KISS-GP / MSGP (infGrid) path against the CPU oracle.
+
+Tolerances: the deterministic parts (grid axes, interpolation, Fiedler bound,
+hyper-derivatives at a converged alpha) are compared at a tight CG tolerance with 1e-8 relative;
+at the reference's loose cg_tol the budget is 10 x |oracle(cg_tol) - oracle(1e-13)| per quantity and
+the iteration count must agree within +-4 (scatter-add order differs from the sparse product's)."""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+
+def rel(a, b):
+    a = np.asarray(a, dtype=float).ravel(); b = np.asarray(b, dtype=float).ravel()
+    return float(np.max(np.abs(a - b)) / max(np.max(np.abs(b)), 1e-300))
+
+
+def make(X, y, cov, hyp_cov, lik, k, opt, mean='meanZero', hyp_mean=(), mean_args=None, Q=0):
+    from kgp_b200 import B200GP
+    gp = B200GP()
+    hyp = {'lik': lik, 'mean': [[v] for v in hyp_mean], 'cov': hyp_cov}
+    gp.configure(X.shape[1], hyp, opt, 'infGrid', mean, cov, 'likGauss', 'dlikGrid', grid_kwargs={'eq': 1, 'k': k},
+                 cov_args=[Q] if Q else None, mean_args=mean_args, verbose=0)
+    gp.update_data('tr', X, y[:, None])
+    gp.update_grid('tr')
+    return gp
+
+
+def oracle_all(gp, X, y, cov, opt, mean, Q, Xs):
+    import gpml_grid as gg
+    hv = gp._hyp_vec(); nc = gp.hyp['cov'].size
+    oh = {'cov': hv[:nc], 'lik': gp.hyp['lik'], 'mean': hv[nc + 1:]}
+    om = {'meanZero': ['meanZero'], 'meanSum': ['meanLinear', 'meanConst']}[mean]
+    xg = gg.creategrid(X, 1, gp._grid_k)
+    post, nlZ, d = gg.inf_grid(oh, om, cov, xg, X, y, opt, Q=Q)
+    g = np.concatenate([d['cov'], [d['lik']], d['mean']])
+    dX = gg.dlik_grid(oh, om, cov, xg, X, y, opt, Q=Q)
+    p = gg.predict_grid(oh, om, cov, xg, post, Xs, Q=Q)
+    return xg, post, nlZ, g, dX, p
+
+
+CASES = {
+    'c4': dict(seed=45, n=460, D=1, cov='covSEiso', hyp=[[-0.7], [0.0]], lik=-2.0, k=100.),
+    'gradcheck_n_lt_N': dict(seed=42, n=100, D=1, cov='covSEiso', hyp=[[np.log(0.5)], [0.0]], lik=np.log(0.1), k=128.),
+    'c3_small': dict(seed=44, n=3000, D=2, cov='covSEiso', hyp=[[0.5], [1.0]], lik=np.log(0.3), k=30.),
+    'sm_mean': dict(seed=46, n=4000, D=2, cov='covSM', Q=3, lik=np.log(0.3), k=32., mean='meanSum', hyp_mean=[0.1, -0.1, 0.2]),
+}
+
+
+def build(name):
+    c = CASES[name]; rng = np.random.RandomState(c['seed']); n, D = c['n'], c['D']
+    if name == 'c4':
+        X = np.tanh(rng.randn(n, 1)); y = np.sin(4 * X[:, 0]) + np.exp(-2) * rng.randn(n); Xs = np.tanh(rng.randn(77, 1)) * 1.3
+    elif name == 'gradcheck_n_lt_N':
+        X = rng.rand(n, 1); y = rng.rand(n); Xs = rng.rand(20, 1) * 1.4 - 0.2
+    elif name == 'c3_small':
+        X = np.maximum(0, rng.normal(0.5, 1, (n, 2))); y = np.sin(3 * X[:, 0]) * np.cos(2 * X[:, 1]) + 0.3 * rng.randn(n)
+        Xs = np.maximum(0, rng.normal(0.5, 1.3, (300, 2)))
+    else:
+        X = rng.rand(n, 2); y = np.sin(2 * np.pi * 3 * X).sum(1) + 0.5 * X[:, 0] + 0.3 * rng.randn(n); Xs = rng.rand(200, 2)
+        Q = c['Q']
+        c = dict(c); c['hyp'] = [[np.log(np.ones((Q, 1)))], [np.log(np.maximum(0.05 * rng.rand(Q, 1), 1e-8))],
+                                 [np.log(np.abs(rng.randn(Q, 1) + 1))]]
+    return c, X, y, Xs
+
+
+@pytest.mark.parametrize('name', list(CASES))
+def test_deterministic_parts_tight_cg(built_lib, name):
+    c, X, y, Xs = build(name)
+    opt = {'cg_maxit': 20000, 'cg_tol': 1e-12}
+    mean = c.get('mean', 'meanZero'); Q = c.get('Q', 0)
+    gp = make(X, y, c['cov'], c['hyp'], c['lik'], c['k'], opt, mean, c.get('hyp_mean', ()),
+              ['{@meanLinear, @meanConst}'] if mean == 'meanSum' else None, Q)
+    nlZ, g = gp.eng.eval(0, 2, gp._n_hyp)
+    dX = gp.get_dlik_dx('tr'); ymu, ys2 = gp.predict(Xs, return_var=True)
+    xg, post, nlZ0, g0, dX0, p0 = oracle_all(gp, X, y, c['cov'], opt, mean, Q, Xs)
+    for a, b in zip(gp.grid(), xg):
+        assert np.array_equal(a, b)                              # axes bit-exact (same linspace arithmetic)
+    assert rel(nlZ, nlZ0) < 1e-8 and rel(g, g0) < 1e-8
+    assert rel(gp.alpha(), post['alpha']) < 1e-7 and rel(dX, dX0) < 1e-7
+    assert rel(ymu, p0[2]) < 1e-7 and rel(ys2, p0[3]) < 1e-12
+    assert ymu.shape == (Xs.shape[0], 1) and dX.shape == X.shape
+
+
+@pytest.mark.parametrize('name,opt', [('c4', {'cg_maxit': 500, 'cg_tol': 1e-4}), ('c3_small', {'cg_maxit': 2000, 'cg_tol': 1e-6}),
+                                      ('sm_mean', {'cg_maxit': 2000, 'cg_tol': 1e-6})])
+def test_iterative_parts_reference_cg_settings(built_lib, name, opt):
+    import gpml_grid as gg
+    c, X, y, Xs = build(name)
+    mean = c.get('mean', 'meanZero'); Q = c.get('Q', 0)
+    gp = make(X, y, c['cov'], c['hyp'], c['lik'], c['k'], opt, mean, c.get('hyp_mean', ()),
+              ['{@meanLinear, @meanConst}'] if mean == 'meanSum' else None, Q)
+    nlZ, g = gp.eng.eval(0, 2, gp._n_hyp)
+    st = gp.stats()
+    xg, post, nlZ0, g0, dX0, p0 = oracle_all(gp, X, y, c['cov'], opt, mean, Q, Xs)
+    _, _, nlZT, gT, dXT, _ = oracle_all(gp, X, y, c['cov'], {'cg_maxit': 50000, 'cg_tol': 1e-13}, mean, Q, Xs)
+    assert abs(st['cg_iters'] - post['cg_iter']) <= 4
+    assert st['cg_relres'] < opt['cg_tol']
+    assert abs(nlZ - nlZ0) <= 10 * abs(nlZ0 - nlZT) + 1e-9 * abs(nlZ0)
+    assert np.max(np.abs(g - g0)) <= 10 * np.max(np.abs(g0 - gT)) + 1e-9 * np.max(np.abs(g0))
+    dX = gp.get_dlik_dx('tr')
+    assert np.max(np.abs(dX - dX0)) <= 10 * np.max(np.abs(dX0 - dXT)) + 1e-9 * np.max(np.abs(dX0))
+
+
+def test_msgp_backend_interface_mirror(built_lib):
+    """tests/backend/test_gpml.py msgp_test_config (N=100, D=1, k=100, cg 500/1e-4): calls, types, shapes."""
+    from kgp_b200 import GP_BACKEND, _cabi
+    rng = np.random.RandomState(42)
+    N, D = 100, 1
+    X_tr = rng.normal(size=(N, D)); y_tr = rng.normal(size=(N, 1)); X_tst = rng.normal(size=(N, D))
+    gp = GP_BACKEND()
+    gp.configure(input_dim=1, hyp={'lik': -2.0, 'mean': [], 'cov': np.array([[-0.7], [0.0]])},
+                 opt={'cg_maxit': 500, 'cg_tol': 1e-4}, inf='infGrid', mean='meanZero', cov='covSEiso',
+                 lik='likGauss', dlik='dlikGrid', grid_kwargs={'eq': 1, 'k': 100}, verbose=0)
+    gp.update_data('tr', X_tr, y_tr)
+    with pytest.raises(_cabi.KgpError) as ei:                   # no grid yet
+        gp.evaluate('tr')
+    assert ei.value.code == _cabi.NO_GRID
+    gp.update_grid('tr')
+    nlZ = gp.evaluate('tr'); assert isinstance(nlZ, float) and np.isfinite(nlZ)
+    ymu, ys2 = gp.predict(X_tst, X_tr, y_tr, return_var=True)
+    assert type(ymu) is np.ndarray and ymu.shape == (N, 1) and ys2.shape == (N, 1)
+    assert np.allclose(ys2, 1.0 + np.exp(-4.0))                  # prior variance + noise (infGrid.m:128,141-143)
+    dl = gp.get_dlik_dx('tr'); assert dl.shape == (N, D)
+    nl2, ymu2 = gp.eval_predict(X_tst, X_tr, y_tr); assert ymu2.shape == (N, 1)
+    hyp = gp.train(5, X_tr, y_tr)
+    assert set(hyp) == {'cov', 'lik', 'mean'} and hyp['cov'].shape == (2, 1)
+    assert gp.evaluate('tr') <= nlZ + 1e-6
+
+
+def test_cg_non_convergence_maps_to_nan_and_raises_in_dlik(built_lib):
+    from kgp_b200 import _cabi
+    c, X, y, Xs = build('c3_small')
+    gp = make(X, y, c['cov'], c['hyp'], np.log(0.01), c['k'], {'cg_maxit': 3, 'cg_tol': 1e-12})
+    with pytest.warns(UserWarning):
+        assert np.isnan(gp.evaluate('tr'))                       # gp.m:117-123
+    with pytest.raises(_cabi.KgpError) as ei:
+        gp.get_dlik_dx('tr')                                     # dlikGrid is outside gp.m's try/catch
+    assert ei.value.code == _cabi.CG_NOT_CONVERGED
+
+
+def test_manual_grid_and_full_size_c3(built_lib):
+    """BASELINE configs[2] shape: n=40000, D=2, k=70 (N=4900), cg 2000/1e-6; plus grid_kwargs['xg']."""
+    import gpml_grid as gg
+    rng = np.random.RandomState(44)
+    n = 40000
+    X = np.maximum(0, rng.normal(0.5, 1, (n, 2))); y = np.sin(3 * X[:, 0]) * np.cos(2 * X[:, 1]) + 0.3 * rng.randn(n)
+    opt = {'cg_maxit': 2000, 'cg_tol': 1e-6}
+    gp = make(X, y, 'covSEiso', [[0.5], [1.0]], np.log(0.3), 70., opt)
+    nlZ, g = gp.eng.eval(0, 2, gp._n_hyp)
+    xg = gg.creategrid(X, 1, 70.)
+    oh = {'cov': gp._hyp_vec()[:4], 'lik': np.log(0.3), 'mean': []}
+    post, nlZ0, d0 = gg.inf_grid(oh, ['meanZero'], 'covSEiso', xg, X, y, opt)
+    assert rel(nlZ, nlZ0) < 1e-6 and rel(g, np.concatenate([d0['cov'], [d0['lik']]])) < 1e-5
+    assert abs(gp.stats()['cg_iters'] - post['cg_iter']) <= 6
+    from kgp_b200 import B200GP
+    gp2 = B200GP()
+    gp2.configure(2, {'lik': np.log(0.3), 'mean': [], 'cov': [[0.5], [1.0]]}, opt, 'infGrid', 'meanZero', 'covSEiso', 'likGauss',
+                  'dlikGrid', grid_kwargs={'eq': 1, 'k': 70., 'xg': xg}, verbose=0)
+    gp2.update_data('tr', X, y[:, None])
+    assert rel(gp2.evaluate('tr'), nlZ) < 1e-9
