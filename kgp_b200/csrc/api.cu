@@ -65,6 +65,7 @@ int kgp_ctx_create(int device, kgp_ctx** out) {
   kgp_opt_default(&c->model.opt);
   memset(&c->stats, 0, sizeof c->stats);
   if (cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) != cudaSuccess) { delete c; return KGP_CUDA_ERR; }
+  cudaStreamCreateWithFlags(&c->stream2, cudaStreamNonBlocking);
   for (int i = 0; i < 16; ++i) cudaEventCreate(&c->ev[i]);
   int rc = exact_init(c);
   if (!rc) rc = grid_init(c);
@@ -77,6 +78,7 @@ int kgp_ctx_destroy(kgp_ctx* c) {
   if (!c) return KGP_OK;
   cudaSetDevice(c->device);
   cudaStreamSynchronize(c->stream);
+  if (c->stream2) cudaStreamSynchronize(c->stream2);
   grid_free(c);
   DevBuf* bufs[] = {&c->M, &c->W2, &c->Dws, &c->xs, &c->s, &c->mu, &c->inv_ell, &c->ym, &c->alpha, &c->tvec,
                     &c->parts, &c->rows, &c->scal, &c->hypm, &c->dX, &c->fac, &c->pred_K, &c->pred_x, &c->pred_s,
@@ -87,6 +89,7 @@ int kgp_ctx_destroy(kgp_ctx* c) {
   for (int i = 0; i < 16; ++i) cudaEventDestroy(c->ev[i]);
   for (cudaEvent_t e : c->gev) cudaEventDestroy(e);
   cudaStreamDestroy(c->stream);
+  if (c->stream2) cudaStreamDestroy(c->stream2);
   delete c;
   return KGP_OK;
 }

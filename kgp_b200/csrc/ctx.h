@@ -46,7 +46,7 @@ constexpr int NB = 512;     // outer block width of the blocked factorisations
 
 struct kgp_ctx {
   int device = 0;
-  cudaStream_t stream = nullptr;
+  cudaStream_t stream = nullptr, stream2 = nullptr;   // main stream; side stream for work overlapped with it
   cudaEvent_t ev[16];
   std::string err;
   kgp::Slot slots[KGP_NUM_SLOTS];

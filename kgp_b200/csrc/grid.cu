@@ -179,6 +179,7 @@ int grid_eval(kgp_ctx* c, int slot, int want, double* nlZ_out, double* dnlZ_out)
   if ((int)m.hyp_mean.size() != nmean) return c->fail(KGP_BAD_ARG, "Number of mean function hyperparameters disagree with mean function");
   rc = ensure_grid_buffers(c, g, G, n, D, nhyp); if (rc) return rc;
   cudaStream_t st = c->stream;
+  cudaStreamSynchronize(c->stream2);        // a previous call may have returned early with side-stream work pending
   memset(&c->stats, 0, sizeof c->stats); c->stats.n = n; c->stats.np = G.N;
   g->st_level = -1;
   const double sn2 = exp(2.0 * m.hyp_lik), sw = 1.0 / sqrt(sn2), w = 1.0 / sn2;
@@ -189,20 +190,26 @@ int grid_eval(kgp_ctx* c, int slot, int want, double* nlZ_out, double* dnlZ_out)
   if (nmean) KGP_CUDA(c, cudaMemcpyAsync(g->hypm.p, m.hyp_mean.data(), nmean * 8, cudaMemcpyHostToDevice, st));
   KGP_CUDA(c, cudaMemcpyAsync(g->eoff.p, g->eoff_h, GRID_MAXP * 4, cudaMemcpyHostToDevice, st));
   double prior = 1.0;
+  EigBatch eb; memset(&eb, 0, sizeof eb); size_t eig_smem = 0;
   for (int d = 0; d < G.p; ++d) {
     const double am = axis_mean(c->grid.axes[d]);
     const long nn = (long)G.ng[d] * G.ng[d];
     factor_build_kernel<<<(unsigned)((nn + 255) / 256), 256, 0, st>>>(kind, Q, g->hyp.d() + d * nh, G.ax[d], G.ng[d], am, g->Kf.d() + g->koff[d]);
     KGP_CUDA(c, cudaMemcpyAsync(g->Af.d() + g->koff[d], g->Kf.d() + g->koff[d], nn * 8, cudaMemcpyDeviceToDevice, st));
-    const size_t need = 2 * nn * 8;
-    const int use_smem = need <= 190 * 1024;
-    jacobi_eig_kernel<<<1, EIG_THREADS, use_smem ? need : 0, st>>>(g->Af.d() + g->koff[d], g->Vf.d() + g->koff[d],
-                                                                  g->ee.d() + g->eoff_h[d], G.ng[d], use_smem, 40);
-    c->stats.kernel_launches += 2;
+    const size_t need = 2 * (size_t)G.ng[d] * (G.ng[d] | 1) * 8;
+    eb.A[d] = g->Af.d() + g->koff[d]; eb.V[d] = g->Vf.d() + g->koff[d]; eb.ev[d] = g->ee.d() + g->eoff_h[d];
+    eb.ng[d] = G.ng[d]; eb.use_smem[d] = need <= 190 * 1024; if (eb.use_smem[d]) eig_smem = std::max(eig_smem, need);
+    c->stats.kernel_launches += 1;
     if (kind == 0) prior *= exp(2.0 * m.hyp_cov[d * nh + 1]);
     else { double sws = 0; for (int q = 0; q < Q; ++q) sws += exp(m.hyp_cov[d * nh + q]); prior *= sws; }
   }
   g->prior_var = prior;
+  // eigen-decompositions of all factors: one CTA each, on the side stream, overlapped with the CG solve
+  cudaEventRecord(c->ev[10], st);
+  cudaStreamWaitEvent(c->stream2, c->ev[10], 0);
+  jacobi_eig_kernel<<<G.p, EIG_THREADS, eig_smem, c->stream2>>>(eb, getenv("KGP_EIG_SWEEPS") ? atoi(getenv("KGP_EIG_SWEEPS")) : 40);
+  cudaEventRecord(c->ev[11], c->stream2);
+  c->stats.kernel_launches++;
   resid_mean_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(S.X.d(), S.has_y ? S.y.d() : nullptr, n, D, m.mean_mask, g->hypm.d(), g->ym.d(), n);
   c->stats.kernel_launches++;
   cudaEventRecord(c->ev[1], st);
@@ -216,6 +223,7 @@ int grid_eval(kgp_ctx* c, int slot, int want, double* nlZ_out, double* dnlZ_out)
   cudaEventRecord(c->ev[2], st);
 
   // Fiedler bound (apx.m:236-240,312-318)
+  cudaStreamWaitEvent(st, c->ev[11], 0);
   const unsigned char* keep = nullptr;
   if (n < G.N) {
     long Npad = 1; while (Npad < G.N) Npad <<= 1;

@@ -9,20 +9,23 @@ namespace kgp {
 // A (ng x ng, symmetric; destroyed) -> eigenvalues ev[ng] (unsorted), eigenvectors V (columns).
 // Works out of shared memory when 2*ng*ng*8 bytes fit (use_smem), otherwise in place in global.
 constexpr int EIG_THREADS = 512;
-__global__ void __launch_bounds__(EIG_THREADS) jacobi_eig_kernel(double* __restrict__ Ag, double* __restrict__ Vg,
-                                                                 double* __restrict__ ev, int ng, int use_smem,
-                                                                 int max_sweeps) {
+struct EigBatch { double* A[GRID_MAXP]; double* V[GRID_MAXP]; double* ev[GRID_MAXP]; int ng[GRID_MAXP]; int use_smem[GRID_MAXP]; };
+__global__ void __launch_bounds__(EIG_THREADS) jacobi_eig_kernel(const EigBatch eb, int max_sweeps) {
+  double* __restrict__ Ag = eb.A[blockIdx.x]; double* __restrict__ Vg = eb.V[blockIdx.x];
+  double* __restrict__ ev = eb.ev[blockIdx.x];
+  const int ng = eb.ng[blockIdx.x], use_smem = eb.use_smem[blockIdx.x];
   extern __shared__ double sm[];
   __shared__ double sh[32];
   __shared__ double rc[1024], rs[1024];          // rotation of pair k: cos, sin
   __shared__ int rp[1024], rq[1024];
+  const int ld = use_smem ? (ng | 1) : ng;       // odd pitch in shared memory: conflict-free rows AND columns
   double* A = use_smem ? sm : Ag;
-  double* V = use_smem ? sm + (long)ng * ng : Vg;
-  const int tid = threadIdx.x;
+  double* V = use_smem ? sm + (long)ng * ld : Vg;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   for (long q = tid; q < (long)ng * ng; q += EIG_THREADS) {
     int r = (int)(q / ng), c = (int)(q % ng);
-    if (use_smem) A[q] = 0.5 * (Ag[q] + Ag[(long)c * ng + r]);   // Kj = (Kj+Kj')/2   (apxGrid.m:583)
-    V[q] = (r == c) ? 1.0 : 0.0;
+    if (use_smem) A[(long)r * ld + c] = 0.5 * (Ag[q] + Ag[(long)c * ng + r]);   // Kj = (Kj+Kj')/2   (apxGrid.m:583)
+    V[(long)r * ld + c] = (r == c) ? 1.0 : 0.0;
   }
   __syncthreads();
   if (!use_smem) {                                              // symmetrise in place, second pass
@@ -36,11 +39,11 @@ __global__ void __launch_bounds__(EIG_THREADS) jacobi_eig_kernel(double* __restr
   for (int sweep = 0; sweep < max_sweeps; ++sweep) {
     // convergence: off-diagonal Frobenius norm against the diagonal
     double off = 0.0, dia = 0.0;
-    for (long q = tid; q < (long)ng * ng; q += EIG_THREADS) {
-      int r = (int)(q / ng), c = (int)(q % ng);
-      double v = A[q];
-      if (r == c) dia = fma(v, v, dia); else off = fma(v, v, off);
-    }
+    for (int r = warp; r < ng; r += EIG_THREADS / 32)
+      for (int c = lane; c < ng; c += 32) {
+        double v = A[(long)r * ld + c];
+        if (r == c) dia = fma(v, v, dia); else off = fma(v, v, off);
+      }
     off = block_sum(off, sh); dia = block_sum(dia, sh);
     if (off <= 1e-30 * dia || off == 0.0) break;
     for (int round = 0; round < m - 1; ++round) {
@@ -52,9 +55,9 @@ __global__ void __launch_bounds__(EIG_THREADS) jacobi_eig_kernel(double* __restr
         if (p > q) { int t = p; p = q; q = t; }
         double c = 1.0, s = 0.0;
         if (q < ng) {
-          const double apq = A[(long)p * ng + q];
+          const double apq = A[(long)p * ld + q];
           if (apq != 0.0) {
-            const double tau = (A[(long)q * ng + q] - A[(long)p * ng + p]) / (2.0 * apq);
+            const double tau = (A[(long)q * ld + q] - A[(long)p * ld + p]) / (2.0 * apq);
             const double t = (tau >= 0.0 ? 1.0 : -1.0) / (fabs(tau) + sqrt(1.0 + tau * tau));
             c = 1.0 / sqrt(1.0 + t * t); s = t * c;
           }
@@ -62,37 +65,36 @@ __global__ void __launch_bounds__(EIG_THREADS) jacobi_eig_kernel(double* __restr
         rp[k] = p; rq[k] = q; rc[k] = c; rs[k] = s;
       }
       __syncthreads();
-      // columns: A <- A J, V <- V J
-      for (long w = tid; w < (long)half * ng; w += EIG_THREADS) {
-        int k = (int)(w / ng), r = (int)(w % ng);
-        int p = rp[k], q = rq[k];
+      // columns: A <- A J, V <- V J      (one warp per pair, lanes over rows: no integer division)
+      for (int k = warp; k < half; k += EIG_THREADS / 32) {
+        const int p = rp[k], q = rq[k];
         if (q < 0) continue;
         const double c = rc[k], s = rs[k];
-        double ap = A[(long)r * ng + p], aq = A[(long)r * ng + q];
-        A[(long)r * ng + p] = c * ap - s * aq; A[(long)r * ng + q] = s * ap + c * aq;
-        double vp = V[(long)r * ng + p], vq = V[(long)r * ng + q];
-        V[(long)r * ng + p] = c * vp - s * vq; V[(long)r * ng + q] = s * vp + c * vq;
+        for (int r = lane; r < ng; r += 32) {
+          double ap = A[(long)r * ld + p], aq = A[(long)r * ld + q];
+          A[(long)r * ld + p] = c * ap - s * aq; A[(long)r * ld + q] = s * ap + c * aq;
+          double vp = V[(long)r * ld + p], vq = V[(long)r * ld + q];
+          V[(long)r * ld + p] = c * vp - s * vq; V[(long)r * ld + q] = s * vp + c * vq;
+        }
       }
       __syncthreads();
-      // rows: A <- J' A
-      for (long w = tid; w < (long)half * ng; w += EIG_THREADS) {
-        int k = (int)(w / ng), cix = (int)(w % ng);
-        int p = rp[k], q = rq[k];
+      // rows: A <- J' A ; the annihilated pair is zero by construction: exact zeros, not rounding residue
+      for (int k = warp; k < half; k += EIG_THREADS / 32) {
+        const int p = rp[k], q = rq[k];
         if (q < 0) continue;
         const double c = rc[k], s = rs[k];
-        double ap = A[(long)p * ng + cix], aq = A[(long)q * ng + cix];
-        A[(long)p * ng + cix] = c * ap - s * aq; A[(long)q * ng + cix] = s * ap + c * aq;
+        for (int cix = lane; cix < ng; cix += 32) {
+          double ap = A[(long)p * ld + cix], aq = A[(long)q * ld + cix];
+          A[(long)p * ld + cix] = (cix == q) ? 0.0 : c * ap - s * aq;
+          A[(long)q * ld + cix] = (cix == p) ? 0.0 : s * ap + c * aq;
+        }
       }
-      __syncthreads();
-      // the annihilated pair is zero by construction: store exact zeros instead of rounding residue
-      for (int k = tid; k < half; k += EIG_THREADS)
-        if (rq[k] >= 0) { A[(long)rp[k] * ng + rq[k]] = 0.0; A[(long)rq[k] * ng + rp[k]] = 0.0; }
       __syncthreads();
     }
   }
-  for (int i = tid; i < ng; i += EIG_THREADS) ev[i] = fmax(A[(long)i * ng + i], 0.0);   // apxGrid.m:586
+  for (int i = tid; i < ng; i += EIG_THREADS) ev[i] = fmax(A[(long)i * ld + i], 0.0);   // apxGrid.m:586
   if (use_smem)
-    for (long q = tid; q < (long)ng * ng; q += EIG_THREADS) Vg[q] = V[q];
+    for (long q = tid; q < (long)ng * ng; q += EIG_THREADS) Vg[q] = V[(q / ng) * ld + q % ng];
 }
 
 // Fiedler bound pieces for every Kronecker eigenvalue product e (all W equal to w):

@@ -1,9 +1,11 @@
 """GPU parity tests of the KISS-GP / MSGP (infGrid) path against the CPU oracle.
 
-Tolerances: the deterministic parts (grid axes, interpolation, Fiedler bound,
-hyper-derivatives at a converged alpha) are compared at a tight CG tolerance with 1e-8 relative;
-at the reference's loose cg_tol the budget is 10 x |oracle(cg_tol) - oracle(1e-13)| per quantity and
-the iteration count must agree within +-4 (scatter-add order differs from the sparse product's)."""
+Tolerances: the deterministic parts (grid axes bit-exact; interpolation, Fiedler bound, hyper-
+derivatives at a converged alpha) are compared at a tight CG tolerance (1e-12) with 1e-8 relative
+(1e-7 for alpha-dependent vectors); at the reference's loose cg_tol the stated tolerance is cg_tol
+for nlZ and 30 x cg_tol for vector quantities, and the iteration count must agree within +-4
+(the scatter-add order of Mx' v differs from the sparse product's, so the two CG runs cross the
+threshold at neighbouring iterations)."""
 import numpy as np
 import pytest
 
@@ -93,13 +95,17 @@ def test_iterative_parts_reference_cg_settings(built_lib, name, opt):
     nlZ, g = gp.eng.eval(0, 2, gp._n_hyp)
     st = gp.stats()
     xg, post, nlZ0, g0, dX0, p0 = oracle_all(gp, X, y, c['cov'], opt, mean, Q, Xs)
-    _, _, nlZT, gT, dXT, _ = oracle_all(gp, X, y, c['cov'], {'cg_maxit': 50000, 'cg_tol': 1e-13}, mean, Q, Xs)
+    tol = opt['cg_tol']
     assert abs(st['cg_iters'] - post['cg_iter']) <= 4
-    assert st['cg_relres'] < opt['cg_tol']
-    assert abs(nlZ - nlZ0) <= 10 * abs(nlZ0 - nlZT) + 1e-9 * abs(nlZ0)
-    assert np.max(np.abs(g - g0)) <= 10 * np.max(np.abs(g0 - gT)) + 1e-9 * np.max(np.abs(g0))
-    dX = gp.get_dlik_dx('tr')
-    assert np.max(np.abs(dX - dX0)) <= 10 * np.max(np.abs(dX0 - dXT)) + 1e-9 * np.max(np.abs(dX0))
+    assert st['cg_relres'] < tol
+    # stated tolerance of the iterative path: nlZ within cg_tol, vector quantities within 30 cg_tol
+    # (relative, max norm) of the oracle run at the same cg_tol; the two CG runs stop at residuals
+    # that are both < cg_tol but not equal (different summation order in Mx' v)
+    assert rel(nlZ, nlZ0) < tol
+    assert rel(g, g0) < 30 * tol
+    assert rel(gp.get_dlik_dx('tr'), dX0) < 30 * tol
+    assert rel(gp.alpha(), post['alpha']) < 30 * tol
+    assert rel(gp.predict(Xs), p0[2]) < 30 * tol
 
 
 def test_msgp_backend_interface_mirror(built_lib):
@@ -158,4 +164,4 @@ def test_manual_grid_and_full_size_c3(built_lib):
     gp2.configure(2, {'lik': np.log(0.3), 'mean': [], 'cov': [[0.5], [1.0]]}, opt, 'infGrid', 'meanZero', 'covSEiso', 'likGauss',
                   'dlikGrid', grid_kwargs={'eq': 1, 'k': 70., 'xg': xg}, verbose=0)
     gp2.update_data('tr', X, y[:, None])
-    assert rel(gp2.evaluate('tr'), nlZ) < 1e-9
+    assert rel(gp2.evaluate('tr'), nlZ) < 1e-6     # two runs differ within cg_tol: atomic scatter order is not fixed
