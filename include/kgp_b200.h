@@ -64,6 +64,9 @@ typedef struct {
   int    cg_iters; double cg_relres;   /* grid path */
   int    potrf_info;      /* 0 or 1-based index of the failing pivot */
   long   n, np;           /* problem size and padded size */
+  /* dgemm_nt launches by call site (profiling on): 0 potrf panel update, 1 potrf trailing SYRK,
+   * 2 Z-sweep GEMM, 3 trsm block update, 4 Z Z^T, 5 predict */
+  double gemm_class_ms[8], gemm_class_flops[8];
 } kgp_stats;
 
 /* lifetime ------------------------------------------------------------------- */

@@ -29,10 +29,11 @@ class KgpStats(C.Structure):
                 ('ms_inverse', C.c_double), ('ms_reduce', C.c_double), ('ms_solve', C.c_double),
                 ('ms_gemm', C.c_double), ('gemm_flops', C.c_double), ('gemm_launches', C.c_long),
                 ('kernel_launches', C.c_long), ('cg_iters', C.c_int), ('cg_relres', C.c_double),
-                ('potrf_info', C.c_int), ('n', C.c_long), ('np', C.c_long)]
+                ('potrf_info', C.c_int), ('n', C.c_long), ('np', C.c_long),
+                ('gemm_class_ms', C.c_double * 8), ('gemm_class_flops', C.c_double * 8)]
 
     def as_dict(self):
-        return {k: getattr(self, k) for k, _ in self._fields_}
+        return {k: (list(getattr(self, k)) if k.startswith('gemm_class') else getattr(self, k)) for k, _ in self._fields_}
 
 
 class KgpError(RuntimeError):

@@ -54,7 +54,7 @@ struct kgp_ctx {
   kgp::Grid grid;
   kgp_stats stats;
   int profiling = 0;
-  std::vector<cudaEvent_t> gev; size_t gev_used = 0;   // event pairs around dgemm_nt launches (profiling)
+  std::vector<cudaEvent_t> gev; size_t gev_used = 0; std::vector<int> gev_class; std::vector<double> gev_flops; int gemm_class = 0;   // event pairs around dgemm_nt launches (profiling)
 
   // exact-path device state
   kgp::DevBuf M, W2, Dws;             // L (lower) | Z upper -> full B^{-1} | diagonal nb-blocks of B^{-1}

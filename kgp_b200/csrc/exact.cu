@@ -19,7 +19,7 @@
 
 namespace kgp {
 
-static inline void count_gemm(kgp_ctx* c, const GemmArgs& g) {
+static inline double count_gemm(kgp_ctx* c, const GemmArgs& g) {
   c->stats.gemm_launches++; c->stats.kernel_launches++;
   double f = 0.0;
   for (int tm = 0; tm < g.ntm; ++tm) {
@@ -28,10 +28,11 @@ static inline void count_gemm(kgp_ctx* c, const GemmArgs& g) {
     f += 2.0 * 128.0 * 128.0 * (double)(g.kend - kb) * ntn;
   }
   c->stats.gemm_flops += f;
+  return f;
 }
 static inline void gemm(kgp_ctx* c, const GemmArgs& g) {
   if (g.ntm <= 0 || g.ntn <= 0) return;
-  count_gemm(c, g);
+  const double fl = count_gemm(c, g);
   if (c->profiling) {
     if (c->gev_used + 2 > c->gev.size()) {
       size_t old = c->gev.size(); c->gev.resize(old + 256);
@@ -40,13 +41,17 @@ static inline void gemm(kgp_ctx* c, const GemmArgs& g) {
     cudaEventRecord(c->gev[c->gev_used], c->stream);
     gemm_launch(g, c->stream);
     cudaEventRecord(c->gev[c->gev_used + 1], c->stream);
+    c->gev_class.push_back(c->gemm_class); c->gev_flops.push_back(fl);
     c->gev_used += 2;
   } else gemm_launch(g, c->stream);
 }
 static void gemm_prof_collect(kgp_ctx* c) {
   double ms = 0.0;
-  for (size_t i = 0; i + 1 < c->gev_used; i += 2) { float t = 0; cudaEventElapsedTime(&t, c->gev[i], c->gev[i + 1]); ms += t; }
-  c->stats.ms_gemm = ms; c->gev_used = 0;
+  for (size_t i = 0; i + 1 < c->gev_used; i += 2) {
+    float t = 0; cudaEventElapsedTime(&t, c->gev[i], c->gev[i + 1]); ms += t;
+    int cl = c->gev_class[i / 2] & 7; c->stats.gemm_class_ms[cl] += t; c->stats.gemm_class_flops[cl] += c->gev_flops[i / 2];
+  }
+  c->stats.ms_gemm = ms; c->gev_used = 0; c->gev_class.clear(); c->gev_flops.clear();
 }
 static inline GemmArgs mkgemm(const double* A, long lda, const double* B, long ldb, double* C, long ldc,
                               int ntm, int ntn, int kbeg, int kend, int shape, int ktri, double alpha, double beta) {
@@ -64,6 +69,7 @@ static void trsm_block(kgp_ctx* c, double* X, long ldx, long mrows, const double
     trsm128_rows_kernel<<<(unsigned)(mrows / 128), TR_THREADS, TR_SMEM, c->stream>>>(
         X + cb * 128, ldx, mrows, Lblk + (long)cb * 128 * ldl + cb * 128, ldl);
     c->stats.kernel_launches++;
+    if (cb + 1 < nc) c->gemm_class = 3;
     if (cb + 1 < nc)
       gemm(c, mkgemm(X + cb * 128, ldx, Lblk + (long)(cb + 1) * 128 * ldl + cb * 128, ldl,
                      X + (cb + 1) * 128, ldx, (int)(mrows / 128), nc - cb - 1, 0, 128, GEMM_FULL, KTRI_NONE, -1.0, 1.0));
@@ -84,12 +90,14 @@ static void potrf(kgp_ctx* c) {
             M + r0 * ld + j, ld, mrows, M + j * ld + j, ld);
         c->stats.kernel_launches++;
         const long ncols = k0 + w - r0;
+        c->gemm_class = 0;
         if (ncols > 0)
           gemm(c, mkgemm(M + r0 * ld + j, ld, M + r0 * ld + j, ld, M + r0 * ld + r0, ld,
                          (int)(mrows / 128), (int)(ncols / 128), 0, 128, GEMM_LOWER, KTRI_NONE, -1.0, 1.0));
       }
     }
     const long r0 = k0 + w, mt = (np - r0) / 128;
+    c->gemm_class = 1;
     if (mt > 0)
       gemm(c, mkgemm(M + r0 * ld + k0, ld, M + r0 * ld + k0, ld, M + r0 * ld + r0, ld,
                      (int)mt, (int)mt, 0, w, GEMM_LOWER, KTRI_NONE, -1.0, 1.0));
@@ -101,6 +109,7 @@ static void zsweep(kgp_ctx* c) {
   const double* M = c->M.d(); double* W = c->W2.d(); const long ld = c->np, np = c->np;
   for (long k0 = 0; k0 < np; k0 += NB) {
     const int w = (int)((np - k0 < NB) ? np - k0 : NB);
+    c->gemm_class = 2;
     if (k0 > 0)
       gemm(c, mkgemm(W, ld, M + k0 * ld, ld, W + k0, ld, (int)(k0 / 128), w / 128, 0, (int)k0,
                      GEMM_FULL, KTRI_FROM_M0, -1.0, 0.0));
@@ -115,6 +124,7 @@ static void zzt(kgp_ctx* c) {
   double* W = c->W2.d(); const long ld = c->np; const int nt = (int)(c->np / 128);
   GemmArgs g = mkgemm(W, ld, W, ld, W, ld, nt, nt, 0, (int)c->np, GEMM_LOWER, KTRI_FROM_M0, 1.0, 0.0);
   g.Cdiag = c->Dws.d(); g.nb = NB; g.cdiag_only = 0;
+  c->gemm_class = 4;
   gemm(c, g);
   dim3 grid((unsigned)(c->np / 32), (unsigned)(c->np / 32)), blk(32, 8);
   mirror_finalize_kernel<<<grid, blk, 0, c->stream>>>(W, ld, c->np, c->Dws.d(), NB);
@@ -334,6 +344,7 @@ int exact_predict(kgp_ctx* c, const double* Xs, long ns, double* ymu, double* ys
         const int w = (int)((np - k0 < NB) ? np - k0 : NB);
         trsm_block(c, X + k0, np, nsp, M + k0 * np + k0, np, w);
         const long rest = np - k0 - w;
+        c->gemm_class = 5;
         if (rest > 0)
           gemm(c, mkgemm(X + k0, np, M + (k0 + w) * np + k0, np, X + k0 + w, np, (int)(nsp / 128), (int)(rest / 128),
                          0, w, GEMM_FULL, KTRI_NONE, -1.0, 1.0));
