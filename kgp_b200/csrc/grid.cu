@@ -7,7 +7,7 @@
 // the whole CG iteration is device-resident (scalars, convergence flag and iteration count live
 // in device memory; the host only polls the flag every few iterations).
 #include "ctx.h"
-#include "grid_kernels3.cuh"
+#include "grid_cg.cuh"
 #include <math.h>
 #include <string.h>
 #include <algorithm>
@@ -17,6 +17,12 @@ namespace kgp {
 struct GridState {
   DevBuf axes, Kf, Vf, Af, ee, eoff, de, zv, Qm, Pm, g0, g1, tgrid, beta;
   DevBuf x, r, d, z, ym, partA, partB, S, hyp, hypm, dX, dhyp, out, sortk, sorti, keep, dmean;
+  // cell-sorted CG state (grid_cg.cuh)
+  DevBuf U, perm, sx, sr, sd, sz, ctl, cnt, KfT, gm0, gm1;
+  double* h_ctl = nullptr;                // pinned host copy of the control blocks
+  long npad = 0; int sort_slot = -1; unsigned long sort_slot_ver = 0, sort_grid_ver = 0;
+  cudaGraphExec_t cg_graph = nullptr; std::vector<char> cg_graph_key;
+  DevBuf pdz, prr, bar; int num_sms = 0; size_t smem_optin = 0; int cg_level_used = -1;
   int p = 0; int ng[GRID_MAXP] = {0}; long N = 0;
   long koff[GRID_MAXP] = {0};            // offsets of factor i inside Kf / Vf
   int eoff_h[GRID_MAXP] = {0};
@@ -35,8 +41,11 @@ void grid_free(kgp_ctx* c) {
   GridState* g = (GridState*)c->gridstate;
   DevBuf* bufs[] = {&g->axes, &g->Kf, &g->Vf, &g->Af, &g->ee, &g->eoff, &g->de, &g->zv, &g->Qm, &g->Pm, &g->g0, &g->g1,
                     &g->tgrid, &g->beta, &g->x, &g->r, &g->d, &g->z, &g->ym, &g->partA, &g->partB, &g->S, &g->hyp,
-                    &g->hypm, &g->dX, &g->dhyp, &g->out, &g->sortk, &g->sorti, &g->keep, &g->dmean};
+                    &g->hypm, &g->dX, &g->dhyp, &g->out, &g->sortk, &g->sorti, &g->keep, &g->dmean,
+                    &g->U, &g->perm, &g->sx, &g->sr, &g->sd, &g->sz, &g->ctl, &g->cnt, &g->KfT, &g->gm0, &g->gm1, &g->pdz, &g->prr, &g->bar};
   for (DevBuf* b : bufs) b->release();
+  if (g->h_ctl) cudaFreeHost(g->h_ctl);
+  if (g->cg_graph) cudaGraphExecDestroy(g->cg_graph);
   delete g; c->gridstate = nullptr;
 }
 
@@ -106,6 +115,7 @@ static int ensure_grid_buffers(kgp_ctx* c, GridState* g, const GridDesc& G, long
   long ksz = 0; int esz = 0, ngmax = 0;
   for (int d = 0; d < G.p; ++d) { ksz += (long)G.ng[d] * G.ng[d]; esz += G.ng[d]; ngmax = std::max(ngmax, G.ng[d]); }
   KGP_CUDA(c, g->Kf.ensure(ksz * 8)); KGP_CUDA(c, g->Vf.ensure(ksz * 8)); KGP_CUDA(c, g->Af.ensure(ksz * 8));
+  KGP_CUDA(c, g->KfT.ensure((long)G.ng[0] * G.ng[0] * 8));
   KGP_CUDA(c, g->ee.ensure(esz * 8)); KGP_CUDA(c, g->eoff.ensure(GRID_MAXP * 4));
   KGP_CUDA(c, g->de.ensure(G.N * 8)); KGP_CUDA(c, g->zv.ensure(ngmax * 8));
   KGP_CUDA(c, g->Qm.ensure((long)ngmax * ngmax * 8)); KGP_CUDA(c, g->Pm.ensure((long)ngmax * ngmax * 8));
@@ -161,6 +171,205 @@ static int cg_solve(kgp_ctx* c, GridState* g, const GridDesc& G, const double* X
   return KGP_OK;
 }
 
+// ---- cell-sorted CG (grid_cg.cuh): 1-D and 2-D grids -------------------------------------------------
+constexpr int CG_MAXCOLS = 64;            // right-hand sides per batched solve
+constexpr int CG_CHECK = 16;              // iterations per graph launch (the host polls the flags in between)
+
+// permutation of the points by interpolation cell + their pre-divided coordinates; cached per (data, grid)
+static int cg_prepare_sorted(kgp_ctx* c, GridState* g, const GridDesc& G, int slot) {
+  Slot& S = c->slots[slot];
+  if (g->sort_slot == slot && g->sort_slot_ver == S.version && g->sort_grid_ver == c->grid.version && g->npad > 0) return KGP_OK;
+  const long n = S.n; const int D = S.D;
+  cudaStream_t st = c->stream;
+  const long npad = ((n + CG_SUB - 1) / CG_SUB) * CG_SUB;
+  long Npad = 1; while (Npad < n) Npad <<= 1;
+  KGP_CUDA(c, g->sortk.ensure(Npad * 8)); KGP_CUDA(c, g->sorti.ensure(Npad * 4));
+  KGP_CUDA(c, g->perm.ensure(n * 4)); KGP_CUDA(c, g->U.ensure(npad * G.p * 8));
+  const unsigned nb = (unsigned)((Npad + 255) / 256);
+  if (G.p == 1) cg_cellkey_kernel<1><<<nb, 256, 0, st>>>(G, S.X.d(), n, D, g->sortk.d(), (int*)g->sorti.p, Npad);
+  else cg_cellkey_kernel<2><<<nb, 256, 0, st>>>(G, S.X.d(), n, D, g->sortk.d(), (int*)g->sorti.p, Npad);
+  for (long k = 2; k <= Npad; k <<= 1)
+    for (long j = k >> 1; j > 0; j >>= 1)
+      bitonic_stage_kernel<<<nb, 256, 0, st>>>(g->sortk.d(), (int*)g->sorti.p, Npad, j, k);
+  KGP_CUDA(c, cudaMemcpyAsync(g->perm.p, g->sorti.p, n * 4, cudaMemcpyDeviceToDevice, st));
+  const unsigned nb2 = (unsigned)((npad + 255) / 256);
+  if (G.p == 1) cg_sorted_coords_kernel<1><<<nb2, 256, 0, st>>>(G, S.X.d(), n, D, (const int*)g->perm.p, npad, g->U.d());
+  else cg_sorted_coords_kernel<2><<<nb2, 256, 0, st>>>(G, S.X.d(), n, D, (const int*)g->perm.p, npad, g->U.d());
+  KGP_CUDA(c, cudaGetLastError());
+  g->npad = npad; g->sort_slot = slot; g->sort_slot_ver = S.version; g->sort_grid_ver = c->grid.version;
+  return KGP_OK;
+}
+
+struct CgLaunch { GridDesc G; long n, npad, N; int m, sub, ctas; double *U, *sx, *sr, *sd, *sz, *ctl, *gm0, *gm1, *Kf, *KfT; unsigned* cnt; long koff1; };
+
+// one CG iteration (apx.m:290-300) as kernel launches on st
+static void cg_iteration(kgp_ctx* c, GridState* g, const CgLaunch& L, cudaStream_t st) {
+  const GridDesc& G = L.G;
+  dim3 grid((unsigned)L.ctas, (unsigned)L.m);
+  double* u;
+  if (G.p == 1) {
+    cg_scatter_kernel<1><<<grid, 256, 0, st>>>(G, L.U, L.npad, L.sr, L.sd, L.ctl, L.gm0);
+    dim3 kg((unsigned)((G.N + 255) / 256), 1);
+    for (int col = 0; col < L.m; ++col)
+      mode_product_kernel<<<kg, 256, 0, st>>>(L.Kf, G.ng[0], L.gm0 + col * G.N, L.gm1 + col * G.N, 1, 1);
+    u = L.gm1;
+    cg_gather_kernel<1><<<grid, 256, 0, st>>>(G, L.U, L.n, L.npad, u, L.sd, L.sz, L.ctl, L.cnt);
+  } else {
+    cg_scatter_kernel<2><<<grid, 256, 0, st>>>(G, L.U, L.npad, L.sr, L.sd, L.ctl, L.gm0);
+    int TA = (G.ng[0] + 31) & ~31; if (TA > 256) TA = 256;
+    const size_t ksm = (size_t)(KRON2_THREADS / TA + 1) * G.ng[0] * 8;
+    kron2_kernel<<<dim3((unsigned)G.ng[1], (unsigned)L.m), KRON2_THREADS, ksm, st>>>(L.KfT, L.Kf + L.koff1, G.ng[0], G.ng[1], L.gm0, L.gm1, L.ctl);
+    u = L.gm1;
+    cg_gather_kernel<2><<<grid, 256, 0, st>>>(G, L.U, L.n, L.npad, u, L.sd, L.sz, L.ctl, L.cnt);
+  }
+  cg_update_kernel<<<grid, 256, 0, st>>>(L.npad, L.sx, L.sr, L.sd, L.sz, L.ctl, L.cnt, L.gm0, G.N);
+}
+static int cg_launches_per_iteration(const CgLaunch& L) { return L.G.p == 1 ? 3 + L.m : 4; }
+
+// whole solve in one cooperative launch (cg_persistent_kernel); returns -1 when the configuration does not fit
+template <int P, int LEVEL>
+static cudaError_t launch_persistent(const CgPersist& A, int ctas, size_t smem, cudaStream_t st) {
+  cudaError_t e = cudaFuncSetAttribute(cg_persistent_kernel<P, LEVEL>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  if (e != cudaSuccess) return e;
+  void* args[] = {(void*)&A};
+  return cudaLaunchCooperativeKernel((const void*)cg_persistent_kernel<P, LEVEL>, dim3((unsigned)ctas), dim3(CGP_THREADS), args, smem, st);
+}
+static int cg_finish(kgp_ctx* c, GridState* g, int m) {
+  int iters = 0, bad = -1; double rel = 0.0;
+  for (int col = 0; col < m; ++col) {
+    const double* ct = g->h_ctl + col * CT_STRIDE;
+    iters = std::max(iters, (int)ct[CT_ITER]); if (ct[CT_RELRES] > rel) rel = ct[CT_RELRES];
+    if (ct[CT_DONE] != 1.0 && bad < 0) bad = col;
+  }
+  c->stats.cg_iters = iters; c->stats.cg_relres = rel;
+  if (bad >= 0)
+    return c->fail(KGP_CG_NOT_CONVERGED, "Not converged after %d iterations, r=%1.2e", (int)g->h_ctl[bad * CT_STRIDE + CT_ITER],
+                   g->h_ctl[bad * CT_STRIDE + CT_RELRES]);
+  return KGP_OK;
+}
+static int cg_run_persistent(kgp_ctx* c, GridState* g, const CgLaunch& L, int maxit) {
+  const GridDesc& G = L.G; cudaStream_t st = c->stream;
+  if (!g->num_sms) {
+    int v = 0; cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, c->device); g->num_sms = v;
+    cudaDeviceGetAttribute(&v, cudaDevAttrMaxSharedMemoryPerBlockOptin, c->device); g->smem_optin = (size_t)v;
+    int coop = 0; cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, c->device);
+    if (!coop) g->num_sms = -1;
+  }
+  if (getenv("KGP_DEBUG")) fprintf(stderr, "[kgp] persistent CG: sms %d optin %zu\n", g->num_sms, g->smem_optin);
+  if (g->num_sms <= 0 || G.p > 2) return -1;
+  const int ctas = g->num_sms;
+  const long nunits = L.npad / 128;
+  const int upc = (int)((nunits + ctas - 1) / ctas);
+  int TA = (G.ng[0] + 31) & ~31; if (TA > CGP_THREADS) TA = CGP_THREADS;
+  const size_t kscr = (((size_t)(CGP_THREADS / TA + 1) * G.ng[0] + 1) & ~(size_t)1) * 8 + (size_t)(CGP_THREADS / 32) * CGP_WSCR * 8;
+  const size_t budget = g->smem_optin - 6 * 1024;                      // static shared of the kernel (< 6 KB)
+  const size_t s1 = kscr + (size_t)upc * 128 * G.p * 8, s2 = s1 + (size_t)upc * 128 * 16;
+  static const int force_level = getenv("KGP_CG_LEVEL") ? atoi(getenv("KGP_CG_LEVEL")) : 2;
+  int level = 0; size_t smem = kscr;
+  if (kscr > budget) return -1;
+  if (s1 <= budget && force_level >= 1) { level = 1; smem = s1; }
+  if (L.m == 1 && s2 <= budget && force_level >= 2) { level = 2; smem = s2; }
+  KGP_CUDA(c, g->pdz.ensure((size_t)L.m * ctas * 8)); KGP_CUDA(c, g->prr.ensure((size_t)L.m * ctas * 8));
+  KGP_CUDA(c, g->bar.ensure(256));
+  KGP_CUDA(c, cudaMemsetAsync(g->bar.p, 0, 256, st));
+  CgPersist A; memset(&A, 0, sizeof A);
+  A.G = G; A.U = L.U; A.n = L.n; A.npad = L.npad; A.m = L.m; A.upc = upc;
+  A.x = L.sx; A.r = L.sr; A.d = L.sd; A.z = L.sz; A.g0 = L.gm0; A.ug = L.gm1;
+  A.K0 = L.Kf; A.K0T = L.KfT; A.K1 = L.Kf + L.koff1;
+  A.ctl = L.ctl; A.part_dz = g->pdz.d(); A.part_rr = g->prr.d(); A.bar = (unsigned*)g->bar.p;
+  A.dbg = getenv("KGP_DEBUG") ? (long long*)((char*)g->bar.p + 128) : nullptr;
+  cudaError_t e;
+  if (G.p == 1) e = level == 2 ? launch_persistent<1, 2>(A, ctas, smem, st) : level == 1 ? launch_persistent<1, 1>(A, ctas, smem, st) : launch_persistent<1, 0>(A, ctas, smem, st);
+  else e = level == 2 ? launch_persistent<2, 2>(A, ctas, smem, st) : level == 1 ? launch_persistent<2, 1>(A, ctas, smem, st) : launch_persistent<2, 0>(A, ctas, smem, st);
+  KGP_CUDA(c, e);
+  g->cg_level_used = level;
+  c->stats.kernel_launches += 1;
+  if (getenv("KGP_DEBUG")) fprintf(stderr, "[kgp] persistent CG: ctas %d upc %d level %d smem %zu m %d\n", ctas, upc, level, smem, L.m);
+  KGP_CUDA(c, cudaMemcpyAsync(g->h_ctl, g->ctl.p, (size_t)L.m * CT_STRIDE * 8, cudaMemcpyDeviceToHost, st));
+  KGP_CUDA(c, cudaStreamSynchronize(st));
+  KGP_CUDA(c, cudaGetLastError());
+  (void)maxit;
+  if (A.dbg) {
+    long long tk[8]; cudaMemcpy(tk, A.dbg, sizeof tk, cudaMemcpyDeviceToHost);
+    const double it = std::max(1.0, g->h_ctl[CT_ITER] - 1.0), f = 1e-3 / 1.965 / it;   // us per iteration at 1.965 GHz
+    fprintf(stderr, "[kgp] us/iter: A %.2f bar %.2f | B %.2f bar %.2f | C %.2f bar %.2f | D %.2f bar %.2f\n", tk[0] * f, tk[1] * f,
+            tk[2] * f, tk[3] * f, tk[4] * f, tk[5] * f, tk[6] * f, tk[7] * f);
+  }
+  return cg_finish(c, g, L.m);
+}
+
+// x = CG(B, sw * rhs[:, col]) for m columns at once (sorted order, result in g->sx); rhs in ORIGINAL point order
+static int cg_solve_sorted(kgp_ctx* c, GridState* g, const GridDesc& G, int slot, const double* rhs, long rhs_stride, int m,
+                           double sw, double tol, int maxit) {
+  if (m < 1 || m > CG_MAXCOLS) return c->fail(KGP_BAD_ARG, "CG batch of %d columns (max %d)", m, CG_MAXCOLS);
+  int rc = cg_prepare_sorted(c, g, G, slot); if (rc) return rc;
+  Slot& S = c->slots[slot];
+  const long n = S.n, npad = g->npad;
+  cudaStream_t st = c->stream;
+  DevBuf* vecs[] = {&g->sx, &g->sr, &g->sd, &g->sz};
+  for (DevBuf* b : vecs) KGP_CUDA(c, b->ensure((size_t)m * npad * 8));
+  KGP_CUDA(c, g->gm0.ensure((size_t)m * G.N * 8)); KGP_CUDA(c, g->gm1.ensure((size_t)m * G.N * 8));
+  KGP_CUDA(c, g->ctl.ensure(CG_MAXCOLS * CT_STRIDE * 8)); KGP_CUDA(c, g->cnt.ensure(CG_MAXCOLS * 4 * 4));
+  if (!g->h_ctl) KGP_CUDA(c, cudaMallocHost((void**)&g->h_ctl, CG_MAXCOLS * CT_STRIDE * 8));
+  CgLaunch L; memset(&L, 0, sizeof L);
+  L.G = G; L.n = n; L.npad = npad; L.N = G.N; L.m = m;
+  L.sub = 0; L.ctas = (int)std::min<long>(npad / CG_SUB, 148 * 3);     // warps stride over 128-point units
+  L.U = g->U.d(); L.sx = g->sx.d(); L.sr = g->sr.d(); L.sd = g->sd.d(); L.sz = g->sz.d(); L.ctl = g->ctl.d();
+  L.gm0 = g->gm0.d(); L.gm1 = g->gm1.d(); L.Kf = g->Kf.d(); L.KfT = g->KfT.d(); L.cnt = (unsigned*)g->cnt.p;
+  L.koff1 = G.p > 1 ? g->koff[1] : 0;
+
+  KGP_CUDA(c, cudaMemsetAsync(g->cnt.p, 0, CG_MAXCOLS * 4 * 4, st));
+  KGP_CUDA(c, cudaMemsetAsync(g->ctl.p, 0, CG_MAXCOLS * CT_STRIDE * 8, st));
+  KGP_CUDA(c, cudaMemsetAsync(g->gm0.p, 0, (size_t)m * G.N * 8, st));
+  cg_init_sorted_kernel<<<dim3((unsigned)std::min<long>(npad / 256, 1184), (unsigned)m), 256, 0, st>>>(
+      rhs, rhs_stride, (const int*)g->perm.p, n, npad, sw, tol, maxit, L.sx, L.sr, L.sd, L.ctl, L.cnt);
+  c->stats.kernel_launches += 1;
+
+  static const int cg_mode = getenv("KGP_CG_MODE") ? atoi(getenv("KGP_CG_MODE")) : 2;     // 2 persistent, 1 streaming kernels
+  if (cg_mode == 2) {
+    rc = cg_run_persistent(c, g, L, maxit);
+    if (rc != -1) return rc;                                  // -1: does not fit -> streaming kernels below
+  }
+  static const bool use_graph = !(getenv("KGP_CG_GRAPH") && atoi(getenv("KGP_CG_GRAPH")) == 0);
+  if (use_graph) {
+    std::vector<char> key(sizeof L); memcpy(key.data(), &L, sizeof L);
+    if (!g->cg_graph || key != g->cg_graph_key) {
+      if (g->cg_graph) { cudaGraphExecDestroy(g->cg_graph); g->cg_graph = nullptr; }
+      cudaGraph_t graph = nullptr;
+      KGP_CUDA(c, cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal));
+      for (int it = 0; it < CG_CHECK; ++it) cg_iteration(c, g, L, st);
+      KGP_CUDA(c, cudaStreamEndCapture(st, &graph));
+      KGP_CUDA(c, cudaGraphInstantiate(&g->cg_graph, graph, 0));
+      cudaGraphDestroy(graph);
+      g->cg_graph_key = key;
+    }
+  }
+  bool done = false; int launched = 0;
+  const int lim = maxit + CG_CHECK;       // the device stops itself at maxit; this only bounds the host loop
+  while (!done && launched < lim) {
+    if (use_graph) KGP_CUDA(c, cudaGraphLaunch(g->cg_graph, st));
+    else for (int it = 0; it < CG_CHECK; ++it) cg_iteration(c, g, L, st);
+    launched += CG_CHECK;
+    c->stats.kernel_launches += (long)CG_CHECK * cg_launches_per_iteration(L);
+    KGP_CUDA(c, cudaMemcpyAsync(g->h_ctl, g->ctl.p, (size_t)m * CT_STRIDE * 8, cudaMemcpyDeviceToHost, st));
+    KGP_CUDA(c, cudaStreamSynchronize(st));
+    done = true;
+    for (int col = 0; col < m; ++col) if (g->h_ctl[col * CT_STRIDE + CT_DONE] == 0.0) done = false;
+  }
+  KGP_CUDA(c, cudaGetLastError());
+  int iters = 0, bad = -1; double rel = 0.0;
+  for (int col = 0; col < m; ++col) {
+    const double* ct = g->h_ctl + col * CT_STRIDE;
+    iters = std::max(iters, (int)ct[CT_ITER]); if (ct[CT_RELRES] > rel) rel = ct[CT_RELRES];
+    if (ct[CT_DONE] != 1.0 && bad < 0) bad = col;
+  }
+  c->stats.cg_iters = iters; c->stats.cg_relres = rel;
+  if (bad >= 0)
+    return c->fail(KGP_CG_NOT_CONVERGED, "Not converged after %d iterations, r=%1.2e", (int)g->h_ctl[bad * CT_STRIDE + CT_ITER],
+                   g->h_ctl[bad * CT_STRIDE + CT_RELRES]);
+  return KGP_OK;
+}
+
 static bool gstate_valid(kgp_ctx* c, GridState* g, int slot, int level) {
   return g->st_level >= level && g->st_slot == slot && g->st_slot_ver == c->slots[slot].version &&
          g->st_model_ver == c->model.version && g->st_grid_ver == c->grid.version;
@@ -196,6 +405,7 @@ int grid_eval(kgp_ctx* c, int slot, int want, double* nlZ_out, double* dnlZ_out)
     const long nn = (long)G.ng[d] * G.ng[d];
     factor_build_kernel<<<(unsigned)((nn + 255) / 256), 256, 0, st>>>(kind, Q, g->hyp.d() + d * nh, G.ax[d], G.ng[d], am, g->Kf.d() + g->koff[d]);
     KGP_CUDA(c, cudaMemcpyAsync(g->Af.d() + g->koff[d], g->Kf.d() + g->koff[d], nn * 8, cudaMemcpyDeviceToDevice, st));
+    if (d == 0) transpose_small_kernel<<<(unsigned)((nn + 255) / 256), 256, 0, st>>>(g->Kf.d(), G.ng[0], g->KfT.d());
     const size_t need = 2 * (size_t)G.ng[d] * (G.ng[d] | 1) * 8;
     eb.A[d] = g->Af.d() + g->koff[d]; eb.V[d] = g->Vf.d() + g->koff[d]; eb.ev[d] = g->ee.d() + g->eoff_h[d];
     eb.ng[d] = G.ng[d]; eb.use_smem[d] = need <= 190 * 1024; if (eb.use_smem[d]) eig_smem = std::max(eig_smem, need);
@@ -215,9 +425,16 @@ int grid_eval(kgp_ctx* c, int slot, int want, double* nlZ_out, double* dnlZ_out)
   cudaEventRecord(c->ev[1], st);
 
   int maxit = m.opt.cg_maxit > 0 ? m.opt.cg_maxit : (int)std::min<long>(n, 20);
-  rc = cg_solve(c, g, G, S.X.d(), n, D, sw, m.opt.cg_tol, maxit);
-  if (rc) return rc;
-  axpy_scale_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(n, sw, g->x.d(), g->x.d());      // alpha = sW q
+  static const bool legacy_cg = getenv("KGP_CG_LEGACY") && atoi(getenv("KGP_CG_LEGACY"));
+  if (G.p <= 2 && !legacy_cg) {
+    rc = cg_solve_sorted(c, g, G, slot, g->ym.d(), n, 1, sw, m.opt.cg_tol, maxit);
+    if (rc) return rc;
+    cg_unsort_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(g->sx.d(), (const int*)g->perm.p, n, sw, g->x.d());   // alpha = sW q
+  } else {
+    rc = cg_solve(c, g, G, S.X.d(), n, D, sw, m.opt.cg_tol, maxit);
+    if (rc) return rc;
+    axpy_scale_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(n, sw, g->x.d(), g->x.d());      // alpha = sW q
+  }
   dot_kernel<<<1, 1024, 0, st>>>(g->ym.d(), g->x.d(), n, g->out.d() + 0);
   dot_kernel<<<1, 1024, 0, st>>>(g->x.d(), g->x.d(), n, g->out.d() + 1);
   cudaEventRecord(c->ev[2], st);
@@ -427,6 +644,7 @@ int grid_create(kgp_ctx* c, int slot, int eq, double k) {
 
 int grid_init(kgp_ctx* c) {
   KGP_CUDA(c, cudaFuncSetAttribute(jacobi_eig_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 190 * 1024));
+  KGP_CUDA(c, cudaFuncSetAttribute(kron2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024));
   KGP_CUDA(c, cudaFuncSetAttribute(interp_scatter_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024));
   KGP_CUDA(c, cudaFuncSetAttribute(interp_scatter_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024));
   KGP_CUDA(c, cudaFuncSetAttribute(interp_scatter_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024));

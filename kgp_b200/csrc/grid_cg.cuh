@@ -1,0 +1,733 @@
+// KISS-GP path, part 4: the conjugate-gradient solve in CELL-SORTED point order.
+//
+// Reference: conjgrad / linsolve (GPML/cov/apx.m:275-302) on B = I + sW Mx Kg Mx' sW with
+// per-column convergence masks (apx.m:296-298) and the `iter = 2..maxit` count (apx.m:289).
+//
+// Layout: points are sorted once per (data, grid) by the interpolation cell they fall into (the
+// clamped first node of eqinterp, apxGrid.m:505-523).  Per point the kernels stream only the
+// pre-divided grid coordinate u = (x - s0)/ds (same FP64 division as eqinterp, done once), so an
+// iteration touches  U (8P B, twice) + the CG vectors: n*(16P + 88) bytes -- SURVEY 8(d).
+// One iteration = 3 streaming kernels + the Kronecker MVM:
+//   scatter : d = r + beta d (fused), g0 += Mx'(sW d)  -- per-thread runs of 4 consecutive sorted
+//             points accumulate their 4^P node weights in registers, a warp-level segmented
+//             reduction (shuffles) merges equal cells, one RED.F64 per node and segment
+//   kron    : u = (K_2 kron K_1) g0                      (grid-sized, L2 resident)
+//   gather  : z = sW Mx u + d, d.z                       (node values cached per cell in registers)
+//   update  : x += a d, r -= a z, r.r, zero g0
+// All scalars (a, beta, relres, iteration count, convergence flag) live in a device control block
+// written by the LAST CTA of the producing kernel (ticket counter), so the whole loop replays as a
+// CUDA graph with no host involvement; the host polls the flag once per graph launch.
+// blockIdx.y = right-hand-side column (each column has its own control block -> the per-column
+// masks of apx.m:296-298).
+#pragma once
+#include "grid_kernels3.cuh"
+
+namespace kgp {
+
+enum { CT_A = 0, CT_BETA, CT_DONE, CT_ITER, CT_RELRES, CT_NB, CT_RRCUR, CT_ACC_RR, CT_ACC_DZ, CT_TOL, CT_MAXIT, CT_SW,
+       CT_STRIDE = 16 };
+constexpr int CG_PTS = 4;                     // consecutive sorted points per thread
+constexpr int CG_SUB = 256 * CG_PTS;          // points per CTA pass
+
+// ---- cubic convolution weights on a pre-divided coordinate --------------------------------------
+// kcub on its two branches with the operation order of kcub() (grid_kernels.cuh)
+__device__ __forceinline__ double kcub_in(double x) { return fma(fma(1.5, x, -2.5) * x, x, 1.0); }           // |x| <= 1
+__device__ __forceinline__ double kcub_out(double x) { return fma(fma(-0.5, x, 2.5) * x - 4.0, x, 2.0); }    // 1 <= |x| <= 2
+
+// encoded coordinate: up >= 0 -> u itself (regular point, floor(u) in [2, ns-3]);
+// up < 0 -> snapped to one node: code = -up-1, bits 0-1 = which of the 4 edge nodes, bit 2 = upper edge
+__device__ __forceinline__ double encode_u(const double* __restrict__ ax, int ns, double s0, double ds, double t) {
+  const double u = (t - s0) / ds;
+  double jf = floor(u);
+  if (jf < 2.0) {
+    int best = 0; double bd = fabs(ax[0] - t);
+#pragma unroll
+    for (int i = 1; i < 4; ++i) { double d = fabs(ax[i] - t); if (d < bd) { bd = d; best = i; } }
+    jf = 1.0;
+    if (!(jf > (double)(ns - 3))) return -(double)(best + 1);
+  }
+  if (jf > (double)(ns - 3)) {
+    int best = 0; double bd = fabs(ax[ns - 4] - t);
+#pragma unroll
+    for (int i = 1; i < 4; ++i) { double d = fabs(ax[ns - 4 + i] - t); if (d < bd) { bd = d; best = i; } }
+    return -(double)(4 + best + 1);
+  }
+  return u;
+}
+__device__ __forceinline__ void decode_u(double up, int ns, int& j, double c[4]) {
+  if (up >= 0.0) {
+    const double fl = floor(up);
+    const double w = up - (fl + 1.0) + 1.0;             // eqinterp: w = u - j + 1 with j = floor(u)+1
+    j = (int)fl - 1;
+    c[0] = kcub_out(w + 1.0); c[1] = kcub_in(w); c[2] = kcub_in(fabs(w - 1.0)); c[3] = kcub_out(fabs(w - 2.0));
+  } else {
+    const int code = (int)(-up) - 1, a = code & 3;
+    j = (code & 4) ? ns - 4 : 0;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) c[i] = (i == a) ? 1.0 : 0.0;
+  }
+}
+
+// ---- set-up: sort key, sorted coordinates ---------------------------------------------------------
+// key = cell * Npad + i (all distinct -> the descending bitonic sort gives one deterministic order)
+template <int P>
+__global__ void cg_cellkey_kernel(GridDesc G, const double* __restrict__ X, long n, int D, double* __restrict__ key,
+                                  int* __restrict__ idx, long Npad) {
+  long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= Npad) return;
+  double k = -1.0;
+  if (i < n) {
+    long cell = 0, mul = 1;
+#pragma unroll
+    for (int d = 0; d < P; ++d) {
+      int j; double c[4];
+      decode_u(encode_u(G.ax[d], G.ng[d], G.s0[d], G.ds[d], X[i * D + d]), G.ng[d], j, c);
+      cell += (long)j * mul; mul *= (long)(G.ng[d] - 3);
+    }
+    k = (double)cell * (double)Npad + (double)i;
+  }
+  key[i] = k; idx[i] = (int)i;
+}
+template <int P>
+__global__ void cg_sorted_coords_kernel(GridDesc G, const double* __restrict__ X, long n, int D,
+                                        const int* __restrict__ perm, long npad, double* __restrict__ U) {
+  long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= npad) return;
+  const long src = perm[i < n ? i : n - 1];             // padding repeats the last point (its vector entries stay 0)
+#pragma unroll
+  for (int d = 0; d < P; ++d) U[i * P + d] = encode_u(G.ax[d], G.ng[d], G.s0[d], G.ds[d], X[src * D + d]);
+}
+
+// ---- last-CTA bookkeeping --------------------------------------------------------------------------
+// adds this CTA's partial to *acc; returns true in thread 0 of the CTA that arrives last (then *acc is complete)
+__device__ __forceinline__ bool cta_accumulate_last(double partial, double* acc, unsigned* counter, unsigned nctas) {
+  if (threadIdx.x != 0) return false;
+  atomicAdd(acc, partial);
+  __threadfence();
+  const unsigned t = atomicAdd(counter, 1u);
+  if (t != nctas - 1) return false;
+  __threadfence();
+  *counter = 0u;
+  return true;
+}
+
+// b = sw * rhs[perm] -> r, d ; x = 0 ; scalars of apx.m:284-287
+__global__ void __launch_bounds__(256) cg_init_sorted_kernel(const double* __restrict__ rhs, long rhs_stride,
+    const int* __restrict__ perm, long n, long npad, double sw, double tol, int maxit, double* __restrict__ x,
+    double* __restrict__ r, double* __restrict__ d, double* __restrict__ ctl, unsigned* __restrict__ cnt) {
+  __shared__ double sh[32];
+  const int col = blockIdx.y;
+  double* ct = ctl + col * CT_STRIDE;
+  rhs += (long)col * rhs_stride; x += (long)col * npad; r += (long)col * npad; d += (long)col * npad;
+  double acc = 0.0;
+  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < npad; i += (long)gridDim.x * blockDim.x) {
+    const double b = (i < n) ? sw * rhs[perm[i]] : 0.0;
+    x[i] = 0.0; r[i] = b; d[i] = b; acc = fma(b, b, acc);
+  }
+  const double t = block_sum(acc, sh);
+  if (cta_accumulate_last(t, ct + CT_ACC_RR, cnt + col * 4, gridDim.x)) {
+    const double rr = atomicAdd(ct + CT_ACC_RR, 0.0);
+    const double nb = sqrt(rr), rel = nb / nb;
+    ct[CT_ACC_RR] = 0.0; ct[CT_ACC_DZ] = 0.0;
+    ct[CT_NB] = nb; ct[CT_RRCUR] = rr; ct[CT_RELRES] = rel; ct[CT_ITER] = 1.0; ct[CT_BETA] = 0.0; ct[CT_A] = 0.0;
+    ct[CT_TOL] = tol; ct[CT_MAXIT] = (double)maxit; ct[CT_SW] = sw;
+    ct[CT_DONE] = (rel >= tol) ? ((2 > maxit) ? 2.0 : 0.0) : 1.0;   // NaN (b == 0): nothing to do, apx.m:286
+  }
+}
+
+template <int P> struct CgNodes { static constexpr int NW = (P == 1) ? 4 : 16; };
+
+template <int P>
+__device__ __forceinline__ void flush_nodes(const GridDesc& G, double* __restrict__ g0, int cell, const double* acc) {
+  if (P == 1) {
+#pragma unroll
+    for (int a = 0; a < 4; ++a) if (acc[a] != 0.0) atomicAdd(g0 + cell + a, acc[a]);
+  } else {
+    const int j1 = cell / G.ng[0], j0 = cell - j1 * G.ng[0];
+#pragma unroll
+    for (int b = 0; b < 4; ++b) {
+      double* row = g0 + (long)(j1 + b) * G.stride[1] + j0;
+#pragma unroll
+      for (int a = 0; a < 4; ++a) if (acc[b * 4 + a] != 0.0) atomicAdd(row + a, acc[b * 4 + a]);
+    }
+  }
+}
+
+// d = r + beta d ;  g0 += Mx' (sw d)
+template <int P>
+__global__ void __launch_bounds__(256, 3) cg_scatter_kernel(GridDesc G, const double* __restrict__ U, long npad,
+    const double* __restrict__ r, double* __restrict__ d, const double* __restrict__ ctl, double* __restrict__ g0) {
+  constexpr int NW = CgNodes<P>::NW;
+  const int col = blockIdx.y;
+  const double* ct = ctl + col * CT_STRIDE;
+  if (ct[CT_DONE] != 0.0) return;
+  const double beta = ct[CT_BETA], sw = ct[CT_SW];
+  r += (long)col * npad; d += (long)col * npad; g0 += (long)col * G.N;
+  const int lane = threadIdx.x & 31;
+  const long nunits = npad / (32 * CG_PTS), nwarps = (long)gridDim.x * (blockDim.x >> 5);
+  for (long unit = (long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); unit < nunits; unit += nwarps) {
+    const long base = unit * (32 * CG_PTS) + (long)(threadIdx.x & 31) * CG_PTS;
+    double dn[CG_PTS], uu[CG_PTS * P];
+    {
+      const double2 r0 = *(const double2*)(r + base), r1 = *(const double2*)(r + base + 2);
+      const double2 d0 = *(const double2*)(d + base), d1 = *(const double2*)(d + base + 2);
+      dn[0] = fma(beta, d0.x, r0.x); dn[1] = fma(beta, d0.y, r0.y); dn[2] = fma(beta, d1.x, r1.x); dn[3] = fma(beta, d1.y, r1.y);
+      *(double2*)(d + base) = make_double2(dn[0], dn[1]); *(double2*)(d + base + 2) = make_double2(dn[2], dn[3]);
+#pragma unroll
+      for (int q = 0; q < CG_PTS * P / 2; ++q) {
+        const double2 t = __ldg((const double2*)(U + base * P) + q);
+        uu[2 * q] = t.x; uu[2 * q + 1] = t.y;
+      }
+    }
+    double acc[NW];
+#pragma unroll
+    for (int v = 0; v < NW; ++v) acc[v] = 0.0;
+    int cur = -1;
+#pragma unroll
+    for (int q = 0; q < CG_PTS; ++q) {
+      int j[P]; double c[P][4];
+#pragma unroll
+      for (int dd = 0; dd < P; ++dd) decode_u(uu[q * P + dd], G.ng[dd], j[dd], c[dd]);
+      const int cell = (P == 1) ? j[0] : j[0] + j[P - 1] * G.ng[0];
+      if (cell != cur) {
+        if (cur >= 0) {
+          flush_nodes<P>(G, g0, cur, acc);
+#pragma unroll
+          for (int v = 0; v < NW; ++v) acc[v] = 0.0;
+        }
+        cur = cell;
+      }
+      const double vi = sw * dn[q];
+      if (P == 1) {
+#pragma unroll
+        for (int a = 0; a < 4; ++a) acc[a] = fma(c[0][a], vi, acc[a]);
+      } else {
+#pragma unroll
+        for (int b = 0; b < 4; ++b) {
+          const double wb = c[P - 1][b] * vi;
+#pragma unroll
+          for (int a = 0; a < 4; ++a) acc[b * 4 + a] = fma(c[0][a], wb, acc[b * 4 + a]);
+        }
+      }
+    }
+    // segmented reduction over the warp (cells are contiguous in sorted order)
+#pragma unroll
+    for (int off = 1; off < 32; off <<= 1) {
+      const int oc = __shfl_down_sync(0xffffffffu, cur, off);
+      const bool take = (lane + off < 32) && (oc == cur);
+#pragma unroll
+      for (int v = 0; v < NW; ++v) {
+        const double o = __shfl_down_sync(0xffffffffu, acc[v], off);
+        if (take) acc[v] += o;
+      }
+    }
+    const int pc = __shfl_up_sync(0xffffffffu, cur, 1);
+    if (lane == 0 || pc != cur) flush_nodes<P>(G, g0, cur, acc);
+  }
+}
+
+// z = sw (Mx u) + d ; d.z ; last CTA: a = r2 / (d.z)
+template <int P>
+__global__ void __launch_bounds__(256, 3) cg_gather_kernel(GridDesc G, const double* __restrict__ U, long n, long npad,
+    const double* __restrict__ ug, const double* __restrict__ d, double* __restrict__ z, double* __restrict__ ctl,
+    unsigned* __restrict__ cnt) {
+  constexpr int NW = CgNodes<P>::NW;
+  __shared__ double sh[32];
+  const int col = blockIdx.y;
+  double* ct = ctl + col * CT_STRIDE;
+  if (ct[CT_DONE] != 0.0) return;
+  const double sw = ct[CT_SW];
+  d += (long)col * npad; z += (long)col * npad; ug += (long)col * G.N;
+  double dz = 0.0;
+  const long nunits = npad / (32 * CG_PTS), nwarps = (long)gridDim.x * (blockDim.x >> 5);
+  for (long unit = (long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); unit < nunits; unit += nwarps) {
+    const long base = unit * (32 * CG_PTS) + (long)(threadIdx.x & 31) * CG_PTS;
+    double dv[CG_PTS], uu[CG_PTS * P], zv[CG_PTS];
+    {
+      const double2 d0 = *(const double2*)(d + base), d1 = *(const double2*)(d + base + 2);
+      dv[0] = d0.x; dv[1] = d0.y; dv[2] = d1.x; dv[3] = d1.y;
+#pragma unroll
+      for (int q = 0; q < CG_PTS * P / 2; ++q) {
+        const double2 t = __ldg((const double2*)(U + base * P) + q);
+        uu[2 * q] = t.x; uu[2 * q + 1] = t.y;
+      }
+    }
+    double nv[NW];
+    int cur = -1;
+#pragma unroll
+    for (int q = 0; q < CG_PTS; ++q) {
+      int j[P]; double c[P][4];
+#pragma unroll
+      for (int dd = 0; dd < P; ++dd) decode_u(uu[q * P + dd], G.ng[dd], j[dd], c[dd]);
+      const int cell = (P == 1) ? j[0] : j[0] + j[P - 1] * G.ng[0];
+      if (cell != cur) {
+        cur = cell;
+        if (P == 1) {
+#pragma unroll
+          for (int a = 0; a < 4; ++a) nv[a] = ug[j[0] + a];
+        } else {
+#pragma unroll
+          for (int b = 0; b < 4; ++b) {
+            const double* row = ug + (long)(j[P - 1] + b) * G.stride[1] + j[0];
+#pragma unroll
+            for (int a = 0; a < 4; ++a) nv[b * 4 + a] = row[a];
+          }
+        }
+      }
+      double mu = 0.0;
+      if (P == 1) {
+#pragma unroll
+        for (int a = 0; a < 4; ++a) mu = fma(c[0][a], nv[a], mu);
+      } else {
+#pragma unroll
+        for (int b = 0; b < 4; ++b) {
+          double rb = 0.0;
+#pragma unroll
+          for (int a = 0; a < 4; ++a) rb = fma(c[0][a], nv[b * 4 + a], rb);
+          mu = fma(c[P - 1][b], rb, mu);
+        }
+      }
+      const double zi = (base + q < n) ? fma(sw, mu, dv[q]) : 0.0;
+      zv[q] = zi; dz = fma(dv[q], zi, dz);
+    }
+    *(double2*)(z + base) = make_double2(zv[0], zv[1]); *(double2*)(z + base + 2) = make_double2(zv[2], zv[3]);
+  }
+  const double t = block_sum(dz, sh);
+  if (cta_accumulate_last(t, ct + CT_ACC_DZ, cnt + col * 4 + 1, gridDim.x)) {
+    const double tot = atomicAdd(ct + CT_ACC_DZ, 0.0);
+    ct[CT_A] = ct[CT_RRCUR] / tot; ct[CT_ACC_DZ] = 0.0;
+  }
+}
+
+// x += a d ; r -= a z ; r.r ; g0 = 0 ; last CTA: relres, convergence, iteration count, beta  (apx.m:291-300)
+__global__ void __launch_bounds__(256) cg_update_kernel(long npad, double* __restrict__ x, double* __restrict__ r,
+    const double* __restrict__ d, const double* __restrict__ z, double* __restrict__ ctl, unsigned* __restrict__ cnt,
+    double* __restrict__ g0, long N) {
+  __shared__ double sh[32];
+  const int col = blockIdx.y;
+  double* ct = ctl + col * CT_STRIDE;
+  if (ct[CT_DONE] != 0.0) return;
+  const double a = ct[CT_A];
+  x += (long)col * npad; r += (long)col * npad; d += (long)col * npad; z += (long)col * npad; g0 += (long)col * N;
+  double rr = 0.0;
+  const long nunits = npad / (32 * CG_PTS), nwarps = (long)gridDim.x * (blockDim.x >> 5);
+  for (long unit = (long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); unit < nunits; unit += nwarps) {
+    const long base = unit * (32 * CG_PTS) + (long)(threadIdx.x & 31) * CG_PTS;
+#pragma unroll
+    for (int h = 0; h < CG_PTS; h += 2) {
+      double2 xv = *(const double2*)(x + base + h), rv = *(const double2*)(r + base + h);
+      const double2 dv = *(const double2*)(d + base + h), zv = *(const double2*)(z + base + h);
+      xv.x = fma(a, dv.x, xv.x); xv.y = fma(a, dv.y, xv.y);
+      rv.x = fma(-a, zv.x, rv.x); rv.y = fma(-a, zv.y, rv.y);
+      rr = fma(rv.x, rv.x, rr); rr = fma(rv.y, rv.y, rr);
+      *(double2*)(x + base + h) = xv; *(double2*)(r + base + h) = rv;
+    }
+  }
+  for (long q = (long)blockIdx.x * blockDim.x + threadIdx.x; q < N; q += (long)gridDim.x * blockDim.x) g0[q] = 0.0;
+  const double t = block_sum(rr, sh);
+  if (cta_accumulate_last(t, ct + CT_ACC_RR, cnt + col * 4 + 2, gridDim.x)) {
+    const double rrn = atomicAdd(ct + CT_ACC_RR, 0.0);
+    ct[CT_ACC_RR] = 0.0;
+    const double it = ct[CT_ITER] + 1.0, rel = sqrt(rrn) / ct[CT_NB];
+    ct[CT_ITER] = it; ct[CT_RELRES] = rel;
+    if (!(rel >= ct[CT_TOL])) ct[CT_DONE] = 1.0;
+    else if (it + 1.0 > ct[CT_MAXIT]) ct[CT_DONE] = 2.0;
+    else { ct[CT_BETA] = rrn / ct[CT_RRCUR]; ct[CT_RRCUR] = rrn; }
+  }
+}
+
+// out = (K2 kron K1) T for a 2-D grid in one launch: CTA b computes output row b,
+//   W[a'] = sum_b' K2[b][b'] T[b'][a'] ;  out[b][a] = sum_a' K1[a][a'] W[a']   (K1T = K1 transposed)
+constexpr int KRON2_THREADS = 1024;
+__global__ void __launch_bounds__(KRON2_THREADS) kron2_kernel(const double* __restrict__ K1T, const double* __restrict__ K2, int ng0, int ng1,
+    const double* __restrict__ T, double* __restrict__ out, const double* __restrict__ ctl) {
+  extern __shared__ double ksh[];                      // [nparts][ng0] partials + [ng0] W
+  const int col = blockIdx.y;
+  if (ctl && ctl[col * CT_STRIDE + CT_DONE] != 0.0) return;
+  const long N = (long)ng0 * ng1;
+  T += (long)col * N; out += (long)col * N;
+  const int b = blockIdx.x;
+  int TA = (ng0 + 31) & ~31; if (TA > 256) TA = 256;
+  const int nparts = KRON2_THREADS / TA, part = threadIdx.x / TA, ta = threadIdx.x - part * TA;
+  double* W = ksh + (long)nparts * ng0;
+  if (part < nparts) {
+    for (int a = ta; a < ng0; a += TA) {
+      double acc = 0.0;
+#pragma unroll 8
+      for (int bp = part; bp < ng1; bp += nparts) acc = fma(K2[(long)b * ng1 + bp], T[(long)bp * ng0 + a], acc);
+      ksh[(long)part * ng0 + a] = acc;
+    }
+  }
+  __syncthreads();
+  for (int a = threadIdx.x; a < ng0; a += KRON2_THREADS) {
+    double acc = 0.0;
+    for (int p2 = 0; p2 < nparts; ++p2) acc += ksh[(long)p2 * ng0 + a];
+    W[a] = acc;
+  }
+  __syncthreads();
+  if (part < nparts) {
+    for (int a = ta; a < ng0; a += TA) {
+      double acc = 0.0;
+#pragma unroll 8
+      for (int ap = part; ap < ng0; ap += nparts) acc = fma(K1T[(long)ap * ng0 + a], W[ap], acc);
+      ksh[(long)part * ng0 + a] = acc;
+    }
+  }
+  __syncthreads();
+  for (int a = threadIdx.x; a < ng0; a += KRON2_THREADS) {
+    double acc = 0.0;
+    for (int p2 = 0; p2 < nparts; ++p2) acc += ksh[(long)p2 * ng0 + a];
+    out[(long)b * ng0 + a] = acc;
+  }
+}
+
+__global__ void transpose_small_kernel(const double* __restrict__ A, int ng, double* __restrict__ At) {
+  long q = (long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (q >= (long)ng * ng) return;
+  int a = (int)(q / ng), b = (int)(q % ng);
+  At[(long)b * ng + a] = A[q];
+}
+
+// alpha[perm[i]] = scale * x[i]
+__global__ void cg_unsort_kernel(const double* __restrict__ x, const int* __restrict__ perm, long n, double scale,
+                                 double* __restrict__ out) {
+  long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) out[perm[i]] = scale * x[i];
+}
+
+
+// ======================================================================================================
+// Persistent cooperative CG: the WHOLE solve (apx.m:281-302) in one launch, one CTA per SM.
+// Every CTA owns a fixed contiguous range of 128-point units of the cell-sorted points.  LEVEL 1 keeps
+// the coordinates U of its range in shared memory for the whole solve; LEVEL 2 (single right-hand side)
+// also keeps d and z there, so an iteration moves only x and r (40 B/point) through L2/HBM instead of
+// the 16P+88 B/point of the streaming formulation.  Phases are separated by grid-wide barriers; the
+// dot products are per-CTA partials summed in a fixed order by every CTA (deterministic, identical on
+// all CTAs), so no control data has to be broadcast.
+// ======================================================================================================
+constexpr int CGP_THREADS = 512;
+constexpr int CG_MAXCOLS_DEV = 64;
+constexpr int CGP_WSCR = 16 * 33 + 16;              // doubles of per-warp scratch: 16 node sums x 33 (padded) + 32 int offsets
+struct CgPersist {
+  GridDesc G;
+  const double* U; long n, npad; int m, upc;          // upc = units (128 points) per CTA
+  double *x, *r, *d, *z;                               // [m][npad], sorted order
+  double *g0, *ug;                                     // [m][N] grid vectors: Mx'(sW d) and Kg g0
+  const double *K0, *K0T, *K1;                         // factor matrices (K0 = first grid axis; K0T its transpose; K1 second axis)
+  double *ctl; double *part_dz, *part_rr;              // control blocks [m][CT_STRIDE]; partials [m][gridDim]
+  unsigned* bar;                                       // grid barrier counter
+  long long* dbg;                                      // optional: clock64 ticks per phase (CTA 0), 8 slots
+};
+
+// sense-free monotonically counting grid barrier (all CTAs co-resident: cooperative launch)
+__device__ __forceinline__ void grid_barrier(unsigned* bar, unsigned& phase) {
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    phase += gridDim.x;
+    __threadfence();
+    atomicAdd(bar, 1u);
+    while (*(volatile unsigned*)bar < phase) { }
+    __threadfence();
+  }
+  __syncthreads();
+}
+
+template <int P, int LEVEL>
+__global__ void __launch_bounds__(CGP_THREADS, 1) cg_persistent_kernel(const CgPersist A) {
+  constexpr int NW = CgNodes<P>::NW;
+  extern __shared__ __align__(16) double psm[];
+  __shared__ double s_red[32];
+  __shared__ double s_beta[CG_MAXCOLS_DEV], s_a[CG_MAXCOLS_DEV], s_rr[CG_MAXCOLS_DEV], s_nb[CG_MAXCOLS_DEV], s_it[CG_MAXCOLS_DEV], s_rel[CG_MAXCOLS_DEV];
+  __shared__ int s_done[CG_MAXCOLS_DEV];
+  __shared__ int s_any;
+  const GridDesc& G = A.G;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nwarp = CGP_THREADS >> 5;
+  const int m = A.m, cta = blockIdx.x, nctas = gridDim.x;
+  const long nunits = A.npad / (32 * CG_PTS);
+  const long u_lo = (long)cta * A.upc, u_hi = (u_lo + A.upc < nunits) ? u_lo + A.upc : nunits;
+  const int nu = (u_hi > u_lo) ? (int)(u_hi - u_lo) : 0;
+  // shared layout: [kron scratch][sU nu*128*P][sd nu*128][sz nu*128]
+  int TA = (G.ng[0] + 31) & ~31; if (TA > CGP_THREADS) TA = CGP_THREADS;
+  const int kparts = CGP_THREADS / TA;
+  double* kscr = psm;
+  double* wscr = psm + (((long)(kparts + 1) * G.ng[0] + 1) & ~1L) + (long)warp * CGP_WSCR;   // this warp's reduction scratch
+  int* woff = (int*)(wscr + NW * 33);
+  double* sU = psm + (((long)(kparts + 1) * G.ng[0] + 1) & ~1L) + (long)nwarp * CGP_WSCR;
+  double* sd = sU + (LEVEL >= 1 ? (long)A.upc * 128 * P : 0);
+  double* sz = sd + (LEVEL >= 2 ? (long)A.upc * 128 : 0);
+  unsigned phase = 0;
+  const double sw = A.ctl[CT_SW], tol = A.ctl[CT_TOL], maxit = A.ctl[CT_MAXIT];
+  if (tid < m) {
+    const double* ct = A.ctl + tid * CT_STRIDE;
+    s_beta[tid] = 0.0; s_a[tid] = 0.0; s_rr[tid] = ct[CT_RRCUR]; s_nb[tid] = ct[CT_NB]; s_it[tid] = ct[CT_ITER];
+    s_rel[tid] = ct[CT_RELRES]; s_done[tid] = (int)ct[CT_DONE];
+  }
+  if (LEVEL >= 1)
+    for (long q = tid; q < (long)nu * 128 * P; q += CGP_THREADS) sU[q] = A.U[u_lo * 128 * P + q];
+  if (LEVEL >= 2)
+    for (long q = tid; q < (long)nu * 128; q += CGP_THREADS) sd[q] = A.d[u_lo * 128 + q];
+  __syncthreads();
+
+  long long tk[8] = {0, 0, 0, 0, 0, 0, 0, 0}, t0 = 0;
+#define CGP_TICK(slot) do { if (A.dbg && cta == 0 && tid == 0) { long long t1 = clock64(); tk[slot] += t1 - t0; t0 = t1; } } while (0)
+  if (A.dbg && cta == 0 && tid == 0) t0 = clock64();
+  while (true) {
+    if (tid == 0) { int any = 0; for (int c = 0; c < m; ++c) any |= (s_done[c] == 0); s_any = any; }
+    __syncthreads();
+    if (!s_any) break;
+    // ---- A: d = r + beta d ; g0 += Mx'(sw d)
+    for (int col = 0; col < m; ++col) {
+      if (s_done[col]) continue;
+      const double beta = s_beta[col];
+      const double* r = A.r + (long)col * A.npad; double* d = A.d + (long)col * A.npad; double* g0 = A.g0 + (long)col * G.N;
+      for (int ul = warp; ul < nu; ul += nwarp) {
+        const long base = (u_lo + ul) * 128 + lane * CG_PTS; const int lb = ul * 128 + lane * CG_PTS;
+        double dn[CG_PTS], uu[CG_PTS * P];
+        {
+          const double2 r0 = *(const double2*)(r + base), r1 = *(const double2*)(r + base + 2);
+          double2 d0, d1;
+          if (LEVEL >= 2) { d0 = *(const double2*)(sd + lb); d1 = *(const double2*)(sd + lb + 2); }
+          else { d0 = *(const double2*)(d + base); d1 = *(const double2*)(d + base + 2); }
+          dn[0] = fma(beta, d0.x, r0.x); dn[1] = fma(beta, d0.y, r0.y); dn[2] = fma(beta, d1.x, r1.x); dn[3] = fma(beta, d1.y, r1.y);
+          if (LEVEL >= 2) { *(double2*)(sd + lb) = make_double2(dn[0], dn[1]); *(double2*)(sd + lb + 2) = make_double2(dn[2], dn[3]); }
+          else { *(double2*)(d + base) = make_double2(dn[0], dn[1]); *(double2*)(d + base + 2) = make_double2(dn[2], dn[3]); }
+#pragma unroll
+          for (int q = 0; q < CG_PTS * P / 2; ++q) {
+            const double2 t = (LEVEL >= 1) ? *((const double2*)(sU + (long)lb * P) + q) : __ldg((const double2*)(A.U + base * P) + q);
+            uu[2 * q] = t.x; uu[2 * q + 1] = t.y;
+          }
+        }
+        double acc[NW];
+#pragma unroll
+        for (int v = 0; v < NW; ++v) acc[v] = 0.0;
+        int cur = -1;
+#pragma unroll
+        for (int q = 0; q < CG_PTS; ++q) {
+          int j[P]; double c[P][4];
+#pragma unroll
+          for (int dd = 0; dd < P; ++dd) decode_u(uu[q * P + dd], G.ng[dd], j[dd], c[dd]);
+          const int cell = (P == 1) ? j[0] : j[0] + j[P - 1] * G.ng[0];
+          if (cell != cur) {
+            if (cur >= 0) {
+              flush_nodes<P>(G, g0, cur, acc);
+#pragma unroll
+              for (int v = 0; v < NW; ++v) acc[v] = 0.0;
+            }
+            cur = cell;
+          }
+          const double vi = sw * dn[q];
+          if (P == 1) {
+#pragma unroll
+            for (int a = 0; a < 4; ++a) acc[a] = fma(c[0][a], vi, acc[a]);
+          } else {
+#pragma unroll
+            for (int b = 0; b < 4; ++b) {
+              const double wb = c[P - 1][b] * vi;
+#pragma unroll
+              for (int a = 0; a < 4; ++a) acc[b * 4 + a] = fma(c[0][a], wb, acc[b * 4 + a]);
+            }
+          }
+        }
+        // segmented reduction through this warp's scratch: lane (k, h) walks 16 source lanes of node k
+        {
+          const int off_cur = (P == 1) ? cur : (cur / G.ng[0]) * (int)G.stride[1] + (cur % G.ng[0]);
+          __syncwarp();
+          woff[lane] = off_cur;
+#pragma unroll
+          for (int v = 0; v < NW; ++v) wscr[v * 33 + lane] = acc[v];
+          __syncwarp();
+          constexpr int LPN = 32 / NW;                       // lanes per node value: 2 (P=2) or 8 (P=1)
+          constexpr int SRC = 32 / LPN;                      // source lanes each of them walks
+          const int k = lane % NW, h = lane / NW;
+          const int node_off = (P == 1) ? k : (k >> 2) * (int)G.stride[1] + (k & 3);
+          double run = 0.0; int po = woff[h * SRC];
+#pragma unroll
+          for (int i2 = 0; i2 < SRC; ++i2) {
+            const int co = woff[h * SRC + i2];
+            const double v = wscr[k * 33 + h * SRC + i2];
+            if (co != po) { if (run != 0.0) atomicAdd(g0 + po + node_off, run); run = 0.0; po = co; }
+            run += v;
+          }
+          if (run != 0.0) atomicAdd(g0 + po + node_off, run);
+        }
+      }
+    }
+    CGP_TICK(0);
+    grid_barrier(A.bar, phase);
+    CGP_TICK(1);
+    // ---- B: ug = Kg g0
+    for (int col = 0; col < m; ++col) {
+      if (s_done[col]) continue;
+      const double* T = A.g0 + (long)col * G.N; double* out = A.ug + (long)col * G.N;
+      if (P == 1) {
+        const int ng = G.ng[0];
+        for (int a = cta * nwarp + warp; a < ng; a += nctas * nwarp) {
+          double acc = 0.0;
+          for (int b = lane; b < ng; b += 32) acc = fma(A.K0[(long)a * ng + b], __ldcg(T + b), acc);
+          acc = warp_sum(acc);
+          if (lane == 0) out[a] = acc;
+        }
+      } else {
+        const int ng0 = G.ng[0], ng1 = G.ng[1];
+        const int part = tid / TA, ta = tid - part * TA;
+        double* W = kscr + (long)kparts * ng0;
+        for (int b = cta; b < ng1; b += nctas) {
+          if (part < kparts)
+            for (int a = ta; a < ng0; a += TA) {
+              double acc = 0.0;
+#pragma unroll 8
+              for (int bp = part; bp < ng1; bp += kparts) acc = fma(A.K1[(long)b * ng1 + bp], __ldcg(T + (long)bp * ng0 + a), acc);
+              kscr[(long)part * ng0 + a] = acc;
+            }
+          __syncthreads();
+          for (int a = tid; a < ng0; a += CGP_THREADS) {
+            double acc = 0.0;
+            for (int p2 = 0; p2 < kparts; ++p2) acc += kscr[(long)p2 * ng0 + a];
+            W[a] = acc;
+          }
+          __syncthreads();
+          if (part < kparts)
+            for (int a = ta; a < ng0; a += TA) {
+              double acc = 0.0;
+#pragma unroll 8
+              for (int ap = part; ap < ng0; ap += kparts) acc = fma(A.K0T[(long)ap * ng0 + a], W[ap], acc);
+              kscr[(long)part * ng0 + a] = acc;
+            }
+          __syncthreads();
+          for (int a = tid; a < ng0; a += CGP_THREADS) {
+            double acc = 0.0;
+            for (int p2 = 0; p2 < kparts; ++p2) acc += kscr[(long)p2 * ng0 + a];
+            out[(long)b * ng0 + a] = acc;
+          }
+          __syncthreads();
+        }
+      }
+    }
+    CGP_TICK(2);
+    grid_barrier(A.bar, phase);
+    CGP_TICK(3);
+    // ---- C: z = sw Mx ug + d ; d.z
+    for (int col = 0; col < m; ++col) {
+      if (s_done[col]) continue;
+      const double* d = A.d + (long)col * A.npad; double* z = A.z + (long)col * A.npad; const double* ug = A.ug + (long)col * G.N;
+      double dz = 0.0;
+      for (int ul = warp; ul < nu; ul += nwarp) {
+        const long base = (u_lo + ul) * 128 + lane * CG_PTS; const int lb = ul * 128 + lane * CG_PTS;
+        double dv[CG_PTS], uu[CG_PTS * P], zv[CG_PTS];
+        {
+          double2 d0, d1;
+          if (LEVEL >= 2) { d0 = *(const double2*)(sd + lb); d1 = *(const double2*)(sd + lb + 2); }
+          else { d0 = *(const double2*)(d + base); d1 = *(const double2*)(d + base + 2); }
+          dv[0] = d0.x; dv[1] = d0.y; dv[2] = d1.x; dv[3] = d1.y;
+#pragma unroll
+          for (int q = 0; q < CG_PTS * P / 2; ++q) {
+            const double2 t = (LEVEL >= 1) ? *((const double2*)(sU + (long)lb * P) + q) : __ldg((const double2*)(A.U + base * P) + q);
+            uu[2 * q] = t.x; uu[2 * q + 1] = t.y;
+          }
+        }
+        double nv[NW];
+        int cur = -1;
+#pragma unroll
+        for (int q = 0; q < CG_PTS; ++q) {
+          int j[P]; double c[P][4];
+#pragma unroll
+          for (int dd = 0; dd < P; ++dd) decode_u(uu[q * P + dd], G.ng[dd], j[dd], c[dd]);
+          const int cell = (P == 1) ? j[0] : j[0] + j[P - 1] * G.ng[0];
+          if (cell != cur) {
+            cur = cell;
+            if (P == 1) {
+#pragma unroll
+              for (int a = 0; a < 4; ++a) nv[a] = __ldcg(ug + j[0] + a);
+            } else {
+#pragma unroll
+              for (int b = 0; b < 4; ++b) {
+                const double* row = ug + (long)(j[P - 1] + b) * G.stride[1] + j[0];
+#pragma unroll
+                for (int a = 0; a < 4; ++a) nv[b * 4 + a] = __ldcg(row + a);
+              }
+            }
+          }
+          double mu = 0.0;
+          if (P == 1) {
+#pragma unroll
+            for (int a = 0; a < 4; ++a) mu = fma(c[0][a], nv[a], mu);
+          } else {
+#pragma unroll
+            for (int b = 0; b < 4; ++b) {
+              double rb = 0.0;
+#pragma unroll
+              for (int a = 0; a < 4; ++a) rb = fma(c[0][a], nv[b * 4 + a], rb);
+              mu = fma(c[P - 1][b], rb, mu);
+            }
+          }
+          const double zi = (base + q < A.n) ? fma(sw, mu, dv[q]) : 0.0;
+          zv[q] = zi; dz = fma(dv[q], zi, dz);
+        }
+        if (LEVEL >= 2) { *(double2*)(sz + lb) = make_double2(zv[0], zv[1]); *(double2*)(sz + lb + 2) = make_double2(zv[2], zv[3]); }
+        else { *(double2*)(z + base) = make_double2(zv[0], zv[1]); *(double2*)(z + base + 2) = make_double2(zv[2], zv[3]); }
+      }
+      const double t = block_sum(dz, s_red);
+      if (tid == 0) A.part_dz[(long)col * nctas + cta] = t;
+    }
+    CGP_TICK(4);
+    grid_barrier(A.bar, phase);
+    CGP_TICK(5);
+    for (int col = warp; col < m; col += nwarp) {
+      if (s_done[col]) continue;
+      double acc = 0.0;
+      for (int i = lane; i < nctas; i += 32) acc += __ldcg(A.part_dz + (long)col * nctas + i);
+      acc = warp_sum(acc);
+      if (lane == 0) s_a[col] = s_rr[col] / acc;
+    }
+    __syncthreads();
+    // ---- D: x += a d ; r -= a z ; r.r ; g0 = 0
+    for (int col = 0; col < m; ++col) {
+      if (s_done[col]) continue;
+      const double a = s_a[col];
+      double* x = A.x + (long)col * A.npad; double* r = A.r + (long)col * A.npad;
+      const double* d = A.d + (long)col * A.npad; const double* z = A.z + (long)col * A.npad;
+      double rr = 0.0;
+      for (int ul = warp; ul < nu; ul += nwarp) {
+        const long base = (u_lo + ul) * 128 + lane * CG_PTS; const int lb = ul * 128 + lane * CG_PTS;
+#pragma unroll
+        for (int h = 0; h < CG_PTS; h += 2) {
+          double2 xv = *(const double2*)(x + base + h), rv = *(const double2*)(r + base + h);
+          const double2 dv = (LEVEL >= 2) ? *(const double2*)(sd + lb + h) : *(const double2*)(d + base + h);
+          const double2 zv = (LEVEL >= 2) ? *(const double2*)(sz + lb + h) : *(const double2*)(z + base + h);
+          xv.x = fma(a, dv.x, xv.x); xv.y = fma(a, dv.y, xv.y);
+          rv.x = fma(-a, zv.x, rv.x); rv.y = fma(-a, zv.y, rv.y);
+          rr = fma(rv.x, rv.x, rr); rr = fma(rv.y, rv.y, rr);
+          *(double2*)(x + base + h) = xv; *(double2*)(r + base + h) = rv;
+        }
+      }
+      double* g0 = A.g0 + (long)col * G.N;
+      for (long q = (long)cta * CGP_THREADS + tid; q < G.N; q += (long)nctas * CGP_THREADS) g0[q] = 0.0;
+      const double t = block_sum(rr, s_red);
+      if (tid == 0) A.part_rr[(long)col * nctas + cta] = t;
+    }
+    CGP_TICK(6);
+    grid_barrier(A.bar, phase);
+    CGP_TICK(7);
+    for (int col = warp; col < m; col += nwarp) {
+      if (s_done[col]) continue;
+      double acc = 0.0;
+      for (int i = lane; i < nctas; i += 32) acc += __ldcg(A.part_rr + (long)col * nctas + i);
+      acc = warp_sum(acc);
+      if (lane == 0) {
+        const double it = s_it[col] + 1.0, rel = sqrt(acc) / s_nb[col];
+        s_it[col] = it; s_rel[col] = rel;
+        if (!(rel >= tol)) s_done[col] = 1;                     // apx.m:295-298
+        else if (it + 1.0 > maxit) s_done[col] = 2;            // loop `for iter=2:maxit` exhausted
+        else { s_beta[col] = acc / s_rr[col]; s_rr[col] = acc; }
+      }
+    }
+    __syncthreads();
+  }
+  if (A.dbg && cta == 0 && tid == 0) for (int q = 0; q < 8; ++q) A.dbg[q] = tk[q];
+  if (cta == 0 && tid < m) {
+    double* ct = A.ctl + tid * CT_STRIDE;
+    ct[CT_DONE] = (double)s_done[tid]; ct[CT_ITER] = s_it[tid]; ct[CT_RELRES] = s_rel[tid];
+  }
+}
+
+}  // namespace kgp
