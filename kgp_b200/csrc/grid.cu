@@ -22,7 +22,8 @@ struct GridState {
   double* h_ctl = nullptr;                // pinned host copy of the control blocks
   long npad = 0; int sort_slot = -1; unsigned long sort_slot_ver = 0, sort_grid_ver = 0;
   cudaGraphExec_t cg_graph = nullptr; std::vector<char> cg_graph_key;
-  DevBuf pdz, prr, bar; int num_sms = 0; size_t smem_optin = 0; int cg_level_used = -1;
+  DevBuf pdz, prr, bar, part4, g0b, wmaxd; int num_sms = 0; size_t smem_optin = 0; int cg_level_used = -1;
+  int wmax = 0; int wmax_ctas = 0; unsigned long wmax_slot_ver = 0, wmax_grid_ver = 0; int wmax_slot = -1;
   int p = 0; int ng[GRID_MAXP] = {0}; long N = 0;
   long koff[GRID_MAXP] = {0};            // offsets of factor i inside Kf / Vf
   int eoff_h[GRID_MAXP] = {0};
@@ -42,7 +43,7 @@ void grid_free(kgp_ctx* c) {
   DevBuf* bufs[] = {&g->axes, &g->Kf, &g->Vf, &g->Af, &g->ee, &g->eoff, &g->de, &g->zv, &g->Qm, &g->Pm, &g->g0, &g->g1,
                     &g->tgrid, &g->beta, &g->x, &g->r, &g->d, &g->z, &g->ym, &g->partA, &g->partB, &g->S, &g->hyp,
                     &g->hypm, &g->dX, &g->dhyp, &g->out, &g->sortk, &g->sorti, &g->keep, &g->dmean,
-                    &g->U, &g->perm, &g->sx, &g->sr, &g->sd, &g->sz, &g->ctl, &g->cnt, &g->KfT, &g->gm0, &g->gm1, &g->pdz, &g->prr, &g->bar};
+                    &g->U, &g->perm, &g->sx, &g->sr, &g->sd, &g->sz, &g->ctl, &g->cnt, &g->KfT, &g->gm0, &g->gm1, &g->pdz, &g->prr, &g->bar, &g->part4, &g->g0b, &g->wmaxd};
   for (DevBuf* b : bufs) b->release();
   if (g->h_ctl) cudaFreeHost(g->h_ctl);
   if (g->cg_graph) cudaGraphExecDestroy(g->cg_graph);
@@ -298,6 +299,86 @@ static int cg_run_persistent(kgp_ctx* c, GridState* g, const CgLaunch& L, int ma
   return cg_finish(c, g, L.m);
 }
 
+template <int P, int LEVEL, bool DBG>
+static cudaError_t launch_persistent2b(const CgPersist2& A, int ctas, size_t smem, cudaStream_t st) {
+  cudaError_t e = cudaFuncSetAttribute(cg_persistent2_kernel<P, LEVEL, DBG>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  if (e != cudaSuccess) return e;
+  void* args[] = {(void*)&A};
+  return cudaLaunchCooperativeKernel((const void*)cg_persistent2_kernel<P, LEVEL, DBG>, dim3((unsigned)ctas), dim3(CGP2_THREADS), args, smem, st);
+}
+template <int P, int LEVEL>
+static cudaError_t launch_persistent2(const CgPersist2& A, int ctas, size_t smem, cudaStream_t st) {
+  return A.dbg ? launch_persistent2b<P, LEVEL, true>(A, ctas, smem, st) : launch_persistent2b<P, LEVEL, false>(A, ctas, smem, st);
+}
+// two-barrier formulation (cg_persistent2_kernel); -1 when it does not fit (node window / staging too large)
+static int cg_run_persistent2(kgp_ctx* c, GridState* g, const CgLaunch& L, int slot) {
+  const GridDesc& G = L.G; cudaStream_t st = c->stream;
+  if (!g->num_sms) {
+    int v = 0; cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, c->device); g->num_sms = v;
+    cudaDeviceGetAttribute(&v, cudaDevAttrMaxSharedMemoryPerBlockOptin, c->device); g->smem_optin = (size_t)v;
+    int coop = 0; cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, c->device);
+    if (!coop) g->num_sms = -1;
+  }
+  if (g->num_sms <= 0 || G.p > 2 || L.m > CG_MAXCOLS_DEV) return -1;
+  const int ctas = g->num_sms;
+  const long nunits = L.npad / 128;
+  const int upc = (int)((nunits + ctas - 1) / ctas);
+  Slot& S = c->slots[slot];
+  if (g->wmax_slot != slot || g->wmax_slot_ver != S.version || g->wmax_grid_ver != c->grid.version || g->wmax_ctas != ctas) {
+    KGP_CUDA(c, g->wmaxd.ensure(64));
+    KGP_CUDA(c, cudaMemsetAsync(g->wmaxd.p, 0, 64, st));
+    if (G.p == 1) cg_window_kernel<1><<<ctas, 32, 0, st>>>(G, L.U, L.npad, upc, (int*)g->wmaxd.p);
+    else cg_window_kernel<2><<<ctas, 32, 0, st>>>(G, L.U, L.npad, upc, (int*)g->wmaxd.p);
+    int w = 0;
+    KGP_CUDA(c, cudaMemcpyAsync(&w, g->wmaxd.p, 4, cudaMemcpyDeviceToHost, st));
+    KGP_CUDA(c, cudaStreamSynchronize(st));
+    g->wmax = w; g->wmax_slot = slot; g->wmax_slot_ver = S.version; g->wmax_grid_ver = c->grid.version; g->wmax_ctas = ctas;
+  }
+  const int wcap = std::max(g->wmax, 4);
+  const long ng0 = G.ng[0], ng1 = G.p > 1 ? G.ng[1] : 1;
+  auto even = [](long v) { return (v + 1) & ~1L; };
+  const long uwin_d = even(G.p == 1 ? wcap : wcap * ng0);
+  long stg_need = (long)(CGP2_THREADS / 32) * CGP_WSCR2;
+  if (G.p == 1) stg_need = std::max(stg_need, even(ng0));
+  else stg_need = std::max(stg_need, even(std::max<long>(G.N, ng0 * ng0)) + even(wcap * ng1) + even(wcap * ng0));
+  const size_t budget = g->smem_optin - 4 * 1024;                     // static shared of the kernel (< 4 KB)
+  const long u_d = (long)upc * 128 * G.p, v_d = (long)upc * 128;
+  const size_t s0 = (size_t)(uwin_d + stg_need) * 8, s1 = (size_t)(uwin_d + u_d + stg_need) * 8,
+               s2 = (size_t)(uwin_d + u_d + v_d + std::max(v_d, stg_need)) * 8;
+  if (s0 > budget) return -1;
+  static const int force_level = getenv("KGP_CG_LEVEL") ? atoi(getenv("KGP_CG_LEVEL")) : 2;
+  int level = 0; size_t smem = s0;
+  if (s1 <= budget && force_level >= 1) { level = 1; smem = s1; }
+  if (L.m == 1 && s2 <= budget && force_level >= 2) { level = 2; smem = s2; }
+  KGP_CUDA(c, g->part4.ensure((size_t)4 * L.m * ctas * 8)); KGP_CUDA(c, g->g0b.ensure((size_t)L.m * G.N * 8));
+  KGP_CUDA(c, g->bar.ensure(256));
+  KGP_CUDA(c, cudaMemsetAsync(g->bar.p, 0, 256, st));
+  KGP_CUDA(c, cudaMemsetAsync(g->g0b.p, 0, (size_t)L.m * G.N * 8, st));
+  if (level < 2) KGP_CUDA(c, cudaMemsetAsync(L.sz, 0, (size_t)L.m * L.npad * 8, st));
+  CgPersist2 A; memset(&A, 0, sizeof A);
+  A.G = G; A.U = L.U; A.n = L.n; A.npad = L.npad; A.m = L.m; A.upc = upc; A.wcap = wcap;
+  A.x = L.sx; A.r = L.sr; A.d = L.sd; A.z = L.sz; A.g0a = L.gm0; A.g0b = g->g0b.d();
+  A.K0 = L.Kf; A.K0T = L.KfT; A.K1 = L.Kf + L.koff1;
+  A.ctl = L.ctl; A.part = g->part4.d(); A.bar = (unsigned*)g->bar.p; A.stg_doubles = stg_need;
+  A.dbg = getenv("KGP_DEBUG") ? (long long*)((char*)g->bar.p + 128) : nullptr;
+  cudaError_t e;
+  if (G.p == 1) e = level == 2 ? launch_persistent2<1, 2>(A, ctas, smem, st) : level == 1 ? launch_persistent2<1, 1>(A, ctas, smem, st) : launch_persistent2<1, 0>(A, ctas, smem, st);
+  else e = level == 2 ? launch_persistent2<2, 2>(A, ctas, smem, st) : level == 1 ? launch_persistent2<2, 1>(A, ctas, smem, st) : launch_persistent2<2, 0>(A, ctas, smem, st);
+  KGP_CUDA(c, e);
+  g->cg_level_used = level;
+  c->stats.kernel_launches += 1;
+  KGP_CUDA(c, cudaMemcpyAsync(g->h_ctl, g->ctl.p, (size_t)L.m * CT_STRIDE * 8, cudaMemcpyDeviceToHost, st));
+  KGP_CUDA(c, cudaStreamSynchronize(st));
+  KGP_CUDA(c, cudaGetLastError());
+  if (A.dbg) {
+    long long tk[8]; cudaMemcpy(tk, A.dbg, sizeof tk, cudaMemcpyDeviceToHost);
+    const double it = std::max(1.0, g->h_ctl[CT_ITER] - 1.0), f = 1e-3 / 1.965 / it;
+    fprintf(stderr, "[kgp] persistent2: level %d smem %zu wcap %d upc %d | us/iter: F1 %.2f F2 %.2f bar %.2f | Cwin %.2f Cloop %.2f bar %.2f | red %.2f\n", level, smem, wcap, upc,
+            tk[5] * f, tk[0] * f, tk[1] * f, tk[6] * f, tk[2] * f, tk[3] * f, tk[4] * f);
+  }
+  return cg_finish(c, g, L.m);
+}
+
 // x = CG(B, sw * rhs[:, col]) for m columns at once (sorted order, result in g->sx); rhs in ORIGINAL point order
 static int cg_solve_sorted(kgp_ctx* c, GridState* g, const GridDesc& G, int slot, const double* rhs, long rhs_stride, int m,
                            double sw, double tol, int maxit) {
@@ -325,8 +406,12 @@ static int cg_solve_sorted(kgp_ctx* c, GridState* g, const GridDesc& G, int slot
       rhs, rhs_stride, (const int*)g->perm.p, n, npad, sw, tol, maxit, L.sx, L.sr, L.sd, L.ctl, L.cnt);
   c->stats.kernel_launches += 1;
 
-  static const int cg_mode = getenv("KGP_CG_MODE") ? atoi(getenv("KGP_CG_MODE")) : 2;     // 2 persistent, 1 streaming kernels
-  if (cg_mode == 2) {
+  static const int cg_mode = getenv("KGP_CG_MODE") ? atoi(getenv("KGP_CG_MODE")) : 3;     // 3 persistent two-barrier, 2 persistent four-phase, 1 streaming kernels
+  if (cg_mode >= 3) {
+    rc = cg_run_persistent2(c, g, L, slot);
+    if (rc != -1) return rc;
+  }
+  if (cg_mode >= 2) {
     rc = cg_run_persistent(c, g, L, maxit);
     if (rc != -1) return rc;                                  // -1: does not fit -> streaming kernels below
   }

@@ -55,17 +55,25 @@ __device__ __forceinline__ double encode_u(const double* __restrict__ ax, int ns
   return u;
 }
 __device__ __forceinline__ void decode_u(double up, int ns, int& j, double c[4]) {
-  if (up >= 0.0) {
-    const double fl = floor(up);
-    const double w = up - (fl + 1.0) + 1.0;             // eqinterp: w = u - j + 1 with j = floor(u)+1
-    j = (int)fl - 1;
-    c[0] = kcub_out(w + 1.0); c[1] = kcub_in(w); c[2] = kcub_in(fabs(w - 1.0)); c[3] = kcub_out(fabs(w - 2.0));
-  } else {
-    const int code = (int)(-up) - 1, a = code & 3;
-    j = (code & 4) ? ns - 4 : 0;
-#pragma unroll
-    for (int i = 0; i < 4; ++i) c[i] = (i == a) ? 1.0 : 0.0;
-  }
+  // branch-free: both forms are evaluated and selected, so the decodes of a thread's points interleave
+  const bool reg = up >= 0.0;
+  const double ur = reg ? up : 2.0;
+  const double fl = floor(ur);
+  const double w = ur - (fl + 1.0) + 1.0;               // eqinterp: w = u - j + 1 with j = floor(u)+1
+  const double c0 = kcub_out(w + 1.0), c1 = kcub_in(w), c2 = kcub_in(fabs(w - 1.0)), c3 = kcub_out(fabs(w - 2.0));
+  const int code = reg ? 0 : (int)(-up) - 1, a = code & 3;
+  j = reg ? (int)fl - 1 : ((code & 4) ? ns - 4 : 0);
+  c[0] = reg ? c0 : (a == 0 ? 1.0 : 0.0);
+  c[1] = reg ? c1 : (a == 1 ? 1.0 : 0.0);
+  c[2] = reg ? c2 : (a == 2 ? 1.0 : 0.0);
+  c[3] = reg ? c3 : (a == 3 ? 1.0 : 0.0);
+}
+
+// first node only (cheap form of decode_u)
+__device__ __forceinline__ int decode_j(double up, int ns) {
+  const bool reg = up >= 0.0;
+  const int code = reg ? 0 : (int)(-up) - 1;
+  return reg ? (int)floor(up) - 1 : ((code & 4) ? ns - 4 : 0);
 }
 
 // ---- set-up: sort key, sorted coordinates ---------------------------------------------------------
@@ -727,6 +735,408 @@ __global__ void __launch_bounds__(CGP_THREADS, 1) cg_persistent_kernel(const CgP
   if (cta == 0 && tid < m) {
     double* ct = A.ctl + tid * CT_STRIDE;
     ct[CT_DONE] = (double)s_done[tid]; ct[CT_ITER] = s_it[tid]; ct[CT_RELRES] = s_rel[tid];
+  }
+}
+
+
+// ======================================================================================================
+// Persistent CG, second formulation: TWO grid barriers per iteration.
+//   F : x += a d ; r -= a z ; |r|^2 ; d = r + beta d ; g0 += Mx'(sw d)        (update fused into the scatter)
+//   -- barrier --
+//   C : u = (Kg g0) on the node rows this CTA's points touch (computed by the CTA itself from g0 staged in
+//       shared memory: no separate Kronecker phase, node values read from shared memory) ;
+//       z = sw Mx u + d ; d.z, r.z, z.z
+//   -- barrier --   every CTA sums the per-CTA partials in the same order:
+//       a = |r|^2 / d.z ;  |r_next|^2 = |r|^2 - 2 a r.z + a^2 z.z  (exact identity for r_next = r - a z) gives the
+//       convergence test and beta = |r_next|^2 / |r|^2 BEFORE the update is applied, so the update can ride in the
+//       next F.  |r|^2 itself is always the directly summed value from F (no drift).
+// Shared memory per CTA: coordinates U (LEVEL>=1), d and z (LEVEL 2, single right-hand side) of its own point
+// range in a bank-conflict-free [double2][lane] layout, the node window, and one staging region (aliased onto z
+// at LEVEL 2) used in turn for the scatter's segmented reduction, g0 and the first-axis factor.
+// ======================================================================================================
+struct CgPersist2 {
+  GridDesc G;
+  const double* U; long n, npad; int m, upc, wcap;     // wcap = node rows the window buffer can hold
+  double *x, *r, *d, *z;                               // [m][npad], sorted order
+  double *g0a, *g0b;                                   // [m][N] scatter targets, alternating per iteration
+  const double *K0, *K0T, *K1;
+  double *ctl; double *part;                           // partials [4][m][gridDim]: |r|^2, d.z, r.z, z.z
+  unsigned* bar; long long* dbg;
+  long stg_doubles;                                    // size of the staging region
+};
+constexpr int CGP2_THREADS = 512;
+constexpr int CGP_VPP = 8;                             // node values per reduction pass (2-D); 1-D uses 4
+constexpr int CGP_WSCR2 = CGP_VPP * 33 + 16;
+
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.commit_group;\ncp.async.wait_group 0;\n" ::: "memory"); }
+
+// per-CTA node-row window [rlo, rhi] of a sorted point range (rows of the LAST grid axis; nodes for 1-D)
+template <int P>
+__global__ void cg_window_kernel(GridDesc G, const double* __restrict__ U, long npad, int upc, int* __restrict__ wmax) {
+  const long nunits = npad / 128;
+  const long u_lo = (long)blockIdx.x * upc, u_hi = (u_lo + upc < nunits) ? u_lo + upc : nunits;
+  if (threadIdx.x != 0 || u_hi <= u_lo) return;
+  int jf, jl; double c[4];
+  decode_u(U[(u_lo * 128) * P + (P - 1)], G.ng[P - 1], jf, c);
+  decode_u(U[(u_hi * 128 - 1) * P + (P - 1)], G.ng[P - 1], jl, c);
+  atomicMax(wmax, jf + 3 - jl + 1);
+}
+
+template <int P, int LEVEL, bool DBG>
+__global__ void __launch_bounds__(CGP2_THREADS, 1) cg_persistent2_kernel(const CgPersist2 A) {
+  constexpr int NW = CgNodes<P>::NW;
+  constexpr int VPP = (P == 1) ? 4 : CGP_VPP, NPASS = NW / VPP;
+  extern __shared__ __align__(16) double psm[];
+  __shared__ double s_red[32];
+  __shared__ double s_beta[CG_MAXCOLS_DEV], s_a[CG_MAXCOLS_DEV], s_rr[CG_MAXCOLS_DEV], s_nb[CG_MAXCOLS_DEV], s_it[CG_MAXCOLS_DEV], s_rel[CG_MAXCOLS_DEV];
+  __shared__ int s_state[CG_MAXCOLS_DEV];              // 0 active, 3 final update pending, 1 converged, 2 exhausted
+  __shared__ int s_final[CG_MAXCOLS_DEV];
+  __shared__ int s_any;
+  __shared__ double s_sum[4][CG_MAXCOLS_DEV];
+  const GridDesc& G = A.G;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nwarp = CGP2_THREADS >> 5;
+  const int m = A.m, cta = blockIdx.x, nctas = gridDim.x;
+  const long nunits = A.npad / 128;
+  const long u_lo = (long)cta * A.upc, u_hi = (u_lo + A.upc < nunits) ? u_lo + A.upc : nunits;
+  const int nu = (u_hi > u_lo) ? (int)(u_hi - u_lo) : 0;
+  const int ng0 = G.ng[0], ngl = G.ng[P - 1];
+  // shared layout: [uwin wcap*ng0 (2-D) | wcap (1-D)] [sU] [sd] [sz / staging]
+  double* uwin = psm;
+  double* sU = uwin + (((P == 1) ? (long)A.wcap : (long)A.wcap * ng0) + 1 & ~1L);
+  double* sd = sU + (LEVEL >= 1 ? (long)A.upc * 128 * P : 0);
+  double* sz = sd + (LEVEL >= 2 ? (long)A.upc * 128 : 0);
+  double* stg = sz;                                    // staging aliases z (z is dead whenever staging is live)
+  unsigned phase = 0;
+  const double sw = A.ctl[CT_SW], tol = A.ctl[CT_TOL], maxit = A.ctl[CT_MAXIT];
+  if (tid < m) {
+    const double* ct = A.ctl + tid * CT_STRIDE;
+    s_beta[tid] = 0.0; s_a[tid] = 0.0; s_rr[tid] = ct[CT_RRCUR]; s_nb[tid] = ct[CT_NB]; s_it[tid] = ct[CT_ITER];
+    s_rel[tid] = ct[CT_RELRES]; s_state[tid] = (int)ct[CT_DONE]; s_final[tid] = 0;
+  }
+  // resident data in the [double2 index][lane] layout
+  if (LEVEL >= 1)
+    for (long q = tid; q < (long)nu * 128 * P; q += CGP2_THREADS) {
+      const long ul = q / (128 * P); const int rem = (int)(q - ul * 128 * P), ln = rem / (CG_PTS * P), w = rem - ln * CG_PTS * P;
+      sU[ul * 128 * P + ((w >> 1) * 32 + ln) * 2 + (w & 1)] = A.U[u_lo * 128 * P + q];
+    }
+  if (LEVEL >= 2)
+    for (long q = tid; q < (long)nu * 128; q += CGP2_THREADS) {
+      const long ul = q >> 7; const int rem = (int)(q & 127), ln = rem >> 2, w = rem & 3;
+      sd[ul * 128 + ((w >> 1) * 32 + ln) * 2 + (w & 1)] = A.d[u_lo * 128 + q];
+    }
+  if (LEVEL >= 2)
+    for (long q = tid; q < (long)nu * 128; q += CGP2_THREADS) sz[q] = 0.0;
+  // node window of this CTA
+  int rlo = 0, wr = 0;
+  if (nu > 0) {
+    int jf, jl; double c[4];
+    decode_u(A.U[(u_lo * 128) * P + (P - 1)], ngl, jf, c);
+    decode_u(A.U[(u_hi * 128 - 1) * P + (P - 1)], ngl, jl, c);
+    rlo = jl; wr = jf + 3 - jl + 1;
+  }
+  __syncthreads();
+  long long tk[DBG ? 8 : 1], t0 = 0;
+  if (DBG) for (int q = 0; q < 8; ++q) tk[q] = 0;
+#define CGP2_TICK(slot) do { if (DBG && cta == 0 && tid == 0) { long long t1 = clock64(); tk[slot] += t1 - t0; t0 = t1; } } while (0)
+  if (DBG && cta == 0 && tid == 0) t0 = clock64();
+  int par = 0;
+
+  while (true) {
+    if (tid == 0) { int any = 0; for (int c = 0; c < m; ++c) any |= (s_state[c] == 0 || s_state[c] == 3); s_any = any; }
+    __syncthreads();
+    if (!s_any) break;
+    double* g0w = par ? A.g0b : A.g0a;                 // scattered into now, read in C
+    double* g0z = par ? A.g0a : A.g0b;                 // read in the previous C: zeroed in this C
+    // ---- F1: x += a d ; r -= a z ; |r|^2 ; d = r + beta d     (streams x and r; z is dead afterwards)
+    for (int col = 0; col < m; ++col) {
+      const int state = s_state[col];
+      if (state != 0 && state != 3) continue;
+      const double beta = s_beta[col], a = s_a[col];
+      double* x = A.x + (long)col * A.npad; double* r = A.r + (long)col * A.npad;
+      double* d = A.d + (long)col * A.npad; const double* z = A.z + (long)col * A.npad;
+      double rr = 0.0;
+      for (int ul0 = warp; ul0 < nu; ul0 += 2 * nwarp) {
+        double2 xv[2][2], rv[2][2];
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+          const int ul = ul0 + h * nwarp;
+          if (ul < nu) {
+            const long base = (u_lo + ul) * 128 + lane * CG_PTS;
+            xv[h][0] = *(const double2*)(x + base); xv[h][1] = *(const double2*)(x + base + 2);
+            rv[h][0] = *(const double2*)(r + base); rv[h][1] = *(const double2*)(r + base + 2);
+          }
+        }
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+          const int ul = ul0 + h * nwarp;
+          if (ul >= nu) continue;
+          const long base = (u_lo + ul) * 128 + lane * CG_PTS;
+          double2* sdu = (double2*)(sd + (long)ul * 128); const double2* szu = (const double2*)(sz + (long)ul * 128);
+          double2 x0 = xv[h][0], x1 = xv[h][1], r0 = rv[h][0], r1 = rv[h][1];
+          double2 d0, d1, z0, z1;
+          if (LEVEL >= 2) { d0 = sdu[lane]; d1 = sdu[32 + lane]; z0 = szu[lane]; z1 = szu[32 + lane]; }
+          else { d0 = *(const double2*)(d + base); d1 = *(const double2*)(d + base + 2); z0 = *(const double2*)(z + base); z1 = *(const double2*)(z + base + 2); }
+          x0.x = fma(a, d0.x, x0.x); x0.y = fma(a, d0.y, x0.y); x1.x = fma(a, d1.x, x1.x); x1.y = fma(a, d1.y, x1.y);
+          r0.x = fma(-a, z0.x, r0.x); r0.y = fma(-a, z0.y, r0.y); r1.x = fma(-a, z1.x, r1.x); r1.y = fma(-a, z1.y, r1.y);
+          rr = fma(r0.x, r0.x, rr); rr = fma(r0.y, r0.y, rr); rr = fma(r1.x, r1.x, rr); rr = fma(r1.y, r1.y, rr);
+          *(double2*)(x + base) = x0; *(double2*)(x + base + 2) = x1;
+          *(double2*)(r + base) = r0; *(double2*)(r + base + 2) = r1;
+          if (state == 3) continue;                        // final update only
+          d0.x = fma(beta, d0.x, r0.x); d0.y = fma(beta, d0.y, r0.y); d1.x = fma(beta, d1.x, r1.x); d1.y = fma(beta, d1.y, r1.y);
+          if (LEVEL >= 2) { sdu[lane] = d0; sdu[32 + lane] = d1; }
+          else { *(double2*)(d + base) = d0; *(double2*)(d + base + 2) = d1; }
+        }
+      }
+      const double t = block_sum(rr, s_red);             // (its barriers also order F1's z reads before F2's scratch writes)
+      if (tid == 0) A.part[((long)0 * m + col) * nctas + cta] = t;
+    }
+    CGP2_TICK(5);
+    // ---- F2: g0 += Mx'(sw d)     (shared memory only at LEVEL 2; the reduction scratch aliases z)
+    for (int col = 0; col < m; ++col) {
+      if (s_state[col] != 0) continue;
+      const double* d = A.d + (long)col * A.npad; double* g0 = g0w + (long)col * G.N;
+      double* wscr = stg + (long)warp * CGP_WSCR2; int* woff = (int*)(wscr + VPP * 33);
+      for (int ul = warp; ul < nu; ul += nwarp) {
+        const long base = (u_lo + ul) * 128 + lane * CG_PTS;
+        const double2* sdu = (const double2*)(sd + (long)ul * 128);
+        double dn[CG_PTS], uu[CG_PTS * P];
+        {
+          double2 d0, d1;
+          if (LEVEL >= 2) { d0 = sdu[lane]; d1 = sdu[32 + lane]; }
+          else { d0 = *(const double2*)(d + base); d1 = *(const double2*)(d + base + 2); }
+          dn[0] = d0.x; dn[1] = d0.y; dn[2] = d1.x; dn[3] = d1.y;
+#pragma unroll
+          for (int q = 0; q < CG_PTS * P / 2; ++q) {
+            const double2 t = (LEVEL >= 1) ? ((const double2*)(sU + (long)ul * 128 * P))[q * 32 + lane] : __ldg((const double2*)(A.U + base * P) + q);
+            uu[2 * q] = t.x; uu[2 * q + 1] = t.y;
+          }
+        }
+        double acc[NW];
+#pragma unroll
+        for (int v = 0; v < NW; ++v) acc[v] = 0.0;
+        int cur;
+        {
+          int cellq[CG_PTS];
+#pragma unroll
+          for (int q = 0; q < CG_PTS; ++q) {
+            const int j0 = decode_j(uu[q * P], G.ng[0]);
+            cellq[q] = (P == 1) ? j0 : j0 + decode_j(uu[q * P + P - 1], G.ng[P - 1]) * ng0;
+          }
+          cur = cellq[CG_PTS - 1];
+          // two points at a time (register budget); points of this thread that fall in an EARLIER cell than its
+          // last one go to the grid directly (rare)
+#pragma unroll
+          for (int q0 = 0; q0 < CG_PTS; q0 += 2) {
+            int jj[2][P]; double cc[2][P][4];
+#pragma unroll
+            for (int h = 0; h < 2; ++h)
+#pragma unroll
+              for (int dd = 0; dd < P; ++dd) decode_u(uu[(q0 + h) * P + dd], G.ng[dd], jj[h][dd], cc[h][dd]);
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+              const int q = q0 + h;
+              const double vi = sw * dn[q];
+              if (cellq[q] == cur) {
+                if (P == 1) {
+#pragma unroll
+                  for (int a2 = 0; a2 < 4; ++a2) acc[a2] = fma(cc[h][0][a2], vi, acc[a2]);
+                } else {
+#pragma unroll
+                  for (int b = 0; b < 4; ++b) {
+                    const double wb = cc[h][P - 1][b] * vi;
+#pragma unroll
+                    for (int a2 = 0; a2 < 4; ++a2) acc[b * 4 + a2] = fma(cc[h][0][a2], wb, acc[b * 4 + a2]);
+                  }
+                }
+              } else {
+                double one[NW];
+                if (P == 1) {
+#pragma unroll
+                  for (int a2 = 0; a2 < 4; ++a2) one[a2] = cc[h][0][a2] * vi;
+                } else {
+#pragma unroll
+                  for (int b = 0; b < 4; ++b) {
+                    const double wb = cc[h][P - 1][b] * vi;
+#pragma unroll
+                    for (int a2 = 0; a2 < 4; ++a2) one[b * 4 + a2] = cc[h][0][a2] * wb;
+                  }
+                }
+                flush_nodes<P>(G, g0, cellq[q], one);
+              }
+            }
+          }
+        }
+        // segmented reduction through this warp's scratch, VPP node values per pass
+        const int off_cur = (P == 1) ? cur : (cur / ng0) * (int)G.stride[1] + (cur % ng0);
+        const int k = lane % VPP, h = lane / VPP;
+#pragma unroll
+        for (int ps = 0; ps < NPASS; ++ps) {
+          __syncwarp();
+          if (ps == 0) woff[lane] = off_cur;
+#pragma unroll
+          for (int v = 0; v < VPP; ++v) wscr[v * 33 + lane] = acc[ps * VPP + v];
+          __syncwarp();
+          const int kv = ps * VPP + k;
+          const int node_off = (P == 1) ? kv : (kv >> 2) * (int)G.stride[1] + (kv & 3);
+          double run = 0.0; int po = woff[h * VPP];
+#pragma unroll
+          for (int i2 = 0; i2 < VPP; ++i2) {
+            const int co = woff[h * VPP + i2];
+            const double v = wscr[k * 33 + h * VPP + i2];
+            if (co != po) { if (run != 0.0) atomicAdd(g0 + po + node_off, run); run = 0.0; po = co; }
+            run += v;
+          }
+          if (run != 0.0) atomicAdd(g0 + po + node_off, run);
+        }
+      }
+    }
+    CGP2_TICK(0);
+    grid_barrier(A.bar, phase);
+    CGP2_TICK(1);
+    // ---- C: node window of u = Kg g0, then z = sw Mx u + d and the three dot products
+    for (int col = 0; col < m; ++col) {
+      if (s_state[col] != 0) continue;
+      const double* T = g0w + (long)col * G.N;
+      if (P == 1) {
+        for (int q = tid; q < ng0; q += CGP2_THREADS) stg[q] = __ldcg(T + q);
+        __syncthreads();
+        for (int a2 = warp; a2 < wr; a2 += nwarp) {
+          double acc2 = 0.0;
+          for (int b = lane; b < ng0; b += 32) acc2 = fma(A.K0[(long)(rlo + a2) * ng0 + b], stg[b], acc2);
+          acc2 = warp_sum(acc2);
+          if (lane == 0) uwin[a2] = acc2;
+        }
+        __syncthreads();
+      } else {
+        const int ng1 = G.ng[1];
+        const long tb = (G.N > (long)ng0 * ng0) ? G.N : (long)ng0 * ng0;
+        double* sT = stg; double* sK1 = stg + ((tb + 1) & ~1L); double* sW = sK1 + (((long)A.wcap * ng1 + 1) & ~1L);
+        for (long q = tid; q < G.N / 2; q += CGP2_THREADS) cp_async16(sT + 2 * q, T + 2 * q);
+        if ((G.N & 1) && tid == 0) sT[G.N - 1] = __ldcg(T + G.N - 1);
+        for (int q = tid; q < wr * ng1; q += CGP2_THREADS) sK1[q] = A.K1[(long)rlo * ng1 + q];
+        cp_async_wait_all();
+        __syncthreads();
+        for (int q = tid; q < wr * ng0; q += CGP2_THREADS) {           // W[bw][a'] = sum_b' K1[rlo+bw][b'] T[b'][a']
+          const int bw = q / ng0, ap = q - bw * ng0;
+          double a0 = 0.0, a1 = 0.0;
+          int bp = 0;
+          for (; bp + 1 < ng1; bp += 2) {
+            a0 = fma(sK1[bw * ng1 + bp], sT[(long)bp * ng0 + ap], a0);
+            a1 = fma(sK1[bw * ng1 + bp + 1], sT[(long)(bp + 1) * ng0 + ap], a1);
+          }
+          if (bp < ng1) a0 = fma(sK1[bw * ng1 + bp], sT[(long)bp * ng0 + ap], a0);
+          sW[q] = a0 + a1;
+        }
+        __syncthreads();
+        double* sK0T = stg;                                           // overwrites T (dead); W lies beyond it
+        const long nk = (long)ng0 * ng0;
+        for (long q = tid; q < nk / 2; q += CGP2_THREADS) cp_async16(sK0T + 2 * q, A.K0T + 2 * q);
+        if ((nk & 1) && tid == 0) sK0T[nk - 1] = A.K0T[nk - 1];
+        cp_async_wait_all();
+        __syncthreads();
+        for (int q = tid; q < wr * ng0; q += CGP2_THREADS) {           // u[bw][a] = sum_a' K0T[a'][a] W[bw][a']
+          const int bw = q / ng0, a2 = q - bw * ng0;
+          double a0 = 0.0, a1 = 0.0;
+          int ap = 0;
+          for (; ap + 1 < ng0; ap += 2) {
+            a0 = fma(sK0T[(long)ap * ng0 + a2], sW[bw * ng0 + ap], a0);
+            a1 = fma(sK0T[(long)(ap + 1) * ng0 + a2], sW[bw * ng0 + ap + 1], a1);
+          }
+          if (ap < ng0) a0 = fma(sK0T[(long)ap * ng0 + a2], sW[bw * ng0 + ap], a0);
+          uwin[q] = a0 + a1;
+        }
+        __syncthreads();
+      }
+      CGP2_TICK(6);
+      const double* d = A.d + (long)col * A.npad; double* z = A.z + (long)col * A.npad; const double* r = A.r + (long)col * A.npad;
+      double dz = 0.0, rz = 0.0, zz = 0.0;
+      for (int ul = warp; ul < nu; ul += nwarp) {
+        const long base = (u_lo + ul) * 128 + lane * CG_PTS;
+        const double2* sdu = (const double2*)(sd + (long)ul * 128); double2* szu = (double2*)(sz + (long)ul * 128);
+        double dv[CG_PTS], rv[CG_PTS], uu[CG_PTS * P], zv[CG_PTS];
+        {
+          const double2 r0 = *(const double2*)(r + base), r1 = *(const double2*)(r + base + 2);
+          rv[0] = r0.x; rv[1] = r0.y; rv[2] = r1.x; rv[3] = r1.y;
+          double2 d0, d1;
+          if (LEVEL >= 2) { d0 = sdu[lane]; d1 = sdu[32 + lane]; }
+          else { d0 = *(const double2*)(d + base); d1 = *(const double2*)(d + base + 2); }
+          dv[0] = d0.x; dv[1] = d0.y; dv[2] = d1.x; dv[3] = d1.y;
+#pragma unroll
+          for (int q = 0; q < CG_PTS * P / 2; ++q) {
+            const double2 t = (LEVEL >= 1) ? ((const double2*)(sU + (long)ul * 128 * P))[q * 32 + lane] : __ldg((const double2*)(A.U + base * P) + q);
+            uu[2 * q] = t.x; uu[2 * q + 1] = t.y;
+          }
+        }
+#pragma unroll
+        for (int q = 0; q < CG_PTS; ++q) {
+          int j[P]; double c[P][4];
+#pragma unroll
+          for (int dd = 0; dd < P; ++dd) decode_u(uu[q * P + dd], G.ng[dd], j[dd], c[dd]);
+          double mu = 0.0;
+          if (P == 1) {
+            const double* nv = uwin + (j[0] - rlo);
+#pragma unroll
+            for (int a2 = 0; a2 < 4; ++a2) mu = fma(c[0][a2], nv[a2], mu);
+          } else {
+#pragma unroll
+            for (int b = 0; b < 4; ++b) {
+              const double* nv = uwin + (long)(j[P - 1] + b - rlo) * ng0 + j[0];
+              double rb = 0.0;
+#pragma unroll
+              for (int a2 = 0; a2 < 4; ++a2) rb = fma(c[0][a2], nv[a2], rb);
+              mu = fma(c[P - 1][b], rb, mu);
+            }
+          }
+          const double zi = (base + q < A.n) ? fma(sw, mu, dv[q]) : 0.0;
+          zv[q] = zi; dz = fma(dv[q], zi, dz); rz = fma(rv[q], zi, rz); zz = fma(zi, zi, zz);
+        }
+        if (LEVEL >= 2) { szu[lane] = make_double2(zv[0], zv[1]); szu[32 + lane] = make_double2(zv[2], zv[3]); }
+        else { *(double2*)(z + base) = make_double2(zv[0], zv[1]); *(double2*)(z + base + 2) = make_double2(zv[2], zv[3]); }
+      }
+      double* gz = g0z + (long)col * G.N;
+      for (long q = (long)cta * CGP2_THREADS + tid; q < G.N; q += (long)nctas * CGP2_THREADS) gz[q] = 0.0;
+      double t = block_sum(dz, s_red);
+      if (tid == 0) A.part[((long)1 * m + col) * nctas + cta] = t;
+      t = block_sum(rz, s_red);
+      if (tid == 0) A.part[((long)2 * m + col) * nctas + cta] = t;
+      t = block_sum(zz, s_red);
+      if (tid == 0) A.part[((long)3 * m + col) * nctas + cta] = t;
+    }
+    CGP2_TICK(2);
+    grid_barrier(A.bar, phase);
+    CGP2_TICK(3);
+    for (int job = warp; job < 4 * m; job += nwarp) {         // one warp per (quantity, column): fixed summation order
+      const int w = job / m, col = job - w * m, state = s_state[col];
+      if (!((state == 0) || (state == 3 && w == 0))) continue;
+      double acc2 = 0.0;
+      for (int i = lane; i < nctas; i += 32) acc2 += __ldcg(A.part + ((long)w * m + col) * nctas + i);
+      acc2 = warp_sum(acc2);
+      if (lane == 0) s_sum[w][col] = acc2;
+    }
+    __syncthreads();
+    for (int col = tid; col < m; col += CGP2_THREADS) {
+      const int state = s_state[col];
+      if (state != 0 && state != 3) continue;
+      const double rr = s_sum[0][col];
+      if (state == 3) { s_rel[col] = sqrt(rr) / s_nb[col]; s_state[col] = s_final[col]; }
+      else {
+        const double a = rr / s_sum[1][col];
+        const double rrn = fma(a * a, s_sum[3][col], fma(-2.0 * a, s_sum[2][col], rr));
+        const double it = s_it[col] + 1.0, rel = sqrt(fmax(rrn, 0.0)) / s_nb[col];
+        s_a[col] = a; s_it[col] = it; s_rel[col] = rel;
+        if (!(rel >= tol)) { s_state[col] = 3; s_final[col] = 1; }            // apx.m:295-298
+        else if (it + 1.0 > maxit) { s_state[col] = 3; s_final[col] = 2; }    // `for iter=2:maxit` exhausted
+        else s_beta[col] = rrn / rr;
+      }
+    }
+    par ^= 1;
+    __syncthreads();
+    CGP2_TICK(4);
+  }
+  if (DBG && cta == 0 && tid == 0) for (int q = 0; q < 8; ++q) A.dbg[q] = tk[q];
+  if (cta == 0 && tid < m) {
+    double* ct = A.ctl + tid * CT_STRIDE;
+    ct[CT_DONE] = (double)s_state[tid]; ct[CT_ITER] = s_it[tid]; ct[CT_RELRES] = s_rel[tid];
   }
 }
 
