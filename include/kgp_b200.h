@@ -77,6 +77,19 @@ const char* kgp_version(void);
 void kgp_opt_default(kgp_opt* opt);
 int  kgp_set_profiling(kgp_ctx* ctx, int on);   /* on: time GEMM launches separately (adds syncs) */
 
+/* multi-GPU: one context per rank / GPU, NCCL over NVLink.  No reference counterpart (the
+ * reference runs one Octave process per GP layer, kgp/layers.py:63).  Rank 0 obtains the 128-byte NCCL id, the
+ * host layer ships it to the other ranks (torch.distributed in this repo), every rank then calls kgp_comm_init.
+ * After that kgp_eval on the exact path shards ONE n x n problem over the ranks (block columns of the Cholesky,
+ * rows of the triangular inverse, tiles of the inverse); every rank must issue the same calls with the same
+ * data and receives the same results.  nccl_lib_path may be NULL (libnccl.so.2 on the loader path). */
+int kgp_nccl_unique_id(char* out128, const char* nccl_lib_path);
+const char* kgp_dist_last_error(void);
+int kgp_comm_init(kgp_ctx* ctx, int nranks, int rank, const char* id128, const char* nccl_lib_path);
+/* ownership maps of the sharded exact path (host logic, callable without a GPU) */
+int  kgp_dist_col_owner(int block, int nranks);              /* rank owning block column `block` (NB = 512) */
+long kgp_dist_zrow_begin(int rank, int nranks, long n);     /* first row of Z = L^-T owned by `rank`; rank = nranks gives the padded order */
+
 /* data: replaces eng.push('X_<set>',X) / push('y_<set>',y)  (kgp/backend/gpml.py:152-158) */
 int kgp_set_data_host(kgp_ctx* ctx, int slot, const double* X, long n, int D, const double* y /* may be NULL */);
 int kgp_set_data_dev (kgp_ctx* ctx, int slot, const double* X, long n, int D, const double* y /* may be NULL */);

@@ -69,6 +69,11 @@ SIGNATURES = {
     'kgp_bench_dmma_peak': (C.c_int, [C.c_void_p, C.c_int, _DP]),
     'kgp_bench_dgemm': (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, _DP, _DP]),
     'kgp_bench_syrk': (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, _DP, _DP]),
+    'kgp_nccl_unique_id': (C.c_int, [C.c_char_p, C.c_char_p]),
+    'kgp_dist_last_error': (C.c_char_p, []),
+    'kgp_comm_init': (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_char_p, C.c_char_p]),
+    'kgp_dist_col_owner': (C.c_int, [C.c_int, C.c_int]),
+    'kgp_dist_zrow_begin': (C.c_long, [C.c_int, C.c_int, C.c_long]),
 }
 
 
@@ -85,6 +90,29 @@ def lib():
             fn.argtypes = args
         _lib = l
     return _lib
+
+
+def nccl_lib_path():
+    """libnccl.so.2 as shipped with PyTorch (nvidia-nccl wheel); None -> the loader's default search."""
+    try:
+        import nvidia.nccl as _n
+        for base in list(getattr(_n, '__path__', [])):
+            cand = os.path.join(base, 'lib', 'libnccl.so.2')
+            if os.path.isfile(cand):
+                return cand
+    except Exception:
+        pass
+    return None
+
+
+def nccl_unique_id():
+    """128-byte NCCL id (rank 0 calls this; the host layer ships it to the other ranks)."""
+    buf = C.create_string_buffer(128)
+    p = nccl_lib_path()
+    rc = lib().kgp_nccl_unique_id(buf, p.encode() if p else None)
+    if rc != OK:
+        raise KgpError(rc, lib().kgp_dist_last_error().decode())
+    return buf.raw
 
 
 def _ptr(a):
@@ -187,6 +215,11 @@ class Context(object):
         for a in range(na.value):
             out.append(cat[o:o + lens[a]].copy()); o += lens[a]
         return out
+
+    def comm_init(self, nranks, rank, unique_id):
+        """Join the NCCL communicator of a multi-GPU job (one Context per rank)."""
+        p = nccl_lib_path()
+        self._chk(self._l.kgp_comm_init(self._h, int(nranks), int(rank), unique_id, p.encode() if p else None))
 
     def set_profiling(self, on):
         self._chk(self._l.kgp_set_profiling(self._h, int(bool(on))))

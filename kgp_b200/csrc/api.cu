@@ -18,6 +18,9 @@ int grid_predict(kgp_ctx* c, const double* Xs, long ns, double* ymu, double* ys2
 int grid_create(kgp_ctx* c, int slot, int eq, double k);
 void grid_free(kgp_ctx* c);
 int grid_init(kgp_ctx* c);
+int dist_unique_id(char* out128, const char* libpath, std::string& err);
+int dist_init(kgp_ctx* c, int nranks, int rank, const char* id128, const char* libpath);
+void dist_free(kgp_ctx* c);
 
 // FP64 DMMA issue-rate micro-benchmark: 8 warps/SMSP-worth of independent DMMA chains
 __global__ void dmma_peak_kernel(double* out, int iters) {
@@ -80,6 +83,7 @@ int kgp_ctx_destroy(kgp_ctx* c) {
   cudaStreamSynchronize(c->stream);
   if (c->stream2) cudaStreamSynchronize(c->stream2);
   grid_free(c);
+  dist_free(c);
   DevBuf* bufs[] = {&c->M, &c->W2, &c->Dws, &c->xs, &c->s, &c->mu, &c->inv_ell, &c->ym, &c->alpha, &c->tvec,
                     &c->parts, &c->rows, &c->scal, &c->hypm, &c->dX, &c->fac, &c->pred_K, &c->pred_x, &c->pred_s,
                     &c->pred_a, &c->pred_b, &c->pred_out, &c->pred_X};
@@ -92,6 +96,23 @@ int kgp_ctx_destroy(kgp_ctx* c) {
   if (c->stream2) cudaStreamDestroy(c->stream2);
   delete c;
   return KGP_OK;
+}
+
+static std::string g_dist_err;
+int kgp_nccl_unique_id(char* out128, const char* nccl_lib_path) {
+  if (!out128) return KGP_BAD_ARG;
+  return dist_unique_id(out128, nccl_lib_path, g_dist_err);
+}
+const char* kgp_dist_last_error(void) { return g_dist_err.c_str(); }
+int kgp_comm_init(kgp_ctx* c, int nranks, int rank, const char* id128, const char* nccl_lib_path) {
+  if (!c) return KGP_BAD_ARG;
+  if (nranks > 1 && !id128) return c->fail(KGP_BAD_ARG, "kgp_comm_init needs the 128-byte NCCL unique id");
+  return dist_init(c, nranks, rank, id128, nccl_lib_path);
+}
+int kgp_dist_col_owner(int block, int nranks) { return nranks > 0 ? dist_col_owner(block, nranks) : -1; }
+long kgp_dist_zrow_begin(int rank, int nranks, long n) {
+  const long np = ((n + 127) / 128) * 128;
+  return dist_zrow_begin(rank, nranks, np, NB);
 }
 
 const char* kgp_last_error(kgp_ctx* c) { return c ? c->err.c_str() : "null context"; }

@@ -65,6 +65,12 @@ struct kgp_ctx {
   // what the factorisation state corresponds to
   unsigned long st_slot_ver = 0, st_model_ver = 0; int st_slot = -1; int st_level = -1;  // -1 none, 0 L+alpha, 2 +dX
   double st_nlZ = 0.0; std::vector<double> st_dnlZ;
+  // multi-GPU (exact_dist.cu): one context per rank, NCCL communicator over all ranks of the job
+  int nranks = 1, rank = 0; void* nccl_comm = nullptr;
+  cudaStream_t stream_p = nullptr;                    // panel stream: factorisation of the next panel + its broadcast
+  cudaEvent_t dev_ev[8];                              // panel ready [2], panel buffer free [2], look-ahead column updated
+  kgp::DevBuf PB[2];                                  // packed panels (rows x NB)
+  double dist_ms_comm = 0.0;
   // grid-path state lives in grid.cu (opaque)
   void* gridstate = nullptr;
 

@@ -30,6 +30,7 @@ namespace kgp {
 enum : int { GEMM_FULL = 0, GEMM_LOWER = 1 };
 enum : int { KTRI_NONE = 0, KTRI_FROM_M0 = 1 };
 
+constexpr int GEMM_MAX_BATCH = 96;
 constexpr int GEMM_MAX_BANDS = 160;     // 160 bands x 8 rows x 128 = order 163 840
 struct GemmArgs {
   const double* A; long lda;   // A[m][k], row m at A + m*lda
@@ -44,6 +45,12 @@ struct GemmArgs {
   double* Cdiag; int nb;       // if Cdiag && (m0/nb == n0/nb): C tile -> Cdiag[blk][m0%nb.., n0%nb..], ld = nb
   int cdiag_only;              // (repurposed) 1: prefetch the C tile into L2 at tile start
   int nbands; int band_base[GEMM_MAX_BANDS];   // LOWER shape: tile index at which each band of 8 tile-rows starts
+  // multi-GPU sharding of one launch (exact_dist.cu):
+  int own_mod, own_rem;        // own_mod > 1: this rank computes tiles idx = t*own_mod + own_rem only (cost-balanced: neighbours cost alike)
+  // batch of FULL problems that share ntn, K and the operand matrices but start at different rows
+  // (trailing update of the block columns a rank owns): problem p covers rows >= bat_roff[p] of A and C and the
+  // ntn tile columns whose B rows start at bat_roff[p]; C tile (tm,tn) of problem p sits at C[roff+tm*128][roff+tn*128]
+  int nbatch; int bat_roff[GEMM_MAX_BATCH]; int bat_base[GEMM_MAX_BATCH + 1];
 };
 
 #ifndef KGP_GEMM_BK
@@ -77,6 +84,11 @@ __device__ __forceinline__ void dmma884(double& c0, double& c1, double a, double
 
 // number of tiles a launch must cover
 inline long gemm_num_tiles(const GemmArgs& g) {
+  if (g.nbatch > 0) {
+    long t = 0;
+    for (int p = 0; p < g.nbatch; ++p) t += (long)(g.ntm - g.bat_roff[p] / 128) * g.ntn;
+    return t;
+  }
   if (g.shape == GEMM_FULL) return (long)g.ntm * g.ntn;
   long t = 0;
   for (int tm = 0; tm < g.ntm; ++tm) t += (tm + 1 < g.ntn ? tm + 1 : g.ntn);
@@ -124,11 +136,28 @@ __device__ __forceinline__ void gemm_tile_coords(const GemmArgs& g, long idx, in
 struct GemmTile {
   int m0, n0, nk; bool in_diag;
   const double* Ag; const double* Bg;
+  long coff;                   // offset of the problem's C origin (batched mode), else 0
 };
 __device__ __forceinline__ bool gemm_fetch_tile(const GemmArgs& g, long idx, long ntiles, GemmTile& t) {
   for (; idx < ntiles; idx += gridDim.x) {     // (cdiag_only filters are not used with skipping here)
     int tm, tn;
-    gemm_tile_coords(g, idx, tm, tn);
+    if (g.nbatch > 0) {
+      int lo = 0, hi = g.nbatch - 1;
+      while (lo < hi) { int mid = (lo + hi + 1) >> 1; if (g.bat_base[mid] <= idx) lo = mid; else hi = mid - 1; }
+      const int roff = g.bat_roff[lo], ntm = g.ntm - roff / 128;
+      const long r0 = idx - g.bat_base[lo], per_band = (long)GEMM_BAND * g.ntn;
+      const int b = (int)(r0 / per_band); const long r = r0 - (long)b * per_band;
+      const int rows = (ntm - b * GEMM_BAND < GEMM_BAND) ? ntm - b * GEMM_BAND : GEMM_BAND;
+      tn = (int)(r / rows); tm = b * GEMM_BAND + (int)(r % rows);
+      t.m0 = tm * GEMM_BM; t.n0 = tn * GEMM_BN; t.in_diag = false;
+      t.nk = (g.kend - g.kbeg) / GEMM_BK;
+      t.Ag = g.A + (long)(roff + t.m0) * g.lda + g.kbeg;
+      t.Bg = g.B + (long)(roff + t.n0) * g.ldb + g.kbeg;
+      t.coff = (long)roff * g.ldc + roff;
+      return true;
+    }
+    gemm_tile_coords(g, g.own_mod > 1 ? idx * g.own_mod + g.own_rem : idx, tm, tn);
+    t.coff = 0;
     t.m0 = tm * GEMM_BM; t.n0 = tn * GEMM_BN;
     t.in_diag = g.Cdiag && (t.m0 / g.nb) == (t.n0 / g.nb);
     const int kbeg = g.kbeg + (g.ktri == KTRI_FROM_M0 ? t.m0 : 0);
@@ -194,7 +223,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) dgemm_nt_kernel(const GemmArg
       int blk = ct.m0 / g.nb;
       Cp = g.Cdiag + (long)blk * g.nb * g.nb; ldc = g.nb;
       crow0 = ct.m0 - blk * g.nb; ccol0 = ct.n0 - blk * g.nb;
-    } else { Cp = g.C; ldc = g.ldc; crow0 = ct.m0; ccol0 = ct.n0; }
+    } else { Cp = g.C + ct.coff; ldc = g.ldc; crow0 = ct.m0; ccol0 = ct.n0; }
     const double alpha = g.alpha, beta = g.beta;
     const bool last_tile = cidx + gridDim.x >= ntiles;
     if (beta != 0.0 && g.cdiag_only) {   // pull the C tile towards L2 while the main loop runs
@@ -300,6 +329,12 @@ inline void gemm_launch(const GemmArgs& g_in, cudaStream_t st) {
     }
     g.nbands = nb_;
   }
+  if (g.nbatch > 0) {
+    long base = 0;
+    for (int p = 0; p < g.nbatch; ++p) { g.bat_base[p] = (int)base; base += (long)(g.ntm - g.bat_roff[p] / 128) * g.ntn; }
+    g.bat_base[g.nbatch] = (int)base;
+  }
+  if (g.own_mod > 1) nt = (nt > g.own_rem) ? (nt - g.own_rem + g.own_mod - 1) / g.own_mod : 0;
   if (nt <= 0 || g.kend <= g.kbeg) return;
   long grid = (g_gemm_persist && nt > g_gemm_num_sms) ? g_gemm_num_sms : nt;
   g.cdiag_only = g_gemm_prefetch_c;

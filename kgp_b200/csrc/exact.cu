@@ -14,6 +14,7 @@
 //   Dws: the diagonal NB x NB blocks of B^{-1} while W2's diagonal blocks still hold Z
 #include "ctx.h"
 #include "exact_kernels2.cuh"
+#include "exact_dist.cuh"
 #include <math.h>
 #include <string.h>
 
@@ -22,11 +23,17 @@ namespace kgp {
 static inline double count_gemm(kgp_ctx* c, const GemmArgs& g) {
   c->stats.gemm_launches++; c->stats.kernel_launches++;
   double f = 0.0;
+  if (g.nbatch > 0) {
+    for (int p = 0; p < g.nbatch; ++p) f += 2.0 * 128.0 * 128.0 * (double)(g.kend - g.kbeg) * (g.ntm - g.bat_roff[p] / 128) * g.ntn;
+    c->stats.gemm_flops += f;
+    return f;
+  }
   for (int tm = 0; tm < g.ntm; ++tm) {
     int ntn = (g.shape == GEMM_LOWER) ? (tm + 1 < g.ntn ? tm + 1 : g.ntn) : g.ntn;
     int kb = g.kbeg + (g.ktri == KTRI_FROM_M0 ? tm * 128 : 0);
     f += 2.0 * 128.0 * 128.0 * (double)(g.kend - kb) * ntn;
   }
+  if (g.own_mod > 1) f /= g.own_mod;
   c->stats.gemm_flops += f;
   return f;
 }
@@ -76,26 +83,31 @@ static void trsm_block(kgp_ctx* c, double* X, long ldx, long mrows, const double
   }
 }
 
+// one NB-wide panel of the blocked Cholesky: factor the diagonal block and the block column below it (on c->stream)
+static void factor_panel(kgp_ctx* c, long k0, int w) {
+  double* M = c->M.d(); const long ld = c->np, np = c->np;
+  for (int cb = 0; cb < w / 128; ++cb) {
+    const long j = k0 + cb * 128, r0 = j + 128, mrows = np - r0;
+    potrf_diag128_kernel<<<1, PD_THREADS, PD_SMEM, c->stream>>>(M + j * ld + j, ld, (int)j, c->d_info);
+    c->stats.kernel_launches++;
+    if (mrows > 0) {
+      trsm128_rows_kernel<<<(unsigned)(mrows / 128), TR_THREADS, TR_SMEM, c->stream>>>(
+          M + r0 * ld + j, ld, mrows, M + j * ld + j, ld);
+      c->stats.kernel_launches++;
+      const long ncols = k0 + w - r0;
+      c->gemm_class = 0;
+      if (ncols > 0)
+        gemm(c, mkgemm(M + r0 * ld + j, ld, M + r0 * ld + j, ld, M + r0 * ld + r0, ld,
+                       (int)(mrows / 128), (int)(ncols / 128), 0, 128, GEMM_LOWER, KTRI_NONE, -1.0, 1.0));
+    }
+  }
+}
 // blocked right-looking Cholesky of the lower triangle of M (two levels: NB / 128)
 static void potrf(kgp_ctx* c) {
   double* M = c->M.d(); const long ld = c->np, np = c->np;
   for (long k0 = 0; k0 < np; k0 += NB) {
     const int w = (int)((np - k0 < NB) ? np - k0 : NB);
-    for (int cb = 0; cb < w / 128; ++cb) {
-      const long j = k0 + cb * 128, r0 = j + 128, mrows = np - r0;
-      potrf_diag128_kernel<<<1, PD_THREADS, PD_SMEM, c->stream>>>(M + j * ld + j, ld, (int)j, c->d_info);
-      c->stats.kernel_launches++;
-      if (mrows > 0) {
-        trsm128_rows_kernel<<<(unsigned)(mrows / 128), TR_THREADS, TR_SMEM, c->stream>>>(
-            M + r0 * ld + j, ld, mrows, M + j * ld + j, ld);
-        c->stats.kernel_launches++;
-        const long ncols = k0 + w - r0;
-        c->gemm_class = 0;
-        if (ncols > 0)
-          gemm(c, mkgemm(M + r0 * ld + j, ld, M + r0 * ld + j, ld, M + r0 * ld + r0, ld,
-                         (int)(mrows / 128), (int)(ncols / 128), 0, 128, GEMM_LOWER, KTRI_NONE, -1.0, 1.0));
-      }
-    }
+    factor_panel(c, k0, w);
     const long r0 = k0 + w, mt = (np - r0) / 128;
     c->gemm_class = 1;
     if (mt > 0)
@@ -129,6 +141,172 @@ static void zzt(kgp_ctx* c) {
   dim3 grid((unsigned)(c->np / 32), (unsigned)(c->np / 32)), blk(32, 8);
   mirror_finalize_kernel<<<grid, blk, 0, c->stream>>>(W, ld, c->np, c->Dws.d(), NB);
   c->stats.kernel_launches++;
+}
+
+// ===== multi-GPU variants (see exact_dist.cuh) ============================================================
+int dist_unique_id(char* out128, const char* libpath, std::string& err) {
+  NcclApi& api = nccl_api(libpath);
+  if (!api.ok) { err = api.err; return KGP_CUDA_ERR; }
+  kgp_ncclUniqueId id; int r = api.GetUniqueId(&id);
+  if (r != 0) { err = api.GetErrorString(r); return KGP_CUDA_ERR; }
+  memcpy(out128, id.internal, 128);
+  return KGP_OK;
+}
+int dist_init(kgp_ctx* c, int nranks, int rank, const char* id128, const char* libpath) {
+  if (nranks < 1 || rank < 0 || rank >= nranks) return c->fail(KGP_BAD_ARG, "bad rank %d of %d", rank, nranks);
+  if (nranks == 1) { c->nranks = 1; c->rank = 0; return KGP_OK; }
+  NcclApi& api = nccl_api(libpath);
+  if (!api.ok) return c->fail(KGP_CUDA_ERR, "%s", api.err.c_str());
+  kgp_ncclUniqueId id; memcpy(id.internal, id128, 128);
+  KGP_CUDA(c, cudaSetDevice(c->device));
+  KGP_NCCL(c, api, api.CommInitRank(&c->nccl_comm, nranks, id, rank));
+  c->nranks = nranks; c->rank = rank;
+  if (!c->stream_p) {
+    int lo = 0, hi = 0; cudaDeviceGetStreamPriorityRange(&lo, &hi);
+    KGP_CUDA(c, cudaStreamCreateWithPriority(&c->stream_p, cudaStreamNonBlocking, hi));
+    for (int i = 0; i < 8; ++i) KGP_CUDA(c, cudaEventCreateWithFlags(&c->dev_ev[i], cudaEventDisableTiming));
+  }
+  return KGP_OK;
+}
+void dist_free(kgp_ctx* c) {
+  if (c->nccl_comm) { NcclApi& api = nccl_api(nullptr); if (api.ok) api.CommDestroy(c->nccl_comm); c->nccl_comm = nullptr; }
+  if (c->stream_p) { cudaStreamDestroy(c->stream_p); for (int i = 0; i < 8; ++i) cudaEventDestroy(c->dev_ev[i]); c->stream_p = nullptr; }
+  c->PB[0].release(); c->PB[1].release();
+}
+
+// Cholesky with block columns dealt cyclically over the ranks, panel broadcast, look-ahead 1
+static int potrf_dist(kgp_ctx* c) {
+  NcclApi& api = nccl_api(nullptr);
+  double* M = c->M.d(); const long ld = c->np, np = c->np;
+  const int P = c->nranks, me = c->rank, nblk = (int)((np + NB - 1) / NB);
+  cudaStream_t sm = c->stream, sp = c->stream_p;
+  cudaEvent_t *ev_panel = c->dev_ev, *ev_free = c->dev_ev + 2, ev_la = c->dev_ev[4];
+  for (int b = 0; b < 2; ++b) KGP_CUDA(c, c->PB[b].ensure((size_t)np * NB * 8));
+  KGP_CUDA(c, cudaEventRecord(ev_la, sm));                          // block column 0 is ready once the kernel matrix is built
+  for (int k = 0; k < nblk; ++k) {
+    const long k0 = (long)k * NB; const int w = (int)((np - k0 < NB) ? np - k0 : NB);
+    const long rows = np - k0; const int owner = dist_col_owner(k, P), b = k & 1;
+    double* PB = c->PB[b].d();
+    // ---- panel stream: factor (owner), broadcast, unpack
+    if (k >= 2) KGP_CUDA(c, cudaStreamWaitEvent(sp, ev_free[b], 0));
+    if (me == owner) {
+      KGP_CUDA(c, cudaStreamWaitEvent(sp, ev_la, 0));
+      c->stream = sp; factor_panel(c, k0, w); c->stream = sm;
+      KGP_CUDA(c, cudaMemcpy2DAsync(PB, (size_t)w * 8, M + k0 * ld + k0, (size_t)ld * 8, (size_t)w * 8, (size_t)rows, cudaMemcpyDeviceToDevice, sp));
+    }
+    KGP_NCCL(c, api, api.Broadcast(PB, PB, (size_t)rows * w, KGP_NCCL_DOUBLE, owner, c->nccl_comm, sp));
+    if (me != owner)
+      KGP_CUDA(c, cudaMemcpy2DAsync(M + k0 * ld + k0, (size_t)ld * 8, PB, (size_t)w * 8, (size_t)w * 8, (size_t)rows, cudaMemcpyDeviceToDevice, sp));
+    KGP_CUDA(c, cudaEventRecord(ev_panel[b], sp));
+    // ---- main stream: update the block columns this rank owns with the packed panel
+    KGP_CUDA(c, cudaStreamWaitEvent(sm, ev_panel[b], 0));
+    const long t0 = k0 + w;                                         // first trailing row
+    if (t0 < np) {
+      const double* Pt = PB + (long)w * w;                          // panel rows from t0 on (row pitch w)
+      const int ntm = (int)((np - t0) / 128);
+      auto launch = [&](const std::vector<int>& blocks) {
+        if (blocks.empty()) return;
+        // blocks of full width NB go into one batched launch; a narrower last block gets its own
+        GemmArgs g = mkgemm(Pt, w, Pt, w, M + t0 * ld + t0, ld, ntm, NB / 128, 0, w, GEMM_FULL, KTRI_NONE, -1.0, 1.0);
+        for (int J : blocks) {
+          const long j0 = (long)J * NB; const int wj = (int)((np - j0 < NB) ? np - j0 : NB);
+          if (wj == NB && g.nbatch < GEMM_MAX_BATCH) g.bat_roff[g.nbatch++] = (int)(j0 - t0);
+          else {
+            GemmArgs h = mkgemm(Pt + (j0 - t0) * w, w, Pt + (j0 - t0) * w, w, M + j0 * ld + j0, ld, (int)((np - j0) / 128), wj / 128,
+                                0, w, GEMM_FULL, KTRI_NONE, -1.0, 1.0);
+            c->gemm_class = 1; gemm(c, h);
+          }
+        }
+        if (g.nbatch > 0) { c->gemm_class = 1; gemm(c, g); }
+      };
+      std::vector<int> first, rest;
+      for (int J = k + 1; J < nblk; ++J) if (dist_col_owner(J, P) == me) (J == k + 1 ? first : rest).push_back(J);
+      launch(first);
+      if (!first.empty()) KGP_CUDA(c, cudaEventRecord(ev_la, sm));   // look-ahead: panel k+1 may be factored now
+      launch(rest);
+    }
+    KGP_CUDA(c, cudaEventRecord(ev_free[b], sm));
+  }
+  KGP_CUDA(c, cudaStreamWaitEvent(sm, ev_panel[(nblk - 1) & 1], 0));
+  if (nblk >= 2) KGP_CUDA(c, cudaStreamWaitEvent(sm, ev_panel[(nblk - 2) & 1], 0));
+  return KGP_OK;
+}
+
+// Z = L^-T on this rank's rows [a, b) (right-looking), then every rank's rows are broadcast to all
+static int zsweep_dist(kgp_ctx* c) {
+  NcclApi& api = nccl_api(nullptr);
+  const double* M = c->M.d(); double* W = c->W2.d(); const long ld = c->np, np = c->np;
+  const int P = c->nranks, me = c->rank;
+  const long a = dist_zrow_begin(me, P, np, NB), b = dist_zrow_begin(me + 1, P, np, NB);
+  cudaStream_t st = c->stream;
+  if (b > a) {
+    KGP_CUDA(c, cudaMemsetAsync(W + a * ld, 0, (size_t)(b - a) * ld * 8, st));
+    for (long k0 = (a / NB) * NB; k0 < np; k0 += NB) {
+      const int w = (int)((np - k0 < NB) ? np - k0 : NB);
+      const long hi = (b < k0 + w) ? b : k0 + w, nact = hi - a;
+      if (k0 >= a && k0 < b) {
+        set_identity_kernel<<<(unsigned)(((long)w * w + 255) / 256), 256, 0, st>>>(W + k0 * ld + k0, ld, w);
+        c->stats.kernel_launches++;
+      }
+      trsm_block(c, W + a * ld + k0, ld, nact, M + k0 * ld + k0, ld, w);
+      const long rest = np - k0 - w;
+      c->gemm_class = 2;
+      if (rest > 0)
+        gemm(c, mkgemm(W + a * ld + k0, ld, M + (k0 + w) * ld + k0, ld, W + a * ld + k0 + w, ld, (int)(nact / 128), (int)(rest / 128),
+                       0, w, GEMM_FULL, KTRI_NONE, -1.0, 1.0));
+    }
+  }
+  cudaEventRecord(c->ev[12], st);
+  KGP_NCCL(c, api, api.GroupStart());
+  for (int r = 0; r < P; ++r) {
+    const long ra = dist_zrow_begin(r, P, np, NB), rb = dist_zrow_begin(r + 1, P, np, NB);
+    if (rb > ra) KGP_NCCL(c, api, api.Broadcast(W + ra * ld, W + ra * ld, (size_t)(rb - ra) * ld, KGP_NCCL_DOUBLE, r, c->nccl_comm, st));
+  }
+  KGP_NCCL(c, api, api.GroupEnd());
+  cudaEventRecord(c->ev[13], st);
+  return KGP_OK;
+}
+
+template <int DP>
+static void launch_reduce_tiles(kgp_ctx* c, const GemmArgs& g, long ntiles, long n, double sf2, double inv_sn2) {
+  static bool attr = false;
+  if (!attr) { cudaFuncSetAttribute(reduce_grad_tile_kernel<DP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)reduce_tile_smem<DP>()); attr = true; }
+  const long grid = std::min<long>(ntiles, 148L * 8);
+  reduce_grad_tile_kernel<DP><<<(unsigned)grid, 128, reduce_tile_smem<DP>(), c->stream>>>(g, ntiles, c->W2.d(), c->np, n, c->xs.d(),
+                                                                                          c->alpha.d(), sf2, inv_sn2, c->rows.d());
+}
+// B^-1 = Z Z^T on this rank's share of the lower tiles + the gradient pass over the same tiles + all-reduce of the row sums
+static int zzt_reduce_dist(kgp_ctx* c, long n, double sf2, double inv_sn2) {
+  NcclApi& api = nccl_api(nullptr);
+  double* W = c->W2.d(); const long ld = c->np; const int nt = (int)(c->np / 128); const int Dp = c->Dp;
+  GemmArgs g = mkgemm(W, ld, W, ld, W, ld, nt, nt, 0, (int)c->np, GEMM_LOWER, KTRI_FROM_M0, 1.0, 0.0);
+  g.Cdiag = c->Dws.d(); g.nb = NB; g.own_mod = c->nranks; g.own_rem = c->rank;
+  c->gemm_class = 4;
+  gemm(c, g);
+  cudaEventRecord(c->ev[5], c->stream);
+  // the same enumeration for the reduction (band table as gemm_launch builds it)
+  long base = 0; int nb_ = 0;
+  for (int r0 = 0; r0 < g.ntm && nb_ < GEMM_MAX_BANDS; r0 += 8) {
+    g.band_base[nb_++] = (int)base;
+    for (int r = r0; r < r0 + 8 && r < g.ntm; ++r) base += (r + 1 < g.ntn) ? r + 1 : g.ntn;
+  }
+  g.nbands = nb_;
+  long ntiles = gemm_num_tiles(g);
+  ntiles = (ntiles > g.own_rem) ? (ntiles - g.own_rem + g.own_mod - 1) / g.own_mod : 0;
+  const size_t rbytes = (size_t)c->np * (Dp + 3) * 8;
+  KGP_CUDA(c, cudaMemsetAsync(c->rows.p, 0, rbytes, c->stream));
+  if (ntiles > 0) {
+    switch (Dp) {
+      case 4: launch_reduce_tiles<4>(c, g, ntiles, n, sf2, inv_sn2); break;
+      case 8: launch_reduce_tiles<8>(c, g, ntiles, n, sf2, inv_sn2); break;
+      case 16: launch_reduce_tiles<16>(c, g, ntiles, n, sf2, inv_sn2); break;
+      default: launch_reduce_tiles<32>(c, g, ntiles, n, sf2, inv_sn2); break;
+    }
+    c->stats.kernel_launches++;
+  }
+  if (c->nranks > 1)
+    KGP_NCCL(c, api, api.AllReduce(c->rows.p, c->rows.p, (size_t)c->np * (Dp + 3), KGP_NCCL_DOUBLE, KGP_NCCL_SUM, c->nccl_comm, c->stream));
+  return KGP_OK;
 }
 
 static int pick_dp(int D) { return D <= 4 ? 4 : D <= 8 ? 8 : D <= 16 ? 16 : 32; }
@@ -205,11 +383,12 @@ int exact_eval(kgp_ctx* c, int slot, int want, double* nlZ_out, double* dnlZ_out
   }
   c->stats.kernel_launches += 4;
   cudaEventRecord(c->ev[1], st);
-  potrf(c);
+  const bool dist = c->nranks > 1;
+  if (dist) { rc = potrf_dist(c); if (rc) return rc; } else potrf(c);
   logdet_kernel<<<1, 1024, 0, st>>>(c->M.d(), np, n, c->scal.d() + 100);
   c->stats.kernel_launches++;
   cudaEventRecord(c->ev[2], st);
-  zsweep(c);
+  if (dist) { rc = zsweep_dist(c); if (rc) return rc; } else zsweep(c);
   cudaEventRecord(c->ev[3], st);
   {  // alpha = B^{-1} ym / sn2 = Z (Z^T ym) / sn2
     const int nch = (int)((np + 511) / 512);
@@ -223,7 +402,15 @@ int exact_eval(kgp_ctx* c, int slot, int want, double* nlZ_out, double* dnlZ_out
   }
   cudaEventRecord(c->ev[4], st);
   int nsc = 0;
-  if (want >= 1) {
+  static const bool tile_reduce = getenv("KGP_TILE_REDUCE") && atoi(getenv("KGP_TILE_REDUCE"));
+  if (want >= 1 && (dist || tile_reduce)) {
+    rc = zzt_reduce_dist(c, n, sf2, 1.0 / sn2); if (rc) return rc;
+    grad_scalars_kernel<<<1, 1024, 0, st>>>(c->rows.d(), n, Dp, c->xs.d(), c->alpha.d(), c->scal.d());
+    dx_from_rows_kernel<<<(unsigned)((n * D + 255) / 256), 256, 0, st>>>(c->rows.d(), n, D, Dp, c->fac.d(), c->dX.d());
+    if (nmean) mean_grad_kernel<<<D + 1, 1024, 0, st>>>(S.X.d(), c->alpha.d(), n, D, c->scal.d() + 110);
+    c->stats.kernel_launches += 2 + (nmean ? 1 : 0);
+    cudaEventRecord(c->ev[6], st);
+  } else if (want >= 1) {
     zzt(c);
     cudaEventRecord(c->ev[5], st);
     const int ntr = (int)(np / 128), nt32 = (int)(np / 32);
