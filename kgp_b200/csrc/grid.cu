@@ -572,7 +572,7 @@ int grid_eval(kgp_ctx* c, int slot, int want, double* nlZ_out, double* dnlZ_out)
     }
     if (nmean) { mean_grad_kernel<<<D + 1, 1024, 0, st>>>(S.X.d(), g->x.d(), n, D, g->dhyp.d() + nhyp); c->stats.kernel_launches++; }
   }
-  if (want >= 2) {
+  if (want >= 1) {      // dnlZ/dX is one gather pass: always kept, so a following get_dlik_dx reuses this inference
     const double* dmean = nullptr;
     if (m.mean_mask & 1) { KGP_CUDA(c, cudaMemcpyAsync(g->dmean.p, m.hyp_mean.data(), D * 8, cudaMemcpyHostToDevice, st)); dmean = g->dmean.d(); }
     for_p(G.p, [&](auto P) {
@@ -602,7 +602,7 @@ int grid_eval(kgp_ctx* c, int slot, int want, double* nlZ_out, double* dnlZ_out)
     if (m.mean_mask & 2) dnlZ_out[o++] = hd[nhyp + D];
   }
   g->st_slot = slot; g->st_slot_ver = S.version; g->st_model_ver = m.version; g->st_grid_ver = c->grid.version;
-  g->st_level = want >= 2 ? 2 : 0;
+  g->st_level = want >= 1 ? 2 : 0;
   return KGP_OK;
 }
 

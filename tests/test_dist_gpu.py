@@ -1,0 +1,55 @@
+"""GPU tests of the sharded exact path (SURVEY App. D "Multi-GPU invariance": 1e-10 relative to the 1-GPU result).
+
+* the tile-symmetric gradient pass + ownership-filtered Z Z^T launch also run on ONE GPU (KGP_TILE_REDUCE=1):
+  parity against the oracle at 1e-8 like the default path;
+* with >= 2 GPUs visible: torchrun world_size 2 over NCCL, sharded vs unsharded results."""
+import os
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+_SINGLE = r'''
+import sys, os, numpy as np
+sys.path.insert(0, %(root)r); sys.path.insert(0, os.path.join(%(root)r, 'oracle'))
+from kgp_b200 import B200GP
+import gpml_exact as orc
+rng = np.random.RandomState(7); n, D = 1100, 5
+X = rng.randn(n, D); y = np.sin(X.sum(1)) + 0.1 * rng.randn(n)
+ell = np.log(np.array([1.0, 2.0, 0.7, 1.5, 3.0]))
+hyp = {'lik': -1.5, 'mean': [], 'cov': np.concatenate([ell, [0.3]])[:, None]}
+gp = B200GP(); gp.configure(D, dict(hyp), {}, 'infExact', 'meanZero', 'covSEard', 'likGauss', 'dlikExact', verbose=0)
+gp.update_data('tr', X, y[:, None])
+nlZ, g = gp.eng.eval(0, 2, gp._n_hyp); dX = gp.get_dlik_dx('tr')
+oh = {'cov': np.concatenate([ell, [0.3]]), 'lik': -1.5, 'mean': []}
+post, nlZ0, d0 = orc.inf_exact(oh, ['meanZero'], 'ard', X, y)
+dX0 = orc.dlik_exact(oh, ['meanZero'], 'ard', X, y, ard_reference_form=False)
+g0 = np.concatenate([d0['cov'], [d0['lik']]])
+rel = lambda a, b: float(np.max(np.abs(np.asarray(a) - np.asarray(b))) / np.max(np.abs(b)))
+print('REL', rel(nlZ, nlZ0), rel(g, g0), rel(dX, dX0))
+'''
+
+
+def test_tile_reduce_path_single_gpu(built_lib):
+    env = dict(os.environ, KGP_TILE_REDUCE='1')
+    out = subprocess.check_output([sys.executable, '-c', _SINGLE % {'root': ROOT}], env=env, timeout=600).decode()
+    vals = [float(v) for v in [l for l in out.splitlines() if l.startswith('REL')][0].split()[1:]]
+    assert max(vals) < 1e-8, out
+
+
+def test_sharded_equals_single_world2(built_lib):
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip('needs 2 GPUs')
+    cmd = [sys.executable, '-m', 'torch.distributed.run', '--nnodes=1', '--nproc-per-node', '2', '--master-addr', '127.0.0.1',
+           '--master-port', '29533', os.path.join(ROOT, 'scripts', 'dist_exact.py'), '1000', '2600']
+    out = subprocess.check_output(cmd, timeout=900, stderr=subprocess.STDOUT).decode()
+    lines = [l for l in out.splitlines() if l.startswith('n=')]
+    assert len(lines) == 2, out
+    for l in lines:
+        rels = [float(tok) for tok in l.split('rel')[1].replace('dnlZ', ' ').replace('dX', ' ').replace('ymu', ' ').replace('ys2', ' ').split()]
+        assert max(rels) < 1e-10, l
