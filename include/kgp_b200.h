@@ -127,6 +127,13 @@ int kgp_grid_create(kgp_ctx* ctx, int slot, int eq, double k);
 int kgp_grid_set_host(kgp_ctx* ctx, int n_axes, const int* axis_len, const double* axes_concat);
 int kgp_grid_get_host(kgp_ctx* ctx, int* n_axes, int* axis_len /* >= 16 ints */, double* axes_concat /* may be NULL */);
 
+/* Chebyshev-Hutchinson log-det (opt.ldB2_cheby = 1; GPML/cov/apx.m:336-391): inject the probe vectors
+ * (V is m x n, one probe per row, entries +-1) and the eigenvalue bound emax.  The reference draws them with
+ * randn('seed',.) / eigs inside Octave, which cannot be reproduced, so a parity run passes the
+ * same V and emax to the oracle and to the engine.  V = NULL returns to generated probes (splitmix64 of
+ * opt.ldB2_cheby_seed) and power-iteration emax; emax <= 0 with V given estimates emax only. */
+int kgp_set_probes_host(kgp_ctx* ctx, const double* V, long n, int m, double emax);
+
 /* posterior pieces for tests / callers that want them (host copies) */
 int kgp_get_alpha_host(kgp_ctx* ctx, double* alpha /* n */);
 

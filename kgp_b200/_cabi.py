@@ -69,6 +69,7 @@ SIGNATURES = {
     'kgp_bench_dmma_peak': (C.c_int, [C.c_void_p, C.c_int, _DP]),
     'kgp_bench_dgemm': (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, _DP, _DP]),
     'kgp_bench_syrk': (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, _DP, _DP]),
+    'kgp_set_probes_host': (C.c_int, [C.c_void_p, C.c_void_p, C.c_long, C.c_int, C.c_double]),
     'kgp_nccl_unique_id': (C.c_int, [C.c_char_p, C.c_char_p]),
     'kgp_dist_last_error': (C.c_char_p, []),
     'kgp_comm_init': (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_char_p, C.c_char_p]),
@@ -220,6 +221,14 @@ class Context(object):
         """Join the NCCL communicator of a multi-GPU job (one Context per rank)."""
         p = nccl_lib_path()
         self._chk(self._l.kgp_comm_init(self._h, int(nranks), int(rank), unique_id, p.encode() if p else None))
+
+    def set_probes(self, V=None, emax=0.0):
+        """Inject Hutchinson probes (V: n x m, +-1) and emax for opt.ldB2_cheby; V=None -> generated probes."""
+        if V is None:
+            self._chk(self._l.kgp_set_probes_host(self._h, None, 0, 0, 0.0)); return
+        V = np.asarray(V, dtype=np.float64)
+        Vt = np.ascontiguousarray(V.T)                    # one probe per row
+        self._chk(self._l.kgp_set_probes_host(self._h, _ptr(Vt), Vt.shape[1], Vt.shape[0], float(emax)))
 
     def set_profiling(self, on):
         self._chk(self._l.kgp_set_profiling(self._h, int(bool(on))))

@@ -18,6 +18,7 @@ int grid_predict(kgp_ctx* c, const double* Xs, long ns, double* ymu, double* ys2
 int grid_create(kgp_ctx* c, int slot, int eq, double k);
 void grid_free(kgp_ctx* c);
 int grid_init(kgp_ctx* c);
+int grid_set_probes(kgp_ctx* c, const double* V, long n, int m, double emax);
 int dist_unique_id(char* out128, const char* libpath, std::string& err);
 int dist_init(kgp_ctx* c, int nranks, int rank, const char* id128, const char* libpath);
 void dist_free(kgp_ctx* c);
@@ -98,6 +99,11 @@ int kgp_ctx_destroy(kgp_ctx* c) {
   return KGP_OK;
 }
 
+int kgp_set_probes_host(kgp_ctx* c, const double* V, long n, int m, double emax) {
+  if (!c) return KGP_BAD_ARG;
+  cudaSetDevice(c->device);
+  return grid_set_probes(c, V, n, m, emax);
+}
 static std::string g_dist_err;
 int kgp_nccl_unique_id(char* out128, const char* nccl_lib_path) {
   if (!out128) return KGP_BAD_ARG;

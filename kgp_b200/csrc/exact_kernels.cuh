@@ -146,36 +146,64 @@ inline size_t kbuild_smem(int Dp) { int ldx = ((Dp + 11) / 16) * 16 + 4; return 
 // info: 1-based global index of the first non-positive pivot (atomicMin), else unchanged.
 // ---------------------------------------------------------------------------
 constexpr int PD_THREADS = 512;
-constexpr int PD_LD = 129;
-constexpr int PD_SMEM = 128 * PD_LD * 8;
+constexpr int PD_SMEM = 0;
+// The whole block lives in registers: thread (ti, tj) owns rows 4 ti..4 ti+3 x columns 8 tj..8 tj+7.  Step k: the
+// owners of column k publish it (unscaled) through a double-buffered shared vector, ONE barrier, then every thread
+// forms l_i = a_ik / sqrt(a_kk) for its rows and columns itself and applies the rank-1 update to its 32 elements.
 __global__ void __launch_bounds__(PD_THREADS) potrf_diag128_kernel(double* __restrict__ A, long ld, int j0, int* info) {
-  extern __shared__ __align__(16) double a[];
-  const int tid = threadIdx.x;
-  for (int q = tid; q < 128 * 128; q += PD_THREADS) {
-    int r = q >> 7, c = q & 127;
-    a[r * PD_LD + c] = A[(long)r * ld + c];
-  }
-  for (int k = 0; k < 128; ++k) {
-    __syncthreads();
-    double d = a[k * PD_LD + k];
-    if (!(d > 0.0)) {
-      if (tid == 0) atomicMin(info, j0 + k + 1);
-      d = nan("");
+  __shared__ double colk[2][128];
+  const int tid = threadIdx.x, ti = tid >> 4, tj = tid & 15;
+  const int r0 = ti * 4, c0 = tj * 8;
+  const bool active = c0 <= r0 + 3;                    // the 4 x 8 block touches the lower triangle
+  double a[4][8];
+#pragma unroll
+  for (int r = 0; r < 4; ++r)
+#pragma unroll
+    for (int c = 0; c < 8; c += 2) {
+      double2 v = make_double2(0.0, 0.0);
+      if (active) v = *reinterpret_cast<const double2*>(A + (long)(r0 + r) * ld + c0 + c);
+      a[r][c] = v.x; a[r][c + 1] = v.y;
     }
-    double dk = sqrt(d);
-    for (int i = k + 1 + tid; i < 128; i += PD_THREADS) a[i * PD_LD + k] = a[i * PD_LD + k] / dk;
-    __syncthreads();
-    if (tid == 0) a[k * PD_LD + k] = dk;
-    const int m = 127 - k;
-    for (int q = tid; q < m * m; q += PD_THREADS) {
-      int i = k + 1 + q / m, j = k + 1 + q % m;
-      if (j <= i) a[i * PD_LD + j] -= a[i * PD_LD + k] * a[j * PD_LD + k];
+  for (int kb = 0; kb < 16; ++kb) {
+#pragma unroll
+    for (int kk = 0; kk < 8; ++kk) {
+      const int k = kb * 8 + kk;
+      double* ck = colk[k & 1];
+      if (tj == kb) {
+#pragma unroll
+        for (int r = 0; r < 4; ++r) if (r0 + r >= k) ck[r0 + r] = a[r][kk];
+      }
+      __syncthreads();
+      if (r0 + 3 < k) continue;                        // (uniform per thread; no barrier below)
+      double akk = ck[k];
+      if (!(akk > 0.0)) {
+        if (tid == (k >> 2) * 16 + (k >> 3)) atomicMin(info, j0 + k + 1);
+        akk = nan("");
+      }
+      const double dk = sqrt(akk), inv = 1.0 / dk;
+      if (active) {
+        double lr[4], lc[8];
+#pragma unroll
+        for (int r = 0; r < 4; ++r) lr[r] = (r0 + r > k) ? ck[r0 + r] * inv : 0.0;
+#pragma unroll
+        for (int c = 0; c < 8; ++c) lc[c] = (c0 + c > k) ? ck[c0 + c] * inv : 0.0;
+#pragma unroll
+        for (int r = 0; r < 4; ++r)
+#pragma unroll
+          for (int c = 0; c < 8; ++c) a[r][c] = fma(-lr[r], lc[c], a[r][c]);
+        if (tj == kb) {
+#pragma unroll
+          for (int r = 0; r < 4; ++r) a[r][kk] = (r0 + r > k) ? lr[r] : ((r0 + r == k) ? dk : a[r][kk]);
+        }
+      }
     }
   }
-  __syncthreads();
-  for (int q = tid; q < 128 * 128; q += PD_THREADS) {
-    int r = q >> 7, c = q & 127;
-    if (c <= r) A[(long)r * ld + c] = a[r * PD_LD + c];
+  if (active) {
+#pragma unroll
+    for (int r = 0; r < 4; ++r)
+#pragma unroll
+      for (int c = 0; c < 8; ++c)
+        if (c0 + c <= r0 + r) A[(long)(r0 + r) * ld + c0 + c] = a[r][c];
   }
 }
 

@@ -7,7 +7,8 @@
 // the whole CG iteration is device-resident (scalars, convergence flag and iteration count live
 // in device memory; the host only polls the flag every few iterations).
 #include "ctx.h"
-#include "grid_cg.cuh"
+#include "grid_cheby.cuh"
+#include "exact_dist.cuh"
 #include <math.h>
 #include <string.h>
 #include <algorithm>
@@ -22,6 +23,8 @@ struct GridState {
   double* h_ctl = nullptr;                // pinned host copy of the control blocks
   long npad = 0; int sort_slot = -1; unsigned long sort_slot_ver = 0, sort_grid_ver = 0;
   cudaGraphExec_t cg_graph = nullptr; std::vector<char> cg_graph_key;
+  DevBuf probes, chT, chU, chY, chS, chC, chP, bva, bvb, chacc;   // Chebyshev log-det (grid_cheby.cuh)
+  long probes_n = 0; int probes_m = 0; double probes_emax = 0.0; bool probes_injected = false;
   DevBuf pdz, prr, bar, part4, g0b, wmaxd; int num_sms = 0; size_t smem_optin = 0; int cg_level_used = -1;
   int wmax = 0; int wmax_ctas = 0; unsigned long wmax_slot_ver = 0, wmax_grid_ver = 0; int wmax_slot = -1;
   int p = 0; int ng[GRID_MAXP] = {0}; long N = 0;
@@ -43,7 +46,8 @@ void grid_free(kgp_ctx* c) {
   DevBuf* bufs[] = {&g->axes, &g->Kf, &g->Vf, &g->Af, &g->ee, &g->eoff, &g->de, &g->zv, &g->Qm, &g->Pm, &g->g0, &g->g1,
                     &g->tgrid, &g->beta, &g->x, &g->r, &g->d, &g->z, &g->ym, &g->partA, &g->partB, &g->S, &g->hyp,
                     &g->hypm, &g->dX, &g->dhyp, &g->out, &g->sortk, &g->sorti, &g->keep, &g->dmean,
-                    &g->U, &g->perm, &g->sx, &g->sr, &g->sd, &g->sz, &g->ctl, &g->cnt, &g->KfT, &g->gm0, &g->gm1, &g->pdz, &g->prr, &g->bar, &g->part4, &g->g0b, &g->wmaxd};
+                    &g->U, &g->perm, &g->sx, &g->sr, &g->sd, &g->sz, &g->ctl, &g->cnt, &g->KfT, &g->gm0, &g->gm1, &g->pdz, &g->prr, &g->bar, &g->part4, &g->g0b, &g->wmaxd,
+                    &g->probes, &g->chT, &g->chU, &g->chY, &g->chS, &g->chC, &g->chP, &g->bva, &g->bvb, &g->chacc};
   for (DevBuf* b : bufs) b->release();
   if (g->h_ctl) cudaFreeHost(g->h_ctl);
   if (g->cg_graph) cudaGraphExecDestroy(g->cg_graph);
@@ -455,6 +459,157 @@ static int cg_solve_sorted(kgp_ctx* c, GridState* g, const GridDesc& G, int slot
   return KGP_OK;
 }
 
+// ---- Chebyshev-Hutchinson log-det and its derivatives (grid_cheby.cuh; apx.m:336-391) --------------------------
+__global__ void sum_scaled_acc_kernel(const double* __restrict__ part, int cnt, double coef, double* __restrict__ out) {
+  __shared__ double sh[32];
+  double t = sum_partials(part, cnt, sh);
+  if (threadIdx.x == 0) out[0] += coef * t;
+}
+// y = Kg x on grid vectors without clobbering x (kron_apply ping-pongs between its two buffers)
+static void kron_to(kgp_ctx* c, GridState* g, const GridDesc& G, const double* x, double* y, int skip) {
+  cudaMemcpyAsync(g->g0.p, x, G.N * 8, cudaMemcpyDeviceToDevice, c->stream);
+  double* r = kron_apply(c, g, G, g->g0.d(), g->g1.d(), skip);
+  cudaMemcpyAsync(y, r, G.N * 8, cudaMemcpyDeviceToDevice, c->stream);
+}
+static int cheby_logdet(kgp_ctx* c, GridState* g, const GridDesc& G, int slot, double sw, bool want_deriv, int kind, int Q, int nh) {
+  (void)kind; (void)Q; (void)nh;
+  Slot& S = c->slots[slot]; Model& mo = c->model;
+  const long n = S.n; const int D = S.D; cudaStream_t st = c->stream;
+  const int d = mo.opt.ldB2_cheby_degree > 0 ? mo.opt.ldB2_cheby_degree : 15;
+  if (d > 48) return c->fail(KGP_BAD_ARG, "ldB2_cheby_degree %d too large (max 48)", d);
+  int m = mo.opt.ldB2_cheby_hutch > 0 ? mo.opt.ldB2_cheby_hutch : 10;
+  if (g->probes_injected) {
+    if (g->probes_n != n) return c->fail(KGP_BAD_ARG, "injected probes have %ld rows, data has %ld", g->probes_n, n);
+    m = g->probes_m;
+  } else {
+    KGP_CUDA(c, g->probes.ensure((size_t)m * n * 8));
+    rademacher_kernel<<<(unsigned)(((long)m * n + 255) / 256), 256, 0, st>>>(mo.opt.ldB2_cheby_seed, n, m, g->probes.d());
+    g->probes_n = n; g->probes_m = m;
+  }
+  long ksz = 0; for (int q = 0; q < G.p; ++q) ksz += (long)G.ng[q] * G.ng[q];
+  KGP_CUDA(c, g->chT.ensure((size_t)d * G.N * 8)); KGP_CUDA(c, g->chU.ensure((size_t)d * G.N * 8));
+  KGP_CUDA(c, g->chY.ensure((size_t)d * G.N * 8)); KGP_CUDA(c, g->chS.ensure((size_t)d * d * 8));
+  KGP_CUDA(c, g->chC.ensure((size_t)2 * d * d * 8)); KGP_CUDA(c, g->chP.ensure((size_t)ksz * 8));
+  KGP_CUDA(c, g->bva.ensure(n * 8)); KGP_CUDA(c, g->bvb.ensure(n * 8)); KGP_CUDA(c, g->chacc.ensure(64));
+  const int nb = nblocks_for(n);
+  auto apply_step = [&](const double* bv, const double* v, double c1, double c2, double* Tj, double* Uj, double* out) {
+    scatter(c, G, S.X.d(), n, D, bv, sw, Tj);                               // T = Mx'(sW bv)
+    kron_to(c, g, G, Tj, Uj, -1);                                           // U = Kg T
+    for_p(G.p, [&](auto P) {
+      cheby_step_kernel<decltype(P)::value><<<nb, 256, 0, st>>>(G, S.X.d(), n, D, Uj, bv, v, c1, c2, out, g->partA.d());
+    });
+    c->stats.kernel_launches += 1;
+  };
+  // ---- emax: injected, or power iteration on B = I + sW K sW   (the reference: eigs(B,1,'lm'), apx.m:344-350)
+  double emax = g->probes_injected ? g->probes_emax : 0.0;
+  if (!(emax > 0.0)) {
+    const int its = mo.opt.ldB2_cheby_maxit > 0 ? mo.opt.ldB2_cheby_maxit : 50;
+    double nrm2 = (double)n, lam = 1.0;
+    KGP_CUDA(c, cudaMemcpyAsync(g->bva.p, g->probes.p, n * 8, cudaMemcpyDeviceToDevice, st));
+    double* cur = g->bva.d(); double* nxt = g->bvb.d();
+    for (int it = 0; it < its; ++it) {
+      apply_step(cur, cur, 1.0, sw, g->chT.d(), g->chU.d(), nxt);            // nxt = B cur ; partials of cur.nxt
+      sum_small_kernel<<<1, 256, 0, st>>>(g->partA.d(), nb, g->chacc.d() + 2);
+      dot_kernel<<<1, 1024, 0, st>>>(nxt, nxt, n, g->chacc.d() + 3);
+      double h2[2];
+      KGP_CUDA(c, cudaMemcpyAsync(h2, g->chacc.d() + 2, 16, cudaMemcpyDeviceToHost, st));
+      KGP_CUDA(c, cudaStreamSynchronize(st));
+      lam = h2[0] / nrm2;
+      vec_scale_copy_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(n, 1.0 / sqrt(h2[1]), nxt, nxt);
+      nrm2 = 1.0; std::swap(cur, nxt);
+    }
+    emax = lam;
+  }
+  // ---- polynomial coefficients exactly as apx.m:356-372
+  const double emin = 1.0, a = emin + emax, dl = 1.0 - emax / a, sf = 2.0 / a / (1.0 - 2.0 * dl), cI = 1.0 / (1.0 - 2.0 * dl);
+  std::vector<double> xk(d + 1), fk(d + 1), cc(d + 1, 0.0), Tk((size_t)(d + 1) * (d + 1));
+  for (int i = 0; i <= d; ++i) { xk[i] = cos(M_PI * ((double)i + 0.5) / (double)(d + 1)); fk[i] = log(((1.0 - 2.0 * dl) / 2.0) * xk[i] + 0.5); }
+  for (int r = 0; r <= d; ++r) {
+    Tk[(size_t)r * (d + 1)] = 1.0; if (d >= 1) Tk[(size_t)r * (d + 1) + 1] = xk[r];
+    for (int i = 2; i <= d; ++i) Tk[(size_t)r * (d + 1) + i] = 2.0 * xk[r] * Tk[(size_t)r * (d + 1) + i - 1] - Tk[(size_t)r * (d + 1) + i - 2];
+  }
+  for (int i = 0; i <= d; ++i) { double sacc = 0.0; for (int r = 0; r <= d; ++r) sacc += Tk[(size_t)r * (d + 1) + i] * fk[r]; cc[i] = 2.0 / (double)(d + 1) * sacc; }
+  cc[0] /= 2.0;
+  std::vector<double> p1(d + 1, 0.0), p2(d + 1, 0.0), p3(d + 1), pp(d + 1);
+  p1[0] = 1.0; p2[1] = 1.0;
+  for (int i = 0; i <= d; ++i) pp[i] = cc[0] * p1[i] + cc[1] * p2[i];
+  for (int i = 2; i <= d; ++i) {
+    p3[0] = -p1[0]; for (int q = 1; q <= d; ++q) p3[q] = 2.0 * p2[q - 1] - p1[q];
+    for (int q = 0; q <= d; ++q) pp[q] += cc[i] * p3[q];
+    p1 = p2; p2 = p3;
+  }
+  // coefficient tables of the grid-space derivative forms
+  std::vector<double> hC((size_t)2 * d * d, 0.0);             // [0]: C[u][s] for dhyp ; [1]: Wd[a][b] for sum(dW)
+  for (int j = 1; j <= d; ++j) {
+    const int kmax = (j + 1) / 2;
+    for (int k = 1; k <= kmax; ++k) {
+      double akj = sf * pp[j] / (double)m;
+      if (k == kmax && (j % 2) == 1) akj /= 2.0;
+      hC[(size_t)(j - k) * d + (k - 1)] += akj;
+    }
+    const double cj = sf * pp[j] / (4.0 * (double)m) / (sw * sw);
+    for (int l = 0; l < j; ++l) { hC[(size_t)d * d + (size_t)(j - 1 - l) * d + l] += cj; hC[(size_t)d * d + (size_t)l * d + (j - 1 - l)] += cj; }
+  }
+  KGP_CUDA(c, cudaMemcpyAsync(g->chC.p, hC.data(), hC.size() * 8, cudaMemcpyHostToDevice, st));
+  KGP_CUDA(c, cudaMemsetAsync(g->chP.p, 0, ksz * 8, st));
+  KGP_CUDA(c, cudaMemsetAsync(g->chacc.p, 0, 64, st));
+  // ---- probes of this rank
+  int lo = 0, hi = m;
+  if (c->nranks > 1) { const int base = m / c->nranks, extra = m % c->nranks; lo = c->rank * base + std::min(c->rank, extra); hi = lo + base + (c->rank < extra ? 1 : 0); }
+  for (int i = lo; i < hi; ++i) {
+    const double* v = g->probes.d() + (long)i * n;
+    dot_kernel<<<1, 1024, 0, st>>>(v, v, n, g->chacc.d() + 2);
+    sum_scaled_acc_kernel<<<1, 256, 0, st>>>(g->chacc.d() + 2, 1, pp[0] / (2.0 * m), g->chacc.d());      // j = 0 term: v'v p_0
+    const double* cur = v; double* bufs[2] = {g->bva.d(), g->bvb.d()};
+    for (int j = 0; j < d; ++j) {
+      double* nxt = bufs[j & 1];
+      apply_step(cur, v, sf - cI, sf * sw, g->chT.d() + (long)j * G.N, g->chU.d() + (long)j * G.N, nxt);   // Bs cur
+      sum_scaled_acc_kernel<<<1, 256, 0, st>>>(g->partA.d(), nb, pp[j + 1] / (2.0 * m), g->chacc.d());
+      cur = nxt;
+    }
+    c->stats.kernel_launches += 2 + d;
+    if (want_deriv) {
+      gram_small_kernel<<<dim3(d, d), 256, 0, st>>>(g->chT.d(), g->chU.d(), G.N, d, g->chS.d());
+      dot_kernel<<<1, 1024, 0, st>>>(g->chS.d(), g->chC.d() + (long)d * d, (long)d * d, g->chacc.d() + 2);
+      sum_scaled_acc_kernel<<<1, 256, 0, st>>>(g->chacc.d() + 2, 1, 1.0, g->chacc.d() + 1);
+      mix_small_kernel<<<dim3((unsigned)((G.N + 255) / 256), d), 256, 0, st>>>(g->chT.d(), g->chC.d(), G.N, d, g->chY.d());
+      for (int f = 0; f < G.p; ++f) {
+        const long inner = G.stride[f], outer = G.N / (inner * G.ng[f]);
+        for (int s2 = 0; s2 < d; ++s2) {
+          kron_to(c, g, G, g->chY.d() + (long)s2 * G.N, g->beta.d(), f);      // beta buffer as scratch (it is rewritten after the log-det section)
+          mode_gram_acc_kernel<<<dim3(G.ng[f], G.ng[f]), 128, 0, st>>>(g->beta.d(), g->chT.d() + (long)s2 * G.N, G.ng[f], inner, outer,
+                                                                    g->chP.d() + g->koff[f]);
+        }
+      }
+      c->stats.kernel_launches += 4 + 2 * d * G.p;
+    }
+  }
+  if (c->nranks > 1) {
+    NcclApi& api = nccl_api(nullptr);
+    KGP_NCCL(c, api, api.AllReduce(g->chP.p, g->chP.p, (size_t)ksz, KGP_NCCL_DOUBLE, KGP_NCCL_SUM, c->nccl_comm, st));
+    KGP_NCCL(c, api, api.AllReduce(g->chacc.p, g->chacc.p, 2, KGP_NCCL_DOUBLE, KGP_NCCL_SUM, c->nccl_comm, st));
+  }
+  // out[2] = ldB2 = n log(a)/2 + probe sum ; out[3] = sum(dW)
+  double h2[2];
+  KGP_CUDA(c, cudaMemcpyAsync(h2, g->chacc.p, 16, cudaMemcpyDeviceToHost, st));
+  KGP_CUDA(c, cudaStreamSynchronize(st));
+  h2[0] += (double)n * log(a) / 2.0;
+  KGP_CUDA(c, cudaMemcpyAsync(g->out.d() + 2, h2, 16, cudaMemcpyHostToDevice, st));
+  KGP_CUDA(c, cudaStreamSynchronize(st));
+  return KGP_OK;
+}
+
+int grid_set_probes(kgp_ctx* c, const double* V, long n, int m, double emax) {
+  GridState* g = gs(c);
+  if (!V || m <= 0) { g->probes_injected = false; return KGP_OK; }
+  KGP_CUDA(c, g->probes.ensure((size_t)m * n * 8));
+  KGP_CUDA(c, cudaMemcpyAsync(g->probes.p, V, (size_t)m * n * 8, cudaMemcpyHostToDevice, c->stream));
+  KGP_CUDA(c, cudaStreamSynchronize(c->stream));
+  g->probes_n = n; g->probes_m = m; g->probes_emax = emax; g->probes_injected = true;
+  c->model.version++;                                  // cached posteriors no longer match
+  return KGP_OK;
+}
+
 static bool gstate_valid(kgp_ctx* c, GridState* g, int slot, int level) {
   return g->st_level >= level && g->st_slot == slot && g->st_slot_ver == c->slots[slot].version &&
          g->st_model_ver == c->model.version && g->st_grid_ver == c->grid.version;
@@ -464,7 +619,7 @@ int grid_eval(kgp_ctx* c, int slot, int want, double* nlZ_out, double* dnlZ_out)
   GridState* g = gs(c); Slot& S = c->slots[slot]; Model& m = c->model;
   const long n = S.n; const int D = S.D;
   if (m.cov_kind != KGP_COV_SEISO && m.cov_kind != KGP_COV_SM) return c->fail(KGP_BAD_ARG, "infGrid supports covSEiso / covSM factors");
-  if (m.opt.ldB2_cheby) return c->fail(KGP_BAD_ARG, "opt.ldB2_cheby (Chebyshev log-det) is not built yet; Fiedler bound only");
+  const bool cheby = m.opt.ldB2_cheby != 0;
   GridDesc G; int rc = grid_setup(c, g, G); if (rc) return rc;
   if (G.p != D) return c->fail(KGP_BAD_ARG, "Grid and data dimension are different.");
   const int nh = factor_nhyp(m), nhyp = nh * G.p;
@@ -502,7 +657,7 @@ int grid_eval(kgp_ctx* c, int slot, int want, double* nlZ_out, double* dnlZ_out)
   // eigen-decompositions of all factors: one CTA each, on the side stream, overlapped with the CG solve
   cudaEventRecord(c->ev[10], st);
   cudaStreamWaitEvent(c->stream2, c->ev[10], 0);
-  jacobi_eig_kernel<<<G.p, EIG_THREADS, eig_smem, c->stream2>>>(eb, getenv("KGP_EIG_SWEEPS") ? atoi(getenv("KGP_EIG_SWEEPS")) : 40);
+  if (!cheby) jacobi_eig_kernel<<<G.p, EIG_THREADS, eig_smem, c->stream2>>>(eb, getenv("KGP_EIG_SWEEPS") ? atoi(getenv("KGP_EIG_SWEEPS")) : 40);
   cudaEventRecord(c->ev[11], c->stream2);
   c->stats.kernel_launches++;
   resid_mean_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(S.X.d(), S.has_y ? S.y.d() : nullptr, n, D, m.mean_mask, g->hypm.d(), g->ym.d(), n);
@@ -524,9 +679,13 @@ int grid_eval(kgp_ctx* c, int slot, int want, double* nlZ_out, double* dnlZ_out)
   dot_kernel<<<1, 1024, 0, st>>>(g->x.d(), g->x.d(), n, g->out.d() + 1);
   cudaEventRecord(c->ev[2], st);
 
-  // Fiedler bound (apx.m:236-240,312-318)
+  // Fiedler bound (apx.m:236-240,312-318) or the Chebyshev-Hutchinson estimator (apx.m:336-391)
   cudaStreamWaitEvent(st, c->ev[11], 0);
   const unsigned char* keep = nullptr;
+  if (cheby) {
+    rc = cheby_logdet(c, g, G, slot, sw, want >= 1, kind, Q, nh);
+    if (rc) return rc;
+  } else {
   if (n < G.N) {
     long Npad = 1; while (Npad < G.N) Npad <<= 1;
     KGP_CUDA(c, g->sortk.ensure(Npad * 8)); KGP_CUDA(c, g->sorti.ensure(Npad * 4)); KGP_CUDA(c, g->keep.ensure(G.N));
@@ -545,6 +704,7 @@ int grid_eval(kgp_ctx* c, int slot, int want, double* nlZ_out, double* dnlZ_out)
   sum_small_kernel<<<1, 256, 0, st>>>(g->partA.d(), fb, g->out.d() + 2);
   sum_small_kernel<<<1, 256, 0, st>>>(g->partB.d(), fb, g->out.d() + 3);
   c->stats.kernel_launches += 6;
+  }
 
   // beta = Kg Mx' alpha (needed by predict and deriv_x); T = Mx' alpha kept for dirder
   scatter(c, G, S.X.d(), n, D, g->x.d(), 1.0, g->tgrid.d());
@@ -557,10 +717,14 @@ int grid_eval(kgp_ctx* c, int slot, int want, double* nlZ_out, double* dnlZ_out)
     for (int d = 0; d < G.p; ++d) {
       const double am = axis_mean(c->grid.axes[d]);
       const long nn = (long)G.ng[d] * G.ng[d];
+      if (cheby) {      // log-det part: dK_d of the accumulated Krylov Gram matrix (cheby_logdet)
+        factor_dirder_kernel<<<nh, 256, 0, st>>>(kind, Q, g->hyp.d() + d * nh, G.ax[d], G.ng[d], am, g->chP.d() + g->koff[d], 1.0, g->dhyp.d() + d * nh, 0);
+      } else {
       // Fiedler part: dK_d( V diag(z) V' )
       fiedler_z_kernel<<<G.ng[d], 256, 0, st>>>(G, d, g->ee.d(), (const int*)g->eoff.p, g->de.d(), g->zv.d());
       vdv_kernel<<<(unsigned)((nn + 255) / 256), 256, 0, st>>>(g->Vf.d() + g->koff[d], g->zv.d(), G.ng[d], g->Qm.d());
       factor_dirder_kernel<<<nh, 256, 0, st>>>(kind, Q, g->hyp.d() + d * nh, G.ax[d], G.ng[d], am, g->Qm.d(), 1.0, g->dhyp.d() + d * nh, 0);
+      }
       // data-fit part: -1/2 dK_d( P ),  P = shp(v) shp(T)',  v = T with every other factor applied
       KGP_CUDA(c, cudaMemcpyAsync(g->g0.p, g->tgrid.p, G.N * 8, cudaMemcpyDeviceToDevice, st));
       double* v = kron_apply(c, g, G, g->g0.d(), g->g1.d(), d);

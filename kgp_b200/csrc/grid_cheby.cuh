@@ -1,0 +1,90 @@
+// KISS-GP path, part 5: stochastic (Chebyshev-Hutchinson) log-determinant, logdet_sample of GPML/cov/apx.m:336-391.
+//
+//   ldB2 = n log(a)/2 + 1/(2m) sum_i v_i' p(Bs) v_i ,  Bs = sf (I + sW K sW) - I/(1-2 dl),  p = degree-d Chebyshev
+// interpolant of log on the scaled interval, evaluated in the monomial basis exactly like the reference
+// (apx.m:365-372).  Probes v_i (Rademacher) and emax are explicit inputs (the reference's seed is
+// mis-wired); when none are injected they are generated from opt.ldB2_cheby_seed by splitmix64 and emax by power
+// iteration.
+//
+// Derivatives (apx.m:373-389) are bilinear forms in the Krylov vectors.  Because W is uniform (likGauss) every
+// one of them collapses to GRID space: with T_j = Mx'(sW Bs^j v) and U_j = Kg T_j (both by-products of the
+// recurrence) the hyper-derivative is  sum_{j,k} a_kj dK(T_{j-k}, T_{k-1})  and  sum(dW) = sum_j sf p_j /(4 m sW^2)
+// sum_l (T_{j-1-l}.U_l + T_l.U_{j-1-l}), so no n-vector other than the current Krylov pair is ever stored.
+// Probes are independent: with several ranks each one handles a contiguous share and the grid-sized
+// accumulators are all-reduced once.
+#pragma once
+#include "grid_cg.cuh"
+
+namespace kgp {
+
+// out = c1 * bv + c2 * (Mx u) ;  part[block] = sum v .* out
+template <int P>
+__global__ void cheby_step_kernel(GridDesc G, const double* __restrict__ X, long n, int D, const double* __restrict__ u,
+                                  const double* __restrict__ bv, const double* __restrict__ v, double c1, double c2,
+                                  double* __restrict__ out, double* __restrict__ part) {
+  __shared__ double sh[32];
+  double acc = 0.0;
+  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long)gridDim.x * blockDim.x) {
+    double xi[P], dd[P];
+#pragma unroll
+    for (int d = 0; d < P; ++d) xi[d] = X[i * D + d];
+    const double mu = interp_gather_point<P, false>(G, xi, u, dd);
+    const double o = fma(c2, mu, c1 * bv[i]);
+    out[i] = o;
+    acc = fma(v[i], o, acc);
+  }
+  const double t = block_sum(acc, sh);
+  if (threadIdx.x == 0) part[blockIdx.x] = t;
+}
+
+// Rademacher probes from a counter-based generator: V[col][i] = +-1 from splitmix64(seed, col*n + i)
+__global__ void rademacher_kernel(unsigned long long seed, long n, int m, double* __restrict__ V) {
+  long q = (long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (q >= n * m) return;
+  unsigned long long z = seed + 0x9E3779B97F4A7C15ULL * (unsigned long long)(q + 1);
+  z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ULL; z = (z ^ (z >> 27)) * 0x94D049BB133111EBULL; z ^= z >> 31;
+  V[q] = (z & 1ULL) ? 1.0 : -1.0;
+}
+
+// S[a][b] = T_a . U_b   (d x d dot products of N-vectors); one CTA per (a, b)
+__global__ void gram_small_kernel(const double* __restrict__ T, const double* __restrict__ U, long N, int d, double* __restrict__ S) {
+  __shared__ double sh[32];
+  const int a = blockIdx.x, b = blockIdx.y;
+  double acc = 0.0;
+  for (long q = threadIdx.x; q < N; q += blockDim.x) acc = fma(T[(long)a * N + q], U[(long)b * N + q], acc);
+  const double t = block_sum(acc, sh);
+  if (threadIdx.x == 0) S[a * d + b] = t;
+}
+
+// Y[s][q] = sum_u C[u][s] T[u][q]   (mix the Krylov grid vectors with the a_kj coefficients)
+__global__ void mix_small_kernel(const double* __restrict__ T, const double* __restrict__ C, long N, int d, double* __restrict__ Y) {
+  long q = (long)blockIdx.x * blockDim.x + threadIdx.x;
+  const int s = blockIdx.y;
+  if (q >= N) return;
+  double acc = 0.0;
+  for (int u = 0; u < d; ++u) acc = fma(C[u * d + s], T[(long)u * N + q], acc);
+  Y[(long)s * N + q] = acc;
+}
+
+// Pm[a][b] += sum_{o,in} A[o][a][in] * B[o][b][in]   (mode_gram_kernel with accumulation)
+__global__ void mode_gram_acc_kernel(const double* __restrict__ A, const double* __restrict__ B, int ng, long inner,
+                                     long outer, double* __restrict__ Pm) {
+  int a = blockIdx.x, b = blockIdx.y;
+  __shared__ double sh[32];
+  double acc = 0.0;
+  const long tot = inner * outer;
+  for (long q = threadIdx.x; q < tot; q += blockDim.x) {
+    long ii = q % inner, o = q / inner;
+    acc = fma(A[(o * ng + a) * inner + ii], B[(o * ng + b) * inner + ii], acc);
+  }
+  const double t = block_sum(acc, sh);
+  if (threadIdx.x == 0) Pm[(long)a * ng + b] += t;
+}
+
+// y = a*x + b*y  /  copy / scale helpers on n-vectors
+__global__ void vec_scale_copy_kernel(long n, double a, const double* __restrict__ x, double* __restrict__ y) {
+  long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) y[i] = a * x[i];
+}
+
+}  // namespace kgp

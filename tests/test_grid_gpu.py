@@ -167,3 +167,34 @@ def test_manual_grid_and_full_size_c3(built_lib):
                   'dlikGrid', grid_kwargs={'eq': 1, 'k': 70., 'xg': xg}, verbose=0)
     gp2.update_data('tr', X, y[:, None])
     assert rel(gp2.evaluate('tr'), nlZ) < 1e-6     # two runs differ within cg_tol: atomic scatter order is not fixed
+
+
+@pytest.mark.parametrize('name', ['c4', 'c3_small', 'sm_mean'])
+def test_chebyshev_logdet_injected_probes(built_lib, name):
+    """opt.ldB2_cheby (apx.m:336-391) with the SAME probes and emax on both sides (SURVEY App. D "Stochastic
+    log-det"): same polynomial, same vectors -> 1e-8 relative on nlZ and dnlZ at a tight CG tolerance."""
+    import gpml_grid as gg
+    c, X, y, Xs = build(name)
+    mean = c.get('mean', 'meanZero'); Q = c.get('Q', 0)
+    opt = {'cg_maxit': 20000, 'cg_tol': 1e-12, 'ldB2_cheby': 1, 'ldB2_cheby_degree': 15, 'ldB2_cheby_hutch': 6}
+    gp = make(X, y, c['cov'], c['hyp'], c['lik'], c['k'], opt, mean, c.get('hyp_mean', ()),
+              ['{@meanLinear, @meanConst}'] if mean == 'meanSum' else None, Q)
+    rng = np.random.RandomState(7)
+    V = np.sign(rng.randn(X.shape[0], 6)); V[V == 0] = 1.0
+    # emax: a safe upper bound of the largest eigenvalue of I + sW K sW from the oracle's own operator
+    hv = gp._hyp_vec(); nc = gp.hyp['cov'].size
+    oh = {'cov': hv[:nc], 'lik': gp.hyp['lik'], 'mean': hv[nc + 1:]}
+    om = {'meanZero': ['meanZero'], 'meanSum': ['meanLinear', 'meanConst']}[mean]
+    xg = gg.creategrid(X, 1, gp._grid_k)
+    emax = 1.0 + X.shape[0] * np.exp(-2 * gp.hyp['lik']) * (4.0 if c['cov'] == 'covSM' else np.exp(2 * 1.0))
+    gp.eng.set_probes(V, emax)
+    nlZ, g = gp.eng.eval(0, 2, gp._n_hyp)
+    post, nlZ0, d0 = gg.inf_grid(oh, om, c['cov'], xg, X, y, {'cg_maxit': 20000, 'cg_tol': 1e-12}, Q=Q,
+                                 cheby={'V': V, 'd': 15, 'emax': emax})
+    g0 = np.concatenate([d0['cov'], [d0['lik']], d0['mean']])
+    assert rel(nlZ, nlZ0) < 1e-8
+    assert rel(g, g0) < 1e-7
+    # generated probes + power-iteration emax: runs and returns finite numbers (accuracy is NOT claimed, App. B-11)
+    gp.eng.set_probes(None)
+    nlZ2, g2 = gp.eng.eval(0, 1, gp._n_hyp)
+    assert np.isfinite(nlZ2) and np.all(np.isfinite(g2))
