@@ -134,6 +134,11 @@ int kgp_grid_get_host(kgp_ctx* ctx, int* n_axes, int* axis_len /* >= 16 ints */,
  * opt.ldB2_cheby_seed) and power-iteration emax; emax <= 0 with V given estimates emax only. */
 int kgp_set_probes_host(kgp_ctx* ctx, const double* V, long n, int m, double emax);
 
+/* post.L of the KISS-GP posterior applied to m right-hand sides in ONE batched CG (GPML/cov/apx.m:219-222,
+ * 281-302, per-column convergence masks): out = sW .* CG(I + sW Mx Kg Mx' sW, sW .* r).  R and out are m x n,
+ * one right-hand side per row.  The building block of opt.pred_var (GPML/inf/infGrid.m:93-104). */
+int kgp_grid_solve_host(kgp_ctx* ctx, int slot, const double* R, int m, double* out);
+
 /* posterior pieces for tests / callers that want them (host copies) */
 int kgp_get_alpha_host(kgp_ctx* ctx, double* alpha /* n */);
 

@@ -70,6 +70,7 @@ SIGNATURES = {
     'kgp_bench_dgemm': (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, _DP, _DP]),
     'kgp_bench_syrk': (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, _DP, _DP]),
     'kgp_set_probes_host': (C.c_int, [C.c_void_p, C.c_void_p, C.c_long, C.c_int, C.c_double]),
+    'kgp_grid_solve_host': (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_void_p]),
     'kgp_nccl_unique_id': (C.c_int, [C.c_char_p, C.c_char_p]),
     'kgp_dist_last_error': (C.c_char_p, []),
     'kgp_comm_init': (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_char_p, C.c_char_p]),
@@ -229,6 +230,15 @@ class Context(object):
         V = np.asarray(V, dtype=np.float64)
         Vt = np.ascontiguousarray(V.T)                    # one probe per row
         self._chk(self._l.kgp_set_probes_host(self._h, _ptr(Vt), Vt.shape[1], Vt.shape[0], float(emax)))
+
+    def grid_solve(self, slot, R):
+        """post.L on the columns of R (n x m): one batched CG with per-column convergence masks."""
+        R = np.asarray(R, dtype=np.float64)
+        if R.ndim == 1:
+            R = R[:, None]
+        Rt = np.ascontiguousarray(R.T); out = np.empty_like(Rt)
+        self._chk(self._l.kgp_grid_solve_host(self._h, slot, _ptr(Rt), Rt.shape[0], _ptr(out)))
+        return np.ascontiguousarray(out.T)
 
     def set_profiling(self, on):
         self._chk(self._l.kgp_set_profiling(self._h, int(bool(on))))

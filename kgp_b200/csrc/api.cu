@@ -18,6 +18,7 @@ int grid_predict(kgp_ctx* c, const double* Xs, long ns, double* ymu, double* ys2
 int grid_create(kgp_ctx* c, int slot, int eq, double k);
 void grid_free(kgp_ctx* c);
 int grid_init(kgp_ctx* c);
+int grid_solve(kgp_ctx* c, int slot, const double* R, int m, double* out);
 int grid_set_probes(kgp_ctx* c, const double* V, long n, int m, double emax);
 int dist_unique_id(char* out128, const char* libpath, std::string& err);
 int dist_init(kgp_ctx* c, int nranks, int rank, const char* id128, const char* libpath);
@@ -103,6 +104,12 @@ int kgp_set_probes_host(kgp_ctx* c, const double* V, long n, int m, double emax)
   if (!c) return KGP_BAD_ARG;
   cudaSetDevice(c->device);
   return grid_set_probes(c, V, n, m, emax);
+}
+int kgp_grid_solve_host(kgp_ctx* c, int slot, const double* R, int m, double* out) {
+  if (!c || slot < 0 || slot >= KGP_NUM_SLOTS || !R || !out || m <= 0) return c ? c->fail(KGP_BAD_ARG, "bad solve arguments") : KGP_BAD_ARG;
+  if (c->model.inf_kind != KGP_INF_GRID) return c->fail(KGP_BAD_ARG, "kgp_grid_solve_host needs infGrid");
+  cudaSetDevice(c->device);
+  return grid_solve(c, slot, R, m, out);
 }
 static std::string g_dist_err;
 int kgp_nccl_unique_id(char* out128, const char* nccl_lib_path) {

@@ -789,6 +789,37 @@ int grid_alpha(kgp_ctx* c, double* out) {
   return KGP_OK;
 }
 
+// post.L applied to m right-hand sides at once: out = sW .* CG(B, sW .* r)  (apx.m:219-222 with the batched conjgrad
+// of apx.m:281-302: per-column convergence masks).  R and out are m x n, one right-hand side per row (host).
+int grid_solve(kgp_ctx* c, int slot, const double* R, int m, double* out) {
+  GridState* g = gs(c);
+  if (!gstate_valid(c, g, slot, 0)) {
+    int rc = grid_eval(c, slot, 0, nullptr, nullptr);
+    if (rc) return rc;
+  }
+  GridDesc G; int rc = grid_setup(c, g, G); if (rc) return rc;
+  if (G.p > 2) return c->fail(KGP_BAD_ARG, "batched solve is built for 1-D and 2-D grids");
+  Slot& S = c->slots[slot]; Model& mo = c->model; const long n = S.n;
+  const double sn2 = exp(2.0 * mo.hyp_lik), sw = 1.0 / sqrt(sn2);
+  const int maxit = mo.opt.cg_maxit > 0 ? mo.opt.cg_maxit : (int)std::min<long>(n, 20);
+  cudaStream_t st = c->stream;
+  DevBuf rhs, res;
+  KGP_CUDA(c, rhs.ensure((size_t)CG_MAXCOLS * n * 8)); KGP_CUDA(c, res.ensure((size_t)CG_MAXCOLS * n * 8));
+  for (int c0 = 0; c0 < m; c0 += CG_MAXCOLS) {
+    const int mb = std::min(CG_MAXCOLS, m - c0);
+    KGP_CUDA(c, cudaMemcpyAsync(rhs.p, R + (long)c0 * n, (size_t)mb * n * 8, cudaMemcpyHostToDevice, st));
+    rc = cg_solve_sorted(c, g, G, slot, rhs.d(), n, mb, sw, mo.opt.cg_tol, maxit);
+    if (rc) { rhs.release(); res.release(); return rc; }
+    for (int col = 0; col < mb; ++col)
+      cg_unsort_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(g->sx.d() + (long)col * g->npad, (const int*)g->perm.p, n, sw, res.d() + (long)col * n);
+    KGP_CUDA(c, cudaMemcpyAsync(out + (long)c0 * n, res.p, (size_t)mb * n * 8, cudaMemcpyDeviceToHost, st));
+    KGP_CUDA(c, cudaStreamSynchronize(st));
+  }
+  rhs.release(); res.release();
+  g->st_level = -1;                 // the CG work vectors were reused: the cached posterior is gone
+  return KGP_OK;
+}
+
 // post.predict (infGrid.m:135-145): fmu = ms + Ms (Kg Mx' alpha); fs2 = prior variance (vg = 0)
 int grid_predict(kgp_ctx* c, const double* Xs, long ns, double* ymu, double* ys2, double* fmu, double* fs2) {
   GridState* g = gs(c);

@@ -13,8 +13,8 @@ for r in rows[1:]:
     a = agg[r[ki].split('(')[0]]; a[0] += 1; a[1] += ms; a[2] = max(a[2], ms)
 tot = sum(a[1] for a in agg.values())
 with open(os.path.join(out, tag + '_launches.md'), 'w') as f:
-    f.write('# %s: ncu launch list of one exact-GP evaluation (n=40000, d=8)\n\n' % tag)
-    f.write('`ncu --metrics gpu__time_duration.sum --clock-control none` on `python bench.py --steps 1 --warmup 1 --no-cpu`; '
+    f.write('# %s: ncu launch list of the exact-GP bench command (n=40000, d=8; the first 4000 launches = warm-up + timed + e2e evaluations)\n\n' % tag)
+    f.write('`ncu --metrics gpu__time_duration.sum --clock-control none` on `python bench.py --steps 1 --warmup 1 --no-cpu --no-kissgp` (-c 4000); '
             'per-launch times are cold-cache and serialised: compare SHARES.\n\n| kernel | launches | total ms | share | max ms |\n|---|---:|---:|---:|---:|\n')
     for k, a in sorted(agg.items(), key=lambda x: -x[1][1]):
         f.write('| %s | %d | %.2f | %.1f%% | %.3f |\n' % (k, a[0], a[1], 100 * a[1] / tot, a[2]))

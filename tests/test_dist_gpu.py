@@ -53,3 +53,15 @@ def test_sharded_equals_single_world2(built_lib):
     for l in lines:
         rels = [float(tok) for tok in l.split('rel')[1].replace('dnlZ', ' ').replace('dX', ' ').replace('ymu', ' ').replace('ys2', ' ').split()]
         assert max(rels) < 1e-10, l
+
+
+def test_sharded_probes_equal_single_world2(built_lib):
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip('needs 2 GPUs')
+    cmd = [sys.executable, '-m', 'torch.distributed.run', '--nnodes=1', '--nproc-per-node', '2', '--master-addr', '127.0.0.1',
+           '--master-port', '29534', os.path.join(ROOT, 'scripts', 'dist_grid.py'), '6000']
+    out = subprocess.check_output(cmd, timeout=900, stderr=subprocess.STDOUT).decode()
+    line = [l for l in out.splitlines() if l.startswith('n=')][0]
+    rels = [float(t) for t in line.split('rel')[1].replace('dnlZ', ' ').split()]
+    assert max(rels) < 1e-9, line

@@ -198,3 +198,31 @@ def test_chebyshev_logdet_injected_probes(built_lib, name):
     gp.eng.set_probes(None)
     nlZ2, g2 = gp.eng.eval(0, 1, gp._n_hyp)
     assert np.isfinite(nlZ2) and np.all(np.isfinite(g2))
+
+
+def test_batched_solve_with_column_masks(built_lib):
+    """post.L on several right-hand sides in one batched CG (apx.m:281-302): columns converge at different
+    iterations and are frozen individually (apx.m:296-298); an all-zero column is done at once (apx.m:286)."""
+    import gpml_grid as gg
+    c, X, y, Xs = build('c3_small')
+    opt = {'cg_maxit': 5000, 'cg_tol': 1e-10}
+    gp = make(X, y, c['cov'], c['hyp'], c['lik'], c['k'], opt)
+    n = X.shape[0]; rng = np.random.RandomState(3)
+    R = np.stack([y, rng.randn(n), np.zeros(n), 1e3 * np.sin(7 * X[:, 0]), rng.randn(n) * (X[:, 1] > 1), np.ones(n), rng.rand(n)], 1)
+    out = gp.eng.grid_solve(0, R)
+    hv = gp._hyp_vec(); nc = gp.hyp['cov'].size
+    xg = gg.creategrid(X, 1, gp._grid_k)
+    hs = gg.split_hyp(c['cov'], hv[:nc], 2); Ks = [gg.factor_cov(c['cov'], hs[i], xg[i])[0] for i in range(2)]
+    Mx = gg.interpgrid(xg, X); MxT = Mx.T.tocsr()
+    sW = np.exp(-gp.hyp['lik'])
+    mvmB = lambda v: sW * (Mx @ gg.kronmvm(Ks, MxT @ (sW * v))) + v
+    q, flag, relres, it = gg.conjgrad(mvmB, sW * R, 1e-10, 5000)
+    assert flag
+    ref = sW * q
+    assert np.all(out[:, 2] == 0.0)
+    for col in range(R.shape[1]):
+        if col != 2:
+            assert rel(out[:, col], ref[:, col]) < 1e-7, col
+    # the posterior is recomputed transparently afterwards
+    nlZ, g = gp.eng.eval(0, 2, gp._n_hyp)
+    assert np.isfinite(nlZ)
