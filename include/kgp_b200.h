@@ -52,6 +52,7 @@ typedef struct {
   int    ldB2_cheby_maxit;   /* power/Lanczos iterations for emax, default 50 */
   uint64_t ldB2_cheby_seed;  /* probe seed (intent of apx.m:130) */
   int    ard_reference_form; /* 1: dcovSEard.m:7 quirk (divide every dim by ell_1^2) */
+  int    cg_precond;         /* 1: grid-space Woodbury preconditioner for the CG (extension); 0 = reference CG */
 } kgp_opt;
 
 /* per-call statistics of the last kgp_eval / kgp_dlik_dx / kgp_predict */

@@ -7,7 +7,7 @@
 // the whole CG iteration is device-resident (scalars, convergence flag and iteration count live
 // in device memory; the host only polls the flag every few iterations).
 #include "ctx.h"
-#include "grid_cheby.cuh"
+#include "grid_precond.cuh"
 #include "exact_dist.cuh"
 #include <math.h>
 #include <string.h>
@@ -25,6 +25,8 @@ struct GridState {
   cudaGraphExec_t cg_graph = nullptr; std::vector<char> cg_graph_key;
   DevBuf probes, chT, chU, chY, chS, chC, chP, bva, bvb, chacc;   // Chebyshev log-det (grid_cheby.cuh)
   long probes_n = 0; int probes_m = 0; double probes_emax = 0.0; bool probes_injected = false;
+  DevBuf Gm, Ht1, Ht2, VT, se, ps, pw;                 // Woodbury preconditioner (grid_precond.cuh)
+  int gram_slot = -1; unsigned long gram_slot_ver = 0, gram_grid_ver = 0; int pcg_iters = 0;
   DevBuf pdz, prr, bar, part4, g0b, wmaxd; int num_sms = 0; size_t smem_optin = 0; int cg_level_used = -1;
   int wmax = 0; int wmax_ctas = 0; unsigned long wmax_slot_ver = 0, wmax_grid_ver = 0; int wmax_slot = -1;
   int p = 0; int ng[GRID_MAXP] = {0}; long N = 0;
@@ -47,7 +49,7 @@ void grid_free(kgp_ctx* c) {
                     &g->tgrid, &g->beta, &g->x, &g->r, &g->d, &g->z, &g->ym, &g->partA, &g->partB, &g->S, &g->hyp,
                     &g->hypm, &g->dX, &g->dhyp, &g->out, &g->sortk, &g->sorti, &g->keep, &g->dmean,
                     &g->U, &g->perm, &g->sx, &g->sr, &g->sd, &g->sz, &g->ctl, &g->cnt, &g->KfT, &g->gm0, &g->gm1, &g->pdz, &g->prr, &g->bar, &g->part4, &g->g0b, &g->wmaxd,
-                    &g->probes, &g->chT, &g->chU, &g->chY, &g->chS, &g->chC, &g->chP, &g->bva, &g->bvb, &g->chacc};
+                    &g->Gm, &g->Ht1, &g->Ht2, &g->VT, &g->se, &g->ps, &g->pw, &g->probes, &g->chT, &g->chU, &g->chY, &g->chS, &g->chC, &g->chP, &g->bva, &g->bvb, &g->chacc};
   for (DevBuf* b : bufs) b->release();
   if (g->h_ctl) cudaFreeHost(g->h_ctl);
   if (g->cg_graph) cudaGraphExecDestroy(g->cg_graph);
@@ -102,12 +104,13 @@ static void scatter(kgp_ctx* c, const GridDesc& G, const double* X, long n, int 
   c->stats.kernel_launches += 2;
 }
 // out = (K_p kron ... kron K_1) in ; skip = mode to leave out (-1: none).  Returns the buffer holding the result.
-static double* kron_apply(kgp_ctx* c, GridState* g, const GridDesc& G, double* in, double* tmp, int skip) {
+static double* kron_apply(kgp_ctx* c, GridState* g, const GridDesc& G, double* in, double* tmp, int skip, const double* mats = nullptr) {
   double* src = in; double* dst = tmp;
+  if (!mats) mats = g->Kf.d();
   for (int d = 0; d < G.p; ++d) {
     if (d == skip) continue;
     long inner = G.stride[d], outer = G.N / (inner * G.ng[d]);
-    mode_product_kernel<<<(unsigned)((G.N + 255) / 256), 256, 0, c->stream>>>(g->Kf.d() + g->koff[d], G.ng[d], src, dst, inner, outer);
+    mode_product_kernel<<<(unsigned)((G.N + 255) / 256), 256, 0, c->stream>>>(mats + g->koff[d], G.ng[d], src, dst, inner, outer);
     c->stats.kernel_launches++;
     std::swap(src, dst);
   }
@@ -459,6 +462,130 @@ static int cg_solve_sorted(kgp_ctx* c, GridState* g, const GridDesc& G, int slot
   return KGP_OK;
 }
 
+// ---- Woodbury-preconditioned CG (grid_precond.cuh) --------------------------------------------
+static int precond_setup(kgp_ctx* c, GridState* g, const GridDesc& G, int slot, double s2) {
+  Slot& S = c->slots[slot]; cudaStream_t st = c->stream;
+  const long N = G.N, n = S.n;
+  if (G.p > 2 || N > 16384) return c->fail(KGP_BAD_ARG, "opt.cg_precond needs a 1-D/2-D grid with N <= 16384 (N = %ld)", N);
+  int rc = cg_prepare_sorted(c, g, G, slot); if (rc) return rc;
+  if (g->gram_slot != slot || g->gram_slot_ver != S.version || g->gram_grid_ver != c->grid.version) {
+    KGP_CUDA(c, g->Gm.ensure((size_t)N * N * 8));
+    KGP_CUDA(c, cudaMemsetAsync(g->Gm.p, 0, (size_t)N * N * 8, st));
+    const unsigned nb = (unsigned)std::min<long>((g->npad / 32 + 7) / 8, 148L * 16);
+    if (G.p == 1) gram_accum_kernel<1><<<nb, 256, 0, st>>>(G, g->U.d(), n, g->npad, g->Gm.d());
+    else gram_accum_kernel<2><<<nb, 256, 0, st>>>(G, g->U.d(), n, g->npad, g->Gm.d());
+    g->gram_slot = slot; g->gram_slot_ver = S.version; g->gram_grid_ver = c->grid.version;
+    c->stats.kernel_launches++;
+  }
+  long ksz = 0; for (int d = 0; d < G.p; ++d) ksz += (long)G.ng[d] * G.ng[d];
+  KGP_CUDA(c, g->VT.ensure(ksz * 8)); KGP_CUDA(c, g->se.ensure(N * 8));
+  KGP_CUDA(c, g->Ht1.ensure((size_t)N * N * 8)); KGP_CUDA(c, g->Ht2.ensure((size_t)N * N * 8));
+  KGP_CUDA(c, g->ps.ensure(n * 8)); KGP_CUDA(c, g->pw.ensure(N * 8));
+  cudaStreamWaitEvent(st, c->ev[11], 0);                         // factor eigen-decompositions (side stream)
+  for (int d = 0; d < G.p; ++d) {
+    const long nn = (long)G.ng[d] * G.ng[d];
+    transpose_small_kernel<<<(unsigned)((nn + 255) / 256), 256, 0, st>>>(g->Vf.d() + g->koff[d], G.ng[d], g->VT.d() + g->koff[d]);
+  }
+  sqrt_kron_eig_kernel<<<(unsigned)((N + 255) / 256), 256, 0, st>>>(G, g->ee.d(), (const int*)g->eoff.p, g->se.d());
+  // H = V' G V : mode products with V_d' along the 2p axes of the N x N array (column axes, then row axes)
+  const double* src = g->Gm.d(); double* bufs[2] = {g->Ht1.d(), g->Ht2.d()}; int which = 0;
+  const long tot = N * N;
+  for (int side = 0; side < 2; ++side)
+    for (int d = 0; d < G.p; ++d) {
+      const long inner = (side == 0 ? 1 : N) * G.stride[d], outer = tot / (inner * G.ng[d]);
+      double* dst = bufs[which];
+      mode_product_kernel<<<(unsigned)((tot + 255) / 256), 256, 0, st>>>(g->VT.d() + g->koff[d], G.ng[d], src, dst, inner, outer);
+      src = dst; which ^= 1;
+      c->stats.kernel_launches++;
+    }
+  // C = I + s2 E^1/2 H E^1/2 -> blocked Cholesky and triangular inverse of the exact path
+  rc = ensure_exact_buffers(c, N, 1); if (rc) return rc;
+  const long np = c->np;
+  c->st_level = -1;
+  int big = 1 << 30;
+  KGP_CUDA(c, cudaMemcpyAsync(c->d_info, &big, sizeof(int), cudaMemcpyHostToDevice, st));
+  assemble_c_kernel<<<dim3((unsigned)((np + 255) / 256), (unsigned)np), 256, 0, st>>>(src, g->se.d(), s2, N, np, c->M.d());
+  potrf(c);
+  zsweep(c);
+  int info = 0;
+  KGP_CUDA(c, cudaMemcpyAsync(&info, c->d_info, sizeof(int), cudaMemcpyDeviceToHost, st));
+  KGP_CUDA(c, cudaStreamSynchronize(st));
+  KGP_CUDA(c, cudaGetLastError());
+  if (info != (1 << 30)) return c->fail(KGP_NOT_PD, "preconditioner: grid-space matrix not positive definite (pivot %d)", info);
+  return KGP_OK;
+}
+// s = B~^-1 r = r - s2 M F C^-1 F' M' r ; partial sums of r.s in partA (nb entries)
+static int precond_apply(kgp_ctx* c, GridState* g, const GridDesc& G, const Slot& S, double s2, const double* r, double* sout, int nb) {
+  cudaStream_t st = c->stream; const long N = G.N, np = c->np, n = S.n; const int D = S.D;
+  scatter(c, G, S.X.d(), n, D, r, 1.0, g->g0.d());                                    // M' r
+  double* t = kron_apply(c, g, G, g->g0.d(), g->g1.d(), -1, g->VT.d());              // V' .
+  mul_pad_kernel<<<(unsigned)((np + 255) / 256), 256, 0, st>>>(t, g->se.d(), N, np, c->ym.d());        // E^1/2 .
+  const int nch = (int)((np + 511) / 512);
+  KGP_CUDA(c, c->parts.ensure((size_t)nch * np * 8));
+  gemv_t_upper_kernel<<<dim3((unsigned)(np / 128), (unsigned)nch), 128, 0, st>>>(c->W2.d(), np, np, c->ym.d(), c->parts.d());
+  sum_parts_kernel<<<(unsigned)((np + 255) / 256), 256, 0, st>>>(c->parts.d(), np, nch, 1.0, c->tvec.d());
+  gemv_n_upper_kernel<<<(unsigned)((np + 7) / 8), 256, 0, st>>>(c->W2.d(), np, np, c->tvec.d(), 1.0, c->alpha.d());   // C^-1 = Z Z'
+  mul_pad_kernel<<<(unsigned)((N + 255) / 256), 256, 0, st>>>(c->alpha.d(), g->se.d(), N, N, g->g0.d());           // E^1/2 .
+  double* w = kron_apply(c, g, G, g->g0.d(), g->g1.d(), -1, g->Vf.d());              // V .
+  for_p(G.p, [&](auto P) {
+    interp_gather_bz_kernel<decltype(P)::value><<<nb, 256, 0, st>>>(G, S.X.d(), n, D, w, -s2, r, sout, g->partA.d());   // r - s2 M w ; r.s
+  });
+  c->stats.kernel_launches += 6;
+  return KGP_OK;
+}
+// alpha = sW CG(B, sW ym) with the Woodbury preconditioner; same stopping rule and iteration count as apx.m:281-302
+static int pcg_solve(kgp_ctx* c, GridState* g, const GridDesc& G, int slot, double sw, double tol, int maxit) {
+  Slot& S = c->slots[slot]; cudaStream_t st = c->stream; const long n = S.n; const int D = S.D;
+  int rc = precond_setup(c, g, G, slot, sw * sw); if (rc) return rc;
+  const int nb = nblocks_for(n);
+  double h[4];
+  auto fetch = [&](const double* dev, int cnt) -> int {
+    KGP_CUDA(c, cudaMemcpyAsync(h, dev, cnt * 8, cudaMemcpyDeviceToHost, st));
+    KGP_CUDA(c, cudaStreamSynchronize(st));
+    return KGP_OK;
+  };
+  double* x = g->x.d(); double* r = g->r.d(); double* d = g->d.d(); double* z = g->z.d(); double* s = g->ps.d();
+  cg_init_kernel<<<nb, 256, 0, st>>>(g->ym.d(), sw, n, x, r, d, g->partA.d());                   // x = 0, r = d = b
+  sum_small_kernel<<<1, 256, 0, st>>>(g->partA.d(), nb, g->out.d() + 8);
+  rc = fetch(g->out.d() + 8, 1); if (rc) return rc;
+  const double nbn = sqrt(h[0]);
+  int iter = 1; double relres = nbn / nbn; bool done = !(relres >= tol);
+  double rz = 0.0;
+  if (!done) {
+    rc = precond_apply(c, g, G, S, sw * sw, r, s, nb); if (rc) return rc;
+    sum_small_kernel<<<1, 256, 0, st>>>(g->partA.d(), nb, g->out.d() + 8);
+    KGP_CUDA(c, cudaMemcpyAsync(d, s, n * 8, cudaMemcpyDeviceToDevice, st));
+    rc = fetch(g->out.d() + 8, 1); if (rc) return rc;
+    rz = h[0];
+  }
+  for (iter = 2; !done && iter <= maxit; ++iter) {
+    scatter(c, G, S.X.d(), n, D, d, sw, g->g0.d());                                        // z = B d
+    double* u = kron_apply(c, g, G, g->g0.d(), g->g1.d(), -1);
+    for_p(G.p, [&](auto P) {
+      interp_gather_bz_kernel<decltype(P)::value><<<nb, 256, 0, st>>>(G, S.X.d(), n, D, u, sw, d, z, g->partA.d());
+    });
+    sum_small_kernel<<<1, 256, 0, st>>>(g->partA.d(), nb, g->out.d() + 8);
+    rc = fetch(g->out.d() + 8, 1); if (rc) return rc;
+    const double a = rz / h[0];
+    pcg_update_kernel<<<nb, 256, 0, st>>>(n, a, x, r, d, z, g->partB.d());
+    sum_small_kernel<<<1, 256, 0, st>>>(g->partB.d(), nb, g->out.d() + 9);
+    rc = fetch(g->out.d() + 9, 1); if (rc) return rc;
+    relres = sqrt(h[0]) / nbn;
+    c->stats.kernel_launches += 5;
+    if (!(relres >= tol)) { done = true; break; }
+    rc = precond_apply(c, g, G, S, sw * sw, r, s, nb); if (rc) return rc;
+    sum_small_kernel<<<1, 256, 0, st>>>(g->partA.d(), nb, g->out.d() + 8);
+    rc = fetch(g->out.d() + 8, 1); if (rc) return rc;
+    const double rzn = h[0];
+    pcg_dir_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(n, rzn / rz, s, d);
+    rz = rzn;
+  }
+  c->stats.cg_iters = std::min(iter, maxit); c->stats.cg_relres = relres;
+  if (!done) return c->fail(KGP_CG_NOT_CONVERGED, "Not converged after %d iterations, r=%1.2e", std::min(iter, maxit), relres);
+  axpy_scale_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(n, sw, x, x);              // alpha = sW q
+  return KGP_OK;
+}
+
 // ---- Chebyshev-Hutchinson log-det and its derivatives (grid_cheby.cuh; apx.m:336-391) --------------------------
 __global__ void sum_scaled_acc_kernel(const double* __restrict__ part, int cnt, double coef, double* __restrict__ out) {
   __shared__ double sh[32];
@@ -657,7 +784,7 @@ int grid_eval(kgp_ctx* c, int slot, int want, double* nlZ_out, double* dnlZ_out)
   // eigen-decompositions of all factors: one CTA each, on the side stream, overlapped with the CG solve
   cudaEventRecord(c->ev[10], st);
   cudaStreamWaitEvent(c->stream2, c->ev[10], 0);
-  if (!cheby) jacobi_eig_kernel<<<G.p, EIG_THREADS, eig_smem, c->stream2>>>(eb, getenv("KGP_EIG_SWEEPS") ? atoi(getenv("KGP_EIG_SWEEPS")) : 40);
+  if (!cheby || m.opt.cg_precond) jacobi_eig_kernel<<<G.p, EIG_THREADS, eig_smem, c->stream2>>>(eb, getenv("KGP_EIG_SWEEPS") ? atoi(getenv("KGP_EIG_SWEEPS")) : 40);
   cudaEventRecord(c->ev[11], c->stream2);
   c->stats.kernel_launches++;
   resid_mean_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(S.X.d(), S.has_y ? S.y.d() : nullptr, n, D, m.mean_mask, g->hypm.d(), g->ym.d(), n);
@@ -666,7 +793,10 @@ int grid_eval(kgp_ctx* c, int slot, int want, double* nlZ_out, double* dnlZ_out)
 
   int maxit = m.opt.cg_maxit > 0 ? m.opt.cg_maxit : (int)std::min<long>(n, 20);
   static const bool legacy_cg = getenv("KGP_CG_LEGACY") && atoi(getenv("KGP_CG_LEGACY"));
-  if (G.p <= 2 && !legacy_cg) {
+  if (m.opt.cg_precond) {
+    rc = pcg_solve(c, g, G, slot, sw, m.opt.cg_tol, maxit);
+    if (rc) return rc;
+  } else if (G.p <= 2 && !legacy_cg) {
     rc = cg_solve_sorted(c, g, G, slot, g->ym.d(), n, 1, sw, m.opt.cg_tol, maxit);
     if (rc) return rc;
     cg_unsort_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(g->sx.d(), (const int*)g->perm.p, n, sw, g->x.d());   // alpha = sW q

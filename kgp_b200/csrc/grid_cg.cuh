@@ -764,7 +764,10 @@ struct CgPersist2 {
   unsigned* bar; long long* dbg;
   long stg_doubles;                                    // size of the staging region
 };
-constexpr int CGP2_THREADS = 512;
+#ifndef KGP_CGP2_THREADS
+#define KGP_CGP2_THREADS 512
+#endif
+constexpr int CGP2_THREADS = KGP_CGP2_THREADS;
 constexpr int CGP_VPP = 8;                             // node values per reduction pass (2-D); 1-D uses 4
 constexpr int CGP_WSCR2 = CGP_VPP * 33 + 16;
 
@@ -782,8 +785,13 @@ __global__ void cg_window_kernel(GridDesc G, const double* __restrict__ U, long 
   atomicMax(wmax, jf + 3 - jl + 1);
 }
 
+#if KGP_CGP2_THREADS > 512
+#define KGP_CGP2_BOUNDS __maxnreg__(112)
+#else
+#define KGP_CGP2_BOUNDS __launch_bounds__(CGP2_THREADS, 1)
+#endif
 template <int P, int LEVEL, bool DBG>
-__global__ void __launch_bounds__(CGP2_THREADS, 1) cg_persistent2_kernel(const CgPersist2 A) {
+__global__ void KGP_CGP2_BOUNDS cg_persistent2_kernel(const CgPersist2 A) {
   constexpr int NW = CgNodes<P>::NW;
   constexpr int VPP = (P == 1) ? 4 : CGP_VPP, NPASS = NW / VPP;
   extern __shared__ __align__(16) double psm[];

@@ -9,7 +9,7 @@ def synth_c5(n, seed=46, Q=6):
     H = rng.rand(n, 2); y = np.sin(2 * np.pi * 3 * H).sum(1) + 0.5 * H[:, 0] + 0.3 * rng.randn(n)
     hyp_cov = [[np.log(np.ones((Q, 1)))], [np.log(np.maximum(0.05 * rng.rand(Q, 1), 1e-8))], [np.log(np.abs(rng.randn(Q, 1) + 1))]]
     return H, y, hyp_cov
-for n in [int(a) for a in sys.argv[1:]]:
+for n in ([int(a) for a in sys.argv[1:]] if __name__ == "__main__" else []):
     H, y, hc = synth_c5(n)
     gp = B200GP()
     gp.configure(2, {'lik': np.log(0.3), 'mean': [[0.], [0.], [0.]], 'cov': hc}, {'cg_maxit': int(os.environ.get('MAXIT', 2000)), 'cg_tol': 1e-6}, 'infGrid', 'meanSum', 'covSM',

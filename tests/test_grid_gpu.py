@@ -226,3 +226,22 @@ def test_batched_solve_with_column_masks(built_lib):
     # the posterior is recomputed transparently afterwards
     nlZ, g = gp.eng.eval(0, 2, gp._n_hyp)
     assert np.isfinite(nlZ)
+
+
+@pytest.mark.parametrize('name', list(CASES))
+def test_woodbury_preconditioned_cg(built_lib, name):
+    """opt.cg_precond (extension): same stopping rule, a handful of iterations instead of hundreds,
+    and the converged quantities agree with the oracle's un-preconditioned solve at a tight tolerance."""
+    c, X, y, Xs = build(name)
+    mean = c.get('mean', 'meanZero'); Q = c.get('Q', 0)
+    opt_ref = {'cg_maxit': 20000, 'cg_tol': 1e-12}
+    opt = dict(opt_ref, cg_precond=1)
+    gp = make(X, y, c['cov'], c['hyp'], c['lik'], c['k'], opt, mean, c.get('hyp_mean', ()),
+              ['{@meanLinear, @meanConst}'] if mean == 'meanSum' else None, Q)
+    nlZ, g = gp.eng.eval(0, 2, gp._n_hyp)
+    st = gp.stats()
+    dX = gp.get_dlik_dx('tr'); ymu = gp.predict(Xs)
+    xg, post, nlZ0, g0, dX0, p0 = oracle_all(gp, X, y, c['cov'], opt_ref, mean, Q, Xs)
+    assert st['cg_relres'] < 1e-12 and st['cg_iters'] <= 8, st
+    assert rel(nlZ, nlZ0) < 1e-8 and rel(g, g0) < 1e-7
+    assert rel(gp.alpha(), post['alpha']) < 1e-7 and rel(dX, dX0) < 1e-7 and rel(ymu, p0[2]) < 1e-7
