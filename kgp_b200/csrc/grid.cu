@@ -463,8 +463,11 @@ static int cg_solve_sorted(kgp_ctx* c, GridState* g, const GridDesc& G, int slot
 }
 
 // ---- Woodbury-preconditioned CG (grid_precond.cuh) --------------------------------------------
+static double dbg_now(cudaStream_t st) { cudaStreamSynchronize(st); timespec ts; clock_gettime(CLOCK_MONOTONIC, &ts); return ts.tv_sec * 1e3 + ts.tv_nsec * 1e-6; }
 static int precond_setup(kgp_ctx* c, GridState* g, const GridDesc& G, int slot, double s2) {
   Slot& S = c->slots[slot]; cudaStream_t st = c->stream;
+  const bool dbg = getenv("KGP_DEBUG") != nullptr; double tq[8] = {0};
+  if (dbg) tq[0] = dbg_now(st);
   const long N = G.N, n = S.n;
   if (G.p > 2 || N > 16384) return c->fail(KGP_BAD_ARG, "opt.cg_precond needs a 1-D/2-D grid with N <= 16384 (N = %ld)", N);
   int rc = cg_prepare_sorted(c, g, G, slot); if (rc) return rc;
@@ -481,7 +484,9 @@ static int precond_setup(kgp_ctx* c, GridState* g, const GridDesc& G, int slot, 
   KGP_CUDA(c, g->VT.ensure(ksz * 8)); KGP_CUDA(c, g->se.ensure(N * 8));
   KGP_CUDA(c, g->Ht1.ensure((size_t)N * N * 8)); KGP_CUDA(c, g->Ht2.ensure((size_t)N * N * 8));
   KGP_CUDA(c, g->ps.ensure(n * 8)); KGP_CUDA(c, g->pw.ensure(N * 8));
+  if (dbg) tq[1] = dbg_now(st);
   cudaStreamWaitEvent(st, c->ev[11], 0);                         // factor eigen-decompositions (side stream)
+  if (dbg) tq[2] = dbg_now(st);
   for (int d = 0; d < G.p; ++d) {
     const long nn = (long)G.ng[d] * G.ng[d];
     transpose_small_kernel<<<(unsigned)((nn + 255) / 256), 256, 0, st>>>(g->Vf.d() + g->koff[d], G.ng[d], g->VT.d() + g->koff[d]);
@@ -494,10 +499,16 @@ static int precond_setup(kgp_ctx* c, GridState* g, const GridDesc& G, int slot, 
     for (int d = 0; d < G.p; ++d) {
       const long inner = (side == 0 ? 1 : N) * G.stride[d], outer = tot / (inner * G.ng[d]);
       double* dst = bufs[which];
-      mode_product_kernel<<<(unsigned)((tot + 255) / 256), 256, 0, st>>>(g->VT.d() + g->koff[d], G.ng[d], src, dst, inner, outer);
+      constexpr int RB = 10;
+      const size_t msm = (size_t)((G.ng[d] + RB - 1) / RB) * RB * G.ng[d] * 8;
+      if (msm <= 96 * 1024)
+        mode_product_rb_kernel<RB><<<148 * 8, 256, msm, st>>>(g->VT.d() + g->koff[d], G.ng[d], src, dst, inner, outer);
+      else
+        mode_product_kernel<<<(unsigned)((tot + 255) / 256), 256, 0, st>>>(g->VT.d() + g->koff[d], G.ng[d], src, dst, inner, outer);
       src = dst; which ^= 1;
       c->stats.kernel_launches++;
     }
+  if (dbg) tq[3] = dbg_now(st);
   // C = I + s2 E^1/2 H E^1/2 -> blocked Cholesky and triangular inverse of the exact path
   rc = ensure_exact_buffers(c, N, 1); if (rc) return rc;
   const long np = c->np;
@@ -506,7 +517,9 @@ static int precond_setup(kgp_ctx* c, GridState* g, const GridDesc& G, int slot, 
   KGP_CUDA(c, cudaMemcpyAsync(c->d_info, &big, sizeof(int), cudaMemcpyHostToDevice, st));
   assemble_c_kernel<<<dim3((unsigned)((np + 255) / 256), (unsigned)np), 256, 0, st>>>(src, g->se.d(), s2, N, np, c->M.d());
   potrf(c);
+  if (dbg) tq[4] = dbg_now(st);
   zsweep(c);
+  if (dbg) { tq[5] = dbg_now(st); fprintf(stderr, "[kgp] precond setup ms: gram %.2f eigwait %.2f modeprod %.2f potrf %.2f zsweep %.2f\n", tq[1] - tq[0], tq[2] - tq[1], tq[3] - tq[2], tq[4] - tq[3], tq[5] - tq[4]); }
   int info = 0;
   KGP_CUDA(c, cudaMemcpyAsync(&info, c->d_info, sizeof(int), cudaMemcpyDeviceToHost, st));
   KGP_CUDA(c, cudaStreamSynchronize(st));
@@ -537,6 +550,7 @@ static int precond_apply(kgp_ctx* c, GridState* g, const GridDesc& G, const Slot
 static int pcg_solve(kgp_ctx* c, GridState* g, const GridDesc& G, int slot, double sw, double tol, int maxit) {
   Slot& S = c->slots[slot]; cudaStream_t st = c->stream; const long n = S.n; const int D = S.D;
   int rc = precond_setup(c, g, G, slot, sw * sw); if (rc) return rc;
+  if (getenv("KGP_DEBUG")) fprintf(stderr, "[kgp] pcg setup done at %.2f ms\n", dbg_now(st));
   const int nb = nblocks_for(n);
   double h[4];
   auto fetch = [&](const double* dev, int cnt) -> int {
@@ -580,6 +594,7 @@ static int pcg_solve(kgp_ctx* c, GridState* g, const GridDesc& G, int slot, doub
     pcg_dir_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(n, rzn / rz, s, d);
     rz = rzn;
   }
+  if (getenv("KGP_DEBUG")) fprintf(stderr, "[kgp] pcg iterations done at %.2f ms\n", dbg_now(st));
   c->stats.cg_iters = std::min(iter, maxit); c->stats.cg_relres = relres;
   if (!done) return c->fail(KGP_CG_NOT_CONVERGED, "Not converged after %d iterations, r=%1.2e", std::min(iter, maxit), relres);
   axpy_scale_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(n, sw, x, x);              // alpha = sW q
@@ -1055,6 +1070,7 @@ int grid_create(kgp_ctx* c, int slot, int eq, double k) {
 int grid_init(kgp_ctx* c) {
   KGP_CUDA(c, cudaFuncSetAttribute(jacobi_eig_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 190 * 1024));
   KGP_CUDA(c, cudaFuncSetAttribute(kron2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024));
+  KGP_CUDA(c, cudaFuncSetAttribute(mode_product_rb_kernel<10>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024));
   KGP_CUDA(c, cudaFuncSetAttribute(interp_scatter_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024));
   KGP_CUDA(c, cudaFuncSetAttribute(interp_scatter_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024));
   KGP_CUDA(c, cudaFuncSetAttribute(interp_scatter_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024));

@@ -79,6 +79,36 @@ __global__ void __launch_bounds__(256) gram_accum_kernel(GridDesc G, const doubl
   }
 }
 
+// Register-blocked mode product for the N x N arrays of the preconditioner set-up:
+//   out[o][a][ii] = sum_j Mat[a][j] in[o][j][ii]; a thread forms R outputs a for one (o, ii), so every loaded input
+// value feeds R FMAs; Mat sits in shared memory (rows padded with zeros to a multiple of R).
+template <int R>
+__global__ void __launch_bounds__(256) mode_product_rb_kernel(const double* __restrict__ Mat, int ng, const double* __restrict__ in,
+                                                             double* __restrict__ out, long inner, long outer) {
+  extern __shared__ double smat[];
+  const int nab = (ng + R - 1) / R;
+  for (int q = threadIdx.x; q < nab * R * ng; q += blockDim.x) smat[q] = (q < ng * ng) ? Mat[q] : 0.0;
+  __syncthreads();
+  const long total = outer * nab * inner;
+  for (long q = (long)blockIdx.x * blockDim.x + threadIdx.x; q < total; q += (long)gridDim.x * blockDim.x) {
+    const long ii = q % inner, r = q / inner; const int ab = (int)(r % nab); const long o = r / nab;
+    const double* src = in + o * ng * inner + ii;
+    const double* m0 = smat + (long)ab * R * ng;
+    double acc[R];
+#pragma unroll
+    for (int t = 0; t < R; ++t) acc[t] = 0.0;
+#pragma unroll 2
+    for (int j = 0; j < ng; ++j) {
+      const double v = src[(long)j * inner];
+#pragma unroll
+      for (int t = 0; t < R; ++t) acc[t] = fma(m0[t * ng + j], v, acc[t]);
+    }
+    double* dst = out + (o * ng + (long)ab * R) * inner + ii;
+#pragma unroll
+    for (int t = 0; t < R; ++t) if (ab * R + t < ng) dst[(long)t * inner] = acc[t];
+  }
+}
+
 // se[k] = sqrt(kron eigenvalue k)  (first axis fastest)
 __global__ void sqrt_kron_eig_kernel(GridDesc G, const double* __restrict__ ee, const int* __restrict__ eoff, double* __restrict__ se) {
   long q = (long)blockIdx.x * blockDim.x + threadIdx.x;
