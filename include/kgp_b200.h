@@ -53,6 +53,8 @@ typedef struct {
   uint64_t ldB2_cheby_seed;  /* probe seed (intent of apx.m:130) */
   int    ard_reference_form; /* 1: dcovSEard.m:7 quirk (divide every dim by ell_1^2) */
   int    cg_precond;         /* 1: grid-space Woodbury preconditioner for the CG (extension); 0 = reference CG */
+  int    pred_var;           /* opt.pred_var (GPML/inf/infGrid.m:94): ns = max(ceil(|pred_var|),20) perturb-and-MAP samples
+                              * for the explained variance that kgp_predict_host subtracts; 0 = prior variance only */
 } kgp_opt;
 
 /* per-call statistics of the last kgp_eval / kgp_dlik_dx / kgp_predict */
@@ -139,6 +141,13 @@ int kgp_set_probes_host(kgp_ctx* ctx, const double* V, long n, int m, double ema
  * 281-302, per-column convergence masks): out = sW .* CG(I + sW Mx Kg Mx' sW, sW .* r).  R and out are m x n,
  * one right-hand side per row.  The building block of opt.pred_var (GPML/inf/infGrid.m:93-104). */
 int kgp_grid_solve_host(kgp_ctx* ctx, int slot, const double* R, int m, double* out);
+
+/* Explained variance on the grid by perturb-and-MAP (GPML/inf/infGrid.m:91-101, sample() :147-152):
+ *   a ~ N(0,Ku) (eigen square root), A = Mx a + randn/sW, A <- post.L(A), z = Ku Mx' A, vg = mean(z.^2).
+ * The reference's unseeded randn(N,ns) / randn(n,ns) are the explicit inputs Rg (ns x N) and Rn (ns x n), one draw per
+ * row; both NULL -> generated on the device from `seed`.  The result is cached for kgp_predict_host (used when
+ * opt.pred_var != 0) and copied to vg_out (N, first axis fastest) when that is not NULL. */
+int kgp_grid_pred_var_host(kgp_ctx* ctx, int slot, const double* Rg, const double* Rn, int ns, uint64_t seed, double* vg_out);
 
 /* posterior pieces for tests / callers that want them (host copies) */
 int kgp_get_alpha_host(kgp_ctx* ctx, double* alpha /* n */);

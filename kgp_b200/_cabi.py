@@ -21,7 +21,7 @@ class KgpOpt(C.Structure):
     _fields_ = [('cg_tol', C.c_double), ('cg_maxit', C.c_int), ('ldB2_cheby', C.c_int),
                 ('ldB2_cheby_hutch', C.c_int), ('ldB2_cheby_degree', C.c_int),
                 ('ldB2_cheby_maxit', C.c_int), ('ldB2_cheby_seed', C.c_uint64),
-                ('ard_reference_form', C.c_int), ('cg_precond', C.c_int)]
+                ('ard_reference_form', C.c_int), ('cg_precond', C.c_int), ('pred_var', C.c_int)]
 
 
 class KgpStats(C.Structure):
@@ -71,6 +71,7 @@ SIGNATURES = {
     'kgp_bench_syrk': (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, _DP, _DP]),
     'kgp_set_probes_host': (C.c_int, [C.c_void_p, C.c_void_p, C.c_long, C.c_int, C.c_double]),
     'kgp_grid_solve_host': (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_void_p]),
+    'kgp_grid_pred_var_host': (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_uint64, C.c_void_p]),
     'kgp_nccl_unique_id': (C.c_int, [C.c_char_p, C.c_char_p]),
     'kgp_dist_last_error': (C.c_char_p, []),
     'kgp_comm_init': (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_char_p, C.c_char_p]),
@@ -169,6 +170,8 @@ class Context(object):
         hc = f64(hyp_cov, (-1,)); hm = f64(hyp_mean, (-1,))
         o = KgpOpt(); self._l.kgp_opt_default(C.byref(o))
         for k, v in (opt or {}).items():
+            if k == 'pred_var':
+                v = int(np.ceil(abs(float(v))))                  # infGrid.m:94
             if hasattr(o, k):
                 setattr(o, k, type(getattr(o, k))(v))
         self._chk(self._l.kgp_set_model(self._h, INF[inf], COV[cov], int(sm_Q), int(mean_mask), _ptr(hc), hc.size,
@@ -239,6 +242,19 @@ class Context(object):
         Rt = np.ascontiguousarray(R.T); out = np.empty_like(Rt)
         self._chk(self._l.kgp_grid_solve_host(self._h, slot, _ptr(Rt), Rt.shape[0], _ptr(out)))
         return np.ascontiguousarray(out.T)
+
+    def grid_pred_var(self, slot, N, Rg=None, Rn=None, ns=20, seed=0):
+        """Explained variance on the grid (infGrid.m:91-101).  Rg (N x ns), Rn (n x ns): the reference's randn draws,
+        or None for device-generated ones.  Returns vg (N,), first axis fastest."""
+        vg = np.empty(int(N))
+        if Rg is not None:
+            Rgt = np.ascontiguousarray(np.asarray(Rg, dtype=np.float64).T)
+            Rnt = np.ascontiguousarray(np.asarray(Rn, dtype=np.float64).T)
+            assert Rgt.shape[1] == int(N) and Rgt.shape[0] == Rnt.shape[0]
+            self._chk(self._l.kgp_grid_pred_var_host(self._h, slot, _ptr(Rgt), _ptr(Rnt), Rgt.shape[0], 0, _ptr(vg)))
+        else:
+            self._chk(self._l.kgp_grid_pred_var_host(self._h, slot, None, None, int(ns), int(seed), _ptr(vg)))
+        return vg
 
     def set_profiling(self, on):
         self._chk(self._l.kgp_set_profiling(self._h, int(bool(on))))

@@ -19,6 +19,7 @@ int grid_create(kgp_ctx* c, int slot, int eq, double k);
 void grid_free(kgp_ctx* c);
 int grid_init(kgp_ctx* c);
 int grid_solve(kgp_ctx* c, int slot, const double* R, int m, double* out);
+int grid_pred_var(kgp_ctx* c, int slot, const double* Rg, const double* Rn, int ns, unsigned long long seed, double* vg_out);
 int grid_set_probes(kgp_ctx* c, const double* V, long n, int m, double emax);
 int dist_unique_id(char* out128, const char* libpath, std::string& err);
 int dist_init(kgp_ctx* c, int nranks, int rank, const char* id128, const char* libpath);
@@ -54,7 +55,7 @@ const char* kgp_version(void) { return "kgp_b200 0.1 (sm_100a)"; }
 void kgp_opt_default(kgp_opt* o) {
   memset(o, 0, sizeof *o);
   o->cg_tol = 1e-6; o->cg_maxit = 0; o->ldB2_cheby = 0; o->ldB2_cheby_hutch = 10;
-  o->ldB2_cheby_degree = 15; o->ldB2_cheby_maxit = 50; o->ldB2_cheby_seed = 0; o->ard_reference_form = 0; o->cg_precond = 0;
+  o->ldB2_cheby_degree = 15; o->ldB2_cheby_maxit = 50; o->ldB2_cheby_seed = 0; o->ard_reference_form = 0; o->cg_precond = 0; o->pred_var = 0;
 }
 
 int kgp_ctx_create(int device, kgp_ctx** out) {
@@ -110,6 +111,12 @@ int kgp_grid_solve_host(kgp_ctx* c, int slot, const double* R, int m, double* ou
   if (c->model.inf_kind != KGP_INF_GRID) return c->fail(KGP_BAD_ARG, "kgp_grid_solve_host needs infGrid");
   cudaSetDevice(c->device);
   return grid_solve(c, slot, R, m, out);
+}
+int kgp_grid_pred_var_host(kgp_ctx* c, int slot, const double* Rg, const double* Rn, int ns, uint64_t seed, double* vg_out) {
+  if (!c || slot < 0 || slot >= KGP_NUM_SLOTS) return c ? c->fail(KGP_BAD_ARG, "bad pred_var arguments") : KGP_BAD_ARG;
+  if (c->model.inf_kind != KGP_INF_GRID) return c->fail(KGP_BAD_ARG, "kgp_grid_pred_var_host needs infGrid");
+  cudaSetDevice(c->device);
+  return grid_pred_var(c, slot, Rg, Rn, ns, (unsigned long long)seed, vg_out);
 }
 static std::string g_dist_err;
 int kgp_nccl_unique_id(char* out128, const char* nccl_lib_path) {

@@ -36,6 +36,9 @@ struct GridState {
   // cached posterior
   unsigned long st_slot_ver = 0, st_model_ver = 0, st_grid_ver = 0; int st_slot = -1, st_level = -1;
   double prior_var = 0.0;
+  // explained variance on the grid (opt.pred_var; infGrid.m:91-101)
+  DevBuf vg, pvA, pvS, pvG; bool eig_ok = false, vg_nonzero = false;
+  unsigned long vg_slot_ver = 0, vg_model_ver = 0, vg_grid_ver = 0; int vg_slot = -1;
 };
 
 static GridState* gs(kgp_ctx* c) {
@@ -49,7 +52,8 @@ void grid_free(kgp_ctx* c) {
                     &g->tgrid, &g->beta, &g->x, &g->r, &g->d, &g->z, &g->ym, &g->partA, &g->partB, &g->S, &g->hyp,
                     &g->hypm, &g->dX, &g->dhyp, &g->out, &g->sortk, &g->sorti, &g->keep, &g->dmean,
                     &g->U, &g->perm, &g->sx, &g->sr, &g->sd, &g->sz, &g->ctl, &g->cnt, &g->KfT, &g->gm0, &g->gm1, &g->pdz, &g->prr, &g->bar, &g->part4, &g->g0b, &g->wmaxd,
-                    &g->Gm, &g->Ht1, &g->Ht2, &g->VT, &g->se, &g->ps, &g->pw, &g->probes, &g->chT, &g->chU, &g->chY, &g->chS, &g->chC, &g->chP, &g->bva, &g->bvb, &g->chacc};
+                    &g->Gm, &g->Ht1, &g->Ht2, &g->VT, &g->se, &g->ps, &g->pw, &g->probes, &g->chT, &g->chU, &g->chY, &g->chS, &g->chC, &g->chP, &g->bva, &g->bvb, &g->chacc,
+                    &g->vg, &g->pvA, &g->pvS, &g->pvG};
   for (DevBuf* b : bufs) b->release();
   if (g->h_ctl) cudaFreeHost(g->h_ctl);
   if (g->cg_graph) cudaGraphExecDestroy(g->cg_graph);
@@ -547,9 +551,10 @@ static int precond_apply(kgp_ctx* c, GridState* g, const GridDesc& G, const Slot
   return KGP_OK;
 }
 // alpha = sW CG(B, sW ym) with the Woodbury preconditioner; same stopping rule and iteration count as apx.m:281-302
-static int pcg_solve(kgp_ctx* c, GridState* g, const GridDesc& G, int slot, double sw, double tol, int maxit) {
+static int pcg_solve(kgp_ctx* c, GridState* g, const GridDesc& G, int slot, double sw, double tol, int maxit,
+                     const double* rhs, double* x, bool setup) {
   Slot& S = c->slots[slot]; cudaStream_t st = c->stream; const long n = S.n; const int D = S.D;
-  int rc = precond_setup(c, g, G, slot, sw * sw); if (rc) return rc;
+  int rc = setup ? precond_setup(c, g, G, slot, sw * sw) : KGP_OK; if (rc) return rc;
   if (getenv("KGP_DEBUG")) fprintf(stderr, "[kgp] pcg setup done at %.2f ms\n", dbg_now(st));
   const int nb = nblocks_for(n);
   double h[4];
@@ -558,8 +563,8 @@ static int pcg_solve(kgp_ctx* c, GridState* g, const GridDesc& G, int slot, doub
     KGP_CUDA(c, cudaStreamSynchronize(st));
     return KGP_OK;
   };
-  double* x = g->x.d(); double* r = g->r.d(); double* d = g->d.d(); double* z = g->z.d(); double* s = g->ps.d();
-  cg_init_kernel<<<nb, 256, 0, st>>>(g->ym.d(), sw, n, x, r, d, g->partA.d());                   // x = 0, r = d = b
+  double* r = g->r.d(); double* d = g->d.d(); double* z = g->z.d(); double* s = g->ps.d();
+  cg_init_kernel<<<nb, 256, 0, st>>>(rhs, sw, n, x, r, d, g->partA.d());                         // x = 0, r = d = b
   sum_small_kernel<<<1, 256, 0, st>>>(g->partA.d(), nb, g->out.d() + 8);
   rc = fetch(g->out.d() + 8, 1); if (rc) return rc;
   const double nbn = sqrt(h[0]);
@@ -799,7 +804,8 @@ int grid_eval(kgp_ctx* c, int slot, int want, double* nlZ_out, double* dnlZ_out)
   // eigen-decompositions of all factors: one CTA each, on the side stream, overlapped with the CG solve
   cudaEventRecord(c->ev[10], st);
   cudaStreamWaitEvent(c->stream2, c->ev[10], 0);
-  if (!cheby || m.opt.cg_precond) jacobi_eig_kernel<<<G.p, EIG_THREADS, eig_smem, c->stream2>>>(eb, getenv("KGP_EIG_SWEEPS") ? atoi(getenv("KGP_EIG_SWEEPS")) : 40);
+  g->eig_ok = !cheby || m.opt.cg_precond || m.opt.pred_var != 0;
+  if (g->eig_ok) jacobi_eig_kernel<<<G.p, EIG_THREADS, eig_smem, c->stream2>>>(eb, getenv("KGP_EIG_SWEEPS") ? atoi(getenv("KGP_EIG_SWEEPS")) : 40);
   cudaEventRecord(c->ev[11], c->stream2);
   c->stats.kernel_launches++;
   resid_mean_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(S.X.d(), S.has_y ? S.y.d() : nullptr, n, D, m.mean_mask, g->hypm.d(), g->ym.d(), n);
@@ -809,7 +815,7 @@ int grid_eval(kgp_ctx* c, int slot, int want, double* nlZ_out, double* dnlZ_out)
   int maxit = m.opt.cg_maxit > 0 ? m.opt.cg_maxit : (int)std::min<long>(n, 20);
   static const bool legacy_cg = getenv("KGP_CG_LEGACY") && atoi(getenv("KGP_CG_LEGACY"));
   if (m.opt.cg_precond) {
-    rc = pcg_solve(c, g, G, slot, sw, m.opt.cg_tol, maxit);
+    rc = pcg_solve(c, g, G, slot, sw, m.opt.cg_tol, maxit, g->ym.d(), g->x.d(), true);
     if (rc) return rc;
   } else if (G.p <= 2 && !legacy_cg) {
     rc = cg_solve_sorted(c, g, G, slot, g->ym.d(), n, 1, sw, m.opt.cg_tol, maxit);
@@ -965,7 +971,115 @@ int grid_solve(kgp_ctx* c, int slot, const double* R, int m, double* out) {
   return KGP_OK;
 }
 
-// post.predict (infGrid.m:135-145): fmu = ms + Ms (Kg Mx' alpha); fs2 = prior variance (vg = 0)
+// ---- opt.pred_var: explained variance on the grid by perturb-and-MAP (infGrid.m:91-101, sample() :147-152) -------
+// standard normals from a counter-based generator (splitmix64 pairs + Box-Muller) when no draws are injected
+__global__ void normal_kernel(unsigned long long seed, long count, double* __restrict__ out) {
+  long q = (long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (q >= count) return;
+  auto mix = [](unsigned long long z) { z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ULL; z = (z ^ (z >> 27)) * 0x94D049BB133111EBULL; return z ^ (z >> 31); };
+  const unsigned long long a = mix(seed + 0x9E3779B97F4A7C15ULL * (unsigned long long)(2 * q + 1));
+  const unsigned long long b = mix(seed + 0x9E3779B97F4A7C15ULL * (unsigned long long)(2 * q + 2));
+  const double u1 = ((double)(a >> 11) + 1.0) * (1.0 / 9007199254740992.0), u2 = (double)(b >> 11) * (1.0 / 9007199254740992.0);
+  out[q] = sqrt(-2.0 * log(u1)) * cospi(2.0 * u2);
+}
+__global__ void sq_acc_kernel(long N, double coef, const double* __restrict__ z, double* __restrict__ vg) {
+  long q = (long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (q < N) vg[q] = fma(coef * z[q], z[q], vg[q]);
+}
+__global__ void absmax_flag_kernel(long N, const double* __restrict__ v, double* __restrict__ out) {
+  __shared__ double sh[32];
+  double a = 0.0;
+  for (long q = threadIdx.x; q < N; q += blockDim.x) a += fabs(v[q]);
+  const double t = block_sum(a, sh);
+  if (threadIdx.x == 0) out[0] = t;
+}
+// Rg: ns x N, Rn: ns x n (host, one draw per row; both NULL -> generated from seed).  vg_out (host, N) optional.
+int grid_pred_var(kgp_ctx* c, int slot, const double* Rg, const double* Rn, int ns, unsigned long long seed, double* vg_out) {
+  GridState* g = gs(c); Model& mo = c->model;
+  if (ns <= 0) return c->fail(KGP_BAD_ARG, "pred_var needs ns > 0 samples");
+  if ((Rg == nullptr) != (Rn == nullptr)) return c->fail(KGP_BAD_ARG, "pred_var: inject both draw matrices or neither");
+  if (!gstate_valid(c, g, slot, 0) || !g->eig_ok) {
+    if (mo.opt.ldB2_cheby && !mo.opt.cg_precond && !mo.opt.pred_var)
+      return c->fail(KGP_BAD_ARG, "pred_var with opt.ldB2_cheby needs opt.pred_var set (factor eigen-decompositions)");
+    int rc = grid_eval(c, slot, 1, nullptr, nullptr); if (rc) return rc;
+  }
+  GridDesc G; int rc = grid_setup(c, g, G); if (rc) return rc;
+  if (G.p > 2) return c->fail(KGP_BAD_ARG, "pred_var is built for 1-D and 2-D grids");
+  Slot& S = c->slots[slot]; const long n = S.n, N = G.N; const int D = S.D;
+  const double sn2 = exp(2.0 * mo.hyp_lik), sw = 1.0 / sqrt(sn2), sn = sqrt(sn2);
+  const int maxit = mo.opt.cg_maxit > 0 ? mo.opt.cg_maxit : (int)std::min<long>(n, 20);
+  cudaStream_t st = c->stream;
+  const bool pre = mo.opt.cg_precond != 0;
+  const int MB = pre ? 1 : CG_MAXCOLS;
+  long ksz = 0; for (int d = 0; d < G.p; ++d) ksz += (long)G.ng[d] * G.ng[d];
+  KGP_CUDA(c, g->VT.ensure(ksz * 8)); KGP_CUDA(c, g->se.ensure(N * 8));
+  KGP_CUDA(c, g->vg.ensure(N * 8)); KGP_CUDA(c, g->pvG.ensure((size_t)2 * N * 8));
+  KGP_CUDA(c, g->pvA.ensure((size_t)MB * n * 8)); KGP_CUDA(c, g->pvS.ensure((size_t)MB * n * 8));
+  cudaStreamWaitEvent(st, c->ev[11], 0);
+  if (!pre) {                                                        // (the preconditioner set-up already made these)
+    for (int d = 0; d < G.p; ++d) {
+      const long nn = (long)G.ng[d] * G.ng[d];
+      transpose_small_kernel<<<(unsigned)((nn + 255) / 256), 256, 0, st>>>(g->Vf.d() + g->koff[d], G.ng[d], g->VT.d() + g->koff[d]);
+    }
+    sqrt_kron_eig_kernel<<<(unsigned)((N + 255) / 256), 256, 0, st>>>(G, g->ee.d(), (const int*)g->eoff.p, g->se.d());
+  }
+  KGP_CUDA(c, cudaMemsetAsync(g->vg.p, 0, N * 8, st));
+  const int nb = nblocks_for(n);
+  double* zg = g->pvG.d(); double* tg = g->pvG.d() + N;
+  int worst_it = 0; double worst_rel = 0.0;
+  for (int c0 = 0; c0 < ns; c0 += MB) {
+    const int mb = std::min(MB, ns - c0);
+    for (int col = 0; col < mb; ++col) {
+      double* Acol = g->pvA.d() + (long)col * n;
+      if (Rg) {
+        KGP_CUDA(c, cudaMemcpyAsync(g->g0.p, Rg + (long)(c0 + col) * N, N * 8, cudaMemcpyHostToDevice, st));
+        KGP_CUDA(c, cudaMemcpyAsync(Acol, Rn + (long)(c0 + col) * n, n * 8, cudaMemcpyHostToDevice, st));
+      } else {
+        normal_kernel<<<(unsigned)((N + 255) / 256), 256, 0, st>>>(seed + 2ULL * (unsigned long long)(c0 + col) * 0x51ED27ULL, N, g->g0.d());
+        normal_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(seed + (2ULL * (unsigned long long)(c0 + col) + 1ULL) * 0x51ED27ULL, n, Acol);
+      }
+      double* t = kron_apply(c, g, G, g->g0.d(), g->g1.d(), -1, g->VT.d());                     // V' r
+      mul_pad_kernel<<<(unsigned)((N + 255) / 256), 256, 0, st>>>(t, g->se.d(), N, N, g->g0.d());   // E^1/2 .
+      double* a = kron_apply(c, g, G, g->g0.d(), g->g1.d(), -1, g->Vf.d());                      // a ~ N(0, Ku)
+      vec_scale_copy_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(n, sn, Acol, Acol);          // randn / sW
+      for_p(G.p, [&](auto P) {
+        interp_gather_bz_kernel<decltype(P)::value><<<nb, 256, 0, st>>>(G, S.X.d(), n, D, a, 1.0, Acol, Acol, nullptr);   // A = M a + randn/sW
+      });
+      c->stats.kernel_launches += 5;
+    }
+    // A <- post.L(A) = -sW CG(B, sW A)  (the sign drops out of z.^2)
+    if (pre) {
+      rc = pcg_solve(c, g, G, slot, sw, mo.opt.cg_tol, maxit, g->pvA.d(), g->pvS.d(), false); if (rc) return rc;
+    } else {
+      rc = cg_solve_sorted(c, g, G, slot, g->pvA.d(), n, mb, sw, mo.opt.cg_tol, maxit); if (rc) return rc;
+      for (int col = 0; col < mb; ++col)
+        cg_unsort_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(g->sx.d() + (long)col * g->npad, (const int*)g->perm.p, n, sw, g->pvS.d() + (long)col * n);
+    }
+    worst_it = std::max(worst_it, c->stats.cg_iters); worst_rel = std::max(worst_rel, c->stats.cg_relres);
+    for (int col = 0; col < mb; ++col) {                                   // z = Ku M' A ; vg += z.^2 / ns
+      scatter(c, G, S.X.d(), n, D, g->pvS.d() + (long)col * n, 1.0, tg);
+      kron_to(c, g, G, tg, zg, -1);
+      sq_acc_kernel<<<(unsigned)((N + 255) / 256), 256, 0, st>>>(N, 1.0 / (double)ns, zg, g->vg.d());
+      c->stats.kernel_launches += 2;
+    }
+  }
+  c->stats.cg_iters = worst_it; c->stats.cg_relres = worst_rel;
+  absmax_flag_kernel<<<1, 1024, 0, st>>>(N, g->vg.d(), g->out.d() + 10);
+  double l1 = 0.0;
+  KGP_CUDA(c, cudaMemcpyAsync(&l1, g->out.d() + 10, 8, cudaMemcpyDeviceToHost, st));
+  if (vg_out) KGP_CUDA(c, cudaMemcpyAsync(vg_out, g->vg.p, N * 8, cudaMemcpyDeviceToHost, st));
+  KGP_CUDA(c, cudaStreamSynchronize(st));
+  KGP_CUDA(c, cudaGetLastError());
+  g->vg_nonzero = l1 > 1e-10;                                               // infGrid.m:141
+  g->vg_slot = slot; g->vg_slot_ver = S.version; g->vg_model_ver = mo.version; g->vg_grid_ver = c->grid.version;
+  return KGP_OK;
+}
+static bool vg_valid(kgp_ctx* c, GridState* g, int slot) {
+  return g->vg_slot == slot && g->vg_slot_ver == c->slots[slot].version && g->vg_model_ver == c->model.version &&
+         g->vg_grid_ver == c->grid.version;
+}
+
+// post.predict (infGrid.m:135-145): fmu = ms + Ms (Kg Mx' alpha); fs2 = max(k** - Ms vg, 0), vg = 0 unless opt.pred_var
 int grid_predict(kgp_ctx* c, const double* Xs, long ns, double* ymu, double* ys2, double* fmu, double* fs2) {
   GridState* g = gs(c);
   const int slot = KGP_SLOT_TR;
@@ -989,9 +1103,24 @@ int grid_predict(kgp_ctx* c, const double* Xs, long ns, double* ymu, double* ys2
   KGP_CUDA(c, cudaMemcpyAsync(b.data(), c->pred_b.p, ns * 8, cudaMemcpyDeviceToHost, st));
   KGP_CUDA(c, cudaStreamSynchronize(st));
   KGP_CUDA(c, cudaGetLastError());
-  const double v = fmax(g->prior_var, 0.0);
+  std::vector<double> ve;
+  if ((fs2 || ys2) && m.opt.pred_var != 0) {                               // explained variance (infGrid.m:94,141-143)
+    if (!vg_valid(c, g, slot)) {
+      const int nsmp = std::max((int)ceil(fabs((double)m.opt.pred_var)), 20);
+      rc = grid_pred_var(c, slot, nullptr, nullptr, nsmp, m.opt.ldB2_cheby_seed ^ 0xC0FFEEULL, nullptr); if (rc) return rc;
+    }
+    if (g->vg_nonzero) {
+      for_p(G.p, [&](auto P) {
+        interp_gather_bz_kernel<decltype(P)::value><<<nblocks_for(ns), 256, 0, st>>>(G, c->pred_X.d(), ns, D, g->vg.d(), 1.0, nullptr, c->pred_a.d(), nullptr);
+      });
+      ve.resize(ns);
+      KGP_CUDA(c, cudaMemcpyAsync(ve.data(), c->pred_a.p, ns * 8, cudaMemcpyDeviceToHost, st));
+      KGP_CUDA(c, cudaStreamSynchronize(st));
+    }
+  }
   for (long i = 0; i < ns; ++i) {
     const double f = a[i] - b[i];
+    const double v = fmax(g->prior_var - (ve.empty() ? 0.0 : ve[i]), 0.0);
     if (fmu) fmu[i] = f; if (ymu) ymu[i] = f;
     if (fs2) fs2[i] = v; if (ys2) ys2[i] = v + sn2;
   }

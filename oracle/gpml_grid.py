@@ -368,11 +368,12 @@ def inf_grid(hyp, mean, kind, xg, x, y, opt=None, Q=0, want_grad=True, cheby=Non
         return (sW[:, None] * Kmvm(sW[:, None] * v) + v) if v.ndim == 2 else sW * Kmvm(sW * v) + v
 
     def solveKiW(r):
-        q, flag, relres, it = conjgrad(mvmB, sW * r, tol, maxit)
+        sw_ = sW[:, None] if np.ndim(r) == 2 else sW
+        q, flag, relres, it = conjgrad(mvmB, sw_ * r, tol, maxit)
         if not flag:
             raise CGNotConverged('Not converged after %d iterations, r=%1.2e' % (it, np.max(relres)))
         solveKiW.iters, solveKiW.relres = it, float(np.max(relres))
-        return sW * q
+        return sw_ * q
 
     dK_ab = lambda a, b: dirder(Ks, dKs, Mx, a, b)
     if cheby is None:
@@ -384,7 +385,8 @@ def inf_grid(hyp, mean, kind, xg, x, y, opt=None, Q=0, want_grad=True, cheby=Non
         ldB2, dhyp_cov, dW = logdet_sample(W, Kmvm, dK_ab, cheby['V'], cheby['d'], cheby['emax'], want_grad)
     alpha = solveKiW(y - m)
     post = {'alpha': alpha, 'Kalpha': kronmvm(Ks, MxT @ alpha), 'cg_iter': solveKiW.iters,
-            'cg_relres': solveKiW.relres, 'ldB2': ldB2}
+            'cg_relres': solveKiW.relres, 'ldB2': ldB2,
+            '_Ks': Ks, '_Mx': Mx, '_sW': sW, '_solveKiW': solveKiW}        # handles for pred_var_grid
     nlZ = (y - m) @ alpha / 2.0 + ldB2 + n * np.log(2 * np.pi * sn2) / 2.0
     if not want_grad:
         return post, nlZ, None
@@ -413,7 +415,24 @@ def dlik_grid(hyp, mean, kind, xg, x, y, opt=None, Q=0, h=1e-5):
     return np.stack(cols, axis=1)
 
 
-def predict_grid(hyp, mean, kind, xg, post, xs, Q=0):
+def pred_var_grid(post, Rg, Rn):
+    """Explained variance on the grid by perturb-and-MAP (infGrid.m:91-101 with sample(), infGrid.m:147-152).
+
+    The reference draws ``randn(N,ns)`` and ``randn(n,ns)`` unseeded; here they are the explicit inputs Rg (N x ns)
+    and Rn (n x ns).  a ~ N(0, Ku) through the clamped eigen-square-root, A = M a + Rn / sW, A <- post.L(A)
+    (= -solveKiW, batched conjgrad), z = Ku M' A, vg = mean(z^2)."""
+    Ks, Mx, sW, solve = post['_Ks'], post['_Mx'], post['_sW'], post['_solveKiW']
+    Rg = np.asarray(Rg, dtype=np.float64); Rn = np.asarray(Rn, dtype=np.float64)
+    ns = Rg.shape[1]
+    V, ee, e = eigkron(Ks)
+    A = kronmvm(V, np.sqrt(e)[:, None] * kronmvm([v.T for v in V], Rg))      # a ~ N(0, Ku)
+    A = Mx @ A + Rn / sW[:, None]
+    A = -solve(A)
+    z = kronmvm(Ks, Mx.T @ A)
+    return (z * z).sum(1) / ns
+
+
+def predict_grid(hyp, mean, kind, xg, post, xs, Q=0, vg=None):
     """[fmu fs2 ymu ys2] = post.predict(xs)  (infGrid.m:135-145; vg = 0 unless opt.pred_var)."""
     xs = np.asarray(xs, dtype=np.float64)
     if xs.ndim == 1:
@@ -423,6 +442,7 @@ def predict_grid(hyp, mean, kind, xg, post, xs, Q=0):
     fmu = ms + Ms @ post['Kalpha']
     hs = split_hyp(kind, hyp['cov'], len(xg), Q)
     ks = np.prod([factor_diag(kind, h_, Q) for h_ in hs]) * np.ones(xs.shape[0])
-    fs2 = np.maximum(ks - 0.0, 0.0)
+    ve = Ms @ vg if (vg is not None and np.abs(vg).sum() > 1e-10) else 0.0      # infGrid.m:141
+    fs2 = np.maximum(ks - ve, 0.0)
     sn2 = np.exp(2.0 * float(hyp['lik']))
     return fmu, fs2, fmu.copy(), fs2 + sn2

@@ -245,3 +245,57 @@ def test_woodbury_preconditioned_cg(built_lib, name):
     assert st['cg_relres'] < 1e-12 and st['cg_iters'] <= 8, st
     assert rel(nlZ, nlZ0) < 1e-8 and rel(g, g0) < 1e-7
     assert rel(gp.alpha(), post['alpha']) < 1e-7 and rel(dX, dX0) < 1e-7 and rel(ymu, p0[2]) < 1e-7
+
+
+@pytest.mark.parametrize('name,precond', [('c4', 0), ('c3_small', 0), ('sm_mean', 0), ('c3_small', 1), ('c4', 1)])
+def test_pred_var_injected_draws(built_lib, name, precond):
+    """opt.pred_var (infGrid.m:91-104,135-152): perturb-and-MAP explained variance with the reference's
+    unseeded randn draws injected into both sides.  vg is a smooth function of the converged solves, so at a tight
+    CG tolerance it must agree to 1e-7 relative; fs2/ys2 = max(k** - Ms vg, 0) (+ sn2) to the same."""
+    import gpml_grid as gg
+    c, X, y, Xs = build(name)
+    mean = c.get('mean', 'meanZero'); Q = c.get('Q', 0)
+    opt_ref = {'cg_maxit': 20000, 'cg_tol': 1e-12}
+    opt = dict(opt_ref, pred_var=20, cg_precond=precond)
+    gp = make(X, y, c['cov'], c['hyp'], c['lik'], c['k'], opt, mean, c.get('hyp_mean', ()),
+              ['{@meanLinear, @meanConst}'] if mean == 'meanSum' else None, Q)
+    xg, post, nlZ0, g0, dX0, p0 = oracle_all(gp, X, y, c['cov'], opt_ref, mean, Q, Xs)
+    N = int(np.prod([len(a) for a in xg])); n = X.shape[0]; ns = 20
+    rng = np.random.RandomState(7)
+    Rg = rng.randn(N, ns); Rn = rng.randn(n, ns)
+    vg0 = gg.pred_var_grid(post, Rg, Rn)
+    nlZ, g = gp.eng.eval(0, 1, gp._n_hyp)
+    vg = gp.eng.grid_pred_var(0, N, Rg, Rn)
+    assert rel(vg, vg0) < 1e-7
+    hv = gp._hyp_vec(); nc = gp.hyp['cov'].size
+    oh = {'cov': hv[:nc], 'lik': gp.hyp['lik'], 'mean': hv[nc + 1:]}
+    om = {'meanZero': ['meanZero'], 'meanSum': ['meanLinear', 'meanConst']}[mean]
+    fmu0, fs20, ymu0, ys20 = gg.predict_grid(oh, om, c['cov'], xg, post, Xs, Q=Q, vg=vg0)
+    ymu, ys2 = gp.predict(Xs, return_var=True)                    # uses the cached vg of the injected draws
+    assert rel(ymu, ymu0) < 1e-7 and rel(ys2, ys20) < 1e-7
+    assert np.all(ys20 <= p0[3] + 1e-12) and np.any(ys20 < p0[3] - 1e-6)     # variance is explained somewhere
+    assert rel(nlZ, nlZ0) < 1e-8                                   # the posterior itself is untouched
+    assert rel(gp.get_dlik_dx('tr'), dX0) < 1e-7
+
+
+def test_pred_var_generated_draws_statistics(built_lib):
+    """Without injected draws the engine generates its own normals; with many samples vg approaches the closed form
+    diag(Ku M'(M Ku M' + sn2 I)^-1 M Ku) (relative accuracy sqrt(2/ns), infGrid.m:99)."""
+    import gpml_grid as gg
+    rng = np.random.RandomState(3)
+    n = 300; X = rng.rand(n, 2); y = np.sin(4 * X[:, 0]) + np.cos(3 * X[:, 1]) + 0.1 * rng.randn(n)
+    opt = {'cg_maxit': 5000, 'cg_tol': 1e-10, 'pred_var': 800}
+    gp = make(X, y, 'covSEiso', [[np.log(0.3)], [0.0]], np.log(0.1), 12., opt)
+    xg = gg.creategrid(X, 1, 12.)
+    hv = gp._hyp_vec(); nc = gp.hyp['cov'].size
+    oh = {'cov': hv[:nc], 'lik': gp.hyp['lik'], 'mean': hv[nc + 1:]}
+    post, _, _ = gg.inf_grid(oh, ['meanZero'], 'covSEiso', xg, X, y, opt, want_grad=False)
+    Ks = post['_Ks']; Ku = np.kron(Ks[1], Ks[0]); M = post['_Mx'].toarray()
+    ex = np.diag(Ku @ M.T @ np.linalg.solve(M @ Ku @ M.T + 0.01 * np.eye(n), M @ Ku))
+    gp.eng.eval(0, 1, gp._n_hyp)
+    vg = gp.eng.grid_pred_var(0, Ku.shape[0], ns=800, seed=11)
+    big = ex > 0.2 * ex.max()
+    err = np.abs(vg[big] / ex[big] - 1.0)
+    assert err.mean() < 2.0 * np.sqrt(2.0 / 800) and err.max() < 6.0 * np.sqrt(2.0 / 800), (err.mean(), err.max())
+    ymu, ys2 = gp.predict(rng.rand(50, 2), return_var=True)       # generated automatically from opt.pred_var
+    assert np.all(ys2 >= 0.01 - 1e-12) and np.all(ys2 <= 1.0 + 0.01 + 1e-9) and ys2.min() < 0.5

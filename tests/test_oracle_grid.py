@@ -113,3 +113,24 @@ def test_chebyshev_estimator_with_injected_probes():
     assert abs(post['ldB2'] - np.linalg.slogdet(B)[1] / 2) < 0.15 * abs(np.linalg.slogdet(B)[1] / 2) + 0.5
     fd = _fd(lambda v: f(np.concatenate([v, v0[4:]]))[1], v0[:4])           # cov derivatives (emax fixed)
     assert np.max(np.abs(d['cov'] - fd)) / np.max(np.abs(fd)) < 1e-5
+
+
+def test_pred_var_matches_closed_form_statistically():
+    """pred_var_grid (infGrid.m:91-101,147-152): E[vg] = diag(Ku M'(M Ku M' + sn2 I)^-1 M Ku); the reference states a
+    relative accuracy of sqrt(2/ns) (infGrid.m:99).  Pins the restatement to the identity it estimates."""
+    rng = np.random.RandomState(3)
+    n = 300; x = rng.rand(n, 2); y = np.sin(4 * x[:, 0]) + np.cos(3 * x[:, 1]) + 0.1 * rng.randn(n)
+    xg = gg.creategrid(x, 1, 12)
+    hyp = {'cov': np.array([np.log(0.3), 0.0, np.log(0.3), 0.0]), 'lik': np.log(0.1), 'mean': []}
+    post, _, _ = gg.inf_grid(hyp, ['meanZero'], 'covSEiso', xg, x, y, {'cg_maxit': 2000, 'cg_tol': 1e-10}, want_grad=False)
+    N = int(np.prod([len(a) for a in xg])); ns = 600
+    vg = gg.pred_var_grid(post, rng.randn(N, ns), rng.randn(n, ns))
+    Ks = post['_Ks']; Ku = np.kron(Ks[1], Ks[0]); M = post['_Mx'].toarray()
+    ex = np.diag(Ku @ M.T @ np.linalg.solve(M @ Ku @ M.T + 0.01 * np.eye(n), M @ Ku))
+    big = ex > 0.2 * ex.max()
+    err = np.abs(vg[big] / ex[big] - 1.0)
+    assert err.mean() < 2.0 * np.sqrt(2.0 / ns) and err.max() < 6.0 * np.sqrt(2.0 / ns)
+    xs = rng.rand(40, 2)
+    f0 = gg.predict_grid(hyp, ['meanZero'], 'covSEiso', xg, post, xs)
+    f1 = gg.predict_grid(hyp, ['meanZero'], 'covSEiso', xg, post, xs, vg=vg)
+    assert np.allclose(f0[0], f1[0]) and np.all(f1[1] <= f0[1] + 1e-12) and np.all(f1[1] >= 0) and f1[1].min() < 0.5 * f0[1].max()
