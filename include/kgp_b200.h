@@ -55,6 +55,9 @@ typedef struct {
   int    cg_precond;         /* 1: grid-space Woodbury preconditioner for the CG (extension); 0 = reference CG */
   int    pred_var;           /* opt.pred_var (GPML/inf/infGrid.m:94): ns = max(ceil(|pred_var|),20) perturb-and-MAP samples
                               * for the explained variance that kgp_predict_host subtracts; 0 = prior variance only */
+  int    ldB2_slq;           /* 1: stochastic Lanczos quadrature log-det + Hutchinson derivatives (extension);
+                              * probes as for ldB2_cheby (ldB2_cheby_hutch, ldB2_cheby_seed, kgp_set_probes_host) */
+  int    ldB2_slq_steps;     /* Lanczos steps per probe, default 30 */
 } kgp_opt;
 
 /* per-call statistics of the last kgp_eval / kgp_dlik_dx / kgp_predict */

@@ -23,7 +23,7 @@ struct GridState {
   double* h_ctl = nullptr;                // pinned host copy of the control blocks
   long npad = 0; int sort_slot = -1; unsigned long sort_slot_ver = 0, sort_grid_ver = 0;
   cudaGraphExec_t cg_graph = nullptr; std::vector<char> cg_graph_key;
-  DevBuf probes, chT, chU, chY, chS, chC, chP, bva, bvb, chacc;   // Chebyshev log-det (grid_cheby.cuh)
+  DevBuf probes, chT, chU, chY, chS, chC, chP, bva, bvb, bvc, lzQ, lzP, lzH, chacc;   // Chebyshev log-det (grid_cheby.cuh)
   long probes_n = 0; int probes_m = 0; double probes_emax = 0.0; bool probes_injected = false;
   DevBuf Gm, Ht1, Ht2, VT, se, ps, pw;                 // Woodbury preconditioner (grid_precond.cuh)
   int gram_slot = -1; unsigned long gram_slot_ver = 0, gram_grid_ver = 0; int pcg_iters = 0;
@@ -52,7 +52,7 @@ void grid_free(kgp_ctx* c) {
                     &g->tgrid, &g->beta, &g->x, &g->r, &g->d, &g->z, &g->ym, &g->partA, &g->partB, &g->S, &g->hyp,
                     &g->hypm, &g->dX, &g->dhyp, &g->out, &g->sortk, &g->sorti, &g->keep, &g->dmean,
                     &g->U, &g->perm, &g->sx, &g->sr, &g->sd, &g->sz, &g->ctl, &g->cnt, &g->KfT, &g->gm0, &g->gm1, &g->pdz, &g->prr, &g->bar, &g->part4, &g->g0b, &g->wmaxd,
-                    &g->Gm, &g->Ht1, &g->Ht2, &g->VT, &g->se, &g->ps, &g->pw, &g->probes, &g->chT, &g->chU, &g->chY, &g->chS, &g->chC, &g->chP, &g->bva, &g->bvb, &g->chacc,
+                    &g->Gm, &g->Ht1, &g->Ht2, &g->VT, &g->se, &g->ps, &g->pw, &g->probes, &g->chT, &g->chU, &g->chY, &g->chS, &g->chC, &g->chP, &g->bva, &g->bvb, &g->bvc, &g->lzQ, &g->lzP, &g->lzH, &g->chacc,
                     &g->vg, &g->pvA, &g->pvS, &g->pvG};
   for (DevBuf* b : bufs) b->release();
   if (g->h_ctl) cudaFreeHost(g->h_ctl);
@@ -746,6 +746,146 @@ static int cheby_logdet(kgp_ctx* c, GridState* g, const GridDesc& G, int slot, d
   return KGP_OK;
 }
 
+// ---- stochastic Lanczos quadrature log-det (extension, no GPML counterpart) -----------------------
+//   ldB2 = 1/(2m) sum_i |v_i|^2 e1' log(T_i) e1 with T_i the Lanczos tridiagonal of B = I + sW K sW started at v_i;
+//   derivatives by Hutchinson: d ldB2 = 1/(2m) sum_i v_i' B^-1 dB v_i, g_i = B^-1 v_i from the (batched or
+//   preconditioned) CG; with uniform sW both bilinear forms collapse to grid space like the Chebyshev ones.
+static void sym_eig_host(std::vector<double>& A, int k, std::vector<double>& V) {      // cyclic Jacobi, A -> diag, V cols = vectors
+  V.assign((size_t)k * k, 0.0); for (int i = 0; i < k; ++i) V[(size_t)i * k + i] = 1.0;
+  for (int sweep = 0; sweep < 60; ++sweep) {
+    double off = 0.0, dg = 0.0;
+    for (int i = 0; i < k; ++i) for (int j = 0; j < k; ++j) (i == j ? dg : off) += A[(size_t)i * k + j] * A[(size_t)i * k + j];
+    if (off <= 1e-30 * dg) break;
+    for (int p = 0; p < k - 1; ++p)
+      for (int q = p + 1; q < k; ++q) {
+        const double apq = A[(size_t)p * k + q];
+        if (fabs(apq) < 1e-300) continue;
+        const double th = (A[(size_t)q * k + q] - A[(size_t)p * k + p]) / (2.0 * apq);
+        const double t = (th >= 0 ? 1.0 : -1.0) / (fabs(th) + sqrt(th * th + 1.0)), cs = 1.0 / sqrt(t * t + 1.0), sn = t * cs;
+        for (int r = 0; r < k; ++r) { const double x = A[(size_t)r * k + p], y = A[(size_t)r * k + q]; A[(size_t)r * k + p] = cs * x - sn * y; A[(size_t)r * k + q] = sn * x + cs * y; }
+        for (int r = 0; r < k; ++r) { const double x = A[(size_t)p * k + r], y = A[(size_t)q * k + r]; A[(size_t)p * k + r] = cs * x - sn * y; A[(size_t)q * k + r] = sn * x + cs * y; }
+        for (int r = 0; r < k; ++r) { const double x = V[(size_t)r * k + p], y = V[(size_t)r * k + q]; V[(size_t)r * k + p] = cs * x - sn * y; V[(size_t)r * k + q] = sn * x + cs * y; }
+      }
+  }
+}
+static int slq_logdet(kgp_ctx* c, GridState* g, const GridDesc& G, int slot, double sw, bool want_deriv) {
+  Slot& S = c->slots[slot]; Model& mo = c->model;
+  const long n = S.n; const int D = S.D; cudaStream_t st = c->stream;
+  const int steps = mo.opt.ldB2_slq_steps > 0 ? mo.opt.ldB2_slq_steps : 30;
+  if (steps > 512) return c->fail(KGP_BAD_ARG, "ldB2_slq_steps %d too large (max 512)", steps);
+  if ((double)steps * (double)n * 8.0 > 64e9) return c->fail(KGP_BAD_ARG, "ldB2_slq_steps x n: Lanczos basis above 64 GB");
+  int m = mo.opt.ldB2_cheby_hutch > 0 ? mo.opt.ldB2_cheby_hutch : 10;
+  if (g->probes_injected) {
+    if (g->probes_n != n) return c->fail(KGP_BAD_ARG, "injected probes have %ld rows, data has %ld", g->probes_n, n);
+    m = g->probes_m;
+  } else {
+    KGP_CUDA(c, g->probes.ensure((size_t)m * n * 8));
+    rademacher_kernel<<<(unsigned)(((long)m * n + 255) / 256), 256, 0, st>>>(mo.opt.ldB2_cheby_seed, n, m, g->probes.d());
+    g->probes_n = n; g->probes_m = m;
+  }
+  long ksz = 0; for (int q = 0; q < G.p; ++q) ksz += (long)G.ng[q] * G.ng[q];
+  KGP_CUDA(c, g->chT.ensure((size_t)2 * G.N * 8)); KGP_CUDA(c, g->chU.ensure((size_t)2 * G.N * 8));
+  KGP_CUDA(c, g->chP.ensure((size_t)ksz * 8)); KGP_CUDA(c, g->chacc.ensure(64));
+  KGP_CUDA(c, g->bvc.ensure(n * 8)); KGP_CUDA(c, g->lzQ.ensure((size_t)steps * n * 8));
+  KGP_CUDA(c, g->lzP.ensure((size_t)steps * nblocks_for(n) * 8)); KGP_CUDA(c, g->lzH.ensure((size_t)steps * 8));
+  KGP_CUDA(c, cudaMemsetAsync(g->chP.p, 0, ksz * 8, st));
+  KGP_CUDA(c, cudaMemsetAsync(g->chacc.p, 0, 64, st));
+  const int nb = nblocks_for(n);
+  int lo = 0, hi = m;
+  if (c->nranks > 1) { const int base = m / c->nranks, extra = m % c->nranks; lo = c->rank * base + std::min(c->rank, extra); hi = lo + base + (c->rank < extra ? 1 : 0); }
+  double quad = 0.0;
+  for (int i = lo; i < hi; ++i) {
+    const double* v = g->probes.d() + (long)i * n;
+    double h2[2];
+    dot_kernel<<<1, 1024, 0, st>>>(v, v, n, g->chacc.d() + 2);
+    KGP_CUDA(c, cudaMemcpyAsync(h2, g->chacc.d() + 2, 8, cudaMemcpyDeviceToHost, st));
+    KGP_CUDA(c, cudaStreamSynchronize(st));
+    const double nv2 = h2[0];
+    // Lanczos with full re-orthogonalisation: the basis is kept (steps x n), so two implementations that round
+    // differently stay on the same Krylov sequence and the quadrature is reproducible
+    double* Qb = g->lzQ.d(); double* w = g->bvc.d();
+    vec_scale_copy_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(n, 1.0 / sqrt(nv2), v, Qb);
+    std::vector<double> al, be; double beta = 0.0;
+    for (int j = 0; j < steps; ++j) {
+      const double* q = Qb + (long)j * n; const double* qp = j > 0 ? Qb + (long)(j - 1) * n : q;     // (beta = 0 at j = 0)
+      scatter(c, G, S.X.d(), n, D, q, sw, g->chT.d());                          // w = B q ; partials of q.w
+      kron_to(c, g, G, g->chT.d(), g->chU.d(), -1);
+      for_p(G.p, [&](auto P) {
+        cheby_step_kernel<decltype(P)::value><<<nb, 256, 0, st>>>(G, S.X.d(), n, D, g->chU.d(), q, q, 1.0, sw, w, g->partA.d());
+      });
+      sum_small_kernel<<<1, 256, 0, st>>>(g->partA.d(), nb, g->chacc.d() + 4);
+      lanczos_update_kernel<<<nb, 256, 0, st>>>(n, g->chacc.d() + 4, beta, q, qp, w, g->partB.d());
+      multi_dot_kernel<<<nb, 256, 0, st>>>(n, j + 1, Qb, w, g->lzP.d());
+      sum_rows_kernel<<<j + 1, 256, 0, st>>>(g->lzP.d(), nb, g->lzH.d());
+      multi_axpy_kernel<<<nb, 256, 0, st>>>(n, j + 1, Qb, g->lzH.d(), w, g->partB.d());
+      sum_small_kernel<<<1, 256, 0, st>>>(g->partB.d(), nb, g->chacc.d() + 5);
+      KGP_CUDA(c, cudaMemcpyAsync(h2, g->chacc.d() + 4, 16, cudaMemcpyDeviceToHost, st));
+      KGP_CUDA(c, cudaStreamSynchronize(st));
+      c->stats.kernel_launches += 7;
+      const double a = h2[0], b = sqrt(h2[1]);
+      al.push_back(a);
+      if (j + 1 == steps || !(b > 1e-12 * std::max(fabs(a), 1.0))) break;
+      be.push_back(b);
+      vec_scale_copy_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(n, 1.0 / b, w, Qb + (long)(j + 1) * n);
+      beta = b;
+    }
+    const int k = (int)al.size();
+    std::vector<double> T((size_t)k * k, 0.0), Vv;
+    for (int r = 0; r < k; ++r) { T[(size_t)r * k + r] = al[r]; if (r + 1 < k) { T[(size_t)r * k + r + 1] = be[r]; T[(size_t)(r + 1) * k + r] = be[r]; } }
+    sym_eig_host(T, k, Vv);
+    double qv = 0.0;
+    for (int r = 0; r < k; ++r) qv += Vv[r] * Vv[r] * log(fmax(T[(size_t)r * k + r], 1e-300));     // first components: row 0 of V
+    quad += nv2 * qv / (2.0 * m);
+  }
+  double sdw = 0.0;
+  if (want_deriv && hi > lo) {
+    const bool pre = mo.opt.cg_precond != 0;
+    const int MB = pre ? 1 : CG_MAXCOLS;
+    const int maxit = mo.opt.cg_maxit > 0 ? mo.opt.cg_maxit : (int)std::min<long>(n, 20);
+    KGP_CUDA(c, g->pvS.ensure((size_t)MB * n * 8));
+    for (int c0 = lo; c0 < hi; c0 += MB) {
+      const int mb = std::min(MB, hi - c0);
+      const double* V0 = g->probes.d() + (long)c0 * n;
+      double gscale;                                                         // pvS = gscale * B^-1 v
+      if (pre) {
+        int rc = pcg_solve(c, g, G, slot, sw, mo.opt.cg_tol, maxit, V0, g->pvS.d(), false); if (rc) return rc;
+        gscale = sw * sw;
+      } else {
+        int rc = cg_solve_sorted(c, g, G, slot, V0, n, mb, sw, mo.opt.cg_tol, maxit); if (rc) return rc;
+        for (int col = 0; col < mb; ++col)
+          cg_unsort_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(g->sx.d() + (long)col * g->npad, (const int*)g->perm.p, n, 1.0, g->pvS.d() + (long)col * n);
+        gscale = sw;
+      }
+      for (int col = 0; col < mb; ++col) {
+        double* Tg = g->chT.d(); double* Tv = g->chT.d() + G.N; double* Uv = g->chU.d();
+        scatter(c, G, S.X.d(), n, D, g->pvS.d() + (long)col * n, sw / gscale, Tg);       // Mx'(sW g)
+        scatter(c, G, S.X.d(), n, D, V0 + (long)col * n, sw, Tv);                          // Mx'(sW v)
+        kron_to(c, g, G, Tv, Uv, -1);
+        dot_kernel<<<1, 1024, 0, st>>>(Tg, Uv, G.N, g->chacc.d() + 2);
+        sum_scaled_acc_kernel<<<1, 256, 0, st>>>(g->chacc.d() + 2, 1, 1.0 / (2.0 * m * sw * sw), g->chacc.d() + 1);   // sum(dW)
+        for (int f = 0; f < G.p; ++f) {
+          const long inner = G.stride[f], outer = G.N / (inner * G.ng[f]);
+          kron_to(c, g, G, Tg, g->chU.d() + G.N, f);
+          mode_gram_acc_kernel<<<dim3(G.ng[f], G.ng[f]), 128, 0, st>>>(g->chU.d() + G.N, Tv, G.ng[f], inner, outer, g->chP.d() + g->koff[f]);
+        }
+        c->stats.kernel_launches += 5 + 2 * G.p;
+      }
+    }
+    vec_scale_copy_kernel<<<(unsigned)((ksz + 255) / 256), 256, 0, st>>>(ksz, 1.0 / (2.0 * m), g->chP.d(), g->chP.d());
+  }
+  (void)sdw;
+  // chacc[0] = ldB2 share of this rank, chacc[1] = sum(dW) share
+  KGP_CUDA(c, cudaMemcpyAsync(g->chacc.p, &quad, 8, cudaMemcpyHostToDevice, st));
+  if (c->nranks > 1) {
+    NcclApi& api = nccl_api(nullptr);
+    KGP_NCCL(c, api, api.AllReduce(g->chP.p, g->chP.p, (size_t)ksz, KGP_NCCL_DOUBLE, KGP_NCCL_SUM, c->nccl_comm, st));
+    KGP_NCCL(c, api, api.AllReduce(g->chacc.p, g->chacc.p, 2, KGP_NCCL_DOUBLE, KGP_NCCL_SUM, c->nccl_comm, st));
+  }
+  KGP_CUDA(c, cudaMemcpyAsync(g->out.d() + 2, g->chacc.p, 16, cudaMemcpyDeviceToDevice, st));
+  KGP_CUDA(c, cudaStreamSynchronize(st));
+  return KGP_OK;
+}
+
 int grid_set_probes(kgp_ctx* c, const double* V, long n, int m, double emax) {
   GridState* g = gs(c);
   if (!V || m <= 0) { g->probes_injected = false; return KGP_OK; }
@@ -766,7 +906,8 @@ int grid_eval(kgp_ctx* c, int slot, int want, double* nlZ_out, double* dnlZ_out)
   GridState* g = gs(c); Slot& S = c->slots[slot]; Model& m = c->model;
   const long n = S.n; const int D = S.D;
   if (m.cov_kind != KGP_COV_SEISO && m.cov_kind != KGP_COV_SM) return c->fail(KGP_BAD_ARG, "infGrid supports covSEiso / covSM factors");
-  const bool cheby = m.opt.ldB2_cheby != 0;
+  const bool slq = m.opt.ldB2_slq != 0;
+  const bool cheby = m.opt.ldB2_cheby != 0 || slq;           // stochastic estimators share the derivative plumbing
   GridDesc G; int rc = grid_setup(c, g, G); if (rc) return rc;
   if (G.p != D) return c->fail(KGP_BAD_ARG, "Grid and data dimension are different.");
   const int nh = factor_nhyp(m), nhyp = nh * G.p;
@@ -834,8 +975,10 @@ int grid_eval(kgp_ctx* c, int slot, int want, double* nlZ_out, double* dnlZ_out)
   cudaStreamWaitEvent(st, c->ev[11], 0);
   const unsigned char* keep = nullptr;
   if (cheby) {
-    rc = cheby_logdet(c, g, G, slot, sw, want >= 1, kind, Q, nh);
+    const int it0 = c->stats.cg_iters; const double rel0 = c->stats.cg_relres;      // keep the alpha solve's CG statistics
+    rc = slq ? slq_logdet(c, g, G, slot, sw, want >= 1) : cheby_logdet(c, g, G, slot, sw, want >= 1, kind, Q, nh);
     if (rc) return rc;
+    c->stats.cg_iters = it0; c->stats.cg_relres = rel0;
   } else {
   if (n < G.N) {
     long Npad = 1; while (Npad < G.N) Npad <<= 1;
@@ -999,7 +1142,7 @@ int grid_pred_var(kgp_ctx* c, int slot, const double* Rg, const double* Rn, int 
   if (ns <= 0) return c->fail(KGP_BAD_ARG, "pred_var needs ns > 0 samples");
   if ((Rg == nullptr) != (Rn == nullptr)) return c->fail(KGP_BAD_ARG, "pred_var: inject both draw matrices or neither");
   if (!gstate_valid(c, g, slot, 0) || !g->eig_ok) {
-    if (mo.opt.ldB2_cheby && !mo.opt.cg_precond && !mo.opt.pred_var)
+    if ((mo.opt.ldB2_cheby || mo.opt.ldB2_slq) && !mo.opt.cg_precond && !mo.opt.pred_var)
       return c->fail(KGP_BAD_ARG, "pred_var with opt.ldB2_cheby needs opt.pred_var set (factor eigen-decompositions)");
     int rc = grid_eval(c, slot, 1, nullptr, nullptr); if (rc) return rc;
   }

@@ -81,6 +81,58 @@ __global__ void mode_gram_acc_kernel(const double* __restrict__ A, const double*
   if (threadIdx.x == 0) Pm[(long)a * ng + b] += t;
 }
 
+// Lanczos three-term update: w -= a q + beta qp  (a read from the device scalar the dot-product reduction wrote);
+// part[block] = sum w.w
+__global__ void lanczos_update_kernel(long n, const double* __restrict__ a_dev, double beta, const double* __restrict__ q,
+                                      const double* __restrict__ qp, double* __restrict__ w, double* __restrict__ part) {
+  __shared__ double sh[32];
+  const double a = a_dev[0];
+  double acc = 0.0;
+  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long)gridDim.x * blockDim.x) {
+    const double wi = w[i] - a * q[i] - beta * qp[i];
+    w[i] = wi; acc = fma(wi, wi, acc);
+  }
+  const double t = block_sum(acc, sh);
+  if (threadIdx.x == 0) part[blockIdx.x] = t;
+}
+
+// Full re-orthogonalisation of the Lanczos vector (classical Gram-Schmidt against the k stored vectors Q[t][.]):
+//   part[t * gridDim.x + block] = sum over the block's contiguous rows of Q[t][i] w[i]
+__global__ void multi_dot_kernel(long n, int k, const double* __restrict__ Q, const double* __restrict__ w, double* __restrict__ part) {
+  __shared__ double sh[32];
+  const long per = (n + gridDim.x - 1) / gridDim.x, i0 = (long)blockIdx.x * per, i1 = (i0 + per < n) ? i0 + per : n;
+  for (int t = 0; t < k; ++t) {
+    const double* q = Q + (long)t * n;
+    double acc = 0.0;
+    for (long i = i0 + threadIdx.x; i < i1; i += blockDim.x) acc = fma(q[i], w[i], acc);
+    const double s = block_sum(acc, sh);
+    if (threadIdx.x == 0) part[(long)t * gridDim.x + blockIdx.x] = s;
+    __syncthreads();
+  }
+}
+// h[t] = sum_b part[t * nb + b]   (one CTA per t)
+__global__ void sum_rows_kernel(const double* __restrict__ part, int nb, double* __restrict__ h) {
+  __shared__ double sh[32];
+  const double t = sum_partials(part + (long)blockIdx.x * nb, nb, sh);
+  if (threadIdx.x == 0) h[blockIdx.x] = t;
+}
+//   w -= sum_t h[t] Q[t][.] ;  part2[block] = sum w.w
+__global__ void multi_axpy_kernel(long n, int k, const double* __restrict__ Q, const double* __restrict__ h, double* __restrict__ w,
+                                  double* __restrict__ part2) {
+  __shared__ double sh[32];
+  __shared__ double hs[512];
+  for (int t = threadIdx.x; t < k; t += blockDim.x) hs[t] = h[t];
+  __syncthreads();
+  double acc = 0.0;
+  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long)gridDim.x * blockDim.x) {
+    double wi = w[i];
+    for (int t = 0; t < k; ++t) wi = fma(-hs[t], Q[(long)t * n + i], wi);
+    w[i] = wi; acc = fma(wi, wi, acc);
+  }
+  const double s = block_sum(acc, sh);
+  if (threadIdx.x == 0) part2[blockIdx.x] = s;
+}
+
 // y = a*x + b*y  /  copy / scale helpers on n-vectors
 __global__ void vec_scale_copy_kernel(long n, double a, const double* __restrict__ x, double* __restrict__ y) {
   long i = (long)blockIdx.x * blockDim.x + threadIdx.x;

@@ -340,13 +340,59 @@ def logdet_sample(W, Kmvm, dK, V, d, emax, want_deriv=True):
 
 
 # ----------------------------------------------------------------------------
+# Stochastic Lanczos quadrature log-det (NOT in GPML 4.0 -- an extension, checked against the
+# dense identities it estimates, never reported as reference parity).  Probes V (n x m) are inputs.
+#   ldB2 = 1/(2m) sum_i |v_i|^2 e1' log(T_i) e1 ,  T_i from `steps` Lanczos steps on B = I + sW K sW started at v_i
+#   d ldB2/d theta = 1/(2m) sum_i dK(sW g_i, sW v_i),  g_i = B^-1 v_i   (Hutchinson estimate of tr(B^-1 dB)/2)
+#   dW             = 1/(2m) sum_i (g_i ./ sW) .* (K (sW .* v_i))
+# ----------------------------------------------------------------------------
+def lanczos_quadrature(B, v, steps):
+    """v' log(B) v by Gauss quadrature on the Lanczos tridiagonal; the basis is kept and every new vector is
+    re-orthogonalised against it (one classical Gram-Schmidt pass), which makes the recurrence reproducible."""
+    nv2 = float(v @ v)
+    q = v / np.sqrt(nv2); qp = np.zeros_like(q); beta = 0.0
+    al, be = [], []; Qm = [q]
+    for j in range(steps):
+        w = B(q)
+        a = float(q @ w)
+        w = w - a * q - beta * qp
+        Qa = np.stack(Qm, axis=1)
+        w = w - Qa @ (Qa.T @ w)
+        b = float(np.sqrt(w @ w))
+        al.append(a)
+        if j + 1 == steps or not (b > 1e-12 * max(abs(a), 1.0)):
+            break
+        be.append(b); qp = q; q = w / b; beta = b; Qm.append(q)
+    k = len(al)
+    T = np.diag(al) + np.diag(be[:k - 1], 1) + np.diag(be[:k - 1], -1)
+    th, S = np.linalg.eigh(T)
+    return nv2 * float((S[0] ** 2) @ np.log(th)), k
+
+
+def logdet_slq(W, Kmvm, dK, V, steps, solve, want_deriv=True):
+    sW = np.sqrt(W); n = W.size; m = V.shape[1]
+    B = lambda x: x + sW * Kmvm(sW * x)
+    ldB2 = 0.0; dhyp = 0.0; dWv = np.zeros(n)
+    for i in range(m):
+        v = V[:, i]
+        val, _ = lanczos_quadrature(B, v, steps)
+        ldB2 += val / (2.0 * m)
+        if want_deriv:
+            g = solve(v)                                   # B^-1 v  (same conjgrad as the alpha solve)
+            dhyp = dhyp + dK(sW * g, sW * v) / (2.0 * m)
+            dWv += (g / sW) * Kmvm(sW * v) / (2.0 * m)
+    return ldB2, dhyp, dWv
+
+
+# ----------------------------------------------------------------------------
 # infGrid with likGauss (infGrid.m:53-89 -> infGaussLik.m:19-33 -> apx.m grid branch)
 # ----------------------------------------------------------------------------
-def inf_grid(hyp, mean, kind, xg, x, y, opt=None, Q=0, want_grad=True, cheby=None):
+def inf_grid(hyp, mean, kind, xg, x, y, opt=None, Q=0, want_grad=True, cheby=None, slq=None):
     """returns post {alpha, Kalpha (grid vector), cg_iter, cg_relres}, nlZ, dnlZ {cov, lik, mean}.
 
     opt: cg_tol (1e-6), cg_maxit (min(n,20)).  cheby = dict(V=..., d=..., emax=...) selects the
-    Chebyshev estimator with injected probes (opt.ldB2_cheby), else the Fiedler bound."""
+    Chebyshev estimator with injected probes (opt.ldB2_cheby), else the Fiedler bound.
+    slq = dict(V=..., steps=...) selects stochastic Lanczos quadrature (extension)."""
     opt = opt or {}
     x = np.asarray(x, dtype=np.float64)
     if x.ndim == 1:
@@ -376,7 +422,14 @@ def inf_grid(hyp, mean, kind, xg, x, y, opt=None, Q=0, want_grad=True, cheby=Non
         return sw_ * q
 
     dK_ab = lambda a, b: dirder(Ks, dKs, Mx, a, b)
-    if cheby is None:
+    if slq is not None:
+        def solveB(r):
+            q, flag, relres, it = conjgrad(mvmB, r, tol, maxit)
+            if not flag:
+                raise CGNotConverged('Not converged after %d iterations, r=%1.2e' % (it, np.max(relres)))
+            return q
+        ldB2, dhyp_cov, dW = logdet_slq(W, Kmvm, dK_ab, slq['V'], slq['steps'], solveB, want_grad)
+    elif cheby is None:
         V, ee, e = eigkron(Ks)
         ldB2, de, dW = logdet_fiedler(e, W)
         de = de * (e > 0)

@@ -299,3 +299,56 @@ def test_pred_var_generated_draws_statistics(built_lib):
     assert err.mean() < 2.0 * np.sqrt(2.0 / 800) and err.max() < 6.0 * np.sqrt(2.0 / 800), (err.mean(), err.max())
     ymu, ys2 = gp.predict(rng.rand(50, 2), return_var=True)       # generated automatically from opt.pred_var
     assert np.all(ys2 >= 0.01 - 1e-12) and np.all(ys2 <= 1.0 + 0.01 + 1e-9) and ys2.min() < 0.5
+
+
+@pytest.mark.parametrize('name,precond', [('c4', 0), ('c3_small', 0), ('sm_mean', 0), ('c3_small', 1)])
+def test_slq_logdet_injected_probes(built_lib, name, precond):
+    """opt.ldB2_slq (EXTENSION, SURVEY a21(ii): stochastic Lanczos quadrature, not in GPML 4.0).  Same probes on both
+    sides.  The Gauss-quadrature value is insensitive to the loss of orthogonality of plain Lanczos, so engine and
+    oracle (different summation orders) agree to 1e-7 on nlZ; the Hutchinson derivatives to 1e-6."""
+    import gpml_grid as gg
+    c, X, y, Xs = build(name)
+    mean = c.get('mean', 'meanZero'); Q = c.get('Q', 0)
+    base = {'cg_maxit': 20000, 'cg_tol': 1e-12}
+    opt = dict(base, ldB2_slq=1, ldB2_slq_steps=25, cg_precond=precond)
+    gp = make(X, y, c['cov'], c['hyp'], c['lik'], c['k'], opt, mean, c.get('hyp_mean', ()),
+              ['{@meanLinear, @meanConst}'] if mean == 'meanSum' else None, Q)
+    rng = np.random.RandomState(7)
+    V = np.sign(rng.randn(X.shape[0], 5)); V[V == 0] = 1.0
+    gp.eng.set_probes(V, 0.0)
+    nlZ, g = gp.eng.eval(0, 2, gp._n_hyp)
+    hv = gp._hyp_vec(); nc = gp.hyp['cov'].size
+    oh = {'cov': hv[:nc], 'lik': gp.hyp['lik'], 'mean': hv[nc + 1:]}
+    om = {'meanZero': ['meanZero'], 'meanSum': ['meanLinear', 'meanConst']}[mean]
+    xg = gg.creategrid(X, 1, gp._grid_k)
+    post, nlZ0, d0 = gg.inf_grid(oh, om, c['cov'], xg, X, y, base, Q=Q, slq={'V': V, 'steps': 25})
+    g0 = np.concatenate([d0['cov'], [d0['lik']], d0['mean']])
+    assert rel(nlZ, nlZ0) < 1e-7, (nlZ, nlZ0)
+    assert rel(g, g0) < 1e-6, (g, g0)
+    assert rel(gp.alpha(), post['alpha']) < 1e-7
+    gp.eng.set_probes(None)                                   # generated probes: finite numbers, no accuracy claim
+    nlZ2, g2 = gp.eng.eval(0, 1, gp._n_hyp)
+    assert np.isfinite(nlZ2) and np.all(np.isfinite(g2))
+
+
+def test_slq_value_against_dense_logdet(built_lib):
+    """SLQ against the quantity it estimates: dense log det(B)/2 at n = 1500 with 30 probes x 40 steps -- within 5 %
+    (the estimator's own Monte-Carlo error), and closer to the truth than the Fiedler upper bound."""
+    import gpml_grid as gg
+    rng = np.random.RandomState(5)
+    n = 1500; X = rng.rand(n, 2); y = np.sin(5 * X[:, 0]) * np.cos(4 * X[:, 1]) + 0.2 * rng.randn(n)
+    opt = {'cg_maxit': 20000, 'cg_tol': 1e-10}
+    gp = make(X, y, 'covSEiso', [[np.log(0.2)], [0.0]], np.log(0.2), 24., dict(opt, ldB2_slq=1, ldB2_slq_steps=40, ldB2_cheby_hutch=30))
+    nlZ, _ = gp.eng.eval(0, 1, gp._n_hyp)
+    gp2 = make(X, y, 'covSEiso', [[np.log(0.2)], [0.0]], np.log(0.2), 24., opt)
+    nlZ_f, _ = gp2.eng.eval(0, 1, gp2._n_hyp)
+    hv = gp._hyp_vec(); nc = gp.hyp['cov'].size
+    oh = {'cov': hv[:nc], 'lik': gp.hyp['lik'], 'mean': hv[nc + 1:]}
+    xg = gg.creategrid(X, 1, 24.)
+    post, nlZ0, _ = gg.inf_grid(oh, ['meanZero'], 'covSEiso', xg, X, y, opt, want_grad=False)
+    Ks = post['_Ks']; M = post['_Mx'].toarray()
+    B = np.eye(n) + M @ np.kron(Ks[1], Ks[0]) @ M.T / np.exp(2 * gp.hyp['lik'])
+    true = 0.5 * np.linalg.slogdet(B)[1]
+    fit = nlZ0 - post['ldB2']                                  # everything except the log-det term
+    assert abs((nlZ - fit) / true - 1.0) < 0.05, (nlZ - fit, true)
+    assert abs((nlZ - fit) - true) < abs((nlZ_f - fit) - true)

@@ -134,3 +134,37 @@ def test_pred_var_matches_closed_form_statistically():
     f0 = gg.predict_grid(hyp, ['meanZero'], 'covSEiso', xg, post, xs)
     f1 = gg.predict_grid(hyp, ['meanZero'], 'covSEiso', xg, post, xs, vg=vg)
     assert np.allclose(f0[0], f1[0]) and np.all(f1[1] <= f0[1] + 1e-12) and np.all(f1[1] >= 0) and f1[1].min() < 0.5 * f0[1].max()
+
+
+def test_slq_matches_the_dense_quantities_it_estimates():
+    """logdet_slq (extension): per probe, the Lanczos Gauss quadrature equals v' log(B) v of the dense
+    matrix, and the Hutchinson derivative equals (1/2m) sum v' B^-1 dB v formed densely (dB by central differences)."""
+    rng = np.random.RandomState(3)
+    n = 200; x = rng.rand(n, 2); y = np.sin(4 * x[:, 0]) + np.cos(3 * x[:, 1]) + 0.1 * rng.randn(n)
+    xg = gg.creategrid(x, 1, 10)
+    hyp = {'cov': np.array([np.log(0.3), 0.0, np.log(0.3), 0.0]), 'lik': np.log(0.1), 'mean': []}
+    opt = {'cg_maxit': 5000, 'cg_tol': 1e-12}
+    m = 8; V = np.sign(rng.randn(n, m))
+    post, nlZ, d = gg.inf_grid(hyp, ['meanZero'], 'covSEiso', xg, x, y, opt, slq={'V': V, 'steps': 60})
+    M = post['_Mx'].toarray()
+
+    def Bof(hc):
+        hs = gg.split_hyp('covSEiso', hc, 2, 0)
+        Ks = [gg.factor_cov('covSEiso', hs[i], xg[i], 0)[0] for i in range(2)]
+        return np.eye(n) + M @ np.kron(Ks[1], Ks[0]) @ M.T / 0.01
+    B = Bof(hyp['cov']); th, S = np.linalg.eigh(B); logB = (S * np.log(th)) @ S.T
+    ex = sum(V[:, i] @ logB @ V[:, i] for i in range(m)) / (2 * m)
+    assert abs(post['ldB2'] - ex) < 1e-9 * abs(ex)
+    Bi = np.linalg.inv(B); ld = []
+    for i in range(4):
+        e = np.zeros(4); e[i] = 1e-6
+        dB = (Bof(hyp['cov'] + e) - Bof(hyp['cov'] - e)) / 2e-6
+        ld.append(sum(V[:, k] @ Bi @ dB @ V[:, k] for k in range(m)) / (2 * m))
+    hs = gg.split_hyp('covSEiso', hyp['cov'], 2, 0); fac = [gg.factor_cov('covSEiso', hs[i], xg[i], 0) for i in range(2)]
+    fit = -gg.dirder([f[0] for f in fac], [f[1] for f in fac], post['_Mx'], post['alpha'], post['alpha']) / 2
+    assert np.allclose(d['cov'] - fit, ld, rtol=1e-6)
+    # lik derivative: B = I + K/sn2 -> d ldB2/d log sn = -(1/m) sum v' B^-1 (B - I) v / 1 ... checked by differences of the value
+    f = lambda lik: gg.inf_grid({'cov': hyp['cov'], 'lik': lik, 'mean': []}, ['meanZero'], 'covSEiso', xg, x, y, opt,
+                                slq={'V': V, 'steps': 60}, want_grad=False)[1]
+    fd = (f(hyp['lik'] + 1e-5) - f(hyp['lik'] - 1e-5)) / 2e-5
+    assert abs(d['lik'] - fd) < 1e-5 * abs(fd)               # dB commutes with B for the noise scale: exact derivative
