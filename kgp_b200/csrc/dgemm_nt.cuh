@@ -132,6 +132,14 @@ __device__ __forceinline__ void gemm_tile_coords(const GemmArgs& g, long idx, in
   tm = r0; tn = 0;   // unreachable
 }
 
+// Tile sequence of a persistent CTA: round p covers tiles [p*G, (p+1)*G); even rounds hand tile p*G + b to CTA b,
+// odd rounds run backwards (p*G + G-1-b).  Tile cost falls linearly along the issue order whenever the K range is
+// triangular (Z-sweep, Z Z^T) -- with the plain stride CTA 0 would get the longest tile of EVERY round; the
+// serpentine pairs a long tile with a short one, so all CTAs finish together (Z-sweep: 28.0 -> 31+ TFLOP/s).
+__device__ __forceinline__ long gemm_seq_idx(long p) {
+  return p * gridDim.x + ((p & 1) ? (long)(gridDim.x - 1 - blockIdx.x) : (long)blockIdx.x);
+}
+
 // One work item of the persistent loop: tile coordinates, K range and operand pointers.
 struct GemmTile {
   int m0, n0, nk; bool in_diag;
@@ -139,7 +147,7 @@ struct GemmTile {
   long coff;                   // offset of the problem's C origin (batched mode), else 0
 };
 __device__ __forceinline__ bool gemm_fetch_tile(const GemmArgs& g, long idx, long ntiles, GemmTile& t) {
-  for (; idx < ntiles; idx += gridDim.x) {     // (cdiag_only filters are not used with skipping here)
+  if (idx < ntiles) {
     int tm, tn;
     if (g.nbatch > 0) {
       int lo = 0, hi = g.nbatch - 1;
@@ -169,7 +177,7 @@ __device__ __forceinline__ bool gemm_fetch_tile(const GemmArgs& g, long idx, lon
   return false;
 }
 
-// Persistent kernel: one CTA per SM walks tiles blockIdx.x, +gridDim.x, ...  The cp.async ring
+// Persistent kernel: one CTA per SM walks its serpentine tile sequence (gemm_seq_idx).  The cp.async ring
 // runs ahead ACROSS tile boundaries (the load cursor is up to 3 k-steps ahead of the compute
 // cursor), so the pipeline fill of the next tile overlaps the epilogue of the current one.
 __global__ void __launch_bounds__(GEMM_THREADS, 1) dgemm_nt_kernel(const GemmArgs g, const long ntiles) {
@@ -179,8 +187,8 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) dgemm_nt_kernel(const GemmArg
   const int gq = lane >> 2, tq = lane & 3;
 
   // --- load cursor
-  GemmTile lt; long lidx = blockIdx.x; int lkt = 0;
-  bool lvalid = gemm_fetch_tile(g, lidx, ntiles, lt);
+  GemmTile lt; long lpos = 0; int lkt = 0;
+  bool lvalid = gemm_fetch_tile(g, gemm_seq_idx(lpos), ntiles, lt);
   auto load_next = [&](int stage) {
     if (lvalid) {
       double* sA = smem + stage * GEMM_STAGE_DOUBLES;
@@ -194,7 +202,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) dgemm_nt_kernel(const GemmArg
         cp_async16(sA + so, lt.Ag + (long)row * g.lda + koff + ch * 2);
         cp_async16(sB + so, lt.Bg + (long)row * g.ldb + koff + ch * 2);
       }
-      if (++lkt == lt.nk) { lkt = 0; lidx += gridDim.x; lvalid = gemm_fetch_tile(g, lidx, ntiles, lt); }
+      if (++lkt == lt.nk) { lkt = 0; ++lpos; lvalid = gemm_fetch_tile(g, gemm_seq_idx(lpos), ntiles, lt); }
     }
     cp_async_commit();
   };
@@ -217,7 +225,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) dgemm_nt_kernel(const GemmArg
   cp_async_wait<GEMM_STAGES - 2>();
   __syncthreads();
   lds(0, smem, 0);
-  for (long cidx = blockIdx.x; gemm_fetch_tile(g, cidx, ntiles, ct); cidx += gridDim.x) {
+  for (long cpos = 0; gemm_fetch_tile(g, gemm_seq_idx(cpos), ntiles, ct); ++cpos) {
     double* Cp; long ldc; long crow0, ccol0;
     if (ct.in_diag) {
       int blk = ct.m0 / g.nb;
@@ -225,7 +233,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) dgemm_nt_kernel(const GemmArg
       crow0 = ct.m0 - blk * g.nb; ccol0 = ct.n0 - blk * g.nb;
     } else { Cp = g.C + ct.coff; ldc = g.ldc; crow0 = ct.m0; ccol0 = ct.n0; }
     const double alpha = g.alpha, beta = g.beta;
-    const bool last_tile = cidx + gridDim.x >= ntiles;
+    const bool last_tile = gemm_seq_idx(cpos + 1) >= ntiles;
     if (beta != 0.0 && g.cdiag_only) {   // pull the C tile towards L2 while the main loop runs
 #pragma unroll
       for (int i = 0; i < 4; ++i) {
