@@ -116,6 +116,24 @@ def kissgp_leg(n, device, steps, warmup):
         gp.update_data('tr', H, y[:, None])
         nl = gp.evaluate('tr'); dX = gp.get_dlik_dx('tr')
     e2e = steps / (time.perf_counter() - t0)
+    # same problem through the grid-space Woodbury preconditioner (opt.cg_precond, an extension: SURVEY a21(i)); same
+    # stopping rule, so the result is the same alpha to cg_tol -- only the iteration count changes
+    gp2 = B200GP(engine_kwargs={'device': device})
+    gp2.configure(2, {'lik': np.log(0.3), 'mean': [[0.], [0.], [0.]], 'cov': hc.copy()}, {'cg_maxit': maxit, 'cg_tol': 1e-6, 'cg_precond': 1},
+                  'infGrid', 'meanSum', 'covSM', 'likGauss', 'dlikGrid', grid_kwargs={'eq': 1, 'k': 70.}, cov_args=[6],
+                  mean_args=['{@meanLinear, @meanConst}'], verbose=0)
+    gp2.update_data('tr', H, y[:, None]); gp2.update_grid('tr')
+    for _ in range(max(1, warmup)):
+        gp2.eng.eval(0, 2, gp2._n_hyp)
+    pms = 0.0; pit = 0
+    for _ in range(steps):
+        nlZp, gpre = gp2.eng.eval(0, 2, gp2._n_hyp)
+        st = gp2.stats(); pms += st['ms_total']; pit += st['cg_iters'] - 1
+    pre = {'value': steps * 1e3 / pms, 'unit': 'evals/s', 'ms_per_eval': pms / steps, 'cg_iterations_per_eval': pit / steps,
+           'nlZ': nlZp, 'rel_diff_nlZ_vs_reference_cg': abs(nlZp - nlZ) / abs(nlZ),
+           'rel_diff_dnlZ_vs_reference_cg': float(np.max(np.abs(gpre - g)) / np.max(np.abs(g))),
+           'note': 'opt.cg_precond=1: B^-1 ~ I - s2 M F C^-1 F\' M\' with C (N x N) factored by the exact path\'s DMMA Cholesky each evaluation'}
+    del gp2
     bytes_iter = n * (16 * 2 + 88) + 32 * N
     peak = 6455.3; src = 'B200_PROFILING.md fallback'
     try:
@@ -129,7 +147,7 @@ def kissgp_leg(n, device, steps, warmup):
             'roofline': {'bound': 'hbm', 'kernel': 'cg_persistent2_kernel (whole CG solve, one cooperative launch)', 'achieved': ach, 'peak': peak,
                          'unit': 'GB/s', 'frac': ach / peak, 'bytes_per_iteration': bytes_iter, 'peak_source': src,
                          'note': 'algorithmic bytes; the working set (48 MB at n=1M) stays in L2 / shared memory, DRAM traffic per iteration is ~0 (profiles/)'},
-            'nlZ': nlZ}
+            'nlZ': nlZ, 'preconditioned': pre}
 
 
 def cpu_threads():
