@@ -150,6 +150,37 @@ def kissgp_leg(n, device, steps, warmup):
             'nlZ': nlZ, 'preconditioned': pre}
 
 
+def kissgp_sharded_leg(n_total, device, steps, warmup, world):
+    """N > 1: the same KISS-GP evaluation with the points ROW-SHARDED over the ranks (SURVEY 8(e) KISS-GP (ii)), weak
+    scaling: n_total = kissgp_n x N points.  The two reductions of every CG iteration (grid vector, four scalars)
+    cross the ranks inside the persistent kernel over peer memory (NVLink); every rank calls this."""
+    import torch
+    import torch.distributed as td
+    from kgp_b200 import B200GP, dist as kdist
+    H, y, hc = synth_c5(n_total)
+    gp = B200GP(engine_kwargs={'device': device})
+    gp.configure(2, {'lik': np.log(0.3), 'mean': [[0.], [0.], [0.]], 'cov': hc}, {'cg_maxit': 200000, 'cg_tol': 1e-6}, 'infGrid',
+                 'meanSum', 'covSM', 'likGauss', 'dlikGrid', grid_kwargs={'eq': 1, 'k': 70.}, cov_args=[6],
+                 mean_args=['{@meanLinear, @meanConst}'], verbose=0)
+    kdist.attach(gp)
+    gp.update_data('tr', H, y[:, None]); gp.update_grid('tr')
+    for _ in range(max(1, min(warmup, 2))):
+        gp.eng.eval(0, 2, gp._n_hyp)
+    ms = 0.0; cg_ms = 0.0; iters = 0
+    for _ in range(steps):
+        td.barrier(); torch.cuda.synchronize()
+        nlZ, g = gp.eng.eval(0, 2, gp._n_hyp)
+        st = gp.stats(); ms += st['ms_total']; cg_ms += st['ms_solve']; iters += st['cg_iters'] - 1
+    t = torch.tensor([ms, cg_ms], dtype=torch.float64, device='cuda')
+    td.all_reduce(t, op=td.ReduceOp.MAX)
+    ms, cg_ms = float(t[0]), float(t[1])
+    N = int(np.prod([a.size for a in gp.grid()]))
+    return {'workload': 'KISS-GP infGrid covSM(Q=6)x2 + meanSum, n=%d (= %d per GPU), 70x70 grid (N=%d), Fiedler log-det, cg_tol 1e-6' % (n_total, n_total // world, N),
+            'scaling': 'weak', 'parallelism': 'points row-sharded over %d GPUs; per CG iteration one grid-vector and one 4-scalar all-reduce inside the persistent kernel over NVLink peer memory (LL-style tagged packets), alpha all-reduced once' % world,
+            'value': steps * 1e3 / ms, 'unit': 'evals/s', 'ms_per_eval': ms / steps, 'cg_iterations_per_eval': iters / steps,
+            'cg_us_per_iteration': 1e3 * cg_ms / max(iters, 1), 'point_iterations_per_s': n_total * iters / (cg_ms * 1e-3), 'nlZ': nlZ}
+
+
 def cpu_threads():
     try:
         from threadpoolctl import threadpool_info
@@ -271,6 +302,13 @@ def main():
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     e2e_val = (1 if sharded else world) * args.steps / float(t.item())
 
+    kiss_sh = None
+    if sharded and not args.no_kissgp:
+        del gp, eng
+        gp = eng = None
+        kiss_sh = kissgp_sharded_leg(args.kissgp_n * world, local, args.steps, args.warmup, world)
+        gp = B200GP(engine_kwargs={'device': local}); eng = gp.eng          # (for the peak micro-benchmark below)
+
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
@@ -303,7 +341,7 @@ def main():
                 'launches_per_step': gemm_l / args.steps, 'share_of_step': gemm_ms / dev_ms if dev_ms else None,
                 'whole_eval_tflops': gemm_fl / (dev_ms * 1e-3) / 1e12}
 
-    kiss = None
+    kiss = kiss_sh
     if world == 1 and not args.no_kissgp:
         del gp, eng
         kiss = kissgp_leg(args.kissgp_n, local, args.steps, args.warmup)

@@ -70,6 +70,10 @@ struct kgp_ctx {
   cudaStream_t stream_p = nullptr;                    // panel stream: factorisation of the next panel + its broadcast
   cudaEvent_t dev_ev[8];                              // panel ready [2], panel buffer free [2], look-ahead column updated
   kgp::DevBuf PB[2];                                  // packed panels (rows x NB)
+  // peer exchange window of the row-sharded KISS-GP CG (grid_cg.cuh, CgDist): one cudaMalloc per rank, mapped into
+  // every peer with CUDA IPC; px_epoch = tag of the last exchange (monotone over all solves, equal on all ranks)
+  void* px_local = nullptr; void* px_peer[8] = {nullptr}; bool px_ok = false; unsigned long long px_epoch = 0;
+  int* px_abort = nullptr;
   double dist_ms_comm = 0.0;
   // grid-path state lives in grid.cu (opaque)
   void* gridstate = nullptr;

@@ -161,6 +161,38 @@ int dist_init(kgp_ctx* c, int nranks, int rank, const char* id128, const char* l
   KGP_CUDA(c, cudaSetDevice(c->device));
   KGP_NCCL(c, api, api.CommInitRank(&c->nccl_comm, nranks, id, rank));
   c->nranks = nranks; c->rank = rank;
+  // peer window for the row-sharded KISS-GP CG: allocate, exchange the IPC handles over the new communicator, map
+  c->px_ok = false;
+  if (nranks <= 8 && !(getenv("KGP_DIST_CG") && atoi(getenv("KGP_DIST_CG")) == 0)) {
+    cudaIpcMemHandle_t mine; char* hdev = nullptr; std::vector<cudaIpcMemHandle_t> all(nranks);
+    bool ok = cudaMalloc(&c->px_local, PX_BYTES) == cudaSuccess && cudaMemset(c->px_local, 0, PX_BYTES) == cudaSuccess &&
+              cudaMalloc((void**)&c->px_abort, 64) == cudaSuccess && cudaMemset(c->px_abort, 0, 64) == cudaSuccess &&
+              cudaIpcGetMemHandle(&mine, c->px_local) == cudaSuccess &&
+              cudaMalloc((void**)&hdev, (size_t)nranks * sizeof(mine)) == cudaSuccess;
+    if (ok) {
+      cudaMemcpy(hdev + (size_t)rank * sizeof(mine), &mine, sizeof(mine), cudaMemcpyHostToDevice);
+      for (int r = 0; r < nranks && ok; ++r)
+        ok = api.Broadcast(hdev + (size_t)r * sizeof(mine), hdev + (size_t)r * sizeof(mine), sizeof(mine), KGP_NCCL_INT8, r, c->nccl_comm, c->stream) == 0;
+      ok = ok && cudaStreamSynchronize(c->stream) == cudaSuccess &&
+           cudaMemcpy(all.data(), hdev, (size_t)nranks * sizeof(mine), cudaMemcpyDeviceToHost) == cudaSuccess;
+      for (int r = 0; r < nranks && ok; ++r) {
+        if (r == rank) { c->px_peer[r] = c->px_local; continue; }
+        ok = cudaIpcOpenMemHandle(&c->px_peer[r], all[r], cudaIpcMemLazyEnablePeerAccess) == cudaSuccess;
+      }
+    }
+    if (hdev) cudaFree(hdev);
+    if (!ok) { cudaGetLastError(); if (getenv("KGP_DEBUG")) fprintf(stderr, "[kgp] rank %d: peer window unavailable, KISS-GP CG stays replicated\n", rank); }
+    // every rank must agree: all-reduce the flag
+    double* flag = nullptr; double hv = ok ? 1.0 : 0.0;
+    if (cudaMalloc((void**)&flag, 8) == cudaSuccess) {
+      cudaMemcpy(flag, &hv, 8, cudaMemcpyHostToDevice);
+      api.AllReduce(flag, flag, 1, KGP_NCCL_DOUBLE, KGP_NCCL_SUM, c->nccl_comm, c->stream);
+      cudaStreamSynchronize(c->stream);
+      cudaMemcpy(&hv, flag, 8, cudaMemcpyDeviceToHost); cudaFree(flag);
+      c->px_ok = hv > (double)nranks - 0.5;
+    }
+    c->px_epoch = 0;
+  }
   if (!c->stream_p) {
     int lo = 0, hi = 0; cudaDeviceGetStreamPriorityRange(&lo, &hi);
     KGP_CUDA(c, cudaStreamCreateWithPriority(&c->stream_p, cudaStreamNonBlocking, hi));
@@ -172,6 +204,10 @@ void dist_free(kgp_ctx* c) {
   if (c->nccl_comm) { NcclApi& api = nccl_api(nullptr); if (api.ok) api.CommDestroy(c->nccl_comm); c->nccl_comm = nullptr; }
   if (c->stream_p) { cudaStreamDestroy(c->stream_p); for (int i = 0; i < 8; ++i) cudaEventDestroy(c->dev_ev[i]); c->stream_p = nullptr; }
   c->PB[0].release(); c->PB[1].release();
+  for (int r = 0; r < 8; ++r) { if (c->px_peer[r] && c->px_peer[r] != c->px_local) cudaIpcCloseMemHandle(c->px_peer[r]); c->px_peer[r] = nullptr; }
+  if (c->px_local) { cudaFree(c->px_local); c->px_local = nullptr; }
+  if (c->px_abort) { cudaFree(c->px_abort); c->px_abort = nullptr; }
+  c->px_ok = false;
 }
 
 // Cholesky with block columns dealt cyclically over the ranks, panel broadcast, look-ahead 1

@@ -36,6 +36,12 @@ struct GridState {
   // cached posterior
   unsigned long st_slot_ver = 0, st_model_ver = 0, st_grid_ver = 0; int st_slot = -1, st_level = -1;
   double prior_var = 0.0;
+  // row-sharded CG (several ranks): the sorted set of THIS rank's rows lives in alt while the full-data set is
+  // active and vice versa (swap_sorted); sub_n < 0 = the active set covers all rows of the slot
+  struct SortedSet { DevBuf U, perm; long npad = 0; int sort_slot = -1; unsigned long sort_slot_ver = 0, sort_grid_ver = 0;
+                     int wmax = 0, wmax_ctas = 0, wmax_slot = -1; unsigned long wmax_slot_ver = 0, wmax_grid_ver = 0;
+                     long sub_lo = 0, sub_n = -1; } alt;
+  long sub_lo = 0, sub_n = -1;
   // explained variance on the grid (opt.pred_var; infGrid.m:91-101)
   DevBuf vg, pvA, pvS, pvG; bool eig_ok = false, vg_nonzero = false;
   unsigned long vg_slot_ver = 0, vg_model_ver = 0, vg_grid_ver = 0; int vg_slot = -1;
@@ -53,13 +59,21 @@ void grid_free(kgp_ctx* c) {
                     &g->hypm, &g->dX, &g->dhyp, &g->out, &g->sortk, &g->sorti, &g->keep, &g->dmean,
                     &g->U, &g->perm, &g->sx, &g->sr, &g->sd, &g->sz, &g->ctl, &g->cnt, &g->KfT, &g->gm0, &g->gm1, &g->pdz, &g->prr, &g->bar, &g->part4, &g->g0b, &g->wmaxd,
                     &g->Gm, &g->Ht1, &g->Ht2, &g->VT, &g->se, &g->ps, &g->pw, &g->probes, &g->chT, &g->chU, &g->chY, &g->chS, &g->chC, &g->chP, &g->bva, &g->bvb, &g->bvc, &g->lzQ, &g->lzP, &g->lzH, &g->chacc,
-                    &g->vg, &g->pvA, &g->pvS, &g->pvG};
+                    &g->vg, &g->pvA, &g->pvS, &g->pvG, &g->alt.U, &g->alt.perm};
   for (DevBuf* b : bufs) b->release();
   if (g->h_ctl) cudaFreeHost(g->h_ctl);
   if (g->cg_graph) cudaGraphExecDestroy(g->cg_graph);
   delete g; c->gridstate = nullptr;
 }
 
+static void swap_sorted(GridState* g) {
+  GridState::SortedSet& a = g->alt;
+  std::swap(g->U, a.U); std::swap(g->perm, a.perm); std::swap(g->npad, a.npad);
+  std::swap(g->sort_slot, a.sort_slot); std::swap(g->sort_slot_ver, a.sort_slot_ver); std::swap(g->sort_grid_ver, a.sort_grid_ver);
+  std::swap(g->wmax, a.wmax); std::swap(g->wmax_ctas, a.wmax_ctas); std::swap(g->wmax_slot, a.wmax_slot);
+  std::swap(g->wmax_slot_ver, a.wmax_slot_ver); std::swap(g->wmax_grid_ver, a.wmax_grid_ver);
+  std::swap(g->sub_lo, a.sub_lo); std::swap(g->sub_n, a.sub_n);
+}
 static int nblocks_for(long n) { long b = (n + 255) / 256; return (int)std::min<long>(std::max<long>(b, 1), 1184); }
 
 // upload axes, fill the descriptor
@@ -191,22 +205,23 @@ constexpr int CG_CHECK = 16;              // iterations per graph launch (the ho
 static int cg_prepare_sorted(kgp_ctx* c, GridState* g, const GridDesc& G, int slot) {
   Slot& S = c->slots[slot];
   if (g->sort_slot == slot && g->sort_slot_ver == S.version && g->sort_grid_ver == c->grid.version && g->npad > 0) return KGP_OK;
-  const long n = S.n; const int D = S.D;
+  const long n = g->sub_n >= 0 ? g->sub_n : S.n; const int D = S.D;
+  const double* Xs = S.X.d() + (g->sub_n >= 0 ? g->sub_lo * D : 0);          // rows of this rank (row-sharded solve)
   cudaStream_t st = c->stream;
   const long npad = ((n + CG_SUB - 1) / CG_SUB) * CG_SUB;
   long Npad = 1; while (Npad < n) Npad <<= 1;
   KGP_CUDA(c, g->sortk.ensure(Npad * 8)); KGP_CUDA(c, g->sorti.ensure(Npad * 4));
   KGP_CUDA(c, g->perm.ensure(n * 4)); KGP_CUDA(c, g->U.ensure(npad * G.p * 8));
   const unsigned nb = (unsigned)((Npad + 255) / 256);
-  if (G.p == 1) cg_cellkey_kernel<1><<<nb, 256, 0, st>>>(G, S.X.d(), n, D, g->sortk.d(), (int*)g->sorti.p, Npad);
-  else cg_cellkey_kernel<2><<<nb, 256, 0, st>>>(G, S.X.d(), n, D, g->sortk.d(), (int*)g->sorti.p, Npad);
+  if (G.p == 1) cg_cellkey_kernel<1><<<nb, 256, 0, st>>>(G, Xs, n, D, g->sortk.d(), (int*)g->sorti.p, Npad);
+  else cg_cellkey_kernel<2><<<nb, 256, 0, st>>>(G, Xs, n, D, g->sortk.d(), (int*)g->sorti.p, Npad);
   for (long k = 2; k <= Npad; k <<= 1)
     for (long j = k >> 1; j > 0; j >>= 1)
       bitonic_stage_kernel<<<nb, 256, 0, st>>>(g->sortk.d(), (int*)g->sorti.p, Npad, j, k);
   KGP_CUDA(c, cudaMemcpyAsync(g->perm.p, g->sorti.p, n * 4, cudaMemcpyDeviceToDevice, st));
   const unsigned nb2 = (unsigned)((npad + 255) / 256);
-  if (G.p == 1) cg_sorted_coords_kernel<1><<<nb2, 256, 0, st>>>(G, S.X.d(), n, D, (const int*)g->perm.p, npad, g->U.d());
-  else cg_sorted_coords_kernel<2><<<nb2, 256, 0, st>>>(G, S.X.d(), n, D, (const int*)g->perm.p, npad, g->U.d());
+  if (G.p == 1) cg_sorted_coords_kernel<1><<<nb2, 256, 0, st>>>(G, Xs, n, D, (const int*)g->perm.p, npad, g->U.d());
+  else cg_sorted_coords_kernel<2><<<nb2, 256, 0, st>>>(G, Xs, n, D, (const int*)g->perm.p, npad, g->U.d());
   KGP_CUDA(c, cudaGetLastError());
   g->npad = npad; g->sort_slot = slot; g->sort_slot_ver = S.version; g->sort_grid_ver = c->grid.version;
   return KGP_OK;
@@ -310,15 +325,16 @@ static int cg_run_persistent(kgp_ctx* c, GridState* g, const CgLaunch& L, int ma
   return cg_finish(c, g, L.m);
 }
 
-template <int P, int LEVEL, bool DBG>
+template <int P, int LEVEL, bool DBG, bool DIST = false>
 static cudaError_t launch_persistent2b(const CgPersist2& A, int ctas, size_t smem, cudaStream_t st) {
-  cudaError_t e = cudaFuncSetAttribute(cg_persistent2_kernel<P, LEVEL, DBG>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  cudaError_t e = cudaFuncSetAttribute(cg_persistent2_kernel<P, LEVEL, DBG, DIST>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return e;
   void* args[] = {(void*)&A};
-  return cudaLaunchCooperativeKernel((const void*)cg_persistent2_kernel<P, LEVEL, DBG>, dim3((unsigned)ctas), dim3(CGP2_THREADS), args, smem, st);
+  return cudaLaunchCooperativeKernel((const void*)cg_persistent2_kernel<P, LEVEL, DBG, DIST>, dim3((unsigned)ctas), dim3(CGP2_THREADS), args, smem, st);
 }
 template <int P, int LEVEL>
 static cudaError_t launch_persistent2(const CgPersist2& A, int ctas, size_t smem, cudaStream_t st) {
+  if (A.X.nranks > 1) return A.dbg ? launch_persistent2b<P, LEVEL, true, true>(A, ctas, smem, st) : launch_persistent2b<P, LEVEL, false, true>(A, ctas, smem, st);
   return A.dbg ? launch_persistent2b<P, LEVEL, true>(A, ctas, smem, st) : launch_persistent2b<P, LEVEL, false>(A, ctas, smem, st);
 }
 // two-barrier formulation (cg_persistent2_kernel); -1 when it does not fit (node window / staging too large)
@@ -372,6 +388,12 @@ static int cg_run_persistent2(kgp_ctx* c, GridState* g, const CgLaunch& L, int s
   A.K0 = L.Kf; A.K0T = L.KfT; A.K1 = L.Kf + L.koff1;
   A.ctl = L.ctl; A.part = g->part4.d(); A.bar = (unsigned*)g->bar.p; A.stg_doubles = stg_need;
   A.dbg = getenv("KGP_DEBUG") ? (long long*)((char*)g->bar.p + 128) : nullptr;
+  if (g->sub_n >= 0) {
+    if (!c->px_ok || G.N > PX_NCAP || L.m != 1) return c->fail(KGP_BAD_ARG, "row-sharded CG needs the peer window, N <= %ld, one right-hand side", PX_NCAP);
+    A.X.nranks = c->nranks; A.X.rank = c->rank; A.X.epoch = c->px_epoch; A.X.ncap = PX_NCAP; A.X.loc = (char*)c->px_local;
+    for (int r = 0; r < c->nranks; ++r) A.X.peer[r] = (char*)c->px_peer[r];
+    A.X.abort = c->px_abort;
+  }
   cudaError_t e;
   if (G.p == 1) e = level == 2 ? launch_persistent2<1, 2>(A, ctas, smem, st) : level == 1 ? launch_persistent2<1, 1>(A, ctas, smem, st) : launch_persistent2<1, 0>(A, ctas, smem, st);
   else e = level == 2 ? launch_persistent2<2, 2>(A, ctas, smem, st) : level == 1 ? launch_persistent2<2, 1>(A, ctas, smem, st) : launch_persistent2<2, 0>(A, ctas, smem, st);
@@ -381,6 +403,7 @@ static int cg_run_persistent2(kgp_ctx* c, GridState* g, const CgLaunch& L, int s
   KGP_CUDA(c, cudaMemcpyAsync(g->h_ctl, g->ctl.p, (size_t)L.m * CT_STRIDE * 8, cudaMemcpyDeviceToHost, st));
   KGP_CUDA(c, cudaStreamSynchronize(st));
   KGP_CUDA(c, cudaGetLastError());
+  if (g->sub_n >= 0) c->px_epoch += (unsigned long long)g->h_ctl[CT_PASSES];
   if (A.dbg) {
     long long tk[8]; cudaMemcpy(tk, A.dbg, sizeof tk, cudaMemcpyDeviceToHost);
     const double it = std::max(1.0, g->h_ctl[CT_ITER] - 1.0), f = 1e-3 / 1.965 / it;
@@ -396,7 +419,9 @@ static int cg_solve_sorted(kgp_ctx* c, GridState* g, const GridDesc& G, int slot
   if (m < 1 || m > CG_MAXCOLS) return c->fail(KGP_BAD_ARG, "CG batch of %d columns (max %d)", m, CG_MAXCOLS);
   int rc = cg_prepare_sorted(c, g, G, slot); if (rc) return rc;
   Slot& S = c->slots[slot];
-  const long n = S.n, npad = g->npad;
+  const bool sharded = g->sub_n >= 0;
+  const long n = sharded ? g->sub_n : S.n, npad = g->npad;
+  if (sharded) { rhs += g->sub_lo; if (m != 1) return c->fail(KGP_BAD_ARG, "row-sharded CG handles one right-hand side"); }
   cudaStream_t st = c->stream;
   DevBuf* vecs[] = {&g->sx, &g->sr, &g->sd, &g->sz};
   for (DevBuf* b : vecs) KGP_CUDA(c, b->ensure((size_t)m * npad * 8));
@@ -416,6 +441,14 @@ static int cg_solve_sorted(kgp_ctx* c, GridState* g, const GridDesc& G, int slot
   cg_init_sorted_kernel<<<dim3((unsigned)std::min<long>(npad / 256, 1184), (unsigned)m), 256, 0, st>>>(
       rhs, rhs_stride, (const int*)g->perm.p, n, npad, sw, tol, maxit, L.sx, L.sr, L.sd, L.ctl, L.cnt);
   c->stats.kernel_launches += 1;
+  if (sharded) {                                               // |b|^2 over all ranks (also the per-solve rendezvous)
+    NcclApi& api = nccl_api(nullptr);
+    KGP_NCCL(c, api, api.AllReduce(L.ctl + CT_RRCUR, L.ctl + CT_RRCUR, 1, KGP_NCCL_DOUBLE, KGP_NCCL_SUM, c->nccl_comm, st));
+    cg_dist_fix_ctl_kernel<<<1, 1, 0, st>>>(L.ctl);
+    rc = cg_run_persistent2(c, g, L, slot);
+    if (rc == -1) return c->fail(KGP_BAD_ARG, "row-sharded CG: the persistent kernel does not fit this grid");
+    return rc;
+  }
 
   static const int cg_mode = getenv("KGP_CG_MODE") ? atoi(getenv("KGP_CG_MODE")) : 3;     // 3 persistent two-barrier, 2 persistent four-phase, 1 streaming kernels
   if (cg_mode >= 3) {
@@ -958,6 +991,21 @@ int grid_eval(kgp_ctx* c, int slot, int want, double* nlZ_out, double* dnlZ_out)
   if (m.opt.cg_precond) {
     rc = pcg_solve(c, g, G, slot, sw, m.opt.cg_tol, maxit, g->ym.d(), g->x.d(), true);
     if (rc) return rc;
+  } else if (G.p <= 2 && !legacy_cg && c->nranks > 1 && c->px_ok && G.N <= PX_NCAP && n >= 4096L * c->nranks) {
+    // row-sharded solve (SURVEY 8(e) KISS-GP (ii)): this rank's contiguous share of the points, the two reductions
+    // of every iteration cross the ranks over peer memory inside the persistent kernel
+    const long lo = n * c->rank / c->nranks, hi = n * (c->rank + 1) / c->nranks;
+    swap_sorted(g);
+    if (g->sub_lo != lo || g->sub_n != hi - lo) { g->sub_lo = lo; g->sub_n = hi - lo; g->sort_slot = -1; }
+    rc = cg_solve_sorted(c, g, G, slot, g->ym.d(), n, 1, sw, m.opt.cg_tol, maxit);
+    if (!rc) {
+      KGP_CUDA(c, cudaMemsetAsync(g->x.p, 0, n * 8, st));
+      cg_unsort_kernel<<<(unsigned)((hi - lo + 255) / 256), 256, 0, st>>>(g->sx.d(), (const int*)g->perm.p, hi - lo, sw, g->x.d() + lo);
+    }
+    swap_sorted(g);
+    if (rc) return rc;
+    NcclApi& api = nccl_api(nullptr);
+    KGP_NCCL(c, api, api.AllReduce(g->x.p, g->x.p, (size_t)n, KGP_NCCL_DOUBLE, KGP_NCCL_SUM, c->nccl_comm, st));
   } else if (G.p <= 2 && !legacy_cg) {
     rc = cg_solve_sorted(c, g, G, slot, g->ym.d(), n, 1, sw, m.opt.cg_tol, maxit);
     if (rc) return rc;

@@ -24,7 +24,7 @@
 
 namespace kgp {
 
-enum { CT_A = 0, CT_BETA, CT_DONE, CT_ITER, CT_RELRES, CT_NB, CT_RRCUR, CT_ACC_RR, CT_ACC_DZ, CT_TOL, CT_MAXIT, CT_SW,
+enum { CT_A = 0, CT_BETA, CT_DONE, CT_ITER, CT_RELRES, CT_NB, CT_RRCUR, CT_ACC_RR, CT_ACC_DZ, CT_TOL, CT_MAXIT, CT_SW, CT_PASSES,
        CT_STRIDE = 16 };
 constexpr int CG_PTS = 4;                     // consecutive sorted points per thread
 constexpr int CG_SUB = 256 * CG_PTS;          // points per CTA pass
@@ -754,7 +754,117 @@ __global__ void __launch_bounds__(CGP_THREADS, 1) cg_persistent_kernel(const CgP
 // range in a bank-conflict-free [double2][lane] layout, the node window, and one staging region (aliased onto z
 // at LEVEL 2) used in turn for the scatter's segmented reduction, g0 and the first-axis factor.
 // ======================================================================================================
+// Row-sharded solve over several GPUs (SURVEY 8(e) KISS-GP (ii)): every rank owns n/P of the points and the whole grid.
+// The two reductions of a CG iteration cross the ranks INSIDE the persistent kernel, over peer memory (NVLink), as a
+// one-shot all-reduce in the style of NCCL's LL protocol: every FP64 value travels as two 8-byte words
+// {32 data bits, 32-bit tag}; an 8-byte store is atomic, so a word whose tag matches carries valid data and no fence,
+// flag or second round trip is needed -- the receiver polls the data itself.
+//   after the scatter:  CTA j stores this rank's partial grid vector (N values) into peer rank+1+j's window;
+//                       the staging step of phase C sums the P partials in rank order (identical on all ranks);
+//   after phase C:      CTA 0 stores the 4 partial sums into every peer's window; every CTA sums them in rank order.
+// All ranks therefore take bit-identical decisions and leave the loop in the same pass.  Tags (epoch + pass) grow
+// monotonically over all solves and the windows are double-buffered by pass parity; the all-reduce of |b|^2 at the
+// start of every solve keeps any rank from running a whole solve ahead.
+struct CgDist {
+  int nranks, rank; unsigned long long epoch; long ncap;
+  char* loc; char* peer[8]; int* abort;
+};
+// window layout (16-byte packets): grid partials [2][8][ncap], scalars [2][8][4], locally combined grid vector [2][ncap]
+constexpr int DX_NPUSH = 4;        // CTAs that share the push of one peer's copy
+constexpr int DX_NCOMB = 16;       // CTAs (from the top of the grid) that sum the P partials of a slice
+__device__ __forceinline__ ulonglong2* dx_rx(char* base, long ncap, int par, int r) { return (ulonglong2*)base + ((long)par * 8 + r) * ncap; }
+__device__ __forceinline__ ulonglong2* dx_sc(char* base, long ncap, int par, int r) { return (ulonglong2*)base + 16 * ncap + (par * 8 + r) * 4; }
+__device__ __forceinline__ ulonglong2* dx_gc(char* base, long ncap, int par) { return (ulonglong2*)base + 16 * ncap + 64 + (long)par * ncap; }
+__device__ __forceinline__ void dx_put(ulonglong2* dst, double v, unsigned tag) {
+  const unsigned long long b = (unsigned long long)__double_as_longlong(v), t = (unsigned long long)tag << 32;
+  ulonglong2 w; w.x = t | (b & 0xffffffffULL); w.y = t | (b >> 32);
+  asm volatile("st.volatile.global.v2.u64 [%0], {%1, %2};" ::"l"(dst), "l"(w.x), "l"(w.y) : "memory");
+}
+// poll one packet until both halves carry `tag`; a peer that never arrives traps the kernel after ~4 s instead of
+// hanging the GPU
+// ---- exchange helpers, kept out of line so their registers do not add to the persistent kernel's budget -------
+__device__ __forceinline__ bool dx_ok(unsigned long long x, unsigned long long y, unsigned tag) {
+  return (unsigned)(x >> 32) == tag && (unsigned)(y >> 32) == tag;
+}
+__device__ __forceinline__ void dx_ld(const ulonglong2* p, unsigned long long& x, unsigned long long& y) {
+  asm volatile("ld.volatile.global.v2.u64 {%0, %1}, [%2];" : "=l"(x), "=l"(y) : "l"(p) : "memory");
+}
+__device__ __forceinline__ double dx_val(unsigned long long x, unsigned long long y) {
+  return __longlong_as_double((long long)((x & 0xffffffffULL) | (y << 32)));
+}
+// re-poll one packet until it carries `tag` (x, y hold the first attempt)
+__device__ __forceinline__ double dx_finish(const ulonglong2* p, unsigned long long x, unsigned long long y, unsigned tag) {
+  long long t0 = 0; bool timing = false;
+  while (!dx_ok(x, y, tag)) {
+    if (!timing) { t0 = clock64(); timing = true; }
+    else if (clock64() - t0 > (1LL << 33)) __trap();
+    dx_ld(p, x, y);
+  }
+  return dx_val(x, y);
+}
+// dst[q] = packet(src[q]) for q in [q0, q1): four loads in flight, then four 16-byte stores
+__device__ __noinline__ void dx_push_slice(const double* __restrict__ src, ulonglong2* dst, long q0, long q1, unsigned tag, int tid, int nthreads) {
+  for (long qb = q0 + tid; qb < q1; qb += 4L * nthreads) {
+    double v[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) { const long q = qb + (long)k * nthreads; v[k] = (q < q1) ? __ldcg(src + q) : 0.0; }
+#pragma unroll
+    for (int k = 0; k < 4; ++k) { const long q = qb + (long)k * nthreads; if (q < q1) dx_put(dst + q, v[k], tag); }
+  }
+}
+// out[q] = own[q] (+) pk[q] summed in rank order for q in [0, N); one peer (two ranks): no combiner stage
+__device__ __noinline__ void dx_stage_pair(const double* __restrict__ own, const ulonglong2* pk, bool own_first, double* out, long N, unsigned tag,
+                                          int tid, int nthreads) {
+  for (long qb = tid; qb < N; qb += 4L * nthreads) {
+    unsigned long long x[4], y[4]; double o[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) { const long q = qb + (long)k * nthreads; if (q < N) { dx_ld(pk + q, x[k], y[k]); o[k] = __ldcg(own + q); } }
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const long q = qb + (long)k * nthreads;
+      if (q < N) { const double pv = dx_finish(pk + q, x[k], y[k], tag); out[q] = own_first ? o[k] + pv : pv + o[k]; }
+    }
+  }
+}
+// out[q] = value of packet pk[q] for q in [0, N)
+__device__ __noinline__ void dx_stage_packets(const ulonglong2* pk, double* out, long N, unsigned tag, int tid, int nthreads) {
+  for (long qb = tid; qb < N; qb += 4L * nthreads) {
+    unsigned long long x[4], y[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) { const long q = qb + (long)k * nthreads; if (q < N) dx_ld(pk + q, x[k], y[k]); }
+#pragma unroll
+    for (int k = 0; k < 4; ++k) { const long q = qb + (long)k * nthreads; if (q < N) out[q] = dx_finish(pk + q, x[k], y[k], tag); }
+  }
+}
+// gc[q] = packet(sum over ranks, rank order) for q in [q0, q1): polls the peers' packets of the slice
+__device__ __noinline__ void dx_combine_slice(const double* __restrict__ own, char* loc, long ncap, int par, int nranks, int rank, long q0, long q1,
+                                             unsigned tag, int tid, int nthreads) {
+  ulonglong2* gc = (ulonglong2*)loc + 16 * ncap + 64 + (long)par * ncap;
+  for (long q = q0 + tid; q < q1; q += nthreads) {
+    unsigned long long x[8], y[8];
+#pragma unroll
+    for (int rk = 0; rk < 8; ++rk) if (rk < nranks && rk != rank) dx_ld((const ulonglong2*)loc + ((long)par * 8 + rk) * ncap + q, x[rk], y[rk]);
+    const double o = __ldcg(own + q);
+    double sacc = 0.0;
+#pragma unroll
+    for (int rk = 0; rk < 8; ++rk)
+      if (rk < nranks) sacc += (rk == rank) ? o : dx_finish((const ulonglong2*)loc + ((long)par * 8 + rk) * ncap + q, x[rk], y[rk], tag);
+    dx_put(gc + q, sacc, tag);
+  }
+}
+__device__ __forceinline__ double dx_get(const ulonglong2* src, unsigned tag) {
+  unsigned long long x, y; long long t0 = 0; bool timing = false;
+  while (true) {
+    asm volatile("ld.volatile.global.v2.u64 {%0, %1}, [%2];" : "=l"(x), "=l"(y) : "l"(src) : "memory");
+    if ((unsigned)(x >> 32) == tag && (unsigned)(y >> 32) == tag) break;
+    if (!timing) { t0 = clock64(); timing = true; }
+    else if (clock64() - t0 > (1LL << 33)) __trap();
+  }
+  return __longlong_as_double((long long)((x & 0xffffffffULL) | (y << 32)));
+}
+
 struct CgPersist2 {
+  CgDist X;
   GridDesc G;
   const double* U; long n, npad; int m, upc, wcap;     // wcap = node rows the window buffer can hold
   double *x, *r, *d, *z;                               // [m][npad], sorted order
@@ -790,7 +900,7 @@ __global__ void cg_window_kernel(GridDesc G, const double* __restrict__ U, long 
 #else
 #define KGP_CGP2_BOUNDS __launch_bounds__(CGP2_THREADS, 1)
 #endif
-template <int P, int LEVEL, bool DBG>
+template <int P, int LEVEL, bool DBG, bool DIST>
 __global__ void KGP_CGP2_BOUNDS cg_persistent2_kernel(const CgPersist2 A) {
   constexpr int NW = CgNodes<P>::NW;
   constexpr int VPP = (P == 1) ? 4 : CGP_VPP, NPASS = NW / VPP;
@@ -848,11 +958,13 @@ __global__ void KGP_CGP2_BOUNDS cg_persistent2_kernel(const CgPersist2 A) {
 #define CGP2_TICK(slot) do { if (DBG && cta == 0 && tid == 0) { long long t1 = clock64(); tk[slot] += t1 - t0; t0 = t1; } } while (0)
   if (DBG && cta == 0 && tid == 0) t0 = clock64();
   int par = 0;
+  unsigned long long pass = 0;
 
   while (true) {
     if (tid == 0) { int any = 0; for (int c = 0; c < m; ++c) any |= (s_state[c] == 0 || s_state[c] == 3); s_any = any; }
     __syncthreads();
     if (!s_any) break;
+    ++pass;
     double* g0w = par ? A.g0b : A.g0a;                 // scattered into now, read in C
     double* g0z = par ? A.g0a : A.g0b;                 // read in the previous C: zeroed in this C
     // ---- F1: x += a d ; r -= a z ; |r|^2 ; d = r + beta d     (streams x and r; z is dead afterwards)
@@ -1000,13 +1112,34 @@ __global__ void KGP_CGP2_BOUNDS cg_persistent2_kernel(const CgPersist2 A) {
     }
     CGP2_TICK(0);
     grid_barrier(A.bar, phase);
+    if (DIST) {
+      const unsigned tag = (unsigned)(A.X.epoch + pass);
+      // (a) push: CTA (j, s), counted from the TOP of the grid (the last CTAs own the fewest points and reach the
+      //     barrier first), stores slice s of this rank's partial grid vector into peer rank+1+j's window
+      const int npush = (A.X.nranks - 1) * DX_NPUSH, rcta = nctas - 1 - cta;
+      if (rcta < npush) {
+        const int pr = (A.X.rank + 1 + rcta / DX_NPUSH) % A.X.nranks, sl = rcta % DX_NPUSH;
+        const long per = (G.N + DX_NPUSH - 1) / DX_NPUSH, q0 = sl * per, q1 = (q0 + per < G.N) ? q0 + per : G.N;
+        dx_push_slice(g0w, dx_rx(A.X.peer[pr], A.X.ncap, par, A.X.rank), q0, q1, tag, tid, CGP2_THREADS);
+      }
+      // (b) more than two ranks: the last DX_NCOMB CTAs sum the P partials of their slice in rank order (polling the
+      //     peers' packets) and publish the result as packets in the LOCAL window -- no second grid barrier
+      if (A.X.nranks > 2 && rcta >= npush && rcta < npush + DX_NCOMB) {
+        const int sl = rcta - npush;
+        const long per = (G.N + DX_NCOMB - 1) / DX_NCOMB, q0 = sl * per, q1 = (q0 + per < G.N) ? q0 + per : G.N;
+        dx_combine_slice(g0w, A.X.loc, A.X.ncap, par, A.X.nranks, A.X.rank, q0, q1, tag, tid, CGP2_THREADS);
+      }
+    }
     CGP2_TICK(1);
     // ---- C: node window of u = Kg g0, then z = sw Mx u + d and the three dot products
     for (int col = 0; col < m; ++col) {
       if (s_state[col] != 0) continue;
       const double* T = g0w + (long)col * G.N;
       if (P == 1) {
-        for (int q = tid; q < ng0; q += CGP2_THREADS) stg[q] = __ldcg(T + q);
+        if (DIST) {
+          if (A.X.nranks == 2) dx_stage_pair(T, dx_rx(A.X.loc, A.X.ncap, par, 1 - A.X.rank), A.X.rank == 0, stg, ng0, (unsigned)(A.X.epoch + pass), tid, CGP2_THREADS);
+          else dx_stage_packets(dx_gc(A.X.loc, A.X.ncap, par), stg, ng0, (unsigned)(A.X.epoch + pass), tid, CGP2_THREADS);
+        } else for (int q = tid; q < ng0; q += CGP2_THREADS) stg[q] = __ldcg(T + q);
         __syncthreads();
         for (int a2 = warp; a2 < wr; a2 += nwarp) {
           double acc2 = 0.0;
@@ -1019,8 +1152,13 @@ __global__ void KGP_CGP2_BOUNDS cg_persistent2_kernel(const CgPersist2 A) {
         const int ng1 = G.ng[1];
         const long tb = (G.N > (long)ng0 * ng0) ? G.N : (long)ng0 * ng0;
         double* sT = stg; double* sK1 = stg + ((tb + 1) & ~1L); double* sW = sK1 + (((long)A.wcap * ng1 + 1) & ~1L);
-        for (long q = tid; q < G.N / 2; q += CGP2_THREADS) cp_async16(sT + 2 * q, T + 2 * q);
-        if ((G.N & 1) && tid == 0) sT[G.N - 1] = __ldcg(T + G.N - 1);
+        if (DIST) {                                                    // the combined grid vector
+          if (A.X.nranks == 2) dx_stage_pair(T, dx_rx(A.X.loc, A.X.ncap, par, 1 - A.X.rank), A.X.rank == 0, sT, G.N, (unsigned)(A.X.epoch + pass), tid, CGP2_THREADS);
+          else dx_stage_packets(dx_gc(A.X.loc, A.X.ncap, par), sT, G.N, (unsigned)(A.X.epoch + pass), tid, CGP2_THREADS);
+        } else {
+          for (long q = tid; q < G.N / 2; q += CGP2_THREADS) cp_async16(sT + 2 * q, T + 2 * q);
+          if ((G.N & 1) && tid == 0) sT[G.N - 1] = __ldcg(T + G.N - 1);
+        }
         for (int q = tid; q < wr * ng1; q += CGP2_THREADS) sK1[q] = A.K1[(long)rlo * ng1 + q];
         cp_async_wait_all();
         __syncthreads();
@@ -1122,6 +1260,20 @@ __global__ void KGP_CGP2_BOUNDS cg_persistent2_kernel(const CgPersist2 A) {
       if (lane == 0) s_sum[w][col] = acc2;
     }
     __syncthreads();
+    if (DIST) {                                                // the four sums cross the ranks (m == 1)
+      const unsigned tag = (unsigned)(A.X.epoch + pass);
+      if (cta == 0 && tid < 4 * A.X.nranks) {
+        const int pr = tid >> 2, w = tid & 3;
+        if (pr != A.X.rank) dx_put(dx_sc(A.X.peer[pr], A.X.ncap, par, A.X.rank) + w, s_sum[w][0], tag);
+      }
+      __syncthreads();
+      if (tid < 4) {
+        double tot = 0.0;
+        for (int rk = 0; rk < A.X.nranks; ++rk) tot += (rk == A.X.rank) ? s_sum[tid][0] : dx_get(dx_sc(A.X.loc, A.X.ncap, par, rk) + tid, tag);
+        s_sum[tid][0] = tot;
+      }
+      __syncthreads();
+    }
     for (int col = tid; col < m; col += CGP2_THREADS) {
       const int state = s_state[col];
       if (state != 0 && state != 3) continue;
@@ -1145,7 +1297,15 @@ __global__ void KGP_CGP2_BOUNDS cg_persistent2_kernel(const CgPersist2 A) {
   if (cta == 0 && tid < m) {
     double* ct = A.ctl + tid * CT_STRIDE;
     ct[CT_DONE] = (double)s_state[tid]; ct[CT_ITER] = s_it[tid]; ct[CT_RELRES] = s_rel[tid];
+    if (tid == 0) ct[CT_PASSES] = (double)pass;
   }
+}
+
+// after the cross-rank all-reduce of |b|^2 (in CT_RRCUR): redo the scalar set-up of cg_init_sorted_kernel
+__global__ void cg_dist_fix_ctl_kernel(double* __restrict__ ct) {
+  const double rr = ct[CT_RRCUR], nb = sqrt(rr), rel = nb / nb;
+  ct[CT_NB] = nb; ct[CT_RELRES] = rel;
+  ct[CT_DONE] = (rel >= ct[CT_TOL]) ? ((2.0 > ct[CT_MAXIT]) ? 2.0 : 0.0) : 1.0;
 }
 
 }  // namespace kgp

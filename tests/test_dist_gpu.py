@@ -65,3 +65,19 @@ def test_sharded_probes_equal_single_world2(built_lib):
     line = [l for l in out.splitlines() if l.startswith('n=')][0]
     rels = [float(t) for t in line.split('rel')[1].replace('dnlZ', ' ').split()]
     assert max(rels) < 1e-9, line
+
+
+def test_row_sharded_kissgp_cg_world2(built_lib):
+    """SURVEY 8(e) KISS-GP (ii): points row-sharded over two ranks, the per-iteration reductions crossing the ranks
+    inside the persistent CG kernel over peer memory.  Same result as one GPU to the CG tolerance (1e-10 here ->
+    1e-7 on vectors), and both ranks must hold bit-identical values (they take the same convergence decisions)."""
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip('needs 2 GPUs')
+    cmd = [sys.executable, '-m', 'torch.distributed.run', '--nnodes=1', '--nproc-per-node', '2', '--master-addr', '127.0.0.1',
+           '--master-port', '29535', os.path.join(ROOT, 'scripts', 'dist_grid_cg.py'), '20000']
+    out = subprocess.check_output(cmd, timeout=900, stderr=subprocess.STDOUT).decode()
+    line = [l for l in out.splitlines() if l.startswith('n=')][0]
+    toks = line.split('|')[0].replace('rel', ' ').split()
+    vals = {toks[i]: float(toks[i + 1]) for i in range(len(toks) - 1) if toks[i] in ('nlZ', 'dnlZ', 'dX', 'alpha', 'ranks_agree')}
+    assert vals['nlZ'] < 1e-9 and vals['dnlZ'] < 1e-7 and vals['dX'] < 1e-7 and vals['alpha'] < 1e-7 and vals['ranks_agree'] == 0.0, line
