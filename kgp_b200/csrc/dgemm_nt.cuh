@@ -326,7 +326,9 @@ inline cudaError_t gemm_init() {
   return cudaFuncSetAttribute(dgemm_nt_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, GEMM_SMEM_BYTES);
 }
 
-inline void gemm_launch(const GemmArgs& g_in, cudaStream_t st) {
+// tile_ctas: one CTA per tile instead of persistent CTAs -- a higher-priority stream's kernels (panel factorisation,
+// NCCL) then get SMs at tile granularity (~80 us) instead of waiting for the whole launch
+inline void gemm_launch(const GemmArgs& g_in, cudaStream_t st, bool tile_ctas = false) {
   GemmArgs g = g_in;
   long nt = gemm_num_tiles(g);
   if (g.shape == GEMM_LOWER) {
@@ -344,7 +346,7 @@ inline void gemm_launch(const GemmArgs& g_in, cudaStream_t st) {
   }
   if (g.own_mod > 1) nt = (nt > g.own_rem) ? (nt - g.own_rem + g.own_mod - 1) / g.own_mod : 0;
   if (nt <= 0 || g.kend <= g.kbeg) return;
-  long grid = (g_gemm_persist && nt > g_gemm_num_sms) ? g_gemm_num_sms : nt;
+  long grid = (g_gemm_persist && !tile_ctas && nt > g_gemm_num_sms) ? g_gemm_num_sms : nt;
   g.cdiag_only = g_gemm_prefetch_c;
   dgemm_nt_kernel<<<(unsigned)grid, GEMM_THREADS, GEMM_SMEM_BYTES, st>>>(g, nt);
 }

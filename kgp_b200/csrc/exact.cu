@@ -37,7 +37,7 @@ static inline double count_gemm(kgp_ctx* c, const GemmArgs& g) {
   c->stats.gemm_flops += f;
   return f;
 }
-static inline void gemm(kgp_ctx* c, const GemmArgs& g) {
+static inline void gemm(kgp_ctx* c, const GemmArgs& g, bool tile_ctas = false) {
   if (g.ntm <= 0 || g.ntn <= 0) return;
   const double fl = count_gemm(c, g);
   if (c->profiling) {
@@ -46,11 +46,11 @@ static inline void gemm(kgp_ctx* c, const GemmArgs& g) {
       for (size_t i = old; i < c->gev.size(); ++i) cudaEventCreate(&c->gev[i]);
     }
     cudaEventRecord(c->gev[c->gev_used], c->stream);
-    gemm_launch(g, c->stream);
+    gemm_launch(g, c->stream, tile_ctas);
     cudaEventRecord(c->gev[c->gev_used + 1], c->stream);
     c->gev_class.push_back(c->gemm_class); c->gev_flops.push_back(fl);
     c->gev_used += 2;
-  } else gemm_launch(g, c->stream);
+  } else gemm_launch(g, c->stream, tile_ctas);
 }
 static void gemm_prof_collect(kgp_ctx* c) {
   double ms = 0.0;
@@ -218,6 +218,9 @@ static int potrf_dist(kgp_ctx* c) {
   cudaStream_t sm = c->stream, sp = c->stream_p;
   cudaEvent_t *ev_panel = c->dev_ev, *ev_free = c->dev_ev + 2, ev_la = c->dev_ev[4];
   for (int b = 0; b < 2; ++b) KGP_CUDA(c, c->PB[b].ensure((size_t)np * NB * 8));
+  // trailing updates run one CTA per tile so that the high-priority panel stream (next panel's factorisation, the NCCL
+  // broadcast kernel) gets SMs at tile granularity; persistent CTAs would hold every SM until the whole update ends
+  static const bool tile_mode = !(getenv("KGP_DIST_TILE_CTAS") && atoi(getenv("KGP_DIST_TILE_CTAS")) == 0);
   KGP_CUDA(c, cudaEventRecord(ev_la, sm));                          // block column 0 is ready once the kernel matrix is built
   for (int k = 0; k < nblk; ++k) {
     const long k0 = (long)k * NB; const int w = (int)((np - k0 < NB) ? np - k0 : NB);
@@ -250,10 +253,10 @@ static int potrf_dist(kgp_ctx* c) {
           else {
             GemmArgs h = mkgemm(Pt + (j0 - t0) * w, w, Pt + (j0 - t0) * w, w, M + j0 * ld + j0, ld, (int)((np - j0) / 128), wj / 128,
                                 0, w, GEMM_FULL, KTRI_NONE, -1.0, 1.0);
-            c->gemm_class = 1; gemm(c, h);
+            c->gemm_class = 1; gemm(c, h, tile_mode);
           }
         }
-        if (g.nbatch > 0) { c->gemm_class = 1; gemm(c, g); }
+        if (g.nbatch > 0) { c->gemm_class = 1; gemm(c, g, tile_mode); }
       };
       std::vector<int> first, rest;
       for (int J = k + 1; J < nblk; ++J) if (dist_col_owner(J, P) == me) (J == k + 1 ? first : rest).push_back(J);
