@@ -116,6 +116,43 @@ static void potrf(kgp_ctx* c) {
   }
 }
 
+// high-priority panel stream + its events (also used by the multi-GPU factorisation)
+static int ensure_panel_stream(kgp_ctx* c) {
+  if (c->stream_p) return KGP_OK;
+  int lo = 0, hi = 0; cudaDeviceGetStreamPriorityRange(&lo, &hi);
+  KGP_CUDA(c, cudaStreamCreateWithPriority(&c->stream_p, cudaStreamNonBlocking, hi));
+  for (int i = 0; i < 8; ++i) KGP_CUDA(c, cudaEventCreateWithFlags(&c->dev_ev[i], cudaEventDisableTiming));
+  return KGP_OK;
+}
+// Single-GPU Cholesky with look-ahead 1: panel k+1 is factored on the high-priority panel stream while the rest of
+// trailing update k runs; the updates use one CTA per tile so that the panel kernels get SMs at tile granularity.
+static int potrf_lookahead(kgp_ctx* c) {
+  int rc = ensure_panel_stream(c); if (rc) return rc;
+  double* M = c->M.d(); const long ld = c->np, np = c->np;
+  cudaStream_t sm = c->stream, sp = c->stream_p;
+  cudaEvent_t* ev_panel = c->dev_ev; cudaEvent_t ev_la = c->dev_ev[4];
+  KGP_CUDA(c, cudaEventRecord(ev_la, sm));
+  int k = 0;
+  for (long k0 = 0; k0 < np; k0 += NB, ++k) {
+    const int w = (int)((np - k0 < NB) ? np - k0 : NB);
+    KGP_CUDA(c, cudaStreamWaitEvent(sp, ev_la, 0));
+    c->stream = sp; factor_panel(c, k0, w); c->stream = sm;
+    KGP_CUDA(c, cudaEventRecord(ev_panel[k & 1], sp));
+    KGP_CUDA(c, cudaStreamWaitEvent(sm, ev_panel[k & 1], 0));
+    const long r0 = k0 + w, mt = (np - r0) / 128;
+    if (mt <= 0) continue;
+    const int w1 = (int)((np - r0 < NB) ? np - r0 : NB), nt1 = w1 / 128;
+    c->gemm_class = 1;
+    gemm(c, mkgemm(M + r0 * ld + k0, ld, M + r0 * ld + k0, ld, M + r0 * ld + r0, ld, (int)mt, nt1, 0, w, GEMM_LOWER, KTRI_NONE, -1.0, 1.0), true);
+    KGP_CUDA(c, cudaEventRecord(ev_la, sm));                       // block column k+1 is up to date: its panel may be factored
+    const long r1 = r0 + w1;
+    if (mt > nt1)
+      gemm(c, mkgemm(M + r1 * ld + k0, ld, M + r1 * ld + k0, ld, M + r1 * ld + r1, ld, (int)(mt - nt1), (int)(mt - nt1), 0, w,
+                     GEMM_LOWER, KTRI_NONE, -1.0, 1.0), true);
+  }
+  return KGP_OK;
+}
+
 // Z = L^{-T} into the upper triangle of W2, block column by block column
 static void zsweep(kgp_ctx* c) {
   const double* M = c->M.d(); double* W = c->W2.d(); const long ld = c->np, np = c->np;
@@ -193,12 +230,7 @@ int dist_init(kgp_ctx* c, int nranks, int rank, const char* id128, const char* l
     }
     c->px_epoch = 0;
   }
-  if (!c->stream_p) {
-    int lo = 0, hi = 0; cudaDeviceGetStreamPriorityRange(&lo, &hi);
-    KGP_CUDA(c, cudaStreamCreateWithPriority(&c->stream_p, cudaStreamNonBlocking, hi));
-    for (int i = 0; i < 8; ++i) KGP_CUDA(c, cudaEventCreateWithFlags(&c->dev_ev[i], cudaEventDisableTiming));
-  }
-  return KGP_OK;
+  return ensure_panel_stream(c);
 }
 void dist_free(kgp_ctx* c) {
   if (c->nccl_comm) { NcclApi& api = nccl_api(nullptr); if (api.ok) api.CommDestroy(c->nccl_comm); c->nccl_comm = nullptr; }
@@ -423,7 +455,10 @@ int exact_eval(kgp_ctx* c, int slot, int want, double* nlZ_out, double* dnlZ_out
   c->stats.kernel_launches += 4;
   cudaEventRecord(c->ev[1], st);
   const bool dist = c->nranks > 1;
-  if (dist) { rc = potrf_dist(c); if (rc) return rc; } else potrf(c);
+  static const bool lookahead = getenv("KGP_LOOKAHEAD") && atoi(getenv("KGP_LOOKAHEAD")) != 0;
+  if (dist) { rc = potrf_dist(c); if (rc) return rc; }
+  else if (lookahead && c->np >= 4 * NB) { rc = potrf_lookahead(c); if (rc) return rc; }
+  else potrf(c);
   logdet_kernel<<<1, 1024, 0, st>>>(c->M.d(), np, n, c->scal.d() + 100);
   c->stats.kernel_launches++;
   cudaEventRecord(c->ev[2], st);
