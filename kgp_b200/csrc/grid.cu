@@ -25,7 +25,8 @@ struct GridState {
   cudaGraphExec_t cg_graph = nullptr; std::vector<char> cg_graph_key;
   DevBuf probes, chT, chU, chY, chS, chC, chP, bva, bvb, bvc, lzQ, lzP, lzH, chacc;   // Chebyshev log-det (grid_cheby.cuh)
   long probes_n = 0; int probes_m = 0; double probes_emax = 0.0; bool probes_injected = false;
-  DevBuf Gm, Ht1, Ht2, VT, se, ps, pw;                 // Woodbury preconditioner (grid_precond.cuh)
+  DevBuf Gm, Ht1, Ht2, VT, se, ps, pw, psel;           // Woodbury preconditioner (grid_precond.cuh); psel: kept modes
+  long prank = 0;
   int gram_slot = -1; unsigned long gram_slot_ver = 0, gram_grid_ver = 0; int pcg_iters = 0;
   DevBuf pdz, prr, bar, part4, g0b, wmaxd; int num_sms = 0; size_t smem_optin = 0; int cg_level_used = -1;
   int wmax = 0; int wmax_ctas = 0; unsigned long wmax_slot_ver = 0, wmax_grid_ver = 0; int wmax_slot = -1;
@@ -58,7 +59,7 @@ void grid_free(kgp_ctx* c) {
                     &g->tgrid, &g->beta, &g->x, &g->r, &g->d, &g->z, &g->ym, &g->partA, &g->partB, &g->S, &g->hyp,
                     &g->hypm, &g->dX, &g->dhyp, &g->out, &g->sortk, &g->sorti, &g->keep, &g->dmean,
                     &g->U, &g->perm, &g->sx, &g->sr, &g->sd, &g->sz, &g->ctl, &g->cnt, &g->KfT, &g->gm0, &g->gm1, &g->pdz, &g->prr, &g->bar, &g->part4, &g->g0b, &g->wmaxd,
-                    &g->Gm, &g->Ht1, &g->Ht2, &g->VT, &g->se, &g->ps, &g->pw, &g->probes, &g->chT, &g->chU, &g->chY, &g->chS, &g->chC, &g->chP, &g->bva, &g->bvb, &g->bvc, &g->lzQ, &g->lzP, &g->lzH, &g->chacc,
+                    &g->Gm, &g->Ht1, &g->Ht2, &g->VT, &g->se, &g->ps, &g->pw, &g->psel, &g->probes, &g->chT, &g->chU, &g->chY, &g->chS, &g->chC, &g->chP, &g->bva, &g->bvb, &g->bvc, &g->lzQ, &g->lzP, &g->lzH, &g->chacc,
                     &g->vg, &g->pvA, &g->pvS, &g->pvG, &g->alt.U, &g->alt.perm};
   for (DevBuf* b : bufs) b->release();
   if (g->h_ctl) cudaFreeHost(g->h_ctl);
@@ -529,6 +530,26 @@ static int precond_setup(kgp_ctx* c, GridState* g, const GridDesc& G, int slot, 
     transpose_small_kernel<<<(unsigned)((nn + 255) / 256), 256, 0, st>>>(g->Vf.d() + g->koff[d], G.ng[d], g->VT.d() + g->koff[d]);
   }
   sqrt_kron_eig_kernel<<<(unsigned)((N + 255) / 256), 256, 0, st>>>(G, g->ee.d(), (const int*)g->eoff.p, g->se.d());
+  // kept modes: s^2 e_k n/N > tau  (host: the factor spectra are ng_0 + ng_1 numbers)
+  {
+    static const double tau = getenv("KGP_PRECOND_TAU") ? atof(getenv("KGP_PRECOND_TAU")) : 1e-3;
+    int etot = 0; for (int d = 0; d < G.p; ++d) etot += G.ng[d];
+    std::vector<double> he(etot);
+    KGP_CUDA(c, cudaMemcpyAsync(he.data(), g->ee.p, (size_t)etot * 8, cudaMemcpyDeviceToHost, st));
+    KGP_CUDA(c, cudaStreamSynchronize(st));
+    std::vector<int> sel; sel.reserve(N);
+    const double scale = s2 * (double)n / (double)N;
+    for (long q = 0; q < N; ++q) {
+      long rr = q; double v = 1.0;
+      for (int d = 0; d < G.p; ++d) { v *= std::max(he[g->eoff_h[d] + (int)(rr % G.ng[d])], 0.0); rr /= G.ng[d]; }
+      if (scale * v > tau) sel.push_back((int)q);
+    }
+    if (sel.empty()) sel.push_back(0);
+    g->prank = (long)sel.size();
+    KGP_CUDA(c, g->psel.ensure((size_t)N * 4));
+    KGP_CUDA(c, cudaMemcpyAsync(g->psel.p, sel.data(), sel.size() * 4, cudaMemcpyHostToDevice, st));
+    KGP_CUDA(c, cudaStreamSynchronize(st));                      // (sel is a local)
+  }
   // H = V' G V : mode products with V_d' along the 2p axes of the N x N array (column axes, then row axes)
   const double* src = g->Gm.d(); double* bufs[2] = {g->Ht1.d(), g->Ht2.d()}; int which = 0;
   const long tot = N * N;
@@ -547,16 +568,16 @@ static int precond_setup(kgp_ctx* c, GridState* g, const GridDesc& G, int slot, 
     }
   if (dbg) tq[3] = dbg_now(st);
   // C = I + s2 E^1/2 H E^1/2 -> blocked Cholesky and triangular inverse of the exact path
-  rc = ensure_exact_buffers(c, N, 1); if (rc) return rc;
+  rc = ensure_exact_buffers(c, g->prank, 1); if (rc) return rc;
   const long np = c->np;
   c->st_level = -1;
   int big = 1 << 30;
   KGP_CUDA(c, cudaMemcpyAsync(c->d_info, &big, sizeof(int), cudaMemcpyHostToDevice, st));
-  assemble_c_kernel<<<dim3((unsigned)((np + 255) / 256), (unsigned)np), 256, 0, st>>>(src, g->se.d(), s2, N, np, c->M.d());
+  assemble_c_sel_kernel<<<dim3((unsigned)((np + 255) / 256), (unsigned)np), 256, 0, st>>>(src, g->se.d(), s2, N, (const int*)g->psel.p, g->prank, np, c->M.d());
   potrf(c);
   if (dbg) tq[4] = dbg_now(st);
   zsweep(c);
-  if (dbg) { tq[5] = dbg_now(st); fprintf(stderr, "[kgp] precond setup ms: gram %.2f eigwait %.2f modeprod %.2f potrf %.2f zsweep %.2f\n", tq[1] - tq[0], tq[2] - tq[1], tq[3] - tq[2], tq[4] - tq[3], tq[5] - tq[4]); }
+  if (dbg) { tq[5] = dbg_now(st); fprintf(stderr, "[kgp] precond setup ms: gram %.2f eigwait %.2f modeprod %.2f potrf %.2f zsweep %.2f (kept %ld of %ld modes)\n", tq[1] - tq[0], tq[2] - tq[1], tq[3] - tq[2], tq[4] - tq[3], tq[5] - tq[4], g->prank, N); }
   int info = 0;
   KGP_CUDA(c, cudaMemcpyAsync(&info, c->d_info, sizeof(int), cudaMemcpyDeviceToHost, st));
   KGP_CUDA(c, cudaStreamSynchronize(st));
@@ -569,13 +590,14 @@ static int precond_apply(kgp_ctx* c, GridState* g, const GridDesc& G, const Slot
   cudaStream_t st = c->stream; const long N = G.N, np = c->np, n = S.n; const int D = S.D;
   scatter(c, G, S.X.d(), n, D, r, 1.0, g->g0.d());                                    // M' r
   double* t = kron_apply(c, g, G, g->g0.d(), g->g1.d(), -1, g->VT.d());              // V' .
-  mul_pad_kernel<<<(unsigned)((np + 255) / 256), 256, 0, st>>>(t, g->se.d(), N, np, c->ym.d());        // E^1/2 .
+  gather_sel_kernel<<<(unsigned)((np + 255) / 256), 256, 0, st>>>(t, g->se.d(), (const int*)g->psel.p, g->prank, np, c->ym.d());   // E^1/2 . on the kept modes
   const int nch = (int)((np + 511) / 512);
   KGP_CUDA(c, c->parts.ensure((size_t)nch * np * 8));
   gemv_t_upper_kernel<<<dim3((unsigned)(np / 128), (unsigned)nch), 128, 0, st>>>(c->W2.d(), np, np, c->ym.d(), c->parts.d());
   sum_parts_kernel<<<(unsigned)((np + 255) / 256), 256, 0, st>>>(c->parts.d(), np, nch, 1.0, c->tvec.d());
   gemv_n_upper_kernel<<<(unsigned)((np + 7) / 8), 256, 0, st>>>(c->W2.d(), np, np, c->tvec.d(), 1.0, c->alpha.d());   // C^-1 = Z Z'
-  mul_pad_kernel<<<(unsigned)((N + 255) / 256), 256, 0, st>>>(c->alpha.d(), g->se.d(), N, N, g->g0.d());           // E^1/2 .
+  KGP_CUDA(c, cudaMemsetAsync(g->g0.p, 0, N * 8, st));
+  scatter_sel_kernel<<<(unsigned)((g->prank + 255) / 256), 256, 0, st>>>(c->alpha.d(), g->se.d(), (const int*)g->psel.p, g->prank, g->g0.d());   // E^1/2 .
   double* w = kron_apply(c, g, G, g->g0.d(), g->g1.d(), -1, g->Vf.d());              // V .
   for_p(G.p, [&](auto P) {
     interp_gather_bz_kernel<decltype(P)::value><<<nb, 256, 0, st>>>(G, S.X.d(), n, D, w, -s2, r, sout, g->partA.d());   // r - s2 M w ; r.s
