@@ -45,7 +45,9 @@ __global__ void __launch_bounds__(EIG_THREADS) jacobi_eig_kernel(const EigBatch 
         if (r == c) dia = fma(v, v, dia); else off = fma(v, v, off);
       }
     off = block_sum(off, sh); dia = block_sum(dia, sh);
-    if (off <= 1e-30 * dia || off == 0.0) break;
+    // squared norms: 1e-26 = relative off-diagonal norm 1e-13; rounding keeps the residue of a 70 x 70 factor near
+    // 70 eps^2 = 3e-30, so a tighter test would never fire and all max_sweeps would run
+    if (off <= 1e-26 * dia || off == 0.0) break;
     for (int round = 0; round < m - 1; ++round) {
       // pairs of this round + their rotation angles
       for (int k = tid; k < half; k += EIG_THREADS) {
@@ -65,28 +67,33 @@ __global__ void __launch_bounds__(EIG_THREADS) jacobi_eig_kernel(const EigBatch 
         rp[k] = p; rq[k] = q; rc[k] = c; rs[k] = s;
       }
       __syncthreads();
-      // columns: A <- A J, V <- V J      (one warp per pair, lanes over rows: no integer division)
-      for (int k = warp; k < half; k += EIG_THREADS / 32) {
-        const int p = rp[k], q = rq[k];
-        if (q < 0) continue;
-        const double c = rc[k], s = rs[k];
-        for (int r = lane; r < ng; r += 32) {
-          double ap = A[(long)r * ld + p], aq = A[(long)r * ld + q];
-          A[(long)r * ld + p] = c * ap - s * aq; A[(long)r * ld + q] = s * ap + c * aq;
-          double vp = V[(long)r * ld + p], vq = V[(long)r * ld + q];
-          V[(long)r * ld + p] = c * vp - s * vq; V[(long)r * ld + q] = s * vp + c * vq;
-        }
-      }
-      __syncthreads();
-      // rows: A <- J' A ; the annihilated pair is zero by construction: exact zeros, not rounding residue
-      for (int k = warp; k < half; k += EIG_THREADS / 32) {
-        const int p = rp[k], q = rq[k];
-        if (q < 0) continue;
-        const double c = rc[k], s = rs[k];
-        for (int cix = lane; cix < ng; cix += 32) {
-          double ap = A[(long)p * ld + cix], aq = A[(long)q * ld + cix];
-          A[(long)p * ld + cix] = (cix == q) ? 0.0 : c * ap - s * aq;
-          A[(long)q * ld + cix] = (cix == p) ? 0.0 : s * ap + c * aq;
+      // A <- J' A J in ONE pass: the index pairs partition the matrix into 2x2 blocks (pair a x pair b), each
+      // rotated from both sides by one thread; V <- V J by (row, pair) items.  Two barriers per round.
+      const int nblk2 = half * half, nitems = nblk2 + ng * half;
+      for (int t = tid; t < nitems; t += EIG_THREADS) {
+        if (t < nblk2) {
+          const int a = t / half, b2 = t - a * half;
+          const int pa = rp[a], qa = rq[a], pb = rp[b2], qb = rq[b2];
+          const double ca = rc[a], sa = rs[a], cb = rc[b2], sb = rs[b2];
+          const bool va = qa >= 0, vb = qb >= 0;
+          const double b00 = A[(long)pa * ld + pb], b01 = vb ? A[(long)pa * ld + qb] : 0.0;
+          const double b10 = va ? A[(long)qa * ld + pb] : 0.0, b11 = (va && vb) ? A[(long)qa * ld + qb] : 0.0;
+          const double tpp = cb * b00 - sb * b01, tpq = sb * b00 + cb * b01;
+          const double tqp = cb * b10 - sb * b11, tqq = sb * b10 + cb * b11;
+          double npp = ca * tpp - sa * tqp, nqp = sa * tpp + ca * tqp, npq = ca * tpq - sa * tqq, nqq = sa * tpq + ca * tqq;
+          if (a == b2) { npq = 0.0; nqp = 0.0; }              // the annihilated pair: exact zeros, not rounding residue
+          A[(long)pa * ld + pb] = npp;
+          if (vb) A[(long)pa * ld + qb] = npq;
+          if (va) A[(long)qa * ld + pb] = nqp;
+          if (va && vb) A[(long)qa * ld + qb] = nqq;
+        } else {
+          const int u = t - nblk2, r = u / half, k = u - r * half;
+          const int pp = rp[k], qq = rq[k];
+          if (qq >= 0) {
+            const double c = rc[k], s2 = rs[k];
+            const double vp = V[(long)r * ld + pp], vq = V[(long)r * ld + qq];
+            V[(long)r * ld + pp] = c * vp - s2 * vq; V[(long)r * ld + qq] = s2 * vp + c * vq;
+          }
         }
       }
       __syncthreads();
