@@ -180,29 +180,47 @@ __device__ __forceinline__ bool gemm_fetch_tile(const GemmArgs& g, long idx, lon
 // Persistent kernel: one CTA per SM walks its serpentine tile sequence (gemm_seq_idx).  The cp.async ring
 // runs ahead ACROSS tile boundaries (the load cursor is up to 3 k-steps ahead of the compute
 // cursor), so the pipeline fill of the next tile overlaps the epilogue of the current one.
-__global__ void __launch_bounds__(GEMM_THREADS, 1) dgemm_nt_kernel(const GemmArgs g, const long ntiles) {
+// BN = 128: one 256-thread CTA per SM on 128x128 tiles.  BN = 64: the tile is split into two 128x64 halves, 128
+// threads each, TWO CTAs per SM (same registers and warps per SM): while one CTA is in its epilogue (C read-modify-
+// write, no DMMAs) the other keeps the tensor pipe busy.
+template <int BN>
+__global__ void __launch_bounds__(2 * BN, 128 / BN) dgemm_nt_kernel_t(const GemmArgs g, const long nitems) {
+  constexpr int THREADS = 2 * BN, WN = BN / 32, HALVES = 128 / BN, STAGE_DOUBLES = (GEMM_BM + BN) * GEMM_BK, LPR = BN / 16;
   extern __shared__ __align__(16) double smem[];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const int wm = warp >> 2, wn = warp & 3;        // 2 x 4 warps
+  const int wm = warp / WN, wn = warp % WN;       // 2 x WN warps
   const int gq = lane >> 2, tq = lane & 3;
+  const long ntiles = nitems / HALVES;
+  auto fetch = [&](long item, GemmTile& t) -> bool {
+    if (item >= nitems) return false;
+    gemm_fetch_tile(g, item / HALVES, ntiles, t);
+    if (HALVES > 1) { const int h = (int)(item % HALVES); t.n0 += h * BN; t.Bg += (long)h * BN * g.ldb; }
+    return true;
+  };
 
   // --- load cursor
   GemmTile lt; long lpos = 0; int lkt = 0;
-  bool lvalid = gemm_fetch_tile(g, gemm_seq_idx(lpos), ntiles, lt);
+  bool lvalid = fetch(gemm_seq_idx(lpos), lt);
   auto load_next = [&](int stage) {
     if (lvalid) {
-      double* sA = smem + stage * GEMM_STAGE_DOUBLES;
+      double* sA = smem + stage * STAGE_DOUBLES;
       double* sB = sA + GEMM_BM * GEMM_BK;
       const long koff = (long)lkt * GEMM_BK;
 #pragma unroll
-      for (int i = 0; i < (GEMM_BM * GEMM_CHUNKS) / GEMM_THREADS; ++i) {
-        int q = tid + i * GEMM_THREADS;
+      for (int i = 0; i < (GEMM_BM * GEMM_CHUNKS) / THREADS; ++i) {
+        int q = tid + i * THREADS;
         int row = q / GEMM_CHUNKS, ch = q % GEMM_CHUNKS;
         int so = ((ch >> 1) * 128 + row) * 4 + (ch & 1) * 2;     // [k4-step][row][4]
         cp_async16(sA + so, lt.Ag + (long)row * g.lda + koff + ch * 2);
+      }
+#pragma unroll
+      for (int i = 0; i < (BN * GEMM_CHUNKS) / THREADS; ++i) {
+        int q = tid + i * THREADS;
+        int row = q / GEMM_CHUNKS, ch = q % GEMM_CHUNKS;
+        int so = ((ch >> 1) * BN + row) * 4 + (ch & 1) * 2;
         cp_async16(sB + so, lt.Bg + (long)row * g.ldb + koff + ch * 2);
       }
-      if (++lkt == lt.nk) { lkt = 0; ++lpos; lvalid = gemm_fetch_tile(g, gemm_seq_idx(lpos), ntiles, lt); }
+      if (++lkt == lt.nk) { lkt = 0; ++lpos; lvalid = fetch(gemm_seq_idx(lpos), lt); }
     }
     cp_async_commit();
   };
@@ -219,13 +237,13 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) dgemm_nt_kernel(const GemmArg
 #pragma unroll
     for (int i = 0; i < 8; ++i) fa[buf][i] = sA[(step * 128 + wm * 64 + i * 8 + gq) * 4 + tq];
 #pragma unroll
-    for (int j = 0; j < 4; ++j) fb[buf][j] = sB[(step * 128 + wn * 32 + j * 8 + gq) * 4 + tq];
+    for (int j = 0; j < 4; ++j) fb[buf][j] = sB[(step * BN + wn * 32 + j * 8 + gq) * 4 + tq];
   };
   GemmTile ct; int it = 0;
   cp_async_wait<GEMM_STAGES - 2>();
   __syncthreads();
   lds(0, smem, 0);
-  for (long cpos = 0; gemm_fetch_tile(g, gemm_seq_idx(cpos), ntiles, ct); ++cpos) {
+  for (long cpos = 0; fetch(gemm_seq_idx(cpos), ct); ++cpos) {
     double* Cp; long ldc; long crow0, ccol0;
     if (ct.in_diag) {
       int blk = ct.m0 / g.nb;
@@ -233,12 +251,12 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) dgemm_nt_kernel(const GemmArg
       crow0 = ct.m0 - blk * g.nb; ccol0 = ct.n0 - blk * g.nb;
     } else { Cp = g.C + ct.coff; ldc = g.ldc; crow0 = ct.m0; ccol0 = ct.n0; }
     const double alpha = g.alpha, beta = g.beta;
-    const bool last_tile = gemm_seq_idx(cpos + 1) >= ntiles;
+    const bool last_tile = gemm_seq_idx(cpos + 1) >= nitems;
     if (beta != 0.0 && g.cdiag_only) {   // pull the C tile towards L2 while the main loop runs
 #pragma unroll
       for (int i = 0; i < 4; ++i) {
         int line = tid * 4 + i;
-        const double* pp = Cp + (crow0 + (line >> 3)) * ldc + ccol0 + (line & 7) * 16;
+        const double* pp = Cp + (crow0 + line / LPR) * ldc + ccol0 + (line % LPR) * 16;
         asm volatile("prefetch.global.L2 [%0];" ::"l"(pp));
       }
     }
@@ -249,7 +267,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) dgemm_nt_kernel(const GemmArg
       for (int j = 0; j < 4; ++j) acc[i][j][0] = acc[i][j][1] = 0.0;
 
     for (int kt = 0; kt < ct.nk; ++kt, ++it) {
-      const double* sA = smem + (it % GEMM_STAGES) * GEMM_STAGE_DOUBLES;
+      const double* sA = smem + (it % GEMM_STAGES) * STAGE_DOUBLES;
 #pragma unroll
       for (int step = 0; step < GEMM_KSTEPS; ++step) {
         const int cur = step & 1;
@@ -272,7 +290,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) dgemm_nt_kernel(const GemmArg
 #endif
           load_next((it + GEMM_STAGES - 1) % GEMM_STAGES);
           if (!(last_tile && kt + 1 == ct.nk))
-            lds(cur ^ 1, smem + ((it + 1) % GEMM_STAGES) * GEMM_STAGE_DOUBLES, 0);
+            lds(cur ^ 1, smem + ((it + 1) % GEMM_STAGES) * STAGE_DOUBLES, 0);
 #pragma unroll
           for (int i = (KGP_GEMM_SPLIT ? 4 : 0); i < 8; ++i)
 #pragma unroll
@@ -317,13 +335,16 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) dgemm_nt_kernel(const GemmArg
 }
 
 static int g_gemm_num_sms = 148;
-static int g_gemm_persist = 1, g_gemm_prefetch_c = 1;   // tuning knobs (env KGP_GEMM_PERSIST / KGP_GEMM_PREFETCHC)
+static int g_gemm_persist = 1, g_gemm_prefetch_c = 1, g_gemm_bn = 128;   // tuning knobs (env KGP_GEMM_PERSIST / KGP_GEMM_PREFETCHC / KGP_GEMM_BN)
 inline cudaError_t gemm_init() {
   int dev = 0; cudaGetDevice(&dev);
   cudaDeviceGetAttribute(&g_gemm_num_sms, cudaDevAttrMultiProcessorCount, dev);
   if (const char* e = getenv("KGP_GEMM_PERSIST")) g_gemm_persist = atoi(e);
   if (const char* e = getenv("KGP_GEMM_PREFETCHC")) g_gemm_prefetch_c = atoi(e);
-  return cudaFuncSetAttribute(dgemm_nt_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, GEMM_SMEM_BYTES);
+  if (const char* e = getenv("KGP_GEMM_BN")) g_gemm_bn = atoi(e) == 64 ? 64 : 128;
+  cudaError_t e1 = cudaFuncSetAttribute(dgemm_nt_kernel_t<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, GEMM_STAGES * (GEMM_BM + 64) * GEMM_BK * 8);
+  if (e1 != cudaSuccess) return e1;
+  return cudaFuncSetAttribute(dgemm_nt_kernel_t<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, GEMM_SMEM_BYTES);
 }
 
 // tile_ctas: one CTA per tile instead of persistent CTAs -- a higher-priority stream's kernels (panel factorisation,
@@ -346,9 +367,15 @@ inline void gemm_launch(const GemmArgs& g_in, cudaStream_t st, bool tile_ctas = 
   }
   if (g.own_mod > 1) nt = (nt > g.own_rem) ? (nt - g.own_rem + g.own_mod - 1) / g.own_mod : 0;
   if (nt <= 0 || g.kend <= g.kbeg) return;
-  long grid = (g_gemm_persist && !tile_ctas && nt > g_gemm_num_sms) ? g_gemm_num_sms : nt;
   g.cdiag_only = g_gemm_prefetch_c;
-  dgemm_nt_kernel<<<(unsigned)grid, GEMM_THREADS, GEMM_SMEM_BYTES, st>>>(g, nt);
+  if (g_gemm_bn == 64) {
+    const long items = 2 * nt, res = 2L * g_gemm_num_sms;
+    const long grid = (g_gemm_persist && !tile_ctas && items > res) ? res : items;
+    dgemm_nt_kernel_t<64><<<(unsigned)grid, 128, GEMM_STAGES * (GEMM_BM + 64) * GEMM_BK * 8, st>>>(g, items);
+    return;
+  }
+  long grid = (g_gemm_persist && !tile_ctas && nt > g_gemm_num_sms) ? g_gemm_num_sms : nt;
+  dgemm_nt_kernel_t<128><<<(unsigned)grid, GEMM_THREADS, GEMM_SMEM_BYTES, st>>>(g, nt);
 }
 
 }  // namespace kgp
