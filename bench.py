@@ -126,13 +126,19 @@ def kissgp_leg(n, device, steps, warmup):
     for _ in range(max(1, warmup)):
         gp2.eng.eval(0, 2, gp2._n_hyp)
     pms = 0.0; pit = 0
-    for _ in range(steps):
-        nlZp, gpre = gp2.eng.eval(0, 2, gp2._n_hyp)
+    v0 = gp2._hyp_vec().copy()
+    for i in range(steps):
+        # hyper-parameters move a little between evaluations, as inside an optimiser run: the eigen-decompositions are
+        # warm-started from the previous evaluation and must not be handed an unchanged problem
+        gp2._set_hyp_vec(v0 + 2e-3 * (1 if i % 2 else -1)); gp2._push_model()
+        gp2.eng.eval(0, 2, gp2._n_hyp)
         st = gp2.stats(); pms += st['ms_total']; pit += st['cg_iters'] - 1
+    gp2._set_hyp_vec(v0); gp2._push_model()
+    nlZp, gpre = gp2.eng.eval(0, 2, gp2._n_hyp)
     pre = {'value': steps * 1e3 / pms, 'unit': 'evals/s', 'ms_per_eval': pms / steps, 'cg_iterations_per_eval': pit / steps,
            'nlZ': nlZp, 'rel_diff_nlZ_vs_reference_cg': abs(nlZp - nlZ) / abs(nlZ),
            'rel_diff_dnlZ_vs_reference_cg': float(np.max(np.abs(gpre - g)) / np.max(np.abs(g))),
-           'note': 'opt.cg_precond=1: B^-1 ~ I - s2 M F C^-1 F\' M\' with C (N x N) factored by the exact path\'s DMMA Cholesky each evaluation'}
+           'note': 'opt.cg_precond=1: B^-1 ~ I - s2 M F C^-1 F\' M\' with C on the kept Kronecker modes, factored by the exact path\'s DMMA Cholesky each evaluation; hyper-parameters perturbed by +-2e-3 between timed evaluations'}
     del gp2
     bytes_iter = n * (16 * 2 + 88) + 32 * N
     peak = 6455.3; src = 'B200_PROFILING.md fallback'
@@ -148,6 +154,48 @@ def kissgp_leg(n, device, steps, warmup):
                          'unit': 'GB/s', 'frac': ach / peak, 'bytes_per_iteration': bytes_iter, 'peak_source': src,
                          'note': 'algorithmic bytes; the working set (48 MB at n=1M) stays in L2 / shared memory, DRAM traffic per iteration is ~0 (profiles/)'},
             'nlZ': nlZ, 'preconditioned': pre}
+
+
+def small_config_legs(device):
+    """The latency-bound reference-sized configurations: C1 exact n=512 d=32 (README demo) and C4
+    KISS-GP n=460 1-D, k=100: device microseconds and kernel launches per nlZ + dnlZ + dnlZ/dX evaluation."""
+    from kgp_b200 import B200GP
+    out = {}
+    rng = np.random.RandomState(42)
+    X = np.tanh(rng.randn(512, 32)); y = np.sin(X.sum(1) / 4) + 0.1 * rng.randn(512)
+    gp = B200GP(engine_kwargs={'device': device})
+    gp.configure(32, {'lik': -2.0, 'mean': [], 'cov': [[-0.7], [0.0]]}, {}, 'infExact', 'meanZero', 'covSEiso', 'likGauss', 'dlikExact', verbose=0)
+    gp.update_data('tr', X, y[:, None])
+    for _ in range(5):
+        gp.eng.eval(0, 2, gp._n_hyp)
+    t = []; 
+    for _ in range(20):
+        gp.eng.eval(0, 2, gp._n_hyp); st = gp.stats(); t.append(st['ms_total'])
+    t0 = time.perf_counter()
+    for _ in range(20):
+        gp.eng.eval(0, 2, gp._n_hyp)
+    out['c1_exact_n512_d32'] = {'device_us_per_eval': 1e3 * float(np.median(t)), 'wall_us_per_eval': 1e6 * (time.perf_counter() - t0) / 20,
+                                'kernel_launches_per_eval': int(st['kernel_launches'])}
+    del gp
+    rng = np.random.RandomState(45)
+    H = np.tanh(rng.randn(460, 1)); y = np.sin(4 * H[:, 0]) + np.exp(-2) * rng.randn(460)
+    gp = B200GP(engine_kwargs={'device': device})
+    gp.configure(1, {'lik': -2.0, 'mean': [], 'cov': [[-0.7], [0.0]]}, {'cg_maxit': 500, 'cg_tol': 1e-4}, 'infGrid', 'meanZero', 'covSEiso', 'likGauss',
+                 'dlikGrid', grid_kwargs={'eq': 1, 'k': 100.}, verbose=0)
+    gp.update_data('tr', H, y[:, None]); gp.update_grid('tr')
+    for _ in range(5):
+        gp.eng.eval(0, 2, gp._n_hyp)
+    t = []; v0 = gp._hyp_vec().copy()
+    for i in range(20):
+        gp._set_hyp_vec(v0 + 2e-3 * (1 if i % 2 else -1)); gp._push_model()        # (see kissgp_leg: no unchanged problem for the warm start)
+        gp.eng.eval(0, 2, gp._n_hyp); st = gp.stats(); t.append(st['ms_total'])
+    t0 = time.perf_counter()
+    for i in range(20):
+        gp._set_hyp_vec(v0 + 2e-3 * (1 if i % 2 else -1)); gp._push_model()
+        gp.eng.eval(0, 2, gp._n_hyp)
+    out['c4_kissgp_n460_k100'] = {'device_us_per_eval': 1e3 * float(np.median(t)), 'wall_us_per_eval': 1e6 * (time.perf_counter() - t0) / 20,
+                                  'kernel_launches_per_eval': int(st['kernel_launches']), 'cg_iterations': int(st['cg_iters'])}
+    return out
 
 
 def kissgp_sharded_leg(n_total, device, steps, warmup, world):
@@ -341,10 +389,14 @@ def main():
                 'launches_per_step': gemm_l / args.steps, 'share_of_step': gemm_ms / dev_ms if dev_ms else None,
                 'whole_eval_tflops': gemm_fl / (dev_ms * 1e-3) / 1e12}
 
-    kiss = kiss_sh
+    kiss = kiss_sh; small = None
     if world == 1 and not args.no_kissgp:
         del gp, eng
         kiss = kissgp_leg(args.kissgp_n, local, args.steps, args.warmup)
+        try:
+            small = small_config_legs(local)
+        except Exception as ex:                       # secondary information only
+            small = {'error': str(ex)}
 
     cpu = None
     if not args.no_cpu:
@@ -367,7 +419,7 @@ def main():
             'roofline': roofline, 'cpu_baseline': cpu,
             'e2e': {'value': e2e_val, 'unit': 'evals/s', 'h2d_bytes_per_step': int(X.nbytes + y.nbytes),
                     'd2h_bytes_per_step': int(n * D * 8 + 8)},
-            'kissgp': kiss, 'gpu_launches': int(launches), 'clocks': sampler.summary(),
+            'kissgp': kiss, 'small_configs': small, 'gpu_launches': int(launches), 'clocks': sampler.summary(),
             'parity_probe': {'nlZ': nlZ, 'nlZ_e2e': nl}}
     print(json.dumps(line), flush=True)
     if world > 1:

@@ -43,6 +43,8 @@ struct GridState {
                      int wmax = 0, wmax_ctas = 0, wmax_slot = -1; unsigned long wmax_slot_ver = 0, wmax_grid_ver = 0;
                      long sub_lo = 0, sub_n = -1; } alt;
   long sub_lo = 0, sub_n = -1;
+  // warm start of the factor eigen-decompositions: eigenvectors of the previous evaluation on the same grid
+  DevBuf eigT; unsigned long eig_grid_ver = 0; int eig_evals = 0; bool eig_have = false;
   // explained variance on the grid (opt.pred_var; infGrid.m:91-101)
   DevBuf vg, pvA, pvS, pvG; bool eig_ok = false, vg_nonzero = false;
   unsigned long vg_slot_ver = 0, vg_model_ver = 0, vg_grid_ver = 0; int vg_slot = -1;
@@ -60,7 +62,7 @@ void grid_free(kgp_ctx* c) {
                     &g->hypm, &g->dX, &g->dhyp, &g->out, &g->sortk, &g->sorti, &g->keep, &g->dmean,
                     &g->U, &g->perm, &g->sx, &g->sr, &g->sd, &g->sz, &g->ctl, &g->cnt, &g->KfT, &g->gm0, &g->gm1, &g->pdz, &g->prr, &g->bar, &g->part4, &g->g0b, &g->wmaxd,
                     &g->Gm, &g->Ht1, &g->Ht2, &g->VT, &g->se, &g->ps, &g->pw, &g->psel, &g->probes, &g->chT, &g->chU, &g->chY, &g->chS, &g->chC, &g->chP, &g->bva, &g->bvb, &g->bvc, &g->lzQ, &g->lzP, &g->lzH, &g->chacc,
-                    &g->vg, &g->pvA, &g->pvS, &g->pvG, &g->alt.U, &g->alt.perm};
+                    &g->vg, &g->pvA, &g->pvS, &g->pvG, &g->alt.U, &g->alt.perm, &g->eigT};
   for (DevBuf* b : bufs) b->release();
   if (g->h_ctl) cudaFreeHost(g->h_ctl);
   if (g->cg_graph) cudaGraphExecDestroy(g->cg_graph);
@@ -1001,7 +1003,25 @@ int grid_eval(kgp_ctx* c, int slot, int want, double* nlZ_out, double* dnlZ_out)
   cudaEventRecord(c->ev[10], st);
   cudaStreamWaitEvent(c->stream2, c->ev[10], 0);
   g->eig_ok = !cheby || m.opt.cg_precond || m.opt.pred_var != 0;
-  if (g->eig_ok) jacobi_eig_kernel<<<G.p, EIG_THREADS, eig_smem, c->stream2>>>(eb, getenv("KGP_EIG_SWEEPS") ? atoi(getenv("KGP_EIG_SWEEPS")) : 40);
+  if (g->eig_ok) {
+    // Jacobi converges quadratically from a nearly diagonal start: within an optimiser run the hyper-parameters move
+    // little between evaluations, so A = V_prev' K V_prev needs 2-4 sweeps instead of ~14.  Cold start on a new grid
+    // and every 32nd evaluation (keeps the accumulated V orthogonal to rounding).
+    static const bool warm_ok = !(getenv("KGP_EIG_WARM") && atoi(getenv("KGP_EIG_WARM")) == 0);
+    const bool warm = warm_ok && g->eig_have && g->eig_grid_ver == c->grid.version && (g->eig_evals % 32) != 0;
+    if (warm) {
+      long ksz = 0; for (int d = 0; d < G.p; ++d) ksz += (long)G.ng[d] * G.ng[d];
+      KGP_CUDA(c, g->eigT.ensure(ksz * 8));
+      for (int d = 0; d < G.p; ++d) {
+        const int ngd = G.ng[d]; const unsigned nbk = (unsigned)(((long)ngd * ngd + 255) / 256);
+        matmul_small_kernel<<<nbk, 256, 0, c->stream2>>>(g->Kf.d() + g->koff[d], g->Vf.d() + g->koff[d], g->eigT.d() + g->koff[d], ngd, 0);
+        matmul_small_kernel<<<nbk, 256, 0, c->stream2>>>(g->Vf.d() + g->koff[d], g->eigT.d() + g->koff[d], g->Af.d() + g->koff[d], ngd, 1);
+        eb.warm[d] = 1;
+      }
+    }
+    jacobi_eig_kernel<<<G.p, EIG_THREADS, eig_smem, c->stream2>>>(eb, getenv("KGP_EIG_SWEEPS") ? atoi(getenv("KGP_EIG_SWEEPS")) : 40);
+    g->eig_have = true; g->eig_grid_ver = c->grid.version; g->eig_evals++;
+  }
   cudaEventRecord(c->ev[11], c->stream2);
   c->stats.kernel_launches++;
   resid_mean_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(S.X.d(), S.has_y ? S.y.d() : nullptr, n, D, m.mean_mask, g->hypm.d(), g->ym.d(), n);

@@ -9,11 +9,21 @@ namespace kgp {
 // A (ng x ng, symmetric; destroyed) -> eigenvalues ev[ng] (unsorted), eigenvectors V (columns).
 // Works out of shared memory when 2*ng*ng*8 bytes fit (use_smem), otherwise in place in global.
 constexpr int EIG_THREADS = 512;
-struct EigBatch { double* A[GRID_MAXP]; double* V[GRID_MAXP]; double* ev[GRID_MAXP]; int ng[GRID_MAXP]; int use_smem[GRID_MAXP]; };
+struct EigBatch { double* A[GRID_MAXP]; double* V[GRID_MAXP]; double* ev[GRID_MAXP]; int ng[GRID_MAXP]; int use_smem[GRID_MAXP];
+                  int warm[GRID_MAXP]; };   // warm: V holds the previous eigenvectors and A = V' K V (nearly diagonal)
+// C = A B (transA = 0) or A' B (transA = 1), n x n row-major; the warm start forms V'(K V) with two launches
+__global__ void matmul_small_kernel(const double* __restrict__ A, const double* __restrict__ B, double* __restrict__ C, int n, int transA) {
+  const int q = blockIdx.x * blockDim.x + threadIdx.x;
+  if (q >= n * n) return;
+  const int i = q / n, j = q - i * n;
+  double acc = 0.0;
+  for (int k = 0; k < n; ++k) acc = fma(transA ? A[(long)k * n + i] : A[(long)i * n + k], B[(long)k * n + j], acc);
+  C[q] = acc;
+}
 __global__ void __launch_bounds__(EIG_THREADS) jacobi_eig_kernel(const EigBatch eb, int max_sweeps) {
   double* __restrict__ Ag = eb.A[blockIdx.x]; double* __restrict__ Vg = eb.V[blockIdx.x];
   double* __restrict__ ev = eb.ev[blockIdx.x];
-  const int ng = eb.ng[blockIdx.x], use_smem = eb.use_smem[blockIdx.x];
+  const int ng = eb.ng[blockIdx.x], use_smem = eb.use_smem[blockIdx.x], warm = eb.warm[blockIdx.x];
   extern __shared__ double sm[];
   __shared__ double sh[32];
   __shared__ double rc[1024], rs[1024];          // rotation of pair k: cos, sin
@@ -25,7 +35,8 @@ __global__ void __launch_bounds__(EIG_THREADS) jacobi_eig_kernel(const EigBatch 
   for (long q = tid; q < (long)ng * ng; q += EIG_THREADS) {
     int r = (int)(q / ng), c = (int)(q % ng);
     if (use_smem) A[(long)r * ld + c] = 0.5 * (Ag[q] + Ag[(long)c * ng + r]);   // Kj = (Kj+Kj')/2   (apxGrid.m:583)
-    V[(long)r * ld + c] = (r == c) ? 1.0 : 0.0;
+    if (warm) { if (use_smem) V[(long)r * ld + c] = Vg[q]; }
+    else V[(long)r * ld + c] = (r == c) ? 1.0 : 0.0;
   }
   __syncthreads();
   if (!use_smem) {                                              // symmetrise in place, second pass
