@@ -95,6 +95,10 @@ int kgp_comm_init(kgp_ctx* ctx, int nranks, int rank, const char* id128, const c
 /* ownership maps of the sharded exact path (host logic, callable without a GPU) */
 int  kgp_dist_col_owner(int block, int nranks);              /* rank owning block column `block` (NB = 512) */
 long kgp_dist_zrow_begin(int rank, int nranks, long n);     /* first row of Z = L^-T owned by `rank`; rank = nranks gives the padded order */
+/* KISS-GP row-sharded CG: first data row owned by `rank` (contiguous shares; rank = nranks gives n); and whether a
+ * problem of n points on N grid nodes is row-sharded at all (needs n >= 4096 per rank and N within the peer window) */
+long kgp_dist_row_begin(int rank, int nranks, long n);
+int  kgp_dist_rows_sharded(int nranks, long n, long N);
 
 /* data: replaces eng.push('X_<set>',X) / push('y_<set>',y)  (kgp/backend/gpml.py:152-158) */
 int kgp_set_data_host(kgp_ctx* ctx, int slot, const double* X, long n, int D, const double* y /* may be NULL */);

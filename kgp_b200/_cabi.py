@@ -78,6 +78,8 @@ SIGNATURES = {
     'kgp_comm_init': (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_char_p, C.c_char_p]),
     'kgp_dist_col_owner': (C.c_int, [C.c_int, C.c_int]),
     'kgp_dist_zrow_begin': (C.c_long, [C.c_int, C.c_int, C.c_long]),
+    'kgp_dist_row_begin': (C.c_long, [C.c_int, C.c_int, C.c_long]),
+    'kgp_dist_rows_sharded': (C.c_int, [C.c_int, C.c_long, C.c_long]),
 }
 
 

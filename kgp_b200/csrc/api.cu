@@ -135,6 +135,9 @@ long kgp_dist_zrow_begin(int rank, int nranks, long n) {
   return dist_zrow_begin(rank, nranks, np, NB);
 }
 
+long kgp_dist_row_begin(int rank, int nranks, long n) { return nranks > 0 ? dist_row_begin(rank, nranks, n) : 0; }
+int kgp_dist_rows_sharded(int nranks, long n, long N) { return dist_rows_sharded(nranks, n, N) ? 1 : 0; }
+
 const char* kgp_last_error(kgp_ctx* c) { return c ? c->err.c_str() : "null context"; }
 int kgp_set_profiling(kgp_ctx* c, int on) { if (!c) return KGP_BAD_ARG; c->profiling = on; return KGP_OK; }
 

@@ -78,6 +78,11 @@ inline long dist_zrow_begin(int r, int nranks, long np, int nb) {
 }
 
 
+// KISS-GP row-sharded CG: contiguous shares of the data rows; sharded only when every rank gets >= 4096 points
+// (below that the exchange latency exceeds the point work) and the grid fits the peer window
+inline long dist_row_begin(int r, int nranks, long n) { return r <= 0 ? 0 : (r >= nranks ? n : n * r / nranks); }
+inline bool dist_rows_sharded(int nranks, long n, long N) { return nranks > 1 && nranks <= 8 && n >= 4096L * nranks && N <= PX_NCAP; }
+
 // ---- gradient pass over the lower 128-tiles of B^-1 a rank owns ------------------------------------------
 // Same arithmetic per element as reduce_grad_kernel (G = (B^-1/sn2 - a_i a_j) K_ij with K recomputed from xs),
 // but a tile (tm > tn) feeds BOTH the row sums of its rows i (over its columns j) and, by symmetry, the row sums

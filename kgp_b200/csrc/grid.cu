@@ -1033,10 +1033,10 @@ int grid_eval(kgp_ctx* c, int slot, int want, double* nlZ_out, double* dnlZ_out)
   if (m.opt.cg_precond) {
     rc = pcg_solve(c, g, G, slot, sw, m.opt.cg_tol, maxit, g->ym.d(), g->x.d(), true);
     if (rc) return rc;
-  } else if (G.p <= 2 && !legacy_cg && c->nranks > 1 && c->px_ok && G.N <= PX_NCAP && n >= 4096L * c->nranks) {
+  } else if (G.p <= 2 && !legacy_cg && c->px_ok && dist_rows_sharded(c->nranks, n, G.N)) {
     // row-sharded solve (SURVEY 8(e) KISS-GP (ii)): this rank's contiguous share of the points, the two reductions
     // of every iteration cross the ranks over peer memory inside the persistent kernel
-    const long lo = n * c->rank / c->nranks, hi = n * (c->rank + 1) / c->nranks;
+    const long lo = dist_row_begin(c->rank, c->nranks, n), hi = dist_row_begin(c->rank + 1, c->nranks, n);
     swap_sorted(g);
     if (g->sub_lo != lo || g->sub_n != hi - lo) { g->sub_lo = lo; g->sub_n = hi - lo; g->sort_slot = -1; }
     rc = cg_solve_sorted(c, g, G, slot, g->ym.d(), n, 1, sw, m.opt.cg_tol, maxit);

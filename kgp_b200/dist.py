@@ -65,6 +65,18 @@ def zrow_ranges(n, world):
     return [(b[r], b[r + 1]) for r in range(int(world))]
 
 
+def row_ranges(n, world):
+    """[(lo, hi)] of the data rows each rank owns in the row-sharded KISS-GP solve (contiguous shares)."""
+    l = _cabi.lib()
+    b = [l.kgp_dist_row_begin(r, int(world), int(n)) for r in range(int(world) + 1)]
+    return [(b[r], b[r + 1]) for r in range(int(world))]
+
+
+def rows_sharded(n, N, world):
+    """True when a KISS-GP problem of n points on N grid nodes runs the row-sharded CG on `world` ranks."""
+    return bool(_cabi.lib().kgp_dist_rows_sharded(int(world), int(n), int(N)))
+
+
 def allreduce_sum(values):
     """Sum a small float64 vector over ranks (scalar / hyper-gradient terms of sharded probes)."""
     import torch

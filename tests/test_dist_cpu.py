@@ -78,3 +78,22 @@ def test_gloo_world2_id_broadcast_and_probe_reduction(built_lib):
     for rank, ok, tot in res:
         assert ok                                  # the 128-byte id arrived intact on every rank
         assert tot == [11.0, float(sum(range(11))), 2.0]
+
+
+@pytest.mark.parametrize('n,world', [(20000, 2), (1000003, 8), (40001, 3)])
+def test_row_ranges_partition_the_points(built_lib, n, world):
+    """Row-sharded KISS-GP solve (SURVEY 8(e) KISS-GP (ii)): contiguous shares that tile [0, n), sizes within one."""
+    from kgp_b200 import dist
+    r = dist.row_ranges(n, world)
+    assert r[0][0] == 0 and r[-1][1] == n
+    assert all(r[i][1] == r[i + 1][0] for i in range(world - 1))
+    sizes = [hi - lo for lo, hi in r]
+    assert max(sizes) - min(sizes) <= 1
+
+
+def test_row_sharding_threshold(built_lib):
+    from kgp_b200 import dist
+    assert not dist.rows_sharded(6000, 1600, 2)          # < 4096 points per rank: the exchange would cost more than it saves
+    assert dist.rows_sharded(20000, 1600, 2) and dist.rows_sharded(8_000_000, 4900, 8)
+    assert not dist.rows_sharded(10**6, 40000, 2)        # grid larger than the peer window
+    assert not dist.rows_sharded(10**6, 4900, 1)
