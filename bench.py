@@ -92,7 +92,36 @@ def synth_c5(n, seed=46, Q=6):
     return H, y, hyp_cov
 
 
-def kissgp_leg(n, device, steps, warmup):
+def kissgp_cpu_sample(n, cg_iters_needed, sample_iters=40):
+    """CPU arm of the KISS-GP leg: the oracle's pieces (scipy.sparse CSR Mx like the reference's sparse path, dense
+    Kronecker factors) on the host cores.  A full solve needs thousands of CG iterations, so the sample times the set-up
+    (grid, interpolation matrix, factors) once and `sample_iters` iterations of B = I + sW Mx Kg Mx' sW, and
+    extrapolates to the iteration count the engine needed.  One evaluation = gp() + dlikGrid() = two inferences
+    (dlikGrid.m:29-36 re-runs the inference)."""
+    sys.path.insert(0, os.path.join(ROOT, 'oracle'))
+    import gpml_grid as gg
+    H, y, hc = synth_c5(n)
+    hv = np.tile(np.concatenate([np.asarray(a, dtype=np.float64).reshape(-1) for a in hc])[:, None], (1, 2)).flatten(order='F')
+    t0 = time.perf_counter()
+    xg = gg.creategrid(H, 1, 70.)
+    Mx = gg.interpgrid(xg, H); MxT = Mx.T.tocsr()
+    hs = gg.split_hyp('covSM', hv, 2, 6)
+    Ks = [gg.factor_cov('covSM', hs[i], xg[i], 6)[0] for i in range(2)]
+    t_setup = time.perf_counter() - t0
+    sw = 1.0 / 0.3
+    v = y.copy()
+    t0 = time.perf_counter()
+    for _ in range(sample_iters):
+        z = v + sw * (Mx @ gg.kronmvm(Ks, MxT @ (sw * v)))
+        a = (v @ v) / (v @ z); v = v - a * z                  # the vector work of one CG iteration (apx.m:290-300)
+    t_iter = (time.perf_counter() - t0) / sample_iters
+    per_inference = t_setup + cg_iters_needed * t_iter
+    return {'value': 1.0 / (2.0 * per_inference), 'unit': 'evals/s', 'cores': cpu_threads(), 'kind': 'port',
+            'sample': 'oracle set-up (grid + CSR Mx + factors) %.2f s once + %d CG iterations at %.1f ms each, extrapolated to %d iterations; x2 inferences per evaluation (gp + dlikGrid)'
+                      % (t_setup, sample_iters, 1e3 * t_iter, int(cg_iters_needed))}
+
+
+def kissgp_leg(n, device, steps, warmup, with_cpu=True):
     """Secondary headline: KISS-GP (infGrid, covSM Q=6 x 2, meanSum, 70 x 70 grid, Fiedler log-det) nlZ + dnlZ + dnlZ/dX
     at n points.  The dominant kernel is the persistent CG kernel; its roofline is HBM: algorithmic bytes per
     iteration n*(16*D + 88) + 32*N over the measured copy bandwidth."""
@@ -153,7 +182,8 @@ def kissgp_leg(n, device, steps, warmup):
             'roofline': {'bound': 'hbm', 'kernel': 'cg_persistent2_kernel (whole CG solve, one cooperative launch)', 'achieved': ach, 'peak': peak,
                          'unit': 'GB/s', 'frac': ach / peak, 'bytes_per_iteration': bytes_iter, 'peak_source': src,
                          'note': 'algorithmic bytes; the working set (48 MB at n=1M) stays in L2 / shared memory, DRAM traffic per iteration is ~0 (profiles/)'},
-            'nlZ': nlZ, 'preconditioned': pre}
+            'nlZ': nlZ, 'preconditioned': pre,
+            'cpu_baseline': kissgp_cpu_sample(n, iters / steps) if with_cpu else None}
 
 
 def small_config_legs(device):
@@ -392,7 +422,7 @@ def main():
     kiss = kiss_sh; small = None
     if world == 1 and not args.no_kissgp:
         del gp, eng
-        kiss = kissgp_leg(args.kissgp_n, local, args.steps, args.warmup)
+        kiss = kissgp_leg(args.kissgp_n, local, args.steps, args.warmup, with_cpu=not args.no_cpu)
         try:
             small = small_config_legs(local)
         except Exception as ex:                       # secondary information only

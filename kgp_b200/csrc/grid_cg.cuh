@@ -780,7 +780,7 @@ __device__ __forceinline__ void dx_put(ulonglong2* dst, double v, unsigned tag) 
   ulonglong2 w; w.x = t | (b & 0xffffffffULL); w.y = t | (b >> 32);
   asm volatile("st.volatile.global.v2.u64 [%0], {%1, %2};" ::"l"(dst), "l"(w.x), "l"(w.y) : "memory");
 }
-// poll one packet until both halves carry `tag`; a peer that never arrives traps the kernel after ~4 s instead of
+// poll one packet until both halves carry `tag`; a peer that never arrives traps the kernel after ~17 s instead of
 // hanging the GPU
 // ---- exchange helpers, kept out of line so their registers do not add to the persistent kernel's budget -------
 __device__ __forceinline__ bool dx_ok(unsigned long long x, unsigned long long y, unsigned tag) {
@@ -797,7 +797,7 @@ __device__ __forceinline__ double dx_finish(const ulonglong2* p, unsigned long l
   long long t0 = 0; bool timing = false;
   while (!dx_ok(x, y, tag)) {
     if (!timing) { t0 = clock64(); timing = true; }
-    else if (clock64() - t0 > (1LL << 33)) __trap();
+    else if (clock64() - t0 > (1LL << 35)) __trap();
     dx_ld(p, x, y);
   }
   return dx_val(x, y);
@@ -858,7 +858,7 @@ __device__ __forceinline__ double dx_get(const ulonglong2* src, unsigned tag) {
     asm volatile("ld.volatile.global.v2.u64 {%0, %1}, [%2];" : "=l"(x), "=l"(y) : "l"(src) : "memory");
     if ((unsigned)(x >> 32) == tag && (unsigned)(y >> 32) == tag) break;
     if (!timing) { t0 = clock64(); timing = true; }
-    else if (clock64() - t0 > (1LL << 33)) __trap();
+    else if (clock64() - t0 > (1LL << 35)) __trap();
   }
   return __longlong_as_double((long long)((x & 0xffffffffULL) | (y << 32)));
 }
