@@ -475,7 +475,6 @@ int exact_eval(kgp_ctx* c, int slot, int want, double* nlZ_out, double* dnlZ_out
     c->stats.kernel_launches += 4;
   }
   cudaEventRecord(c->ev[4], st);
-  int nsc = 0;
   static const bool tile_reduce = getenv("KGP_TILE_REDUCE") && atoi(getenv("KGP_TILE_REDUCE"));
   if (want >= 1 && (dist || tile_reduce)) {
     rc = zzt_reduce_dist(c, n, sf2, 1.0 / sn2); if (rc) return rc;
@@ -503,7 +502,6 @@ int exact_eval(kgp_ctx* c, int slot, int want, double* nlZ_out, double* dnlZ_out
     dx_from_rows_kernel<<<(unsigned)((n * D + 255) / 256), 256, 0, st>>>(c->rows.d(), n, D, Dp, c->fac.d(), c->dX.d());
     if (nmean) mean_grad_kernel<<<D + 1, 1024, 0, st>>>(S.X.d(), c->alpha.d(), n, D, c->scal.d() + 110);
     c->stats.kernel_launches += 4 + (nmean ? 1 : 0);
-    nsc = 4 + Dp;
     cudaEventRecord(c->ev[6], st);
   }
   double h[256];
@@ -529,7 +527,6 @@ int exact_eval(kgp_ctx* c, int slot, int want, double* nlZ_out, double* dnlZ_out
   if (nlZ_out) *nlZ_out = nlZ;
   c->st_nlZ = nlZ; c->st_dnlZ.clear();
   if (want >= 1) {
-    (void)nsc;
     std::vector<double> g;
     if (ard) for (int d = 0; d < D; ++d) g.push_back(h[4 + d]);
     else g.push_back(0.5 * h[1]);

@@ -894,7 +894,6 @@ static int slq_logdet(kgp_ctx* c, GridState* g, const GridDesc& G, int slot, dou
     for (int r = 0; r < k; ++r) qv += Vv[r] * Vv[r] * log(fmax(T[(size_t)r * k + r], 1e-300));     // first components: row 0 of V
     quad += nv2 * qv / (2.0 * m);
   }
-  double sdw = 0.0;
   if (want_deriv && hi > lo) {
     const bool pre = mo.opt.cg_precond != 0;
     const int MB = pre ? 1 : CG_MAXCOLS;
@@ -930,7 +929,6 @@ static int slq_logdet(kgp_ctx* c, GridState* g, const GridDesc& G, int slot, dou
     }
     vec_scale_copy_kernel<<<(unsigned)((ksz + 255) / 256), 256, 0, st>>>(ksz, 1.0 / (2.0 * m), g->chP.d(), g->chP.d());
   }
-  (void)sdw;
   // chacc[0] = ldB2 share of this rank, chacc[1] = sum(dW) share
   KGP_CUDA(c, cudaMemcpyAsync(g->chacc.p, &quad, 8, cudaMemcpyHostToDevice, st));
   if (c->nranks > 1) {
