@@ -248,12 +248,18 @@ static int potrf_dist(kgp_ctx* c) {
   double* M = c->M.d(); const long ld = c->np, np = c->np;
   const int P = c->nranks, me = c->rank, nblk = (int)((np + NB - 1) / NB);
   cudaStream_t sm = c->stream, sp = c->stream_p;
-  cudaEvent_t *ev_panel = c->dev_ev, *ev_free = c->dev_ev + 2, ev_la = c->dev_ev[4];
+  cudaEvent_t *ev_panel = c->dev_ev, *ev_free = c->dev_ev + 2, ev_la = c->dev_ev[4], ev_second = c->dev_ev[5];
   for (int b = 0; b < 2; ++b) KGP_CUDA(c, c->PB[b].ensure((size_t)np * NB * 8));
   // trailing updates run one CTA per tile so that the high-priority panel stream (next panel's factorisation, the NCCL
   // broadcast kernel) gets SMs at tile granularity; persistent CTAs would hold every SM until the whole update ends
   static const bool tile_mode = !(getenv("KGP_DIST_TILE_CTAS") && atoi(getenv("KGP_DIST_TILE_CTAS")) == 0);
+  // look-ahead 2 (opt-in, KGP_DIST_LA2=1; measured neutral at 4 GPUs: potrf 229.6 vs 231.0 ms): at step k the main
+  // stream updates column k+2 first ("second"), then the rest; the update
+  // of column k+1 with panel k ("first") runs on the PANEL stream right in front of panel k+1's factorisation and only
+  // waits for second(k-1) -- the serial chain is broadcast -> first -> factor, independent of the bulk update.
+  static const bool la2 = getenv("KGP_DIST_LA2") && atoi(getenv("KGP_DIST_LA2")) != 0;
   KGP_CUDA(c, cudaEventRecord(ev_la, sm));                          // block column 0 is ready once the kernel matrix is built
+  KGP_CUDA(c, cudaEventRecord(ev_second, sm));
   for (int k = 0; k < nblk; ++k) {
     const long k0 = (long)k * NB; const int w = (int)((np - k0 < NB) ? np - k0 : NB);
     const long rows = np - k0; const int owner = dist_col_owner(k, P), b = k & 1;
@@ -261,7 +267,7 @@ static int potrf_dist(kgp_ctx* c) {
     // ---- panel stream: factor (owner), broadcast, unpack
     if (k >= 2) KGP_CUDA(c, cudaStreamWaitEvent(sp, ev_free[b], 0));
     if (me == owner) {
-      KGP_CUDA(c, cudaStreamWaitEvent(sp, ev_la, 0));
+      if (!la2 || k == 0) KGP_CUDA(c, cudaStreamWaitEvent(sp, ev_la, 0));
       c->stream = sp; factor_panel(c, k0, w); c->stream = sm;
       KGP_CUDA(c, cudaMemcpy2DAsync(PB, (size_t)w * 8, M + k0 * ld + k0, (size_t)ld * 8, (size_t)w * 8, (size_t)rows, cudaMemcpyDeviceToDevice, sp));
     }
@@ -269,31 +275,41 @@ static int potrf_dist(kgp_ctx* c) {
     if (me != owner)
       KGP_CUDA(c, cudaMemcpy2DAsync(M + k0 * ld + k0, (size_t)ld * 8, PB, (size_t)w * 8, (size_t)w * 8, (size_t)rows, cudaMemcpyDeviceToDevice, sp));
     KGP_CUDA(c, cudaEventRecord(ev_panel[b], sp));
+    const long t0 = k0 + w;                                         // first trailing row
+    const double* Pt = PB + (long)w * w;                            // panel rows from t0 on (row pitch w)
+    const int ntm = (int)((np - t0) / 128);
+    auto launch = [&](const std::vector<int>& blocks) {
+      if (blocks.empty()) return;
+      // blocks of full width NB go into one batched launch; a narrower last block gets its own
+      GemmArgs g = mkgemm(Pt, w, Pt, w, M + t0 * ld + t0, ld, ntm, NB / 128, 0, w, GEMM_FULL, KTRI_NONE, -1.0, 1.0);
+      for (int J : blocks) {
+        const long j0 = (long)J * NB; const int wj = (int)((np - j0 < NB) ? np - j0 : NB);
+        if (wj == NB && g.nbatch < GEMM_MAX_BATCH) g.bat_roff[g.nbatch++] = (int)(j0 - t0);
+        else {
+          GemmArgs h = mkgemm(Pt + (j0 - t0) * w, w, Pt + (j0 - t0) * w, w, M + j0 * ld + j0, ld, (int)((np - j0) / 128), wj / 128,
+                              0, w, GEMM_FULL, KTRI_NONE, -1.0, 1.0);
+          c->gemm_class = 1; gemm(c, h, tile_mode);
+        }
+      }
+      if (g.nbatch > 0) { c->gemm_class = 1; gemm(c, g, tile_mode); }
+    };
+    std::vector<int> first, second, rest;
+    for (int J = k + 1; J < nblk; ++J)
+      if (dist_col_owner(J, P) == me) (J == k + 1 ? first : (la2 && J == k + 2) ? second : rest).push_back(J);
+    if (t0 < np && la2) {                                           // first(k) on the panel stream, after second(k-1)
+      KGP_CUDA(c, cudaStreamWaitEvent(sp, ev_second, 0));
+      c->stream = sp; launch(first); c->stream = sm;
+    }
     // ---- main stream: update the block columns this rank owns with the packed panel
     KGP_CUDA(c, cudaStreamWaitEvent(sm, ev_panel[b], 0));
-    const long t0 = k0 + w;                                         // first trailing row
     if (t0 < np) {
-      const double* Pt = PB + (long)w * w;                          // panel rows from t0 on (row pitch w)
-      const int ntm = (int)((np - t0) / 128);
-      auto launch = [&](const std::vector<int>& blocks) {
-        if (blocks.empty()) return;
-        // blocks of full width NB go into one batched launch; a narrower last block gets its own
-        GemmArgs g = mkgemm(Pt, w, Pt, w, M + t0 * ld + t0, ld, ntm, NB / 128, 0, w, GEMM_FULL, KTRI_NONE, -1.0, 1.0);
-        for (int J : blocks) {
-          const long j0 = (long)J * NB; const int wj = (int)((np - j0 < NB) ? np - j0 : NB);
-          if (wj == NB && g.nbatch < GEMM_MAX_BATCH) g.bat_roff[g.nbatch++] = (int)(j0 - t0);
-          else {
-            GemmArgs h = mkgemm(Pt + (j0 - t0) * w, w, Pt + (j0 - t0) * w, w, M + j0 * ld + j0, ld, (int)((np - j0) / 128), wj / 128,
-                                0, w, GEMM_FULL, KTRI_NONE, -1.0, 1.0);
-            c->gemm_class = 1; gemm(c, h, tile_mode);
-          }
-        }
-        if (g.nbatch > 0) { c->gemm_class = 1; gemm(c, g, tile_mode); }
-      };
-      std::vector<int> first, rest;
-      for (int J = k + 1; J < nblk; ++J) if (dist_col_owner(J, P) == me) (J == k + 1 ? first : rest).push_back(J);
-      launch(first);
-      if (!first.empty()) KGP_CUDA(c, cudaEventRecord(ev_la, sm));   // look-ahead: panel k+1 may be factored now
+      if (la2) {
+        launch(second);
+        KGP_CUDA(c, cudaEventRecord(ev_second, sm));
+      } else {
+        launch(first);
+        if (!first.empty()) KGP_CUDA(c, cudaEventRecord(ev_la, sm));   // look-ahead: panel k+1 may be factored now
+      }
       launch(rest);
     }
     KGP_CUDA(c, cudaEventRecord(ev_free[b], sm));
