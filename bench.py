@@ -228,6 +228,27 @@ def small_config_legs(device):
     return out
 
 
+def epoch_leg(device):
+    """one training epoch of BASELINE configs[0] (README GP-RNN: SimpleRNN(32) -> exact GP covSEiso,
+    (10,2) sequences, 512 train, batch 32, one GP update with gp_n_iter = 5) through the PyTorch restatement of
+    UpdateGP + gen_gp_loss (kgp_b200/harness.py); reports the GP-update share, i.e. what the reference pays through
+    oct2py per epoch."""
+    import torch
+    from kgp_b200 import harness
+    torch.manual_seed(0); rng = np.random.RandomState(42)
+    X = rng.randn(512, 10, 2).astype(np.float32); y = np.sin(X.sum((1, 2)) / 4)[:, None] + 0.1 * rng.randn(512, 1)
+    net = harness.make_net('rnn', (10, 2), hidden=32).cuda(device)
+    head = harness.GPHead(32, {'lik': -2.0, 'mean': [], 'cov': np.array([[-0.7], [0.0]])}, inf='infExact', cov='covSEiso', device=device)
+    Xt = torch.from_numpy(X).cuda(device)
+    opt = torch.optim.RMSprop(net.parameters(), lr=1e-3)
+    harness.fit(net, head, Xt, y, opt, epochs=1, batch_size=32, gp_n_iter=5)            # warm-up epoch
+    torch.cuda.synchronize(); t0 = time.perf_counter()
+    hist = harness.fit(net, head, Xt, y, opt, epochs=3, batch_size=32, gp_n_iter=5)
+    torch.cuda.synchronize(); per = (time.perf_counter() - t0) / 3
+    return {'config': 'README GP-RNN n=512, 16 mini-batches, gp_n_iter=5', 'epoch_ms': 1e3 * per,
+            'gp_update_ms': 1e3 * float(np.mean([h['gp_update_elapsed'] for h in hist])), 'nlml_last': float(hist[-1]['nlml'])}
+
+
 def kissgp_sharded_leg(n_total, device, steps, warmup, world):
     """N > 1: the same KISS-GP evaluation with the points ROW-SHARDED over the ranks (SURVEY 8(e) KISS-GP (ii)), weak
     scaling: n_total = kissgp_n x N points.  The two reductions of every CG iteration (grid vector, four scalars)
@@ -425,6 +446,7 @@ def main():
         kiss = kissgp_leg(args.kissgp_n, local, args.steps, args.warmup, with_cpu=not args.no_cpu)
         try:
             small = small_config_legs(local)
+            small['c1_gp_rnn_epoch'] = epoch_leg(local)
         except Exception as ex:                       # secondary information only
             small = {'error': str(ex)}
 
