@@ -168,3 +168,12 @@ def test_slq_matches_the_dense_quantities_it_estimates():
                                 slq={'V': V, 'steps': 60}, want_grad=False)[1]
     fd = (f(hyp['lik'] + 1e-5) - f(hyp['lik'] - 1e-5)) / 2e-5
     assert abs(d['lik'] - fd) < 1e-5 * abs(fd)               # dB commutes with B for the noise scale: exact derivative
+
+
+def test_bench_kissgp_cpu_sample_runs():
+    """bench.py's CPU arm of the KISS-GP leg (oracle pieces on a bounded sample) stays runnable."""
+    import os, sys
+    sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+    import bench
+    r = bench.kissgp_cpu_sample(20000, 100, sample_iters=3)
+    assert r['kind'] == 'port' and r['unit'] == 'evals/s' and r['value'] > 0 and r['cores'] >= 1
