@@ -6,6 +6,30 @@ line search, constants minimize.m:42-46), which is what `GPML.train` runs throug
 function evaluation is one kgp_eval(want=1) on the device.  ``f(X) -> (value,
 grad)``; a raised exception / NaN / Inf during extrapolation bisects the step
 (minimize.m:94-103).  Returns (X, fX list, number of function evaluations).
+
+This file is a Python restatement of minimize.m and keeps its notice, as the
+GPML licence (FreeBSD) asks:
+
+  minimize.m -- Copyright (C) 2001 - 2010 by Carl Edward Rasmussen, 2010-01-03.
+  GPML Toolbox 4.0 -- Copyright (c) 2005-2016 Carl Edward Rasmussen & Hannes
+  Nickisch.  All rights reserved.  Redistribution and use in source and binary
+  forms, with or without modification, are permitted provided that the
+  following conditions are met: 1. Redistributions of source code must retain
+  the above copyright notice, this list of conditions and the following
+  disclaimer.  2. Redistributions in binary form must reproduce the above
+  copyright notice, this list of conditions and the following disclaimer in the
+  documentation and/or other materials provided with the distribution.
+  THIS SOFTWARE IS PROVIDED BY CARL EDWARD RASMUSSEN & HANNES NICKISCH "AS IS"
+  AND ANY EXPRESS OR IMPLIED WARRANTIES, INCLUDING, BUT NOT LIMITED TO, THE
+  IMPLIED WARRANTIES OF MERCHANTABILITY AND FITNESS FOR A PARTICULAR PURPOSE ARE
+  DISCLAIMED.  IN NO EVENT SHALL CARL EDWARD RASMUSSEN & HANNES NICKISCH OR
+  CONTRIBUTORS BE LIABLE FOR ANY DIRECT, INDIRECT, INCIDENTAL, SPECIAL,
+  EXEMPLARY, OR CONSEQUENTIAL DAMAGES HOWEVER CAUSED AND ON ANY THEORY OF
+  LIABILITY ARISING IN ANY WAY OUT OF THE USE OF THIS SOFTWARE, EVEN IF ADVISED
+  OF THE POSSIBILITY OF SUCH DAMAGE.
+
+There is ONE copy of this logic in the repository: the tests (KAT-2 of the GPML
+manual, 14.13 / 0.15) run on this file; the oracle has no optimiser of its own.
 """
 import numpy as np
 

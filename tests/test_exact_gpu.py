@@ -95,7 +95,7 @@ def test_backend_interface_mirror(built_lib):
     """tests/backend/test_gpml.py scenarios (N=100, D=1, seed 42): same calls, same types and shapes --
     plus the numbers, which the reference's tests never check."""
     import gpml_exact as orc
-    from gpml_minimize import minimize
+    from kgp_b200.minimize import minimize
     from kgp_b200 import GP_BACKEND
     rng = np.random.RandomState(42)
     N, D = 100, 1

@@ -5,7 +5,7 @@ import numpy as np
 import scipy.linalg as sla
 
 import gpml_exact as orc
-from gpml_minimize import minimize
+from kgp_b200.minimize import minimize
 
 
 def demo_data():
