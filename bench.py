@@ -26,6 +26,13 @@ import time
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
+# The CPU arm must use every host core at every N: torchrun exports OMP_NUM_THREADS=1 to its workers, which would hand
+# the oracle's BLAS a single thread (round 1: `cores` 16 at N=1, 1 at N=2/4/8).  Set the BLAS pools BEFORE numpy loads.
+_NCPU = os.cpu_count() or 1
+if int(os.environ.get('RANK', 0)) == 0:
+    for _k in ('OMP_NUM_THREADS', 'OPENBLAS_NUM_THREADS', 'MKL_NUM_THREADS'):
+        os.environ[_k] = str(_NCPU)
+
 import numpy as np
 
 
@@ -67,6 +74,57 @@ class ClockSampler(threading.Thread):
         reasons = [nm for k, nm in enumerate(names) if any(s[3 + k].lower().startswith('active') for s in self.samples)]
         return {'sm_mhz': sm[len(sm) // 2], 'sm_max_mhz': float(self.samples[0][1]),
                 'power_w_max': max(float(s[2]) for s in self.samples), 'reasons': reasons, 'samples': len(sm)}
+
+
+def cpu_model():
+    try:
+        for ln in open('/proc/cpuinfo'):
+            if ln.startswith('model name'):
+                return ln.split(':', 1)[1].strip()
+    except Exception:
+        pass
+    return 'unknown'
+
+
+def use_all_cores():
+    """BLAS pools at os.cpu_count() threads (belt and braces beside the environment variables above)."""
+    try:
+        from threadpoolctl import threadpool_limits
+        threadpool_limits(limits=_NCPU)
+    except Exception:
+        pass
+
+
+def _fit_cubic(ns, ts):
+    """t(n) = a n^3 + b n^2, a, b >= 0: the O(n^3) factorisation / triangular solves plus the O(n^2 D) passes."""
+    ns = np.asarray(ns, dtype=np.float64); ts = np.asarray(ts, dtype=np.float64)
+    A = np.stack([ns ** 3, ns ** 2], 1) / ts[:, None]              # relative residuals
+    sol = np.linalg.lstsq(A, np.ones(len(ns)), rcond=None)[0]
+    if sol[0] < 0 or sol[1] < 0:                                    # one term suffices
+        a = float(np.mean(ts / ns ** 3)); b = 0.0
+        if sol[0] < 0:
+            a, b = 0.0, float(np.mean(ts / ns ** 2))
+        return a, b
+    return float(sol[0]), float(sol[1])
+
+
+def cpu_fit(sizes, n_target, D=8):
+    """Oracle evaluation time MEASURED at each of `sizes` on all host cores, then the two-term cost model
+    t(n) = a n^3 + b n^2 fitted to the points and evaluated at n_target.  `loo_error` is the error bar of that
+    extrapolation: the largest measured size predicted from a fit of the smaller ones, against its measurement."""
+    use_all_cores()
+    ts = [cpu_eval_seconds(n) for n in sizes]
+    a, b = _fit_cubic(sizes, ts)
+    out = {'model': 't = a n^3 + b n^2', 'n': list(map(int, sizes)), 'seconds': [float(t) for t in ts], 'a': a, 'b': b,
+           'predicted_seconds_at_target': a * float(n_target) ** 3 + b * float(n_target) ** 2, 'n_target': int(n_target),
+           'n3_from_largest_seconds': float(ts[-1]) * (n_target / float(sizes[-1])) ** 3}
+    if len(sizes) >= 3:
+        a2, b2 = _fit_cubic(sizes[:-1], ts[:-1])
+        pred = a2 * float(sizes[-1]) ** 3 + b2 * float(sizes[-1]) ** 2
+        out['loo_error'] = {'n': int(sizes[-1]), 'predicted_s': pred, 'measured_s': float(ts[-1]), 'rel': pred / float(ts[-1]) - 1.0}
+    ln, lt = np.log(np.asarray(sizes, dtype=np.float64)), np.log(np.asarray(ts))
+    out['local_exponent_last_two'] = float((lt[-1] - lt[-2]) / (ln[-1] - ln[-2]))
+    return out
 
 
 def cpu_eval_seconds(n_s, D=8, reps=1):

@@ -1,6 +1,6 @@
 // C ABI of libkgp_b200.so (declared in include/kgp_b200.h).
 #include "ctx.h"
-#include "dgemm_nt.cuh"
+#include "dgemm_nt_tma.cuh"
 #include <string.h>
 #include <math.h>
 #include <new>

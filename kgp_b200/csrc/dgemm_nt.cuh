@@ -11,12 +11,10 @@
 //   128x128 C tile, 256 threads = 8 warps as 2(m) x 4(n), warp tile 64x32 =
 //   8x4 DMMA tiles, 64 FP64 accumulators per thread.
 //   K is consumed in steps of BK=16 through a 4-stage cp.async ring in shared
-//   memory (32 KB per stage).  A stage holds two "k-slabs" of 8 doubles per row,
-//   stored [slab][row][8]; a thread fetches its A/B fragments with one LDS.128
-//   that yields the operands of TWO consecutive DMMA k-steps: inside a slab the
-//   K order is permuted (step0 uses k={0,2,4,6}, step1 uses k={1,3,5,7}) for A
-//   and B alike, which leaves the dot product unchanged and makes the quarter-
-//   warp LDS.128 pattern bank-conflict free without padding.
+//   memory (32 KB per stage).  A stage is stored [k4-step][row][4]: the four K
+//   values of one DMMA k-step are contiguous per row, so a thread's fragment
+//   element is sA[(step*128 + row)*4 + tq] and a warp's LDS.64 touches 8 rows x
+//   4 consecutive doubles = 32 distinct banks-pairs (conflict-free, no padding).
 // All extents are multiples of 128 (rows/cols) and 16 (K): the engine pads the
 // matrix order to a multiple of 128 with an identity block, so there are no
 // bounds checks in the hot loop.
@@ -145,6 +143,7 @@ struct GemmTile {
   int m0, n0, nk; bool in_diag;
   const double* Ag; const double* Bg;
   long coff;                   // offset of the problem's C origin (batched mode), else 0
+  int arow, brow, kc;          // the same tile as coordinates relative to g.A / g.B (TMA path): first A row, first B row, first k
 };
 __device__ __forceinline__ bool gemm_fetch_tile(const GemmArgs& g, long idx, long ntiles, GemmTile& t) {
   if (idx < ntiles) {
@@ -162,6 +161,7 @@ __device__ __forceinline__ bool gemm_fetch_tile(const GemmArgs& g, long idx, lon
       t.Ag = g.A + (long)(roff + t.m0) * g.lda + g.kbeg;
       t.Bg = g.B + (long)(roff + t.n0) * g.ldb + g.kbeg;
       t.coff = (long)roff * g.ldc + roff;
+      t.arow = roff + t.m0; t.brow = roff + t.n0; t.kc = g.kbeg;
       return true;
     }
     gemm_tile_coords(g, g.own_mod > 1 ? idx * g.own_mod + g.own_rem : idx, tm, tn);
@@ -172,6 +172,7 @@ __device__ __forceinline__ bool gemm_fetch_tile(const GemmArgs& g, long idx, lon
     t.nk = (g.kend - kbeg) / GEMM_BK;
     t.Ag = g.A + (long)t.m0 * g.lda + kbeg;
     t.Bg = g.B + (long)t.n0 * g.ldb + kbeg;
+    t.arow = t.m0; t.brow = t.n0; t.kc = kbeg;
     return true;
   }
   return false;
@@ -345,37 +346,6 @@ inline cudaError_t gemm_init() {
   cudaError_t e1 = cudaFuncSetAttribute(dgemm_nt_kernel_t<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, GEMM_STAGES * (GEMM_BM + 64) * GEMM_BK * 8);
   if (e1 != cudaSuccess) return e1;
   return cudaFuncSetAttribute(dgemm_nt_kernel_t<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, GEMM_SMEM_BYTES);
-}
-
-// tile_ctas: one CTA per tile instead of persistent CTAs -- a higher-priority stream's kernels (panel factorisation,
-// NCCL) then get SMs at tile granularity (~80 us) instead of waiting for the whole launch
-inline void gemm_launch(const GemmArgs& g_in, cudaStream_t st, bool tile_ctas = false) {
-  GemmArgs g = g_in;
-  long nt = gemm_num_tiles(g);
-  if (g.shape == GEMM_LOWER) {
-    long base = 0; int nb_ = 0;
-    for (int r0 = 0; r0 < g.ntm && nb_ < GEMM_MAX_BANDS; r0 += 8) {
-      g.band_base[nb_++] = (int)base;
-      for (int r = r0; r < r0 + 8 && r < g.ntm; ++r) base += (r + 1 < g.ntn) ? r + 1 : g.ntn;
-    }
-    g.nbands = nb_;
-  }
-  if (g.nbatch > 0) {
-    long base = 0;
-    for (int p = 0; p < g.nbatch; ++p) { g.bat_base[p] = (int)base; base += (long)(g.ntm - g.bat_roff[p] / 128) * g.ntn; }
-    g.bat_base[g.nbatch] = (int)base;
-  }
-  if (g.own_mod > 1) nt = (nt > g.own_rem) ? (nt - g.own_rem + g.own_mod - 1) / g.own_mod : 0;
-  if (nt <= 0 || g.kend <= g.kbeg) return;
-  g.cdiag_only = g_gemm_prefetch_c;
-  if (g_gemm_bn == 64) {
-    const long items = 2 * nt, res = 2L * g_gemm_num_sms;
-    const long grid = (g_gemm_persist && !tile_ctas && items > res) ? res : items;
-    dgemm_nt_kernel_t<64><<<(unsigned)grid, 128, GEMM_STAGES * (GEMM_BM + 64) * GEMM_BK * 8, st>>>(g, items);
-    return;
-  }
-  long grid = (g_gemm_persist && !tile_ctas && nt > g_gemm_num_sms) ? g_gemm_num_sms : nt;
-  dgemm_nt_kernel_t<128><<<(unsigned)grid, GEMM_THREADS, GEMM_SMEM_BYTES, st>>>(g, nt);
 }
 
 }  // namespace kgp

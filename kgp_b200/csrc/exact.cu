@@ -471,9 +471,11 @@ int exact_eval(kgp_ctx* c, int slot, int want, double* nlZ_out, double* dnlZ_out
   c->stats.kernel_launches += 4;
   cudaEventRecord(c->ev[1], st);
   const bool dist = c->nranks > 1;
-  static const bool lookahead = getenv("KGP_LOOKAHEAD") && atoi(getenv("KGP_LOOKAHEAD")) != 0;
+  // look-ahead (panel k+1 factored on the high-priority stream under trailing update k) is the default; it is switched
+  // off while per-launch GEMM profiling is on, because overlapped launches blur the event pairs around each GEMM
+  static const bool lookahead = !(getenv("KGP_LOOKAHEAD") && atoi(getenv("KGP_LOOKAHEAD")) == 0);
   if (dist) { rc = potrf_dist(c); if (rc) return rc; }
-  else if (lookahead && c->np >= 4 * NB) { rc = potrf_lookahead(c); if (rc) return rc; }
+  else if (lookahead && !c->profiling && c->np >= 4 * NB) { rc = potrf_lookahead(c); if (rc) return rc; }
   else potrf(c);
   logdet_kernel<<<1, 1024, 0, st>>>(c->M.d(), np, n, c->scal.d() + 100);
   c->stats.kernel_launches++;
@@ -491,7 +493,8 @@ int exact_eval(kgp_ctx* c, int slot, int want, double* nlZ_out, double* dnlZ_out
     c->stats.kernel_launches += 4;
   }
   cudaEventRecord(c->ev[4], st);
-  static const bool tile_reduce = getenv("KGP_TILE_REDUCE") && atoi(getenv("KGP_TILE_REDUCE"));
+  // symmetric gradient pass over the lower tiles of B^-1 (reads 4n^2 bytes instead of 8n^2, no mirror pass) is the default
+  static const bool tile_reduce = !(getenv("KGP_TILE_REDUCE") && atoi(getenv("KGP_TILE_REDUCE")) == 0);
   if (want >= 1 && (dist || tile_reduce)) {
     rc = zzt_reduce_dist(c, n, sf2, 1.0 / sn2); if (rc) return rc;
     grad_scalars_kernel<<<1, 1024, 0, st>>>(c->rows.d(), n, Dp, c->xs.d(), c->alpha.d(), c->scal.d());
@@ -642,6 +645,7 @@ int exact_predict(kgp_ctx* c, const double* Xs, long ns, double* ymu, double* ys
 
 int exact_init(kgp_ctx* c) {
   KGP_CUDA(c, gemm_init());
+  KGP_CUDA(c, gemm_tma_init());
   KGP_CUDA(c, cudaFuncSetAttribute(potrf_diag128_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, PD_SMEM));
   KGP_CUDA(c, cudaFuncSetAttribute(trsm128_rows_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, TR_SMEM));
   KGP_CUDA(c, cudaFuncSetAttribute(kbuild_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kbuild_smem(32)));

@@ -4,7 +4,7 @@
 // (chol, log-det, inverse), GPML/inf/infGaussLik.m:25-32 (alpha, nlZ, dnlZ),
 // kgp/backend/utils/dlikExact.m:19-25 (input gradient), GPML/gp.m:151-164 (predict).
 #pragma once
-#include "dgemm_nt.cuh"
+#include "dgemm_nt_tma.cuh"
 #include <math.h>
 
 namespace kgp {
