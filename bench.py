@@ -288,24 +288,45 @@ def small_config_legs(device):
 
 
 def epoch_leg(device):
-    """one training epoch of BASELINE configs[0] (README GP-RNN: SimpleRNN(32) -> exact GP covSEiso,
-    (10,2) sequences, 512 train, batch 32, one GP update with gp_n_iter = 5) through the PyTorch restatement of
-    UpdateGP + gen_gp_loss (kgp_b200/harness.py); reports the GP-update share, i.e. what the reference pays through
-    oct2py per epoch."""
+    """training epochs of the reference-sized BASELINE configs through the PyTorch restatement of UpdateGP +
+    gen_gp_loss (kgp_b200/harness.py): C1 README GP-RNN (SimpleRNN(32) -> exact GP covSEiso, (10,2) sequences, 512 train,
+    batch 32), C3 msgp_mlp_kin40k (MLP -> KISS-GP covSEiso on a 2-D feature grid, n = 40 000, k = 70, cg 2000/1e-6) and
+    C4 msgp_lstm_actuator (LSTM(16) -> KISS-GP, n = 460, k = 100, cg 500/1e-4); gp_n_iter = 5 each.  Reports the epoch
+    time and the GP-update share, i.e. what the reference pays through oct2py per epoch."""
     import torch
     from kgp_b200 import harness
+    out = {}
+
+    def run(name, net, head, Xt, y, opt, bs, desc):
+        harness.fit(net, head, Xt, y, opt, epochs=1, batch_size=bs, gp_n_iter=5)            # warm-up epoch
+        torch.cuda.synchronize(); t0 = time.perf_counter()
+        hist = harness.fit(net, head, Xt, y, opt, epochs=3, batch_size=bs, gp_n_iter=5)
+        torch.cuda.synchronize(); per = (time.perf_counter() - t0) / 3
+        out[name] = {'config': desc, 'epoch_ms': 1e3 * per, 'gp_update_ms': 1e3 * float(np.mean([h['gp_update_elapsed'] for h in hist])),
+                     'nlml_last': float(hist[-1]['nlml'])}
+
     torch.manual_seed(0); rng = np.random.RandomState(42)
     X = rng.randn(512, 10, 2).astype(np.float32); y = np.sin(X.sum((1, 2)) / 4)[:, None] + 0.1 * rng.randn(512, 1)
     net = harness.make_net('rnn', (10, 2), hidden=32).cuda(device)
     head = harness.GPHead(32, {'lik': -2.0, 'mean': [], 'cov': np.array([[-0.7], [0.0]])}, inf='infExact', cov='covSEiso', device=device)
-    Xt = torch.from_numpy(X).cuda(device)
-    opt = torch.optim.RMSprop(net.parameters(), lr=1e-3)
-    harness.fit(net, head, Xt, y, opt, epochs=1, batch_size=32, gp_n_iter=5)            # warm-up epoch
-    torch.cuda.synchronize(); t0 = time.perf_counter()
-    hist = harness.fit(net, head, Xt, y, opt, epochs=3, batch_size=32, gp_n_iter=5)
-    torch.cuda.synchronize(); per = (time.perf_counter() - t0) / 3
-    return {'config': 'README GP-RNN n=512, 16 mini-batches, gp_n_iter=5', 'epoch_ms': 1e3 * per,
-            'gp_update_ms': 1e3 * float(np.mean([h['gp_update_elapsed'] for h in hist])), 'nlml_last': float(hist[-1]['nlml'])}
+    run('c1_gp_rnn', net, head, torch.from_numpy(X).cuda(device), y, torch.optim.RMSprop(net.parameters(), lr=1e-3), 32,
+        'README GP-RNN n=512, 16 mini-batches, gp_n_iter=5')
+    torch.manual_seed(1); rng = np.random.RandomState(44)
+    X = rng.randn(40000, 8).astype(np.float32); y = (np.sin(X[:, 0] * X[:, 1]) + X[:, 2])[:, None] + 0.1 * rng.randn(40000, 1)
+    net = harness.make_net('mlp', (8,), hidden=16, out_dim=2).cuda(device)
+    head = harness.GPHead(2, {'lik': np.log(0.3), 'mean': [], 'cov': np.array([[0.5], [1.0]])}, inf='infGrid', cov='covSEiso',
+                          opt={'cg_maxit': 2000, 'cg_tol': 1e-6}, grid_kwargs={'eq': 1, 'k': 70.}, update_grid=1, device=device)
+    run('c3_msgp_mlp', net, head, torch.from_numpy(X).cuda(device), y, torch.optim.Adam(net.parameters(), lr=1e-3), 128,
+        'msgp_mlp_kin40k n=40000, 2-D grid 70x70, 313 mini-batches, gp_n_iter=5')
+    torch.manual_seed(3); rng = np.random.RandomState(45)
+    u = np.cumsum(rng.randn(1024 + 33)) * 0.1; yy = np.tanh(np.convolve(u, np.ones(8) / 8, 'same'))
+    X = np.stack([u[i:i + 32] for i in range(460)])[:, :, None].astype(np.float32); y = yy[32:32 + 460][:, None]
+    net = harness.make_net('lstm', (32, 1), hidden=16, out_dim=1).cuda(device)
+    head = harness.GPHead(1, {'lik': -2.0, 'mean': [], 'cov': [[-0.7], [0.0]]}, inf='infGrid', cov='covSEiso',
+                          opt={'cg_maxit': 500, 'cg_tol': 1e-4}, grid_kwargs={'eq': 1, 'k': 100.}, update_grid=1, device=device)
+    run('c4_gp_lstm', net, head, torch.from_numpy(X).cuda(device), y, torch.optim.Adam(net.parameters(), lr=1e-2), 128,
+        'msgp_lstm_actuator n=460, grid k=100, 4 mini-batches, gp_n_iter=5')
+    return out
 
 
 def kissgp_sharded_leg(n_total, device, steps, warmup, world):
@@ -526,7 +547,7 @@ def main():
         kiss = kissgp_leg(args.kissgp_n, local, args.steps, args.warmup, with_cpu=not args.no_cpu)
         try:
             small = small_config_legs(local)
-            small['c1_gp_rnn_epoch'] = epoch_leg(local)
+            small['epochs'] = epoch_leg(local)
         except Exception as ex:                       # secondary information only
             small = {'error': str(ex)}
 

@@ -135,6 +135,9 @@ int kgp_predict_host(kgp_ctx* ctx, const double* Xs, long ns,
  * GPML/cov/apxGrid.m:389-416) and push('xg', ...) (kgp/backend/gpml.py:125-126). */
 int kgp_grid_create(kgp_ctx* ctx, int slot, int eq, double k);
 int kgp_grid_set_host(kgp_ctx* ctx, int n_axes, const int* axis_len, const double* axes_concat);
+/* GPML's equi() test for one axis (GPML/cov/apxGrid.m:684-695): 1 when max|diff(a) - (a[1]-a[0])| < 1e-9 and the axis
+ * increases.  kgp_grid_set_host refuses axes that fail it (the neqinterp branch is not built).  Host logic, no GPU. */
+int kgp_grid_axis_equispaced(const double* axis, int len);
 int kgp_grid_get_host(kgp_ctx* ctx, int* n_axes, int* axis_len /* >= 16 ints */, double* axes_concat /* may be NULL */);
 
 /* Chebyshev-Hutchinson log-det (opt.ldB2_cheby = 1; GPML/cov/apx.m:336-391): inject the probe vectors

@@ -64,6 +64,7 @@ SIGNATURES = {
     'kgp_predict_host': (C.c_int, [C.c_void_p, C.c_void_p, C.c_long, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     'kgp_grid_create': (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_double]),
     'kgp_grid_set_host': (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]),
+    'kgp_grid_axis_equispaced': (C.c_int, [C.c_void_p, C.c_int]),
     'kgp_grid_get_host': (C.c_int, [C.c_void_p, C.POINTER(C.c_int), C.c_void_p, C.c_void_p]),
     'kgp_get_alpha_host': (C.c_int, [C.c_void_p, C.c_void_p]),
     'kgp_last_stats': (C.c_int, [C.c_void_p, C.POINTER(KgpStats)]),
@@ -177,6 +178,17 @@ class Context(object):
                 v = int(np.ceil(abs(float(v))))                  # infGrid.m:94
             if hasattr(o, k):
                 setattr(o, k, type(getattr(o, k))(v))
+            elif k == 'deg' and int(v) == 3:
+                pass                                             # cubic interpolation is what the engine builds (apx.m:123 default)
+            elif k == 'stat' and not v:
+                pass
+            elif k in ('deg', 'proj', 'ndcovs', 'stat'):
+                # GPML options that change the numbers (apx.m:123, infGrid.m:56,70): refusing beats returning cubic /
+                # un-projected results as if the option had been honoured
+                raise ValueError('opt.%s=%r is not supported by the B200 engine' % (k, v))
+            else:
+                import warnings
+                warnings.warn('opt.%s is not a known GPML option of this path; ignored' % k)
         self._chk(self._l.kgp_set_model(self._h, INF[inf], COV[cov], int(sm_Q), int(mean_mask), _ptr(hc), hc.size,
                                         float(hyp_lik), _ptr(hm), hm.size, C.byref(o)))
 

@@ -89,7 +89,7 @@ int kgp_ctx_destroy(kgp_ctx* c) {
   dist_free(c);
   DevBuf* bufs[] = {&c->M, &c->W2, &c->Dws, &c->xs, &c->s, &c->mu, &c->inv_ell, &c->ym, &c->alpha, &c->tvec,
                     &c->parts, &c->rows, &c->scal, &c->hypm, &c->dX, &c->fac, &c->pred_K, &c->pred_x, &c->pred_s,
-                    &c->pred_a, &c->pred_b, &c->pred_out, &c->pred_X};
+                    &c->pred_a, &c->pred_b, &c->pred_out, &c->pred_X, &c->smV, &c->smM, &c->smAcc};
   for (DevBuf* b : bufs) b->release();
   for (auto& s : c->slots) { s.X.release(); s.y.release(); }
   if (c->d_info) cudaFree(c->d_info);
@@ -170,7 +170,6 @@ int kgp_set_model(kgp_ctx* c, int inf_kind, int cov_kind, int sm_Q, int mean_mas
   if (!c) return KGP_BAD_ARG;
   if (inf_kind != KGP_INF_EXACT && inf_kind != KGP_INF_GRID) return c->fail(KGP_BAD_ARG, "unknown inference method %d", inf_kind);
   if (cov_kind < KGP_COV_SEISO || cov_kind > KGP_COV_SM) return c->fail(KGP_BAD_ARG, "unknown covariance %d", cov_kind);
-  if (inf_kind == KGP_INF_EXACT && cov_kind == KGP_COV_SM) return c->fail(KGP_BAD_ARG, "covSM is supported on the infGrid path only");
   if (n_cov < 0 || n_mean < 0 || (n_cov && !hyp_cov) || (n_mean && !hyp_mean)) return c->fail(KGP_BAD_ARG, "bad hyp arrays");
   if (mean_mask & ~3) return c->fail(KGP_BAD_ARG, "unknown mean mask %d", mean_mask);
   Model& m = c->model;
@@ -224,14 +223,30 @@ int kgp_grid_create(kgp_ctx* c, int slot, int eq, double k) {
   cudaSetDevice(c->device);
   return grid_create(c, slot, eq, k);
 }
+// the reference's per-axis dispatch test (GPML/cov/apxGrid.m:684-695 equi): max |diff(a) - (a(2)-a(1))| < 1e-9; a usable
+// interpolation axis must also increase
+int kgp_grid_axis_equispaced(const double* a, int len) {
+  if (!a || len < 2) return 0;
+  const double d0 = a[1] - a[0];
+  if (!(d0 > 0.0)) return 0;
+  double dev = 0.0;
+  for (int i = 1; i < len; ++i) { const double e = fabs((a[i] - a[i - 1]) - d0); if (e > dev || e != e) dev = e != e ? 1.0 : e; }
+  return dev < 1e-9 ? 1 : 0;
+}
 int kgp_grid_set_host(kgp_ctx* c, int n_axes, const int* axis_len, const double* axes) {
   if (!c || n_axes <= 0 || n_axes > 16 || !axis_len || !axes) return c ? c->fail(KGP_BAD_ARG, "bad grid") : KGP_BAD_ARG;
-  c->grid.axes.clear();
   long o = 0;
   for (int a = 0; a < n_axes; ++a) {
     if (axis_len[a] < 4) return c->fail(KGP_BAD_ARG, "grid axis %d needs >= 4 points", a);
-    c->grid.axes.emplace_back(axes + o, axes + o + axis_len[a]); o += axis_len[a];
+    // interpgrid / deriv_x dispatch on equi(xg,i) (apxGrid.m:447-449, deriv_x.m:11-15); the non-equispaced branch
+    // (neqinterp, wi = 1) is not built, so such an axis is refused instead of being silently treated as equispaced
+    if (!kgp_grid_axis_equispaced(axes + o, axis_len[a]))
+      return c->fail(KGP_BAD_ARG, "grid axis %d is not equispaced and increasing: only equispaced grids are built", a);
+    o += axis_len[a];
   }
+  c->grid.axes.clear();
+  o = 0;
+  for (int a = 0; a < n_axes; ++a) { c->grid.axes.emplace_back(axes + o, axes + o + axis_len[a]); o += axis_len[a]; }
   c->grid.set = true; c->grid.version++;
   return KGP_OK;
 }

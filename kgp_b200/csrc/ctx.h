@@ -60,6 +60,7 @@ struct kgp_ctx {
   kgp::DevBuf M, W2, Dws;             // L (lower) | Z upper -> full B^{-1} | diagonal nb-blocks of B^{-1}
   kgp::DevBuf xs, s, mu, inv_ell, ym, alpha, tvec, parts, rows, scal, hypm, dX, fac;
   kgp::DevBuf pred_K, pred_x, pred_s, pred_a, pred_b, pred_out, pred_X;
+  kgp::DevBuf smV, smM, smAcc;        // covSM exact path: 4 pi^2 v, 2 pi m tables and the reduction accumulators
   int* d_info = nullptr;
   long np = 0; int Dp = 0;
   // what the factorisation state corresponds to

@@ -15,6 +15,7 @@
 #include "ctx.h"
 #include "exact_kernels2.cuh"
 #include "exact_dist.cuh"
+#include "exact_sm.cuh"
 #include <math.h>
 #include <string.h>
 
@@ -428,6 +429,50 @@ static int ensure_exact_buffers(kgp_ctx* c, long n, int D) {
   return KGP_OK;
 }
 
+// covSM (exact path): host-side unpacking of hyp = [log w; log m (D x Q); log sqrt v (D x Q)] (covSM.m:127-129) into the
+// kernel tables Vq = 4 pi^2 v, Mq = 2 pi m ([q][Dp], zero padded)
+static int sm_prepare(kgp_ctx* c, int D, int Dp, SmHyp& h, std::vector<double>& Vq, std::vector<double>& Mq) {
+  Model& m = c->model; const int Q = m.sm_Q;
+  if (Q < 1 || Q > SM_MAXQ) return c->fail(KGP_BAD_ARG, "covSM needs 1 <= Q <= %d (got %d)", SM_MAXQ, Q);
+  if (D > 16) return c->fail(KGP_BAD_ARG, "exact covSM supports input_dim <= 16 (got %d)", D);
+  if ((int)m.hyp_cov.size() != (1 + 2 * D) * Q)
+    return c->fail(KGP_BAD_ARG, "Wrong number of hyperparameters (cov): got %d, need %d", (int)m.hyp_cov.size(), (1 + 2 * D) * Q);
+  memset(&h, 0, sizeof h); h.Q = Q;
+  Vq.assign((size_t)Q * Dp, 0.0); Mq.assign((size_t)Q * Dp, 0.0);
+  for (int q = 0; q < Q; ++q) {
+    h.w[q] = exp(m.hyp_cov[q]);
+    for (int d = 0; d < D; ++d) {
+      Mq[(size_t)q * Dp + d] = 2.0 * M_PI * exp(m.hyp_cov[Q + q * D + d]);
+      Vq[(size_t)q * Dp + d] = 4.0 * M_PI * M_PI * exp(2.0 * m.hyp_cov[Q + D * Q + q * D + d]);
+    }
+  }
+  KGP_CUDA(c, c->smV.ensure(Vq.size() * 8)); KGP_CUDA(c, c->smM.ensure(Mq.size() * 8));
+  KGP_CUDA(c, cudaMemcpyAsync(c->smV.p, Vq.data(), Vq.size() * 8, cudaMemcpyHostToDevice, c->stream));
+  KGP_CUDA(c, cudaMemcpyAsync(c->smM.p, Mq.data(), Mq.size() * 8, cudaMemcpyHostToDevice, c->stream));
+  KGP_CUDA(c, cudaStreamSynchronize(c->stream));               // Vq / Mq are locals of the caller
+  return KGP_OK;
+}
+template <int DP>
+static void launch_sm_build(kgp_ctx* c, const double* xr, long nR, long rowsp, const double* xc, long nC, long colsp, const SmHyp& h,
+                            double scale, int diag_add, int lower_only, double* out, long ld) {
+  dim3 grid((unsigned)(colsp / 32), (unsigned)(rowsp / 128));
+  sm_build_kernel<DP><<<grid, 128, 0, c->stream>>>(xr, nR, xc, nC, h, c->smV.d(), c->smM.d(), scale, diag_add, lower_only, out, ld);
+}
+static void sm_build(kgp_ctx* c, int Dp, const double* xr, long nR, long rowsp, const double* xc, long nC, long colsp, const SmHyp& h,
+                     double scale, int diag_add, int lower_only, double* out, long ld) {
+  switch (Dp) {
+    case 4: launch_sm_build<4>(c, xr, nR, rowsp, xc, nC, colsp, h, scale, diag_add, lower_only, out, ld); break;
+    case 8: launch_sm_build<8>(c, xr, nR, rowsp, xc, nC, colsp, h, scale, diag_add, lower_only, out, ld); break;
+    default: launch_sm_build<16>(c, xr, nR, rowsp, xc, nC, colsp, h, scale, diag_add, lower_only, out, ld); break;
+  }
+  c->stats.kernel_launches++;
+}
+template <int DP>
+static void launch_sm_reduce(kgp_ctx* c, long n, int D, const SmHyp& h, double inv_sn2, int nsplit, int per, double* acc) {
+  dim3 grid((unsigned)(c->np / 128), (unsigned)nsplit, (unsigned)h.Q);
+  sm_reduce_kernel<DP><<<grid, 128, 0, c->stream>>>(c->W2.d(), c->np, n, c->xs.d(), c->alpha.d(), h, c->smV.d(), c->smM.d(), inv_sn2, per, D, acc, c->dX.d());
+}
+
 static float ev_ms(cudaEvent_t a, cudaEvent_t b) { float ms = 0; cudaEventElapsedTime(&ms, a, b); return ms; }
 
 // ---------------------------------------------------------------------------
@@ -435,9 +480,10 @@ int exact_eval(kgp_ctx* c, int slot, int want, double* nlZ_out, double* dnlZ_out
   Slot& S = c->slots[slot]; Model& m = c->model;
   const long n = S.n; const int D = S.D;
   if (D > 32) return c->fail(KGP_BAD_ARG, "exact path supports input_dim <= 32 (got %d)", D);
-  const bool ard = m.cov_kind == KGP_COV_SEARD;
+  const bool ard = m.cov_kind == KGP_COV_SEARD, sm = m.cov_kind == KGP_COV_SM;
   const int nl = ard ? D : 1;
-  if ((int)m.hyp_cov.size() != nl + 1) return c->fail(KGP_BAD_ARG, "Wrong number of hyperparameters (cov): got %d, need %d", (int)m.hyp_cov.size(), nl + 1);
+  if (!sm && (int)m.hyp_cov.size() != nl + 1) return c->fail(KGP_BAD_ARG, "Wrong number of hyperparameters (cov): got %d, need %d", (int)m.hyp_cov.size(), nl + 1);
+  if (sm && c->nranks > 1) return c->fail(KGP_BAD_ARG, "exact covSM runs on one GPU (the sharded exact path covers covSEiso / covSEard)");
   const int nmean = ((m.mean_mask & 1) ? D : 0) + ((m.mean_mask & 2) ? 1 : 0);
   if ((int)m.hyp_mean.size() != nmean) return c->fail(KGP_BAD_ARG, "Number of mean function hyperparameters disagree with mean function");
   int rc = ensure_exact_buffers(c, n, D); if (rc) return rc;
@@ -445,11 +491,13 @@ int exact_eval(kgp_ctx* c, int slot, int want, double* nlZ_out, double* dnlZ_out
   cudaStream_t st = c->stream;
   memset(&c->stats, 0, sizeof c->stats); c->stats.n = n; c->stats.np = np;
   c->st_level = -1;
+  SmHyp smh; std::vector<double> smVq, smMq;
+  if (sm) { rc = sm_prepare(c, D, Dp, smh, smVq, smMq); if (rc) return rc; }
 
-  const double sn2 = exp(2.0 * m.hyp_lik), sf2 = exp(2.0 * m.hyp_cov[nl]);
+  const double sn2 = exp(2.0 * m.hyp_lik), sf2 = sm ? 1.0 : exp(2.0 * m.hyp_cov[nl]);
   double h_inv_ell[64], h_fac[64];
   for (int d = 0; d < D; ++d) {
-    double ell = exp(m.hyp_cov[ard ? d : 0]);
+    double ell = sm ? 1.0 : exp(m.hyp_cov[ard ? d : 0]);
     h_inv_ell[d] = 1.0 / ell;
     h_fac[d] = (ard && m.opt.ard_reference_form) ? ell / exp(2.0 * m.hyp_cov[0]) : 1.0 / ell;
   }
@@ -463,7 +511,8 @@ int exact_eval(kgp_ctx* c, int slot, int want, double* nlZ_out, double* dnlZ_out
   col_mean_kernel<<<D, 1024, 0, st>>>(S.X.d(), n, D, c->mu.d());
   scale_x_kernel<<<(unsigned)((np + 255) / 256), 256, 0, st>>>(S.X.d(), n, D, c->mu.d(), c->inv_ell.d(), c->xs.d(), c->s.d(), np, Dp);
   resid_mean_kernel<<<(unsigned)((np + 255) / 256), 256, 0, st>>>(S.X.d(), S.has_y ? S.y.d() : nullptr, n, D, m.mean_mask, c->hypm.d(), c->ym.d(), np);
-  {
+  if (sm) sm_build(c, Dp, c->xs.d(), n, np, c->xs.d(), n, np, smh, 1.0 / sn2, 1, 1, c->M.d(), np);
+  else {
     dim3 grid((unsigned)(np / 128), (unsigned)(np / 128));
     kbuild_kernel<<<grid, KB_THREADS, kbuild_smem(Dp), st>>>(c->xs.d(), c->s.d(), n, c->xs.d(), c->s.d(), n, Dp,
                                                             sf2 / sn2, 1, 1, c->M.d(), np);
@@ -474,7 +523,13 @@ int exact_eval(kgp_ctx* c, int slot, int want, double* nlZ_out, double* dnlZ_out
   // look-ahead (panel k+1 factored on the high-priority stream under trailing update k) is the default; it is switched
   // off while per-launch GEMM profiling is on, because overlapped launches blur the event pairs around each GEMM
   static const bool lookahead = !(getenv("KGP_LOOKAHEAD") && atoi(getenv("KGP_LOOKAHEAD")) == 0);
-  if (dist) { rc = potrf_dist(c); if (rc) return rc; }
+  if (dist) {
+    rc = potrf_dist(c); if (rc) return rc;
+    // the failing-pivot flag is written by the owner of the failing panel only: make it global (min over the ranks) so
+    // that every rank returns the same status -- otherwise the ranks' optimisers diverge and the next collective hangs
+    NcclApi& api = nccl_api(nullptr);
+    KGP_NCCL(c, api, api.AllReduce(c->d_info, c->d_info, 1, KGP_NCCL_INT32, KGP_NCCL_MIN, c->nccl_comm, st));
+  }
   else if (lookahead && !c->profiling && c->np >= 4 * NB) { rc = potrf_lookahead(c); if (rc) return rc; }
   else potrf(c);
   logdet_kernel<<<1, 1024, 0, st>>>(c->M.d(), np, n, c->scal.d() + 100);
@@ -495,7 +550,27 @@ int exact_eval(kgp_ctx* c, int slot, int want, double* nlZ_out, double* dnlZ_out
   cudaEventRecord(c->ev[4], st);
   // symmetric gradient pass over the lower tiles of B^-1 (reads 4n^2 bytes instead of 8n^2, no mirror pass) is the default
   static const bool tile_reduce = !(getenv("KGP_TILE_REDUCE") && atoi(getenv("KGP_TILE_REDUCE")) == 0);
-  if (want >= 1 && (dist || tile_reduce)) {
+  if (want >= 1 && sm) {
+    // covSM: full symmetric B^-1 (Z Z^T + mirror), then one pass per mixture component (exact_sm.cuh)
+    zzt(c);
+    cudaEventRecord(c->ev[5], st);
+    const int ntr = (int)(np / 128), nt32 = (int)(np / 32);
+    int nsplit = (1184 + ntr * smh.Q - 1) / (ntr * smh.Q); if (nsplit < 1) nsplit = 1; if (nsplit > nt32) nsplit = nt32;
+    const int per = (nt32 + nsplit - 1) / nsplit; nsplit = (nt32 + per - 1) / per;
+    const size_t accn = 1 + (size_t)smh.Q * (1 + 2 * Dp);
+    KGP_CUDA(c, c->smAcc.ensure(accn * 8));
+    KGP_CUDA(c, cudaMemsetAsync(c->smAcc.p, 0, accn * 8, st));
+    KGP_CUDA(c, cudaMemsetAsync(c->dX.p, 0, (size_t)n * D * 8, st));
+    switch (Dp) {
+      case 4: launch_sm_reduce<4>(c, n, D, smh, 1.0 / sn2, nsplit, per, c->smAcc.d()); break;
+      case 8: launch_sm_reduce<8>(c, n, D, smh, 1.0 / sn2, nsplit, per, c->smAcc.d()); break;
+      default: launch_sm_reduce<16>(c, n, D, smh, 1.0 / sn2, nsplit, per, c->smAcc.d()); break;
+    }
+    dot_kernel<<<1, 1024, 0, st>>>(c->alpha.d(), c->alpha.d(), n, c->scal.d() + 3);
+    if (nmean) mean_grad_kernel<<<D + 1, 1024, 0, st>>>(S.X.d(), c->alpha.d(), n, D, c->scal.d() + 110);
+    c->stats.kernel_launches += 2 + (nmean ? 1 : 0);
+    cudaEventRecord(c->ev[6], st);
+  } else if (want >= 1 && (dist || tile_reduce)) {
     rc = zzt_reduce_dist(c, n, sf2, 1.0 / sn2); if (rc) return rc;
     grad_scalars_kernel<<<1, 1024, 0, st>>>(c->rows.d(), n, Dp, c->xs.d(), c->alpha.d(), c->scal.d());
     dx_from_rows_kernel<<<(unsigned)((n * D + 255) / 256), 256, 0, st>>>(c->rows.d(), n, D, Dp, c->fac.d(), c->dX.d());
@@ -545,7 +620,25 @@ int exact_eval(kgp_ctx* c, int slot, int want, double* nlZ_out, double* dnlZ_out
   const double nlZ = yta / 2.0 + ldB2 + (double)n * log(2.0 * M_PI * sn2) / 2.0;     // infGaussLik.m:29
   if (nlZ_out) *nlZ_out = nlZ;
   c->st_nlZ = nlZ; c->st_dnlZ.clear();
-  if (want >= 1) {
+  if (want >= 1 && sm) {
+    const int Q = smh.Q; const size_t accn = 1 + (size_t)Q * (1 + 2 * Dp);
+    std::vector<double> a(accn);
+    KGP_CUDA(c, cudaMemcpy(a.data(), c->smAcc.p, accn * 8, cudaMemcpyDeviceToHost));
+    std::vector<double> g((size_t)(1 + 2 * D) * Q);
+    for (int q = 0; q < Q; ++q) {                                          // dnlZ.cov = dKdhyp(R) / 2 (covSM.m:150-153, apx.m:173)
+      const double* aq = a.data() + 1 + (size_t)q * (1 + 2 * Dp);
+      g[q] = 0.5 * smh.w[q] * aq[0];
+      for (int d = 0; d < D; ++d) {
+        g[Q + q * D + d] = -0.5 * smh.w[q] * smMq[(size_t)q * Dp + d] * aq[1 + d];
+        g[Q + D * Q + q * D + d] = -0.5 * smh.w[q] * smVq[(size_t)q * Dp + d] * aq[1 + Dp + d];
+      }
+    }
+    g.push_back(-sn2 * h[3] - a[0] / sn2 + (double)n);                     // infGaussLik.m:32
+    if (m.mean_mask & 1) for (int d = 0; d < D; ++d) g.push_back(h[110 + d]);
+    if (m.mean_mask & 2) g.push_back(h[110 + D]);
+    c->st_dnlZ = g;
+    if (dnlZ_out) memcpy(dnlZ_out, g.data(), g.size() * 8);
+  } else if (want >= 1) {
     std::vector<double> g;
     if (ard) for (int d = 0; d < D; ++d) g.push_back(h[4 + d]);
     else g.push_back(0.5 * h[1]);
@@ -593,8 +686,12 @@ int exact_predict(kgp_ctx* c, const double* Xs, long ns, double* ymu, double* ys
   }
   Slot& S = c->slots[slot]; Model& m = c->model;
   const long n = S.n, np = c->np; const int D = S.D, Dp = c->Dp;
-  const bool ard = m.cov_kind == KGP_COV_SEARD; const int nl = ard ? D : 1;
-  const double sn2 = exp(2.0 * m.hyp_lik), sf2 = exp(2.0 * m.hyp_cov[nl]);
+  const bool ard = m.cov_kind == KGP_COV_SEARD, sm = m.cov_kind == KGP_COV_SM; const int nl = ard ? D : 1;
+  SmHyp smh; std::vector<double> smVq, smMq;
+  if (sm) { int rc = sm_prepare(c, D, Dp, smh, smVq, smMq); if (rc) return rc; }
+  double sf2 = 0.0;                                               // prior variance k(x*, x*): sf^2, or sum_q w_q for covSM
+  if (sm) for (int q = 0; q < smh.Q; ++q) sf2 += smh.w[q]; else sf2 = exp(2.0 * m.hyp_cov[nl]);
+  const double sn2 = exp(2.0 * m.hyp_lik);
   const bool want_var = ys2 || fs2;
   cudaStream_t st = c->stream;
   const long BATCH = 1024;
@@ -611,9 +708,12 @@ int exact_predict(kgp_ctx* c, const double* Xs, long ns, double* ymu, double* ys
     KGP_CUDA(c, cudaMemcpyAsync(c->pred_X.p, Xs + s0 * D, (size_t)nsb * D * 8, cudaMemcpyHostToDevice, st));
     scale_x_kernel<<<(unsigned)((nsp + 255) / 256), 256, 0, st>>>(c->pred_X.d(), nsb, D, c->mu.d(), c->inv_ell.d(),
                                                                   c->pred_x.d(), c->pred_s.d(), nsp, Dp);
-    dim3 grid((unsigned)(np / 128), (unsigned)(nsp / 128));
-    kbuild_kernel<<<grid, KB_THREADS, kbuild_smem(Dp), st>>>(c->pred_x.d(), c->pred_s.d(), nsb, c->xs.d(), c->s.d(), n,
-                                                            Dp, sf2, 0, 0, c->pred_K.d(), np);
+    if (sm) sm_build(c, Dp, c->pred_x.d(), nsb, nsp, c->xs.d(), n, np, smh, 1.0, 0, 0, c->pred_K.d(), np);
+    else {
+      dim3 grid((unsigned)(np / 128), (unsigned)(nsp / 128));
+      kbuild_kernel<<<grid, KB_THREADS, kbuild_smem(Dp), st>>>(c->pred_x.d(), c->pred_s.d(), nsb, c->xs.d(), c->s.d(), n,
+                                                              Dp, sf2, 0, 0, c->pred_K.d(), np);
+    }
     gemv_rows_kernel<<<(unsigned)((nsp + 7) / 8), 256, 0, st>>>(c->pred_K.d(), np, nsp, np, c->alpha.d(), c->pred_a.d());
     if (want_var) {
       double* X = c->pred_K.d(); const double* M = c->M.d();

@@ -29,7 +29,7 @@ struct NcclApi {
   int (*GroupEnd)() = nullptr;
   const char* (*GetErrorString)(int) = nullptr;
 };
-constexpr int KGP_NCCL_DOUBLE = 8, KGP_NCCL_SUM = 0, KGP_NCCL_INT8 = 0;   // ncclFloat64, ncclSum, ncclInt8 (nccl.h enum values)
+constexpr int KGP_NCCL_DOUBLE = 8, KGP_NCCL_SUM = 0, KGP_NCCL_INT8 = 0, KGP_NCCL_INT32 = 2, KGP_NCCL_MIN = 3;   // ncclFloat64, ncclSum, ncclInt8, ncclInt32, ncclMin (nccl.h enum values)
 // peer exchange window (see grid_cg.cuh CgDist), 16-byte packets: [2][8][PX_NCAP] grid partials, [2][8][4] scalars,
 // [2][PX_NCAP] locally combined grid vector
 constexpr long PX_NCAP = 32768;

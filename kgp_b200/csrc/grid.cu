@@ -1397,7 +1397,7 @@ int grid_create(kgp_ctx* c, int slot, int eq, double k) {
     KGP_CUDA(c, cudaMemcpyAsync(mm, g->out.p, 16, cudaMemcpyDeviceToHost, st));
     KGP_CUDA(c, cudaStreamSynchronize(st));
     if (!(mm[1] > mm[0])) return c->fail(KGP_BAD_ARG, "Two few unique points.");
-    long ngj;
+    double ngj;                                       // stays fractional in du (apxGrid.m:404-406); only linspace floors it
     if (k >= 0.0 && k <= 1.0) {                       // fraction of the unique values (apxGrid.m:402-403)
       long Npad = 1; while (Npad < n) Npad <<= 1;
       KGP_CUDA(c, g->sortk.ensure(Npad * 8)); KGP_CUDA(c, g->sorti.ensure(Npad * 4));
@@ -1411,11 +1411,11 @@ int grid_create(kgp_ctx* c, int slot, int eq, double k) {
       unsigned long long hc = 0;
       KGP_CUDA(c, cudaMemcpyAsync(&hc, cnt, 8, cudaMemcpyDeviceToHost, st));
       KGP_CUDA(c, cudaStreamSynchronize(st));
-      ngj = (long)ceil(k * (double)hc);
-    } else ngj = (long)k;
-    if (ngj < 1) return c->fail(KGP_BAD_ARG, "bad grid size k=%g", k);
-    const double du = (mm[1] - mm[0]) / (double)ngj, b0 = mm[0] - 5.0 * du, b1 = mm[1] + 5.0 * du;
-    const long np_ = std::max<long>(ngj, 5);
+      ngj = ceil(k * (double)hc);
+    } else ngj = k;
+    if (!(ngj >= 1.0)) return c->fail(KGP_BAD_ARG, "bad grid size k=%g", k);
+    const double du = (mm[1] - mm[0]) / ngj, b0 = mm[0] - 5.0 * du, b1 = mm[1] + 5.0 * du;
+    const long np_ = (long)floor(std::max(ngj, 5.0));  // Octave's linspace(a, b, n) uses floor(n) points
     std::vector<double> ax(np_);                      // Octave linspace: base + i*delta, last point exact
     const double delta = (b1 - b0) / (double)(np_ - 1);
     for (long i = 0; i < np_; ++i) ax[i] = b0 + (double)i * delta;

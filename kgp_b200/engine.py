@@ -81,6 +81,9 @@ class B200GP(object):
                 self.eng.grid_set([np.asarray(a, dtype=np.float64).reshape(-1) for a in xg])
             # same in-place tiling as gpml.py:134; GPML then reads it column-major
             hyp['cov'] = np.tile(hyp['cov'], (1, self.input_dim))
+        elif cov == 'covSM' and isinstance(hyp['cov'], (list, tuple)):
+            # multivariate covSM: [log w (Q); log m (D x Q); log sqrt v (D x Q)], each block column-major (covSM.m:127-129)
+            hyp['cov'] = np.concatenate([np.asarray(a, dtype=np.float64).reshape(-1, order='F') for a in hyp['cov']])[:, None]
         else:
             hyp['cov'] = np.asarray(hyp['cov'])
         self.hyp = {'cov': np.asarray(hyp['cov'], dtype=np.float64),
@@ -144,7 +147,7 @@ class B200GP(object):
         self.update_data('tst', X)
         if X_tr is not None and y_tr is not None:
             self.update_data('tr', X_tr, y_tr)
-        ymu, ys2 = self.eng.predict(np.asarray(X), want_var=True)
+        ymu, ys2 = self.eng.predict(np.asarray(X), want_var=bool(return_var))
         preds = ymu[:, None]
         if return_var:
             preds = (preds, ys2[:, None])
@@ -179,7 +182,7 @@ class B200GP(object):
         if X_tr is not None and y_tr is not None:
             self.update_data('tr', X_tr, y_tr)
         nlZ, _ = self._eval('tr', 1)
-        ymu, _ = self.eng.predict(np.asarray(X), want_var=not self.using_grid)
+        ymu, _ = self.eng.predict(np.asarray(X), want_var=False)       # only ymu is pulled (gpml.py:224-229)
         return nlZ, ymu[:, None]
 
     # -- extras the reference keeps in the Octave workspace -----------------

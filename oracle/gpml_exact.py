@@ -131,6 +131,57 @@ def cov_se_dirder(mode, hyp_cov, x, Q):
     return np.concatenate([dlen, [dsf]])
 
 
+# ----------------------------------------------------------------------------
+# spectral mixture, multivariate form (Q > 0): covSM.m:124-156 covSMfast
+#   hyp = [log w (Q); log m (D x Q, column-major); log sqrt(v) (D x Q)]
+# covmode ('sm', Q) selects it in inf_exact / gp_predict.
+# ----------------------------------------------------------------------------
+def _sm_unpack(Q, hyp, D):
+    hyp = np.asarray(hyp, dtype=np.float64).reshape(-1)
+    assert hyp.size == (1 + 2 * D) * Q, 'Wrong number of hyperparameters'
+    w = np.exp(hyp[:Q])
+    m = np.exp(hyp[Q:Q + D * Q].reshape(Q, D).T)                 # reshape(.,D,Q), column-major
+    v = np.exp(2.0 * hyp[Q + D * Q:Q + 2 * D * Q].reshape(Q, D).T)
+    return w, m, v
+
+
+def cov_sm(Q, hyp, x, z=None):
+    """K = sum_q w_q exp(-0.5 sum_d T_d^2 v_dq) cos(sum_d T_d m_dq), T = 2 pi (x - z)   (covSM.m:127-149)"""
+    n, D = x.shape
+    w, m, v = _sm_unpack(Q, hyp, D)
+    if isinstance(z, str) and z == 'diag':
+        return np.full(n, w.sum())
+    zz = x if z is None else z
+    K = np.zeros((n, zz.shape[0]))
+    for q in range(Q):                                # q by q: the reference's (n^2 x Q) intermediates do not fit at large n
+        T2 = np.zeros_like(K); Tm = np.zeros_like(K)
+        for d in range(D):
+            Td = 2 * np.pi * (x[:, d][:, None] - zz[:, d][None, :])
+            T2 += Td * Td * v[d, q]; Tm += Td * m[d, q]
+        K += w[q] * np.exp(-0.5 * T2) * np.cos(Tm)
+    return K
+
+
+def cov_sm_dirder(Q, hyp, x, R, want_dx=False):
+    """dKdhyp(R) of covSMfast (covSM.m:150-153) and, as in dirder_fast (covSM.m:158-168), dx (n x D)."""
+    n, D = x.shape
+    w, m, v = _sm_unpack(Q, hyp, D)
+    dw = np.zeros(Q); dm = np.zeros((D, Q)); dv = np.zeros((D, Q)); dx = np.zeros((n, D))
+    T = [2 * np.pi * (x[:, d][:, None] - x[:, d][None, :]) for d in range(D)]
+    for q in range(Q):
+        T2 = sum(T[d] * T[d] * v[d, q] for d in range(D)); Tm = sum(T[d] * m[d, q] for d in range(D))
+        E = np.exp(-0.5 * T2); H = E * np.cos(Tm); S = E * np.sin(Tm)
+        dw[q] = (H * R).sum() * w[q]
+        for d in range(D):
+            dm[d, q] = -((S * R * w[q]) * T[d]).sum() * m[d, q]
+            dv[d, q] = -((H * R * w[q]) * T[d] * T[d]).sum() * v[d, q]
+            if want_dx:
+                A = (R * w[q]) * S * m[d, q] + (R * w[q]) * H * v[d, q] * T[d]
+                dx[:, d] += -2 * np.pi * A.sum(1) + 2 * np.pi * A.sum(0)
+    dhyp = np.concatenate([dw, dm.T.reshape(-1), dv.T.reshape(-1)])
+    return (dhyp, dx) if want_dx else dhyp
+
+
 # Matern (oracle only; used by KAT-1)   covMatern.m / covMaterniso.m
 def cov_matern_iso(d, hyp_cov, x, z=None):
     ell, sf = np.exp(hyp_cov[0]), np.exp(hyp_cov[1])
@@ -173,7 +224,10 @@ def inf_exact(hyp, mean, covmode, x, y, want_grad=True, K=None, dK=None):
     n, D = x.shape
     m, dm = mean_eval(mean, hyp.get('mean', []), x)
     sn2 = np.exp(2.0 * float(hyp['lik']))
-    if K is None:
+    if K is None and isinstance(covmode, tuple):            # ('sm', Q): covSM.m multivariate spectral mixture
+        K = cov_sm(covmode[1], hyp['cov'], x)
+        dK = lambda R: cov_sm_dirder(covmode[1], hyp['cov'], x, R)
+    elif K is None:
         K = cov_se(covmode, hyp['cov'], x)
         dK = lambda Q: cov_se_dirder(covmode, hyp['cov'], x, Q)
     sW = 1.0 / np.sqrt(sn2)
@@ -222,6 +276,18 @@ def dlik_exact(hyp, mean, covmode, x, y, ard_reference_form=False):
     return -(r[:, None] * x - G @ x) / ell2[None, :]
 
 
+def dlik_exact_sm(hyp, mean, Q, x, y):
+    """dnlZ/dX for exact covSM -- an EXTENSION: the reference ships no dcovSM.m, so dlikExact cannot run with covSM
+    there.  Same contraction as dlikExact.m:19-25 with the x-derivative of covSMfast (covSM.m:158-168):
+    dnlZ/dx = 1/2 dx(R), R = K^-1 - alpha alpha' (the factor 1/2 because dirder_fast's dx counts both arguments)."""
+    x = np.asarray(x, dtype=np.float64)
+    n = x.shape[0]
+    sn2 = np.exp(2.0 * float(hyp['lik']))
+    post, _, _ = inf_exact(hyp, mean, ('sm', Q), x, y, want_grad=False)
+    R = solve_chol(post['L'], np.eye(n)) / sn2 - np.outer(post['alpha'], post['alpha'])
+    return cov_sm_dirder(Q, hyp['cov'], x, R, want_dx=True)[1] / 2.0
+
+
 def gp_predict(hyp, mean, covmode, x, y, xs, post=None):
     """[ymu ys2 fmu fs2] = gp(hyp, inf, mean, cov, lik, x, y, xs)  (gp.m:128-181)."""
     x = np.asarray(x, dtype=np.float64)
@@ -234,8 +300,12 @@ def gp_predict(hyp, mean, covmode, x, y, xs, post=None):
     fmu = np.zeros(ns); fs2 = np.zeros(ns)
     for s in range(0, ns, 1000):                      # gp.m:142-146
         idx = slice(s, min(s + 1000, ns))
-        kss = cov_se(covmode, hyp['cov'], xs[idx], 'diag')
-        Ks = cov_se(covmode, hyp['cov'], x, xs[idx])
+        if isinstance(covmode, tuple):
+            kss = cov_sm(covmode[1], hyp['cov'], xs[idx], 'diag')
+            Ks = cov_sm(covmode[1], hyp['cov'], x, xs[idx])
+        else:
+            kss = cov_se(covmode, hyp['cov'], xs[idx], 'diag')
+            Ks = cov_se(covmode, hyp['cov'], x, xs[idx])
         ms, _ = mean_eval(mean, hyp.get('mean', []), xs[idx])
         fmu[idx] = ms + Ks.T @ alpha
         V = sla.solve_triangular(L, sW[:, None] * Ks, trans='T', lower=False,

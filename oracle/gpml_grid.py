@@ -39,11 +39,11 @@ def creategrid(x, eq=1, k=1.0):
         if u.size < 2:
             raise ValueError('Two few unique points.')
         if 0 <= k <= 1:
-            ngj = int(np.ceil(k * u.size))
+            ngj = float(np.ceil(k * u.size))
         else:
-            ngj = int(k)
+            ngj = float(k)                           # stays fractional in du (apxGrid.m:404-406)
         du = (u[-1] - u[0]) / ngj
-        xg.append(np.linspace(u[0] - 5 * du, u[-1] + 5 * du, max(ngj, 5)))
+        xg.append(np.linspace(u[0] - 5 * du, u[-1] + 5 * du, int(np.floor(max(ngj, 5)))))   # Octave linspace floors n
     return xg
 
 
@@ -170,6 +170,98 @@ def factor_diag(kind, hyp, Q=0):
     return np.exp(2 * hyp[1]) if kind == 'covSEiso' else np.exp(hyp[:Q]).sum()
 
 
+# ----------------------------------------------------------------------------
+# Toeplitz factors: xg{i} given as a nested cell {axis} with an equispaced axis (apxGrid.m:258-281).  GPML then keeps
+# only the covariance as a function of the lag (kii), multiplies by FFT through a Strang circulant embedding of length
+# 2 ng - 1 (bttbmvmsymfft, apxGrid.m:335-346), takes the Fiedler eigenvalues from a WHITTLE circulant embedding
+# (circ with s = 3, apxGrid.m:576-580,617-627; apx.m:236) -- which are not the eigenvalues of the Toeplitz matrix, so
+# ldB2 differs from the dense-factor value on the same axis -- and evaluates all hyper-derivatives as sums over lags
+# (apx.m:256-266, apxGrid.m:642-650).  Only 1-D sub-grids (Toeplitz, not BTTB) are restated.
+# In this module such a grid entry is a list / tuple holding the one axis array:  xg = [[ax1], ax2]  <->  {{ax1}, ax2}.
+# ----------------------------------------------------------------------------
+def is_toep(xgi):
+    return isinstance(xgi, (list, tuple))
+
+
+def axis_of(xgi):
+    if is_toep(xgi):
+        assert len(xgi) == 1, 'only 1-D Toeplitz sub-grids are restated (no BTTB)'
+        return np.asarray(xgi[0], dtype=np.float64).reshape(-1)
+    return np.asarray(xgi, dtype=np.float64).reshape(-1)
+
+
+def flat_grid(xg):
+    return [axis_of(a) for a in xg]
+
+
+class ToepFactor(object):
+    """K.kron(i).factor of a Toeplitz grid dimension: struct('descr','toep','mvm',..,'kii',..,'size',..)."""
+
+    def __init__(self, kind, hyp, ax, Q=0):
+        self.kind, self.Q = kind, Q
+        self.hyp = np.asarray(hyp, dtype=np.float64).reshape(-1)
+        ax = np.asarray(ax, dtype=np.float64)
+        dev = np.abs(np.diff(ax) - (ax[1] - ax[0]))
+        if dev.max() >= 1e-9:
+            raise ValueError('Subgrid not equispaced.')                        # apxGrid.m:262-263
+        self.n = ax.size
+        self.h = (ax[-1] - ax[0]) / (self.n - 1)                               # wi./(ni-1), apxGrid.m:265
+        xc = np.concatenate([np.arange(1, self.n + 1), np.arange(2 - self.n, 1)])   # Strang embedding grid, apxGrid.m:267
+        self.xc = xc
+        self.fi = np.real(np.fft.fft(self.kii(xc)))                            # apxGrid.m:268-269
+        self.shape = (self.n, self.n)
+
+    def _parts(self, idx):
+        tau = (np.asarray(idx, dtype=np.float64) - 1.0) * self.h              # kii(n) = k((n-1) h, 0)
+        if self.kind == 'covSEiso':
+            ell, sf2 = np.exp(self.hyp[0]), np.exp(2 * self.hyp[1])
+            d2 = (tau / ell) ** 2
+            return tau, d2, sf2 * np.exp(-d2 / 2.0)
+        Q = self.Q
+        w = np.exp(self.hyp[:Q]); m = np.exp(self.hyp[Q:2 * Q]); v = np.exp(2 * self.hyp[2 * Q:3 * Q])
+        T = 2 * np.pi * tau
+        E = np.exp(-0.5 * (T * T)[:, None] * v[None, :]); Tm = T[:, None] * m[None, :]
+        return T, (E, Tm, w, m, v), (E * np.cos(Tm)) @ w
+
+    def kii(self, idx):
+        return self._parts(idx)[2]
+
+    def dkii(self, idx, R):
+        """second output of kii: d sum(R .* k(lags)) / d hyp  (the dK functional of the cross-covariance call)."""
+        R = np.asarray(R, dtype=np.float64).reshape(-1)
+        if self.kind == 'covSEiso':
+            _, d2, k = self._parts(idx)
+            return np.array([np.sum(R * k * d2), 2.0 * np.sum(R * k)])
+        T, (E, Tm, w, m, v), _ = self._parts(idx)
+        H = E * np.cos(Tm)
+        dw = (R @ H) * w
+        dm = -((R * T) @ (E * np.sin(Tm))) * w * m
+        dv = -((R * T * T) @ H) * w * v
+        return np.concatenate([dw, dm, dv])
+
+    def mvm(self, A):
+        """bttbmvmsymfft for p = 1 (apxGrid.m:335-346): A is (n, m)."""
+        L = 2 * self.n - 1
+        B = np.fft.ifft(self.fi[:, None] * np.fft.fft(A, L, axis=0), axis=0)
+        return np.real(B[:self.n])
+
+    def dense(self):
+        i = np.arange(self.n)
+        return self.kii((np.abs(i[:, None] - i[None, :]) + 1).reshape(-1)).reshape(self.n, self.n)
+
+
+def circ_whittle(f, s=3):
+    """circ(kii, n, s) for p = 1 (apxGrid.m:617-627): c[j] = sum_{r=-s}^{s-1} k((j + r n) h); returns c and the lag grid."""
+    n = f.n
+    xw = np.arange(1 - s * n, s * n + 1)
+    c = f.kii(xw).reshape(2 * s, n).sum(0)                 # reshape(.,[n, 2s]) column-major, summed over the 2nd dimension
+    return c, xw
+
+
+def _fsize(K):
+    return K.n if isinstance(K, ToepFactor) else K.shape[0]
+
+
 def split_hyp(kind, hyp_cov, p, Q=0):
     nh = factor_nhyp(kind, Q)
     hyp_cov = np.asarray(hyp_cov, dtype=np.float64).reshape(-1)
@@ -184,11 +276,15 @@ def kronmvm(Ks, v):
     if one:
         v = v[:, None]
     m = v.shape[1]
-    ng = [K.shape[0] for K in Ks]
+    ng = [_fsize(K) for K in Ks]
     t = v.T.reshape([m] + ng[::-1])                       # axes: rhs, dim p, ..., dim 1
     for i, K in enumerate(Ks):
         axn = t.ndim - 1 - i
-        t = np.moveaxis(np.tensordot(K, t, axes=([1], [axn])), 0, axn)
+        if isinstance(K, ToepFactor):                     # FFT product along this mode (apxGrid.m:326)
+            tt = np.moveaxis(t, axn, 0); shp = tt.shape
+            t = np.moveaxis(K.mvm(tt.reshape(ng[i], -1)).reshape(shp), 0, axn)
+        else:
+            t = np.moveaxis(np.tensordot(K, t, axes=([1], [axn])), 0, axn)
     out = t.reshape(m, -1).T
     return out[:, 0] if one else out
 
@@ -237,9 +333,13 @@ class CGNotConverged(Exception):
 # ----------------------------------------------------------------------------
 # Fiedler log-det bound and its derivatives (apxGrid.m:571-588, apx.m:246-269,312-318)
 # ----------------------------------------------------------------------------
-def eigkron(Ks):
+def eigkron(Ks, s=3):
     V, ee = [], []
     for K in Ks:
+        if isinstance(K, ToepFactor):                     # Whittle-circulant eigenvalues, V = Fourier matrix (apxGrid.m:576-580)
+            ej = np.real(np.fft.fft(circ_whittle(K, s)[0]))
+            V.append(None); ee.append(np.maximum(ej, 0.0))
+            continue
         ej, Vj = np.linalg.eigh((K + K.T) / 2.0)
         V.append(Vj); ee.append(np.maximum(ej, 0.0))
     e = np.ones(1)
@@ -262,9 +362,9 @@ def logdet_fiedler(E, W):
     return ub, dE, dW
 
 
-def fiedler_dhyp(Ks, dKs, V, ee, de):
+def fiedler_dhyp(Ks, dKs, V, ee, de, s=3):
     """dhyp_i = dK_i( V_i diag(z_i) V_i' ),  z_i = de contracted with the other factors' eigenvalues."""
-    ng = [K.shape[0] for K in Ks]; p = len(Ks)
+    ng = [_fsize(K) for K in Ks]; p = len(Ks)
     out = []
     for i in range(p):
         z = de.reshape(ng[::-1])                          # axes: dim p ... dim 1
@@ -273,6 +373,11 @@ def fiedler_dhyp(Ks, dKs, V, ee, de):
                 axn = z.ndim - 1 - j
                 z = np.moveaxis(np.tensordot(ee[j][None, :], z, axes=([1], [axn])), 0, axn)
         z = z.reshape(-1)
+        if isinstance(Ks[i], ToepFactor):                 # apx.m:256-266: sum over the 2 s n Whittle lags
+            Fz = np.real(np.fft.fft(z))
+            _, xw = circ_whittle(Ks[i], s)
+            out.append(Ks[i].dkii(xw, np.tile(Fz, 2 * s)))
+            continue
         Q = (V[i] * z[None, :]) @ V[i].T
         out.append(dKs[i](Q))
     return np.concatenate(out)
@@ -280,7 +385,7 @@ def fiedler_dhyp(Ks, dKs, V, ee, de):
 
 def dirder(Ks, dKs, Mx, a, b):
     """d (a' Mx Kg Mx' b) / d hyp   (apxGrid.m:631-652), dense factors."""
-    ng = [K.shape[0] for K in Ks]; p = len(Ks)
+    ng = [_fsize(K) for K in Ks]; p = len(Ks)
     Mta = Mx.T @ a; Mtb = Mx.T @ b
     out = []
     for i in range(p):
@@ -288,10 +393,19 @@ def dirder(Ks, dKs, Mx, a, b):
         for j in range(p):
             if j != i:
                 axn = v.ndim - 1 - j
-                v = np.moveaxis(np.tensordot(Ks[j], v, axes=([1], [axn])), 0, axn)
+                if isinstance(Ks[j], ToepFactor):
+                    vv = np.moveaxis(v, axn, 0); shp = vv.shape
+                    v = np.moveaxis(Ks[j].mvm(vv.reshape(ng[j], -1)).reshape(shp), 0, axn)
+                else:
+                    v = np.moveaxis(np.tensordot(Ks[j], v, axes=([1], [axn])), 0, axn)
         axi = len(ng) - 1 - i
         A = np.moveaxis(v, axi, 0).reshape(ng[i], -1)
         B = np.moveaxis(Mtb.reshape(ng[::-1]), axi, 0).reshape(ng[i], -1)
+        if isinstance(Ks[i], ToepFactor):                 # apxGrid.m:642-650: lag sums of A B' through padded FFTs
+            L = 2 * ng[i] - 1
+            Fvb = np.fft.fft((np.fft.fft(A, L, axis=0) * np.fft.ifft(B, L, axis=0)).sum(1))
+            out.append(Ks[i].dkii(Ks[i].xc, np.real(Fvb)))
+            continue
         out.append(dKs[i](A @ B.T))
     return np.concatenate(out)
 
@@ -402,8 +516,13 @@ def inf_grid(hyp, mean, kind, xg, x, y, opt=None, Q=0, want_grad=True, cheby=Non
     assert p == D, 'Grid and data dimension are different.'
     tol = opt.get('cg_tol', 1e-6); maxit = opt.get('cg_maxit', min(n, 20))
     hs = split_hyp(kind, hyp['cov'], p, Q)
-    fac = [factor_cov(kind, hs[i], xg[i], Q) for i in range(p)]
-    Ks = [f[0] for f in fac]; dKs = [f[1] for f in fac]
+    Ks, dKs = [], []
+    for i in range(p):
+        if is_toep(xg[i]):
+            Ks.append(ToepFactor(kind, hs[i], axis_of(xg[i]), Q)); dKs.append(None)
+        else:
+            K_, dK_ = factor_cov(kind, hs[i], xg[i], Q); Ks.append(K_); dKs.append(dK_)
+    xg = flat_grid(xg)
     Mx = interpgrid(xg, x)
     MxT = Mx.T.tocsr()
     m, dm = mean_eval(mean, hyp.get('mean', []), x)
@@ -456,6 +575,7 @@ def dlik_grid(hyp, mean, kind, xg, x, y, opt=None, Q=0, h=1e-5):
         x = x[:, None]
     post, _, _ = inf_grid(hyp, mean, kind, xg, x, y, opt, Q, want_grad=False)
     alpha = post['alpha']
+    xg = flat_grid(xg)
     _, dM = interpgrid(xg, x, want_deriv=True)
     beta = post['Kalpha']
     cols = []
@@ -490,6 +610,7 @@ def predict_grid(hyp, mean, kind, xg, post, xs, Q=0, vg=None):
     xs = np.asarray(xs, dtype=np.float64)
     if xs.ndim == 1:
         xs = xs[:, None]
+    xg = flat_grid(xg)
     Ms = interpgrid(xg, xs)
     ms, _ = mean_eval(mean, hyp.get('mean', []), xs)
     fmu = ms + Ms @ post['Kalpha']

@@ -37,4 +37,26 @@ for n in [int(a) for a in sys.argv[1:]] or [3000]:
             n, world, t1 - t0, st['ms_total'], st['ms_potrf'], st['ms_inverse'], st['ms_reduce'], t3 - t2, nlZ, nlZ1, rel(nlZ, nlZ1), rel(g, g1), rel(dX, dX1), rel(ymu, ymu1), rel(ys2, ys21)), flush=True)
         del gps
     del gpd
+# a matrix that is not positive definite (duplicated rows, vanishing noise): EVERY rank must report NOT_PD -- the owner of
+# the failing panel is one rank only, the status is made global inside the library (all-reduce of the pivot flag)
+if os.environ.get('KGP_DIST_NOTPD', '1') != '0':
+    import warnings
+    from kgp_b200 import _cabi
+    rng = np.random.RandomState(5); n, D = 1500, 3
+    X = rng.randn(n, D); X[700:1400] = X[:700]; y = rng.randn(n)
+    gp = B200GP(engine_kwargs={'device': local})
+    gp.configure(D, {'lik': -40.0, 'mean': [], 'cov': np.array([[0.0], [0.0]])}, {}, 'infExact', 'meanZero', 'covSEiso', 'likGauss', 'dlikExact', verbose=0)
+    dist.attach(gp); gp.update_data('tr', X, y[:, None])
+    code = 0
+    try:
+        gp.eng.eval(0, 1, gp._n_hyp)
+    except _cabi.KgpError as e:
+        code = e.code
+    t = torch.tensor([code], dtype=torch.int64, device='cuda'); lo = t.clone(); hi = t.clone()
+    td.all_reduce(lo, op=td.ReduceOp.MIN); td.all_reduce(hi, op=td.ReduceOp.MAX)
+    with warnings.catch_warnings():
+        warnings.simplefilter('ignore')
+        nl = gp.evaluate('tr')                              # gp.m training mode: NaN + warning on every rank
+    if rank == 0:
+        print('NOTPD status min %d max %d (NOT_PD = %d) nlZ %s' % (int(lo), int(hi), _cabi.NOT_PD, nl), flush=True)
 td.destroy_process_group()

@@ -65,3 +65,46 @@ def test_product_minimize_reproduces_kat2():
     v, fX, nev = pmin(np.array([0.0, 0.0, np.log(0.1)]), f, -100)
     assert '%.2f' % fX[-1] == '14.13' and '%.2f' % np.exp(v[2]) == '0.15'
     assert nev <= 100
+
+
+def test_grid_axis_equispaced_rule():
+    """kgp_grid_set_host refuses axes that fail GPML's equi() test (apxGrid.m:684-695) instead of treating them as
+    equispaced; the rule itself is host logic and callable without a GPU."""
+    import ctypes as C
+    from kgp_b200 import _cabi
+    l = _cabi.lib()
+    def eq(a):
+        a = np.ascontiguousarray(a, dtype=np.float64)
+        return l.kgp_grid_axis_equispaced(a.ctypes.data_as(C.c_void_p), a.size)
+    assert eq(np.linspace(-1, 2, 50)) == 1
+    assert eq(np.linspace(-1, 2, 50) ** 3) == 0                       # non-uniform
+    assert eq(np.linspace(2, -1, 50)) == 0                            # decreasing
+    a = np.linspace(0, 1, 20); a[7] += 1e-8
+    assert eq(a) == 0                                                 # beyond the 1e-9 tolerance
+    a = np.linspace(0, 1, 20); a[7] += 1e-11
+    assert eq(a) == 1
+
+
+def test_unsupported_opt_keys_are_refused():
+    from kgp_b200 import _cabi
+    class Dummy(_cabi.Context):
+        def __init__(self):
+            self._l = _cabi.lib(); self._h = None
+        def _chk(self, rc):
+            pass
+    d = Dummy()
+    d._l = type('L', (), {'kgp_opt_default': staticmethod(_cabi.lib().kgp_opt_default), 'kgp_set_model': staticmethod(lambda *a: 0)})()
+    d.set_model('infGrid', 'covSEiso', [0., 0.], 0.0, opt={'cg_tol': 1e-4, 'deg': 3})
+    for bad in ({'deg': 1}, {'proj': 'orth'}, {'ndcovs': 5}):
+        with pytest.raises(ValueError):
+            d.set_model('infGrid', 'covSEiso', [0., 0.], 0.0, opt=bad)
+
+
+def test_creategrid_fractional_k():
+    """apxGrid.m:404-409: k > 1 stays fractional in du = range/k, only linspace floors the point count."""
+    import gpml_grid as gg
+    x = np.linspace(0.0, 10.0, 101)[:, None]
+    ax = gg.creategrid(x, 1, 12.5)[0]
+    du = 10.0 / 12.5
+    assert ax.size == 12 and abs(ax[0] - (0.0 - 5 * du)) < 1e-15 and abs(ax[-1] - (10.0 + 5 * du)) < 1e-15
+    assert np.allclose(np.diff(ax), (10.0 + 10 * du) / 11)

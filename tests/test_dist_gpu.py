@@ -34,8 +34,10 @@ print('REL', rel(nlZ, nlZ0), rel(g, g0), rel(dX, dX0))
 '''
 
 
-def test_tile_reduce_path_single_gpu(built_lib):
-    env = dict(os.environ, KGP_TILE_REDUCE='1')
+@pytest.mark.parametrize('tile_reduce', ['1', '0'])
+def test_tile_reduce_path_single_gpu(built_lib, tile_reduce):
+    """both gradient passes: the symmetric tile pass (default) and the full-square pass (KGP_TILE_REDUCE=0)"""
+    env = dict(os.environ, KGP_TILE_REDUCE=tile_reduce)
     out = subprocess.check_output([sys.executable, '-c', _SINGLE % {'root': ROOT}], env=env, timeout=600).decode()
     vals = [float(v) for v in [l for l in out.splitlines() if l.startswith('REL')][0].split()[1:]]
     assert max(vals) < 1e-8, out
@@ -53,6 +55,9 @@ def test_sharded_equals_single_world2(built_lib):
     for l in lines:
         rels = [float(tok) for tok in l.split('rel')[1].replace('dnlZ', ' ').replace('dX', ' ').replace('ymu', ' ').replace('ys2', ' ').split()]
         assert max(rels) < 1e-10, l
+    # a non-positive-definite input: both ranks return NOT_PD (status 3), none is left with NaNs and status OK
+    npd = [l for l in out.splitlines() if l.startswith('NOTPD')]
+    assert npd and 'min 3 max 3' in npd[0] and 'nan' in npd[0], out
 
 
 def test_sharded_probes_equal_single_world2(built_lib):

@@ -172,3 +172,54 @@ def test_full_size_properties_n40000(built_lib):
         vals.append(gp.eng.eval(0, 0, D + 2)[0])
     fd = (vals[0] - vals[1]) / (2 * h)
     assert abs(fd - g @ dirv) < 1e-5 * max(abs(fd), np.linalg.norm(g) * 1e-2)
+
+
+def test_parity_vs_oracle_n16384_c2(built_lib):
+    """BASELINE configs[1] shape (covSEard, d=8, the bench's synthetic inputs and hyper-parameters) at n = 16 384 -- the
+    largest size the CPU oracle finishes in a couple of minutes on the box's 16 cores: every output against the oracle
+    at the 1e-8 relative bar north_star states (cond(B) ~ 1e6 here, so cond * eps ~ 1e-10 leaves room)."""
+    import gpml_exact as orc
+    from bench import synth_c2
+    n, D = 16384, 8
+    X, y, hyp = synth_c2(n)
+    Xs = np.random.RandomState(9).randn(500, D)
+    gp = make_gp(D, hyp['cov'], hyp['lik'], 'covSEard')
+    nlZ, g, dX = full_eval(gp, X, y)
+    alpha = gp.alpha()
+    ymu, ys2 = gp.predict(Xs, return_var=True)
+    oh = {'cov': hyp['cov'], 'lik': hyp['lik'], 'mean': []}
+    post, nlZ0, d0 = orc.inf_exact(oh, ['meanZero'], 'ard', X, y)
+    g0 = np.concatenate([d0['cov'], [d0['lik']]])
+    assert rel(nlZ, nlZ0) < TOL and rel(g, g0) < TOL and rel(alpha, post['alpha']) < TOL
+    p0 = orc.gp_predict(oh, ['meanZero'], 'ard', X, y, Xs, post)
+    assert rel(ymu[:, 0], p0[0]) < TOL and rel(ys2[:, 0], p0[1]) < TOL
+    del post['Q']
+    dX0 = orc.dlik_exact(oh, ['meanZero'], 'ard', X, y)
+    assert rel(dX, dX0) < TOL
+
+
+@pytest.mark.parametrize('n,D,Q,mean', [(300, 1, 2, 'meanZero'), (700, 3, 4, 'meanSum'), (1500, 8, 6, 'meanZero')])
+def test_exact_covsm_vs_oracle(built_lib, n, D, Q, mean):
+    """infExact with the multivariate spectral-mixture kernel (covSM.m:124-156, Q > 0): nlZ, dnlZ, alpha, predictions
+    at 1e-8 against the oracle restatement of covSMfast.  dnlZ/dX is an extension (the reference ships no dcovSM.m, so
+    its dlikExact cannot run with covSM): checked against the oracle's contraction of covSMfast's own x-derivative."""
+    import gpml_exact as orc
+    from kgp_b200 import B200GP
+    rng = np.random.RandomState(100 + n)
+    X = rng.randn(n, D) * 0.7; y = np.sin(2 * X.sum(1)) + 0.2 * rng.randn(n); Xs = rng.randn(90, D) * 0.7
+    blocks = [np.log(rng.rand(Q, 1) + 0.5), np.log(0.3 * rng.rand(D * Q, 1) + 0.02), np.log(0.3 * rng.rand(D * Q, 1) + 0.05)]
+    hc = np.concatenate([b.ravel() for b in blocks])
+    hm = rng.randn(D + 1) * 0.1 if mean == 'meanSum' else np.zeros(0)
+    gp = B200GP()
+    gp.configure(D, {'lik': np.log(0.25), 'mean': [[v] for v in hm], 'cov': blocks}, {}, 'infExact', mean, 'covSM', 'likGauss', 'dlikExact',
+                 cov_args=[Q], mean_args=['{@meanLinear, @meanConst}'] if mean == 'meanSum' else None, verbose=0)
+    nlZ, g, dX = full_eval(gp, X, y)
+    ymu, ys2 = gp.predict(Xs, return_var=True)
+    oh = {'cov': hc, 'lik': np.log(0.25), 'mean': hm}
+    om = ['meanLinear', 'meanConst'] if mean == 'meanSum' else ['meanZero']
+    post, nlZ0, d0 = orc.inf_exact(oh, om, ('sm', Q), X, y)
+    g0 = np.concatenate([d0['cov'], [d0['lik']], d0['mean']])
+    p0 = orc.gp_predict(oh, om, ('sm', Q), X, y, Xs, post)
+    assert rel(nlZ, nlZ0) < TOL and rel(g, g0) < TOL and rel(gp.alpha(), post['alpha']) < TOL
+    assert rel(ymu[:, 0], p0[0]) < TOL and rel(ys2[:, 0], p0[1]) < TOL
+    assert rel(dX, orc.dlik_exact_sm(oh, om, Q, X, y)) < TOL

@@ -352,3 +352,70 @@ def test_slq_value_against_dense_logdet(built_lib):
     fit = nlZ0 - post['ldB2']                                  # everything except the log-det term
     assert abs((nlZ - fit) / true - 1.0) < 0.05, (nlZ - fit, true)
     assert abs((nlZ - fit) - true) < abs((nlZ_f - fit) - true)
+
+
+def test_c5_shape_vs_oracle(built_lib):
+    """BASELINE configs[4] at its own shape (covSM Q=6 per dimension x 2, meanSum{meanLinear, meanConst}, k=70 -> 70 x 70
+    grid, Fiedler log-det; hyper-parameters by the initCovSM rule of msgp_sm_kernel_mlp_kin40k.py:44-48) at n = 100 000,
+    the reference's cg_tol 1e-6 (cg_maxit raised so that the un-preconditioned solve converges: the reference's 2000
+    would stop in NaN).  Stated tolerance of the iterative path: nlZ within cg_tol, vectors within 30 cg_tol of the oracle
+    run with the same settings; plus the deterministic parts at a tight tolerance."""
+    import gpml_grid as gg
+    from bench import synth_c5
+    n = 100000
+    H, y, hc = synth_c5(n)
+    Xs = np.random.RandomState(3).rand(400, 2)
+    for opt, tn, tv in (({'cg_maxit': 30000, 'cg_tol': 1e-6}, 1e-6, 3e-5), ({'cg_maxit': 60000, 'cg_tol': 1e-11}, 1e-8, 1e-6)):
+        gp = make(H, y, 'covSM', hc, np.log(0.3), 70., opt, 'meanSum', [0.0, 0.0, 0.0],
+                  ['{@meanLinear, @meanConst}'], 6)
+        nlZ, g = gp.eng.eval(0, 2, gp._n_hyp); st = gp.stats()
+        dX = gp.get_dlik_dx('tr'); ymu = gp.predict(Xs)
+        xg, post, nlZ0, g0, dX0, p0 = oracle_all(gp, H, y, 'covSM', opt, 'meanSum', 6, Xs)
+        for a, b in zip(gp.grid(), xg):
+            assert np.array_equal(a, b)
+        assert st['cg_relres'] < opt['cg_tol']
+        assert abs(st['cg_iters'] - post['cg_iter']) <= max(4, 0.08 * post['cg_iter'])
+        assert rel(nlZ, nlZ0) < tn, (rel(nlZ, nlZ0), opt)
+        assert rel(g, g0) < tv and rel(gp.alpha(), post['alpha']) < tv and rel(dX, dX0) < tv and rel(ymu, p0[2]) < tv, opt
+        del gp
+
+
+def test_grid_engine_agrees_with_exact_engine_on_fine_grid(built_lib):
+    """The cross-check of tests/test_oracle_grid.py::test_grid_oracle_agrees_with_kat_pinned_exact_oracle through the CUDA
+    engine (demoGrid1d.m:22-33 set-up on gpml_randn data, manual grid via grid_kwargs['xg']): on a fine grid infGrid's
+    alpha, data-fit term and predictive mean approach infExact's; both engine paths against each other."""
+    from kgp_b200 import B200GP
+    from test_oracle_grid import demo_grid_data
+    X, y, hyp = demo_grid_data()
+    xs = np.linspace(-5.5, 7.5, 300)[:, None]
+    ge = B200GP()
+    ge.configure(1, {'lik': hyp['lik'], 'mean': [[hyp['mean'][0]], [hyp['mean'][1]]], 'cov': hyp['cov'][:, None].copy()}, {}, 'infExact', 'meanSum',
+                 'covSEiso', 'likGauss', 'dlikExact', mean_args=['{@meanLinear, @meanConst}'], verbose=0)
+    ge.update_data('tr', X, y[:, None]); ge.evaluate('tr')
+    a_e = ge.alpha(); ymu_e = ge.predict(xs)
+    errs = []
+    for ng in (40, 640):
+        gk = B200GP()
+        gk.configure(1, {'lik': hyp['lik'], 'mean': [[hyp['mean'][0]], [hyp['mean'][1]]], 'cov': hyp['cov'][:, None].copy()},
+                     {'cg_maxit': 5000, 'cg_tol': 1e-12}, 'infGrid', 'meanSum', 'covSEiso', 'likGauss', 'dlikGrid',
+                     grid_kwargs={'eq': 1, 'k': float(ng), 'xg': [np.linspace(-6, 8, ng)]}, mean_args=['{@meanLinear, @meanConst}'], verbose=0)
+        gk.update_data('tr', X, y[:, None]); gk.evaluate('tr')
+        errs.append((rel(gk.alpha(), a_e), rel(gk.predict(xs), ymu_e)))
+    assert errs[1][0] < 2e-5 and errs[1][1] < 2e-5 and errs[1][0] < errs[0][0] / 30, errs
+
+
+def test_fractional_k_and_non_equispaced_axes(built_lib):
+    """creategrid keeps k fractional in du (apxGrid.m:404-409); a hand-supplied non-equispaced axis is refused (the
+    neqinterp branch of apxGrid.m:547-557 is not built) instead of being silently treated as equispaced."""
+    import gpml_grid as gg
+    from kgp_b200 import B200GP, _cabi
+    rng = np.random.RandomState(1); X = rng.randn(300, 1); y = rng.randn(300)
+    gp = make(X, y, 'covSEiso', [[0.0], [0.0]], -1.0, 12.5, {'cg_maxit': 200})
+    ax = gp.grid()[0]; ax0 = gg.creategrid(X, 1, 12.5)[0]
+    u = np.unique(X[:, 0]); du = (u[-1] - u[0]) / 12.5
+    assert ax.size == 12 and np.array_equal(ax, ax0) and abs(ax[0] - (u[0] - 5 * du)) < 1e-14
+    bad = B200GP()
+    with pytest.raises(_cabi.KgpError) as ei:
+        bad.configure(1, {'lik': -1.0, 'mean': [], 'cov': [[0.0], [0.0]]}, {}, 'infGrid', 'meanZero', 'covSEiso', 'likGauss', 'dlikGrid',
+                      grid_kwargs={'eq': 1, 'k': 20., 'xg': [np.linspace(-3, 3, 20) ** 3]}, verbose=0)
+    assert ei.value.code == _cabi.BAD_ARG

@@ -33,3 +33,120 @@ def test_msgp_mlp_epochs(built_lib):
     hist = harness.fit(net, head, Xt, y, torch.optim.Adam(net.parameters(), lr=1e-3), epochs=3, batch_size=128, gp_n_iter=3)
     assert all(np.isfinite(h['nlml']) for h in hist)
     assert hist[-1]['nlml'] < hist[0]['nlml']
+
+
+def _oracle_update_gp(H, y, hyp0, n_iter, path, opt=None, k=None):
+    """The UpdateGP call sequence (kgp/callbacks.py:56-67: update_data, [update_grid], train(n), get_dlik_dx, eval_predict)
+    driven through the CPU oracle, with the one shared host-side optimiser (kgp_b200/minimize.py = minimize.m)."""
+    import gpml_exact as orc
+    import gpml_grid as gg
+    from kgp_b200.minimize import minimize
+    yv = y.reshape(-1)
+    if path == 'exact':
+        def f(v):
+            _, nl, d = orc.inf_exact({'cov': v[:2], 'lik': v[2], 'mean': []}, ['meanZero'], 'iso', H, yv)
+            return nl, np.concatenate([d['cov'], [d['lik']]])
+    else:
+        xg = gg.creategrid(H, 1, k)
+        def f(v):
+            _, nl, d = gg.inf_grid({'cov': v[:-1], 'lik': v[-1], 'mean': []}, ['meanZero'], 'covSEiso', xg, H, yv, opt)
+            return nl, np.concatenate([d['cov'], [d['lik']]])
+    v, fX, nev = minimize(np.asarray(hyp0, dtype=float), f, -n_iter)
+    if path == 'exact':
+        oh = {'cov': v[:2], 'lik': v[2], 'mean': []}
+        dX = orc.dlik_exact(oh, ['meanZero'], 'iso', H, yv)
+        post, nlZ, _ = orc.inf_exact(oh, ['meanZero'], 'iso', H, yv)
+        ymu = orc.gp_predict(oh, ['meanZero'], 'iso', H, yv, H, post)[0]
+    else:
+        oh = {'cov': v[:-1], 'lik': v[-1], 'mean': []}
+        dX = gg.dlik_grid(oh, ['meanZero'], 'covSEiso', xg, H, yv, opt)
+        post, nlZ, _ = gg.inf_grid(oh, ['meanZero'], 'covSEiso', xg, H, yv, opt)
+        ymu = gg.predict_grid(oh, ['meanZero'], 'covSEiso', xg, post, H)[2]
+    return v, nev, dX, nlZ, ymu
+
+
+def _rel(a, b):
+    a = np.asarray(a, dtype=float).ravel(); b = np.asarray(b, dtype=float).ravel()
+    return float(np.max(np.abs(a - b)) / max(np.max(np.abs(b)), 1e-300))
+
+
+class _Frozen(torch.nn.Module):
+    """a frozen 'network' that returns pre-computed features: the GP side of one epoch is then a pure function of H"""
+    def forward(self, x):
+        return x
+
+
+def test_c1_epoch_gp_update_equals_oracle_sequence(built_lib):
+    """One UpdateGP pass of BASELINE configs[0] (README GP-RNN shape: n=512 features of dimension 32, exact covSEiso,
+    gp_n_iter=5) with a frozen net: hyp after train(5), dlik_dh, nlml and the predictions equal the oracle driven
+    through the same call sequence at 1e-8."""
+    from kgp_b200 import harness
+    rng = np.random.RandomState(42)
+    H = np.tanh(rng.randn(512, 32)); y = (np.sin(H.sum(1) / 4) + 0.1 * rng.randn(512))[:, None]
+    head = harness.GPHead(32, {'lik': -2.0, 'mean': [], 'cov': np.array([[-0.7], [0.0]])}, inf='infExact', cov='covSEiso')
+    harness.update_gp(_Frozen(), head, torch.from_numpy(H), y, epoch=0, batch_size=128, gp_n_iter=5)
+    v, nev, dX, nlZ, ymu = _oracle_update_gp(H, y, [-0.7, 0.0, -2.0], 5, 'exact')
+    hv = np.concatenate([head.hyp['cov'].ravel(), [head.hyp['lik']]])
+    assert head.backend.last_train['n_evals'] == nev
+    assert _rel(hv, v) < 1e-8 and _rel(head.dlik_dh, dX) < 1e-8 and _rel(head.nlml, nlZ) < 1e-8
+    assert abs(head.mse - float(np.mean((y[:, 0] - ymu) ** 2))) < 1e-8 * max(head.mse, 1e-30) + 1e-14
+
+
+def test_c4_epoch_gp_update_equals_oracle_sequence(built_lib):
+    """The same for BASELINE configs[3] (msgp_lstm_actuator shape: n=460 one-dimensional features, infGrid covSEiso,
+    k=100, gp_n_iter=5).  The line search of minimize compares function values, so the trajectory is only comparable
+    when both CG solves are converged: cg_tol 1e-11 here (at the example's 1e-4 the two runs may legitimately take
+    different steps); tolerance 1e-6."""
+    from kgp_b200 import harness
+    rng = np.random.RandomState(45)
+    H = np.tanh(rng.randn(460, 1)); y = (np.sin(4 * H[:, 0]) + np.exp(-2) * rng.randn(460))[:, None]
+    opt = {'cg_maxit': 5000, 'cg_tol': 1e-11}
+    head = harness.GPHead(1, {'lik': -2.0, 'mean': [], 'cov': [[-0.7], [0.0]]}, inf='infGrid', cov='covSEiso', opt=opt,
+                          grid_kwargs={'eq': 1, 'k': 100.}, update_grid=1)
+    harness.update_gp(_Frozen(), head, torch.from_numpy(H), y, epoch=0, batch_size=128, gp_n_iter=5)
+    v, nev, dX, nlZ, ymu = _oracle_update_gp(H, y, [-0.7, 0.0, -2.0], 5, 'grid', opt, 100.)
+    hv = np.concatenate([head.hyp['cov'].flatten(order='F'), [head.hyp['lik']]])
+    assert head.backend.last_train['n_evals'] == nev
+    assert _rel(hv, v) < 1e-6 and _rel(head.dlik_dh, dX) < 1e-6 and _rel(head.nlml, nlZ) < 1e-6
+
+
+def test_c4_gp_lstm_semi_stochastic_epochs(built_lib):
+    """BASELINE configs[3] end to end (examples/msgp_lstm_actuator.py:58-100): LSTM(16) -> Dense(1) -> MSGP covSEiso,
+    k=100, cg 500/1e-4, update_grid every epoch, gp_n_iter=5, batch 128, Adam(1e-2): full-batch GP update per epoch,
+    mini-batch steps of the network on the surrogate loss (the semi-stochastic scheme of tutorials/README.md:108-109)."""
+    from kgp_b200 import harness
+    torch.manual_seed(3); rng = np.random.RandomState(45)
+    u = np.cumsum(rng.randn(1024 + 33)) * 0.1; yy = np.tanh(np.convolve(u, np.ones(8) / 8, 'same'))
+    X = np.stack([u[i:i + 32] for i in range(460)])[:, :, None].astype(np.float32); y = yy[32:32 + 460][:, None]
+    net = harness.make_net('lstm', (32, 1), hidden=16, out_dim=1).cuda()
+    head = harness.GPHead(1, {'lik': -2.0, 'mean': [], 'cov': [[-0.7], [0.0]]}, inf='infGrid', cov='covSEiso',
+                          opt={'cg_maxit': 500, 'cg_tol': 1e-4}, grid_kwargs={'eq': 1, 'k': 100.}, update_grid=1)
+    Xt = torch.from_numpy(X).cuda()
+    hist = harness.fit(net, head, Xt, y, torch.optim.Adam(net.parameters(), lr=1e-2), epochs=5, batch_size=128, gp_n_iter=5)
+    assert all(np.isfinite(h['nlml']) for h in hist) and hist[-1]['nlml'] < hist[0]['nlml']
+    hyp = harness.finetune(net, head, Xt, y, batch_size=128, gp_n_iter=20)
+    assert np.isfinite(hyp['lik'])
+    assert harness.predict(net, head, Xt[:50]).shape == (50, 1)
+
+
+def test_c5_sm_kernel_mlp_epochs(built_lib):
+    """BASELINE configs[4] end to end at a test-sized n (examples/msgp_sm_kernel_mlp_kin40k.py:50-75): MLP 8-1024-512-64-2
+    (ReLU) -> MSGP covSM(Q=6) x 2 + meanSum{meanLinear, meanConst}, k=70, cg 2000/1e-6, update_grid=1."""
+    from kgp_b200 import harness
+    import torch.nn as nn
+    torch.manual_seed(5); rng = np.random.RandomState(46)
+    n = 6000
+    X = rng.randn(n, 8).astype(np.float32); y = (np.sin(X[:, 0] * X[:, 1]) + 0.5 * X[:, 2] + 0.3 * rng.randn(n))[:, None]
+    net = nn.Sequential(nn.Linear(8, 1024), nn.ReLU(), nn.Dropout(0.5), nn.Linear(1024, 512), nn.ReLU(), nn.Dropout(0.5),
+                        nn.Linear(512, 64), nn.ReLU(), nn.Dropout(0.25), nn.Linear(64, 2), nn.ReLU()).cuda()
+    with torch.no_grad():
+        net[-2].bias.fill_(0.5)                                      # keep both ReLU outputs alive at initialisation
+    Q = 6
+    hc = [[np.log(np.ones((Q, 1)))], [np.log(np.maximum(0.05 * rng.rand(Q, 1), 1e-8))], [np.log(np.abs(rng.randn(Q, 1) + 1))]]
+    head = harness.GPHead(2, {'lik': np.log(0.3), 'mean': [[0.], [0.], [0.]], 'cov': hc}, inf='infGrid', mean='meanSum', cov='covSM',
+                          opt={'cg_maxit': 5000, 'cg_tol': 1e-6}, grid_kwargs={'eq': 1, 'k': 70.}, cov_args=[6],
+                          mean_args=['{@meanLinear, @meanConst}'], update_grid=1)   # (cg_maxit above the script's 2000: no NaN epochs in a test)
+    Xt = torch.from_numpy(X).cuda()
+    hist = harness.fit(net, head, Xt, y, torch.optim.Adam(net.parameters(), lr=1e-3), epochs=3, batch_size=128, gp_n_iter=5)
+    assert all(np.isfinite(h['nlml']) for h in hist) and hist[-1]['nlml'] < hist[0]['nlml']
+    assert harness.predict(net, head, Xt[:40]).shape == (40, 1)

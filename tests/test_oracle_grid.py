@@ -177,3 +177,125 @@ def test_bench_kissgp_cpu_sample_runs():
     import bench
     r = bench.kissgp_cpu_sample(20000, 100, sample_iters=3)
     assert r['kind'] == 'port' and r['unit'] == 'evals/s' and r['value'] > 0 and r['cores'] >= 1
+
+
+def demo_grid_data(n=30):
+    """The set-up of GPML/doc/demoGrid1d.m:6-12 (f = a x + b + sin x, x = 1 + 4u + sign(u), covSEiso ell 1 sf 2, sn 0.5,
+    meanSum) with the draws taken from GPML's portable generator gpml_randn (doc/gpml_randn.m) instead of Octave's
+    rand/randn('seed',3), which cannot be reproduced outside Octave."""
+    import gpml_exact as orc
+    from scipy.stats import norm
+    a, b, sn = 0.3, 1.2, 0.5
+    u = 2 * norm.cdf(orc.gpml_randn(0.3, n)) - 1                         # uniform(-1,1) from the portable normal stream
+    x = 1 + 4 * u + np.sign(u)
+    y = a * x + b + np.sin(x) + sn * orc.gpml_randn(0.15, n)
+    hyp = {'cov': np.log([1.0, 2.0]), 'lik': np.log(sn), 'mean': np.array([a, b])}
+    return x[:, None], y, hyp
+
+
+def test_grid_oracle_agrees_with_kat_pinned_exact_oracle():
+    """KISS-GP parity is unpinned by the reference (no infGrid number is recorded anywhere), so the grid oracle is tied
+    to the exact oracle -- itself pinned on GPML's manual values -- the way demoGrid1d.m:22-33 compares the two paths:
+    on a fine grid the SKI covariance approaches the exact one, hence alpha, the data-fit term and the predictive mean
+    must agree to the interpolation error; CG alpha must equal a dense solve with the SKI matrix; the Fiedler bound
+    must lie above the dense 1/2 log det of the SKI matrix (it is an upper bound, apx.m:312-318)."""
+    import gpml_exact as orc
+    X, y, hyp = demo_grid_data()
+    mean = ['meanLinear', 'meanConst']
+    xs = np.linspace(-5.5, 7.5, 300)[:, None]
+    post_e, nlZ_e, _ = orc.inf_exact(hyp, mean, 'iso', X, y)
+    ymu_e = orc.gp_predict(hyp, mean, 'iso', X, y, xs, post_e)[0]
+    m, _ = orc.mean_eval(mean, hyp['mean'], X)
+    fit_e = (y - m) @ post_e['alpha'] / 2
+    errs = []
+    for ng in (40, 160, 640):
+        xg = [np.linspace(-6, 8, ng)]
+        opt = {'cg_maxit': 5000, 'cg_tol': 1e-12}
+        post, nlZ, _ = gg.inf_grid(hyp, mean, 'covSEiso', xg, X, y, opt)
+        ymu = gg.predict_grid(hyp, mean, 'covSEiso', xg, post, xs)[2]
+        fit = (y - m) @ post['alpha'] / 2
+        errs.append((np.max(np.abs(post['alpha'] - post_e['alpha'])) / np.max(np.abs(post_e['alpha'])),
+                     abs(fit - fit_e) / abs(fit_e), np.max(np.abs(ymu - ymu_e)) / np.max(np.abs(ymu_e))))
+        # CG alpha = dense solve with the explicit SKI matrix; Fiedler bound >= dense 1/2 log det
+        Mx = gg.interpgrid(xg, X).toarray(); K = gg.factor_cov('covSEiso', hyp['cov'], xg[0])[0]
+        sn2 = np.exp(2 * hyp['lik']); Kski = Mx @ K @ Mx.T
+        assert np.allclose(post['alpha'], np.linalg.solve(Kski + sn2 * np.eye(len(y)), y - m), rtol=1e-8, atol=1e-10)
+        ld_dense = 0.5 * np.linalg.slogdet(np.eye(len(y)) + Kski / sn2)[1]
+        ld_fiedler = nlZ - fit - len(y) * np.log(2 * np.pi * sn2) / 2
+        assert ld_fiedler >= ld_dense - 1e-9
+    # cubic interpolation: the error falls with the grid spacing (>= 30x from 40 to 640 nodes) and is small on the fine grid
+    for k in range(3):
+        assert errs[2][k] < 2e-5 and errs[2][k] < errs[0][k] / 30, errs
+
+
+# ---- Toeplitz factors (nested-cell xg; apxGrid.m:258-281,335-346,571-588,617-627,642-650; apx.m:256-266) -------------
+def _toep_case(kind, seed=3, n=400):
+    rng = np.random.RandomState(seed)
+    X = rng.rand(n, 2) * np.array([2.0, 1.0]); y = np.sin(3 * X[:, 0]) + np.cos(5 * X[:, 1]) + 0.2 * rng.randn(n)
+    a1 = np.linspace(-0.3, 2.3, 64); a2 = np.linspace(-0.2, 1.2, 20)
+    if kind == 'covSEiso':
+        hc, Q = np.array([np.log(0.4), 0.1, np.log(0.3), -0.2]), 0
+    else:
+        Q = 2
+        blk = lambda: np.concatenate([np.log(rng.rand(Q) + 0.5), np.log(0.5 * rng.rand(Q) + 0.1), np.log(0.4 * rng.rand(Q) + 0.2)])
+        hc = np.concatenate([blk(), blk()])
+    return X, y, a1, a2, hc, Q
+
+
+def test_toeplitz_mvm_equals_dense_product():
+    X, y, a1, a2, hc, Q = _toep_case('covSM')
+    f = gg.ToepFactor('covSM', hc[:6], a1, Q)
+    Kd = f.dense()
+    assert np.allclose(Kd, gg.factor_cov('covSM', hc[:6], a1, Q)[0], atol=1e-13)      # same matrix as the dense factor
+    A = np.random.RandomState(0).randn(64, 7)
+    assert np.allclose(f.mvm(A), Kd @ A, atol=1e-12)
+    # mixed Kronecker product: Toeplitz first factor, dense second factor
+    K2 = gg.factor_cov('covSM', hc[6:], a2, Q)[0]
+    v = np.random.RandomState(1).randn(64 * 20, 3)
+    assert np.allclose(gg.kronmvm([f, K2], v), np.kron(K2, Kd) @ v, atol=1e-11)
+
+
+def test_whittle_eigenvalues_follow_the_closed_form():
+    X, y, a1, a2, hc, Q = _toep_case('covSEiso')
+    f = gg.ToepFactor('covSEiso', hc[:2], a1)
+    c, xw = gg.circ_whittle(f, 3)
+    n, h = f.n, f.h
+    ell, sf2 = np.exp(hc[0]), np.exp(2 * hc[1])
+    k = lambda t: sf2 * np.exp(-0.5 * (t / ell) ** 2)
+    c0 = np.array([sum(k((j + r * n) * h) for r in range(-3, 3)) for j in range(n)])        # SURVEY App. A
+    assert np.allclose(c, c0, rtol=1e-13) and xw.size == 6 * n and xw[0] == 1 - 3 * n
+    _, ee, _ = gg.eigkron([f])
+    assert np.allclose(ee[0], np.maximum(np.real(np.fft.fft(c0)), 0), atol=1e-12)
+    ed = np.linalg.eigvalsh(f.dense())
+    assert abs(ee[0].sum() - ed.sum()) / ed.sum() < 0.2 and not np.allclose(np.sort(ee[0]), ed, rtol=1e-3)   # a different spectrum
+
+
+import pytest
+
+
+@pytest.mark.parametrize('kind', ['covSEiso', 'covSM'])
+def test_toeplitz_mode_inference_and_derivatives(kind):
+    """Toeplitz mode changes only the log-det term (Whittle eigenvalues); alpha, the data-fit term and dirder equal the
+    dense-factor values; the analytic hyper-gradient matches central differences of the Toeplitz-mode nlZ."""
+    X, y, a1, a2, hc, Q = _toep_case(kind)
+    opt = {'cg_maxit': 4000, 'cg_tol': 1e-13}
+    hyp = {'cov': hc, 'lik': np.log(0.2), 'mean': []}
+    xg_t, xg_d = [[a1], a2], [a1, a2]
+    pt, nt, dt = gg.inf_grid(hyp, ['meanZero'], kind, xg_t, X, y, opt, Q=Q)
+    pd, nd, dd = gg.inf_grid(hyp, ['meanZero'], kind, xg_d, X, y, opt, Q=Q)
+    assert np.allclose(pt['alpha'], pd['alpha'], rtol=1e-8, atol=1e-10)
+    assert abs(pt['ldB2'] - pd['ldB2']) > 1e-6 * abs(pd['ldB2'])                     # a different numerical definition
+    assert abs((nt - pt['ldB2']) - (nd - pd['ldB2'])) < 1e-8 * abs(nd)
+    assert np.allclose(gg.predict_grid(hyp, ['meanZero'], kind, xg_t, pt, X[:50], Q=Q)[0],
+                       gg.predict_grid(hyp, ['meanZero'], kind, xg_d, pd, X[:50], Q=Q)[0], rtol=1e-8, atol=1e-10)
+
+    def f(v):
+        return gg.inf_grid({'cov': v[:-1], 'lik': v[-1], 'mean': []}, ['meanZero'], kind, xg_t, X, y, opt, Q=Q, want_grad=False)[1]
+    v0 = np.concatenate([hc, [hyp['lik']]]); g = np.concatenate([dt['cov'], [dt['lik']]])
+    fd = _fd(f, v0, 1e-5)
+    assert np.max(np.abs(fd - g)) < 2e-6 * np.max(np.abs(g)), (fd, g)
+    # both Toeplitz: only ldB2 and its derivative change again
+    pt2, nt2, dt2 = gg.inf_grid(hyp, ['meanZero'], kind, [[a1], [a2]], X, y, opt, Q=Q)
+    assert np.allclose(pt2['alpha'], pd['alpha'], rtol=1e-8, atol=1e-10)
+    assert np.allclose(gg.dlik_grid(hyp, ['meanZero'], kind, [[a1], [a2]], X, y, opt, Q=Q),
+                       gg.dlik_grid(hyp, ['meanZero'], kind, xg_d, X, y, opt, Q=Q), rtol=1e-7, atol=1e-9)
