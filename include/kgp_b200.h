@@ -135,6 +135,11 @@ int kgp_predict_host(kgp_ctx* ctx, const double* Xs, long ns,
  * GPML/cov/apxGrid.m:389-416) and push('xg', ...) (kgp/backend/gpml.py:125-126). */
 int kgp_grid_create(kgp_ctx* ctx, int slot, int eq, double k);
 int kgp_grid_set_host(kgp_ctx* ctx, int n_axes, const int* axis_len, const double* axes_concat);
+/* Mark grid dimensions as Toeplitz factors -- what a nested cell xg{i} = {axis} selects in GPML (GPML/cov/apxGrid.m:258-281):
+ * the MVM is the same Toeplitz product, but the Fiedler log-det takes the factor's eigenvalues from a Whittle circulant
+ * embedding (apxGrid.m:576-580,617-627) and differentiates it over the embedding lags (GPML/cov/apx.m:256-266), so nlZ and
+ * dnlZ differ from dense-factor mode on the same axes.  flags: n_axes ints (NULL clears); call after kgp_grid_set_host. */
+int kgp_grid_set_toeplitz(kgp_ctx* ctx, int n_axes, const int* flags);
 /* GPML's equi() test for one axis (GPML/cov/apxGrid.m:684-695): 1 when max|diff(a) - (a[1]-a[0])| < 1e-9 and the axis
  * increases.  kgp_grid_set_host refuses axes that fail it (the neqinterp branch is not built).  Host logic, no GPU. */
 int kgp_grid_axis_equispaced(const double* axis, int len);

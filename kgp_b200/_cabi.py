@@ -64,6 +64,7 @@ SIGNATURES = {
     'kgp_predict_host': (C.c_int, [C.c_void_p, C.c_void_p, C.c_long, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     'kgp_grid_create': (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_double]),
     'kgp_grid_set_host': (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]),
+    'kgp_grid_set_toeplitz': (C.c_int, [C.c_void_p, C.c_int, C.c_void_p]),
     'kgp_grid_axis_equispaced': (C.c_int, [C.c_void_p, C.c_int]),
     'kgp_grid_get_host': (C.c_int, [C.c_void_p, C.POINTER(C.c_int), C.c_void_p, C.c_void_p]),
     'kgp_get_alpha_host': (C.c_int, [C.c_void_p, C.c_void_p]),
@@ -221,6 +222,14 @@ class Context(object):
         self._chk(self._l.kgp_grid_create(self._h, slot, int(eq), float(k)))
 
     def grid_set(self, axes):
+        """axes: one array per grid dimension; a list / tuple holding one array (GPML's nested cell {axis}) marks the
+        dimension as a Toeplitz factor (apxGrid.m:258-281)."""
+        toep = np.array([1 if isinstance(a, (list, tuple)) else 0 for a in axes], dtype=np.int32)
+        axes = [a[0] if isinstance(a, (list, tuple)) else a for a in axes]
+        self._grid_set_plain(axes)
+        self._chk(self._l.kgp_grid_set_toeplitz(self._h, len(axes), _ptr(toep)))
+
+    def _grid_set_plain(self, axes):
         axes = [f64(a, (-1,)) for a in axes]
         lens = np.array([a.size for a in axes], dtype=np.int32)
         cat = np.concatenate(axes)

@@ -247,7 +247,16 @@ int kgp_grid_set_host(kgp_ctx* c, int n_axes, const int* axis_len, const double*
   c->grid.axes.clear();
   o = 0;
   for (int a = 0; a < n_axes; ++a) { c->grid.axes.emplace_back(axes + o, axes + o + axis_len[a]); o += axis_len[a]; }
+  c->grid.toep.assign(n_axes, 0);
   c->grid.set = true; c->grid.version++;
+  return KGP_OK;
+}
+int kgp_grid_set_toeplitz(kgp_ctx* c, int n_axes, const int* flags) {
+  if (!c) return KGP_BAD_ARG;
+  if (!c->grid.set || n_axes != (int)c->grid.axes.size()) return c->fail(KGP_NO_GRID, "set the grid axes first (kgp_grid_set_host)");
+  c->grid.toep.assign(n_axes, 0);
+  if (flags) for (int a = 0; a < n_axes; ++a) c->grid.toep[a] = flags[a] ? 1 : 0;
+  c->grid.version++;
   return KGP_OK;
 }
 int kgp_grid_get_host(kgp_ctx* c, int* n_axes, int* axis_len, double* axes) {

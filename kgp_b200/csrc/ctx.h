@@ -37,6 +37,7 @@ struct Model {
 
 struct Grid {
   std::vector<std::vector<double>> axes;   // xg{d} = equispaced axis values
+  std::vector<int> toep;                   // xg{d} was a nested cell {axis}: Toeplitz factor (apxGrid.m:258-281)
   bool set = false; unsigned long version = 0;
 };
 

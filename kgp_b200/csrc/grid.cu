@@ -8,6 +8,7 @@
 // in device memory; the host only polls the flag every few iterations).
 #include "ctx.h"
 #include "grid_precond.cuh"
+#include "grid_toeplitz.cuh"
 #include "exact_dist.cuh"
 #include <math.h>
 #include <string.h>
@@ -983,6 +984,10 @@ int grid_eval(kgp_ctx* c, int slot, int want, double* nlZ_out, double* dnlZ_out)
   KGP_CUDA(c, cudaMemcpyAsync(g->eoff.p, g->eoff_h, GRID_MAXP * 4, cudaMemcpyHostToDevice, st));
   double prior = 1.0;
   EigBatch eb; memset(&eb, 0, sizeof eb); size_t eig_smem = 0;
+  bool toep[GRID_MAXP] = {false}, any_toep = false;
+  for (int d = 0; d < G.p; ++d) { toep[d] = d < (int)c->grid.toep.size() && c->grid.toep[d] != 0; any_toep |= toep[d]; }
+  if (any_toep && (m.opt.cg_precond || m.opt.pred_var != 0))
+    return c->fail(KGP_BAD_ARG, "opt.cg_precond / opt.pred_var need the factor eigenvectors: not available for Toeplitz factors (nested xg)");
   for (int d = 0; d < G.p; ++d) {
     const double am = axis_mean(c->grid.axes[d]);
     const long nn = (long)G.ng[d] * G.ng[d];
@@ -991,7 +996,7 @@ int grid_eval(kgp_ctx* c, int slot, int want, double* nlZ_out, double* dnlZ_out)
     if (d == 0) transpose_small_kernel<<<(unsigned)((nn + 255) / 256), 256, 0, st>>>(g->Kf.d(), G.ng[0], g->KfT.d());
     const size_t need = 2 * (size_t)G.ng[d] * (G.ng[d] | 1) * 8;
     eb.A[d] = g->Af.d() + g->koff[d]; eb.V[d] = g->Vf.d() + g->koff[d]; eb.ev[d] = g->ee.d() + g->eoff_h[d];
-    eb.ng[d] = G.ng[d]; eb.use_smem[d] = need <= 190 * 1024; if (eb.use_smem[d]) eig_smem = std::max(eig_smem, need);
+    eb.ng[d] = toep[d] ? 0 : G.ng[d]; eb.use_smem[d] = need <= 190 * 1024; if (eb.use_smem[d] && !toep[d]) eig_smem = std::max(eig_smem, need);
     c->stats.kernel_launches += 1;
     if (kind == 0) prior *= exp(2.0 * m.hyp_cov[d * nh + 1]);
     else { double sws = 0; for (int q = 0; q < Q; ++q) sws += exp(m.hyp_cov[d * nh + q]); prior *= sws; }
@@ -1011,6 +1016,7 @@ int grid_eval(kgp_ctx* c, int slot, int want, double* nlZ_out, double* dnlZ_out)
       long ksz = 0; for (int d = 0; d < G.p; ++d) ksz += (long)G.ng[d] * G.ng[d];
       KGP_CUDA(c, g->eigT.ensure(ksz * 8));
       for (int d = 0; d < G.p; ++d) {
+        if (toep[d]) continue;
         const int ngd = G.ng[d]; const unsigned nbk = (unsigned)(((long)ngd * ngd + 255) / 256);
         matmul_small_kernel<<<nbk, 256, 0, c->stream2>>>(g->Kf.d() + g->koff[d], g->Vf.d() + g->koff[d], g->eigT.d() + g->koff[d], ngd, 0);
         matmul_small_kernel<<<nbk, 256, 0, c->stream2>>>(g->Vf.d() + g->koff[d], g->eigT.d() + g->koff[d], g->Af.d() + g->koff[d], ngd, 1);
@@ -1018,6 +1024,12 @@ int grid_eval(kgp_ctx* c, int slot, int want, double* nlZ_out, double* dnlZ_out)
       }
     }
     jacobi_eig_kernel<<<G.p, EIG_THREADS, eig_smem, c->stream2>>>(eb, getenv("KGP_EIG_SWEEPS") ? atoi(getenv("KGP_EIG_SWEEPS")) : 40);
+    for (int d = 0; d < G.p; ++d)                               // Toeplitz factors: Whittle-circulant eigenvalues (apxGrid.m:576-580)
+      if (toep[d]) {
+        whittle_eig_kernel<<<1, 1024, (size_t)G.ng[d] * 8, c->stream2>>>(kind, Q, g->hyp.d() + d * nh, G.ng[d], G.range[d] / (double)(G.ng[d] - 1),
+                                                                        g->ee.d() + g->eoff_h[d]);
+        c->stats.kernel_launches++;
+      }
     g->eig_have = true; g->eig_grid_ver = c->grid.version; g->eig_evals++;
   }
   cudaEventRecord(c->ev[11], c->stream2);
@@ -1102,10 +1114,15 @@ int grid_eval(kgp_ctx* c, int slot, int want, double* nlZ_out, double* dnlZ_out)
       if (cheby) {      // log-det part: dK_d of the accumulated Krylov Gram matrix (cheby_logdet)
         factor_dirder_kernel<<<nh, 256, 0, st>>>(kind, Q, g->hyp.d() + d * nh, G.ax[d], G.ng[d], am, g->chP.d() + g->koff[d], 1.0, g->dhyp.d() + d * nh, 0);
       } else {
-      // Fiedler part: dK_d( V diag(z) V' )
+      // Fiedler part: dK_d( V diag(z) V' ), or for a Toeplitz factor the sum over the Whittle lags (apx.m:256-266)
       fiedler_z_kernel<<<G.ng[d], 256, 0, st>>>(G, d, g->ee.d(), (const int*)g->eoff.p, g->de.d(), g->zv.d());
+      if (toep[d]) {
+        toep_fiedler_dirder_kernel<<<nh, 256, (size_t)G.ng[d] * 8, st>>>(kind, Q, g->hyp.d() + d * nh, G.ng[d], G.range[d] / (double)(G.ng[d] - 1),
+                                                                     g->zv.d(), g->dhyp.d() + d * nh);
+      } else {
       vdv_kernel<<<(unsigned)((nn + 255) / 256), 256, 0, st>>>(g->Vf.d() + g->koff[d], g->zv.d(), G.ng[d], g->Qm.d());
       factor_dirder_kernel<<<nh, 256, 0, st>>>(kind, Q, g->hyp.d() + d * nh, G.ax[d], G.ng[d], am, g->Qm.d(), 1.0, g->dhyp.d() + d * nh, 0);
+      }
       }
       // data-fit part: -1/2 dK_d( P ),  P = shp(v) shp(T)',  v = T with every other factor applied
       KGP_CUDA(c, cudaMemcpyAsync(g->g0.p, g->tgrid.p, G.N * 8, cudaMemcpyDeviceToDevice, st));
@@ -1423,7 +1440,7 @@ int grid_create(kgp_ctx* c, int slot, int eq, double k) {
     axes.push_back(ax);
   }
   KGP_CUDA(c, cudaGetLastError());
-  c->grid.axes = axes; c->grid.set = true; c->grid.version++;
+  c->grid.axes = axes; c->grid.toep.assign(axes.size(), 0); c->grid.set = true; c->grid.version++;
   return KGP_OK;
 }
 

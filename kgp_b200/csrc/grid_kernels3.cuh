@@ -24,6 +24,7 @@ __global__ void __launch_bounds__(EIG_THREADS) jacobi_eig_kernel(const EigBatch 
   double* __restrict__ Ag = eb.A[blockIdx.x]; double* __restrict__ Vg = eb.V[blockIdx.x];
   double* __restrict__ ev = eb.ev[blockIdx.x];
   const int ng = eb.ng[blockIdx.x], use_smem = eb.use_smem[blockIdx.x], warm = eb.warm[blockIdx.x];
+  if (ng == 0) return;                           // Toeplitz factor: Whittle eigenvalues instead (grid_toeplitz.cuh)
   extern __shared__ double sm[];
   __shared__ double sh[32];
   __shared__ double rc[1024], rs[1024];          // rotation of pair k: cos, sin

@@ -78,7 +78,9 @@ class B200GP(object):
             self._grid_eq = int(float(grid_kwargs['eq']))
             if 'xg' in grid_kwargs:
                 xg = grid_kwargs['xg']
-                self.eng.grid_set([np.asarray(a, dtype=np.float64).reshape(-1) for a in xg])
+                # a nested entry [axis] (GPML's cell {axis}) selects a Toeplitz factor; plain arrays are dense factors
+                self.eng.grid_set([([np.asarray(a[0], dtype=np.float64).reshape(-1)] if isinstance(a, (list, tuple)) else
+                                    np.asarray(a, dtype=np.float64).reshape(-1)) for a in xg])
             # same in-place tiling as gpml.py:134; GPML then reads it column-major
             hyp['cov'] = np.tile(hyp['cov'], (1, self.input_dim))
         elif cov == 'covSM' and isinstance(hyp['cov'], (list, tuple)):

@@ -419,3 +419,50 @@ def test_fractional_k_and_non_equispaced_axes(built_lib):
         bad.configure(1, {'lik': -1.0, 'mean': [], 'cov': [[0.0], [0.0]]}, {}, 'infGrid', 'meanZero', 'covSEiso', 'likGauss', 'dlikGrid',
                       grid_kwargs={'eq': 1, 'k': 20., 'xg': [np.linspace(-3, 3, 20) ** 3]}, verbose=0)
     assert ei.value.code == _cabi.BAD_ARG
+
+
+@pytest.mark.parametrize('kind,shape', [('covSEiso', '2d'), ('covSM', '2d'), ('covSEiso', '1d_1000'), ('covSM', 'both')])
+def test_toeplitz_factors_vs_oracle(built_lib, kind, shape):
+    """Toeplitz grid factors (nested xg, apxGrid.m:258-281): Whittle-circulant Fiedler eigenvalues (apxGrid.m:576-580,
+    617-627), lag-sum derivatives (apx.m:256-266), same MVM.  Like is compared with like: the oracle runs in Toeplitz mode
+    too (ldB2 differs from dense-factor mode by definition).  ng = 64 x 20 (one / both factors Toeplitz) and ng = 1000."""
+    import gpml_grid as gg
+    from kgp_b200 import B200GP
+    rng = np.random.RandomState(3)
+    opt = {'cg_maxit': 20000, 'cg_tol': 1e-12}
+    if shape == '1d_1000':
+        n = 3000; X = rng.rand(n, 1) * 2.0; y = np.sin(6 * X[:, 0]) + 0.2 * rng.randn(n)
+        xg = [[np.linspace(-0.3, 2.3, 1000)]]; Xs = rng.rand(100, 1) * 2.2 - 0.1
+        hc, Q = [[np.log(0.15)], [0.1]], 0
+    else:
+        n = 2500; X = rng.rand(n, 2) * np.array([2.0, 1.0]); y = np.sin(3 * X[:, 0]) + np.cos(5 * X[:, 1]) + 0.2 * rng.randn(n)
+        a1, a2 = np.linspace(-0.3, 2.3, 64), np.linspace(-0.2, 1.2, 20)
+        xg = [[a1], [a2]] if shape == 'both' else [[a1], a2]
+        Xs = rng.rand(100, 2) * np.array([2.0, 1.0])
+        if kind == 'covSEiso':
+            hc, Q = [[np.log(0.4)], [0.1]], 0
+        else:
+            Q = 2
+            hc = [[np.log(rng.rand(Q, 1) + 0.5)], [np.log(0.5 * rng.rand(Q, 1) + 0.1)], [np.log(0.4 * rng.rand(Q, 1) + 0.2)]]
+    D = X.shape[1]
+    gp = B200GP()
+    gp.configure(D, {'lik': np.log(0.2), 'mean': [], 'cov': hc}, opt, 'infGrid', 'meanZero', kind, 'likGauss', 'dlikGrid',
+                 grid_kwargs={'eq': 1, 'k': 64., 'xg': xg}, cov_args=[Q] if Q else None, verbose=0)
+    gp.update_data('tr', X, y[:, None])
+    nlZ, g = gp.eng.eval(0, 2, gp._n_hyp)
+    dX = gp.get_dlik_dx('tr'); ymu = gp.predict(Xs)
+    hv = gp._hyp_vec(); nc = gp.hyp['cov'].size
+    oh = {'cov': hv[:nc], 'lik': gp.hyp['lik'], 'mean': []}
+    post, nlZ0, d0 = gg.inf_grid(oh, ['meanZero'], kind, xg, X, y, opt, Q=Q)
+    g0 = np.concatenate([d0['cov'], [d0['lik']]])
+    assert rel(nlZ, nlZ0) < 1e-8 and rel(g, g0) < 1e-7, (rel(nlZ, nlZ0), rel(g, g0))
+    assert rel(gp.alpha(), post['alpha']) < 1e-7
+    assert rel(dX, gg.dlik_grid(oh, ['meanZero'], kind, xg, X, y, opt, Q=Q)) < 1e-7
+    assert rel(ymu, gg.predict_grid(oh, ['meanZero'], kind, xg, post, Xs, Q=Q)[2]) < 1e-7
+    # dense-factor mode on the same axes: a different log-det, the same alpha
+    dense = B200GP()
+    dense.configure(D, {'lik': np.log(0.2), 'mean': [], 'cov': hc}, opt, 'infGrid', 'meanZero', kind, 'likGauss', 'dlikGrid',
+                    grid_kwargs={'eq': 1, 'k': 64., 'xg': [a[0] if isinstance(a, list) else a for a in xg]}, cov_args=[Q] if Q else None, verbose=0)
+    dense.update_data('tr', X, y[:, None])
+    nlZd, _ = dense.eng.eval(0, 1, dense._n_hyp)
+    assert abs(nlZd - nlZ) > 1e-9 * abs(nlZ) and rel(dense.alpha(), gp.alpha()) < 1e-7
