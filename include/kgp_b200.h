@@ -58,6 +58,9 @@ typedef struct {
   int    ldB2_slq;           /* 1: stochastic Lanczos quadrature log-det + Hutchinson derivatives (extension);
                               * probes as for ldB2_cheby (ldB2_cheby_hutch, ldB2_cheby_seed, kgp_set_probes_host) */
   int    ldB2_slq_steps;     /* Lanczos steps per probe, default 30 */
+  int    cg_deterministic;   /* 1 (default): the scatter Mx'(sW d) of the persistent CG accumulates in order-independent fixed point
+                              * (integer atomics) -> two runs of a solve are bit-identical; 0: FP64 atomics, ~25 % faster at n = 1M,
+                              * last-bit differences from run to run (iteration counts may differ by a few per cent) */
 } kgp_opt;
 
 /* per-call statistics of the last kgp_eval / kgp_dlik_dx / kgp_predict */

@@ -22,7 +22,7 @@ class KgpOpt(C.Structure):
                 ('ldB2_cheby_hutch', C.c_int), ('ldB2_cheby_degree', C.c_int),
                 ('ldB2_cheby_maxit', C.c_int), ('ldB2_cheby_seed', C.c_uint64),
                 ('ard_reference_form', C.c_int), ('cg_precond', C.c_int), ('pred_var', C.c_int),
-                ('ldB2_slq', C.c_int), ('ldB2_slq_steps', C.c_int)]
+                ('ldB2_slq', C.c_int), ('ldB2_slq_steps', C.c_int), ('cg_deterministic', C.c_int)]
 
 
 class KgpStats(C.Structure):

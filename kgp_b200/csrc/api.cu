@@ -55,7 +55,7 @@ const char* kgp_version(void) { return "kgp_b200 0.1 (sm_100a)"; }
 void kgp_opt_default(kgp_opt* o) {
   memset(o, 0, sizeof *o);
   o->cg_tol = 1e-6; o->cg_maxit = 0; o->ldB2_cheby = 0; o->ldB2_cheby_hutch = 10;
-  o->ldB2_cheby_degree = 15; o->ldB2_cheby_maxit = 50; o->ldB2_cheby_seed = 0; o->ard_reference_form = 0; o->cg_precond = 0; o->pred_var = 0; o->ldB2_slq = 0; o->ldB2_slq_steps = 30;
+  o->ldB2_cheby_degree = 15; o->ldB2_cheby_maxit = 50; o->ldB2_cheby_seed = 0; o->ard_reference_form = 0; o->cg_precond = 0; o->pred_var = 0; o->ldB2_slq = 0; o->ldB2_slq_steps = 30; o->cg_deterministic = 1;
 }
 
 int kgp_ctx_create(int device, kgp_ctx** out) {

@@ -29,6 +29,7 @@ struct GridState {
   DevBuf Gm, Ht1, Ht2, VT, se, ps, pw, psel;           // Woodbury preconditioner (grid_precond.cuh); psel: kept modes
   long prank = 0;
   int gram_slot = -1; unsigned long gram_slot_ver = 0, gram_grid_ver = 0; int pcg_iters = 0;
+  DevBuf kp0, kp1, gpad, tpad, upad;       // large-factor Kronecker MVM through the DMMA GEMM: zero-padded factors and grid matrices
   DevBuf pdz, prr, bar, part4, g0b, wmaxd; int num_sms = 0; size_t smem_optin = 0; int cg_level_used = -1;
   int wmax = 0; int wmax_ctas = 0; unsigned long wmax_slot_ver = 0, wmax_grid_ver = 0; int wmax_slot = -1;
   int p = 0; int ng[GRID_MAXP] = {0}; long N = 0;
@@ -63,7 +64,7 @@ void grid_free(kgp_ctx* c) {
                     &g->hypm, &g->dX, &g->dhyp, &g->out, &g->sortk, &g->sorti, &g->keep, &g->dmean,
                     &g->U, &g->perm, &g->sx, &g->sr, &g->sd, &g->sz, &g->ctl, &g->cnt, &g->KfT, &g->gm0, &g->gm1, &g->pdz, &g->prr, &g->bar, &g->part4, &g->g0b, &g->wmaxd,
                     &g->Gm, &g->Ht1, &g->Ht2, &g->VT, &g->se, &g->ps, &g->pw, &g->psel, &g->probes, &g->chT, &g->chU, &g->chY, &g->chS, &g->chC, &g->chP, &g->bva, &g->bvb, &g->bvc, &g->lzQ, &g->lzP, &g->lzH, &g->chacc,
-                    &g->vg, &g->pvA, &g->pvS, &g->pvG, &g->alt.U, &g->alt.perm, &g->eigT};
+                    &g->vg, &g->pvA, &g->pvS, &g->pvG, &g->alt.U, &g->alt.perm, &g->eigT, &g->kp0, &g->kp1, &g->gpad, &g->tpad, &g->upad};
   for (DevBuf* b : bufs) b->release();
   if (g->h_ctl) cudaFreeHost(g->h_ctl);
   if (g->cg_graph) cudaGraphExecDestroy(g->cg_graph);
@@ -231,7 +232,37 @@ static int cg_prepare_sorted(kgp_ctx* c, GridState* g, const GridDesc& G, int sl
   return KGP_OK;
 }
 
-struct CgLaunch { GridDesc G; long n, npad, N; int m, sub, ctas; double *U, *sx, *sr, *sd, *sz, *ctl, *gm0, *gm1, *Kf, *KfT; unsigned* cnt; long koff1; };
+struct CgLaunch { GridDesc G; long n, npad, N; int m, sub, ctas; double *U, *sx, *sr, *sd, *sz, *ctl, *gm0, *gm1, *Kf, *KfT; unsigned* cnt; long koff1;
+                  int big; int ngp0, ngp1; double *kp0, *kp1, *gpad, *tpad, *upad; };
+
+// dst (rp x cp, zero padded) <- src (r x c), both row-major; and back
+__global__ void pad_matrix_kernel(const double* __restrict__ src, int r, int c, double* __restrict__ dst, int rp, int cp) {
+  const long q = (long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (q >= (long)rp * cp) return;
+  const int i = (int)(q / cp), j = (int)(q - (long)i * cp);
+  dst[q] = (i < r && j < c) ? src[(long)i * c + j] : 0.0;
+}
+__global__ void unpad_matrix_kernel(const double* __restrict__ src, int rp, int cp, double* __restrict__ dst, int r, int c) {
+  const long q = (long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (q >= (long)r * c) return;
+  const int i = (int)(q / c), j = (int)(q - (long)i * c);
+  dst[q] = src[(long)i * cp + j];
+}
+// (K2 kron K1) g for LARGE factors (k = 1000 grids): two FP64 tensor-core GEMMs on zero-padded operands, no transposes:
+//   T'[a][j1] = sum_j0 K1[a][j0] G[j1][j0]   (A = K1, B = G, both K-contiguous)   then   U[r][a] = sum_j1 K2[r][j1] T'[a][j1]
+static void kron2_gemm(const CgLaunch& L, cudaStream_t st) {
+  const int n0 = L.G.ng[0], n1 = L.G.ng[1], p0 = L.ngp0, p1 = L.ngp1;
+  pad_matrix_kernel<<<(unsigned)(((long)p1 * p0 + 255) / 256), 256, 0, st>>>(L.gm0, n1, n0, L.gpad, p1, p0);
+  GemmArgs a; memset(&a, 0, sizeof a);
+  a.A = L.kp0; a.lda = p0; a.B = L.gpad; a.ldb = p0; a.C = L.tpad; a.ldc = p1; a.ntm = p0 / 128; a.ntn = p1 / 128;
+  a.kbeg = 0; a.kend = p0; a.shape = GEMM_FULL; a.ktri = KTRI_NONE; a.alpha = 1.0; a.beta = 0.0; a.nb = NB;
+  gemm_launch(a, st);
+  GemmArgs b; memset(&b, 0, sizeof b);
+  b.A = L.kp1; b.lda = p1; b.B = L.tpad; b.ldb = p1; b.C = L.upad; b.ldc = p0; b.ntm = p1 / 128; b.ntn = p0 / 128;
+  b.kbeg = 0; b.kend = p1; b.shape = GEMM_FULL; b.ktri = KTRI_NONE; b.alpha = 1.0; b.beta = 0.0; b.nb = NB;
+  gemm_launch(b, st);
+  unpad_matrix_kernel<<<(unsigned)(((long)n1 * n0 + 255) / 256), 256, 0, st>>>(L.upad, p1, p0, L.gm1, n1, n0);
+}
 
 // one CG iteration (apx.m:290-300) as kernel launches on st
 static void cg_iteration(kgp_ctx* c, GridState* g, const CgLaunch& L, cudaStream_t st) {
@@ -247,15 +278,18 @@ static void cg_iteration(kgp_ctx* c, GridState* g, const CgLaunch& L, cudaStream
     cg_gather_kernel<1><<<grid, 256, 0, st>>>(G, L.U, L.n, L.npad, u, L.sd, L.sz, L.ctl, L.cnt);
   } else {
     cg_scatter_kernel<2><<<grid, 256, 0, st>>>(G, L.U, L.npad, L.sr, L.sd, L.ctl, L.gm0);
+    if (L.big) kron2_gemm(L, st);
+    else {
     int TA = (G.ng[0] + 31) & ~31; if (TA > 256) TA = 256;
     const size_t ksm = (size_t)(KRON2_THREADS / TA + 1) * G.ng[0] * 8;
     kron2_kernel<<<dim3((unsigned)G.ng[1], (unsigned)L.m), KRON2_THREADS, ksm, st>>>(L.KfT, L.Kf + L.koff1, G.ng[0], G.ng[1], L.gm0, L.gm1, L.ctl);
+    }
     u = L.gm1;
     cg_gather_kernel<2><<<grid, 256, 0, st>>>(G, L.U, L.n, L.npad, u, L.sd, L.sz, L.ctl, L.cnt);
   }
   cg_update_kernel<<<grid, 256, 0, st>>>(L.npad, L.sx, L.sr, L.sd, L.sz, L.ctl, L.cnt, L.gm0, G.N);
 }
-static int cg_launches_per_iteration(const CgLaunch& L) { return L.G.p == 1 ? 3 + L.m : 4; }
+static int cg_launches_per_iteration(const CgLaunch& L) { return L.G.p == 1 ? 3 + L.m : (L.big ? 7 : 4); }
 
 // whole solve in one cooperative launch (cg_persistent_kernel); returns -1 when the configuration does not fit
 template <int P, int LEVEL>
@@ -329,17 +363,21 @@ static int cg_run_persistent(kgp_ctx* c, GridState* g, const CgLaunch& L, int ma
   return cg_finish(c, g, L.m);
 }
 
-template <int P, int LEVEL, bool DBG, bool DIST = false>
-static cudaError_t launch_persistent2b(const CgPersist2& A, int ctas, size_t smem, cudaStream_t st) {
-  cudaError_t e = cudaFuncSetAttribute(cg_persistent2_kernel<P, LEVEL, DBG, DIST>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+template <int P, int LEVEL, bool DBG, bool DIST, bool FX>
+static cudaError_t launch_persistent2c(const CgPersist2& A, int ctas, size_t smem, cudaStream_t st) {
+  cudaError_t e = cudaFuncSetAttribute(cg_persistent2_kernel<P, LEVEL, DBG, DIST, FX>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return e;
   void* args[] = {(void*)&A};
-  return cudaLaunchCooperativeKernel((const void*)cg_persistent2_kernel<P, LEVEL, DBG, DIST>, dim3((unsigned)ctas), dim3(CGP2_THREADS), args, smem, st);
+  return cudaLaunchCooperativeKernel((const void*)cg_persistent2_kernel<P, LEVEL, DBG, DIST, FX>, dim3((unsigned)ctas), dim3(CGP2_THREADS), args, smem, st);
+}
+template <int P, int LEVEL, bool DBG, bool DIST = false>
+static cudaError_t launch_persistent2b(const CgPersist2& A, int ctas, size_t smem, cudaStream_t st, bool fx) {
+  return fx ? launch_persistent2c<P, LEVEL, DBG, DIST, true>(A, ctas, smem, st) : launch_persistent2c<P, LEVEL, DBG, DIST, false>(A, ctas, smem, st);
 }
 template <int P, int LEVEL>
-static cudaError_t launch_persistent2(const CgPersist2& A, int ctas, size_t smem, cudaStream_t st) {
-  if (A.X.nranks > 1) return A.dbg ? launch_persistent2b<P, LEVEL, true, true>(A, ctas, smem, st) : launch_persistent2b<P, LEVEL, false, true>(A, ctas, smem, st);
-  return A.dbg ? launch_persistent2b<P, LEVEL, true>(A, ctas, smem, st) : launch_persistent2b<P, LEVEL, false>(A, ctas, smem, st);
+static cudaError_t launch_persistent2(const CgPersist2& A, int ctas, size_t smem, cudaStream_t st, bool fx) {
+  if (A.X.nranks > 1) return A.dbg ? launch_persistent2b<P, LEVEL, true, true>(A, ctas, smem, st, fx) : launch_persistent2b<P, LEVEL, false, true>(A, ctas, smem, st, fx);
+  return A.dbg ? launch_persistent2b<P, LEVEL, true>(A, ctas, smem, st, fx) : launch_persistent2b<P, LEVEL, false>(A, ctas, smem, st, fx);
 }
 // two-barrier formulation (cg_persistent2_kernel); -1 when it does not fit (node window / staging too large)
 static int cg_run_persistent2(kgp_ctx* c, GridState* g, const CgLaunch& L, int slot) {
@@ -372,7 +410,7 @@ static int cg_run_persistent2(kgp_ctx* c, GridState* g, const CgLaunch& L, int s
   long stg_need = (long)(CGP2_THREADS / 32) * CGP_WSCR2;
   if (G.p == 1) stg_need = std::max(stg_need, even(ng0));
   else stg_need = std::max(stg_need, even(std::max<long>(G.N, ng0 * ng0)) + even(wcap * ng1) + even(wcap * ng0));
-  const size_t budget = g->smem_optin - 4 * 1024;                     // static shared of the kernel (< 4 KB)
+  const size_t budget = g->smem_optin - 8704;                         // static shared of the kernel (8192 B, see ptxas.log)
   const long u_d = (long)upc * 128 * G.p, v_d = (long)upc * 128;
   const size_t s0 = (size_t)(uwin_d + stg_need) * 8, s1 = (size_t)(uwin_d + u_d + stg_need) * 8,
                s2 = (size_t)(uwin_d + u_d + v_d + std::max(v_d, stg_need)) * 8;
@@ -381,14 +419,17 @@ static int cg_run_persistent2(kgp_ctx* c, GridState* g, const CgLaunch& L, int s
   int level = 0; size_t smem = s0;
   if (s1 <= budget && force_level >= 1) { level = 1; smem = s1; }
   if (L.m == 1 && s2 <= budget && force_level >= 2) { level = 2; smem = s2; }
-  KGP_CUDA(c, g->part4.ensure((size_t)4 * L.m * ctas * 8)); KGP_CUDA(c, g->g0b.ensure((size_t)L.m * G.N * 8));
+  KGP_CUDA(c, g->part4.ensure((size_t)4 * L.m * ctas * 8));
+  const size_t fxbytes = (size_t)L.m * 2 * G.N * 8;                  // fixed-point scatter targets: (hi, lo) per column
+  KGP_CUDA(c, g->g0b.ensure(2 * fxbytes));
   KGP_CUDA(c, g->bar.ensure(256));
   KGP_CUDA(c, cudaMemsetAsync(g->bar.p, 0, 256, st));
-  KGP_CUDA(c, cudaMemsetAsync(g->g0b.p, 0, (size_t)L.m * G.N * 8, st));
+  KGP_CUDA(c, cudaMemsetAsync(g->g0b.p, 0, 2 * fxbytes, st));
   if (level < 2) KGP_CUDA(c, cudaMemsetAsync(L.sz, 0, (size_t)L.m * L.npad * 8, st));
   CgPersist2 A; memset(&A, 0, sizeof A);
   A.G = G; A.U = L.U; A.n = L.n; A.npad = L.npad; A.m = L.m; A.upc = upc; A.wcap = wcap;
-  A.x = L.sx; A.r = L.sr; A.d = L.sd; A.z = L.sz; A.g0a = L.gm0; A.g0b = g->g0b.d();
+  A.x = L.sx; A.r = L.sr; A.d = L.sd; A.z = L.sz;
+  A.fxa = (long long*)g->g0b.p; A.fxb = (long long*)((char*)g->g0b.p + fxbytes); A.npts_bound = L.n;
   A.K0 = L.Kf; A.K0T = L.KfT; A.K1 = L.Kf + L.koff1;
   A.ctl = L.ctl; A.part = g->part4.d(); A.bar = (unsigned*)g->bar.p; A.stg_doubles = stg_need;
   A.dbg = getenv("KGP_DEBUG") ? (long long*)((char*)g->bar.p + 128) : nullptr;
@@ -399,8 +440,10 @@ static int cg_run_persistent2(kgp_ctx* c, GridState* g, const CgLaunch& L, int s
     A.X.abort = c->px_abort;
   }
   cudaError_t e;
-  if (G.p == 1) e = level == 2 ? launch_persistent2<1, 2>(A, ctas, smem, st) : level == 1 ? launch_persistent2<1, 1>(A, ctas, smem, st) : launch_persistent2<1, 0>(A, ctas, smem, st);
-  else e = level == 2 ? launch_persistent2<2, 2>(A, ctas, smem, st) : level == 1 ? launch_persistent2<2, 1>(A, ctas, smem, st) : launch_persistent2<2, 0>(A, ctas, smem, st);
+  // opt.cg_deterministic (default 1): order-independent fixed-point scatter -> bit-reproducible solves; 0: FP64 atomics (faster)
+  const bool fx = c->model.opt.cg_deterministic != 0;
+  if (G.p == 1) e = level == 2 ? launch_persistent2<1, 2>(A, ctas, smem, st, fx) : level == 1 ? launch_persistent2<1, 1>(A, ctas, smem, st, fx) : launch_persistent2<1, 0>(A, ctas, smem, st, fx);
+  else e = level == 2 ? launch_persistent2<2, 2>(A, ctas, smem, st, fx) : level == 1 ? launch_persistent2<2, 1>(A, ctas, smem, st, fx) : launch_persistent2<2, 0>(A, ctas, smem, st, fx);
   KGP_CUDA(c, e);
   g->cg_level_used = level;
   c->stats.kernel_launches += 1;
@@ -454,12 +497,25 @@ static int cg_solve_sorted(kgp_ctx* c, GridState* g, const GridDesc& G, int slot
     return rc;
   }
 
+  // large Kronecker factors (k = 1000 grids): the dense mode products are 4 ng^3 flops per MVM -- they go to the FP64
+  // tensor-core GEMM (streaming iteration replayed as a CUDA graph) instead of the in-kernel scalar products
+  static const int big_min = getenv("KGP_KRON_GEMM_MIN") ? atoi(getenv("KGP_KRON_GEMM_MIN")) : 192;
+  if (G.p == 2 && m == 1 && G.ng[0] >= big_min && G.ng[1] >= big_min) {
+    L.big = 1; L.ngp0 = (G.ng[0] + 127) / 128 * 128; L.ngp1 = (G.ng[1] + 127) / 128 * 128;
+    KGP_CUDA(c, g->kp0.ensure((size_t)L.ngp0 * L.ngp0 * 8)); KGP_CUDA(c, g->kp1.ensure((size_t)L.ngp1 * L.ngp1 * 8));
+    KGP_CUDA(c, g->gpad.ensure((size_t)L.ngp1 * L.ngp0 * 8)); KGP_CUDA(c, g->tpad.ensure((size_t)L.ngp0 * L.ngp1 * 8));
+    KGP_CUDA(c, g->upad.ensure((size_t)L.ngp1 * L.ngp0 * 8));
+    L.kp0 = g->kp0.d(); L.kp1 = g->kp1.d(); L.gpad = g->gpad.d(); L.tpad = g->tpad.d(); L.upad = g->upad.d();
+    pad_matrix_kernel<<<(unsigned)(((long)L.ngp0 * L.ngp0 + 255) / 256), 256, 0, st>>>(L.Kf, G.ng[0], G.ng[0], L.kp0, L.ngp0, L.ngp0);
+    pad_matrix_kernel<<<(unsigned)(((long)L.ngp1 * L.ngp1 + 255) / 256), 256, 0, st>>>(L.Kf + L.koff1, G.ng[1], G.ng[1], L.kp1, L.ngp1, L.ngp1);
+    c->stats.kernel_launches += 2;
+  }
   static const int cg_mode = getenv("KGP_CG_MODE") ? atoi(getenv("KGP_CG_MODE")) : 3;     // 3 persistent two-barrier, 2 persistent four-phase, 1 streaming kernels
-  if (cg_mode >= 3) {
+  if (cg_mode >= 3 && !L.big) {
     rc = cg_run_persistent2(c, g, L, slot);
     if (rc != -1) return rc;
   }
-  if (cg_mode >= 2) {
+  if (cg_mode >= 2 && !L.big) {
     rc = cg_run_persistent(c, g, L, maxit);
     if (rc != -1) return rc;                                  // -1: does not fit -> streaming kernels below
   }

@@ -161,6 +161,49 @@ __device__ __forceinline__ void flush_nodes(const GridDesc& G, double* __restric
   }
 }
 
+// ---- order-independent scatter accumulation (cg_persistent2_kernel) -------------------------------------------------
+// Floating-point atomics make Mx'(sW d) depend on the order in which warps and CTAs reach a node, so two runs of the
+// same solve differed in the last bits and could stop one iteration apart.  Integer atomics are associative: every
+// flushed value v is split into hi = rint(v 2^e1) and lo = rint((v - hi 2^-e1) 2^(e1+36)) -- both exact operations --
+// and the two parts are accumulated with 64-bit integer REDs into separate arrays.  The sum hi 2^-e1 + lo 2^-(e1+36) is
+// then the same for every arrival order (resolution 2^-96 of the bound, i.e. finer than FP64 on the node values).
+// e1 comes from the Cauchy-Schwarz bound |sum_i c_i sw d_i| <= sw sqrt(n) |d|_2 with |d|_2^2 from the recursion
+// |d_k|^2 = |r_k|^2 + beta^2 |d_k-1|^2, which every CTA evaluates identically from the shared scalars.
+struct FxScale { double s1, i1, s2, i2; };
+__device__ __forceinline__ FxScale fx_scale(double bound) {
+  int e1 = 0;
+  if (bound > 0.0 && bound < 1e300) e1 = 59 - ilogb(bound);
+  e1 = e1 < -1000 ? -1000 : (e1 > 960 ? 960 : e1);
+  FxScale f; f.s1 = scalbn(1.0, e1); f.i1 = scalbn(1.0, -e1); f.s2 = scalbn(1.0, e1 + 36); f.i2 = scalbn(1.0, -e1 - 36);
+  return f;
+}
+__device__ __forceinline__ void fx_add(long long* __restrict__ hi, long long* __restrict__ lo, long idx, double v, const FxScale& f) {
+  const long long h = __double2ll_rn(v * f.s1);
+  const long long l = __double2ll_rn((v - (double)h * f.i1) * f.s2);
+  atomicAdd((unsigned long long*)(hi + idx), (unsigned long long)h);
+  if (l) atomicAdd((unsigned long long*)(lo + idx), (unsigned long long)l);
+}
+__device__ __forceinline__ double fx_load(const long long* __restrict__ hi, const long long* __restrict__ lo, long idx, const FxScale& f) {
+  if (!lo) return __ldcg((const double*)hi + idx);      // FP64-atomics mode: the array holds plain doubles
+  return (double)__ldcg(hi + idx) * f.i1 + (double)__ldcg(lo + idx) * f.i2;
+}
+template <int P>
+__device__ __forceinline__ void flush_nodes_fx(const GridDesc& G, long long* __restrict__ hi, long long* __restrict__ lo, int cell, const double* acc,
+                                               const FxScale& f) {
+  if (P == 1) {
+#pragma unroll
+    for (int a = 0; a < 4; ++a) if (acc[a] != 0.0) fx_add(hi, lo, cell + a, acc[a], f);
+  } else {
+    const int j1 = cell / G.ng[0], j0 = cell - j1 * G.ng[0];
+#pragma unroll
+    for (int b = 0; b < 4; ++b) {
+      const long row = (long)(j1 + b) * G.stride[1] + j0;
+#pragma unroll
+      for (int a = 0; a < 4; ++a) if (acc[b * 4 + a] != 0.0) fx_add(hi, lo, row + a, acc[b * 4 + a], f);
+    }
+  }
+}
+
 // d = r + beta d ;  g0 += Mx' (sw d)
 template <int P>
 __global__ void __launch_bounds__(256, 3) cg_scatter_kernel(GridDesc G, const double* __restrict__ U, long npad,
@@ -803,22 +846,23 @@ __device__ __forceinline__ double dx_finish(const ulonglong2* p, unsigned long l
   return dx_val(x, y);
 }
 // dst[q] = packet(src[q]) for q in [q0, q1): four loads in flight, then four 16-byte stores
-__device__ __noinline__ void dx_push_slice(const double* __restrict__ src, ulonglong2* dst, long q0, long q1, unsigned tag, int tid, int nthreads) {
+__device__ __noinline__ void dx_push_slice(const long long* __restrict__ shi, const long long* __restrict__ slo, FxScale f, ulonglong2* dst, long q0, long q1,
+                                          unsigned tag, int tid, int nthreads) {
   for (long qb = q0 + tid; qb < q1; qb += 4L * nthreads) {
     double v[4];
 #pragma unroll
-    for (int k = 0; k < 4; ++k) { const long q = qb + (long)k * nthreads; v[k] = (q < q1) ? __ldcg(src + q) : 0.0; }
+    for (int k = 0; k < 4; ++k) { const long q = qb + (long)k * nthreads; v[k] = (q < q1) ? fx_load(shi, slo, q, f) : 0.0; }
 #pragma unroll
     for (int k = 0; k < 4; ++k) { const long q = qb + (long)k * nthreads; if (q < q1) dx_put(dst + q, v[k], tag); }
   }
 }
 // out[q] = own[q] (+) pk[q] summed in rank order for q in [0, N); one peer (two ranks): no combiner stage
-__device__ __noinline__ void dx_stage_pair(const double* __restrict__ own, const ulonglong2* pk, bool own_first, double* out, long N, unsigned tag,
-                                          int tid, int nthreads) {
+__device__ __noinline__ void dx_stage_pair(const long long* __restrict__ ohi, const long long* __restrict__ olo, FxScale f, const ulonglong2* pk, bool own_first,
+                                          double* out, long N, unsigned tag, int tid, int nthreads) {
   for (long qb = tid; qb < N; qb += 4L * nthreads) {
     unsigned long long x[4], y[4]; double o[4];
 #pragma unroll
-    for (int k = 0; k < 4; ++k) { const long q = qb + (long)k * nthreads; if (q < N) { dx_ld(pk + q, x[k], y[k]); o[k] = __ldcg(own + q); } }
+    for (int k = 0; k < 4; ++k) { const long q = qb + (long)k * nthreads; if (q < N) { dx_ld(pk + q, x[k], y[k]); o[k] = fx_load(ohi, olo, q, f); } }
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
       const long q = qb + (long)k * nthreads;
@@ -837,14 +881,14 @@ __device__ __noinline__ void dx_stage_packets(const ulonglong2* pk, double* out,
   }
 }
 // gc[q] = packet(sum over ranks, rank order) for q in [q0, q1): polls the peers' packets of the slice
-__device__ __noinline__ void dx_combine_slice(const double* __restrict__ own, char* loc, long ncap, int par, int nranks, int rank, long q0, long q1,
-                                             unsigned tag, int tid, int nthreads) {
+__device__ __noinline__ void dx_combine_slice(const long long* __restrict__ ohi, const long long* __restrict__ olo, FxScale f, char* loc, long ncap, int par,
+                                             int nranks, int rank, long q0, long q1, unsigned tag, int tid, int nthreads) {
   ulonglong2* gc = (ulonglong2*)loc + 16 * ncap + 64 + (long)par * ncap;
   for (long q = q0 + tid; q < q1; q += nthreads) {
     unsigned long long x[8], y[8];
 #pragma unroll
     for (int rk = 0; rk < 8; ++rk) if (rk < nranks && rk != rank) dx_ld((const ulonglong2*)loc + ((long)par * 8 + rk) * ncap + q, x[rk], y[rk]);
-    const double o = __ldcg(own + q);
+    const double o = fx_load(ohi, olo, q, f);
     double sacc = 0.0;
 #pragma unroll
     for (int rk = 0; rk < 8; ++rk)
@@ -868,7 +912,8 @@ struct CgPersist2 {
   GridDesc G;
   const double* U; long n, npad; int m, upc, wcap;     // wcap = node rows the window buffer can hold
   double *x, *r, *d, *z;                               // [m][npad], sorted order
-  double *g0a, *g0b;                                   // [m][N] scatter targets, alternating per iteration
+  long long *fxa, *fxb;                                // [m][2][N] fixed-point scatter targets (hi, lo), alternating per iteration
+  long npts_bound;                                     // points this launch scatters (bound of the accumulation)
   const double *K0, *K0T, *K1;
   double *ctl; double *part;                           // partials [4][m][gridDim]: |r|^2, d.z, r.z, z.z
   unsigned* bar; long long* dbg;
@@ -900,7 +945,9 @@ __global__ void cg_window_kernel(GridDesc G, const double* __restrict__ U, long 
 #else
 #define KGP_CGP2_BOUNDS __launch_bounds__(CGP2_THREADS, 1)
 #endif
-template <int P, int LEVEL, bool DBG, bool DIST>
+// FX: order-independent fixed-point scatter (bit-reproducible solves, two integer REDs per flush); !FX: FP64 atomics (one RED per
+// flush, ~25 % faster at n = 1M, results differ in the last bits from run to run).  Without FX the (hi) array holds plain doubles.
+template <int P, int LEVEL, bool DBG, bool DIST, bool FX>
 __global__ void KGP_CGP2_BOUNDS cg_persistent2_kernel(const CgPersist2 A) {
   constexpr int NW = CgNodes<P>::NW;
   constexpr int VPP = (P == 1) ? 4 : CGP_VPP, NPASS = NW / VPP;
@@ -911,6 +958,8 @@ __global__ void KGP_CGP2_BOUNDS cg_persistent2_kernel(const CgPersist2 A) {
   __shared__ int s_final[CG_MAXCOLS_DEV];
   __shared__ int s_any;
   __shared__ double s_sum[4][CG_MAXCOLS_DEV];
+  __shared__ double s_dn2[CG_MAXCOLS_DEV];             // bound of |d|^2 of the direction about to be scattered
+  __shared__ FxScale s_fx[CG_MAXCOLS_DEV];
   const GridDesc& G = A.G;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nwarp = CGP2_THREADS >> 5;
   const int m = A.m, cta = blockIdx.x, nctas = gridDim.x;
@@ -930,6 +979,7 @@ __global__ void KGP_CGP2_BOUNDS cg_persistent2_kernel(const CgPersist2 A) {
     const double* ct = A.ctl + tid * CT_STRIDE;
     s_beta[tid] = 0.0; s_a[tid] = 0.0; s_rr[tid] = ct[CT_RRCUR]; s_nb[tid] = ct[CT_NB]; s_it[tid] = ct[CT_ITER];
     s_rel[tid] = ct[CT_RELRES]; s_state[tid] = (int)ct[CT_DONE]; s_final[tid] = 0;
+    s_dn2[tid] = ct[CT_RRCUR];                         // first direction: d = r
   }
   // resident data in the [double2 index][lane] layout
   if (LEVEL >= 1)
@@ -962,11 +1012,12 @@ __global__ void KGP_CGP2_BOUNDS cg_persistent2_kernel(const CgPersist2 A) {
 
   while (true) {
     if (tid == 0) { int any = 0; for (int c = 0; c < m; ++c) any |= (s_state[c] == 0 || s_state[c] == 3); s_any = any; }
+    if (FX && tid < m) s_fx[tid] = fx_scale(4.0 * sw * sqrt((double)A.npts_bound) * sqrt(fmax(s_dn2[tid], 0.0)));
     __syncthreads();
     if (!s_any) break;
     ++pass;
-    double* g0w = par ? A.g0b : A.g0a;                 // scattered into now, read in C
-    double* g0z = par ? A.g0a : A.g0b;                 // read in the previous C: zeroed in this C
+    long long* g0w = par ? A.fxb : A.fxa;              // scattered into now, read in C
+    long long* g0z = par ? A.fxa : A.fxb;              // read in the previous C: zeroed in this C
     // ---- F1: x += a d ; r -= a z ; |r|^2 ; d = r + beta d     (streams x and r; z is dead afterwards)
     for (int col = 0; col < m; ++col) {
       const int state = s_state[col];
@@ -1014,7 +1065,8 @@ __global__ void KGP_CGP2_BOUNDS cg_persistent2_kernel(const CgPersist2 A) {
     // ---- F2: g0 += Mx'(sw d)     (shared memory only at LEVEL 2; the reduction scratch aliases z)
     for (int col = 0; col < m; ++col) {
       if (s_state[col] != 0) continue;
-      const double* d = A.d + (long)col * A.npad; double* g0 = g0w + (long)col * G.N;
+      const double* d = A.d + (long)col * A.npad;
+      long long* ghi = g0w + (long)col * 2 * G.N; long long* glo = ghi + G.N; const FxScale fx = s_fx[col];
       double* wscr = stg + (long)warp * CGP_WSCR2; int* woff = (int*)(wscr + VPP * 33);
       for (int ul = warp; ul < nu; ul += nwarp) {
         const long base = (u_lo + ul) * 128 + lane * CG_PTS;
@@ -1081,7 +1133,8 @@ __global__ void KGP_CGP2_BOUNDS cg_persistent2_kernel(const CgPersist2 A) {
                     for (int a2 = 0; a2 < 4; ++a2) one[b * 4 + a2] = cc[h][0][a2] * wb;
                   }
                 }
-                flush_nodes<P>(G, g0, cellq[q], one);
+                if (FX) flush_nodes_fx<P>(G, ghi, glo, cellq[q], one, fx);
+                else flush_nodes<P>(G, (double*)ghi, cellq[q], one);
               }
             }
           }
@@ -1103,10 +1156,10 @@ __global__ void KGP_CGP2_BOUNDS cg_persistent2_kernel(const CgPersist2 A) {
           for (int i2 = 0; i2 < VPP; ++i2) {
             const int co = woff[h * VPP + i2];
             const double v = wscr[k * 33 + h * VPP + i2];
-            if (co != po) { if (run != 0.0) atomicAdd(g0 + po + node_off, run); run = 0.0; po = co; }
+            if (co != po) { if (run != 0.0) { if (FX) fx_add(ghi, glo, po + node_off, run, fx); else atomicAdd((double*)ghi + po + node_off, run); } run = 0.0; po = co; }
             run += v;
           }
-          if (run != 0.0) atomicAdd(g0 + po + node_off, run);
+          if (run != 0.0) { if (FX) fx_add(ghi, glo, po + node_off, run, fx); else atomicAdd((double*)ghi + po + node_off, run); }
         }
       }
     }
@@ -1120,26 +1173,26 @@ __global__ void KGP_CGP2_BOUNDS cg_persistent2_kernel(const CgPersist2 A) {
       if (rcta < npush) {
         const int pr = (A.X.rank + 1 + rcta / DX_NPUSH) % A.X.nranks, sl = rcta % DX_NPUSH;
         const long per = (G.N + DX_NPUSH - 1) / DX_NPUSH, q0 = sl * per, q1 = (q0 + per < G.N) ? q0 + per : G.N;
-        dx_push_slice(g0w, dx_rx(A.X.peer[pr], A.X.ncap, par, A.X.rank), q0, q1, tag, tid, CGP2_THREADS);
+        dx_push_slice(g0w, FX ? g0w + G.N : nullptr, s_fx[0], dx_rx(A.X.peer[pr], A.X.ncap, par, A.X.rank), q0, q1, tag, tid, CGP2_THREADS);
       }
       // (b) more than two ranks: the last DX_NCOMB CTAs sum the P partials of their slice in rank order (polling the
       //     peers' packets) and publish the result as packets in the LOCAL window -- no second grid barrier
       if (A.X.nranks > 2 && rcta >= npush && rcta < npush + DX_NCOMB) {
         const int sl = rcta - npush;
         const long per = (G.N + DX_NCOMB - 1) / DX_NCOMB, q0 = sl * per, q1 = (q0 + per < G.N) ? q0 + per : G.N;
-        dx_combine_slice(g0w, A.X.loc, A.X.ncap, par, A.X.nranks, A.X.rank, q0, q1, tag, tid, CGP2_THREADS);
+        dx_combine_slice(g0w, FX ? g0w + G.N : nullptr, s_fx[0], A.X.loc, A.X.ncap, par, A.X.nranks, A.X.rank, q0, q1, tag, tid, CGP2_THREADS);
       }
     }
     CGP2_TICK(1);
     // ---- C: node window of u = Kg g0, then z = sw Mx u + d and the three dot products
     for (int col = 0; col < m; ++col) {
       if (s_state[col] != 0) continue;
-      const double* T = g0w + (long)col * G.N;
+      const long long* Thi = g0w + (long)col * 2 * G.N; const long long* Tlo = FX ? Thi + G.N : nullptr; const FxScale fx = s_fx[col];
       if (P == 1) {
         if (DIST) {
-          if (A.X.nranks == 2) dx_stage_pair(T, dx_rx(A.X.loc, A.X.ncap, par, 1 - A.X.rank), A.X.rank == 0, stg, ng0, (unsigned)(A.X.epoch + pass), tid, CGP2_THREADS);
+          if (A.X.nranks == 2) dx_stage_pair(Thi, Tlo, fx, dx_rx(A.X.loc, A.X.ncap, par, 1 - A.X.rank), A.X.rank == 0, stg, ng0, (unsigned)(A.X.epoch + pass), tid, CGP2_THREADS);
           else dx_stage_packets(dx_gc(A.X.loc, A.X.ncap, par), stg, ng0, (unsigned)(A.X.epoch + pass), tid, CGP2_THREADS);
-        } else for (int q = tid; q < ng0; q += CGP2_THREADS) stg[q] = __ldcg(T + q);
+        } else for (int q = tid; q < ng0; q += CGP2_THREADS) stg[q] = fx_load(Thi, Tlo, q, fx);
         __syncthreads();
         for (int a2 = warp; a2 < wr; a2 += nwarp) {
           double acc2 = 0.0;
@@ -1153,11 +1206,16 @@ __global__ void KGP_CGP2_BOUNDS cg_persistent2_kernel(const CgPersist2 A) {
         const long tb = (G.N > (long)ng0 * ng0) ? G.N : (long)ng0 * ng0;
         double* sT = stg; double* sK1 = stg + ((tb + 1) & ~1L); double* sW = sK1 + (((long)A.wcap * ng1 + 1) & ~1L);
         if (DIST) {                                                    // the combined grid vector
-          if (A.X.nranks == 2) dx_stage_pair(T, dx_rx(A.X.loc, A.X.ncap, par, 1 - A.X.rank), A.X.rank == 0, sT, G.N, (unsigned)(A.X.epoch + pass), tid, CGP2_THREADS);
+          if (A.X.nranks == 2) dx_stage_pair(Thi, Tlo, fx, dx_rx(A.X.loc, A.X.ncap, par, 1 - A.X.rank), A.X.rank == 0, sT, G.N, (unsigned)(A.X.epoch + pass), tid, CGP2_THREADS);
           else dx_stage_packets(dx_gc(A.X.loc, A.X.ncap, par), sT, G.N, (unsigned)(A.X.epoch + pass), tid, CGP2_THREADS);
         } else {
-          for (long q = tid; q < G.N / 2; q += CGP2_THREADS) cp_async16(sT + 2 * q, T + 2 * q);
-          if ((G.N & 1) && tid == 0) sT[G.N - 1] = __ldcg(T + G.N - 1);
+          for (long qb = tid; qb < G.N; qb += 4L * CGP2_THREADS) {           // fixed point -> FP64, four nodes in flight per thread
+            double v[4];
+#pragma unroll
+            for (int k = 0; k < 4; ++k) { const long q = qb + (long)k * CGP2_THREADS; v[k] = (q < G.N) ? fx_load(Thi, Tlo, q, fx) : 0.0; }
+#pragma unroll
+            for (int k = 0; k < 4; ++k) { const long q = qb + (long)k * CGP2_THREADS; if (q < G.N) sT[q] = v[k]; }
+          }
         }
         for (int q = tid; q < wr * ng1; q += CGP2_THREADS) sK1[q] = A.K1[(long)rlo * ng1 + q];
         cp_async_wait_all();
@@ -1239,8 +1297,8 @@ __global__ void KGP_CGP2_BOUNDS cg_persistent2_kernel(const CgPersist2 A) {
         if (LEVEL >= 2) { szu[lane] = make_double2(zv[0], zv[1]); szu[32 + lane] = make_double2(zv[2], zv[3]); }
         else { *(double2*)(z + base) = make_double2(zv[0], zv[1]); *(double2*)(z + base + 2) = make_double2(zv[2], zv[3]); }
       }
-      double* gz = g0z + (long)col * G.N;
-      for (long q = (long)cta * CGP2_THREADS + tid; q < G.N; q += (long)nctas * CGP2_THREADS) gz[q] = 0.0;
+      long long* gz = g0z + (long)col * 2 * G.N;
+      for (long q = (long)cta * CGP2_THREADS + tid; q < 2 * G.N; q += (long)nctas * CGP2_THREADS) gz[q] = 0;
       double t = block_sum(dz, s_red);
       if (tid == 0) A.part[((long)1 * m + col) * nctas + cta] = t;
       t = block_sum(rz, s_red);
@@ -1286,7 +1344,7 @@ __global__ void KGP_CGP2_BOUNDS cg_persistent2_kernel(const CgPersist2 A) {
         s_a[col] = a; s_it[col] = it; s_rel[col] = rel;
         if (!(rel >= tol)) { s_state[col] = 3; s_final[col] = 1; }            // apx.m:295-298
         else if (it + 1.0 > maxit) { s_state[col] = 3; s_final[col] = 2; }    // `for iter=2:maxit` exhausted
-        else s_beta[col] = rrn / rr;
+        else { const double beta = rrn / rr; s_beta[col] = beta; s_dn2[col] = fmax(rrn, 0.0) + beta * beta * s_dn2[col]; }
       }
     }
     par ^= 1;

@@ -466,3 +466,28 @@ def test_toeplitz_factors_vs_oracle(built_lib, kind, shape):
     dense.update_data('tr', X, y[:, None])
     nlZd, _ = dense.eng.eval(0, 1, dense._n_hyp)
     assert abs(nlZd - nlZ) > 1e-9 * abs(nlZ) and rel(dense.alpha(), gp.alpha()) < 1e-7
+
+
+def test_fp_atomics_mode_matches_within_cg_tolerance(built_lib):
+    """opt.cg_deterministic = 0 (FP64 atomics in the scatter, the faster mode): same results to the CG tolerance."""
+    c, X, y, Xs = build('c3_small')
+    opt = {'cg_maxit': 2000, 'cg_tol': 1e-6}
+    a = make(X, y, c['cov'], c['hyp'], c['lik'], c['k'], opt); na, ga = a.eng.eval(0, 2, a._n_hyp)
+    b = make(X, y, c['cov'], c['hyp'], c['lik'], c['k'], dict(opt, cg_deterministic=0)); nb, gb = b.eng.eval(0, 2, b._n_hyp)
+    assert rel(nb, na) < 1e-6 and rel(gb, ga) < 3e-5 and rel(b.alpha(), a.alpha()) < 3e-5
+    assert abs(a.stats()['cg_iters'] - b.stats()['cg_iters']) <= max(4, 0.08 * a.stats()['cg_iters'])
+
+
+def test_cg_solve_is_bit_reproducible(built_lib):
+    """The scatter Mx'(sW d) accumulates in order-independent fixed point (integer atomics), so two runs of the same solve
+    are bit-identical: same iteration count, same alpha, same nlZ -- SURVEY 7.3 'fixed seed => fixed result'."""
+    c, X, y, Xs = build('c3_small')
+    opt = {'cg_maxit': 2000, 'cg_tol': 1e-6}
+    outs = []
+    for rep in range(3):
+        gp = make(X, y, c['cov'], c['hyp'], c['lik'], c['k'], opt)
+        nlZ, g = gp.eng.eval(0, 2, gp._n_hyp)
+        outs.append((nlZ, g.copy(), gp.alpha().copy(), gp.stats()['cg_iters']))
+        del gp
+    for o in outs[1:]:
+        assert o[3] == outs[0][3] and o[0] == outs[0][0] and np.array_equal(o[2], outs[0][2])
