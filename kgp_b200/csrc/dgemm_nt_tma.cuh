@@ -110,20 +110,14 @@ dgemm_nt_tma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     do { __nanosleep(256); asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1)); } while (t1 - t0 < (unsigned long long)skew_ns);
   }
 
-  // per-thread fragment addresses inside stage 0.  128B swizzle: the 16-byte chunk index of a row is XORed with (row & 7).
-  // A warp-wide LDS.64 is served per half-warp (lanes gq 0..3 / 4..7), so the four rows of a half-warp must land in four
-  // different chunk PAIRS: lane gq therefore takes row rho(gq) = 2 (gq & 3) + (gq >> 2) of each 8-row fragment (rows 0,2,4,6 |
-  // 1,3,5,7) -- with the natural order rows 0,1 (and 2,3) share a pair and every fragment load is a 2-way bank conflict.
-  // The permutation is applied to the A rows (C rows follow in the epilogue) and to the B rows (C columns: undone by one
-  // lane exchange per accumulator pair in the epilogue).
-  const int rho = 2 * (gq & 3) + (gq >> 2);
-  const uint32_t tsw = (uint32_t)((tq >> 1) ^ rho);
+  // per-thread fragment addresses inside stage 0 (128B swizzle: 16-byte chunk index XOR (row & 7), row & 7 == gq)
+  const uint32_t tsw = (uint32_t)((tq >> 1) ^ gq);
   uint32_t offA[4], offB[4];
 #pragma unroll
   for (int st = 0; st < 4; ++st) {
     const uint32_t sw = (((uint32_t)(2 * st) ^ tsw) << 4) + (uint32_t)(tq & 1) * 8u;
-    offA[st] = sbase + (uint32_t)(wm * 64 + rho) * 128u + sw;
-    offB[st] = sbase + TG_OPER_BYTES + (uint32_t)(wn * 32 + rho) * 128u + sw;
+    offA[st] = sbase + (uint32_t)(wm * 64 + gq) * 128u + sw;
+    offB[st] = sbase + TG_OPER_BYTES + (uint32_t)(wn * 32 + gq) * 128u + sw;
   }
   double fa[2][8], fb[2][4];
   auto lds = [&](int buf, uint32_t soff, int step) {              // soff = slot * TG_STAGE_BYTES
@@ -198,19 +192,8 @@ dgemm_nt_tma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       slot = nslot; par = npar;
     }
 
-    // ---- epilogue (registers -> global).  A thread holds the logical column pair (2 tq, 2 tq + 1) = actual columns
-    // (rho(2 tq), rho(2 tq + 1)) = (0,2) (4,6) (1,3) (5,7): one exchange with lane ^ 2 gives every thread two ADJACENT columns
-    // again -- (0,1) (4,5) (2,3) (6,7) -- so the stores stay 16-byte vectors.
-    const bool hi_half = (tq & 2) != 0;
-#pragma unroll
-    for (int i = 0; i < 8; ++i)
-#pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        const double give = hi_half ? acc[i][j][0] : acc[i][j][1];
-        const double got = __shfl_xor_sync(0xffffffffu, give, 2);
-        if (hi_half) acc[i][j][0] = got; else acc[i][j][1] = got;
-      }
-    double* cbase = Cp + (crow0 + wm * 64 + rho) * ldc + ccol0 + wn * 32 + (tq & 1) * 4 + (tq & 2);
+    // ---- epilogue (registers -> global), same as dgemm_nt_kernel_t
+    double* cbase = Cp + (crow0 + wm * 64 + gq) * ldc + ccol0 + wn * 32 + tq * 2;
     if (beta != 0.0) {
 #pragma unroll
       for (int ih = 0; ih < 2; ++ih) {

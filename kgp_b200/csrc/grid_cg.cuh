@@ -1209,13 +1209,7 @@ __global__ void KGP_CGP2_BOUNDS cg_persistent2_kernel(const CgPersist2 A) {
           if (A.X.nranks == 2) dx_stage_pair(Thi, Tlo, fx, dx_rx(A.X.loc, A.X.ncap, par, 1 - A.X.rank), A.X.rank == 0, sT, G.N, (unsigned)(A.X.epoch + pass), tid, CGP2_THREADS);
           else dx_stage_packets(dx_gc(A.X.loc, A.X.ncap, par), sT, G.N, (unsigned)(A.X.epoch + pass), tid, CGP2_THREADS);
         } else {
-          for (long qb = tid; qb < G.N; qb += 4L * CGP2_THREADS) {           // fixed point -> FP64, four nodes in flight per thread
-            double v[4];
-#pragma unroll
-            for (int k = 0; k < 4; ++k) { const long q = qb + (long)k * CGP2_THREADS; v[k] = (q < G.N) ? fx_load(Thi, Tlo, q, fx) : 0.0; }
-#pragma unroll
-            for (int k = 0; k < 4; ++k) { const long q = qb + (long)k * CGP2_THREADS; if (q < G.N) sT[q] = v[k]; }
-          }
+          for (long q = tid; q < G.N; q += CGP2_THREADS) sT[q] = fx_load(Thi, Tlo, q, fx);      // fixed point -> FP64 (an unrolled form measured slower)
         }
         for (int q = tid; q < wr * ng1; q += CGP2_THREADS) sK1[q] = A.K1[(long)rlo * ng1 + q];
         cp_async_wait_all();
