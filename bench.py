@@ -556,6 +556,7 @@ def main():
         nlZ, grad = eng.eval(0, 2, nh)                 # blocking; device time from CUDA events inside
         st = eng.stats()
         dev_ms += st['ms_total']; launches += st['kernel_launches']
+    phases = {k: st[k] for k in ('ms_kbuild', 'ms_potrf', 'ms_inverse', 'ms_solve', 'ms_reduce')}      # (last timed step, this rank)
     barrier()
     wall = time.perf_counter() - t0
     # ---- the same evaluation with an event pair around every GEMM launch (roofline of the dominant kernel); still inside
@@ -690,7 +691,7 @@ def main():
             'e2e': {'value': e2e_val, 'unit': 'evals/s', 'h2d_bytes_per_step': int(X.nbytes + y.nbytes),
                     'd2h_bytes_per_step': int(n * D * 8 + 8)},
             'kissgp': kiss, 'small_configs': small, 'gpu_launches': int(launches), 'clocks': sampler.summary(),
-            'parity_probe': {'nlZ': nlZ, 'nlZ_e2e': nl}, 'multi_gpu_invariance': invariance}
+            'parity_probe': {'nlZ': nlZ, 'nlZ_e2e': nl}, 'multi_gpu_invariance': invariance, 'phases_ms': phases}
     print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()

@@ -9,7 +9,7 @@ import os
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, 'libkgp_b200.so')
+LIB_PATH = os.environ.get('KGP_B200_LIB') or os.path.join(_HERE, 'libkgp_b200.so')   # (override: A/B builds of the library)
 
 OK, BAD_ARG, CUDA_ERR, NOT_PD, CG_NOT_CONVERGED, NO_GRID, NO_DATA = range(7)
 SLOTS = {'tr': 0, 'tst': 1, 'val': 2, 'tmp': 3}

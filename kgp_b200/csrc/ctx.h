@@ -71,6 +71,7 @@ struct kgp_ctx {
   int nranks = 1, rank = 0; void* nccl_comm = nullptr;
   cudaStream_t stream_p = nullptr;                    // panel stream: factorisation of the next panel + its broadcast
   cudaEvent_t dev_ev[8];                              // panel ready [2], panel buffer free [2], look-ahead column updated
+  cudaEvent_t zev[8]; bool zpipe_active = false;      // "rank r's rows of Z = L^-T have arrived" (pipelined all-gather under Z Z^T)
   kgp::DevBuf PB[2];                                  // packed panels (rows x NB)
   // peer exchange window of the row-sharded KISS-GP CG (grid_cg.cuh, CgDist): one cudaMalloc per rank, mapped into
   // every peer with CUDA IPC; px_epoch = tag of the last exchange (monotone over all solves, equal on all ranks)

@@ -45,6 +45,8 @@ struct GemmArgs {
   int nbands; int band_base[GEMM_MAX_BANDS];   // LOWER shape: tile index at which each band of 8 tile-rows starts
   // multi-GPU sharding of one launch (exact_dist.cu):
   int own_mod, own_rem;        // own_mod > 1: this rank computes tiles idx = t*own_mod + own_rem only (cost-balanced: neighbours cost alike)
+  long tile_off, tile_cnt;     // tile_cnt > 0: this launch covers only the tile_cnt owned tiles that follow global tile index tile_off
+                               // (same global enumeration and ownership; staged launches of one problem: exact.cu zzt_reduce_dist)
   // batch of FULL problems that share ntn, K and the operand matrices but start at different rows
   // (trailing update of the block columns a rank owns): problem p covers rows >= bat_roff[p] of A and C and the
   // ntn tile columns whose B rows start at bat_roff[p]; C tile (tm,tn) of problem p sits at C[roff+tm*128][roff+tn*128]
@@ -164,7 +166,7 @@ __device__ __forceinline__ bool gemm_fetch_tile(const GemmArgs& g, long idx, lon
       t.arow = roff + t.m0; t.brow = roff + t.n0; t.kc = g.kbeg;
       return true;
     }
-    gemm_tile_coords(g, g.own_mod > 1 ? idx * g.own_mod + g.own_rem : idx, tm, tn);
+    gemm_tile_coords(g, (g.own_mod > 1 ? idx * g.own_mod + g.own_rem : idx) + g.tile_off, tm, tn);
     t.coff = 0;
     t.m0 = tm * GEMM_BM; t.n0 = tn * GEMM_BN;
     t.in_diag = g.Cdiag && (t.m0 / g.nb) == (t.n0 / g.nb);

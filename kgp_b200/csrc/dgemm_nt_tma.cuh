@@ -296,6 +296,7 @@ inline void gemm_launch(const GemmArgs& g_in, cudaStream_t st, bool tile_ctas = 
     g.bat_base[g.nbatch] = (int)base;
   }
   if (g.own_mod > 1) nt = (nt > g.own_rem) ? (nt - g.own_rem + g.own_mod - 1) / g.own_mod : 0;
+  if (g.tile_cnt > 0) nt = g.tile_cnt;                 // a stage of a staged launch (tile_off already points at its first tile)
   if (nt <= 0 || g.kend <= g.kbeg) return;
   g.cdiag_only = g_gemm_prefetch_c;
   if (g_gemm_bn == 64) {

@@ -123,6 +123,7 @@ static int ensure_panel_stream(kgp_ctx* c) {
   int lo = 0, hi = 0; cudaDeviceGetStreamPriorityRange(&lo, &hi);
   KGP_CUDA(c, cudaStreamCreateWithPriority(&c->stream_p, cudaStreamNonBlocking, hi));
   for (int i = 0; i < 8; ++i) KGP_CUDA(c, cudaEventCreateWithFlags(&c->dev_ev[i], cudaEventDisableTiming));
+  for (int i = 0; i < 8; ++i) KGP_CUDA(c, cudaEventCreateWithFlags(&c->zev[i], cudaEventDisableTiming));
   return KGP_OK;
 }
 // Single-GPU Cholesky with look-ahead 1: panel k+1 is factored on the high-priority panel stream while the rest of
@@ -235,7 +236,7 @@ int dist_init(kgp_ctx* c, int nranks, int rank, const char* id128, const char* l
 }
 void dist_free(kgp_ctx* c) {
   if (c->nccl_comm) { NcclApi& api = nccl_api(nullptr); if (api.ok) api.CommDestroy(c->nccl_comm); c->nccl_comm = nullptr; }
-  if (c->stream_p) { cudaStreamDestroy(c->stream_p); for (int i = 0; i < 8; ++i) cudaEventDestroy(c->dev_ev[i]); c->stream_p = nullptr; }
+  if (c->stream_p) { cudaStreamDestroy(c->stream_p); for (int i = 0; i < 8; ++i) { cudaEventDestroy(c->dev_ev[i]); cudaEventDestroy(c->zev[i]); } c->stream_p = nullptr; }
   c->PB[0].release(); c->PB[1].release();
   for (int r = 0; r < 8; ++r) { if (c->px_peer[r] && c->px_peer[r] != c->px_local) cudaIpcCloseMemHandle(c->px_peer[r]); c->px_peer[r] = nullptr; }
   if (c->px_local) { cudaFree(c->px_local); c->px_local = nullptr; }
@@ -273,9 +274,9 @@ static int potrf_dist(kgp_ctx* c) {
       KGP_CUDA(c, cudaMemcpy2DAsync(PB, (size_t)w * 8, M + k0 * ld + k0, (size_t)ld * 8, (size_t)w * 8, (size_t)rows, cudaMemcpyDeviceToDevice, sp));
     }
     KGP_NCCL(c, api, api.Broadcast(PB, PB, (size_t)rows * w, KGP_NCCL_DOUBLE, owner, c->nccl_comm, sp));
+    KGP_CUDA(c, cudaEventRecord(ev_panel[b], sp));                  // the updates read the PACKED panel: they need not wait for the unpack
     if (me != owner)
       KGP_CUDA(c, cudaMemcpy2DAsync(M + k0 * ld + k0, (size_t)ld * 8, PB, (size_t)w * 8, (size_t)w * 8, (size_t)rows, cudaMemcpyDeviceToDevice, sp));
-    KGP_CUDA(c, cudaEventRecord(ev_panel[b], sp));
     const long t0 = k0 + w;                                         // first trailing row
     const double* Pt = PB + (long)w * w;                            // panel rows from t0 on (row pitch w)
     const int ntm = (int)((np - t0) / 128);
@@ -315,8 +316,8 @@ static int potrf_dist(kgp_ctx* c) {
     }
     KGP_CUDA(c, cudaEventRecord(ev_free[b], sm));
   }
-  KGP_CUDA(c, cudaStreamWaitEvent(sm, ev_panel[(nblk - 1) & 1], 0));
-  if (nblk >= 2) KGP_CUDA(c, cudaStreamWaitEvent(sm, ev_panel[(nblk - 2) & 1], 0));
+  KGP_CUDA(c, cudaEventRecord(c->dev_ev[6], sp));                   // every panel is unpacked into M behind this point
+  KGP_CUDA(c, cudaStreamWaitEvent(sm, c->dev_ev[6], 0));
   return KGP_OK;
 }
 
@@ -345,12 +346,20 @@ static int zsweep_dist(kgp_ctx* c) {
     }
   }
   cudaEventRecord(c->ev[12], st);
-  KGP_NCCL(c, api, api.GroupStart());
+  // all-gather of Z as one broadcast per rank, in rank order, on the (high-priority) panel stream: rank r's rows are the
+  // top rows with the long K ranges, i.e. the tiles of Z Z^T that become computable first.  One event per rank lets
+  // zzt_reduce_dist start its tiles while the later (larger) broadcasts are still in flight.
+  static const bool zpipe = !(getenv("KGP_DIST_ZPIPE") && atoi(getenv("KGP_DIST_ZPIPE")) == 0);
+  cudaStream_t sc = zpipe ? c->stream_p : st;
+  if (zpipe) KGP_CUDA(c, cudaStreamWaitEvent(sc, c->ev[12], 0));
+  if (!zpipe) KGP_NCCL(c, api, api.GroupStart());
   for (int r = 0; r < P; ++r) {
     const long ra = dist_zrow_begin(r, P, np, NB), rb = dist_zrow_begin(r + 1, P, np, NB);
-    if (rb > ra) KGP_NCCL(c, api, api.Broadcast(W + ra * ld, W + ra * ld, (size_t)(rb - ra) * ld, KGP_NCCL_DOUBLE, r, c->nccl_comm, st));
+    if (rb > ra) KGP_NCCL(c, api, api.Broadcast(W + ra * ld, W + ra * ld, (size_t)(rb - ra) * ld, KGP_NCCL_DOUBLE, r, c->nccl_comm, sc));
+    if (zpipe) KGP_CUDA(c, cudaEventRecord(c->zev[r], sc));
   }
-  KGP_NCCL(c, api, api.GroupEnd());
+  if (!zpipe) KGP_NCCL(c, api, api.GroupEnd());
+  c->zpipe_active = zpipe;
   cudaEventRecord(c->ev[13], st);
   return KGP_OK;
 }
@@ -365,12 +374,45 @@ static void launch_reduce_tiles(kgp_ctx* c, const GemmArgs& g, long ntiles, long
 }
 // B^-1 = Z Z^T on this rank's share of the lower tiles + the gradient pass over the same tiles + all-reduce of the row sums
 static int zzt_reduce_dist(kgp_ctx* c, long n, double sf2, double inv_sn2) {
-  NcclApi& api = nccl_api(nullptr);
   double* W = c->W2.d(); const long ld = c->np; const int nt = (int)(c->np / 128); const int Dp = c->Dp;
   GemmArgs g = mkgemm(W, ld, W, ld, W, ld, nt, nt, 0, (int)c->np, GEMM_LOWER, KTRI_FROM_M0, 1.0, 0.0);
   g.Cdiag = c->Dws.d(); g.nb = NB; g.own_mod = c->nranks; g.own_rem = c->rank;
   c->gemm_class = 4;
-  gemm(c, g);
+  if (c->nranks > 1 && c->zpipe_active) {
+    // staged: the global tile enumeration runs band by band (8 tile rows) from the top; a prefix of it needs only the Z rows of
+    // the first ranks.  Stage r covers the bands that lie completely above the end of rank r's rows and starts when that
+    // rank's broadcast has arrived; one CTA per tile, so that the NCCL kernels of the later broadcasts (high-priority
+    // stream) get SMs as tiles retire.  Ownership stays the global idx = t P + rank rule, so the gradient pass below still
+    // enumerates exactly the tiles this rank produced.
+    const int P = c->nranks, me = c->rank;
+    const double fl = count_gemm(c, g);                           // flops of this rank's share, counted once for all stages
+    const bool prof = c->profiling != 0;
+    if (prof) {
+      if (c->gev_used + 2 > c->gev.size()) { size_t old = c->gev.size(); c->gev.resize(old + 256); for (size_t i = old; i < c->gev.size(); ++i) cudaEventCreate(&c->gev[i]); }
+      cudaEventRecord(c->gev[c->gev_used], c->stream);
+    }
+    long tile_lo = 0;                                              // global tile index where the next stage begins
+    for (int r = 0; r < P; ++r) {
+      const long rb = dist_zrow_begin(r + 1, P, c->np, NB);
+      long tile_hi;
+      if (r == P - 1) tile_hi = (long)nt * (nt + 1) / 2;
+      else { const long rows_t = rb / 128, bands = rows_t / GEMM_BAND, tr = bands * GEMM_BAND; tile_hi = tr * (tr + 1) / 2; }
+      KGP_CUDA(c, cudaStreamWaitEvent(c->stream, c->zev[r], 0));
+      if (tile_hi > tile_lo) {
+        // owned global indices in [tile_lo, tile_hi): first one G0 = smallest >= tile_lo with G0 % P == me
+        long G0 = tile_lo + ((me - tile_lo % P) + P) % P;
+        if (G0 < tile_hi) {
+          GemmArgs h = g; h.tile_off = G0 - me; h.tile_cnt = (tile_hi - G0 + P - 1) / P;
+          gemm_launch(h, c->stream, true);
+        }
+        tile_lo = tile_hi;
+      }
+    }
+    if (prof) {                                                    // (one event pair for the staged launch: it includes waiting for rows)
+      cudaEventRecord(c->gev[c->gev_used + 1], c->stream);
+      c->gev_class.push_back(c->gemm_class); c->gev_flops.push_back(fl); c->gev_used += 2;
+    }
+  } else gemm(c, g);
   cudaEventRecord(c->ev[5], c->stream);
   // the same enumeration for the reduction (band table as gemm_launch builds it)
   long base = 0; int nb_ = 0;
@@ -392,8 +434,10 @@ static int zzt_reduce_dist(kgp_ctx* c, long n, double sf2, double inv_sn2) {
     }
     c->stats.kernel_launches++;
   }
-  if (c->nranks > 1)
+  if (c->nranks > 1) {                                   // (NCCL is bound only here: single-GPU use never loads libnccl)
+    NcclApi& api = nccl_api(nullptr);
     KGP_NCCL(c, api, api.AllReduce(c->rows.p, c->rows.p, (size_t)c->np * (Dp + 3), KGP_NCCL_DOUBLE, KGP_NCCL_SUM, c->nccl_comm, c->stream));
+  }
   return KGP_OK;
 }
 
@@ -538,10 +582,11 @@ int exact_eval(kgp_ctx* c, int slot, int want, double* nlZ_out, double* dnlZ_out
   if (dist) { rc = zsweep_dist(c); if (rc) return rc; } else zsweep(c);
   cudaEventRecord(c->ev[3], st);
   {  // alpha = B^{-1} ym / sn2 = Z (Z^T ym) / sn2
-    const int nch = (int)((np + 511) / 512);
+    const int chunk = np <= 8192 ? 64 : 512;          // small problems: shorter serial loops, more CTAs (latency-bound)
+    const int nch = (int)((np + chunk - 1) / chunk);
     KGP_CUDA(c, c->parts.ensure((size_t)nch * np * 8));
     dim3 grid((unsigned)(np / 128), (unsigned)nch);
-    gemv_t_upper_kernel<<<grid, 128, 0, st>>>(c->W2.d(), np, np, c->ym.d(), c->parts.d());
+    gemv_t_upper_kernel<<<grid, 128, 0, st>>>(c->W2.d(), np, np, c->ym.d(), c->parts.d(), chunk);
     sum_parts_kernel<<<(unsigned)((np + 255) / 256), 256, 0, st>>>(c->parts.d(), np, nch, 1.0, c->tvec.d());
     gemv_n_upper_kernel<<<(unsigned)((np + 7) / 8), 256, 0, st>>>(c->W2.d(), np, np, c->tvec.d(), 1.0 / sn2, c->alpha.d());
     dot_kernel<<<1, 1024, 0, st>>>(c->ym.d(), c->alpha.d(), n, c->scal.d() + 101);
@@ -550,6 +595,8 @@ int exact_eval(kgp_ctx* c, int slot, int want, double* nlZ_out, double* dnlZ_out
   cudaEventRecord(c->ev[4], st);
   // symmetric gradient pass over the lower tiles of B^-1 (reads 4n^2 bytes instead of 8n^2, no mirror pass) is the default
   static const bool tile_reduce = !(getenv("KGP_TILE_REDUCE") && atoi(getenv("KGP_TILE_REDUCE")) == 0);
+  // small problems (a handful of 128-tiles) do not fill the GPU with one CTA per tile: the row-split full-square pass is faster there
+  const bool use_tiles = dist || (tile_reduce && np > 2048);
   if (want >= 1 && sm) {
     // covSM: full symmetric B^-1 (Z Z^T + mirror), then one pass per mixture component (exact_sm.cuh)
     zzt(c);
@@ -570,7 +617,7 @@ int exact_eval(kgp_ctx* c, int slot, int want, double* nlZ_out, double* dnlZ_out
     if (nmean) mean_grad_kernel<<<D + 1, 1024, 0, st>>>(S.X.d(), c->alpha.d(), n, D, c->scal.d() + 110);
     c->stats.kernel_launches += 2 + (nmean ? 1 : 0);
     cudaEventRecord(c->ev[6], st);
-  } else if (want >= 1 && (dist || tile_reduce)) {
+  } else if (want >= 1 && use_tiles) {
     rc = zzt_reduce_dist(c, n, sf2, 1.0 / sn2); if (rc) return rc;
     grad_scalars_kernel<<<1, 1024, 0, st>>>(c->rows.d(), n, Dp, c->xs.d(), c->alpha.d(), c->scal.d());
     dx_from_rows_kernel<<<(unsigned)((n * D + 255) / 256), 256, 0, st>>>(c->rows.d(), n, D, Dp, c->fac.d(), c->dX.d());

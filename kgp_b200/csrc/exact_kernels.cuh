@@ -145,14 +145,64 @@ inline size_t kbuild_smem(int Dp) { int ldx = ((Dp + 11) / 16) * 16 + 4; return 
 // Cholesky of one 128x128 diagonal block in shared memory (lower, row-major).
 // info: 1-based global index of the first non-positive pivot (atomicMin), else unchanged.
 // ---------------------------------------------------------------------------
-constexpr int PD_THREADS = 512;
+constexpr int PD_OWNERS = 512, PD_THREADS = PD_OWNERS + 32;
 constexpr int PD_SMEM = 0;
-// The whole block lives in registers: thread (ti, tj) owns rows 4 ti..4 ti+3 x columns 8 tj..8 tj+7.  Step k: the
-// owners of column k publish it (unscaled) through a double-buffered shared vector, ONE barrier, then every thread
-// forms l_i = a_ik / sqrt(a_kk) for its rows and columns itself and applies the rank-1 update to its 32 elements.
+// Cholesky of one 128 x 128 diagonal block (lower triangle, in place), one CTA: 16 owner warps + ONE PANEL WARP.
+// The block lives in the owners' registers: thread (ti, tj) holds rows 4 ti..4 ti+3 x columns 8 tj..8 tj+7.  Columns are processed
+// EIGHT at a time: the owners publish the 128 x 8 panel in shared memory, the panel warp (which holds no part of the block, so its
+// registers carry only the panel: lane l = rows 4 l..4 l+3) factors it with shuffles alone -- eight dependent
+// rsqrt / scale / update steps without a block barrier --, then every owner applies the rank-8 update to its 32 elements from
+// shared memory.  Three block barriers per eight columns (48) instead of one per column (128): the kernel is a chain of dependent
+// FP64 operations and sits on the critical path of every panel (small problems; the multi-GPU panel chain, where it was
+// 4 x ~100 us of every ~1 ms step).  The two roles run in separate branches (register allocation = the larger of the two, not
+// their sum) and meet at a NAMED barrier with an explicit thread count (bar.sync 1, 544).
+// Shared layout: element (row, k) at pan[k][(row & 7) * 16 + (row >> 3)] -- the rank-8 update reads rows 8 tj + c across a
+// half-warp, which this makes contiguous (conflict-free).
+__device__ __forceinline__ int pd_slot(int row) { return (row & 7) * 16 + (row >> 3); }
+__device__ __forceinline__ void pd_bar() { asm volatile("bar.sync 1, %0;" ::"n"(PD_THREADS) : "memory"); }
 __global__ void __launch_bounds__(PD_THREADS) potrf_diag128_kernel(double* __restrict__ A, long ld, int j0, int* info) {
-  __shared__ double colk[2][128];
-  const int tid = threadIdx.x, ti = tid >> 4, tj = tid & 15;
+  __shared__ double pan[8][128];
+  const int tid = threadIdx.x;
+  if (tid >= PD_OWNERS) {                              // ---- panel warp
+    const int lane = tid & 31;
+    for (int kb = 0; kb < 16; ++kb) {
+      pd_bar();                                        // panel published
+      double p[4][8];
+#pragma unroll
+      for (int r = 0; r < 4; ++r)
+#pragma unroll
+        for (int c = 0; c < 8; ++c) p[r][c] = pan[c][pd_slot(4 * lane + r)];
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        const int krow = 8 * kb + k;                   // pivot row: lane 2 kb + (k >> 2), local row k & 3
+        double akk = __shfl_sync(0xffffffffu, p[k & 3][k], 2 * kb + (k >> 2));
+        if (!(akk > 0.0)) { if (lane == 0) atomicMin(info, j0 + krow + 1); akk = nan(""); }
+        const double inv = rsqrt(akk), dk = akk * inv;
+        double lc[8];
+#pragma unroll
+        for (int c = k + 1; c < 8; ++c) lc[c] = __shfl_sync(0xffffffffu, p[c & 3][k], 2 * kb + (c >> 2)) * inv;   // L[8 kb + c][k]
+#pragma unroll
+        for (int r = 0; r < 4; ++r) {
+          const int row = 4 * lane + r;
+          if (row > krow) {
+            const double lr = p[r][k] * inv;
+#pragma unroll
+            for (int c = k + 1; c < 8; ++c) p[r][c] = fma(-lr, lc[c], p[r][c]);
+            p[r][k] = lr;
+          } else if (row == krow) p[r][k] = dk;
+        }
+      }
+#pragma unroll
+      for (int r = 0; r < 4; ++r)
+#pragma unroll
+        for (int c = 0; c < 8; ++c) pan[c][pd_slot(4 * lane + r)] = p[r][c];
+      pd_bar();                                        // panel factored
+      pd_bar();                                        // owners are done reading it
+    }
+    return;
+  }
+  // ---- owners
+  const int ti = tid >> 4, tj = tid & 15;
   const int r0 = ti * 4, c0 = tj * 8;
   const bool active = c0 <= r0 + 3;                    // the 4 x 8 block touches the lower triangle
   double a[4][8];
@@ -165,38 +215,36 @@ __global__ void __launch_bounds__(PD_THREADS) potrf_diag128_kernel(double* __res
       a[r][c] = v.x; a[r][c + 1] = v.y;
     }
   for (int kb = 0; kb < 16; ++kb) {
+    if (tj == kb) {                                    // publish the panel (rows above it are never read)
 #pragma unroll
-    for (int kk = 0; kk < 8; ++kk) {
-      const int k = kb * 8 + kk;
-      double* ck = colk[k & 1];
-      if (tj == kb) {
+      for (int r = 0; r < 4; ++r)
 #pragma unroll
-        for (int r = 0; r < 4; ++r) if (r0 + r >= k) ck[r0 + r] = a[r][kk];
-      }
-      __syncthreads();
-      if (r0 + 3 < k) continue;                        // (uniform per thread; no barrier below)
-      double akk = ck[k];
-      if (!(akk > 0.0)) {
-        if (tid == (k >> 2) * 16 + (k >> 3)) atomicMin(info, j0 + k + 1);
-        akk = nan("");
-      }
-      const double dk = sqrt(akk), inv = 1.0 / dk;
-      if (active) {
-        double lr[4], lc[8];
-#pragma unroll
-        for (int r = 0; r < 4; ++r) lr[r] = (r0 + r > k) ? ck[r0 + r] * inv : 0.0;
-#pragma unroll
-        for (int c = 0; c < 8; ++c) lc[c] = (c0 + c > k) ? ck[c0 + c] * inv : 0.0;
+        for (int c = 0; c < 8; ++c) pan[c][pd_slot(r0 + r)] = a[r][c];
+    }
+    pd_bar();
+    pd_bar();                                          // (the panel warp factors)
+    if (active) {
+      if (tj == kb) {                                  // the factored panel back into the owners' registers
 #pragma unroll
         for (int r = 0; r < 4; ++r)
 #pragma unroll
-          for (int c = 0; c < 8; ++c) a[r][c] = fma(-lr[r], lc[c], a[r][c]);
-        if (tj == kb) {
+          for (int c = 0; c < 8; ++c) if (r0 + r >= 8 * kb) a[r][c] = pan[c][pd_slot(r0 + r)];
+      } else if (tj > kb) {                            // rank-8 update of the columns to the right of the panel
 #pragma unroll
-          for (int r = 0; r < 4; ++r) a[r][kk] = (r0 + r > k) ? lr[r] : ((r0 + r == k) ? dk : a[r][kk]);
+        for (int k = 0; k < 8; ++k) {
+          double lr[4], lcv[8];
+#pragma unroll
+          for (int r = 0; r < 4; ++r) lr[r] = pan[k][pd_slot(r0 + r)];
+#pragma unroll
+          for (int c = 0; c < 8; ++c) lcv[c] = pan[k][pd_slot(c0 + c)];
+#pragma unroll
+          for (int r = 0; r < 4; ++r)
+#pragma unroll
+            for (int c = 0; c < 8; ++c) a[r][c] = fma(-lr[r], lcv[c], a[r][c]);
         }
       }
     }
+    pd_bar();                                          // the panel buffer is rewritten in the next round
   }
   if (active) {
 #pragma unroll

@@ -11,12 +11,12 @@ namespace kgp {
 // and reduced in a second pass (deterministic).
 // ---------------------------------------------------------------------------
 __global__ void gemv_t_upper_kernel(const double* __restrict__ Z, long ld, long np,
-                                    const double* __restrict__ b, double* __restrict__ part) {
+                                    const double* __restrict__ b, double* __restrict__ part, int chunk = 512) {
   const long i = (long)blockIdx.x * 128 + threadIdx.x;
-  const long c0 = (long)blockIdx.y * 512;
+  const long c0 = (long)blockIdx.y * chunk;
   double acc = 0.0;
   if (c0 <= (long)blockIdx.x * 128 + 127) {
-    long c1 = c0 + 512; if (c1 > np) c1 = np;
+    long c1 = c0 + chunk; if (c1 > np) c1 = np;
     long cmax = (long)blockIdx.x * 128 + 128; if (c1 > cmax) c1 = cmax;
     for (long c = c0; c < c1; ++c) acc += Z[c * ld + i] * b[c];     // Z[c][i]==0 for c>i inside the diag block
   }

@@ -940,7 +940,9 @@ __global__ void cg_window_kernel(GridDesc G, const double* __restrict__ U, long 
   atomicMax(wmax, jf + 3 - jl + 1);
 }
 
-#if KGP_CGP2_THREADS > 512
+#if KGP_CGP2_THREADS > 576
+#define KGP_CGP2_BOUNDS __maxnreg__(96)
+#elif KGP_CGP2_THREADS > 512
 #define KGP_CGP2_BOUNDS __maxnreg__(112)
 #else
 #define KGP_CGP2_BOUNDS __launch_bounds__(CGP2_THREADS, 1)
