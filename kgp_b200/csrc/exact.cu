@@ -349,7 +349,10 @@ static int zsweep_dist(kgp_ctx* c) {
   // all-gather of Z as one broadcast per rank, in rank order, on the (high-priority) panel stream: rank r's rows are the
   // top rows with the long K ranges, i.e. the tiles of Z Z^T that become computable first.  One event per rank lets
   // zzt_reduce_dist start its tiles while the later (larger) broadcasts are still in flight.
-  static const bool zpipe = !(getenv("KGP_DIST_ZPIPE") && atoi(getenv("KGP_DIST_ZPIPE")) == 0);
+  // Measured (n = 40 000): 2 GPUs 1035 -> 1024 ms per evaluation; 8 GPUs 344.7 -> 348.2 ms -- P sequential broadcasts lose the
+  // concurrency of the grouped form (eight roots sending at once) and the one-CTA-per-tile stages run ~5 % below the
+  // persistent launch.  Default: pipelined at P = 2 only (KGP_DIST_ZPIPE=0/1 forces it).
+  const bool zpipe = getenv("KGP_DIST_ZPIPE") ? atoi(getenv("KGP_DIST_ZPIPE")) != 0 : (P == 2);
   cudaStream_t sc = zpipe ? c->stream_p : st;
   if (zpipe) KGP_CUDA(c, cudaStreamWaitEvent(sc, c->ev[12], 0));
   if (!zpipe) KGP_NCCL(c, api, api.GroupStart());
