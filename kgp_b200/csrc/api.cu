@@ -238,16 +238,22 @@ int kgp_grid_set_host(kgp_ctx* c, int n_axes, const int* axis_len, const double*
   long o = 0;
   for (int a = 0; a < n_axes; ++a) {
     if (axis_len[a] < 4) return c->fail(KGP_BAD_ARG, "grid axis %d needs >= 4 points", a);
-    // interpgrid / deriv_x dispatch on equi(xg,i) (apxGrid.m:447-449, deriv_x.m:11-15); the non-equispaced branch
-    // (neqinterp, wi = 1) is not built, so such an axis is refused instead of being silently treated as equispaced
-    if (!kgp_grid_axis_equispaced(axes + o, axis_len[a]))
-      return c->fail(KGP_BAD_ARG, "grid axis %d is not equispaced and increasing: only equispaced grids are built", a);
+    // interpgrid / deriv_x dispatch per axis on equi(xg,i) (apxGrid.m:453-465, deriv_x.m:11-15): an equispaced axis gets the cubic
+    // eqinterp, any other INCREASING axis the linear neqinterp (apxGrid.m:547-557).  The reference also sorts an unsorted axis
+    // and maps back through the permutation; that is not built: such an axis is refused.
+    if (!kgp_grid_axis_equispaced(axes + o, axis_len[a])) {
+      for (int i = 1; i < axis_len[a]; ++i)
+        if (!(axes[o + i] - axes[o + i - 1] >= 1e-10))
+          return c->fail(KGP_BAD_ARG, "grid axis %d is neither equispaced nor strictly increasing (apxGrid.m:551 'Some source points are equal' / unsorted axes are not built)", a);
+    }
     o += axis_len[a];
   }
   c->grid.axes.clear();
   o = 0;
   for (int a = 0; a < n_axes; ++a) { c->grid.axes.emplace_back(axes + o, axes + o + axis_len[a]); o += axis_len[a]; }
   c->grid.toep.assign(n_axes, 0);
+  c->grid.neq.assign(n_axes, 0);
+  for (int a = 0; a < n_axes; ++a) c->grid.neq[a] = kgp_grid_axis_equispaced(c->grid.axes[a].data(), (int)c->grid.axes[a].size()) ? 0 : 1;
   c->grid.set = true; c->grid.version++;
   return KGP_OK;
 }
@@ -255,7 +261,10 @@ int kgp_grid_set_toeplitz(kgp_ctx* c, int n_axes, const int* flags) {
   if (!c) return KGP_BAD_ARG;
   if (!c->grid.set || n_axes != (int)c->grid.axes.size()) return c->fail(KGP_NO_GRID, "set the grid axes first (kgp_grid_set_host)");
   c->grid.toep.assign(n_axes, 0);
-  if (flags) for (int a = 0; a < n_axes; ++a) c->grid.toep[a] = flags[a] ? 1 : 0;
+  if (flags) for (int a = 0; a < n_axes; ++a) {
+    if (flags[a] && a < (int)c->grid.neq.size() && c->grid.neq[a]) return c->fail(KGP_BAD_ARG, "Subgrid not equispaced.");   // apxGrid.m:262-263
+    c->grid.toep[a] = flags[a] ? 1 : 0;
+  }
   c->grid.version++;
   return KGP_OK;
 }

@@ -38,6 +38,7 @@ struct Model {
 struct Grid {
   std::vector<std::vector<double>> axes;   // xg{d} = equispaced axis values
   std::vector<int> toep;                   // xg{d} was a nested cell {axis}: Toeplitz factor (apxGrid.m:258-281)
+  std::vector<int> neq;                    // axis fails equi() (apxGrid.m:684-695): linear neqinterp instead of cubic eqinterp
   bool set = false; unsigned long version = 0;
 };
 

@@ -32,7 +32,7 @@ struct GridState {
   DevBuf kp0, kp1, gpad, tpad, upad;       // large-factor Kronecker MVM through the DMMA GEMM: zero-padded factors and grid matrices
   DevBuf pdz, prr, bar, part4, g0b, wmaxd; int num_sms = 0; size_t smem_optin = 0; int cg_level_used = -1;
   int wmax = 0; int wmax_ctas = 0; unsigned long wmax_slot_ver = 0, wmax_grid_ver = 0; int wmax_slot = -1;
-  int p = 0; int ng[GRID_MAXP] = {0}; long N = 0;
+  int p = 0; int ng[GRID_MAXP] = {0}; long N = 0; bool any_neq = false;
   long koff[GRID_MAXP] = {0};            // offsets of factor i inside Kf / Vf
   int eoff_h[GRID_MAXP] = {0};
   unsigned long grid_ver = 0;
@@ -98,13 +98,16 @@ static int grid_setup(kgp_ctx* c, GridState* g, GridDesc& G) {
     g->grid_ver = c->grid.version;
   }
   memset(&G, 0, sizeof G);
+  g->any_neq = false;
   G.p = p; g->p = p; long o = 0, N = 1, ko = 0; int eo = 0;
   for (int d = 0; d < p; ++d) {
     const std::vector<double>& a = c->grid.axes[d];
     G.ng[d] = (int)a.size(); G.stride[d] = N; N *= G.ng[d];
     G.ax[d] = g->axes.d() + o; o += (long)a.size();
-    G.s0[d] = a[0]; G.ds[d] = a[1] - a[0];
-    G.range[d] = *std::max_element(a.begin(), a.end()) - *std::min_element(a.begin(), a.end());
+    const bool neq = d < (int)c->grid.neq.size() && c->grid.neq[d] != 0;
+    g->any_neq |= neq;
+    G.s0[d] = a[0]; G.ds[d] = neq ? 0.0 : a[1] - a[0];           // ds = 0 marks a non-equispaced axis for the interpolation kernels
+    G.range[d] = neq ? 1.0 : *std::max_element(a.begin(), a.end()) - *std::min_element(a.begin(), a.end());   // deriv_x.m:11-15: wi = 1
     g->ng[d] = G.ng[d]; g->koff[d] = ko; ko += (long)G.ng[d] * G.ng[d]; g->eoff_h[d] = eo; eo += G.ng[d];
   }
   G.N = N; g->N = N;
@@ -1042,6 +1045,8 @@ int grid_eval(kgp_ctx* c, int slot, int want, double* nlZ_out, double* dnlZ_out)
   EigBatch eb; memset(&eb, 0, sizeof eb); size_t eig_smem = 0;
   bool toep[GRID_MAXP] = {false}, any_toep = false;
   for (int d = 0; d < G.p; ++d) { toep[d] = d < (int)c->grid.toep.size() && c->grid.toep[d] != 0; any_toep |= toep[d]; }
+  if (g->any_neq && (any_toep || m.opt.cg_precond || m.opt.pred_var != 0 || slq))
+    return c->fail(KGP_BAD_ARG, "non-equispaced grid axes (neqinterp) run with the plain CG and the Fiedler / Chebyshev log-det only");
   if (any_toep && (m.opt.cg_precond || m.opt.pred_var != 0))
     return c->fail(KGP_BAD_ARG, "opt.cg_precond / opt.pred_var need the factor eigenvectors: not available for Toeplitz factors (nested xg)");
   for (int d = 0; d < G.p; ++d) {
@@ -1099,7 +1104,7 @@ int grid_eval(kgp_ctx* c, int slot, int want, double* nlZ_out, double* dnlZ_out)
   if (m.opt.cg_precond) {
     rc = pcg_solve(c, g, G, slot, sw, m.opt.cg_tol, maxit, g->ym.d(), g->x.d(), true);
     if (rc) return rc;
-  } else if (G.p <= 2 && !legacy_cg && c->px_ok && dist_rows_sharded(c->nranks, n, G.N)) {
+  } else if (G.p <= 2 && !legacy_cg && !g->any_neq && c->px_ok && dist_rows_sharded(c->nranks, n, G.N)) {
     // row-sharded solve (SURVEY 8(e) KISS-GP (ii)): this rank's contiguous share of the points, the two reductions
     // of every iteration cross the ranks over peer memory inside the persistent kernel
     const long lo = dist_row_begin(c->rank, c->nranks, n), hi = dist_row_begin(c->rank + 1, c->nranks, n);
@@ -1114,7 +1119,7 @@ int grid_eval(kgp_ctx* c, int slot, int want, double* nlZ_out, double* dnlZ_out)
     if (rc) return rc;
     NcclApi& api = nccl_api(nullptr);
     KGP_NCCL(c, api, api.AllReduce(g->x.p, g->x.p, (size_t)n, KGP_NCCL_DOUBLE, KGP_NCCL_SUM, c->nccl_comm, st));
-  } else if (G.p <= 2 && !legacy_cg) {
+  } else if (G.p <= 2 && !legacy_cg && !g->any_neq) {          // (non-equispaced axes: general streaming kernels below)
     rc = cg_solve_sorted(c, g, G, slot, g->ym.d(), n, 1, sw, m.opt.cg_tol, maxit);
     if (rc) return rc;
     cg_unsort_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(g->sx.d(), (const int*)g->perm.p, n, sw, g->x.d());   // alpha = sW q
@@ -1254,6 +1259,7 @@ int grid_solve(kgp_ctx* c, int slot, const double* R, int m, double* out) {
   }
   GridDesc G; int rc = grid_setup(c, g, G); if (rc) return rc;
   if (G.p > 2) return c->fail(KGP_BAD_ARG, "batched solve is built for 1-D and 2-D grids");
+  if (g->any_neq) return c->fail(KGP_BAD_ARG, "batched solve needs equispaced grid axes (cell-sorted CG)");
   Slot& S = c->slots[slot]; Model& mo = c->model; const long n = S.n;
   const double sn2 = exp(2.0 * mo.hyp_lik), sw = 1.0 / sqrt(sn2);
   const int maxit = mo.opt.cg_maxit > 0 ? mo.opt.cg_maxit : (int)std::min<long>(n, 20);
@@ -1309,6 +1315,7 @@ int grid_pred_var(kgp_ctx* c, int slot, const double* Rg, const double* Rn, int 
   }
   GridDesc G; int rc = grid_setup(c, g, G); if (rc) return rc;
   if (G.p > 2) return c->fail(KGP_BAD_ARG, "pred_var is built for 1-D and 2-D grids");
+  if (g->any_neq) return c->fail(KGP_BAD_ARG, "pred_var needs equispaced grid axes (cell-sorted CG)");
   Slot& S = c->slots[slot]; const long n = S.n, N = G.N; const int D = S.D;
   const double sn2 = exp(2.0 * mo.hyp_lik), sw = 1.0 / sqrt(sn2), sn = sqrt(sn2);
   const int maxit = mo.opt.cg_maxit > 0 ? mo.opt.cg_maxit : (int)std::min<long>(n, 20);
@@ -1496,7 +1503,7 @@ int grid_create(kgp_ctx* c, int slot, int eq, double k) {
     axes.push_back(ax);
   }
   KGP_CUDA(c, cudaGetLastError());
-  c->grid.axes = axes; c->grid.toep.assign(axes.size(), 0); c->grid.set = true; c->grid.version++;
+  c->grid.axes = axes; c->grid.toep.assign(axes.size(), 0); c->grid.neq.assign(axes.size(), 0); c->grid.set = true; c->grid.version++;
   return KGP_OK;
 }
 

@@ -36,9 +36,33 @@ __device__ __forceinline__ double dkcub(double x) {
 
 // eqinterp for one coordinate: first node j (0-based), weights c[4], optional derivative weights
 // dc[4] (already multiplied by ns-1 as in apxGrid.m:512).
+// neqinterp for one coordinate (apxGrid.m:547-557): piecewise linear on an increasing, non-equispaced axis, expressed as a
+// 4-node stencil with two zero weights so that every kernel keeps its 4^p structure.  Interval ii from
+// histc(t, [-inf; s(2:end-1); inf]); outside the axis the weight 1 goes to the end node and the derivative is 0.  The derivative
+// weights are per unit of x (deriv_x.m:11-15 divides by w_i = 1 for such an axis: GridDesc.range = 1).
+template <bool DERIV>
+__device__ __forceinline__ void neqinterp1(const double* __restrict__ ax, int ns, double t, int& j, double c[4], double dc[4]) {
+  int lo = 0, hi = ns - 2;
+  while (lo < hi) { const int mid = (lo + hi + 1) >> 1; if (ax[mid] <= t) lo = mid; else hi = mid - 1; }
+  const int ii = lo;
+  double d0 = t - ax[ii], d1 = ax[ii + 1] - t;
+  const bool out = (d0 < 0.0) || (d1 < 0.0);
+  d0 = fmax(d0, 0.0); d1 = fmax(d1, 0.0);
+  const double inv = 1.0 / (d1 + d0);
+  int jb = ii - 1; if (jb < 0) jb = 0; if (jb > ns - 4) jb = ns - 4;
+  const int s0 = ii - jb;
+#pragma unroll
+  for (int q = 0; q < 4; ++q) {
+    c[q] = (q == s0) ? d1 * inv : ((q == s0 + 1) ? d0 * inv : 0.0);
+    if (DERIV) dc[q] = out ? 0.0 : ((q == s0) ? -inv : ((q == s0 + 1) ? inv : 0.0));
+  }
+  j = jb;
+}
+
 template <bool DERIV>
 __device__ __forceinline__ void eqinterp1(const double* __restrict__ ax, int ns, double s0, double ds, double t,
                                           int& j, double c[4], double dc[4]) {
+  if (ds <= 0.0) { neqinterp1<DERIV>(ax, ns, t, j, c, dc); return; }       // non-equispaced axis (grid_setup sets ds = 0)
   const double u = (t - s0) / ds;
   double jf = floor(u) + 1.0;
   const double w = u - jf + 1.0;

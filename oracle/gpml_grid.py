@@ -100,6 +100,29 @@ def eqinterp(s, t):
     return J, C, dC
 
 
+def equi(ax):
+    """apxGrid.m:684-695: the axis is equispaced when max |diff(ax) - (ax[1] - ax[0])| < 1e-9."""
+    ax = np.asarray(ax, dtype=np.float64)
+    return ax.size < 2 or float(np.max(np.abs(np.diff(ax) - (ax[1] - ax[0])))) < 1e-9
+
+
+def neqinterp(s, t):
+    """apxGrid.m:547-557: piecewise linear interpolation on a non-equispaced (increasing) axis; J (nt,2), C, dC.
+    The reference sorts s and maps back through `ord`; only increasing axes are restated (ord = identity)."""
+    s = np.asarray(s, dtype=np.float64); t = np.asarray(t, dtype=np.float64)
+    ns = s.size
+    assert ns >= 2 and np.all(np.diff(s) >= 1e-10), 'Some source points are equal.'
+    ii = np.searchsorted(s[1:ns - 1], t, side='right')            # histc(t, [-inf; s(2:end-1); inf]) - 1
+    d0 = t - s[ii]; d1 = s[ii + 1] - t
+    d0n = d0 < 0; d1n = d1 < 0
+    d0 = np.where(d0n, 0.0, d0); d1 = np.where(d1n, 0.0, d1)
+    J = np.stack([ii, ii + 1], axis=1).astype(np.int64)
+    C = np.stack([d1 / (d1 + d0), d0 / (d1 + d0)], axis=1)
+    nz = 1.0 - (d1n | d0n)
+    dC = np.stack([-nz / (d1 + d0), nz / (d1 + d0)], axis=1)
+    return J, C, dC
+
+
 def interpgrid(xg, x, want_deriv=False):
     """Sparse Mx (n x N) and optionally dMx[i]; grid linear index has the first axis fastest."""
     x = np.asarray(x, dtype=np.float64)
@@ -111,7 +134,7 @@ def interpgrid(xg, x, want_deriv=False):
     dC = [np.ones((n, 1)) for _ in range(p)]
     s = 1
     for i in range(p):
-        Ji, Ci, dCi = eqinterp(xg[i], x[:, i])
+        Ji, Ci, dCi = eqinterp(xg[i], x[:, i]) if equi(xg[i]) else neqinterp(xg[i], x[:, i])   # apxGrid.m:453-465
         J = (J[:, :, None] + s * Ji[:, None, :]).reshape(n, -1)
         C = (C[:, :, None] * Ci[:, None, :]).reshape(n, -1)
         for jd in range(p):
@@ -580,7 +603,7 @@ def dlik_grid(hyp, mean, kind, xg, x, y, opt=None, Q=0, h=1e-5):
     beta = post['Kalpha']
     cols = []
     for i in range(x.shape[1]):
-        wi = xg[i].max() - xg[i].min()
+        wi = (xg[i].max() - xg[i].min()) if equi(xg[i]) else 1.0     # deriv_x.m:11-15
         xm = x.copy(); xm[:, i] -= h
         xp = x.copy(); xp[:, i] += h            # reference: -h then +2h (deriv_x.m:16-19)
         dmi = (mean_eval(mean, hyp.get('mean', []), xp)[0] - mean_eval(mean, hyp.get('mean', []), xm)[0]) / (2 * h)

@@ -77,7 +77,7 @@ def test_grid_axis_equispaced_rule():
         a = np.ascontiguousarray(a, dtype=np.float64)
         return l.kgp_grid_axis_equispaced(a.ctypes.data_as(C.c_void_p), a.size)
     assert eq(np.linspace(-1, 2, 50)) == 1
-    assert eq(np.linspace(-1, 2, 50) ** 3) == 0                       # non-uniform
+    assert eq(np.linspace(-1, 2, 50) ** 3) == 0                       # non-uniform (-> neqinterp, or refused if not increasing)
     assert eq(np.linspace(2, -1, 50)) == 0                            # decreasing
     a = np.linspace(0, 1, 20); a[7] += 1e-8
     assert eq(a) == 0                                                 # beyond the 1e-9 tolerance

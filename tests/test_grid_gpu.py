@@ -404,9 +404,9 @@ def test_grid_engine_agrees_with_exact_engine_on_fine_grid(built_lib):
     assert errs[1][0] < 2e-5 and errs[1][1] < 2e-5 and errs[1][0] < errs[0][0] / 30, errs
 
 
-def test_fractional_k_and_non_equispaced_axes(built_lib):
-    """creategrid keeps k fractional in du (apxGrid.m:404-409); a hand-supplied non-equispaced axis is refused (the
-    neqinterp branch of apxGrid.m:547-557 is not built) instead of being silently treated as equispaced."""
+def test_fractional_k_and_unsorted_axes(built_lib):
+    """creategrid keeps k fractional in du (apxGrid.m:404-409); a hand-supplied axis that is neither equispaced nor increasing is
+    refused (the reference would sort it and map back through the permutation: not built)."""
     import gpml_grid as gg
     from kgp_b200 import B200GP, _cabi
     rng = np.random.RandomState(1); X = rng.randn(300, 1); y = rng.randn(300)
@@ -417,8 +417,41 @@ def test_fractional_k_and_non_equispaced_axes(built_lib):
     bad = B200GP()
     with pytest.raises(_cabi.KgpError) as ei:
         bad.configure(1, {'lik': -1.0, 'mean': [], 'cov': [[0.0], [0.0]]}, {}, 'infGrid', 'meanZero', 'covSEiso', 'likGauss', 'dlikGrid',
-                      grid_kwargs={'eq': 1, 'k': 20., 'xg': [np.linspace(-3, 3, 20) ** 3]}, verbose=0)
+                      grid_kwargs={'eq': 1, 'k': 20., 'xg': [np.linspace(-3, 3, 20)[::-1].copy() ** 3]}, verbose=0)
     assert ei.value.code == _cabi.BAD_ARG
+
+
+@pytest.mark.parametrize('shape', ['1d', 'neq_x_eq'])
+def test_non_equispaced_axes_vs_oracle(built_lib, shape):
+    """SURVEY 8(f)-4, non-equispaced axes: interpgrid dispatches per axis on equi() (apxGrid.m:453-465); a non-equispaced increasing
+    axis gets the linear neqinterp (apxGrid.m:547-557) and w_i = 1 in deriv_x (deriv_x.m:11-15).  Engine vs oracle at tight CG."""
+    import gpml_grid as gg
+    from kgp_b200 import B200GP
+    rng = np.random.RandomState(5)
+    opt = {'cg_maxit': 5000, 'cg_tol': 1e-12}
+    if shape == '1d':
+        n = 400; X = rng.rand(n, 1); y = np.sin(5 * X[:, 0]) + 0.1 * rng.randn(n)
+        xg = [np.sort(np.concatenate([[-0.3, 1.3], rng.rand(38) * 1.4 - 0.2]))]; Xs = rng.rand(60, 1) * 1.8 - 0.4
+        hc = [[np.log(0.2)], [0.1]]
+    else:
+        n = 900; X = rng.rand(n, 2); y = np.sin(4 * X[:, 0]) + X[:, 1] + 0.1 * rng.randn(n)
+        xg = [np.sort(np.concatenate([[-0.3, 1.3], rng.rand(22) * 1.4 - 0.2])), np.linspace(-0.4, 1.4, 19)]
+        Xs = rng.rand(80, 2) * 1.6 - 0.3
+        hc = [[np.log(0.3)], [0.0]]
+    D = X.shape[1]
+    gp = B200GP()
+    gp.configure(D, {'lik': np.log(0.1), 'mean': [], 'cov': hc}, opt, 'infGrid', 'meanZero', 'covSEiso', 'likGauss', 'dlikGrid',
+                 grid_kwargs={'eq': 1, 'k': 20., 'xg': xg}, verbose=0)
+    gp.update_data('tr', X, y[:, None])
+    nlZ, g = gp.eng.eval(0, 2, gp._n_hyp)
+    dX = gp.get_dlik_dx('tr'); ymu = gp.predict(Xs)
+    hv = gp._hyp_vec(); nc = gp.hyp['cov'].size
+    oh = {'cov': hv[:nc], 'lik': gp.hyp['lik'], 'mean': []}
+    post, nlZ0, d0 = gg.inf_grid(oh, ['meanZero'], 'covSEiso', xg, X, y, opt)
+    g0 = np.concatenate([d0['cov'], [d0['lik']]])
+    assert rel(nlZ, nlZ0) < 1e-8 and rel(g, g0) < 1e-7 and rel(gp.alpha(), post['alpha']) < 1e-7
+    assert rel(dX, gg.dlik_grid(oh, ['meanZero'], 'covSEiso', xg, X, y, opt)) < 1e-7
+    assert rel(ymu, gg.predict_grid(oh, ['meanZero'], 'covSEiso', xg, post, Xs)[2]) < 1e-7
 
 
 @pytest.mark.parametrize('kind,shape', [('covSEiso', '2d'), ('covSM', '2d'), ('covSEiso', '1d_1000'), ('covSM', 'both')])

@@ -299,3 +299,27 @@ def test_toeplitz_mode_inference_and_derivatives(kind):
     assert np.allclose(pt2['alpha'], pd['alpha'], rtol=1e-8, atol=1e-10)
     assert np.allclose(gg.dlik_grid(hyp, ['meanZero'], kind, [[a1], [a2]], X, y, opt, Q=Q),
                        gg.dlik_grid(hyp, ['meanZero'], kind, xg_d, X, y, opt, Q=Q), rtol=1e-7, atol=1e-9)
+
+
+def test_neqinterp_matches_definition_and_gradcheck():
+    """Non-equispaced axes (apxGrid.m:453-465 dispatch on equi(), neqinterp :547-557): linear weights on the bracketing nodes, weight 1
+    on the end node outside the axis, rows sum to 1; dlik_grid (deriv_x.m:11-15: w_i = 1) against central differences of nlZ."""
+    ax = np.array([0., 0.3, 0.5, 1.1, 1.2, 2.0])
+    J, C, dC = gg.neqinterp(ax, np.array([-0.2, 0.29, 0.8, 2.5]))
+    assert J.tolist() == [[0, 1], [0, 1], [2, 3], [4, 5]]
+    assert np.allclose(C, [[1, 0], [1 / 30, 29 / 30], [0.5, 0.5], [0, 1]]) and np.allclose(C.sum(1), 1)
+    assert np.allclose(dC[[0, 3]], 0) and np.allclose(dC[2], [-1 / 0.6, 1 / 0.6])
+    assert gg.equi(np.linspace(0, 1, 9)) and not gg.equi(ax)
+    rng = np.random.RandomState(5)
+    n = 120; X = rng.rand(n, 2); y = np.sin(4 * X[:, 0]) + X[:, 1] + 0.1 * rng.randn(n)
+    a1 = np.sort(np.concatenate([[-0.3, 1.3], rng.rand(22) * 1.4 - 0.2])); a2 = np.linspace(-0.4, 1.4, 19)       # neq x eq
+    hyp = {'cov': np.array([np.log(0.3), 0.0, np.log(0.4), 0.1]), 'lik': np.log(0.1), 'mean': []}
+    opt = {'cg_maxit': 3000, 'cg_tol': 1e-13}
+    Mx = gg.interpgrid([a1, a2], X)
+    assert np.allclose(Mx.sum(1), 1.0) and (Mx.getnnz(axis=1) <= 8).all()
+    dX = gg.dlik_grid(hyp, ['meanZero'], 'covSEiso', [a1, a2], X, y, opt)
+    f = lambda xx: gg.inf_grid(hyp, ['meanZero'], 'covSEiso', [a1, a2], xx, y, opt, want_grad=False)[1]
+    for (i, d) in ((3, 0), (40, 1), (77, 0)):
+        e = np.zeros_like(X); e[i, d] = 1e-6
+        # the Fiedler bound does not depend on x, the data-fit term does; linear interpolation is differentiable inside a cell
+        assert abs((f(X + e) - f(X - e)) / 2e-6 - dX[i, d]) < 1e-5 * max(1.0, abs(dX[i, d]))
