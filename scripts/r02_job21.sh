@@ -1,0 +1,7 @@
+#!/bin/bash
+set -x
+O=gpurun_out/job21; mkdir -p $O
+timeout 1500 python -m pytest tests -m gpu -q > $O/pytest.log 2>&1; echo "pytest rc=$?" >> $O/pytest.log
+timeout 300 python -c "import __graft_entry__ as g; g.smoke()" > $O/smoke.log 2>&1; echo "smoke rc=$?" >> $O/smoke.log
+( time timeout 1200 python bench.py --steps 5 --warmup 3 ) > $O/bench_n1.log 2>&1; echo "rc=$?" >> $O/bench_n1.log
+( time timeout 1500 python bench.py --impl reference --steps 3 --warmup 1 ) > $O/bench_ref.log 2>&1; echo "rc=$?" >> $O/bench_ref.log
