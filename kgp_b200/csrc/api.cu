@@ -89,7 +89,8 @@ int kgp_ctx_destroy(kgp_ctx* c) {
   dist_free(c);
   DevBuf* bufs[] = {&c->M, &c->W2, &c->Dws, &c->xs, &c->s, &c->mu, &c->inv_ell, &c->ym, &c->alpha, &c->tvec,
                     &c->parts, &c->rows, &c->scal, &c->hypm, &c->dX, &c->fac, &c->pred_K, &c->pred_x, &c->pred_s,
-                    &c->pred_a, &c->pred_b, &c->pred_out, &c->pred_X, &c->smV, &c->smM, &c->smAcc};
+                    &c->pred_a, &c->pred_b, &c->pred_out, &c->pred_X, &c->smV, &c->smM, &c->smAcc, &c->gws[0], &c->gws[1],
+                    &c->gcnt[0], &c->gcnt[1]};
   for (DevBuf* b : bufs) b->release();
   for (auto& s : c->slots) { s.X.release(); s.y.release(); }
   if (c->d_info) cudaFree(c->d_info);

@@ -60,6 +60,7 @@ struct kgp_ctx {
 
   // exact-path device state
   kgp::DevBuf M, W2, Dws;             // L (lower) | Z upper -> full B^{-1} | diagonal nb-blocks of B^{-1}
+  kgp::DevBuf gws[2], gcnt[2];        // small-tile GEMM (dgemm_nt_small.cuh): split-K partials + arrival counters, [main | panel stream]
   kgp::DevBuf xs, s, mu, inv_ell, ym, alpha, tvec, parts, rows, scal, hypm, dX, fac;
   kgp::DevBuf pred_K, pred_x, pred_s, pred_a, pred_b, pred_out, pred_X;
   kgp::DevBuf smV, smM, smAcc;        // covSM exact path: 4 pi^2 v, 2 pi m tables and the reduction accumulators

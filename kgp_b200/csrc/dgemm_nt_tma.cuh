@@ -11,7 +11,7 @@
 // sm_100a has no FP64 kind for tcgen05.mma (ptxas rejects .kind::f64), so the math instruction stays the warp-level
 // DMMA.8x8x4 (mma.sync.m8n8k4.f64) with register accumulators; TMA/mbarrier are the Blackwell parts that apply.
 #pragma once
-#include "dgemm_nt.cuh"
+#include "dgemm_nt_small.cuh"
 #include <cuda.h>
 
 namespace kgp {
@@ -279,7 +279,9 @@ inline bool gemm_launch_tma(const GemmArgs& g, long nt, bool persistent, cudaStr
 
 // tile_ctas: one CTA per tile instead of persistent CTAs -- a higher-priority stream's kernels (panel factorisation,
 // NCCL) then get SMs at tile granularity (~80 us) instead of waiting for the whole launch
-inline void gemm_launch(const GemmArgs& g_in, cudaStream_t st, bool tile_ctas = false) {
+// workspace of the small-tile path (dgemm_nt_small.cuh); one per stream that may carry small launches
+struct GemmSmallWs { double* ws; size_t ws_bytes; unsigned* cnt; long cnt_n; };
+inline void gemm_launch(const GemmArgs& g_in, cudaStream_t st, bool tile_ctas = false, const GemmSmallWs* sw = nullptr) {
   GemmArgs g = g_in;
   long nt = gemm_num_tiles(g);
   if (g.shape == GEMM_LOWER) {
@@ -299,6 +301,13 @@ inline void gemm_launch(const GemmArgs& g_in, cudaStream_t st, bool tile_ctas = 
   if (g.tile_cnt > 0) nt = g.tile_cnt;                 // a stage of a staged launch (tile_off already points at its first tile)
   if (nt <= 0 || g.kend <= g.kbeg) return;
   g.cdiag_only = g_gemm_prefetch_c;
+  if (sw) {
+    int nchmax = 0; size_t need = 0;
+    if (gemm_small_eligible(g, nt, nchmax, need) && need <= sw->ws_bytes && nt * 16 <= sw->cnt_n) {
+      gemm_launch_small(g, nt, nchmax, sw->ws, sw->cnt, st);
+      return;
+    }
+  }
   if (g_gemm_bn == 64) {
     const long items = 2 * nt, res = 2L * g_gemm_num_sms;
     const long grid = (g_gemm_persist && !tile_ctas && items > res) ? res : items;

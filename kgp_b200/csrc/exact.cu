@@ -38,20 +38,41 @@ static inline double count_gemm(kgp_ctx* c, const GemmArgs& g) {
   c->stats.gemm_flops += f;
   return f;
 }
+// launches of the reference-sized problems (np <= KGP_SMALL_NP, default 2048) that cannot fill the GPU with 128-tiles go
+// to the small-tile kernel; the decision depends only on the problem, never on the number of ranks
+static const GemmSmallWs* small_ws(kgp_ctx* c, const GemmArgs& g, GemmSmallWs& sw) {
+  static const int small_np = getenv("KGP_SMALL_NP") ? atoi(getenv("KGP_SMALL_NP")) : 2048;
+  if (c->np > small_np || c->nranks > 1) return nullptr;
+  int nchmax = 0; size_t need = 0;
+  if (!gemm_small_eligible(g, gemm_num_tiles(g), nchmax, need)) return nullptr;
+  const int w = (c->stream_p && c->stream == c->stream_p) ? 1 : 0;
+  constexpr long NCNT = 96 * 16;
+  if (!c->gcnt[w].p) {
+    if (c->gcnt[w].ensure(NCNT * sizeof(unsigned)) != cudaSuccess) return nullptr;
+    cudaMemsetAsync(c->gcnt[w].p, 0, NCNT * sizeof(unsigned), c->stream);
+  }
+  if (need > c->gws[w].bytes) {
+    cudaStreamSynchronize(c->stream);                      // a launch in flight may still use the old buffer
+    if (c->gws[w].ensure(need) != cudaSuccess) return nullptr;
+  }
+  sw.ws = c->gws[w].d(); sw.ws_bytes = c->gws[w].bytes; sw.cnt = (unsigned*)c->gcnt[w].p; sw.cnt_n = NCNT;
+  return &sw;
+}
 static inline void gemm(kgp_ctx* c, const GemmArgs& g, bool tile_ctas = false) {
   if (g.ntm <= 0 || g.ntn <= 0) return;
   const double fl = count_gemm(c, g);
+  GemmSmallWs sws; const GemmSmallWs* sw = small_ws(c, g, sws);
   if (c->profiling) {
     if (c->gev_used + 2 > c->gev.size()) {
       size_t old = c->gev.size(); c->gev.resize(old + 256);
       for (size_t i = old; i < c->gev.size(); ++i) cudaEventCreate(&c->gev[i]);
     }
     cudaEventRecord(c->gev[c->gev_used], c->stream);
-    gemm_launch(g, c->stream, tile_ctas);
+    gemm_launch(g, c->stream, tile_ctas, sw);
     cudaEventRecord(c->gev[c->gev_used + 1], c->stream);
     c->gev_class.push_back(c->gemm_class); c->gev_flops.push_back(fl);
     c->gev_used += 2;
-  } else gemm_launch(g, c->stream, tile_ctas);
+  } else gemm_launch(g, c->stream, tile_ctas, sw);
 }
 static void gemm_prof_collect(kgp_ctx* c) {
   double ms = 0.0;
@@ -70,12 +91,16 @@ static inline GemmArgs mkgemm(const double* A, long lda, const double* B, long l
   return g;
 }
 
+// 32-row CTAs while a launch has too few 128-row blocks to occupy the GPU (the reference-sized problems)
+static inline bool trsm_small(kgp_ctx* c, long mrows) {
+  static const int on = getenv("KGP_SMALL_TRSM") ? atoi(getenv("KGP_SMALL_TRSM")) : 1;
+  return on && mrows <= 4096;
+}
 // X (mrows x w, leading dim ldx) <- X * Lblk^{-T}, Lblk lower w x w (w multiple of 128, <= NB)
 static void trsm_block(kgp_ctx* c, double* X, long ldx, long mrows, const double* Lblk, long ldl, int w) {
   const int nc = w / 128;
   for (int cb = 0; cb < nc; ++cb) {
-    trsm128_rows_kernel<<<(unsigned)(mrows / 128), TR_THREADS, TR_SMEM, c->stream>>>(
-        X + cb * 128, ldx, mrows, Lblk + (long)cb * 128 * ldl + cb * 128, ldl);
+    trsm128_rows_launch(X + cb * 128, ldx, mrows, Lblk + (long)cb * 128 * ldl + cb * 128, ldl, c->stream, trsm_small(c, mrows));
     c->stats.kernel_launches++;
     if (cb + 1 < nc) c->gemm_class = 3;
     if (cb + 1 < nc)
@@ -92,8 +117,7 @@ static void factor_panel(kgp_ctx* c, long k0, int w) {
     potrf_diag128_kernel<<<1, PD_THREADS, PD_SMEM, c->stream>>>(M + j * ld + j, ld, (int)j, c->d_info);
     c->stats.kernel_launches++;
     if (mrows > 0) {
-      trsm128_rows_kernel<<<(unsigned)(mrows / 128), TR_THREADS, TR_SMEM, c->stream>>>(
-          M + r0 * ld + j, ld, mrows, M + j * ld + j, ld);
+      trsm128_rows_launch(M + r0 * ld + j, ld, mrows, M + j * ld + j, ld, c->stream, trsm_small(c, mrows));
       c->stats.kernel_launches++;
       const long ncols = k0 + w - r0;
       c->gemm_class = 0;
@@ -622,7 +646,7 @@ int exact_eval(kgp_ctx* c, int slot, int want, double* nlZ_out, double* dnlZ_out
     cudaEventRecord(c->ev[6], st);
   } else if (want >= 1 && use_tiles) {
     rc = zzt_reduce_dist(c, n, sf2, 1.0 / sn2); if (rc) return rc;
-    grad_scalars_kernel<<<1, 1024, 0, st>>>(c->rows.d(), n, Dp, c->xs.d(), c->alpha.d(), c->scal.d());
+    grad_scalars_kernel<<<4 + Dp, 1024, 0, st>>>(c->rows.d(), n, Dp, c->xs.d(), c->alpha.d(), c->scal.d());
     dx_from_rows_kernel<<<(unsigned)((n * D + 255) / 256), 256, 0, st>>>(c->rows.d(), n, D, Dp, c->fac.d(), c->dX.d());
     if (nmean) mean_grad_kernel<<<D + 1, 1024, 0, st>>>(S.X.d(), c->alpha.d(), n, D, c->scal.d() + 110);
     c->stats.kernel_launches += 2 + (nmean ? 1 : 0);
@@ -642,7 +666,7 @@ int exact_eval(kgp_ctx* c, int slot, int want, double* nlZ_out, double* dnlZ_out
     }
     const long tot = np * (Dp + 3);
     reduce_rows_kernel<<<(unsigned)((tot + 255) / 256), 256, 0, st>>>(c->parts.d(), np, nsplit, Dp + 3, c->rows.d());
-    grad_scalars_kernel<<<1, 1024, 0, st>>>(c->rows.d(), n, Dp, c->xs.d(), c->alpha.d(), c->scal.d());
+    grad_scalars_kernel<<<4 + Dp, 1024, 0, st>>>(c->rows.d(), n, Dp, c->xs.d(), c->alpha.d(), c->scal.d());
     dx_from_rows_kernel<<<(unsigned)((n * D + 255) / 256), 256, 0, st>>>(c->rows.d(), n, D, Dp, c->fac.d(), c->dX.d());
     if (nmean) mean_grad_kernel<<<D + 1, 1024, 0, st>>>(S.X.d(), c->alpha.d(), n, D, c->scal.d() + 110);
     c->stats.kernel_launches += 4 + (nmean ? 1 : 0);
@@ -797,7 +821,8 @@ int exact_init(kgp_ctx* c) {
   KGP_CUDA(c, gemm_init());
   KGP_CUDA(c, gemm_tma_init());
   KGP_CUDA(c, cudaFuncSetAttribute(potrf_diag128_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, PD_SMEM));
-  KGP_CUDA(c, cudaFuncSetAttribute(trsm128_rows_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, TR_SMEM));
+  KGP_CUDA(c, cudaFuncSetAttribute(trsm128_rows_kernel_t<16>, cudaFuncAttributeMaxDynamicSharedMemorySize, TR_SMEM));
+  KGP_CUDA(c, cudaFuncSetAttribute(trsm128_rows_kernel_t<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, TR_SMEM));
   KGP_CUDA(c, cudaFuncSetAttribute(kbuild_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kbuild_smem(32)));
   return KGP_OK;
 }

@@ -142,116 +142,128 @@ __global__ void __launch_bounds__(KB_THREADS) kbuild_kernel(
 inline size_t kbuild_smem(int Dp) { int ldx = ((Dp + 11) / 16) * 16 + 4; return (size_t)(2 * 128 * ldx + 256) * 8; }
 
 // ---------------------------------------------------------------------------
-// Cholesky of one 128x128 diagonal block in shared memory (lower, row-major).
+// Cholesky of one 128 x 128 diagonal block (lower triangle, in place), one CTA: 16 owner warps + ONE PANEL WARP.
 // info: 1-based global index of the first non-positive pivot (atomicMin), else unchanged.
+//
+// The kernel is a chain of dependent FP64 operations and sits on the critical path of every panel (the reference-sized
+// problems, where four of these are most of the factorisation; the multi-GPU panel chain).  Round-2 form:
+//   * the block lives in the owners' registers as 8 x 8 tiles in the DMMA C-fragment layout: warp w holds tile row w
+//     (tiles (w, 0..w)), so the rank-8 update of a tile with a factored 128 x 8 panel is TWO DMMA.8x8x4 (k = 0..3, 4..7)
+//     instead of 64 scalar DFMAs per thread -- the update stops being the larger half of a step;
+//   * columns are processed eight at a time by the panel warp (lane l = rows l, l+32, l+64, l+96 of the panel), with
+//     shuffles alone: eight dependent rsqrt / scale / update steps without a block barrier;
+//   * look-ahead: the owners first update tile column kb+1 with panel kb and publish it, THEN update the rest while the
+//     panel warp already factors panel kb+1 (two barriers per eight columns, the panel warp never waits for the bulk).
+// Shared memory: pin[c][row] (the published panel, column-major: the panel warp reads it conflict-free),
+// pout[2][row][12] (the factored panel, row stride 12 doubles: gq*12 + tq hits 16 distinct banks per half-warp for the
+// owners' fragment loads; double-buffered because the owners still read panel kb while panel kb+1 is written).
+// The two roles run in separate branches and meet at a NAMED barrier with an explicit thread count (bar.sync 1, 544).
 // ---------------------------------------------------------------------------
 constexpr int PD_OWNERS = 512, PD_THREADS = PD_OWNERS + 32;
 constexpr int PD_SMEM = 0;
-// Cholesky of one 128 x 128 diagonal block (lower triangle, in place), one CTA: 16 owner warps + ONE PANEL WARP.
-// The block lives in the owners' registers: thread (ti, tj) holds rows 4 ti..4 ti+3 x columns 8 tj..8 tj+7.  Columns are processed
-// EIGHT at a time: the owners publish the 128 x 8 panel in shared memory, the panel warp (which holds no part of the block, so its
-// registers carry only the panel: lane l = rows 4 l..4 l+3) factors it with shuffles alone -- eight dependent
-// rsqrt / scale / update steps without a block barrier --, then every owner applies the rank-8 update to its 32 elements from
-// shared memory.  Three block barriers per eight columns (48) instead of one per column (128): the kernel is a chain of dependent
-// FP64 operations and sits on the critical path of every panel (small problems; the multi-GPU panel chain, where it was
-// 4 x ~100 us of every ~1 ms step).  The two roles run in separate branches (register allocation = the larger of the two, not
-// their sum) and meet at a NAMED barrier with an explicit thread count (bar.sync 1, 544).
-// Shared layout: element (row, k) at pan[k][(row & 7) * 16 + (row >> 3)] -- the rank-8 update reads rows 8 tj + c across a
-// half-warp, which this makes contiguous (conflict-free).
-__device__ __forceinline__ int pd_slot(int row) { return (row & 7) * 16 + (row >> 3); }
+constexpr int PD_PIN_LD = 132, PD_POUT_LD = 12;
 __device__ __forceinline__ void pd_bar() { asm volatile("bar.sync 1, %0;" ::"n"(PD_THREADS) : "memory"); }
 __global__ void __launch_bounds__(PD_THREADS) potrf_diag128_kernel(double* __restrict__ A, long ld, int j0, int* info) {
-  __shared__ double pan[8][128];
+  __shared__ __align__(16) double pin[8 * PD_PIN_LD];
+  __shared__ __align__(16) double pout[2][128 * PD_POUT_LD];
   const int tid = threadIdx.x;
   if (tid >= PD_OWNERS) {                              // ---- panel warp
     const int lane = tid & 31;
-    for (int kb = 0; kb < 16; ++kb) {
-      pd_bar();                                        // panel published
-      double p[4][8];
 #pragma unroll
-      for (int r = 0; r < 4; ++r)
+    for (int q = 0; q < 4; ++q) {                      // panels 4q .. 4q+3 have their pivot rows in register row q
+      for (int kk = 0; kk < 4; ++kk) {
+        const int kb = 4 * q + kk;
+        pd_bar();                                      // panel kb published
+        double p[4][8];
 #pragma unroll
-        for (int c = 0; c < 8; ++c) p[r][c] = pan[c][pd_slot(4 * lane + r)];
+        for (int r = q; r < 4; ++r)
 #pragma unroll
-      for (int k = 0; k < 8; ++k) {
-        const int krow = 8 * kb + k;                   // pivot row: lane 2 kb + (k >> 2), local row k & 3
-        double akk = __shfl_sync(0xffffffffu, p[k & 3][k], 2 * kb + (k >> 2));
-        if (!(akk > 0.0)) { if (lane == 0) atomicMin(info, j0 + krow + 1); akk = nan(""); }
-        const double inv = rsqrt(akk), dk = akk * inv;
-        double lc[8];
+          for (int c = 0; c < 8; ++c) p[r][c] = pin[c * PD_PIN_LD + lane + 32 * r];
 #pragma unroll
-        for (int c = k + 1; c < 8; ++c) lc[c] = __shfl_sync(0xffffffffu, p[c & 3][k], 2 * kb + (c >> 2)) * inv;   // L[8 kb + c][k]
+        for (int k = 0; k < 8; ++k) {
+          const int krow = 8 * kb + k, src = 8 * kk + k;          // pivot row krow = 32 q + src
+          double akk = __shfl_sync(0xffffffffu, p[q][k], src);
+          if (!(akk > 0.0)) { if (lane == 0) atomicMin(info, j0 + krow + 1); akk = nan(""); }
+          const double inv = rsqrt(akk), dk = akk * inv;
+          double lc[8];
 #pragma unroll
-        for (int r = 0; r < 4; ++r) {
-          const int row = 4 * lane + r;
-          if (row > krow) {
-            const double lr = p[r][k] * inv;
+          for (int c = k + 1; c < 8; ++c) lc[c] = __shfl_sync(0xffffffffu, p[q][k], 8 * kk + c) * inv;   // L[8 kb + c][k]
 #pragma unroll
-            for (int c = k + 1; c < 8; ++c) p[r][c] = fma(-lr, lc[c], p[r][c]);
-            p[r][k] = lr;
-          } else if (row == krow) p[r][k] = dk;
+          for (int r = q; r < 4; ++r) {
+            const int row = lane + 32 * r;
+            if (row > krow) {
+              const double lr = p[r][k] * inv;
+#pragma unroll
+              for (int c = k + 1; c < 8; ++c) p[r][c] = fma(-lr, lc[c], p[r][c]);
+              p[r][k] = lr;
+            } else if (row == krow) p[r][k] = dk;
+          }
         }
+        double* po = pout[kb & 1];
+#pragma unroll
+        for (int r = q; r < 4; ++r)
+#pragma unroll
+          for (int c = 0; c < 8; c += 2)
+            *reinterpret_cast<double2*>(po + (lane + 32 * r) * PD_POUT_LD + c) = make_double2(p[r][c], p[r][c + 1]);
+        pd_bar();                                      // panel kb factored
       }
-#pragma unroll
-      for (int r = 0; r < 4; ++r)
-#pragma unroll
-        for (int c = 0; c < 8; ++c) pan[c][pd_slot(4 * lane + r)] = p[r][c];
-      pd_bar();                                        // panel factored
-      pd_bar();                                        // owners are done reading it
     }
     return;
   }
-  // ---- owners
-  const int ti = tid >> 4, tj = tid & 15;
-  const int r0 = ti * 4, c0 = tj * 8;
-  const bool active = c0 <= r0 + 3;                    // the 4 x 8 block touches the lower triangle
-  double a[4][8];
+  // ---- owners: warp w = tile row w
+  const int w = tid >> 5, lane = tid & 31, gq = lane >> 2, tq = lane & 3;
+  const int row = 8 * w + gq;
+  double c[16][2];
 #pragma unroll
-  for (int r = 0; r < 4; ++r)
-#pragma unroll
-    for (int c = 0; c < 8; c += 2) {
-      double2 v = make_double2(0.0, 0.0);
-      if (active) v = *reinterpret_cast<const double2*>(A + (long)(r0 + r) * ld + c0 + c);
-      a[r][c] = v.x; a[r][c + 1] = v.y;
+  for (int J = 0; J < 16; ++J) {
+    c[J][0] = c[J][1] = 0.0;
+    if (J <= w) {
+      const double2 v = *reinterpret_cast<const double2*>(A + (long)row * ld + 8 * J + 2 * tq);
+      c[J][0] = v.x; c[J][1] = v.y;
     }
-  for (int kb = 0; kb < 16; ++kb) {
-    if (tj == kb) {                                    // publish the panel (rows above it are never read)
+  }
+  pin[(2 * tq) * PD_PIN_LD + row] = c[0][0];           // publish panel 0
+  pin[(2 * tq + 1) * PD_PIN_LD + row] = c[0][1];
+  pd_bar();
+  pd_bar();
 #pragma unroll
-      for (int r = 0; r < 4; ++r)
-#pragma unroll
-        for (int c = 0; c < 8; ++c) pan[c][pd_slot(r0 + r)] = a[r][c];
+  for (int kb = 0; kb < 15; ++kb) {
+    const double* po = pout[kb & 1];
+    if (w >= kb) {                                     // final values of tile (w, kb)
+      const double2 v = *reinterpret_cast<const double2*>(po + row * PD_POUT_LD + 2 * tq);
+      c[kb][0] = v.x; c[kb][1] = v.y;
     }
-    pd_bar();
-    pd_bar();                                          // (the panel warp factors)
-    if (active) {
-      if (tj == kb) {                                  // the factored panel back into the owners' registers
+    double a0 = 0.0, a1 = 0.0;
+    if (w > kb) {
+      a0 = -po[row * PD_POUT_LD + tq]; a1 = -po[row * PD_POUT_LD + tq + 4];
+      const double b0 = po[(8 * (kb + 1) + gq) * PD_POUT_LD + tq], b1 = po[(8 * (kb + 1) + gq) * PD_POUT_LD + tq + 4];
+      dmma884(c[kb + 1][0], c[kb + 1][1], a0, b0);
+      dmma884(c[kb + 1][0], c[kb + 1][1], a1, b1);
+      pin[(2 * tq) * PD_PIN_LD + row] = c[kb + 1][0];  // publish panel kb+1
+      pin[(2 * tq + 1) * PD_PIN_LD + row] = c[kb + 1][1];
+    }
+    pd_bar();                                          // the panel warp factors kb+1 while the rest is updated
 #pragma unroll
-        for (int r = 0; r < 4; ++r)
-#pragma unroll
-          for (int c = 0; c < 8; ++c) if (r0 + r >= 8 * kb) a[r][c] = pan[c][pd_slot(r0 + r)];
-      } else if (tj > kb) {                            // rank-8 update of the columns to the right of the panel
-#pragma unroll
-        for (int k = 0; k < 8; ++k) {
-          double lr[4], lcv[8];
-#pragma unroll
-          for (int r = 0; r < 4; ++r) lr[r] = pan[k][pd_slot(r0 + r)];
-#pragma unroll
-          for (int c = 0; c < 8; ++c) lcv[c] = pan[k][pd_slot(c0 + c)];
-#pragma unroll
-          for (int r = 0; r < 4; ++r)
-#pragma unroll
-            for (int c = 0; c < 8; ++c) a[r][c] = fma(-lr[r], lcv[c], a[r][c]);
-        }
+    for (int J = kb + 2; J < 16; ++J) {
+      if (J <= w) {
+        const double b0 = po[(8 * J + gq) * PD_POUT_LD + tq], b1 = po[(8 * J + gq) * PD_POUT_LD + tq + 4];
+        dmma884(c[J][0], c[J][1], a0, b0);
+        dmma884(c[J][0], c[J][1], a1, b1);
       }
     }
-    pd_bar();                                          // the panel buffer is rewritten in the next round
+    pd_bar();
   }
-  if (active) {
+  if (w == 15) {
+    const double2 v = *reinterpret_cast<const double2*>(pout[1] + row * PD_POUT_LD + 2 * tq);
+    c[15][0] = v.x; c[15][1] = v.y;
+  }
 #pragma unroll
-    for (int r = 0; r < 4; ++r)
-#pragma unroll
-      for (int c = 0; c < 8; ++c)
-        if (c0 + c <= r0 + r) A[(long)(r0 + r) * ld + c0 + c] = a[r][c];
+  for (int J = 0; J < 16; ++J) {
+    if (J < w) *reinterpret_cast<double2*>(A + (long)row * ld + 8 * J + 2 * tq) = make_double2(c[J][0], c[J][1]);
+    else if (J == w) {
+      if (2 * tq <= gq) A[(long)row * ld + 8 * J + 2 * tq] = c[J][0];
+      if (2 * tq + 1 <= gq) A[(long)row * ld + 8 * J + 2 * tq + 1] = c[J][1];
+    }
   }
 }
 
@@ -266,19 +278,26 @@ __global__ void __launch_bounds__(PD_THREADS) potrf_diag128_kernel(double* __res
 // off-diagonal part is plain substitution.  ~1.1 MFMA per CTA: 9 us at the FP64 tensor rate (was ~60 us of
 // dependent shuffles and divisions).
 // ---------------------------------------------------------------------------
+// WARPS = 16: 128 rows per CTA (large problems: the L block is loaded once per 128 rows).  WARPS = 4: 32 rows per
+// CTA, for the reference-sized problems where a launch has only a few hundred rows: the work of a row block is
+// bound by ONE SM's DMMA rate (9 us per 128 rows), so spreading the rows over 4x as many SMs cuts the latency.
 constexpr int TR_THREADS = 512;                 // 16 warps x 8 rows = 128 rows per CTA
 constexpr int TR_LDL = 136;                     // % 16 == 8 -> conflict-free LDS.128 B fragments
 constexpr int TR_SMEM = (128 * TR_LDL + 16 * 64) * 8;
-__global__ void __launch_bounds__(TR_THREADS, 1) trsm128_rows_kernel(
+template <int WARPS>
+__global__ void __launch_bounds__(WARPS * 32, 1) trsm128_rows_kernel_t(
     double* __restrict__ X, long ldx, long nrows, const double* __restrict__ L, long ldl) {
+  constexpr int TR_THREADS = WARPS * 32;
   extern __shared__ __align__(16) double Ls[];
   double* Di = Ls + 128 * TR_LDL;               // [16][8][8] inverses of the diagonal 8x8 blocks (row-major)
+  // lower triangle only (nothing above the diagonal is ever read), straight into shared memory: all of a thread's
+  // 16-byte copies are in flight together instead of a register-staged loop of dependent L2 round trips
   for (int q = threadIdx.x; q < 128 * 64; q += TR_THREADS) {
-    int r = q >> 6, c2 = (q & 63) * 2;
-    double2 v = make_double2(0.0, 0.0);
-    if (c2 <= r) v = *reinterpret_cast<const double2*>(L + (long)r * ldl + c2);
-    *reinterpret_cast<double2*>(Ls + r * TR_LDL + c2) = v;
+    const int r = q >> 6, c2 = (q & 63) * 2;
+    if (c2 <= r) cp_async16(Ls + r * TR_LDL + c2, L + (long)r * ldl + c2);
   }
+  cp_async_commit();
+  cp_async_wait<0>();
   __syncthreads();
   if (threadIdx.x < 128) {                      // column j of inv(D_blk): D y = e_j
     const int blk = threadIdx.x >> 3, j = threadIdx.x & 7;
@@ -296,8 +315,8 @@ __global__ void __launch_bounds__(TR_THREADS, 1) trsm128_rows_kernel(
   }
   __syncthreads();
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, gq = lane >> 2, tq = lane & 3;
-  const long row = (long)blockIdx.x * 128 + warp * 8 + gq;
-  if ((long)blockIdx.x * 128 + warp * 8 >= nrows) return;
+  const long row = (long)blockIdx.x * (WARPS * 8) + warp * 8 + gq;
+  if ((long)blockIdx.x * (WARPS * 8) + warp * 8 >= nrows) return;
   double* xp = X + row * ldx + tq * 2;
   double x[16][2];
 #pragma unroll
@@ -326,6 +345,12 @@ __global__ void __launch_bounds__(TR_THREADS, 1) trsm128_rows_kernel(
 #pragma unroll
   for (int cb = 0; cb < 16; ++cb)
     *reinterpret_cast<double2*>(xp + cb * 8) = make_double2(x[cb][0], x[cb][1]);
+}
+
+// rows: multiple of 128.  small: 32 rows per CTA
+inline void trsm128_rows_launch(double* X, long ldx, long nrows, const double* L, long ldl, cudaStream_t st, bool small) {
+  if (small) trsm128_rows_kernel_t<4><<<(unsigned)(nrows / 32), 128, TR_SMEM, st>>>(X, ldx, nrows, L, ldl);
+  else trsm128_rows_kernel_t<16><<<(unsigned)(nrows / 128), 512, TR_SMEM, st>>>(X, ldx, nrows, L, ldl);
 }
 
 // w x w block <- identity

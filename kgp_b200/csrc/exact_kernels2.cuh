@@ -173,14 +173,15 @@ __global__ void reduce_rows_kernel(const double* __restrict__ partial, long np, 
   rows[q] = a;
 }
 
-// Scalars from the row sums (single CTA):  out[0]=sum r, out[1]=sum rd2, out[2]=sum rk,
+// Scalars from the row sums (one CTA per scalar, blockIdx.x = c):  out[0]=sum r, out[1]=sum rd2, out[2]=sum rk,
 // out[3]=alpha.alpha, out[4+d] = sum_i xs_id gd_id  (d < DP)
 __global__ void grad_scalars_kernel(const double* __restrict__ rows, long n, int DP,
                                     const double* __restrict__ xs, const double* __restrict__ alpha,
                                     double* __restrict__ out) {
   __shared__ double sh[32];
   const int W = DP + 3;
-  for (int c = 0; c < 4 + DP; ++c) {
+  {
+    const int c = blockIdx.x;
     double a = 0.0;
     for (long i = threadIdx.x; i < n; i += blockDim.x) {
       double v;
