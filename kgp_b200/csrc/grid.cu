@@ -325,8 +325,12 @@ static int cg_run_persistent(kgp_ctx* c, GridState* g, const CgLaunch& L, int ma
   }
   if (getenv("KGP_DEBUG")) fprintf(stderr, "[kgp] persistent CG: sms %d optin %zu\n", g->num_sms, g->smem_optin);
   if (g->num_sms <= 0 || G.p > 2) return -1;
-  const int ctas = g->num_sms;
+  // one CTA per SM, but never more CTAs than 128-point units: the reference-sized problems (n = 460: 4 units) pay for
+  // every participant of the two grid barriers per iteration, and a cooperative launch over all SMs cannot start while
+  // the factor eigen-decompositions (side stream) hold two of them -- the two would serialise instead of overlapping
   const long nunits = L.npad / 128;
+  static const bool small_grid = !(getenv("KGP_CG_SMALL_GRID") && atoi(getenv("KGP_CG_SMALL_GRID")) == 0);
+  const int ctas = (small_grid && g->sub_n < 0 && c->nranks == 1 && nunits < g->num_sms) ? (int)std::max<long>(nunits, 1) : g->num_sms;
   const int upc = (int)((nunits + ctas - 1) / ctas);
   int TA = (G.ng[0] + 31) & ~31; if (TA > CGP_THREADS) TA = CGP_THREADS;
   const size_t kscr = (((size_t)(CGP_THREADS / TA + 1) * G.ng[0] + 1) & ~(size_t)1) * 8 + (size_t)(CGP_THREADS / 32) * CGP_WSCR * 8;
@@ -392,8 +396,12 @@ static int cg_run_persistent2(kgp_ctx* c, GridState* g, const CgLaunch& L, int s
     if (!coop) g->num_sms = -1;
   }
   if (g->num_sms <= 0 || G.p > 2 || L.m > CG_MAXCOLS_DEV) return -1;
-  const int ctas = g->num_sms;
+  // one CTA per SM, but never more CTAs than 128-point units: the reference-sized problems (n = 460: 4 units) pay for
+  // every participant of the two grid barriers per iteration, and a cooperative launch over all SMs cannot start while
+  // the factor eigen-decompositions (side stream) hold two of them -- the two would serialise instead of overlapping
   const long nunits = L.npad / 128;
+  static const bool small_grid = !(getenv("KGP_CG_SMALL_GRID") && atoi(getenv("KGP_CG_SMALL_GRID")) == 0);
+  const int ctas = (small_grid && g->sub_n < 0 && c->nranks == 1 && nunits < g->num_sms) ? (int)std::max<long>(nunits, 1) : g->num_sms;
   const int upc = (int)((nunits + ctas - 1) / ctas);
   Slot& S = c->slots[slot];
   if (g->wmax_slot != slot || g->wmax_slot_ver != S.version || g->wmax_grid_ver != c->grid.version || g->wmax_ctas != ctas) {
@@ -1058,6 +1066,23 @@ int grid_eval(kgp_ctx* c, int slot, int want, double* nlZ_out, double* dnlZ_out)
     const size_t need = 2 * (size_t)G.ng[d] * (G.ng[d] | 1) * 8;
     eb.A[d] = g->Af.d() + g->koff[d]; eb.V[d] = g->Vf.d() + g->koff[d]; eb.ev[d] = g->ee.d() + g->eoff_h[d];
     eb.ng[d] = toep[d] ? 0 : G.ng[d]; eb.use_smem[d] = need <= 190 * 1024; if (eb.use_smem[d] && !toep[d]) eig_smem = std::max(eig_smem, need);
+    {
+      // mirror-symmetric axis (every equispaced one) + stationary factor kernel => centrosymmetric factor: two half-order
+      // eigenproblems (jacobi_eig_kernel).  The test is on the spacings, to rounding: an axis that merely passes equi()'s
+      // 1e-9 does not qualify.
+      static const bool split_ok = !(getenv("KGP_EIG_SPLIT") && atoi(getenv("KGP_EIG_SPLIT")) == 0);
+      const std::vector<double>& ax = c->grid.axes[d];
+      const int na = (int)ax.size(), nh = (na + 1) / 2;
+      const size_t need3 = 3 * (size_t)nh * (nh | 1) * 8;
+      bool sym = split_ok && !toep[d] && na == G.ng[d] && na >= 2 && need3 <= 190 * 1024;
+      if (sym) {
+        double amax = 0.0; for (double v : ax) amax = std::max(amax, fabs(v));
+        for (int a = 0; a + 1 < na && sym; ++a)
+          if (fabs((ax[a + 1] - ax[a]) - (ax[na - 1 - a] - ax[na - 2 - a])) > 8.0 * 2.220446049250313e-16 * amax) sym = false;
+      }
+      eb.split[d] = sym ? 1 : 0;
+      if (sym) eig_smem = std::max(eig_smem, need3);
+    }
     c->stats.kernel_launches += 1;
     if (kind == 0) prior *= exp(2.0 * m.hyp_cov[d * nh + 1]);
     else { double sws = 0; for (int q = 0; q < Q; ++q) sws += exp(m.hyp_cov[d * nh + q]); prior *= sws; }
@@ -1078,13 +1103,14 @@ int grid_eval(kgp_ctx* c, int slot, int want, double* nlZ_out, double* dnlZ_out)
       KGP_CUDA(c, g->eigT.ensure(ksz * 8));
       for (int d = 0; d < G.p; ++d) {
         if (toep[d]) continue;
+        if (eb.split[d]) { eb.warm[d] = 1; continue; }           // the split kernel transforms its half problems itself
         const int ngd = G.ng[d]; const unsigned nbk = (unsigned)(((long)ngd * ngd + 255) / 256);
         matmul_small_kernel<<<nbk, 256, 0, c->stream2>>>(g->Kf.d() + g->koff[d], g->Vf.d() + g->koff[d], g->eigT.d() + g->koff[d], ngd, 0);
         matmul_small_kernel<<<nbk, 256, 0, c->stream2>>>(g->Vf.d() + g->koff[d], g->eigT.d() + g->koff[d], g->Af.d() + g->koff[d], ngd, 1);
         eb.warm[d] = 1;
       }
     }
-    jacobi_eig_kernel<<<G.p, EIG_THREADS, eig_smem, c->stream2>>>(eb, getenv("KGP_EIG_SWEEPS") ? atoi(getenv("KGP_EIG_SWEEPS")) : 40);
+    jacobi_eig_kernel<<<2 * G.p, EIG_THREADS, eig_smem, c->stream2>>>(eb, getenv("KGP_EIG_SWEEPS") ? atoi(getenv("KGP_EIG_SWEEPS")) : 40);
     for (int d = 0; d < G.p; ++d)                               // Toeplitz factors: Whittle-circulant eigenvalues (apxGrid.m:576-580)
       if (toep[d]) {
         whittle_eig_kernel<<<1, 1024, (size_t)G.ng[d] * 8, c->stream2>>>(kind, Q, g->hyp.d() + d * nh, G.ng[d], G.range[d] / (double)(G.ng[d] - 1),

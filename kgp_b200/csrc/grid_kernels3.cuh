@@ -10,7 +10,8 @@ namespace kgp {
 // Works out of shared memory when 2*ng*ng*8 bytes fit (use_smem), otherwise in place in global.
 constexpr int EIG_THREADS = 512;
 struct EigBatch { double* A[GRID_MAXP]; double* V[GRID_MAXP]; double* ev[GRID_MAXP]; int ng[GRID_MAXP]; int use_smem[GRID_MAXP];
-                  int warm[GRID_MAXP]; };   // warm: V holds the previous eigenvectors and A = V' K V (nearly diagonal)
+                  int warm[GRID_MAXP];      // warm: V holds the previous eigenvectors (split = 0: and A = V' K V, nearly diagonal)
+                  int split[GRID_MAXP]; };  // centrosymmetric factor: two half-order problems (jacobi_eig_kernel)
 // C = A B (transA = 0) or A' B (transA = 1), n x n row-major; the warm start forms V'(K V) with two launches
 __global__ void matmul_small_kernel(const double* __restrict__ A, const double* __restrict__ B, double* __restrict__ C, int n, int transA) {
   const int q = blockIdx.x * blockDim.x + threadIdx.x;
@@ -20,40 +21,67 @@ __global__ void matmul_small_kernel(const double* __restrict__ A, const double* 
   for (int k = 0; k < n; ++k) acc = fma(transA ? A[(long)k * n + i] : A[(long)i * n + k], B[(long)k * n + j], acc);
   C[q] = acc;
 }
-__global__ void __launch_bounds__(EIG_THREADS) jacobi_eig_kernel(const EigBatch eb, int max_sweeps) {
-  double* __restrict__ Ag = eb.A[blockIdx.x]; double* __restrict__ Vg = eb.V[blockIdx.x];
-  double* __restrict__ ev = eb.ev[blockIdx.x];
-  const int ng = eb.ng[blockIdx.x], use_smem = eb.use_smem[blockIdx.x], warm = eb.warm[blockIdx.x];
-  if (ng == 0) return;                           // Toeplitz factor: Whittle eigenvalues instead (grid_toeplitz.cuh)
-  extern __shared__ double sm[];
-  __shared__ double sh[32];
-  __shared__ double rc[1024], rs[1024];          // rotation of pair k: cos, sin
-  __shared__ int rp[1024], rq[1024];
-  const int ld = use_smem ? (ng | 1) : ng;       // odd pitch in shared memory: conflict-free rows AND columns
-  double* A = use_smem ? sm : Ag;
-  double* V = use_smem ? sm + (long)ng * ld : Vg;
+// Cyclic two-sided Jacobi sweeps on A (n x n, pitch ld; destroyed: ends diagonal) with V <- V J accumulated.
+// Round-robin ordering: every round rotates n/2 disjoint index pairs.  The pairs partition the matrix into 2x2 blocks
+// (pair a x pair b), each rotated from both sides by one thread; V <- V J by (row, pair) items.  Both kinds of item go
+// through one flat index (no division: a float reciprocal is exact at these sizes) and are handled TWO at a time with all
+// loads ahead of the stores -- a round is a chain of dependent shared-memory round trips, not a throughput problem.
+// The rotation comes from two rsqrt instead of div / sqrt / div / sqrt:  with d = aqq - app, b = 2 apq, r = hypot(d, b):
+//   cos 2t = |d| / r,  c = sqrt((1 + cos 2t) / 2),  s = sign(d) b / (2 r c)      (|t| <= pi/4, the classical choice).
+// Two barriers per round.
+struct JacItem { int i0, i1, i2, i3; double c0, s0, c1, s1; double v00, v01, v10, v11; int kind; };
+__device__ __forceinline__ void jac_load(JacItem& it, int t, int nblk2, int nitems, int half, float inv_half, int ld,
+                                         const double* __restrict__ A, const double* __restrict__ V,
+                                         const double2* __restrict__ rcs, const int2* __restrict__ rpq) {
+  it.kind = 0;
+  if (t >= nitems) return;
+  if (t < nblk2) {
+    const int a = (int)(((float)t + 0.5f) * inv_half), b2 = t - a * half;
+    const int2 pqa = rpq[a], pqb = rpq[b2]; const double2 csa = rcs[a], csb = rcs[b2];
+    const bool va = pqa.y >= 0, vb = pqb.y >= 0;
+    it.kind = 1 | (va ? 2 : 0) | (vb ? 4 : 0) | (a == b2 ? 8 : 0);
+    it.i0 = pqa.x * ld; it.i1 = (va ? pqa.y : pqa.x) * ld; it.i2 = pqb.x; it.i3 = vb ? pqb.y : pqb.x;
+    it.c0 = csa.x; it.s0 = csa.y; it.c1 = csb.x; it.s1 = csb.y;
+    it.v00 = A[it.i0 + it.i2]; it.v01 = vb ? A[it.i0 + it.i3] : 0.0;
+    it.v10 = va ? A[it.i1 + it.i2] : 0.0; it.v11 = (va && vb) ? A[it.i1 + it.i3] : 0.0;
+  } else {
+    const int u = t - nblk2, r = (int)(((float)u + 0.5f) * inv_half), k = u - r * half;
+    const int2 pq = rpq[k];
+    if (pq.y < 0) return;
+    const double2 cs = rcs[k];
+    it.kind = 16; it.i0 = r * ld + pq.x; it.i1 = r * ld + pq.y; it.c0 = cs.x; it.s0 = cs.y;
+    it.v00 = V[it.i0]; it.v01 = V[it.i1];
+  }
+}
+__device__ __forceinline__ void jac_store(const JacItem& it, double* __restrict__ A, double* __restrict__ V) {
+  if (it.kind & 1) {
+    const double ca = it.c0, sa = it.s0, cb = it.c1, sb = it.s1;
+    const double tpp = cb * it.v00 - sb * it.v01, tpq = sb * it.v00 + cb * it.v01;
+    const double tqp = cb * it.v10 - sb * it.v11, tqq = sb * it.v10 + cb * it.v11;
+    double npp = ca * tpp - sa * tqp, nqp = sa * tpp + ca * tqp, npq = ca * tpq - sa * tqq, nqq = sa * tpq + ca * tqq;
+    if (it.kind & 8) { npq = 0.0; nqp = 0.0; }                    // the annihilated pair: exact zeros, not rounding residue
+    const bool va = it.kind & 2, vb = it.kind & 4;
+    A[it.i0 + it.i2] = npp;
+    if (vb) A[it.i0 + it.i3] = npq;
+    if (va) A[it.i1 + it.i2] = nqp;
+    if (va && vb) A[it.i1 + it.i3] = nqq;
+  } else if (it.kind & 16) {
+    V[it.i0] = it.c0 * it.v00 - it.s0 * it.v01; V[it.i1] = it.s0 * it.v00 + it.c0 * it.v01;
+  }
+}
+__device__ void jacobi_sweeps(double* __restrict__ A, double* __restrict__ V, const int ng, const int ld, const int max_sweeps,
+                              double* sh, double2* rcs, int2* rpq) {
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  for (long q = tid; q < (long)ng * ng; q += EIG_THREADS) {
-    int r = (int)(q / ng), c = (int)(q % ng);
-    if (use_smem) A[(long)r * ld + c] = 0.5 * (Ag[q] + Ag[(long)c * ng + r]);   // Kj = (Kj+Kj')/2   (apxGrid.m:583)
-    if (warm) { if (use_smem) V[(long)r * ld + c] = Vg[q]; }
-    else V[(long)r * ld + c] = (r == c) ? 1.0 : 0.0;
-  }
-  __syncthreads();
-  if (!use_smem) {                                              // symmetrise in place, second pass
-    for (long q = tid; q < (long)ng * ng; q += EIG_THREADS) {
-      int r = (int)(q / ng), c = (int)(q % ng);
-      if (c > r) { double v = 0.5 * (A[q] + A[(long)c * ng + r]); A[q] = v; A[(long)c * ng + r] = v; }
-    }
-    __syncthreads();
-  }
+  constexpr int NW = EIG_THREADS / 32;
   const int m = (ng + 1) & ~1, half = m / 2;
+  const float inv_half = 1.0f / (float)half;
+  const int nblk2 = half * half, nitems = nblk2 + ng * half;
   for (int sweep = 0; sweep < max_sweeps; ++sweep) {
     // convergence: off-diagonal Frobenius norm against the diagonal
     double off = 0.0, dia = 0.0;
-    for (int r = warp; r < ng; r += EIG_THREADS / 32)
+    for (int r = warp; r < ng; r += NW)
       for (int c = lane; c < ng; c += 32) {
-        double v = A[(long)r * ld + c];
+        const double v = A[r * ld + c];
         if (r == c) dia = fma(v, v, dia); else off = fma(v, v, off);
       }
     off = block_sum(off, sh); dia = block_sum(dia, sh);
@@ -65,55 +93,133 @@ __global__ void __launch_bounds__(EIG_THREADS) jacobi_eig_kernel(const EigBatch 
       for (int k = tid; k < half; k += EIG_THREADS) {
         int p, q;
         if (k == 0) { p = m - 1; q = round; }
-        else { p = (round + k) % (m - 1); q = (round - k + m - 1) % (m - 1); }
+        else { p = round + k; if (p >= m - 1) p -= m - 1; q = round - k; if (q < 0) q += m - 1; }
         if (p > q) { int t = p; p = q; q = t; }
         double c = 1.0, s = 0.0;
         if (q < ng) {
-          const double apq = A[(long)p * ld + q];
+          const double apq = A[p * ld + q];
           if (apq != 0.0) {
-            const double tau = (A[(long)q * ld + q] - A[(long)p * ld + p]) / (2.0 * apq);
-            const double t = (tau >= 0.0 ? 1.0 : -1.0) / (fabs(tau) + sqrt(1.0 + tau * tau));
-            c = 1.0 / sqrt(1.0 + t * t); s = t * c;
+            const double d = A[q * ld + q] - A[p * ld + p], b = 2.0 * apq, ss = fma(d, d, b * b);
+            if (ss > 1e-290 && ss < 1e290) {
+              const double inv_r = rsqrt(ss), h2 = fma(0.5 * fabs(d), inv_r, 0.5), ic = rsqrt(h2);
+              c = h2 * ic; s = (d >= 0.0 ? 0.5 : -0.5) * b * inv_r * ic;
+            } else {                                              // out-of-range magnitudes: the division form
+              const double tau = d / b, t = (tau >= 0.0 ? 1.0 : -1.0) / (fabs(tau) + sqrt(1.0 + tau * tau));
+              c = 1.0 / sqrt(1.0 + t * t); s = t * c;
+            }
           }
         } else q = -1;
-        rp[k] = p; rq[k] = q; rc[k] = c; rs[k] = s;
+        rpq[k] = make_int2(p, q); rcs[k] = make_double2(c, s);
       }
       __syncthreads();
-      // A <- J' A J in ONE pass: the index pairs partition the matrix into 2x2 blocks (pair a x pair b), each
-      // rotated from both sides by one thread; V <- V J by (row, pair) items.  Two barriers per round.
-      const int nblk2 = half * half, nitems = nblk2 + ng * half;
-      for (int t = tid; t < nitems; t += EIG_THREADS) {
-        if (t < nblk2) {
-          const int a = t / half, b2 = t - a * half;
-          const int pa = rp[a], qa = rq[a], pb = rp[b2], qb = rq[b2];
-          const double ca = rc[a], sa = rs[a], cb = rc[b2], sb = rs[b2];
-          const bool va = qa >= 0, vb = qb >= 0;
-          const double b00 = A[(long)pa * ld + pb], b01 = vb ? A[(long)pa * ld + qb] : 0.0;
-          const double b10 = va ? A[(long)qa * ld + pb] : 0.0, b11 = (va && vb) ? A[(long)qa * ld + qb] : 0.0;
-          const double tpp = cb * b00 - sb * b01, tpq = sb * b00 + cb * b01;
-          const double tqp = cb * b10 - sb * b11, tqq = sb * b10 + cb * b11;
-          double npp = ca * tpp - sa * tqp, nqp = sa * tpp + ca * tqp, npq = ca * tpq - sa * tqq, nqq = sa * tpq + ca * tqq;
-          if (a == b2) { npq = 0.0; nqp = 0.0; }              // the annihilated pair: exact zeros, not rounding residue
-          A[(long)pa * ld + pb] = npp;
-          if (vb) A[(long)pa * ld + qb] = npq;
-          if (va) A[(long)qa * ld + pb] = nqp;
-          if (va && vb) A[(long)qa * ld + qb] = nqq;
-        } else {
-          const int u = t - nblk2, r = u / half, k = u - r * half;
-          const int pp = rp[k], qq = rq[k];
-          if (qq >= 0) {
-            const double c = rc[k], s2 = rs[k];
-            const double vp = V[(long)r * ld + pp], vq = V[(long)r * ld + qq];
-            V[(long)r * ld + pp] = c * vp - s2 * vq; V[(long)r * ld + qq] = s2 * vp + c * vq;
-          }
-        }
+      for (int t = tid; t < nitems; t += 2 * EIG_THREADS) {       // A <- J' A J and V <- V J in one pass
+        JacItem i0, i1;
+        jac_load(i0, t, nblk2, nitems, half, inv_half, ld, A, V, rcs, rpq);
+        jac_load(i1, t + EIG_THREADS, nblk2, nitems, half, inv_half, ld, A, V, rcs, rpq);
+        jac_store(i0, A, V);
+        jac_store(i1, A, V);
       }
       __syncthreads();
     }
   }
-  for (int i = tid; i < ng; i += EIG_THREADS) ev[i] = fmax(A[(long)i * ld + i], 0.0);   // apxGrid.m:586
-  if (use_smem)
-    for (long q = tid; q < (long)ng * ng; q += EIG_THREADS) Vg[q] = V[(q / ng) * ld + q % ng];
+}
+
+// One CTA pair per factor (blockIdx.x = 2 d + h).
+// split[d] = 0: CTA h = 0 decomposes the whole ng x ng factor (shared memory when it fits, else in place in global).
+// split[d] = 1 (the grid axis is mirror-symmetric -- every equispaced axis is -- and the factor kernel stationary, so the
+//   factor is symmetric Toeplitz, hence centrosymmetric, J T J = T): with Q = [I I; J -J]/sqrt 2 (odd ng: a middle row)
+//   Q' T Q = diag(C+, C-),  C+-[i][j] = T[i][j] +- T[i][ng-1-j]  (odd: C+ bordered by sqrt 2 T[i][m], T[m][m]),
+//   two independent problems of HALF the order: a quarter of the work per round, half the rounds per sweep, and the two
+//   halves run on two SMs.  Eigenvectors [u; (a); J u]/sqrt 2 and [w; (0); -J w]/sqrt 2.  ng = 100: 7.9 ms -> cold / 1.07 ms
+//   warm of the full-order kernel were the whole evaluation time of the reference's msgp_lstm_actuator-sized problems.
+//   Warm start inside the kernel: the previous half-eigenvectors are read back out of V's columns, C <- U' C U.
+__global__ void __launch_bounds__(EIG_THREADS) jacobi_eig_kernel(const EigBatch eb, int max_sweeps) {
+  const int d = blockIdx.x >> 1, h = blockIdx.x & 1;
+  double* __restrict__ Ag = eb.A[d]; double* __restrict__ Vg = eb.V[d];
+  double* __restrict__ ev = eb.ev[d];
+  const int ng = eb.ng[d], use_smem = eb.use_smem[d], warm = eb.warm[d];
+  if (ng == 0) return;                           // Toeplitz factor: Whittle eigenvalues instead (grid_toeplitz.cuh)
+  extern __shared__ double sm[];
+  __shared__ double sh[32];
+  __shared__ double2 rcs[1024];                  // rotation of pair k: cos, sin
+  __shared__ int2 rpq[1024];
+  const int tid = threadIdx.x;
+  if (!eb.split[d]) {
+    if (h) return;
+    const int ld = use_smem ? (ng | 1) : ng;     // odd pitch in shared memory: conflict-free rows AND columns
+    double* A = use_smem ? sm : Ag;
+    double* V = use_smem ? sm + (long)ng * ld : Vg;
+    for (long q = tid; q < (long)ng * ng; q += EIG_THREADS) {
+      int r = (int)(q / ng), c = (int)(q % ng);
+      if (use_smem) A[(long)r * ld + c] = 0.5 * (Ag[q] + Ag[(long)c * ng + r]);   // Kj = (Kj+Kj')/2   (apxGrid.m:583)
+      if (warm) { if (use_smem) V[(long)r * ld + c] = Vg[q]; }
+      else V[(long)r * ld + c] = (r == c) ? 1.0 : 0.0;
+    }
+    __syncthreads();
+    if (!use_smem) {                                              // symmetrise in place, second pass
+      for (long q = tid; q < (long)ng * ng; q += EIG_THREADS) {
+        int r = (int)(q / ng), c = (int)(q % ng);
+        if (c > r) { double v = 0.5 * (A[q] + A[(long)c * ng + r]); A[q] = v; A[(long)c * ng + r] = v; }
+      }
+      __syncthreads();
+    }
+    jacobi_sweeps(A, V, ng, ld, max_sweeps, sh, rcs, rpq);
+    for (int i = tid; i < ng; i += EIG_THREADS) ev[i] = fmax(A[(long)i * ld + i], 0.0);   // apxGrid.m:586
+    if (use_smem)
+      for (long q = tid; q < (long)ng * ng; q += EIG_THREADS) Vg[q] = V[(q / ng) * ld + q % ng];
+    return;
+  }
+  // ---- centrosymmetric split: half h (0: symmetric eigenvectors, 1: skew-symmetric)
+  const int m = ng >> 1, odd = ng & 1, nh = h == 0 ? m + odd : m, col0 = h == 0 ? 0 : m + odd;
+  if (nh == 0) return;
+  const int ld = nh | 1;
+  double* C = sm; double* U = sm + nh * ld; double* T = U + nh * ld;
+  const double sgn = h == 0 ? 1.0 : -1.0, r2 = sqrt(2.0), ir2 = 1.0 / r2;
+  auto Ks = [&](int i, int j) { return 0.5 * (Ag[(long)i * ng + j] + Ag[(long)j * ng + i]); };
+  for (int q = tid; q < nh * nh; q += EIG_THREADS) {
+    const int i = q / nh, j = q - i * nh;
+    double v;
+    if (i < m && j < m) v = 0.5 * ((Ks(i, j) + sgn * Ks(i, ng - 1 - j)) + (Ks(j, i) + sgn * Ks(j, ng - 1 - i)));
+    else if (i == m && j == m) v = Ks(m, m);
+    else v = r2 * Ks(i < m ? i : j, m);                            // the border of C+ (odd ng)
+    C[i * ld + j] = v;
+    double u = (i == j) ? 1.0 : 0.0;
+    if (warm) u = (i < m ? r2 : 1.0) * Vg[(long)i * ng + col0 + j];   // previous half-eigenvectors out of V's columns
+    U[i * ld + j] = u;
+  }
+  __syncthreads();
+  if (warm) {                                                     // C <- U' (C U): nearly diagonal start
+    for (int q = tid; q < nh * nh; q += EIG_THREADS) {
+      const int i = q / nh, j = q - i * nh;
+      double acc = 0.0;
+      for (int k = 0; k < nh; ++k) acc = fma(C[i * ld + k], U[k * ld + j], acc);
+      T[i * ld + j] = acc;
+    }
+    __syncthreads();
+    for (int q = tid; q < nh * nh; q += EIG_THREADS) {
+      const int i = q / nh, j = q - i * nh;
+      double acc = 0.0;
+      if (j >= i) {
+        for (int k = 0; k < nh; ++k) acc = fma(U[k * ld + i], T[k * ld + j], acc);
+        C[i * ld + j] = acc;
+      }
+    }
+    __syncthreads();
+    for (int q = tid; q < nh * nh; q += EIG_THREADS) {            // exact symmetry from the upper triangle
+      const int i = q / nh, j = q - i * nh;
+      if (j < i) C[i * ld + j] = C[j * ld + i];
+    }
+    __syncthreads();
+  }
+  jacobi_sweeps(C, U, nh, ld, max_sweeps, sh, rcs, rpq);
+  for (int k = tid; k < nh; k += EIG_THREADS) ev[col0 + k] = fmax(C[k * ld + k], 0.0);   // apxGrid.m:586
+  for (int q = tid; q < nh * nh; q += EIG_THREADS) {
+    const int i = q / nh, k = q - i * nh;
+    const double u = U[i * ld + k];
+    if (i < m) { Vg[(long)i * ng + col0 + k] = u * ir2; Vg[(long)(ng - 1 - i) * ng + col0 + k] = sgn * u * ir2; }
+    else Vg[(long)m * ng + col0 + k] = u;
+  }
+  if (odd && h == 1) for (int k = tid; k < nh; k += EIG_THREADS) Vg[(long)m * ng + col0 + k] = 0.0;
 }
 
 // Fiedler bound pieces for every Kronecker eigenvalue product e (all W equal to w):

@@ -46,6 +46,8 @@ CASES = {
     'gradcheck_n_lt_N': dict(seed=42, n=100, D=1, cov='covSEiso', hyp=[[np.log(0.5)], [0.0]], lik=np.log(0.1), k=128.),
     'c3_small': dict(seed=44, n=3000, D=2, cov='covSEiso', hyp=[[0.5], [1.0]], lik=np.log(0.3), k=30.),
     'sm_mean': dict(seed=46, n=4000, D=2, cov='covSM', Q=3, lik=np.log(0.3), k=32., mean='meanSum', hyp_mean=[0.1, -0.1, 0.2]),
+    # odd factor order: the centrosymmetric split of the eigen-decomposition has a middle row (jacobi_eig_kernel)
+    'odd_grid': dict(seed=44, n=3000, D=2, cov='covSEiso', hyp=[[0.5], [1.0]], lik=np.log(0.3), k=31.),
 }
 
 
@@ -55,7 +57,7 @@ def build(name):
         X = np.tanh(rng.randn(n, 1)); y = np.sin(4 * X[:, 0]) + np.exp(-2) * rng.randn(n); Xs = np.tanh(rng.randn(77, 1)) * 1.3
     elif name == 'gradcheck_n_lt_N':
         X = rng.rand(n, 1); y = rng.rand(n); Xs = rng.rand(20, 1) * 1.4 - 0.2
-    elif name == 'c3_small':
+    elif name in ('c3_small', 'odd_grid'):
         X = np.maximum(0, rng.normal(0.5, 1, (n, 2))); y = np.sin(3 * X[:, 0]) * np.cos(2 * X[:, 1]) + 0.3 * rng.randn(n)
         Xs = np.maximum(0, rng.normal(0.5, 1.3, (300, 2)))
     else:
@@ -82,6 +84,26 @@ def test_deterministic_parts_tight_cg(built_lib, name):
     assert rel(gp.alpha(), post['alpha']) < 1e-7 and rel(dX, dX0) < 1e-7
     assert rel(ymu, p0[2]) < 1e-7 and rel(ys2, p0[3]) < 1e-12
     assert ymu.shape == (Xs.shape[0], 1) and dX.shape == X.shape
+
+
+def test_eig_warm_start_sequence_vs_oracle(built_lib):
+    """The factor eigen-decompositions are warm-started from the previous evaluation's eigenvectors (split into the
+    symmetric / skew-symmetric halves of the centrosymmetric factor): every evaluation of a sequence of moving
+    hyper-parameters, as minimize produces it, must equal the oracle's cold eig (apxGrid.m:571-588) -- odd and even orders."""
+    import gpml_grid as gg
+    for name in ('odd_grid', 'c4'):
+        c, X, y, Xs = build(name)
+        opt = {'cg_maxit': 20000, 'cg_tol': 1e-12}
+        gp = make(X, y, c['cov'], c['hyp'], c['lik'], c['k'], opt)
+        v0 = gp._hyp_vec().copy()
+        for step in (0.0, 3e-3, -2e-2, 0.3, 0.301):
+            gp._set_hyp_vec(v0 + step * np.resize([1.0, -0.5, 0.25], v0.size)); gp._push_model()
+            nlZ, g = gp.eng.eval(0, 2, gp._n_hyp)
+            hv = gp._hyp_vec(); nc = gp.hyp['cov'].size; oh = {'cov': hv[:nc], 'lik': hv[nc], 'mean': hv[nc + 1:]}
+            xg = gg.creategrid(X, 1, gp._grid_k)
+            post, nlZ0, d = gg.inf_grid(oh, ['meanZero'], c['cov'], xg, X, y, opt)
+            g0 = np.concatenate([d['cov'], [d['lik']]])
+            assert rel(nlZ, nlZ0) < 1e-8 and rel(g, g0) < 1e-8, (name, step)
 
 
 @pytest.mark.parametrize('name,opt', [('c4', {'cg_maxit': 500, 'cg_tol': 1e-4}), ('c3_small', {'cg_maxit': 2000, 'cg_tol': 1e-6}),
