@@ -144,9 +144,18 @@ int kgp_grid_set_host(kgp_ctx* ctx, int n_axes, const int* axis_len, const doubl
  * dnlZ differ from dense-factor mode on the same axes.  flags: n_axes ints (NULL clears); call after kgp_grid_set_host. */
 int kgp_grid_set_toeplitz(kgp_ctx* ctx, int n_axes, const int* flags);
 /* GPML's equi() test for one axis (GPML/cov/apxGrid.m:684-695): 1 when max|diff(a) - (a[1]-a[0])| < 1e-9 and the axis
- * increases.  kgp_grid_set_host refuses axes that fail it (the neqinterp branch is not built).  Host logic, no GPU. */
+ * increases.  Axes that fail it but increase take the linear neqinterp branch (apxGrid.m:541-557).  Host logic, no GPU. */
 int kgp_grid_axis_equispaced(const double* axis, int len);
 int kgp_grid_get_host(kgp_ctx* ctx, int* n_axes, int* axis_len /* >= 16 ints */, double* axes_concat /* may be NULL */);
+
+/* Learned input projection hyp.proj (GPML/inf/infGrid.m:56-65,82-87,155-167; kgp/backend/utils/dlikGrid.m:13-22,
+ * deriv_x.m:5-6,24).  P is the EFFECTIVE projector hP (d x D row-major; the caller has applied opt.proj = 'orth' / 'norm').
+ * While set, kgp_set_data_* takes n x D inputs and the engine works on x hP' (n x d); kgp_predict_host projects its test
+ * inputs; kgp_dlik_dx_* returns dxP hP (n x D); a new P re-projects the loaded slots.  P = NULL or d = 0 clears.
+ * kgp_dnlZ_proj_host: dnlZ/dhP (d x D) = dxP' x -- deriv_proj's dP(i,j) = -alpha' (x(:,j) .* beta_i), with the mean's input
+ * derivative analytic instead of the reference's forward difference.  infGrid only. */
+int kgp_set_proj_host(kgp_ctx* ctx, const double* P, int d, int D);
+int kgp_dnlZ_proj_host(kgp_ctx* ctx, int slot, double* out /* d x D */);
 
 /* Chebyshev-Hutchinson log-det (opt.ldB2_cheby = 1; GPML/cov/apx.m:336-391): inject the probe vectors
  * (V is m x n, one probe per row, entries +-1) and the eigenvalue bound emax.  The reference draws them with

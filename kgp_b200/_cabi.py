@@ -67,6 +67,8 @@ SIGNATURES = {
     'kgp_grid_set_toeplitz': (C.c_int, [C.c_void_p, C.c_int, C.c_void_p]),
     'kgp_grid_axis_equispaced': (C.c_int, [C.c_void_p, C.c_int]),
     'kgp_grid_get_host': (C.c_int, [C.c_void_p, C.POINTER(C.c_int), C.c_void_p, C.c_void_p]),
+    'kgp_set_proj_host': (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int]),
+    'kgp_dnlZ_proj_host': (C.c_int, [C.c_void_p, C.c_int, C.c_void_p]),
     'kgp_get_alpha_host': (C.c_int, [C.c_void_p, C.c_void_p]),
     'kgp_last_stats': (C.c_int, [C.c_void_p, C.POINTER(KgpStats)]),
     'kgp_bench_dmma_peak': (C.c_int, [C.c_void_p, C.c_int, _DP]),
@@ -183,7 +185,9 @@ class Context(object):
                 pass                                             # cubic interpolation is what the engine builds (apx.m:123 default)
             elif k == 'stat' and not v:
                 pass
-            elif k in ('deg', 'proj', 'ndcovs', 'stat'):
+            elif k == 'proj':
+                pass                                             # handled above the C ABI (engine.py: hyp.proj, orth / norm)
+            elif k in ('deg', 'ndcovs', 'stat'):
                 # GPML options that change the numbers (apx.m:123, infGrid.m:56,70): refusing beats returning cubic /
                 # un-projected results as if the option had been honoured
                 raise ValueError('opt.%s=%r is not supported by the B200 engine' % (k, v))
@@ -234,6 +238,18 @@ class Context(object):
         lens = np.array([a.size for a in axes], dtype=np.int32)
         cat = np.concatenate(axes)
         self._chk(self._l.kgp_grid_set_host(self._h, len(axes), _ptr(lens), _ptr(cat)))
+
+    def set_proj(self, P):
+        """hyp.proj: the effective projector hP (d x D), or None to clear (kgp_set_proj_host)."""
+        if P is None:
+            self._chk(self._l.kgp_set_proj_host(self._h, None, 0, 0)); return
+        P = f64(np.atleast_2d(P))
+        self._chk(self._l.kgp_set_proj_host(self._h, _ptr(P), P.shape[0], P.shape[1]))
+
+    def dnlZ_proj(self, slot, d, D):
+        out = np.empty((d, D))
+        self._chk(self._l.kgp_dnlZ_proj_host(self._h, slot, _ptr(out)))
+        return out
 
     def grid_get(self):
         na = C.c_int(); lens = np.zeros(16, dtype=np.int32)

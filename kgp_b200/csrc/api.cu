@@ -90,9 +90,9 @@ int kgp_ctx_destroy(kgp_ctx* c) {
   DevBuf* bufs[] = {&c->M, &c->W2, &c->Dws, &c->xs, &c->s, &c->mu, &c->inv_ell, &c->ym, &c->alpha, &c->tvec,
                     &c->parts, &c->rows, &c->scal, &c->hypm, &c->dX, &c->fac, &c->pred_K, &c->pred_x, &c->pred_s,
                     &c->pred_a, &c->pred_b, &c->pred_out, &c->pred_X, &c->smV, &c->smM, &c->smAcc, &c->gws[0], &c->gws[1],
-                    &c->gcnt[0], &c->gcnt[1]};
+                    &c->gcnt[0], &c->gcnt[1], &c->projP, &c->projXs, &c->projdX};
   for (DevBuf* b : bufs) b->release();
-  for (auto& s : c->slots) { s.X.release(); s.y.release(); }
+  for (auto& s : c->slots) { s.X.release(); s.y.release(); s.Xraw.release(); }
   if (c->d_info) cudaFree(c->d_info);
   for (int i = 0; i < 16; ++i) cudaEventDestroy(c->ev[i]);
   for (cudaEvent_t e : c->gev) cudaEventDestroy(e);
@@ -142,20 +142,79 @@ int kgp_dist_rows_sharded(int nranks, long n, long N) { return dist_rows_sharded
 const char* kgp_last_error(kgp_ctx* c) { return c ? c->err.c_str() : "null context"; }
 int kgp_set_profiling(kgp_ctx* c, int on) { if (!c) return KGP_BAD_ARG; c->profiling = on; return KGP_OK; }
 
+// ---- hyp.proj (GPML/inf/infGrid.m:56-65,82-87,155-167; kgp/backend/utils/dlikGrid.m:13-22, deriv_x.m:5-6,24) -----------------
+// The inference runs on x hP'; dnlZ/dX = dxP hP and dnlZ/dhP = dxP' x with dxP = dnlZ/d(x hP') (deriv_x's columns:
+// deriv_proj's dP(i,j) = -alpha' (x(:,j) .* beta_i) is exactly sum_n x(n,j) dxP(n,i)).  The orth / norm re-parametrisation
+// of hyp.proj and its chain rule are d x D host algebra above the C ABI (kgp_b200/engine.py).
+__global__ void proj_apply_kernel(const double* __restrict__ X, long n, int D, const double* __restrict__ P, int d, double* __restrict__ Y) {
+  const long q = (long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (q >= n * d) return;
+  const long i = q / d; const int a = (int)(q - i * d);
+  double acc = 0.0;
+  for (int j = 0; j < D; ++j) acc = fma(X[i * D + j], P[a * D + j], acc);
+  Y[q] = acc;
+}
+__global__ void proj_back_kernel(const double* __restrict__ dXp, long n, int d, const double* __restrict__ P, int D, double* __restrict__ dX) {
+  const long q = (long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (q >= n * D) return;
+  const long i = q / D; const int j = (int)(q - i * D);
+  double acc = 0.0;
+  for (int a = 0; a < d; ++a) acc = fma(dXp[i * d + a], P[a * D + j], acc);
+  dX[q] = acc;
+}
+// dP[a][j] = sum_i dXp[i][a] X[i][j]: one CTA per entry, fixed summation order
+__global__ void proj_grad_kernel(const double* __restrict__ dXp, const double* __restrict__ X, long n, int d, int D, double* __restrict__ dP) {
+  __shared__ double sh[32];
+  const int a = blockIdx.x / D, j = blockIdx.x % D;
+  double acc = 0.0;
+  for (long i = threadIdx.x; i < n; i += blockDim.x) acc = fma(dXp[i * d + a], X[i * D + j], acc);
+  const double t = block_sum(acc, sh);
+  if (threadIdx.x == 0) dP[blockIdx.x] = t;
+}
+static int project_slot(kgp_ctx* c, Slot& S) {
+  KGP_CUDA(c, S.X.ensure((size_t)S.n * c->proj_d * 8));
+  const long tot = S.n * c->proj_d;
+  proj_apply_kernel<<<(unsigned)((tot + 255) / 256), 256, 0, c->stream>>>(S.Xraw.d(), S.n, S.Draw, c->projP.d(), c->proj_d, S.X.d());
+  S.D = c->proj_d; S.version++;
+  return KGP_OK;
+}
+int kgp_set_proj_host(kgp_ctx* c, const double* P, int d, int D) {
+  if (!c) return KGP_BAD_ARG;
+  cudaSetDevice(c->device);
+  if (!P || d <= 0) {                                             // clear: slots keep what they hold; new data is taken as is
+    c->proj_d = c->proj_D = 0;
+    for (auto& S : c->slots) S.Draw = 0;
+    return KGP_OK;
+  }
+  if (D <= 0) return c->fail(KGP_BAD_ARG, "bad projection shape %d x %d", d, D);
+  KGP_CUDA(c, c->projP.ensure((size_t)d * D * 8));
+  KGP_CUDA(c, cudaMemcpyAsync(c->projP.p, P, (size_t)d * D * 8, cudaMemcpyHostToDevice, c->stream));
+  c->proj_d = d; c->proj_D = D;
+  for (auto& S : c->slots)                                        // the points moved: re-project what is loaded
+    if (S.n > 0 && S.Draw == D) { int rc = project_slot(c, S); if (rc) return rc; }
+  KGP_CUDA(c, cudaStreamSynchronize(c->stream));
+  KGP_CUDA(c, cudaGetLastError());
+  return KGP_OK;
+}
+
 static int set_data(kgp_ctx* c, int slot, const double* X, long n, int D, const double* y, cudaMemcpyKind kind) {
   if (!c) return KGP_BAD_ARG;
   if (slot < 0 || slot >= KGP_NUM_SLOTS) return c->fail(KGP_BAD_ARG, "bad slot %d", slot);
   if (!X || n <= 0 || D <= 0) return c->fail(KGP_BAD_ARG, "bad data shape n=%ld D=%d", n, D);
   cudaSetDevice(c->device);
   Slot& S = c->slots[slot];
-  KGP_CUDA(c, S.X.ensure((size_t)n * D * 8));
-  KGP_CUDA(c, cudaMemcpyAsync(S.X.p, X, (size_t)n * D * 8, kind, c->stream));
+  const bool proj = c->proj_d > 0;
+  if (proj && D != c->proj_D) return c->fail(KGP_BAD_ARG, "hyp.proj is %d x %d but the inputs have %d columns", c->proj_d, c->proj_D, D);
+  DevBuf& dst = proj ? S.Xraw : S.X;
+  KGP_CUDA(c, dst.ensure((size_t)n * D * 8));
+  KGP_CUDA(c, cudaMemcpyAsync(dst.p, X, (size_t)n * D * 8, kind, c->stream));
   if (y) {
     KGP_CUDA(c, S.y.ensure((size_t)n * 8));
     KGP_CUDA(c, cudaMemcpyAsync(S.y.p, y, (size_t)n * 8, kind, c->stream));
     S.has_y = true;
   } else if (S.n != n) S.has_y = false;     // a stale y of another length cannot be used
-  S.n = n; S.D = D; S.version++;
+  S.n = n; S.D = D; S.version++; S.Draw = 0;
+  if (proj) { S.Draw = D; int rc = project_slot(c, S); if (rc) return rc; }
   KGP_CUDA(c, cudaStreamSynchronize(c->stream));
   return KGP_OK;
 }
@@ -196,19 +255,58 @@ int kgp_eval(kgp_ctx* c, int slot, int want, double* nlZ, double* dnlZ) {
   if (want < 0 || want > 2) return c->fail(KGP_BAD_ARG, "want must be 0, 1 or 2");
   return c->model.inf_kind == KGP_INF_EXACT ? exact_eval(c, slot, want, nlZ, dnlZ) : grid_eval(c, slot, want, nlZ, dnlZ);
 }
+// dnlZ/d(x hP') into c->projdX (device), then out (n x Draw) = dxP hP
+static int dlik_projected(kgp_ctx* c, int slot, double* out, bool out_is_dev) {
+  Slot& S = c->slots[slot];
+  if (c->model.inf_kind != KGP_INF_GRID) return c->fail(KGP_BAD_ARG, "hyp.proj belongs to infGrid (GPML/inf/infGrid.m:56-65)");
+  KGP_CUDA(c, c->projdX.ensure((size_t)S.n * (c->proj_d + S.Draw) * 8));
+  double* dxp = c->projdX.d(); double* dx = dxp + S.n * c->proj_d;
+  int rc = grid_dlik(c, slot, dxp, true); if (rc) return rc;
+  const long tot = S.n * S.Draw;
+  proj_back_kernel<<<(unsigned)((tot + 255) / 256), 256, 0, c->stream>>>(dxp, S.n, c->proj_d, c->projP.d(), S.Draw, dx);
+  KGP_CUDA(c, cudaMemcpyAsync(out, dx, (size_t)tot * 8, out_is_dev ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost, c->stream));
+  KGP_CUDA(c, cudaStreamSynchronize(c->stream));
+  return KGP_OK;
+}
 int kgp_dlik_dx_host(kgp_ctx* c, int slot, double* out) {
   int rc = check_ready(c, slot, true); if (rc) return rc;
   if (!out) return c->fail(KGP_BAD_ARG, "null output");
+  if (c->proj_d > 0 && c->slots[slot].Draw > 0) return dlik_projected(c, slot, out, false);
   return c->model.inf_kind == KGP_INF_EXACT ? exact_dlik(c, slot, out, false) : grid_dlik(c, slot, out, false);
 }
 int kgp_dlik_dx_dev(kgp_ctx* c, int slot, double* out) {
   int rc = check_ready(c, slot, true); if (rc) return rc;
   if (!out) return c->fail(KGP_BAD_ARG, "null output");
+  if (c->proj_d > 0 && c->slots[slot].Draw > 0) return dlik_projected(c, slot, out, true);
   return c->model.inf_kind == KGP_INF_EXACT ? exact_dlik(c, slot, out, true) : grid_dlik(c, slot, out, true);
+}
+int kgp_dnlZ_proj_host(kgp_ctx* c, int slot, double* out) {
+  int rc = check_ready(c, slot, true); if (rc) return rc;
+  Slot& S = c->slots[slot];
+  if (!out || c->proj_d <= 0 || S.Draw <= 0) return c->fail(KGP_BAD_ARG, "no projection set (kgp_set_proj_host) or null output");
+  if (c->model.inf_kind != KGP_INF_GRID) return c->fail(KGP_BAD_ARG, "hyp.proj belongs to infGrid (GPML/inf/infGrid.m:56-65)");
+  const int d = c->proj_d, D = S.Draw;
+  KGP_CUDA(c, c->projdX.ensure((size_t)S.n * (d + D) * 8 + (size_t)d * D * 8));
+  double* dxp = c->projdX.d(); double* dP = dxp + S.n * (d + D);
+  rc = grid_dlik(c, slot, dxp, true); if (rc) return rc;
+  proj_grad_kernel<<<d * D, 1024, 0, c->stream>>>(dxp, S.Xraw.d(), S.n, d, D, dP);
+  KGP_CUDA(c, cudaMemcpyAsync(out, dP, (size_t)d * D * 8, cudaMemcpyDeviceToHost, c->stream));
+  KGP_CUDA(c, cudaStreamSynchronize(c->stream));
+  KGP_CUDA(c, cudaGetLastError());
+  return KGP_OK;
 }
 int kgp_predict_host(kgp_ctx* c, const double* Xs, long ns, double* ymu, double* ys2, double* fmu, double* fs2) {
   int rc = check_ready(c, KGP_SLOT_TR, true); if (rc) return rc;
   if (!Xs || ns <= 0) return c->fail(KGP_BAD_ARG, "bad test inputs");
+  if (c->proj_d > 0 && c->slots[KGP_SLOT_TR].Draw > 0) {           // test inputs go through the same projector (infGrid.m:120)
+    if (c->model.inf_kind != KGP_INF_GRID) return c->fail(KGP_BAD_ARG, "hyp.proj belongs to infGrid (GPML/inf/infGrid.m:56-65)");
+    const int d = c->proj_d, D = c->proj_D;
+    KGP_CUDA(c, c->projXs.ensure((size_t)ns * (d + D) * 8));
+    double* raw = c->projXs.d(); double* xp = raw + ns * D;
+    KGP_CUDA(c, cudaMemcpyAsync(raw, Xs, (size_t)ns * D * 8, cudaMemcpyHostToDevice, c->stream));
+    proj_apply_kernel<<<(unsigned)((ns * d + 255) / 256), 256, 0, c->stream>>>(raw, ns, D, c->projP.d(), d, xp);
+    return grid_predict(c, xp, ns, ymu, ys2, fmu, fs2);           // (grid_predict copies with cudaMemcpyDefault)
+  }
   return c->model.inf_kind == KGP_INF_EXACT ? exact_predict(c, Xs, ns, ymu, ys2, fmu, fs2)
                                             : grid_predict(c, Xs, ns, ymu, ys2, fmu, fs2);
 }

@@ -25,6 +25,7 @@ struct DevBuf {
 
 struct Slot {
   DevBuf X, y; long n = 0; int D = 0; bool has_y = false;
+  DevBuf Xraw; int Draw = 0;               // hyp.proj set: the un-projected inputs (n x Draw); X then holds Xraw hP' (n x d)
   unsigned long version = 0;
 };
 
@@ -64,6 +65,8 @@ struct kgp_ctx {
   kgp::DevBuf xs, s, mu, inv_ell, ym, alpha, tvec, parts, rows, scal, hypm, dX, fac;
   kgp::DevBuf pred_K, pred_x, pred_s, pred_a, pred_b, pred_out, pred_X;
   kgp::DevBuf smV, smM, smAcc;        // covSM exact path: 4 pi^2 v, 2 pi m tables and the reduction accumulators
+  kgp::DevBuf projP, projXs, projdX;  // hyp.proj (infGrid.m:56-65): effective projector hP (d x D), projected test inputs, dnlZ/d(x hP')
+  int proj_d = 0, proj_D = 0;
   int* d_info = nullptr;
   long np = 0; int Dp = 0;
   // what the factorisation state corresponds to

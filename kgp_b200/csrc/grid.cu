@@ -1430,7 +1430,7 @@ int grid_predict(kgp_ctx* c, const double* Xs, long ns, double* ymu, double* ys2
   cudaStream_t st = c->stream;
   KGP_CUDA(c, c->pred_X.ensure((size_t)ns * D * 8)); KGP_CUDA(c, c->pred_a.ensure((size_t)ns * 8));
   KGP_CUDA(c, c->pred_b.ensure((size_t)ns * 8));
-  KGP_CUDA(c, cudaMemcpyAsync(c->pred_X.p, Xs, (size_t)ns * D * 8, cudaMemcpyHostToDevice, st));
+  KGP_CUDA(c, cudaMemcpyAsync(c->pred_X.p, Xs, (size_t)ns * D * 8, cudaMemcpyDefault, st));    // host, or the projected inputs on the device (hyp.proj)
   resid_mean_kernel<<<(unsigned)((ns + 255) / 256), 256, 0, st>>>(c->pred_X.d(), nullptr, ns, D, m.mean_mask, g->hypm.d(), c->pred_b.d(), ns);   // = -ms
   for_p(G.p, [&](auto P) {
     interp_gather_bz_kernel<decltype(P)::value><<<nblocks_for(ns), 256, 0, st>>>(G, c->pred_X.d(), ns, D, g->beta.d(), 1.0, nullptr, c->pred_a.d(), nullptr);

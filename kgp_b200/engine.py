@@ -22,6 +22,30 @@ from .minimize import minimize
 _MEANS = {'meanZero': 0, 'meanLinear': 1, 'meanConst': 2}
 
 
+# ---- hyp.proj re-parametrisations (GPML/inf/infGrid.m:56-65) and their chain rules (infGrid.m:176-185): d x D host algebra
+def _eff_proj(P, mode):
+    eps = np.finfo(np.float64).eps
+    if mode.startswith('orth'):                                    # sqrtm(P P' + eps I) \ P
+        w, V = np.linalg.eigh(P.dot(P.T) + eps * np.eye(P.shape[0]))
+        return np.linalg.solve((V * np.sqrt(w)).dot(V.T), P)
+    if mode.startswith('norm'):                                    # diag(1 / sqrt(diag(P P') + eps)) P
+        return P / np.sqrt(np.sum(P * P, axis=1) + eps)[:, None]
+    return P
+
+
+def _chain_proj(P, dP, mode):
+    if mode.startswith('orth'):
+        F, V = np.linalg.eigh(P.dot(P.T))
+        sf = np.sqrt(F); S = (V * sf).dot(V.T)
+        H = np.linalg.solve(S, dP).T
+        G = H.T.dot(np.linalg.solve(S, P).T)
+        return (H - P.T.dot(V).dot(V.T.dot(G + G.T).dot(V) / (sf[:, None] + sf[None, :])).dot(V.T)).T
+    if mode.startswith('norm'):
+        p = 1.0 / np.sqrt(np.sum(P * P, axis=1))
+        return p[:, None] * dP - (np.sum(dP * P, axis=1) * p ** 3)[:, None] * P
+    return dP
+
+
 def _mean_mask(mean, mean_args):
     """'meanZero' | 'meanConst' | 'meanLinear' | 'meanSum' + ['{@meanLinear, @meanConst}']"""
     if mean == 'meanSum':
@@ -70,6 +94,11 @@ class B200GP(object):
         self._mean_mask = _mean_mask(mean, mean_args)
         self._sm_Q = int(cov_args[0]) if (cov == 'covSM' and cov_args) else 0
         self._opt = dict(opt or {})
+        self._proj_mode = str(self._opt.get('proj', 'none')).lower()
+        if self._proj_mode[:4] not in ('none', 'orth', 'norm'):
+            raise ValueError("opt.proj must be 'none', 'orth' or 'norm' (infGrid.m:56-65)")
+        if hyp.get('proj') is not None and inf != 'infGrid':
+            raise ValueError('hyp.proj belongs to infGrid (infGrid.m:56-65)')
         self.using_grid = (inf == 'infGrid')
         if self.using_grid:
             assert grid_kwargs is not None, (
@@ -91,6 +120,8 @@ class B200GP(object):
         self.hyp = {'cov': np.asarray(hyp['cov'], dtype=np.float64),
                     'lik': float(np.asarray(hyp['lik']).reshape(-1)[0]),
                     'mean': np.asarray(hyp.get('mean', []), dtype=np.float64)}
+        if hyp.get('proj') is not None:                           # learned projection, d x D (infGrid.m:58)
+            self.hyp['proj'] = np.atleast_2d(np.asarray(hyp['proj'], dtype=np.float64))
         self._push_model()
         if verbose:
             print("GP configuration:")
@@ -98,20 +129,26 @@ class B200GP(object):
 
     def _hyp_vec(self):
         """unwrap(hyp): fields in alphabetical order cov, lik, mean (minimize.m:173-186)."""
-        return np.concatenate([self.hyp['cov'].flatten(order='F'), [self.hyp['lik']],
-                               self.hyp['mean'].flatten(order='F')])
+        v = [self.hyp['cov'].flatten(order='F'), [self.hyp['lik']], self.hyp['mean'].flatten(order='F')]
+        if 'proj' in self.hyp:
+            v.append(self.hyp['proj'].flatten(order='F'))
+        return np.concatenate(v)
 
     def _set_hyp_vec(self, v):
         nc, nm = self.hyp['cov'].size, self.hyp['mean'].size
         self.hyp['cov'] = np.asarray(v[:nc]).reshape(self.hyp['cov'].shape, order='F')
         self.hyp['lik'] = float(v[nc])
         self.hyp['mean'] = np.asarray(v[nc + 1:nc + 1 + nm]).reshape(self.hyp['mean'].shape, order='F')
+        if 'proj' in self.hyp:
+            self.hyp['proj'] = np.asarray(v[nc + 1 + nm:], dtype=np.float64).reshape(self.hyp['proj'].shape, order='F')
 
     def _push_model(self):
         self.eng.set_model(self._inf, self._cov, self.hyp['cov'].flatten(order='F'), self.hyp['lik'],
                            self.hyp['mean'].flatten(order='F'), mean_mask=self._mean_mask,
                            sm_Q=self._sm_Q, opt=self._opt)
         self._n_hyp = self.hyp['cov'].size + 1 + self.hyp['mean'].size
+        if 'proj' in self.hyp:                                    # loaded slots are re-projected by the engine
+            self.eng.set_proj(_eff_proj(self.hyp['proj'], self._proj_mode))
 
     # -- data / grid (gpml.py:152-165) --------------------------------------
     def update_data(self, which_set, X, y=None, verbose=0):
@@ -129,12 +166,18 @@ class B200GP(object):
     # -- evaluate (gpml.py:167-178; gp.m:93-126) ----------------------------
     def _eval(self, which_set, want):
         """gp.m training mode: an inference failure becomes NaN + zero gradient + warning."""
+        n_out = self._n_hyp + (self.hyp['proj'].size if 'proj' in self.hyp else 0)
         try:
-            return self.eng.eval(_cabi.SLOTS[which_set], want, self._n_hyp)
+            nlZ, g = self.eng.eval(_cabi.SLOTS[which_set], want, self._n_hyp)
+            if 'proj' in self.hyp and want >= 1:                  # dnlZ.proj (infGrid.m:82-87): deriv_proj + chain rule
+                P = self.hyp['proj']
+                dP = self.eng.dnlZ_proj(_cabi.SLOTS[which_set], P.shape[0], P.shape[1])
+                g = np.concatenate([g, _chain_proj(P, dP, self._proj_mode).flatten(order='F')])
+            return nlZ, g
         except _cabi.KgpError as e:
             if e.code in (_cabi.NOT_PD, _cabi.CG_NOT_CONVERGED):
                 warnings.warn('Inference method failed [%s] .. attempting to continue' % e)   # gp.m:121
-                return float('nan'), np.zeros(self._n_hyp)
+                return float('nan'), np.zeros(n_out)
             raise
 
     def evaluate(self, which_set, X=None, y=None, verbose=0):
@@ -169,8 +212,10 @@ class B200GP(object):
         self._set_hyp_vec(v)
         self._push_model()
         self.last_train = {'fX': fX, 'n_evals': nev}
-        return {'cov': self.hyp['cov'].copy(), 'lik': self.hyp['lik'],
-                'mean': self.hyp['mean'].copy()}
+        out = {'cov': self.hyp['cov'].copy(), 'lik': self.hyp['lik'], 'mean': self.hyp['mean'].copy()}
+        if 'proj' in self.hyp:
+            out['proj'] = self.hyp['proj'].copy()
+        return out
 
     # -- dlik/dx (gpml.py:207-215) ------------------------------------------
     def get_dlik_dx(self, which_set, verbose=0):

@@ -643,3 +643,65 @@ def predict_grid(hyp, mean, kind, xg, post, xs, Q=0, vg=None):
     fs2 = np.maximum(ks - ve, 0.0)
     sn2 = np.exp(2.0 * float(hyp['lik']))
     return fmu, fs2, fmu.copy(), fs2 + sn2
+
+
+# ---- learned input projection hyp.proj (infGrid.m:56-65,82-87,155-186; dlikGrid.m:13-22,39) ----------------------
+def eff_proj(P, mode='none'):
+    """hP of infGrid.m:58-65: 'orth' -> sqrtm(P P' + eps I) \\ P, 'norm' -> diag(1/sqrt(diag(P P') + eps)) P."""
+    P = np.atleast_2d(np.asarray(P, dtype=np.float64))
+    eps = np.finfo(np.float64).eps
+    if str(mode).lower().startswith('orth'):
+        w, V = np.linalg.eigh(P @ P.T + eps * np.eye(P.shape[0]))
+        return np.linalg.solve((V * np.sqrt(w)) @ V.T, P)
+    if str(mode).lower().startswith('norm'):
+        return P / np.sqrt(np.sum(P * P, axis=1) + eps)[:, None]
+    return P
+
+
+def chain_orth(P, dP):
+    """infGrid.m:176-180: chain rule for Q = sqrtm(P P') \\ P."""
+    F, V = np.linalg.eigh(P @ P.T)
+    sf = np.sqrt(F); S = (V * sf) @ V.T
+    H = np.linalg.solve(S.T, dP).T                      # dP' / S
+    G = H.T @ np.linalg.solve(S.T, P).T                 # H' * (P' / S)
+    o = np.ones((dP.shape[0], 1))
+    return (H - P.T @ V @ ((V.T @ (G + G.T) @ V) / (sf[:, None] @ o.T + o @ sf[None, :])) @ V.T).T
+
+
+def chain_norm(P, dP):
+    """infGrid.m:183-185: chain rule for Q = diag(1 / sqrt(diag(P P'))) P."""
+    p = 1.0 / np.sqrt(np.sum(P * P, axis=1))
+    return p[:, None] * dP - (np.sum(dP * P, axis=1) * p ** 3)[:, None] * P
+
+
+def inf_grid_proj(hyp, mean, kind, xg, x, y, opt=None, Q=0, mode='none', h=1e-4):
+    """infGrid with hyp['proj'] (d x D): inference on x hP'; dnlZ['proj'] by deriv_proj (infGrid.m:155-167: the mean's
+    input derivative is a FORWARD difference with h = 1e-4) followed by the orth / norm chain rule."""
+    x = np.asarray(x, dtype=np.float64)
+    P = np.atleast_2d(np.asarray(hyp['proj'], dtype=np.float64)); hP = eff_proj(P, mode)
+    xP = x @ hP.T
+    post, nlZ, d = inf_grid(hyp, mean, kind, xg, xP, y, opt, Q)
+    alpha = post['alpha']; beta = post['Kalpha']
+    fg = flat_grid(xg)
+    _, dM = interpgrid(fg, xP, want_deriv=True)
+    m0 = mean_eval(mean, hyp.get('mean', []), xP)[0]
+    dP = np.zeros_like(hP)
+    for i in range(hP.shape[0]):
+        wi = (fg[i].max() - fg[i].min()) if equi(fg[i]) else 1.0
+        xq = xP.copy(); xq[:, i] += h
+        dmi = (mean_eval(mean, hyp.get('mean', []), xq)[0] - m0) / h
+        betai = dmi + dM[i] @ beta / wi
+        for j in range(hP.shape[1]):
+            dP[i, j] = -alpha @ (x[:, j] * betai)
+    if str(mode).lower().startswith('orth'):
+        dP = chain_orth(P, dP)
+    elif str(mode).lower().startswith('norm'):
+        dP = chain_norm(P, dP)
+    d = dict(d); d['proj'] = dP
+    return post, nlZ, d, hP
+
+
+def dlik_grid_proj(hyp, mean, kind, xg, x, y, opt=None, Q=0, mode='none'):
+    """dlikGrid.m with hyp.proj: deriv_x on x hP', then dx = dxP * hP (deriv_x.m:24)."""
+    hP = eff_proj(hyp['proj'], mode)
+    return dlik_grid(hyp, mean, kind, xg, np.asarray(x, dtype=np.float64) @ hP.T, y, opt, Q) @ hP

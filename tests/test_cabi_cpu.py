@@ -95,7 +95,8 @@ def test_unsupported_opt_keys_are_refused():
     d = Dummy()
     d._l = type('L', (), {'kgp_opt_default': staticmethod(_cabi.lib().kgp_opt_default), 'kgp_set_model': staticmethod(lambda *a: 0)})()
     d.set_model('infGrid', 'covSEiso', [0., 0.], 0.0, opt={'cg_tol': 1e-4, 'deg': 3})
-    for bad in ({'deg': 1}, {'proj': 'orth'}, {'ndcovs': 5}):
+    d.set_model('infGrid', 'covSEiso', [0., 0.], 0.0, opt={'proj': 'orth'})     # handled above the C ABI (engine.py)
+    for bad in ({'deg': 1}, {'ndcovs': 5}):
         with pytest.raises(ValueError):
             d.set_model('infGrid', 'covSEiso', [0., 0.], 0.0, opt=bad)
 

@@ -546,3 +546,37 @@ def test_cg_solve_is_bit_reproducible(built_lib):
         del gp
     for o in outs[1:]:
         assert o[3] == outs[0][3] and o[0] == outs[0][0] and np.array_equal(o[2], outs[0][2])
+
+
+@pytest.mark.parametrize('mode', ['none', 'orth', 'norm'])
+def test_learned_projection_vs_oracle(built_lib, mode):
+    """hyp.proj / opt.proj (infGrid.m:56-65,82-87,155-186; dlikGrid.m:13-22): inference on x hP', dnlZ.proj through the
+    orth / norm chain rule, dnlZ/dX = dxP hP, prediction through the same projector -- against the oracle."""
+    import gpml_grid as gg
+    from kgp_b200 import B200GP
+    rng = np.random.RandomState(5); n, D, d = 3000, 5, 2
+    X = rng.randn(n, D); P = 0.4 * rng.randn(d, D)
+    y = np.sin((X @ P.T).sum(1)) + 0.1 * rng.randn(n); Xs = rng.randn(50, D)
+    xg = [np.linspace(-6.0, 6.0, 40), np.linspace(-6.0, 6.0, 36)]
+    opt = {'cg_tol': 1e-12, 'cg_maxit': 20000, 'proj': mode}
+    gp = B200GP()
+    hyp = {'lik': np.log(0.2), 'mean': [[0.3], [-0.2], [0.1]], 'cov': [[0.1], [0.2]], 'proj': P.copy()}
+    gp.configure(d, hyp, opt, 'infGrid', 'meanSum', 'covSEiso', 'likGauss', 'dlikGrid', grid_kwargs={'eq': 1, 'k': 40., 'xg': xg},
+                 mean_args=['{@meanLinear, @meanConst}'], verbose=0)
+    gp.update_data('tr', X, y[:, None])
+    nlZ, g = gp._eval('tr', 2)
+    dX = gp.get_dlik_dx('tr'); ymu = gp.predict(Xs)
+    oh = {'cov': np.array([0.1, 0.2, 0.1, 0.2]), 'lik': np.log(0.2), 'mean': np.array([0.3, -0.2, 0.1]), 'proj': P}
+    oopt = {'cg_tol': 1e-12, 'cg_maxit': 20000}
+    post, nlZ0, d0, hP = gg.inf_grid_proj(oh, ['meanLinear', 'meanConst'], 'covSEiso', xg, X, y, oopt, mode=mode)
+    g0 = np.concatenate([d0['cov'], [d0['lik']], d0['mean'], d0['proj'].flatten(order='F')])
+    dX0 = gg.dlik_grid_proj(oh, ['meanLinear', 'meanConst'], 'covSEiso', xg, X, y, oopt, mode=mode)
+    p0 = gg.predict_grid(oh, ['meanLinear', 'meanConst'], 'covSEiso', xg, post, Xs @ hP.T)
+    assert g.size == g0.size and dX.shape == X.shape
+    assert rel(nlZ, nlZ0) < 1e-8 and rel(g[:-P.size], g0[:-P.size]) < 1e-8
+    # the reference takes the mean's input derivative by a forward difference (h = 1e-4): exact for the linear mean up to ~1e-11
+    assert rel(g[-P.size:], g0[-P.size:]) < 1e-7
+    assert rel(dX, dX0) < 1e-7 and rel(ymu, p0[2]) < 1e-7
+    # training moves hyp.proj and returns it (minimize over cov, lik, mean, proj)
+    h1 = gp.train(3)
+    assert h1['proj'].shape == P.shape and gp.last_train['fX'][-1] <= gp.last_train['fX'][0]

@@ -323,3 +323,38 @@ def test_neqinterp_matches_definition_and_gradcheck():
         e = np.zeros_like(X); e[i, d] = 1e-6
         # the Fiedler bound does not depend on x, the data-fit term does; linear interpolation is differentiable inside a cell
         assert abs((f(X + e) - f(X - e)) / 2e-6 - dX[i, d]) < 1e-5 * max(1.0, abs(dX[i, d]))
+
+
+def proj_problem(seed=5, n=400, D=5, d=2):
+    rng = np.random.RandomState(seed)
+    X = rng.randn(n, D)
+    P = 0.4 * rng.randn(d, D)
+    y = np.sin((X @ P.T).sum(1)) + 0.1 * rng.randn(n)
+    xg = [np.linspace(-6.0, 6.0, 40), np.linspace(-6.0, 6.0, 36)]
+    return X, y, P, xg
+
+
+@pytest.mark.parametrize('mode', ['none', 'orth', 'norm'])
+def test_proj_gradient_matches_finite_differences(mode):
+    """hyp.proj (infGrid.m:56-65,82-87,155-186): dnlZ.proj from deriv_proj + the orth / norm chain rule against central
+    differences of nlZ in the entries of hyp.proj; dlik_grid_proj = dxP hP against differences in x."""
+    X, y, P, xg = proj_problem()
+    opt = {'cg_tol': 1e-13, 'cg_maxit': 5000}
+    hyp = {'cov': np.array([0.1, 0.2, -0.1, 0.1]), 'lik': np.log(0.2), 'mean': np.array([0.3, -0.2, 0.1])}
+    mean = ['meanLinear', 'meanConst']
+    f = lambda pv: gg.inf_grid_proj(dict(hyp, proj=pv.reshape(P.shape)), mean, 'covSEiso', xg, X, y, opt, mode=mode)
+    post, nlZ, d, hP = f(P.ravel())
+    fd = _fd(lambda pv: f(pv)[1], P.ravel().copy()).reshape(P.shape)
+    assert np.max(np.abs(d['proj'] - fd)) / np.max(np.abs(fd)) < 2e-5
+    if mode == 'orth':
+        assert np.allclose(hP @ hP.T, np.eye(2), atol=1e-12)
+    if mode == 'norm':
+        assert np.allclose(np.sum(hP * hP, 1), 1.0, atol=1e-12)
+    dX = gg.dlik_grid_proj(dict(hyp, proj=P), mean, 'covSEiso', xg, X, y, opt, mode=mode)
+    assert dX.shape == X.shape
+    for (i, j) in ((0, 0), (7, 3), (123, 4)):
+        def fx(t):
+            Xt = X.copy(); Xt[i, j] += t
+            return gg.inf_grid_proj(dict(hyp, proj=P), mean, 'covSEiso', xg, Xt, y, opt, mode=mode)[1]
+        num = (fx(1e-5) - fx(-1e-5)) / 2e-5
+        assert abs(num - dX[i, j]) < 2e-5 * max(1.0, np.max(np.abs(dX)))
