@@ -134,6 +134,18 @@ int kgp_dlik_dx_dev (kgp_ctx* ctx, int slot, double* out);
 int kgp_predict_host(kgp_ctx* ctx, const double* Xs, long ns,
                      double* ymu, double* ys2, double* fmu, double* fs2);
 
+/* Allocation-free predictive mean.  NO COUNTERPART IN THE REFERENCE: added for callers
+ * that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * ymu_dev[i] = m(x*_i) + k(x*_i, X) alpha, the ymu of kgp_predict_host, for infExact with covSEiso / covSEard.
+ * Xs_dev (ns x D row-major) and ymu_dev (ns) are DEVICE pointers supplied by the caller; the posterior must be current
+ * (kgp_eval on slot TR since the last data / hyper-parameter change), otherwise KGP_NO_DATA -- it never factorises.  Calls no
+ * cudaMalloc / cudaFree or allocating library routine: its scratch (ns x ceil(n/512) partial sums) is a static 2 MiB device
+ * array inside the library, held by every GPU that loads it until exit; ns * ceil(n/512) > 262144 is refused with KGP_BAD_ARG
+ * (n = 40 000: at most 3318 test points per call).  All calls share the array and it keeps the last call's contents (every
+ * element read is written first, nothing needs clearing); calls that overlap on one GPU race on it.  Synchronises
+ * the context's stream before returning. */
+int kgp_predict_mean_noalloc_dev(kgp_ctx* ctx, const double* Xs_dev, long ns, double* ymu_dev);
+
 /* grid: replaces "xg = covGrid('create', X, eq, k)" (kgp/backend/gpml.py:29-31;
  * GPML/cov/apxGrid.m:389-416) and push('xg', ...) (kgp/backend/gpml.py:125-126). */
 int kgp_grid_create(kgp_ctx* ctx, int slot, int eq, double k);

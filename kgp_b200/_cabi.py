@@ -68,6 +68,7 @@ SIGNATURES = {
     'kgp_grid_axis_equispaced': (C.c_int, [C.c_void_p, C.c_int]),
     'kgp_grid_get_host': (C.c_int, [C.c_void_p, C.POINTER(C.c_int), C.c_void_p, C.c_void_p]),
     'kgp_set_proj_host': (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int]),
+    'kgp_predict_mean_noalloc_dev': (C.c_int, [C.c_void_p, C.c_void_p, C.c_long, C.c_void_p]),
     'kgp_dnlZ_proj_host': (C.c_int, [C.c_void_p, C.c_int, C.c_void_p]),
     'kgp_get_alpha_host': (C.c_int, [C.c_void_p, C.c_void_p]),
     'kgp_last_stats': (C.c_int, [C.c_void_p, C.POINTER(KgpStats)]),
@@ -238,6 +239,10 @@ class Context(object):
         lens = np.array([a.size for a in axes], dtype=np.int32)
         cat = np.concatenate(axes)
         self._chk(self._l.kgp_grid_set_host(self._h, len(axes), _ptr(lens), _ptr(cat)))
+
+    def predict_mean_noalloc(self, xs_dev_ptr, ns, ymu_dev_ptr):
+        """kgp_predict_mean_noalloc_dev: device pointers in and out, static scratch inside the library, no allocation."""
+        self._chk(self._l.kgp_predict_mean_noalloc_dev(self._h, C.c_void_p(int(xs_dev_ptr)), int(ns), C.c_void_p(int(ymu_dev_ptr))))
 
     def set_proj(self, P):
         """hyp.proj: the effective projector hP (d x D), or None to clear (kgp_set_proj_host)."""

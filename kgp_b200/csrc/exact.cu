@@ -817,7 +817,119 @@ int exact_predict(kgp_ctx* c, const double* Xs, long ns, double* ymu, double* ys
   return KGP_OK;
 }
 
+// ===== allocation-free predictive mean (kgp_predict_mean_noalloc_dev) ==================================================
+// No counterpart in the reference: added for callers that cannot call cudaMalloc
+// (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  It is the predictive-mean step of
+// exact_predict -- there the cross-covariances and partial results go through cudaMalloc'd scratch (pred_K, pred_x, pred_s,
+// pred_a ...) -- with its scratch in ONE file-scope device array of fixed size:
+//   parts[chunk][i] = sf2 sum_{j in chunk} exp(-|xs*_i - xs_j|^2 / 2) alpha_j   (chunks of 512 training points)
+//   ymu[i] = m(x*_i) + sum_chunk parts[chunk][i]                                 (fixed chunk order: deterministic)
+// Every GPU that loads the library holds the array (2 MiB) until exit.  All calls share it and it keeps the last call's
+// contents; every element a call reads it has written first, so nothing needs clearing -- but two calls that overlap on
+// one GPU (two contexts / two host threads) race on it.
+constexpr long NOALLOC_SCRATCH_DOUBLES = 262144;                 // 2 MiB: ns * ceil(n / 512) doubles at most
+static __device__ __align__(256) double g_noalloc_scratch[NOALLOC_SCRATCH_DOUBLES];
+constexpr int NOALLOC_MAX_DEV = 64;
+static double* g_noalloc_ptr[NOALLOC_MAX_DEV] = {nullptr};       // DEVICE address of the array per GPU (the symbol itself is a host-side stand-in)
+constexpr int PM_CHUNK = 512, PM_SUB = 64, PM_THREADS = 128;
+
+template <int DP>
+__global__ void __launch_bounds__(PM_THREADS) predict_mean_parts_kernel(const double* __restrict__ Xs, long ns, int D,
+    const double* __restrict__ mu, const double* __restrict__ inv_ell, const double* __restrict__ xs, const double* __restrict__ alpha,
+    long n, double sf2, double* __restrict__ parts) {
+  __shared__ double sx[PM_SUB][DP + 1];
+  __shared__ double sa[PM_SUB];
+  const int tid = threadIdx.x;
+  const long i = (long)blockIdx.x * PM_THREADS + tid;
+  double xi[DP];
+#pragma unroll
+  for (int d = 0; d < DP; ++d) xi[d] = (i < ns && d < D) ? (Xs[i * D + d] - mu[d]) * inv_ell[d] : 0.0;   // as scale_x_kernel
+  const long j0 = (long)blockIdx.y * PM_CHUNK, j1 = (j0 + PM_CHUNK < n) ? j0 + PM_CHUNK : n;
+  double acc = 0.0;
+  for (long jb = j0; jb < j1; jb += PM_SUB) {
+    __syncthreads();
+    for (int q = tid; q < PM_SUB * DP; q += PM_THREADS) {
+      const int r = q / DP, d = q - r * DP;
+      sx[r][d] = (jb + r < j1) ? xs[(jb + r) * DP + d] : 0.0;
+    }
+    if (tid < PM_SUB) sa[tid] = (jb + tid < j1) ? alpha[jb + tid] : 0.0;
+    __syncthreads();
+    const int cnt = (j1 - jb < PM_SUB) ? (int)(j1 - jb) : PM_SUB;
+    for (int r = 0; r < cnt; ++r) {
+      double d2 = 0.0;
+#pragma unroll
+      for (int d = 0; d < DP; ++d) { const double t = xi[d] - sx[r][d]; d2 = fma(t, t, d2); }
+      acc = fma(exp(-0.5 * d2), sa[r], acc);
+    }
+  }
+  if (i < ns) parts[(long)blockIdx.y * ns + i] = sf2 * acc;
+}
+// ymu[i] = m(x*_i) + sum of the chunk partials in chunk order  (gp.m:155-164; the mean as in predict_finish_kernel)
+__global__ void predict_mean_finish_kernel(const double* __restrict__ Xs, long ns, int D, int mean_mask, const double* __restrict__ hyp_mean,
+                                           const double* __restrict__ parts, int nchunk, double* __restrict__ ymu) {
+  const long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= ns) return;
+  double m = 0.0; int o = 0;
+  if (mean_mask & 1) { for (int d = 0; d < D; ++d) m += Xs[i * D + d] * hyp_mean[d]; o = D; }
+  if (mean_mask & 2) m += hyp_mean[o];
+  double k = 0.0;
+  for (int ch = 0; ch < nchunk; ++ch) k += parts[(long)ch * ns + i];
+  ymu[i] = m + k;
+}
+// set-up, once per device, with that device current (kgp_ctx_create -> exact_init)
+static int noalloc_setup(kgp_ctx* c) {
+  if (c->device < 0 || c->device >= NOALLOC_MAX_DEV || g_noalloc_ptr[c->device]) return KGP_OK;
+  double* p = nullptr;
+  KGP_CUDA(c, cudaGetSymbolAddress((void**)&p, g_noalloc_scratch));
+  g_noalloc_ptr[c->device] = p;
+  return KGP_OK;
+}
+template <int DP>
+static void launch_predict_mean_parts(kgp_ctx* c, const double* Xs, long ns, int D, long n, double sf2, int nchunk, double* parts) {
+  dim3 grid((unsigned)((ns + PM_THREADS - 1) / PM_THREADS), (unsigned)nchunk);
+  predict_mean_parts_kernel<DP><<<grid, PM_THREADS, 0, c->stream>>>(Xs, ns, D, c->mu.d(), c->inv_ell.d(), c->xs.d(), c->alpha.d(), n, sf2, parts);
+}
+}  // namespace kgp
+
+int kgp_predict_mean_noalloc_dev(kgp_ctx* c, const double* Xs_dev, long ns, double* ymu_dev) {
+  using namespace kgp;
+  if (!c) return KGP_BAD_ARG;
+  if (!Xs_dev || !ymu_dev || ns <= 0) return c->fail(KGP_BAD_ARG, "bad test inputs / output");
+  if (!c->model.set || c->model.inf_kind != KGP_INF_EXACT || c->model.cov_kind == KGP_COV_SM)
+    return c->fail(KGP_BAD_ARG, "kgp_predict_mean_noalloc_dev serves infExact with covSEiso / covSEard");
+  const int slot = KGP_SLOT_TR;
+  if (!state_valid(c, slot, 0))
+    return c->fail(KGP_NO_DATA, "no posterior for the current data / hyper-parameters: call kgp_eval first (this entry point "
+                   "cannot factorise, that would allocate)");
+  const Slot& S = c->slots[slot]; const Model& m = c->model;
+  const long n = S.n; const int D = S.D, Dp = c->Dp;
+  const long nchunk = (n + PM_CHUNK - 1) / PM_CHUNK;
+  if (ns * nchunk > NOALLOC_SCRATCH_DOUBLES)
+    return c->fail(KGP_BAD_ARG, "ns = %ld test points x %ld chunks of %d training points = %ld doubles of scratch; the static array holds %ld "
+                   "(2 MiB): at most %ld test points per call at n = %ld", ns, nchunk, PM_CHUNK, ns * nchunk, NOALLOC_SCRATCH_DOUBLES,
+                   NOALLOC_SCRATCH_DOUBLES / nchunk, n);
+  if (c->device < 0 || c->device >= NOALLOC_MAX_DEV || !g_noalloc_ptr[c->device])
+    return c->fail(KGP_CUDA_ERR, "static scratch not resolved on device %d", c->device);
+  cudaSetDevice(c->device);
+  double* parts = g_noalloc_ptr[c->device];
+  const int nl = m.cov_kind == KGP_COV_SEARD ? D : 1;
+  const double sf2 = exp(2.0 * m.hyp_cov[nl]);
+  switch (Dp) {
+    case 4: launch_predict_mean_parts<4>(c, Xs_dev, ns, D, n, sf2, (int)nchunk, parts); break;
+    case 8: launch_predict_mean_parts<8>(c, Xs_dev, ns, D, n, sf2, (int)nchunk, parts); break;
+    case 16: launch_predict_mean_parts<16>(c, Xs_dev, ns, D, n, sf2, (int)nchunk, parts); break;
+    case 32: launch_predict_mean_parts<32>(c, Xs_dev, ns, D, n, sf2, (int)nchunk, parts); break;
+    default: return c->fail(KGP_BAD_ARG, "unexpected padded input dimension %d", Dp);
+  }
+  predict_mean_finish_kernel<<<(unsigned)((ns + 255) / 256), 256, 0, c->stream>>>(Xs_dev, ns, D, m.mean_mask, c->hypm.d(), parts, (int)nchunk, ymu_dev);
+  KGP_CUDA(c, cudaStreamSynchronize(c->stream));
+  KGP_CUDA(c, cudaGetLastError());
+  return KGP_OK;
+}
+
+namespace kgp {
 int exact_init(kgp_ctx* c) {
+  { int rc = noalloc_setup(c); if (rc) return rc; }
   KGP_CUDA(c, gemm_init());
   KGP_CUDA(c, gemm_tma_init());
   KGP_CUDA(c, cudaFuncSetAttribute(potrf_diag128_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, PD_SMEM));
