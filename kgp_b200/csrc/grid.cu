@@ -30,7 +30,7 @@ struct GridState {
   long prank = 0;
   int gram_slot = -1; unsigned long gram_slot_ver = 0, gram_grid_ver = 0; int pcg_iters = 0;
   DevBuf kp0, kp1, gpad, tpad, upad;       // large-factor Kronecker MVM through the DMMA GEMM: zero-padded factors and grid matrices
-  DevBuf pdz, prr, bar, part4, g0b, wmaxd; int num_sms = 0; size_t smem_optin = 0; int cg_level_used = -1;
+  DevBuf pdz, prr, bar, part4, g0b, wmaxd, nodew2; double c2max2 = 0.0; int num_sms = 0; size_t smem_optin = 0; int cg_level_used = -1;
   int wmax = 0; int wmax_ctas = 0; unsigned long wmax_slot_ver = 0, wmax_grid_ver = 0; int wmax_slot = -1;
   int p = 0; int ng[GRID_MAXP] = {0}; long N = 0; bool any_neq = false;
   long koff[GRID_MAXP] = {0};            // offsets of factor i inside Kf / Vf
@@ -43,7 +43,7 @@ struct GridState {
   // active and vice versa (swap_sorted); sub_n < 0 = the active set covers all rows of the slot
   struct SortedSet { DevBuf U, perm; long npad = 0; int sort_slot = -1; unsigned long sort_slot_ver = 0, sort_grid_ver = 0;
                      int wmax = 0, wmax_ctas = 0, wmax_slot = -1; unsigned long wmax_slot_ver = 0, wmax_grid_ver = 0;
-                     long sub_lo = 0, sub_n = -1; } alt;
+                     long sub_lo = 0, sub_n = -1; double c2max2 = 0.0; } alt;
   long sub_lo = 0, sub_n = -1;
   // warm start of the factor eigen-decompositions: eigenvectors of the previous evaluation on the same grid
   DevBuf eigT; unsigned long eig_grid_ver = 0; int eig_evals = 0; bool eig_have = false;
@@ -62,7 +62,7 @@ void grid_free(kgp_ctx* c) {
   DevBuf* bufs[] = {&g->axes, &g->Kf, &g->Vf, &g->Af, &g->ee, &g->eoff, &g->de, &g->zv, &g->Qm, &g->Pm, &g->g0, &g->g1,
                     &g->tgrid, &g->beta, &g->x, &g->r, &g->d, &g->z, &g->ym, &g->partA, &g->partB, &g->S, &g->hyp,
                     &g->hypm, &g->dX, &g->dhyp, &g->out, &g->sortk, &g->sorti, &g->keep, &g->dmean,
-                    &g->U, &g->perm, &g->sx, &g->sr, &g->sd, &g->sz, &g->ctl, &g->cnt, &g->KfT, &g->gm0, &g->gm1, &g->pdz, &g->prr, &g->bar, &g->part4, &g->g0b, &g->wmaxd,
+                    &g->U, &g->perm, &g->sx, &g->sr, &g->sd, &g->sz, &g->ctl, &g->cnt, &g->KfT, &g->gm0, &g->gm1, &g->pdz, &g->prr, &g->bar, &g->part4, &g->g0b, &g->wmaxd, &g->nodew2,
                     &g->Gm, &g->Ht1, &g->Ht2, &g->VT, &g->se, &g->ps, &g->pw, &g->psel, &g->probes, &g->chT, &g->chU, &g->chY, &g->chS, &g->chC, &g->chP, &g->bva, &g->bvb, &g->bvc, &g->lzQ, &g->lzP, &g->lzH, &g->chacc,
                     &g->vg, &g->pvA, &g->pvS, &g->pvG, &g->alt.U, &g->alt.perm, &g->eigT, &g->kp0, &g->kp1, &g->gpad, &g->tpad, &g->upad};
   for (DevBuf* b : bufs) b->release();
@@ -77,7 +77,7 @@ static void swap_sorted(GridState* g) {
   std::swap(g->sort_slot, a.sort_slot); std::swap(g->sort_slot_ver, a.sort_slot_ver); std::swap(g->sort_grid_ver, a.sort_grid_ver);
   std::swap(g->wmax, a.wmax); std::swap(g->wmax_ctas, a.wmax_ctas); std::swap(g->wmax_slot, a.wmax_slot);
   std::swap(g->wmax_slot_ver, a.wmax_slot_ver); std::swap(g->wmax_grid_ver, a.wmax_grid_ver);
-  std::swap(g->sub_lo, a.sub_lo); std::swap(g->sub_n, a.sub_n);
+  std::swap(g->sub_lo, a.sub_lo); std::swap(g->sub_n, a.sub_n); std::swap(g->c2max2, a.c2max2);
 }
 static int nblocks_for(long n) { long b = (n + 255) / 256; return (int)std::min<long>(std::max<long>(b, 1), 1184); }
 
@@ -409,9 +409,20 @@ static int cg_run_persistent2(kgp_ctx* c, GridState* g, const CgLaunch& L, int s
     KGP_CUDA(c, cudaMemsetAsync(g->wmaxd.p, 0, 64, st));
     if (G.p == 1) cg_window_kernel<1><<<ctas, 32, 0, st>>>(G, L.U, L.npad, upc, (int*)g->wmaxd.p);
     else cg_window_kernel<2><<<ctas, 32, 0, st>>>(G, L.U, L.npad, upc, (int*)g->wmaxd.p);
-    int w = 0;
+    // bound of the fixed-point scatter (fx_scale): max over nodes of sum_i c_i^2, integer-accumulated (deterministic)
+    KGP_CUDA(c, g->nodew2.ensure((size_t)G.N * 8));
+    KGP_CUDA(c, cudaMemsetAsync(g->nodew2.p, 0, (size_t)G.N * 8, st));
+    {
+      const unsigned nb = (unsigned)std::min<long>((L.npad + 255) / 256, 2048);
+      if (G.p == 1) cg_node_weight2_kernel<1><<<nb, 256, 0, st>>>(G, L.U, L.npad, (unsigned long long*)g->nodew2.p);
+      else cg_node_weight2_kernel<2><<<nb, 256, 0, st>>>(G, L.U, L.npad, (unsigned long long*)g->nodew2.p);
+      cg_umax_kernel<<<(unsigned)std::min<long>((G.N + 255) / 256, 256), 256, 0, st>>>((const unsigned long long*)g->nodew2.p, G.N, (unsigned long long*)((char*)g->wmaxd.p + 8));
+    }
+    int w = 0; unsigned long long w2max = 0;
     KGP_CUDA(c, cudaMemcpyAsync(&w, g->wmaxd.p, 4, cudaMemcpyDeviceToHost, st));
+    KGP_CUDA(c, cudaMemcpyAsync(&w2max, (char*)g->wmaxd.p + 8, 8, cudaMemcpyDeviceToHost, st));
     KGP_CUDA(c, cudaStreamSynchronize(st));
+    g->c2max2 = std::max((double)w2max / 1073741824.0, 1.0);
     g->wmax = w; g->wmax_slot = slot; g->wmax_slot_ver = S.version; g->wmax_grid_ver = c->grid.version; g->wmax_ctas = ctas;
   }
   const int wcap = std::max(g->wmax, 4);
@@ -440,7 +451,7 @@ static int cg_run_persistent2(kgp_ctx* c, GridState* g, const CgLaunch& L, int s
   CgPersist2 A; memset(&A, 0, sizeof A);
   A.G = G; A.U = L.U; A.n = L.n; A.npad = L.npad; A.m = L.m; A.upc = upc; A.wcap = wcap;
   A.x = L.sx; A.r = L.sr; A.d = L.sd; A.z = L.sz;
-  A.fxa = (long long*)g->g0b.p; A.fxb = (long long*)((char*)g->g0b.p + fxbytes); A.npts_bound = L.n;
+  A.fxa = (long long*)g->g0b.p; A.fxb = (long long*)((char*)g->g0b.p + fxbytes); A.npts_bound = L.n; A.c2max2 = g->c2max2;
   A.K0 = L.Kf; A.K0T = L.KfT; A.K1 = L.Kf + L.koff1;
   A.ctl = L.ctl; A.part = g->part4.d(); A.bar = (unsigned*)g->bar.p; A.stg_doubles = stg_need;
   A.dbg = getenv("KGP_DEBUG") ? (long long*)((char*)g->bar.p + 128) : nullptr;

@@ -164,28 +164,58 @@ __device__ __forceinline__ void flush_nodes(const GridDesc& G, double* __restric
 // ---- order-independent scatter accumulation (cg_persistent2_kernel) -------------------------------------------------
 // Floating-point atomics make Mx'(sW d) depend on the order in which warps and CTAs reach a node, so two runs of the
 // same solve differed in the last bits and could stop one iteration apart.  Integer atomics are associative: every
-// flushed value v is split into hi = rint(v 2^e1) and lo = rint((v - hi 2^-e1) 2^(e1+36)) -- both exact operations --
-// and the two parts are accumulated with 64-bit integer REDs into separate arrays.  The sum hi 2^-e1 + lo 2^-(e1+36) is
-// then the same for every arrival order (resolution 2^-96 of the bound, i.e. finer than FP64 on the node values).
-// e1 comes from the Cauchy-Schwarz bound |sum_i c_i sw d_i| <= sw sqrt(n) |d|_2 with |d|_2^2 from the recursion
-// |d_k|^2 = |r_k|^2 + beta^2 |d_k-1|^2, which every CTA evaluates identically from the shared scalars.
+// flushed value v becomes hi = rint(v 2^e1) and is accumulated with ONE 64-bit integer RED; the sum hi 2^-e1 is the same
+// for every arrival order.  e1 = 61 - ilogb(bound) with a bound that holds for every partial sum of a node:
+//   |sum_i c_i sw d_i| <= sw sqrt(sum_i c_i^2) |d|_2 <= sw C2max |d|_2,   C2max^2 = max over nodes of sum_i c_i^2
+// (Cauchy-Schwarz over the points that touch the node; C2max^2 is a property of data + grid, accumulated once in integer
+// arithmetic by cg_node_weight2_kernel so that it is itself run-to-run identical) and |d|_2^2 from the recursion
+// |d_k|^2 = |r_k|^2 + beta^2 |d_k-1|^2, which every CTA evaluates identically from the shared scalars (x16 safety).
+// Resolution: 2^-61 of the bound.  With ~3000 points per node C2max is ~20, not sqrt(n) = 1000, so the absolute resolution
+// is ~2^-55 of a typical node value -- the level of the FP64 atomics it replaces -- and normwise (what CG needs) far below.
+// (Round 2 first shipped a two-word form, hi + lo with the sqrt(n) bound: two REDs per flush, 53 us per iteration at
+// n = 1M against 38 with FP64 atomics; the tighter bound makes the second word unnecessary.)
 struct FxScale { double s1, i1, s2, i2; };
 __device__ __forceinline__ FxScale fx_scale(double bound) {
   int e1 = 0;
-  if (bound > 0.0 && bound < 1e300) e1 = 59 - ilogb(bound);
+  if (bound > 0.0 && bound < 1e300) e1 = 61 - ilogb(bound);
   e1 = e1 < -1000 ? -1000 : (e1 > 960 ? 960 : e1);
-  FxScale f; f.s1 = scalbn(1.0, e1); f.i1 = scalbn(1.0, -e1); f.s2 = scalbn(1.0, e1 + 36); f.i2 = scalbn(1.0, -e1 - 36);
+  FxScale f; f.s1 = scalbn(1.0, e1); f.i1 = scalbn(1.0, -e1); f.s2 = 0.0; f.i2 = 0.0;
   return f;
 }
+// lo is only a mode flag now: non-null = fixed point in hi, null = the array holds plain doubles (FP64-atomics mode)
 __device__ __forceinline__ void fx_add(long long* __restrict__ hi, long long* __restrict__ lo, long idx, double v, const FxScale& f) {
-  const long long h = __double2ll_rn(v * f.s1);
-  const long long l = __double2ll_rn((v - (double)h * f.i1) * f.s2);
-  atomicAdd((unsigned long long*)(hi + idx), (unsigned long long)h);
-  if (l) atomicAdd((unsigned long long*)(lo + idx), (unsigned long long)l);
+  atomicAdd((unsigned long long*)(hi + idx), (unsigned long long)__double2ll_rn(v * f.s1));
 }
 __device__ __forceinline__ double fx_load(const long long* __restrict__ hi, const long long* __restrict__ lo, long idx, const FxScale& f) {
   if (!lo) return __ldcg((const double*)hi + idx);      // FP64-atomics mode: the array holds plain doubles
-  return (double)__ldcg(hi + idx) * f.i1 + (double)__ldcg(lo + idx) * f.i2;
+  return (double)__ldcg(hi + idx) * f.i1;
+}
+// w2[node] += ceil(c^2 2^30) for every point and stencil node: integer sums, hence deterministic; ceil keeps it an upper bound
+template <int P>
+__global__ void cg_node_weight2_kernel(GridDesc G, const double* __restrict__ U, long npts, unsigned long long* __restrict__ w2) {
+  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < npts; i += (long)gridDim.x * blockDim.x) {
+    int j[P]; double c[P][4];
+#pragma unroll
+    for (int d = 0; d < P; ++d) decode_u(U[i * P + d], G.ng[d], j[d], c[d]);
+    if (P == 1) {
+#pragma unroll
+      for (int a = 0; a < 4; ++a) { const double w = c[0][a]; if (w != 0.0) atomicAdd(w2 + j[0] + a, (unsigned long long)ceil(w * w * 1073741824.0)); }
+    } else {
+#pragma unroll
+      for (int b = 0; b < 4; ++b)
+#pragma unroll
+        for (int a = 0; a < 4; ++a) {
+          const double w = c[0][a] * c[P - 1][b];
+          if (w != 0.0) atomicAdd(w2 + (long)(j[P - 1] + b) * G.stride[1] + j[0] + a, (unsigned long long)ceil(w * w * 1073741824.0));
+        }
+    }
+  }
+}
+__global__ void cg_umax_kernel(const unsigned long long* __restrict__ w2, long N, unsigned long long* __restrict__ out) {
+  unsigned long long m = 0;
+  for (long q = (long)blockIdx.x * blockDim.x + threadIdx.x; q < N; q += (long)gridDim.x * blockDim.x) m = w2[q] > m ? w2[q] : m;
+  for (int o = 16; o; o >>= 1) { const unsigned long long t = __shfl_xor_sync(0xffffffffu, m, o); m = t > m ? t : m; }
+  if ((threadIdx.x & 31) == 0 && m) atomicMax(out, m);
 }
 template <int P>
 __device__ __forceinline__ void flush_nodes_fx(const GridDesc& G, long long* __restrict__ hi, long long* __restrict__ lo, int cell, const double* acc,
@@ -913,7 +943,8 @@ struct CgPersist2 {
   const double* U; long n, npad; int m, upc, wcap;     // wcap = node rows the window buffer can hold
   double *x, *r, *d, *z;                               // [m][npad], sorted order
   long long *fxa, *fxb;                                // [m][2][N] fixed-point scatter targets (hi, lo), alternating per iteration
-  long npts_bound;                                     // points this launch scatters (bound of the accumulation)
+  long npts_bound;                                     // points this launch scatters
+  double c2max2;                                       // max over nodes of sum_i c_i^2 (bound of the accumulation, see fx_scale)
   const double *K0, *K0T, *K1;
   double *ctl; double *part;                           // partials [4][m][gridDim]: |r|^2, d.z, r.z, z.z
   unsigned* bar; long long* dbg;
@@ -947,8 +978,8 @@ __global__ void cg_window_kernel(GridDesc G, const double* __restrict__ U, long 
 #else
 #define KGP_CGP2_BOUNDS __launch_bounds__(CGP2_THREADS, 1)
 #endif
-// FX: order-independent fixed-point scatter (bit-reproducible solves, two integer REDs per flush); !FX: FP64 atomics (one RED per
-// flush, ~25 % faster at n = 1M, results differ in the last bits from run to run).  Without FX the (hi) array holds plain doubles.
+// FX: order-independent fixed-point scatter (bit-reproducible solves, one integer RED per flush); !FX: FP64 atomics (results differ
+// in the last bits from run to run).  Without FX the (hi) array holds plain doubles.
 template <int P, int LEVEL, bool DBG, bool DIST, bool FX>
 __global__ void KGP_CGP2_BOUNDS cg_persistent2_kernel(const CgPersist2 A) {
   constexpr int NW = CgNodes<P>::NW;
@@ -1014,7 +1045,7 @@ __global__ void KGP_CGP2_BOUNDS cg_persistent2_kernel(const CgPersist2 A) {
 
   while (true) {
     if (tid == 0) { int any = 0; for (int c = 0; c < m; ++c) any |= (s_state[c] == 0 || s_state[c] == 3); s_any = any; }
-    if (FX && tid < m) s_fx[tid] = fx_scale(4.0 * sw * sqrt((double)A.npts_bound) * sqrt(fmax(s_dn2[tid], 0.0)));
+    if (FX && tid < m) s_fx[tid] = fx_scale(4.0 * sw * sqrt(A.c2max2) * sqrt(fmax(s_dn2[tid], 0.0)));
     __syncthreads();
     if (!s_any) break;
     ++pass;
@@ -1294,7 +1325,7 @@ __global__ void KGP_CGP2_BOUNDS cg_persistent2_kernel(const CgPersist2 A) {
         else { *(double2*)(z + base) = make_double2(zv[0], zv[1]); *(double2*)(z + base + 2) = make_double2(zv[2], zv[3]); }
       }
       long long* gz = g0z + (long)col * 2 * G.N;
-      for (long q = (long)cta * CGP2_THREADS + tid; q < 2 * G.N; q += (long)nctas * CGP2_THREADS) gz[q] = 0;
+      for (long q = (long)cta * CGP2_THREADS + tid; q < G.N; q += (long)nctas * CGP2_THREADS) gz[q] = 0;     // (only the first of the two words per node is in use)
       double t = block_sum(dz, s_red);
       if (tid == 0) A.part[((long)1 * m + col) * nctas + cta] = t;
       t = block_sum(rz, s_red);
