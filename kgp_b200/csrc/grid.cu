@@ -24,7 +24,7 @@ struct GridState {
   double* h_ctl = nullptr;                // pinned host copy of the control blocks
   long npad = 0; int sort_slot = -1; unsigned long sort_slot_ver = 0, sort_grid_ver = 0;
   cudaGraphExec_t cg_graph = nullptr; std::vector<char> cg_graph_key;
-  DevBuf probes, chT, chU, chY, chS, chC, chP, bva, bvb, bvc, lzQ, lzP, lzH, chacc;   // Chebyshev log-det (grid_cheby.cuh)
+  DevBuf probes, chT, chU, chY, chZ, chZ2, chS, chC, chP, bva, bvb, bvc, bvs, lzQ, lzP, lzH, chacc;   // Chebyshev log-det (grid_cheby.cuh)
   long probes_n = 0; int probes_m = 0; double probes_emax = 0.0; bool probes_injected = false;
   DevBuf Gm, Ht1, Ht2, VT, se, ps, pw, psel;           // Woodbury preconditioner (grid_precond.cuh); psel: kept modes
   long prank = 0;
@@ -63,7 +63,7 @@ void grid_free(kgp_ctx* c) {
                     &g->tgrid, &g->beta, &g->x, &g->r, &g->d, &g->z, &g->ym, &g->partA, &g->partB, &g->S, &g->hyp,
                     &g->hypm, &g->dX, &g->dhyp, &g->out, &g->sortk, &g->sorti, &g->keep, &g->dmean,
                     &g->U, &g->perm, &g->sx, &g->sr, &g->sd, &g->sz, &g->ctl, &g->cnt, &g->KfT, &g->gm0, &g->gm1, &g->pdz, &g->prr, &g->bar, &g->part4, &g->g0b, &g->wmaxd, &g->nodew2,
-                    &g->Gm, &g->Ht1, &g->Ht2, &g->VT, &g->se, &g->ps, &g->pw, &g->psel, &g->probes, &g->chT, &g->chU, &g->chY, &g->chS, &g->chC, &g->chP, &g->bva, &g->bvb, &g->bvc, &g->lzQ, &g->lzP, &g->lzH, &g->chacc,
+                    &g->Gm, &g->Ht1, &g->Ht2, &g->VT, &g->se, &g->ps, &g->pw, &g->psel, &g->probes, &g->chT, &g->chU, &g->chY, &g->chZ, &g->chZ2, &g->bvs, &g->chS, &g->chC, &g->chP, &g->bva, &g->bvb, &g->bvc, &g->lzQ, &g->lzP, &g->lzH, &g->chacc,
                     &g->vg, &g->pvA, &g->pvS, &g->pvG, &g->alt.U, &g->alt.perm, &g->eigT, &g->kp0, &g->kp1, &g->gpad, &g->tpad, &g->upad};
   for (DevBuf* b : bufs) b->release();
   if (g->h_ctl) cudaFreeHost(g->h_ctl);
@@ -773,22 +773,53 @@ static int cheby_logdet(kgp_ctx* c, GridState* g, const GridDesc& G, int slot, d
   KGP_CUDA(c, g->chT.ensure((size_t)d * G.N * 8)); KGP_CUDA(c, g->chU.ensure((size_t)d * G.N * 8));
   KGP_CUDA(c, g->chY.ensure((size_t)d * G.N * 8)); KGP_CUDA(c, g->chS.ensure((size_t)d * d * 8));
   KGP_CUDA(c, g->chC.ensure((size_t)2 * d * d * 8)); KGP_CUDA(c, g->chP.ensure((size_t)ksz * 8));
-  KGP_CUDA(c, g->bva.ensure(n * 8)); KGP_CUDA(c, g->bvb.ensure(n * 8)); KGP_CUDA(c, g->chacc.ensure(64));
+  KGP_CUDA(c, g->chZ.ensure((size_t)d * G.N * 8)); KGP_CUDA(c, g->chZ2.ensure((size_t)d * G.N * 8));
+  KGP_CUDA(c, g->chacc.ensure(64));
+  // the recurrence runs on the cell-sorted point set of the CG path when there is one (1-D / 2-D equispaced grids, all rows
+  // of the slot active): sorted_scatter_kernel / cheby_step_sorted_kernel; otherwise on the points as given
+  static const bool sorted_ok = !(getenv("KGP_CHEBY_SORTED") && atoi(getenv("KGP_CHEBY_SORTED")) == 0);
+  bool sorted = sorted_ok && G.p <= 2 && !g->any_neq && g->sub_n < 0;
+  if (sorted) { int rc = cg_prepare_sorted(c, g, G, slot); if (rc) return rc; sorted = g->sub_n < 0 && g->npad >= n; }
+  const long nv = sorted ? g->npad : n;                                     // length of a Krylov vector
+  KGP_CUDA(c, g->bva.ensure(nv * 8)); KGP_CUDA(c, g->bvb.ensure(nv * 8)); KGP_CUDA(c, g->bvs.ensure(nv * 8));
   const int nb = nblocks_for(n);
+  const bool k2 = G.p == 2 && std::max(G.ng[0], G.ng[1]) < 192;
   auto apply_step = [&](const double* bv, const double* v, double c1, double c2, double* Tj, double* Uj, double* out) {
-    scatter(c, G, S.X.d(), n, D, bv, sw, Tj);                               // T = Mx'(sW bv)
-    kron_to(c, g, G, Tj, Uj, -1);                                           // U = Kg T
-    for_p(G.p, [&](auto P) {
-      cheby_step_kernel<decltype(P)::value><<<nb, 256, 0, st>>>(G, S.X.d(), n, D, Uj, bv, v, c1, c2, out, g->partA.d());
-    });
-    c->stats.kernel_launches += 1;
+    if (!sorted) {
+      scatter(c, G, S.X.d(), n, D, bv, sw, Tj);                             // T = Mx'(sW bv)
+      kron_to(c, g, G, Tj, Uj, -1);                                         // U = Kg T
+      for_p(G.p, [&](auto P) {
+        cheby_step_kernel<decltype(P)::value><<<nb, 256, 0, st>>>(G, S.X.d(), n, D, Uj, bv, v, c1, c2, out, g->partA.d());
+      });
+      c->stats.kernel_launches += 1;
+      return;
+    }
+    cudaMemsetAsync(Tj, 0, G.N * 8, st);
+    if (G.p == 1) sorted_scatter_kernel<1><<<nb, 256, 0, st>>>(G, g->U.d(), g->npad, bv, sw, Tj);
+    else sorted_scatter_kernel<2><<<nb, 256, 0, st>>>(G, g->U.d(), g->npad, bv, sw, Tj);
+    if (G.p == 1) mode_product_kernel<<<(unsigned)((G.N + 255) / 256), 256, 0, st>>>(g->Kf.d(), G.ng[0], Tj, Uj, 1, 1);
+    else if (k2) {
+      int TA = (G.ng[0] + 31) & ~31; if (TA > 256) TA = 256;
+      const size_t ksm = (size_t)(KRON2_THREADS / TA + 1) * G.ng[0] * 8;
+      kron2_kernel<<<dim3((unsigned)G.ng[1], 1), KRON2_THREADS, ksm, st>>>(g->KfT.d(), g->Kf.d() + g->koff[1], G.ng[0], G.ng[1], Tj, Uj, nullptr);
+    } else kron_to(c, g, G, Tj, Uj, -1);
+    if (G.p == 1) cheby_step_sorted_kernel<1><<<nb, 256, 0, st>>>(G, g->U.d(), n, g->npad, Uj, bv, v, c1, c2, out, g->partA.d());
+    else cheby_step_sorted_kernel<2><<<nb, 256, 0, st>>>(G, g->U.d(), n, g->npad, Uj, bv, v, c1, c2, out, g->partA.d());
+    c->stats.kernel_launches += 3;
+  };
+  // probe i in the order the recurrence works in
+  auto probe_vec = [&](int i) -> const double* {
+    const double* v = g->probes.d() + (long)i * n;
+    if (!sorted) return v;
+    permute_in_kernel<<<nb, 256, 0, st>>>(v, (const int*)g->perm.p, n, g->npad, g->bvs.d());
+    return g->bvs.d();
   };
   // ---- emax: injected, or power iteration on B = I + sW K sW   (the reference: eigs(B,1,'lm'), apx.m:344-350)
   double emax = g->probes_injected ? g->probes_emax : 0.0;
   if (!(emax > 0.0)) {
     const int its = mo.opt.ldB2_cheby_maxit > 0 ? mo.opt.ldB2_cheby_maxit : 50;
     double nrm2 = (double)n, lam = 1.0;
-    KGP_CUDA(c, cudaMemcpyAsync(g->bva.p, g->probes.p, n * 8, cudaMemcpyDeviceToDevice, st));
+    KGP_CUDA(c, cudaMemcpyAsync(g->bva.p, probe_vec(0), nv * 8, cudaMemcpyDeviceToDevice, st));
     double* cur = g->bva.d(); double* nxt = g->bvb.d();
     for (int it = 0; it < its; ++it) {
       apply_step(cur, cur, 1.0, sw, g->chT.d(), g->chU.d(), nxt);            // nxt = B cur ; partials of cur.nxt
@@ -840,7 +871,7 @@ static int cheby_logdet(kgp_ctx* c, GridState* g, const GridDesc& G, int slot, d
   int lo = 0, hi = m;
   if (c->nranks > 1) { const int base = m / c->nranks, extra = m % c->nranks; lo = c->rank * base + std::min(c->rank, extra); hi = lo + base + (c->rank < extra ? 1 : 0); }
   for (int i = lo; i < hi; ++i) {
-    const double* v = g->probes.d() + (long)i * n;
+    const double* v = probe_vec(i);
     dot_kernel<<<1, 1024, 0, st>>>(v, v, n, g->chacc.d() + 2);
     sum_scaled_acc_kernel<<<1, 256, 0, st>>>(g->chacc.d() + 2, 1, pp[0] / (2.0 * m), g->chacc.d());      // j = 0 term: v'v p_0
     const double* cur = v; double* bufs[2] = {g->bva.d(), g->bvb.d()};
@@ -857,14 +888,18 @@ static int cheby_logdet(kgp_ctx* c, GridState* g, const GridDesc& G, int slot, d
       sum_scaled_acc_kernel<<<1, 256, 0, st>>>(g->chacc.d() + 2, 1, 1.0, g->chacc.d() + 1);
       mix_small_kernel<<<dim3((unsigned)((G.N + 255) / 256), d), 256, 0, st>>>(g->chT.d(), g->chC.d(), G.N, d, g->chY.d());
       for (int f = 0; f < G.p; ++f) {
-        const long inner = G.stride[f], outer = G.N / (inner * G.ng[f]);
-        for (int s2 = 0; s2 < d; ++s2) {
-          kron_to(c, g, G, g->chY.d() + (long)s2 * G.N, g->beta.d(), f);      // beta buffer as scratch (it is rewritten after the log-det section)
-          mode_gram_acc_kernel<<<dim3(G.ng[f], G.ng[f]), 128, 0, st>>>(g->beta.d(), g->chT.d() + (long)s2 * G.N, G.ng[f], inner, outer,
-                                                                    g->chP.d() + g->koff[f]);
+        // all d mixed vectors at once: [d][N] contiguous is the same as d times as many outer slices of every mode
+        const double* src = g->chY.d(); double* zb[2] = {g->chZ.d(), g->chZ2.d()}; int bi = 0;
+        for (int dd = 0; dd < G.p; ++dd) {
+          if (dd == f) continue;
+          const long in2 = G.stride[dd], out2 = G.N / (in2 * G.ng[dd]) * d;
+          mode_product_kernel<<<(unsigned)(((long)d * G.N + 255) / 256), 256, 0, st>>>(g->Kf.d() + g->koff[dd], G.ng[dd], src, zb[bi], in2, out2);
+          src = zb[bi]; bi ^= 1; c->stats.kernel_launches++;
         }
+        const long inner = G.stride[f], outer = G.N / (inner * G.ng[f]) * d;
+        mode_gram_acc_kernel<<<dim3(G.ng[f], G.ng[f]), 128, 0, st>>>(src, g->chT.d(), G.ng[f], inner, outer, g->chP.d() + g->koff[f]);
       }
-      c->stats.kernel_launches += 4 + 2 * d * G.p;
+      c->stats.kernel_launches += 4 + G.p;
     }
   }
   if (c->nranks > 1) {

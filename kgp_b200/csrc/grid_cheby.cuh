@@ -37,6 +37,145 @@ __global__ void cheby_step_kernel(GridDesc G, const double* __restrict__ X, long
   if (threadIdx.x == 0) part[blockIdx.x] = t;
 }
 
+// ---- the same step on the CELL-SORTED point set of the CG path (cg_prepare_sorted: encoded coordinates U, permutation) ----
+// The Krylov vectors of a probe live in sorted order for the whole recurrence (dot products do not care), so the
+// scatter is the segmented one of cg_scatter_kernel -- one flush per run of equal cells instead of 16 atomics per point on
+// 4900 hot nodes -- and the gather reads a cell's 4^P node values once per run.  Per step at n = 1M: ~200 us -> ~35 us.
+// vs[k] = v[perm[k]] (k < n), 0 on the padding
+__global__ void permute_in_kernel(const double* __restrict__ v, const int* __restrict__ perm, long n, long npad, double* __restrict__ vs) {
+  for (long k = (long)blockIdx.x * blockDim.x + threadIdx.x; k < npad; k += (long)gridDim.x * blockDim.x) vs[k] = (k < n) ? v[perm[k]] : 0.0;
+}
+// g0 += Mx'(sw v), v in sorted order (padding entries are zero)
+template <int P>
+__global__ void __launch_bounds__(256, 3) sorted_scatter_kernel(GridDesc G, const double* __restrict__ U, long npad,
+    const double* __restrict__ v, double sw, double* __restrict__ g0) {
+  constexpr int NW = CgNodes<P>::NW;
+  const int lane = threadIdx.x & 31;
+  const long nunits = npad / (32 * CG_PTS), nwarps = (long)gridDim.x * (blockDim.x >> 5);
+  for (long unit = (long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); unit < nunits; unit += nwarps) {
+    const long base = unit * (32 * CG_PTS) + (long)lane * CG_PTS;
+    double dn[CG_PTS], uu[CG_PTS * P];
+    {
+      const double2 d0 = *(const double2*)(v + base), d1 = *(const double2*)(v + base + 2);
+      dn[0] = d0.x; dn[1] = d0.y; dn[2] = d1.x; dn[3] = d1.y;
+#pragma unroll
+      for (int q = 0; q < CG_PTS * P / 2; ++q) {
+        const double2 t = __ldg((const double2*)(U + base * P) + q);
+        uu[2 * q] = t.x; uu[2 * q + 1] = t.y;
+      }
+    }
+    double acc[NW];
+#pragma unroll
+    for (int w = 0; w < NW; ++w) acc[w] = 0.0;
+    int cur = -1;
+#pragma unroll
+    for (int q = 0; q < CG_PTS; ++q) {
+      int j[P]; double c[P][4];
+#pragma unroll
+      for (int dd = 0; dd < P; ++dd) decode_u(uu[q * P + dd], G.ng[dd], j[dd], c[dd]);
+      const int cell = (P == 1) ? j[0] : j[0] + j[P - 1] * G.ng[0];
+      if (cell != cur) {
+        if (cur >= 0) {
+          flush_nodes<P>(G, g0, cur, acc);
+#pragma unroll
+          for (int w = 0; w < NW; ++w) acc[w] = 0.0;
+        }
+        cur = cell;
+      }
+      const double vi = sw * dn[q];
+      if (P == 1) {
+#pragma unroll
+        for (int a = 0; a < 4; ++a) acc[a] = fma(c[0][a], vi, acc[a]);
+      } else {
+#pragma unroll
+        for (int b = 0; b < 4; ++b) {
+          const double wb = c[P - 1][b] * vi;
+#pragma unroll
+          for (int a = 0; a < 4; ++a) acc[b * 4 + a] = fma(c[0][a], wb, acc[b * 4 + a]);
+        }
+      }
+    }
+#pragma unroll
+    for (int off = 1; off < 32; off <<= 1) {              // segmented reduction over the warp (cells are contiguous)
+      const int oc = __shfl_down_sync(0xffffffffu, cur, off);
+      const bool take = (lane + off < 32) && (oc == cur);
+#pragma unroll
+      for (int w = 0; w < NW; ++w) {
+        const double o = __shfl_down_sync(0xffffffffu, acc[w], off);
+        if (take) acc[w] += o;
+      }
+    }
+    const int pc = __shfl_up_sync(0xffffffffu, cur, 1);
+    if (lane == 0 || pc != cur) flush_nodes<P>(G, g0, cur, acc);
+  }
+}
+
+// out = c1 * bv + c2 * (Mx u) ;  part[block] = sum v .* out      (all n-vectors in sorted order, padding stays zero)
+template <int P>
+__global__ void __launch_bounds__(256, 3) cheby_step_sorted_kernel(GridDesc G, const double* __restrict__ U, long n, long npad,
+    const double* __restrict__ ug, const double* __restrict__ bv, const double* __restrict__ v, double c1, double c2,
+    double* __restrict__ out, double* __restrict__ part) {
+  constexpr int NW = CgNodes<P>::NW;
+  __shared__ double sh[32];
+  double acc = 0.0;
+  const long nunits = npad / (32 * CG_PTS), nwarps = (long)gridDim.x * (blockDim.x >> 5);
+  for (long unit = (long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); unit < nunits; unit += nwarps) {
+    const long base = unit * (32 * CG_PTS) + (long)(threadIdx.x & 31) * CG_PTS;
+    double bq[CG_PTS], vq[CG_PTS], uu[CG_PTS * P], ov[CG_PTS];
+    {
+      const double2 b0 = *(const double2*)(bv + base), b1 = *(const double2*)(bv + base + 2);
+      const double2 v0 = *(const double2*)(v + base), v1 = *(const double2*)(v + base + 2);
+      bq[0] = b0.x; bq[1] = b0.y; bq[2] = b1.x; bq[3] = b1.y; vq[0] = v0.x; vq[1] = v0.y; vq[2] = v1.x; vq[3] = v1.y;
+#pragma unroll
+      for (int q = 0; q < CG_PTS * P / 2; ++q) {
+        const double2 t = __ldg((const double2*)(U + base * P) + q);
+        uu[2 * q] = t.x; uu[2 * q + 1] = t.y;
+      }
+    }
+    double nv[NW];
+    int cur = -1;
+#pragma unroll
+    for (int q = 0; q < CG_PTS; ++q) {
+      int j[P]; double c[P][4];
+#pragma unroll
+      for (int dd = 0; dd < P; ++dd) decode_u(uu[q * P + dd], G.ng[dd], j[dd], c[dd]);
+      const int cell = (P == 1) ? j[0] : j[0] + j[P - 1] * G.ng[0];
+      if (cell != cur) {
+        cur = cell;
+        if (P == 1) {
+#pragma unroll
+          for (int a = 0; a < 4; ++a) nv[a] = ug[j[0] + a];
+        } else {
+#pragma unroll
+          for (int b = 0; b < 4; ++b) {
+            const double* row = ug + (long)(j[P - 1] + b) * G.stride[1] + j[0];
+#pragma unroll
+            for (int a = 0; a < 4; ++a) nv[b * 4 + a] = row[a];
+          }
+        }
+      }
+      double mu = 0.0;
+      if (P == 1) {
+#pragma unroll
+        for (int a = 0; a < 4; ++a) mu = fma(c[0][a], nv[a], mu);
+      } else {
+#pragma unroll
+        for (int b = 0; b < 4; ++b) {
+          double rb = 0.0;
+#pragma unroll
+          for (int a = 0; a < 4; ++a) rb = fma(c[0][a], nv[b * 4 + a], rb);
+          mu = fma(c[P - 1][b], rb, mu);
+        }
+      }
+      const double o = (base + q < n) ? fma(c2, mu, c1 * bq[q]) : 0.0;
+      ov[q] = o; acc = fma(vq[q], o, acc);
+    }
+    *(double2*)(out + base) = make_double2(ov[0], ov[1]); *(double2*)(out + base + 2) = make_double2(ov[2], ov[3]);
+  }
+  const double t = block_sum(acc, sh);
+  if (threadIdx.x == 0) part[blockIdx.x] = t;
+}
+
 // Rademacher probes from a counter-based generator: V[col][i] = +-1 from splitmix64(seed, col*n + i)
 __global__ void rademacher_kernel(unsigned long long seed, long n, int m, double* __restrict__ V) {
   long q = (long)blockIdx.x * blockDim.x + threadIdx.x;
