@@ -285,7 +285,7 @@ static void cg_iteration(kgp_ctx* c, GridState* g, const CgLaunch& L, cudaStream
     else {
     int TA = (G.ng[0] + 31) & ~31; if (TA > 256) TA = 256;
     const size_t ksm = (size_t)(KRON2_THREADS / TA + 1) * G.ng[0] * 8;
-    kron2_kernel<<<dim3((unsigned)G.ng[1], (unsigned)L.m), KRON2_THREADS, ksm, st>>>(L.KfT, L.Kf + L.koff1, G.ng[0], G.ng[1], L.gm0, L.gm1, L.ctl);
+    kron2_kernel<<<dim3((unsigned)G.ng[1], (unsigned)L.m), KRON2_THREADS, ksm, st>>>(L.KfT, L.Kf + L.koff1, G.ng[0], G.ng[1], L.gm0, L.gm1, L.ctl, G.N);
     }
     u = L.gm1;
     cg_gather_kernel<2><<<grid, 256, 0, st>>>(G, L.U, L.n, L.npad, u, L.sd, L.sz, L.ctl, L.cnt);
@@ -770,10 +770,8 @@ static int cheby_logdet(kgp_ctx* c, GridState* g, const GridDesc& G, int slot, d
     g->probes_n = n; g->probes_m = m;
   }
   long ksz = 0; for (int q = 0; q < G.p; ++q) ksz += (long)G.ng[q] * G.ng[q];
-  KGP_CUDA(c, g->chT.ensure((size_t)d * G.N * 8)); KGP_CUDA(c, g->chU.ensure((size_t)d * G.N * 8));
-  KGP_CUDA(c, g->chY.ensure((size_t)d * G.N * 8)); KGP_CUDA(c, g->chS.ensure((size_t)d * d * 8));
+
   KGP_CUDA(c, g->chC.ensure((size_t)2 * d * d * 8)); KGP_CUDA(c, g->chP.ensure((size_t)ksz * 8));
-  KGP_CUDA(c, g->chZ.ensure((size_t)d * G.N * 8)); KGP_CUDA(c, g->chZ2.ensure((size_t)d * G.N * 8));
   KGP_CUDA(c, g->chacc.ensure(64));
   // the recurrence runs on the cell-sorted point set of the CG path when there is one (1-D / 2-D equispaced grids, all rows
   // of the slot active): sorted_scatter_kernel / cheby_step_sorted_kernel; otherwise on the points as given
@@ -781,10 +779,28 @@ static int cheby_logdet(kgp_ctx* c, GridState* g, const GridDesc& G, int slot, d
   bool sorted = sorted_ok && G.p <= 2 && !g->any_neq && g->sub_n < 0;
   if (sorted) { int rc = cg_prepare_sorted(c, g, G, slot); if (rc) return rc; sorted = g->sub_n < 0 && g->npad >= n; }
   const long nv = sorted ? g->npad : n;                                     // length of a Krylov vector
-  KGP_CUDA(c, g->bva.ensure(nv * 8)); KGP_CUDA(c, g->bvb.ensure(nv * 8)); KGP_CUDA(c, g->bvs.ensure(nv * 8));
+  // probes of this rank; on the sorted set MB of them advance together (blockIdx.y): the grid-sized middle of a step
+  // (memset, Kronecker product, scalar accumulation) is launch latency, shared by the batch
+  int lo = 0, hi = m;
+  if (c->nranks > 1) { const int base = m / c->nranks, extra = m % c->nranks; lo = c->rank * base + std::min(c->rank, extra); hi = lo + base + (c->rank < extra ? 1 : 0); }
+  static const int mb_env = getenv("KGP_CHEBY_BATCH") ? atoi(getenv("KGP_CHEBY_BATCH")) : 8;
+  int MB = sorted ? std::max(1, std::min(std::min(mb_env, 16), hi - lo)) : 1;
+  while (MB > 1 && (size_t)MB * nv * 8 * 3 > ((size_t)3 << 29)) MB /= 2;     // three vector buffers: keep them under 1.5 GB
+  KGP_CUDA(c, g->chT.ensure((size_t)MB * d * G.N * 8)); KGP_CUDA(c, g->chU.ensure((size_t)MB * d * G.N * 8));
+  KGP_CUDA(c, g->bva.ensure((size_t)MB * nv * 8)); KGP_CUDA(c, g->bvb.ensure((size_t)MB * nv * 8)); KGP_CUDA(c, g->bvs.ensure((size_t)MB * nv * 8));
   const int nb = nblocks_for(n);
+  KGP_CUDA(c, g->partA.ensure((size_t)std::max(2048, MB * nb) * 8));
+  const long gst = (long)d * G.N;                                           // grid vectors of one probe: [d][N]
+  KGP_CUDA(c, g->chY.ensure((size_t)MB * gst * 8)); KGP_CUDA(c, g->chS.ensure((size_t)MB * d * d * 8));
+  KGP_CUDA(c, g->chZ.ensure((size_t)MB * gst * 8)); KGP_CUDA(c, g->chZ2.ensure((size_t)MB * gst * 8));
+  KGP_CUDA(c, g->partB.ensure((size_t)2048 * 8));
+  auto dot_to = [&](const double* a, const double* b2, long cnt, double* out) {   // out[0] = a.b, two-stage (deterministic)
+    const int nbd = (int)std::min<long>(std::max<long>((cnt + 1023) / 1024, 1), 1184);
+    dot_part_kernel<<<nbd, 256, 0, st>>>(a, b2, cnt, g->partB.d());
+    sum_small_kernel<<<1, 256, 0, st>>>(g->partB.d(), nbd, out);
+  };
   const bool k2 = G.p == 2 && std::max(G.ng[0], G.ng[1]) < 192;
-  auto apply_step = [&](const double* bv, const double* v, double c1, double c2, double* Tj, double* Uj, double* out) {
+  auto apply_step = [&](const double* bv, const double* v, double c1, double c2, double* Tj, double* Uj, double* out, int mb) {
     if (!sorted) {
       scatter(c, G, S.X.d(), n, D, bv, sw, Tj);                             // T = Mx'(sW bv)
       kron_to(c, g, G, Tj, Uj, -1);                                         // U = Kg T
@@ -794,24 +810,29 @@ static int cheby_logdet(kgp_ctx* c, GridState* g, const GridDesc& G, int slot, d
       c->stats.kernel_launches += 1;
       return;
     }
-    cudaMemsetAsync(Tj, 0, G.N * 8, st);
-    if (G.p == 1) sorted_scatter_kernel<1><<<nb, 256, 0, st>>>(G, g->U.d(), g->npad, bv, sw, Tj);
-    else sorted_scatter_kernel<2><<<nb, 256, 0, st>>>(G, g->U.d(), g->npad, bv, sw, Tj);
-    if (G.p == 1) mode_product_kernel<<<(unsigned)((G.N + 255) / 256), 256, 0, st>>>(g->Kf.d(), G.ng[0], Tj, Uj, 1, 1);
-    else if (k2) {
+    // (the T_j of the batch were zeroed together before the recurrence; mb = 1 callers zero theirs)
+    const dim3 gp((unsigned)nb, (unsigned)mb);
+    if (G.p == 1) sorted_scatter_kernel<1><<<gp, 256, 0, st>>>(G, g->U.d(), g->npad, bv, sw, Tj, nv, gst);
+    else sorted_scatter_kernel<2><<<gp, 256, 0, st>>>(G, g->U.d(), g->npad, bv, sw, Tj, nv, gst);
+    if (G.p == 1) {
+      for (int i = 0; i < mb; ++i)
+        mode_product_kernel<<<(unsigned)((G.N + 255) / 256), 256, 0, st>>>(g->Kf.d(), G.ng[0], Tj + i * gst, Uj + i * gst, 1, 1);
+    } else if (k2) {
       int TA = (G.ng[0] + 31) & ~31; if (TA > 256) TA = 256;
       const size_t ksm = (size_t)(KRON2_THREADS / TA + 1) * G.ng[0] * 8;
-      kron2_kernel<<<dim3((unsigned)G.ng[1], 1), KRON2_THREADS, ksm, st>>>(g->KfT.d(), g->Kf.d() + g->koff[1], G.ng[0], G.ng[1], Tj, Uj, nullptr);
-    } else kron_to(c, g, G, Tj, Uj, -1);
-    if (G.p == 1) cheby_step_sorted_kernel<1><<<nb, 256, 0, st>>>(G, g->U.d(), n, g->npad, Uj, bv, v, c1, c2, out, g->partA.d());
-    else cheby_step_sorted_kernel<2><<<nb, 256, 0, st>>>(G, g->U.d(), n, g->npad, Uj, bv, v, c1, c2, out, g->partA.d());
+      kron2_kernel<<<dim3((unsigned)G.ng[1], (unsigned)mb), KRON2_THREADS, ksm, st>>>(g->KfT.d(), g->Kf.d() + g->koff[1], G.ng[0], G.ng[1], Tj, Uj, nullptr, gst);
+    } else {
+      for (int i = 0; i < mb; ++i) kron_to(c, g, G, Tj + i * gst, Uj + i * gst, -1);
+    }
+    if (G.p == 1) cheby_step_sorted_kernel<1><<<gp, 256, 0, st>>>(G, g->U.d(), n, g->npad, Uj, bv, v, c1, c2, out, g->partA.d(), nv, gst);
+    else cheby_step_sorted_kernel<2><<<gp, 256, 0, st>>>(G, g->U.d(), n, g->npad, Uj, bv, v, c1, c2, out, g->partA.d(), nv, gst);
     c->stats.kernel_launches += 3;
   };
-  // probe i in the order the recurrence works in
-  auto probe_vec = [&](int i) -> const double* {
+  // probes i .. i+mb-1 in the order the recurrence works in
+  auto probe_vec = [&](int i, int mb) -> const double* {
     const double* v = g->probes.d() + (long)i * n;
     if (!sorted) return v;
-    permute_in_kernel<<<nb, 256, 0, st>>>(v, (const int*)g->perm.p, n, g->npad, g->bvs.d());
+    permute_in_kernel<<<dim3((unsigned)nb, (unsigned)mb), 256, 0, st>>>(v, (const int*)g->perm.p, n, g->npad, g->bvs.d());
     return g->bvs.d();
   };
   // ---- emax: injected, or power iteration on B = I + sW K sW   (the reference: eigs(B,1,'lm'), apx.m:344-350)
@@ -819,12 +840,13 @@ static int cheby_logdet(kgp_ctx* c, GridState* g, const GridDesc& G, int slot, d
   if (!(emax > 0.0)) {
     const int its = mo.opt.ldB2_cheby_maxit > 0 ? mo.opt.ldB2_cheby_maxit : 50;
     double nrm2 = (double)n, lam = 1.0;
-    KGP_CUDA(c, cudaMemcpyAsync(g->bva.p, probe_vec(0), nv * 8, cudaMemcpyDeviceToDevice, st));
+    KGP_CUDA(c, cudaMemcpyAsync(g->bva.p, probe_vec(0, 1), nv * 8, cudaMemcpyDeviceToDevice, st));
     double* cur = g->bva.d(); double* nxt = g->bvb.d();
     for (int it = 0; it < its; ++it) {
-      apply_step(cur, cur, 1.0, sw, g->chT.d(), g->chU.d(), nxt);            // nxt = B cur ; partials of cur.nxt
+      if (sorted) cudaMemsetAsync(g->chT.p, 0, G.N * 8, st);
+      apply_step(cur, cur, 1.0, sw, g->chT.d(), g->chU.d(), nxt, 1);         // nxt = B cur ; partials of cur.nxt
       sum_small_kernel<<<1, 256, 0, st>>>(g->partA.d(), nb, g->chacc.d() + 2);
-      dot_kernel<<<1, 1024, 0, st>>>(nxt, nxt, n, g->chacc.d() + 3);
+      dot_to(nxt, nxt, n, g->chacc.d() + 3);
       double h2[2];
       KGP_CUDA(c, cudaMemcpyAsync(h2, g->chacc.d() + 2, 16, cudaMemcpyDeviceToHost, st));
       KGP_CUDA(c, cudaStreamSynchronize(st));
@@ -867,37 +889,38 @@ static int cheby_logdet(kgp_ctx* c, GridState* g, const GridDesc& G, int slot, d
   KGP_CUDA(c, cudaMemcpyAsync(g->chC.p, hC.data(), hC.size() * 8, cudaMemcpyHostToDevice, st));
   KGP_CUDA(c, cudaMemsetAsync(g->chP.p, 0, ksz * 8, st));
   KGP_CUDA(c, cudaMemsetAsync(g->chacc.p, 0, 64, st));
-  // ---- probes of this rank
-  int lo = 0, hi = m;
-  if (c->nranks > 1) { const int base = m / c->nranks, extra = m % c->nranks; lo = c->rank * base + std::min(c->rank, extra); hi = lo + base + (c->rank < extra ? 1 : 0); }
-  for (int i = lo; i < hi; ++i) {
-    const double* v = probe_vec(i);
-    dot_kernel<<<1, 1024, 0, st>>>(v, v, n, g->chacc.d() + 2);
+  // ---- probes of this rank, MB at a time
+  for (int i0 = lo; i0 < hi; i0 += MB) {
+    const int mb = std::min(MB, hi - i0);
+    const double* v = probe_vec(i0, mb);
+    dot_to(v, v, sorted ? (long)mb * nv : n, g->chacc.d() + 2);                                          // (padding entries are zero)
     sum_scaled_acc_kernel<<<1, 256, 0, st>>>(g->chacc.d() + 2, 1, pp[0] / (2.0 * m), g->chacc.d());      // j = 0 term: v'v p_0
+    if (sorted) KGP_CUDA(c, cudaMemsetAsync(g->chT.p, 0, (size_t)mb * gst * 8, st));
     const double* cur = v; double* bufs[2] = {g->bva.d(), g->bvb.d()};
     for (int j = 0; j < d; ++j) {
       double* nxt = bufs[j & 1];
-      apply_step(cur, v, sf - cI, sf * sw, g->chT.d() + (long)j * G.N, g->chU.d() + (long)j * G.N, nxt);   // Bs cur
-      sum_scaled_acc_kernel<<<1, 256, 0, st>>>(g->partA.d(), nb, pp[j + 1] / (2.0 * m), g->chacc.d());
+      apply_step(cur, v, sf - cI, sf * sw, g->chT.d() + (long)j * G.N, g->chU.d() + (long)j * G.N, nxt, mb);   // Bs cur
+      sum_scaled_acc_kernel<<<1, 256, 0, st>>>(g->partA.d(), nb * mb, pp[j + 1] / (2.0 * m), g->chacc.d());
       cur = nxt;
     }
     c->stats.kernel_launches += 2 + d;
     if (want_deriv) {
-      gram_small_kernel<<<dim3(d, d), 256, 0, st>>>(g->chT.d(), g->chU.d(), G.N, d, g->chS.d());
-      dot_kernel<<<1, 1024, 0, st>>>(g->chS.d(), g->chC.d() + (long)d * d, (long)d * d, g->chacc.d() + 2);
+      // the whole batch at once: [mb][d][N] contiguous is mb d times as many outer slices of every mode
+      const int nd = mb * d;
+      gram_small_kernel<<<dim3(d, d, mb), 256, 0, st>>>(g->chT.d(), g->chU.d(), G.N, d, g->chS.d());
+      dot_tiled_kernel<<<1, 1024, 0, st>>>(g->chS.d(), g->chC.d() + (long)d * d, d * d, mb, g->chacc.d() + 2);
       sum_scaled_acc_kernel<<<1, 256, 0, st>>>(g->chacc.d() + 2, 1, 1.0, g->chacc.d() + 1);
-      mix_small_kernel<<<dim3((unsigned)((G.N + 255) / 256), d), 256, 0, st>>>(g->chT.d(), g->chC.d(), G.N, d, g->chY.d());
+      mix_small_kernel<<<dim3((unsigned)((G.N + 255) / 256), d, mb), 256, 0, st>>>(g->chT.d(), g->chC.d(), G.N, d, g->chY.d());
       for (int f = 0; f < G.p; ++f) {
-        // all d mixed vectors at once: [d][N] contiguous is the same as d times as many outer slices of every mode
         const double* src = g->chY.d(); double* zb[2] = {g->chZ.d(), g->chZ2.d()}; int bi = 0;
         for (int dd = 0; dd < G.p; ++dd) {
           if (dd == f) continue;
-          const long in2 = G.stride[dd], out2 = G.N / (in2 * G.ng[dd]) * d;
-          mode_product_kernel<<<(unsigned)(((long)d * G.N + 255) / 256), 256, 0, st>>>(g->Kf.d() + g->koff[dd], G.ng[dd], src, zb[bi], in2, out2);
+          const long in2 = G.stride[dd], out2 = G.N / (in2 * G.ng[dd]) * nd;
+          mode_product_kernel<<<(unsigned)(((long)nd * G.N + 255) / 256), 256, 0, st>>>(g->Kf.d() + g->koff[dd], G.ng[dd], src, zb[bi], in2, out2);
           src = zb[bi]; bi ^= 1; c->stats.kernel_launches++;
         }
-        const long inner = G.stride[f], outer = G.N / (inner * G.ng[f]) * d;
-        mode_gram_acc_kernel<<<dim3(G.ng[f], G.ng[f]), 128, 0, st>>>(src, g->chT.d(), G.ng[f], inner, outer, g->chP.d() + g->koff[f]);
+        const long inner = G.stride[f], outer = G.N / (inner * G.ng[f]) * nd;
+        mode_gram_acc_kernel<<<dim3(G.ng[f], G.ng[f]), 256, 0, st>>>(src, g->chT.d(), G.ng[f], inner, outer, g->chP.d() + g->koff[f]);
       }
       c->stats.kernel_launches += 4 + G.p;
     }

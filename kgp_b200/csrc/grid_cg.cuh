@@ -421,12 +421,11 @@ __global__ void __launch_bounds__(256) cg_update_kernel(long npad, double* __res
 //   W[a'] = sum_b' K2[b][b'] T[b'][a'] ;  out[b][a] = sum_a' K1[a][a'] W[a']   (K1T = K1 transposed)
 constexpr int KRON2_THREADS = 1024;
 __global__ void __launch_bounds__(KRON2_THREADS) kron2_kernel(const double* __restrict__ K1T, const double* __restrict__ K2, int ng0, int ng1,
-    const double* __restrict__ T, double* __restrict__ out, const double* __restrict__ ctl) {
+    const double* __restrict__ T, double* __restrict__ out, const double* __restrict__ ctl, long col_stride) {
   extern __shared__ double ksh[];                      // [nparts][ng0] partials + [ng0] W
   const int col = blockIdx.y;
   if (ctl && ctl[col * CT_STRIDE + CT_DONE] != 0.0) return;
-  const long N = (long)ng0 * ng1;
-  T += (long)col * N; out += (long)col * N;
+  T += (long)col * col_stride; out += (long)col * col_stride;   // column = blockIdx.y (right-hand sides of a batched solve, probes)
   const int b = blockIdx.x;
   int TA = (ng0 + 31) & ~31; if (TA > 256) TA = 256;
   const int nparts = KRON2_THREADS / TA, part = threadIdx.x / TA, ta = threadIdx.x - part * TA;

@@ -42,15 +42,18 @@ __global__ void cheby_step_kernel(GridDesc G, const double* __restrict__ X, long
 // scatter is the segmented one of cg_scatter_kernel -- one flush per run of equal cells instead of 16 atomics per point on
 // 4900 hot nodes -- and the gather reads a cell's 4^P node values once per run.  Per step at n = 1M: ~200 us -> ~35 us.
 // vs[k] = v[perm[k]] (k < n), 0 on the padding
+// (blockIdx.y = probe of the batch in all three kernels: vectors v + col * vstride, grid vectors g + col * gstride)
 __global__ void permute_in_kernel(const double* __restrict__ v, const int* __restrict__ perm, long n, long npad, double* __restrict__ vs) {
+  v += (long)blockIdx.y * n; vs += (long)blockIdx.y * npad;
   for (long k = (long)blockIdx.x * blockDim.x + threadIdx.x; k < npad; k += (long)gridDim.x * blockDim.x) vs[k] = (k < n) ? v[perm[k]] : 0.0;
 }
 // g0 += Mx'(sw v), v in sorted order (padding entries are zero)
 template <int P>
 __global__ void __launch_bounds__(256, 3) sorted_scatter_kernel(GridDesc G, const double* __restrict__ U, long npad,
-    const double* __restrict__ v, double sw, double* __restrict__ g0) {
+    const double* __restrict__ v, double sw, double* __restrict__ g0, long vstride, long gstride) {
   constexpr int NW = CgNodes<P>::NW;
   const int lane = threadIdx.x & 31;
+  v += (long)blockIdx.y * vstride; g0 += (long)blockIdx.y * gstride;
   const long nunits = npad / (32 * CG_PTS), nwarps = (long)gridDim.x * (blockDim.x >> 5);
   for (long unit = (long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); unit < nunits; unit += nwarps) {
     const long base = unit * (32 * CG_PTS) + (long)lane * CG_PTS;
@@ -114,10 +117,12 @@ __global__ void __launch_bounds__(256, 3) sorted_scatter_kernel(GridDesc G, cons
 template <int P>
 __global__ void __launch_bounds__(256, 3) cheby_step_sorted_kernel(GridDesc G, const double* __restrict__ U, long n, long npad,
     const double* __restrict__ ug, const double* __restrict__ bv, const double* __restrict__ v, double c1, double c2,
-    double* __restrict__ out, double* __restrict__ part) {
+    double* __restrict__ out, double* __restrict__ part, long vstride, long gstride) {
   constexpr int NW = CgNodes<P>::NW;
   __shared__ double sh[32];
   double acc = 0.0;
+  ug += (long)blockIdx.y * gstride; bv += (long)blockIdx.y * vstride; v += (long)blockIdx.y * vstride; out += (long)blockIdx.y * vstride;
+  part += (long)blockIdx.y * gridDim.x;
   const long nunits = npad / (32 * CG_PTS), nwarps = (long)gridDim.x * (blockDim.x >> 5);
   for (long unit = (long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); unit < nunits; unit += nwarps) {
     const long base = unit * (32 * CG_PTS) + (long)(threadIdx.x & 31) * CG_PTS;
@@ -176,6 +181,23 @@ __global__ void __launch_bounds__(256, 3) cheby_step_sorted_kernel(GridDesc G, c
   if (threadIdx.x == 0) part[blockIdx.x] = t;
 }
 
+// part[block] = sum over the block's grid-stride share of a .* b  (a one-CTA dot over 10^6..10^7 entries costs 0.1 - 1 ms)
+__global__ void dot_part_kernel(const double* __restrict__ a, const double* __restrict__ b, long n, double* __restrict__ part) {
+  __shared__ double sh[32];
+  double acc = 0.0;
+  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long)gridDim.x * blockDim.x) acc = fma(a[i], b[i], acc);
+  const double t = block_sum(acc, sh);
+  if (threadIdx.x == 0) part[blockIdx.x] = t;
+}
+// out[0] = sum_i S[i mod cnt? no: S is [reps][cnt]] : out = sum_r sum_k S[r][k] C[k]   (bilinear form summed over the batch)
+__global__ void dot_tiled_kernel(const double* __restrict__ S, const double* __restrict__ C, int cnt, int reps, double* __restrict__ out) {
+  __shared__ double sh[32];
+  double acc = 0.0;
+  for (int q = threadIdx.x; q < cnt * reps; q += blockDim.x) acc = fma(S[q], C[q % cnt], acc);
+  const double t = block_sum(acc, sh);
+  if (threadIdx.x == 0) out[0] = t;
+}
+
 // Rademacher probes from a counter-based generator: V[col][i] = +-1 from splitmix64(seed, col*n + i)
 __global__ void rademacher_kernel(unsigned long long seed, long n, int m, double* __restrict__ V) {
   long q = (long)blockIdx.x * blockDim.x + threadIdx.x;
@@ -189,6 +211,7 @@ __global__ void rademacher_kernel(unsigned long long seed, long n, int m, double
 __global__ void gram_small_kernel(const double* __restrict__ T, const double* __restrict__ U, long N, int d, double* __restrict__ S) {
   __shared__ double sh[32];
   const int a = blockIdx.x, b = blockIdx.y;
+  T += (long)blockIdx.z * d * N; U += (long)blockIdx.z * d * N; S += (long)blockIdx.z * d * d;      // blockIdx.z = probe of the batch
   double acc = 0.0;
   for (long q = threadIdx.x; q < N; q += blockDim.x) acc = fma(T[(long)a * N + q], U[(long)b * N + q], acc);
   const double t = block_sum(acc, sh);
@@ -200,6 +223,7 @@ __global__ void mix_small_kernel(const double* __restrict__ T, const double* __r
   long q = (long)blockIdx.x * blockDim.x + threadIdx.x;
   const int s = blockIdx.y;
   if (q >= N) return;
+  T += (long)blockIdx.z * d * N; Y += (long)blockIdx.z * d * N;                                      // blockIdx.z = probe of the batch
   double acc = 0.0;
   for (int u = 0; u < d; ++u) acc = fma(C[u * d + s], T[(long)u * N + q], acc);
   Y[(long)s * N + q] = acc;
