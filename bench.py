@@ -240,7 +240,7 @@ def kissgp_leg(n, device, steps, warmup, with_cpu=True):
         st = gpf.stats(); fms += st['ms_total']; fcg += st['ms_solve']; fit_ += st['cg_iters'] - 1; fiters.append(int(st['cg_iters']))
     fp_atomics = {'value': steps * 1e3 / fms, 'unit': 'evals/s', 'ms_per_eval': fms / steps, 'cg_us_per_iteration': 1e3 * fcg / max(fit_, 1),
                   'cg_iterations_seen': fiters, 'rel_diff_nlZ_vs_deterministic': abs(nlZf - nlZ) / abs(nlZ),
-                  'note': 'opt.cg_deterministic=0: one FP64 RED per flush instead of two integer REDs; iteration counts vary from run to run'}
+                  'note': 'opt.cg_deterministic=0: FP64 REDs instead of the order-independent fixed-point integer REDs; iteration counts vary from run to run'}
     del gpf
     # same problem through the grid-space Woodbury preconditioner (opt.cg_precond, an extension: SURVEY a21(i)); same
     # stopping rule, so the result is the same alpha to cg_tol -- only the iteration count changes
