@@ -158,6 +158,12 @@ int kgp_grid_set_toeplitz(kgp_ctx* ctx, int n_axes, const int* flags);
 /* GPML's equi() test for one axis (GPML/cov/apxGrid.m:684-695): 1 when max|diff(a) - (a[1]-a[0])| < 1e-9 and the axis
  * increases.  Axes that fail it but increase take the linear neqinterp branch (apxGrid.m:541-557).  Host logic, no GPU. */
 int kgp_grid_axis_equispaced(const double* axis, int len);
+/* The clustering step of covGrid('create', x, 0, k) (GPML/cov/apxGrid.m:411 "[idx,xgj] = kmeans(u, min(numel(u),ngj-2))") for
+ * one axis: u = the sorted unique values (ascending, nu of them), K clusters, centres written in increasing order.  Octave's
+ * kmeans() starts from random centres and cannot be reproduced; this is Lloyd's algorithm from an equal-count partition,
+ * deterministic.  kgp_grid_create(eq = 0) calls it per axis and adds the boundary nodes of apxGrid.m:412-415.  Host logic,
+ * no GPU.  Returns 0, or -1 on bad arguments (K < 1 or K > nu). */
+int kgp_kmeans1d_host(const double* u, long nu, long K, double* centres);
 int kgp_grid_get_host(kgp_ctx* ctx, int* n_axes, int* axis_len /* >= 16 ints */, double* axes_concat /* may be NULL */);
 
 /* Learned input projection hyp.proj (GPML/inf/infGrid.m:56-65,82-87,155-167; kgp/backend/utils/dlikGrid.m:13-22,

@@ -66,6 +66,7 @@ SIGNATURES = {
     'kgp_grid_set_host': (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]),
     'kgp_grid_set_toeplitz': (C.c_int, [C.c_void_p, C.c_int, C.c_void_p]),
     'kgp_grid_axis_equispaced': (C.c_int, [C.c_void_p, C.c_int]),
+    'kgp_kmeans1d_host': (C.c_int, [C.c_void_p, C.c_long, C.c_long, C.c_void_p]),
     'kgp_grid_get_host': (C.c_int, [C.c_void_p, C.POINTER(C.c_int), C.c_void_p, C.c_void_p]),
     'kgp_set_proj_host': (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int]),
     'kgp_predict_mean_noalloc_dev': (C.c_int, [C.c_void_p, C.c_void_p, C.c_long, C.c_void_p]),

@@ -16,6 +16,7 @@ int grid_dlik(kgp_ctx* c, int slot, double* out, bool out_is_dev);
 int grid_alpha(kgp_ctx* c, double* out);
 int grid_predict(kgp_ctx* c, const double* Xs, long ns, double* ymu, double* ys2, double* fmu, double* fs2);
 int grid_create(kgp_ctx* c, int slot, int eq, double k);
+int kmeans1d_host(const double* u, long nu, long K, double* cent);
 void grid_free(kgp_ctx* c);
 int grid_init(kgp_ctx* c);
 int grid_solve(kgp_ctx* c, int slot, const double* R, int m, double* out);
@@ -332,6 +333,7 @@ int kgp_grid_axis_equispaced(const double* a, int len) {
   for (int i = 1; i < len; ++i) { const double e = fabs((a[i] - a[i - 1]) - d0); if (e > dev || e != e) dev = e != e ? 1.0 : e; }
   return dev < 1e-9 ? 1 : 0;
 }
+int kgp_kmeans1d_host(const double* u, long nu, long K, double* centres) { return kmeans1d_host(u, nu, K, centres); }
 int kgp_grid_set_host(kgp_ctx* c, int n_axes, const int* axis_len, const double* axes) {
   if (!c || n_axes <= 0 || n_axes > 16 || !axis_len || !axes) return c ? c->fail(KGP_BAD_ARG, "bad grid") : KGP_BAD_ARG;
   long o = 0;

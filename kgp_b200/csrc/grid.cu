@@ -1558,14 +1558,41 @@ __global__ void count_unique_kernel(const double* __restrict__ key, long n, unsi
   if (i == 0 || key[i] != key[i - 1]) atomicAdd(cnt, 1ULL);     // integer count: order-independent
 }
 
+// 1-D k-means of the sorted unique values u (ascending) into K clusters, for covGrid('create', x, 0, k) (apxGrid.m:411).  The
+// reference calls kmeans() of Octave's statistics package, whose random initialisation cannot be reproduced; this is Lloyd's
+// algorithm from an equal-count initial partition, deterministic, every step in a fixed order of FP64 operations so that a
+// CPU restatement can agree to the last bit (the parity tests check that).  In one dimension the nearest-centroid rule is a set
+// of thresholds at the midpoints of neighbouring centroids; segment means come from sequential prefix sums.
+int kmeans1d_host(const double* u, long nu, long K, double* cent) {
+  if (!u || !cent || K < 1 || K > nu) return -1;
+  std::vector<double> S(nu + 1); S[0] = 0.0;
+  for (long i = 0; i < nu; ++i) S[i + 1] = S[i] + u[i];
+  std::vector<long> bnd(K + 1), nb(K + 1);
+  for (long cc = 0; cc <= K; ++cc) bnd[cc] = (cc * nu) / K;
+  for (long cc = 0; cc < K; ++cc) cent[cc] = (S[bnd[cc + 1]] - S[bnd[cc]]) / (double)(bnd[cc + 1] - bnd[cc]);
+  for (int it = 0; it < 200; ++it) {
+    nb[0] = 0; nb[K] = nu;
+    for (long cc = 0; cc + 1 < K; ++cc) {
+      const double mid = 0.5 * (cent[cc] + cent[cc + 1]);                  // a tie goes to the lower cluster
+      nb[cc + 1] = (long)(std::upper_bound(u, u + nu, mid) - u);
+      if (nb[cc + 1] < nb[cc]) nb[cc + 1] = nb[cc];
+    }
+    if (nb == bnd) break;
+    bnd = nb;
+    for (long cc = 0; cc < K; ++cc)
+      if (bnd[cc + 1] > bnd[cc]) cent[cc] = (S[bnd[cc + 1]] - S[bnd[cc]]) / (double)(bnd[cc + 1] - bnd[cc]);   // an emptied cluster keeps its centre
+  }
+  return 0;
+}
+
 int grid_create(kgp_ctx* c, int slot, int eq, double k) {
-  if (!eq) return c->fail(KGP_BAD_ARG, "covGrid('create') with eq=0 needs kmeans (statistics package); only eq=1 is built");
   GridState* g = gs(c); Slot& S = c->slots[slot];
   const long n = S.n; const int D = S.D;
   if (D > GRID_MAXP) return c->fail(KGP_BAD_ARG, "at most %d grid dimensions", GRID_MAXP);
   cudaStream_t st = c->stream;
   KGP_CUDA(c, g->out.ensure(64 * 8));
   std::vector<std::vector<double>> axes;
+  std::vector<double> uq;                             // sorted unique values of a column (eq = 0 only)
   for (int j = 0; j < D; ++j) {
     double mm[2];
     col_minmax_kernel<<<1, 1024, 0, st>>>(S.X.d(), n, D, j, g->out.d());
@@ -1573,7 +1600,8 @@ int grid_create(kgp_ctx* c, int slot, int eq, double k) {
     KGP_CUDA(c, cudaStreamSynchronize(st));
     if (!(mm[1] > mm[0])) return c->fail(KGP_BAD_ARG, "Two few unique points.");
     double ngj;                                       // stays fractional in du (apxGrid.m:404-406); only linspace floors it
-    if (k >= 0.0 && k <= 1.0) {                       // fraction of the unique values (apxGrid.m:402-403)
+    const bool frac = (k >= 0.0 && k <= 1.0);
+    if (frac || !eq) {                                // u = sort(unique(x(:,j))): descending bitonic sort, padding -inf at the end
       long Npad = 1; while (Npad < n) Npad <<= 1;
       KGP_CUDA(c, g->sortk.ensure(Npad * 8)); KGP_CUDA(c, g->sorti.ensure(Npad * 4));
       col_gather_kernel<<<(unsigned)((Npad + 255) / 256), 256, 0, st>>>(S.X.d(), n, D, j, g->sortk.d(), (int*)g->sorti.p, Npad);
@@ -1585,20 +1613,45 @@ int grid_create(kgp_ctx* c, int slot, int eq, double k) {
       count_unique_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(g->sortk.d(), n, cnt);
       unsigned long long hc = 0;
       KGP_CUDA(c, cudaMemcpyAsync(&hc, cnt, 8, cudaMemcpyDeviceToHost, st));
+      if (!eq) { uq.resize(n); KGP_CUDA(c, cudaMemcpyAsync(uq.data(), g->sortk.p, (size_t)n * 8, cudaMemcpyDeviceToHost, st)); }
       KGP_CUDA(c, cudaStreamSynchronize(st));
-      ngj = ceil(k * (double)hc);
+      ngj = frac ? ceil(k * (double)hc) : k;          // fraction of the unique values (apxGrid.m:402-403)
     } else ngj = k;
     if (!(ngj >= 1.0)) return c->fail(KGP_BAD_ARG, "bad grid size k=%g", k);
     const double du = (mm[1] - mm[0]) / ngj, b0 = mm[0] - 5.0 * du, b1 = mm[1] + 5.0 * du;
-    const long np_ = (long)floor(std::max(ngj, 5.0));  // Octave's linspace(a, b, n) uses floor(n) points
-    std::vector<double> ax(np_);                      // Octave linspace: base + i*delta, last point exact
-    const double delta = (b1 - b0) / (double)(np_ - 1);
-    for (long i = 0; i < np_; ++i) ax[i] = b0 + (double)i * delta;
-    ax[np_ - 1] = b1;
-    axes.push_back(ax);
+    auto linspace = [](double lo, double hi, long np_) {            // Octave linspace: base + i*delta, last point exact
+      std::vector<double> v(np_);
+      const double delta = (np_ > 1) ? (hi - lo) / (double)(np_ - 1) : 0.0;
+      for (long i = 0; i < np_; ++i) v[i] = lo + (double)i * delta;
+      if (np_ > 0) v[np_ - 1] = hi;
+      return v;
+    };
+    if (eq) {
+      axes.push_back(linspace(b0, b1, (long)floor(std::max(ngj, 5.0))));   // Octave's linspace(a, b, n) uses floor(n) points
+    } else {                                          // non-equispaced axis: cluster centres + boundary points (apxGrid.m:410-415)
+      std::reverse(uq.begin(), uq.end());
+      uq.erase(std::unique(uq.begin(), uq.end()), uq.end());
+      const long nu = (long)uq.size(), ngi = (long)floor(ngj);
+      const long K = std::min(nu, ngi - 2);
+      if (K < 1) return c->fail(KGP_BAD_ARG, "covGrid('create', x, 0, k): k=%g leaves no cluster centres (need k >= 3)", k);
+      std::vector<double> cent(K);
+      if (kmeans1d_host(uq.data(), nu, K, cent.data())) return c->fail(KGP_BAD_ARG, "kmeans failed");
+      const long nb = ngi - K, nb1 = nb / 2, nb2 = nb - nb1;
+      std::vector<double> x1 = linspace(b0, cent[0], nb1 + 1), x2 = linspace(cent[K - 1], b1, nb2 + 1), ax;
+      ax.insert(ax.end(), x1.begin(), x1.begin() + nb1);
+      ax.insert(ax.end(), cent.begin(), cent.end());
+      ax.insert(ax.end(), x2.begin() + 1, x2.end());
+      if (ax.size() < 4) return c->fail(KGP_BAD_ARG, "grid axis %d needs >= 4 points", j);
+      for (size_t i = 1; i < ax.size(); ++i)
+        if (!(ax[i] - ax[i - 1] >= 1e-10)) return c->fail(KGP_BAD_ARG, "k-means grid axis %d is not strictly increasing (an emptied cluster)", j);
+      axes.push_back(ax);
+    }
   }
   KGP_CUDA(c, cudaGetLastError());
-  c->grid.axes = axes; c->grid.toep.assign(axes.size(), 0); c->grid.neq.assign(axes.size(), 0); c->grid.set = true; c->grid.version++;
+  c->grid.axes = axes; c->grid.toep.assign(axes.size(), 0); c->grid.neq.assign(axes.size(), 0);
+  // interpgrid dispatches per axis on equi() (apxGrid.m:684-695): a k-means axis runs neqinterp unless it happens to be equispaced
+  if (!eq) for (size_t a = 0; a < axes.size(); ++a) c->grid.neq[a] = kgp_grid_axis_equispaced(axes[a].data(), (int)axes[a].size()) ? 0 : 1;
+  c->grid.set = true; c->grid.version++;
   return KGP_OK;
 }
 

@@ -4,7 +4,7 @@ NumPy/SciPy restatement of the reference's grid inference; parity checker for th
 CUDA engine and timed CPU baseline.  Nothing under kgp_b200/ may import it.
 
 Reference restated (GPML/ = kgp/backend/gpml/ of alshedivat/keras-gp):
-  grid creation      GPML/cov/apxGrid.m:389-416 (creategrid, eq=1 only)
+  grid creation      GPML/cov/apxGrid.m:389-416 (creategrid; eq=0: kmeans -> deterministic Lloyd stand-in, see kmeans1d)
   interpolation      GPML/cov/apxGrid.m:440-490 (interpgrid), 495-523 (eqinterp), 527-539 (kcub/dkcub)
   Kronecker MVM      GPML/cov/apxGrid.m:302-329 (kronmvm), dense factors (plain numeric axes)
   CG                 GPML/cov/apx.m:275-302 (conjgrad/linsolve), 218-226 (ldB2_grid)
@@ -26,13 +26,46 @@ from gpml_exact import mean_eval
 
 
 # ----------------------------------------------------------------------------
-# grid creation (apxGrid.m:389-416), eq = 1
+# grid creation (apxGrid.m:389-416)
 # ----------------------------------------------------------------------------
+def kmeans1d(u, K):
+    """Stand-in for `[idx,xgj] = kmeans(u, K)` (apxGrid.m:411) on the sorted unique values u.  Octave's kmeans (statistics
+    package) starts from random centres, so no implementation can reproduce its output; this is Lloyd's algorithm from an
+    equal-count initial partition (deterministic).  In 1-D the nearest-centre rule is a set of thresholds at the midpoints of
+    neighbouring centres (a tie goes to the lower cluster, as Octave's min does); segment means come from sequential prefix
+    sums, so the engine's host routine (kgp_kmeans1d_host) agrees to the last bit."""
+    u = np.asarray(u, dtype=np.float64)
+    nu = u.size
+    assert 1 <= K <= nu
+    S = np.concatenate([[0.0], np.cumsum(u)])          # sequential sums
+    bnd = [(c * nu) // K for c in range(K + 1)]
+    cent = [(S[bnd[c + 1]] - S[bnd[c]]) / float(bnd[c + 1] - bnd[c]) for c in range(K)]
+    for _ in range(200):
+        nb = [0] * (K + 1)
+        nb[K] = nu
+        for c in range(K - 1):
+            nb[c + 1] = max(int(np.searchsorted(u, 0.5 * (cent[c] + cent[c + 1]), side='right')), nb[c])
+        if nb == bnd:
+            break
+        bnd = nb
+        for c in range(K):
+            if bnd[c + 1] > bnd[c]:                    # an emptied cluster keeps its centre
+                cent[c] = (S[bnd[c + 1]] - S[bnd[c]]) / float(bnd[c + 1] - bnd[c])
+    return np.array(cent)
+
+
+def _linspace(lo, hi, n):
+    """Octave linspace: base + i*delta, the last point exact."""
+    v = lo + np.arange(n, dtype=np.float64) * ((hi - lo) / float(n - 1) if n > 1 else 0.0)
+    if n > 0:
+        v[-1] = hi
+    return v
+
+
 def creategrid(x, eq=1, k=1.0):
     x = np.asarray(x, dtype=np.float64)
     if x.ndim == 1:
         x = x[:, None]
-    assert eq, 'only equispaced grids (eq=1): eq=0 needs kmeans from the statistics package'
     xg = []
     for j in range(x.shape[1]):
         u = np.unique(x[:, j])
@@ -43,7 +76,15 @@ def creategrid(x, eq=1, k=1.0):
         else:
             ngj = float(k)                           # stays fractional in du (apxGrid.m:404-406)
         du = (u[-1] - u[0]) / ngj
-        xg.append(np.linspace(u[0] - 5 * du, u[-1] + 5 * du, int(np.floor(max(ngj, 5)))))   # Octave linspace floors n
+        bu = (u[0] - 5 * du, u[-1] + 5 * du)
+        if eq:
+            xg.append(np.linspace(bu[0], bu[1], int(np.floor(max(ngj, 5)))))   # Octave linspace floors n
+        else:                                        # apxGrid.m:410-415: cluster centres + boundary nodes
+            ngi = int(np.floor(ngj))
+            xgj = kmeans1d(u, min(u.size, ngi - 2))
+            nb = ngi - xgj.size; nb1 = nb // 2; nb2 = nb - nb1
+            xg1 = _linspace(bu[0], xgj[0], nb1 + 1); xg2 = _linspace(xgj[-1], bu[1], nb2 + 1)
+            xg.append(np.concatenate([xg1[:nb1], xgj, xg2[1:]]))
     return xg
 
 

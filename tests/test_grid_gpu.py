@@ -476,6 +476,47 @@ def test_non_equispaced_axes_vs_oracle(built_lib, shape):
     assert rel(ymu, gg.predict_grid(oh, ['meanZero'], 'covSEiso', xg, post, Xs)[2]) < 1e-7
 
 
+def test_kmeans_grid_eq0_vs_oracle(built_lib):
+    """SURVEY 8(f)-4, k-means grid: grid_kwargs eq = 0 -> covGrid('create', x, 0, k) (kgp/backend/gpml.py:29-31, apxGrid.m:410-415).
+    Octave's randomly initialised kmeans cannot be reproduced; engine and oracle share the deterministic Lloyd stand-in, so the
+    axes agree bit for bit, and the evaluation on them (neqinterp path) agrees at the usual tight-CG tolerances."""
+    import gpml_grid as gg
+    from kgp_b200 import B200GP, _cabi
+    rng = np.random.RandomState(8)
+    n = 1200
+    X = np.concatenate([rng.randn(n // 2, 2) * 0.25 + [0.3, 0.7], rng.rand(n - n // 2, 2)])     # clustered: a k-means grid differs from linspace
+    X = np.round(X, 4); X[5] = X[6]                                                             # duplicate values in a column
+    y = np.sin(4 * X[:, 0]) + X[:, 1] ** 2 + 0.1 * rng.randn(n)
+    Xs = rng.rand(70, 2) * 1.4 - 0.2
+    opt = {'cg_maxit': 8000, 'cg_tol': 1e-12}
+    gp = B200GP()
+    gp.configure(2, {'lik': np.log(0.1), 'mean': [], 'cov': [[np.log(0.3)], [0.0]]}, opt, 'infGrid', 'meanZero', 'covSEiso', 'likGauss',
+                 'dlikGrid', grid_kwargs={'eq': 0, 'k': 24.}, verbose=0)
+    gp.update_data('tr', X, y[:, None]); gp.update_grid('tr')
+    xg = gg.creategrid(X, 0, 24.)
+    ax = gp.grid()
+    assert len(ax) == 2 and all(a.size == 24 and np.array_equal(a, b) for a, b in zip(ax, xg))
+    assert not gg.equi(xg[0]) and not gg.equi(xg[1])
+    nlZ, g = gp.eng.eval(0, 2, gp._n_hyp)
+    dX = gp.get_dlik_dx('tr'); ymu = gp.predict(Xs)
+    hv = gp._hyp_vec(); nc = gp.hyp['cov'].size
+    oh = {'cov': hv[:nc], 'lik': gp.hyp['lik'], 'mean': []}
+    post, nlZ0, d0 = gg.inf_grid(oh, ['meanZero'], 'covSEiso', xg, X, y, opt)
+    g0 = np.concatenate([d0['cov'], [d0['lik']]])
+    assert rel(nlZ, nlZ0) < 1e-8 and rel(g, g0) < 1e-7 and rel(gp.alpha(), post['alpha']) < 1e-7
+    assert rel(dX, gg.dlik_grid(oh, ['meanZero'], 'covSEiso', xg, X, y, opt)) < 1e-7
+    assert rel(ymu, gg.predict_grid(oh, ['meanZero'], 'covSEiso', xg, post, Xs)[2]) < 1e-7
+    # a fractional k (share of the unique values) and a grid too small for any centre
+    gp.configure(2, {'lik': np.log(0.1), 'mean': [], 'cov': [[np.log(0.3)], [0.0]]}, opt, 'infGrid', 'meanZero', 'covSEiso', 'likGauss',
+                 'dlikGrid', grid_kwargs={'eq': 0, 'k': 0.02}, verbose=0)
+    gp.update_grid('tr')
+    assert all(np.array_equal(a, b) for a, b in zip(gp.grid(), gg.creategrid(X, 0, 0.02)))
+    gp.configure(2, {'lik': np.log(0.1), 'mean': [], 'cov': [[np.log(0.3)], [0.0]]}, opt, 'infGrid', 'meanZero', 'covSEiso', 'likGauss',
+                 'dlikGrid', grid_kwargs={'eq': 0, 'k': 2.}, verbose=0)
+    with pytest.raises(_cabi.KgpError):
+        gp.update_grid('tr')
+
+
 @pytest.mark.parametrize('kind,shape', [('covSEiso', '2d'), ('covSM', '2d'), ('covSEiso', '1d_1000'), ('covSM', 'both')])
 def test_toeplitz_factors_vs_oracle(built_lib, kind, shape):
     """Toeplitz grid factors (nested xg, apxGrid.m:258-281): Whittle-circulant Fiedler eigenvalues (apxGrid.m:576-580,

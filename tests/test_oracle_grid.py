@@ -358,3 +358,48 @@ def test_proj_gradient_matches_finite_differences(mode):
             return gg.inf_grid_proj(dict(hyp, proj=P), mean, 'covSEiso', xg, Xt, y, opt, mode=mode)[1]
         num = (fx(1e-5) - fx(-1e-5)) / 2e-5
         assert abs(num - dX[i, j]) < 2e-5 * max(1.0, np.max(np.abs(dX)))
+
+
+def test_kmeans_grid_eq0_structure_and_host_routine():
+    """covGrid('create', x, 0, k) (apxGrid.m:393-415): k-means centres of the unique values plus boundary nodes.  Octave's
+    kmeans is randomly initialised (not reproducible), so the deterministic Lloyd stand-in is checked by what defines a k-means
+    solution -- every value sits in the cluster of its nearest centre, every centre is its cluster's mean -- by the structure of
+    the axis the reference builds around it, and bit for bit against the engine's host routine (kgp_kmeans1d_host, no GPU)."""
+    import ctypes as C
+    from kgp_b200 import _cabi
+    rng = np.random.RandomState(11)
+    x = np.concatenate([rng.randn(300) * 0.2 - 2.0, rng.randn(500) * 0.5 + 1.0, rng.rand(100) * 6 - 3])[:, None]
+    x = np.round(x, 3)                                                  # duplicates: unique() matters
+    u = np.unique(x[:, 0])
+    for k in (12, 40, 0.05):
+        xg = gg.creategrid(x, 0, k)[0]
+        ngj = int(np.ceil(k * u.size)) if k <= 1 else int(k)
+        assert xg.size == ngj and np.all(np.diff(xg) > 0)
+        du = (u[-1] - u[0]) / ngj
+        assert xg[0] == u[0] - 5 * du and xg[-1] == u[-1] + 5 * du       # bu (apxGrid.m:407)
+        cent = xg[1:-1]                                                 # nb = 2: one boundary node per side
+        lab = np.argmin(np.abs(u[:, None] - cent[None, :]), axis=1)
+        assert np.all(np.diff(lab) >= 0)
+        for c in range(cent.size):
+            assert abs(u[lab == c].mean() - cent[c]) < 1e-12            # a fixed point of Lloyd's iteration
+        assert not gg.equi(xg)
+        out = np.zeros(cent.size)
+        rc = _cabi.lib().kgp_kmeans1d_host(u.ctypes.data_as(C.c_void_p), u.size, cent.size, out.ctypes.data_as(C.c_void_p))
+        assert rc == 0 and np.array_equal(out, cent)
+    # more clusters requested than unique values: every value is its own centre, the rest are boundary nodes (apxGrid.m:412-415)
+    xs = np.array([0.0, 1.0, 1.5, 4.0])[:, None]
+    xg = gg.creategrid(xs, 0, 9)[0]
+    assert xg.size == 9 and np.array_equal(xg[2:6], xs[:, 0]) and np.all(np.diff(xg) > 0)
+    assert _cabi.lib().kgp_kmeans1d_host(u.ctypes.data_as(C.c_void_p), 3, 4, out.ctypes.data_as(C.c_void_p)) == -1
+    # the oracle runs infGrid on such a grid (neqinterp path) and its gradient passes the finite-difference check
+    X = rng.rand(150, 2); y = np.sin(5 * X[:, 0]) + X[:, 1] + 0.1 * rng.randn(150)
+    xg2 = gg.creategrid(X, 0, 16)
+    hyp = {'cov': np.array([np.log(0.3), 0.0, np.log(0.4), 0.1]), 'lik': np.log(0.1), 'mean': []}
+    opt = {'cg_maxit': 3000, 'cg_tol': 1e-13}
+    _, nl, d = gg.inf_grid(hyp, ['meanZero'], 'covSEiso', xg2, X, y, opt)
+    for i in range(4):
+        hp = dict(hyp); hm = dict(hyp); e = np.zeros(4); e[i] = 1e-6
+        hp['cov'] = hyp['cov'] + e; hm['cov'] = hyp['cov'] - e
+        fd = (gg.inf_grid(hp, ['meanZero'], 'covSEiso', xg2, X, y, opt, want_grad=False)[1] -
+              gg.inf_grid(hm, ['meanZero'], 'covSEiso', xg2, X, y, opt, want_grad=False)[1]) / 2e-6
+        assert abs(fd - d['cov'][i]) < 1e-5 * max(1.0, abs(fd))
