@@ -684,7 +684,8 @@ def main():
                                    'nlZ + dnlZ + dnlZ/dX per step' % (n, D),
                        'l2': 'inputs larger than L2 (two %.1f GB matrices per step)' % (n * n * 8 / 1e9),
                        'parallelism': ('one problem sharded over %d GPUs: block-column Cholesky + NCCL panel broadcast, row-sharded '
-                                       'L^-T, tile-sharded B^-1 and gradient pass, all-reduce of the row sums' % world) if sharded
+                                       'L^-T gathered by peer copies under the sweep (P > 2) or pipelined broadcasts (P = 2), '
+                                       'tile-sharded B^-1 and gradient pass, all-reduce of the row sums' % world) if sharded
                                       else ('one independent GP per GPU (no collective)' if world > 1 else 'single GPU'),
                        'wall_s_timed_region': wall},
             'roofline': roofline, 'cpu_baseline': cpu,

@@ -78,6 +78,10 @@ struct kgp_ctx {
   cudaEvent_t dev_ev[8];                              // panel ready [2], panel buffer free [2], look-ahead column updated
   cudaEvent_t zev[8]; bool zpipe_active = false;      // "rank r's rows of Z = L^-T have arrived" (pipelined all-gather under Z Z^T)
   kgp::DevBuf PB[2];                                  // packed panels (rows x NB)
+  // pipelined all-gather of Z = L^-T by peer copies (exact.cu, zsweep_dist): every rank's W2 mapped into every peer with CUDA IPC;
+  // w2_mapped = the local allocation the peers hold a mapping of; one copy stream + event per peer; zbar = 8-byte all-reduce word
+  void* w2_peer[8] = {nullptr}; void* w2_mapped = nullptr; bool w2_push_ok = false;
+  cudaStream_t zstream[8] = {nullptr}; cudaEvent_t zpush_ev[8] = {nullptr}; cudaEvent_t zcol_ev = nullptr; double* zbar = nullptr;
   // peer exchange window of the row-sharded KISS-GP CG (grid_cg.cuh, CgDist): one cudaMalloc per rank, mapped into
   // every peer with CUDA IPC; px_epoch = tag of the last exchange (monotone over all solves, equal on all ranks)
   void* px_local = nullptr; void* px_peer[8] = {nullptr}; bool px_ok = false; unsigned long long px_epoch = 0;

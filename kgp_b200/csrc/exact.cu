@@ -262,10 +262,78 @@ void dist_free(kgp_ctx* c) {
   if (c->nccl_comm) { NcclApi& api = nccl_api(nullptr); if (api.ok) api.CommDestroy(c->nccl_comm); c->nccl_comm = nullptr; }
   if (c->stream_p) { cudaStreamDestroy(c->stream_p); for (int i = 0; i < 8; ++i) { cudaEventDestroy(c->dev_ev[i]); cudaEventDestroy(c->zev[i]); } c->stream_p = nullptr; }
   c->PB[0].release(); c->PB[1].release();
+  for (int r = 0; r < 8; ++r) {
+    if (c->w2_peer[r] && r != c->rank) cudaIpcCloseMemHandle(c->w2_peer[r]);
+    c->w2_peer[r] = nullptr;
+    if (c->zstream[r]) { cudaStreamDestroy(c->zstream[r]); c->zstream[r] = nullptr; }
+    if (c->zpush_ev[r]) { cudaEventDestroy(c->zpush_ev[r]); c->zpush_ev[r] = nullptr; }
+  }
+  if (c->zcol_ev) { cudaEventDestroy(c->zcol_ev); c->zcol_ev = nullptr; }
+  if (c->zbar) { cudaFree(c->zbar); c->zbar = nullptr; }
+  c->w2_mapped = nullptr; c->w2_push_ok = false;
   for (int r = 0; r < 8; ++r) { if (c->px_peer[r] && c->px_peer[r] != c->px_local) cudaIpcCloseMemHandle(c->px_peer[r]); c->px_peer[r] = nullptr; }
   if (c->px_local) { cudaFree(c->px_local); c->px_local = nullptr; }
   if (c->px_abort) { cudaFree(c->px_abort); c->px_abort = nullptr; }
   c->px_ok = false;
+}
+
+// host-synchronous sum of one double over the ranks (set-up decisions every rank must take alike)
+static int dist_allreduce_host(kgp_ctx* c, double* v) {
+  NcclApi& api = nccl_api(nullptr);
+  if (!c->zbar) KGP_CUDA(c, cudaMalloc((void**)&c->zbar, 64));
+  KGP_CUDA(c, cudaMemcpyAsync(c->zbar, v, 8, cudaMemcpyHostToDevice, c->stream));
+  KGP_NCCL(c, api, api.AllReduce(c->zbar, c->zbar, 1, KGP_NCCL_DOUBLE, KGP_NCCL_SUM, c->nccl_comm, c->stream));
+  KGP_CUDA(c, cudaMemcpyAsync(v, c->zbar, 8, cudaMemcpyDeviceToHost, c->stream));
+  KGP_CUDA(c, cudaStreamSynchronize(c->stream));
+  return KGP_OK;
+}
+// Z's all-gather runs as peer copies straight into the other ranks' W2 (zsweep_dist), so every rank needs a mapping of every
+// peer's W2.  Called at the start of an evaluation, collectively, BEFORE W2 may be (re)allocated: if any rank is about to
+// reallocate, or holds an allocation its peers have not mapped, every rank closes its mappings first (an exporter must not free
+// memory a peer still maps), then allocates, then the IPC handles are exchanged over the communicator.  Steady state: one 8-byte
+// all-reduce per evaluation.  On failure (no peer access) the broadcast all-gather stays in use -- decided alike on all ranks.
+static int w2_peer_sync(kgp_ctx* c, size_t need_bytes) {
+  NcclApi& api = nccl_api(nullptr);
+  const int P = c->nranks, me = c->rank;
+  double flag = (need_bytes > c->W2.bytes || !c->W2.p || c->W2.p != c->w2_mapped) ? 1.0 : 0.0;
+  int rc = dist_allreduce_host(c, &flag); if (rc) return rc;
+  if (flag == 0.0) return KGP_OK;
+  for (int r = 0; r < P; ++r) { if (c->w2_peer[r] && r != me) cudaIpcCloseMemHandle(c->w2_peer[r]); c->w2_peer[r] = nullptr; }
+  c->w2_mapped = nullptr; c->w2_push_ok = false;
+  double zero = 0.0;
+  rc = dist_allreduce_host(c, &zero); if (rc) return rc;          // every rank has closed its mappings: owners may free now
+  KGP_CUDA(c, c->W2.ensure(need_bytes));
+  cudaIpcMemHandle_t mine; char* hdev = nullptr; std::vector<cudaIpcMemHandle_t> all(P);
+  bool ok = cudaIpcGetMemHandle(&mine, c->W2.p) == cudaSuccess && cudaMalloc((void**)&hdev, (size_t)P * sizeof(mine)) == cudaSuccess;
+  double okall = ok ? 1.0 : 0.0;
+  rc = dist_allreduce_host(c, &okall); if (rc) { if (hdev) cudaFree(hdev); return rc; }
+  if (okall > (double)P - 0.5) {
+    cudaMemcpy(hdev + (size_t)me * sizeof(mine), &mine, sizeof(mine), cudaMemcpyHostToDevice);
+    for (int r = 0; r < P && ok; ++r)
+      ok = api.Broadcast(hdev + (size_t)r * sizeof(mine), hdev + (size_t)r * sizeof(mine), sizeof(mine), KGP_NCCL_INT8, r, c->nccl_comm, c->stream) == 0;
+    ok = ok && cudaStreamSynchronize(c->stream) == cudaSuccess &&
+         cudaMemcpy(all.data(), hdev, (size_t)P * sizeof(mine), cudaMemcpyDeviceToHost) == cudaSuccess;
+    for (int r = 0; r < P && ok; ++r) {
+      if (r == me) { c->w2_peer[r] = c->W2.p; continue; }
+      ok = cudaIpcOpenMemHandle(&c->w2_peer[r], all[r], cudaIpcMemLazyEnablePeerAccess) == cudaSuccess;
+      if (!ok) c->w2_peer[r] = nullptr;
+    }
+    for (int r = 0; r < P && ok; ++r) {
+      if (r == me) continue;
+      if (!c->zstream[r]) ok = cudaStreamCreateWithFlags(&c->zstream[r], cudaStreamNonBlocking) == cudaSuccess;
+      if (ok && !c->zpush_ev[r]) ok = cudaEventCreateWithFlags(&c->zpush_ev[r], cudaEventDisableTiming) == cudaSuccess;
+    }
+    if (ok && !c->zcol_ev) ok = cudaEventCreateWithFlags(&c->zcol_ev, cudaEventDisableTiming) == cudaSuccess;
+    if (!ok) cudaGetLastError();
+    okall = ok ? 1.0 : 0.0;
+    rc = dist_allreduce_host(c, &okall);
+    if (rc) { if (hdev) cudaFree(hdev); return rc; }
+  }
+  if (hdev) cudaFree(hdev);
+  c->w2_mapped = c->W2.p;                                          // (also when mapping failed: do not retry every evaluation)
+  c->w2_push_ok = okall > (double)P - 0.5;
+  if (!c->w2_push_ok && getenv("KGP_DEBUG")) fprintf(stderr, "[kgp] rank %d: peer mapping of W2 unavailable, Z is gathered by broadcasts\n", me);
+  return KGP_OK;
 }
 
 // Cholesky with block columns dealt cyclically over the ranks, panel broadcast, look-ahead 1
@@ -352,8 +420,15 @@ static int zsweep_dist(kgp_ctx* c) {
   const int P = c->nranks, me = c->rank;
   const long a = dist_zrow_begin(me, P, np, NB), b = dist_zrow_begin(me + 1, P, np, NB);
   cudaStream_t st = c->stream;
+  // Pipelined all-gather by peer copies (default for P > 2; KGP_DIST_ZPUSH=0/1 forces): the sweep is right-looking, so after the
+  // triangular solve of block column k0 the columns < k0 + w of this rank's rows are final.  Finished column ranges are copied
+  // straight into every peer's W2 (cudaMemcpy2DAsync on one copy stream per peer: copy engines over NVLink, no SMs, no packing)
+  // while the sweep goes on -- eight block columns at a time, the last ones in smaller pieces so that the exposed tail is short.
+  // Rows >= c1 of a range [c0, c1) are zero there and never read by Z Z^T (its K range starts at the tile's own row).
+  const bool zpush = c->w2_push_ok && (getenv("KGP_DIST_ZPUSH") ? atoi(getenv("KGP_DIST_ZPUSH")) != 0 : (P > 2));
   if (b > a) {
     KGP_CUDA(c, cudaMemsetAsync(W + a * ld, 0, (size_t)(b - a) * ld * 8, st));
+    long c0 = (a / NB) * NB; int since = 0;
     for (long k0 = (a / NB) * NB; k0 < np; k0 += NB) {
       const int w = (int)((np - k0 < NB) ? np - k0 : NB);
       const long hi = (b < k0 + w) ? b : k0 + w, nact = hi - a;
@@ -362,6 +437,21 @@ static int zsweep_dist(kgp_ctx* c) {
         c->stats.kernel_launches++;
       }
       trsm_block(c, W + a * ld + k0, ld, nact, M + k0 * ld + k0, ld, w);
+      if (zpush) {
+        const long rem = (np - k0 - w + NB - 1) / NB;             // block columns still to come
+        ++since;
+        if (rem < 2 || (rem < 8 && since >= 2) || since >= 8) {
+          const long c1 = k0 + w;
+          KGP_CUDA(c, cudaEventRecord(c->zcol_ev, st));
+          for (int p = 0; p < P; ++p) {
+            if (p == me) continue;
+            KGP_CUDA(c, cudaStreamWaitEvent(c->zstream[p], c->zcol_ev, 0));
+            KGP_CUDA(c, cudaMemcpy2DAsync((double*)c->w2_peer[p] + a * ld + c0, (size_t)ld * 8, W + a * ld + c0, (size_t)ld * 8,
+                                          (size_t)(c1 - c0) * 8, (size_t)nact, cudaMemcpyDefault, c->zstream[p]));
+          }
+          c0 = c1; since = 0;
+        }
+      }
       const long rest = np - k0 - w;
       c->gemm_class = 2;
       if (rest > 0)
@@ -370,6 +460,19 @@ static int zsweep_dist(kgp_ctx* c) {
     }
   }
   cudaEventRecord(c->ev[12], st);
+  if (zpush) {
+    // this rank's copies are complete -> tiny all-reduce: when it returns on a rank, every peer's copies into that rank's W2 have
+    // completed as well (a rank joins only after its own copy streams have drained)
+    for (int p = 0; p < P; ++p) {
+      if (p == me) continue;
+      KGP_CUDA(c, cudaEventRecord(c->zpush_ev[p], c->zstream[p]));
+      KGP_CUDA(c, cudaStreamWaitEvent(st, c->zpush_ev[p], 0));
+    }
+    KGP_NCCL(c, api, api.AllReduce(c->zbar, c->zbar, 1, KGP_NCCL_DOUBLE, KGP_NCCL_SUM, c->nccl_comm, st));
+    c->zpipe_active = false;
+    cudaEventRecord(c->ev[13], st);
+    return KGP_OK;
+  }
   // all-gather of Z as one broadcast per rank, in rank order, on the (high-priority) panel stream: rank r's rows are the
   // top rows with the long K ranges, i.e. the tiles of Z Z^T that become computable first.  One event per rank lets
   // zzt_reduce_dist start its tiles while the later (larger) broadcasts are still in flight.
@@ -557,7 +660,12 @@ int exact_eval(kgp_ctx* c, int slot, int want, double* nlZ_out, double* dnlZ_out
   if (sm && c->nranks > 1) return c->fail(KGP_BAD_ARG, "exact covSM runs on one GPU (the sharded exact path covers covSEiso / covSEard)");
   const int nmean = ((m.mean_mask & 1) ? D : 0) + ((m.mean_mask & 2) ? 1 : 0);
   if ((int)m.hyp_mean.size() != nmean) return c->fail(KGP_BAD_ARG, "Number of mean function hyperparameters disagree with mean function");
-  int rc = ensure_exact_buffers(c, n, D); if (rc) return rc;
+  int rc;
+  if (c->nranks > 1 && c->nranks <= 8 && !sm && !(getenv("KGP_DIST_ZPUSH") && atoi(getenv("KGP_DIST_ZPUSH")) == 0)) {
+    const long npp = ((n + 127) / 128) * 128;
+    rc = w2_peer_sync(c, (size_t)npp * npp * 8); if (rc) return rc;
+  }
+  rc = ensure_exact_buffers(c, n, D); if (rc) return rc;
   const long np = c->np; const int Dp = c->Dp;
   cudaStream_t st = c->stream;
   memset(&c->stats, 0, sizeof c->stats); c->stats.n = n; c->stats.np = np;

@@ -35,6 +35,7 @@ for n in [int(a) for a in sys.argv[1:]] or [3000]:
         dX1 = gps.get_dlik_dx('tr'); ymu1, ys21 = gps.predict(X[:300] + 0.1, return_var=True)
         print('n=%d world=%d: sharded %.4fs (dev %.1f ms, potrf %.1f inv %.1f red %.1f) single %.4fs | nlZ %.12g vs %.12g rel %.2e dnlZ %.2e dX %.2e ymu %.2e ys2 %.2e' % (
             n, world, t1 - t0, st['ms_total'], st['ms_potrf'], st['ms_inverse'], st['ms_reduce'], t3 - t2, nlZ, nlZ1, rel(nlZ, nlZ1), rel(g, g1), rel(dX, dX1), rel(ymu, ymu1), rel(ys2, ys21)), flush=True)
+        print('   stats:', {k: (round(v, 2) if isinstance(v, float) else v) for k, v in st.items()}, flush=True)
         del gps
     del gpd
 # a matrix that is not positive definite (duplicated rows, vanishing noise): EVERY rank must report NOT_PD -- the owner of

@@ -43,13 +43,17 @@ def test_tile_reduce_path_single_gpu(built_lib, tile_reduce):
     assert max(vals) < 1e-8, out
 
 
-def test_sharded_equals_single_world2(built_lib):
+@pytest.mark.parametrize('zpush', ['default', '1'])
+def test_sharded_equals_single_world2(built_lib, zpush):
+    """zpush = '1': the all-gather of Z = L^-T as pipelined peer copies into the other ranks' W2 (the default for more than two
+    ranks) instead of the default of two ranks (pipelined broadcasts under a staged Z Z^T)."""
     import torch
     if torch.cuda.device_count() < 2:
         pytest.skip('needs 2 GPUs')
     cmd = [sys.executable, '-m', 'torch.distributed.run', '--nnodes=1', '--nproc-per-node', '2', '--master-addr', '127.0.0.1',
-           '--master-port', '29533', os.path.join(ROOT, 'scripts', 'dist_exact.py'), '1000', '2600']
-    out = subprocess.check_output(cmd, timeout=900, stderr=subprocess.STDOUT).decode()
+           '--master-port', '29533' if zpush == 'default' else '29536', os.path.join(ROOT, 'scripts', 'dist_exact.py'), '1000', '2600']
+    env = dict(os.environ) if zpush == 'default' else dict(os.environ, KGP_DIST_ZPUSH=zpush)
+    out = subprocess.check_output(cmd, timeout=900, stderr=subprocess.STDOUT, env=env).decode()
     lines = [l for l in out.splitlines() if l.startswith('n=')]
     assert len(lines) == 2, out
     for l in lines:
