@@ -81,6 +81,7 @@ struct kgp_ctx {
   // pipelined all-gather of Z = L^-T by peer copies (exact.cu, zsweep_dist): every rank's W2 mapped into every peer with CUDA IPC;
   // w2_mapped = the local allocation the peers hold a mapping of; one copy stream + event per peer; zbar = 8-byte all-reduce word
   void* w2_peer[8] = {nullptr}; void* w2_mapped = nullptr; bool w2_push_ok = false;
+  std::vector<void*> w2_retired;                      // allocations outgrown while peers still map them: freed once the peers have closed
   cudaStream_t zstream[8] = {nullptr}; cudaEvent_t zpush_ev[8] = {nullptr}; cudaEvent_t zcol_ev = nullptr; double* zbar = nullptr;
   // peer exchange window of the row-sharded KISS-GP CG (grid_cg.cuh, CgDist): one cudaMalloc per rank, mapped into
   // every peer with CUDA IPC; px_epoch = tag of the last exchange (monotone over all solves, equal on all ranks)

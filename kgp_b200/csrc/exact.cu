@@ -271,6 +271,8 @@ void dist_free(kgp_ctx* c) {
   if (c->zcol_ev) { cudaEventDestroy(c->zcol_ev); c->zcol_ev = nullptr; }
   if (c->zbar) { cudaFree(c->zbar); c->zbar = nullptr; }
   c->w2_mapped = nullptr; c->w2_push_ok = false;
+  for (void* q : c->w2_retired) cudaFree(q);
+  c->w2_retired.clear();
   for (int r = 0; r < 8; ++r) { if (c->px_peer[r] && c->px_peer[r] != c->px_local) cudaIpcCloseMemHandle(c->px_peer[r]); c->px_peer[r] = nullptr; }
   if (c->px_local) { cudaFree(c->px_local); c->px_local = nullptr; }
   if (c->px_abort) { cudaFree(c->px_abort); c->px_abort = nullptr; }
@@ -302,6 +304,8 @@ static int w2_peer_sync(kgp_ctx* c, size_t need_bytes) {
   c->w2_mapped = nullptr; c->w2_push_ok = false;
   double zero = 0.0;
   rc = dist_allreduce_host(c, &zero); if (rc) return rc;          // every rank has closed its mappings: owners may free now
+  for (void* q : c->w2_retired) cudaFree(q);
+  c->w2_retired.clear();
   KGP_CUDA(c, c->W2.ensure(need_bytes));
   cudaIpcMemHandle_t mine; char* hdev = nullptr; std::vector<cudaIpcMemHandle_t> all(P);
   bool ok = cudaIpcGetMemHandle(&mine, c->W2.p) == cudaSuccess && cudaMalloc((void**)&hdev, (size_t)P * sizeof(mine)) == cudaSuccess;
@@ -585,6 +589,11 @@ static int ensure_exact_buffers(kgp_ctx* c, long n, int D) {
   const int Dp = pick_dp(D);
   c->np = np; c->Dp = Dp;
   KGP_CUDA(c, c->M.ensure((size_t)np * np * 8));
+  if ((size_t)np * np * 8 > c->W2.bytes && c->W2.p && c->W2.p == c->w2_mapped) {
+    // peers hold CUDA-IPC mappings of this allocation (w2_peer_sync): an exporter must not free it under them.  Outside the
+    // collective re-mapping (e.g. the KISS-GP preconditioner growing the matrix on a sharded context) it is set aside instead.
+    c->w2_retired.push_back(c->W2.p); c->W2.p = nullptr; c->W2.bytes = 0;
+  }
   KGP_CUDA(c, c->W2.ensure((size_t)np * np * 8));
   KGP_CUDA(c, c->Dws.ensure((size_t)np * NB * 8));
   KGP_CUDA(c, c->xs.ensure((size_t)np * Dp * 8));
