@@ -670,7 +670,9 @@ int exact_eval(kgp_ctx* c, int slot, int want, double* nlZ_out, double* dnlZ_out
   const int nmean = ((m.mean_mask & 1) ? D : 0) + ((m.mean_mask & 2) ? 1 : 0);
   if ((int)m.hyp_mean.size() != nmean) return c->fail(KGP_BAD_ARG, "Number of mean function hyperparameters disagree with mean function");
   int rc;
-  if (c->nranks > 1 && c->nranks <= 8 && !sm && !(getenv("KGP_DIST_ZPUSH") && atoi(getenv("KGP_DIST_ZPUSH")) == 0)) {
+  // (the peer mappings are set up only where the peer-copy gather is in use: more than two ranks, or forced by KGP_DIST_ZPUSH=1)
+  if (c->nranks > 1 && c->nranks <= 8 && !sm &&
+      (getenv("KGP_DIST_ZPUSH") ? atoi(getenv("KGP_DIST_ZPUSH")) != 0 : c->nranks > 2)) {
     const long npp = ((n + 127) / 128) * 128;
     rc = w2_peer_sync(c, (size_t)npp * npp * 8); if (rc) return rc;
   }
