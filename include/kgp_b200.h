@@ -61,6 +61,10 @@ typedef struct {
   int    cg_deterministic;   /* 1 (default): the scatter Mx'(sW d) of the persistent CG accumulates in order-independent fixed point
                               * (integer atomics) -> two runs of a solve are bit-identical; 0: FP64 atomics, ~25 % faster at n = 1M,
                               * last-bit differences from run to run (iteration counts may differ by a few per cent) */
+  int    deg;                /* opt.deg (GPML/cov/apx.m:27-32,122; apxGrid.m:495-504): interpolation degree on equispaced axes.
+                              * 3 (default) Keys cubic, 1 linear, 0 nearest node; other values (GP interpolation) are refused.
+                              * Non-equispaced axes ignore it.  deg != 3 runs the general CG path (no cg_precond / pred_var /
+                              * SLQ / Toeplitz factors, like non-equispaced axes) */
 } kgp_opt;
 
 /* per-call statistics of the last kgp_eval / kgp_dlik_dx / kgp_predict */

@@ -22,7 +22,7 @@ class KgpOpt(C.Structure):
                 ('ldB2_cheby_hutch', C.c_int), ('ldB2_cheby_degree', C.c_int),
                 ('ldB2_cheby_maxit', C.c_int), ('ldB2_cheby_seed', C.c_uint64),
                 ('ard_reference_form', C.c_int), ('cg_precond', C.c_int), ('pred_var', C.c_int),
-                ('ldB2_slq', C.c_int), ('ldB2_slq_steps', C.c_int), ('cg_deterministic', C.c_int)]
+                ('ldB2_slq', C.c_int), ('ldB2_slq_steps', C.c_int), ('cg_deterministic', C.c_int), ('deg', C.c_int)]
 
 
 class KgpStats(C.Structure):
@@ -181,17 +181,18 @@ class Context(object):
         for k, v in (opt or {}).items():
             if k == 'pred_var':
                 v = int(np.ceil(abs(float(v))))                  # infGrid.m:94
+            if k == 'deg' and (np.ndim(v) != 0 or int(v) not in (0, 1, 3)):
+                # apxGrid.m:448 also takes one degree per dimension, and d > 3 selects GP interpolation (apxGrid.m:501-504): not built
+                raise ValueError('opt.deg=%r is not supported by the B200 engine (0, 1 or 3, one value for all axes)' % (v,))
             if hasattr(o, k):
                 setattr(o, k, type(getattr(o, k))(v))
-            elif k == 'deg' and int(v) == 3:
-                pass                                             # cubic interpolation is what the engine builds (apx.m:123 default)
             elif k == 'stat' and not v:
                 pass
             elif k == 'proj':
                 pass                                             # handled above the C ABI (engine.py: hyp.proj, orth / norm)
-            elif k in ('deg', 'ndcovs', 'stat'):
-                # GPML options that change the numbers (apx.m:123, infGrid.m:56,70): refusing beats returning cubic /
-                # un-projected results as if the option had been honoured
+            elif k in ('ndcovs', 'stat'):
+                # GPML options that change the numbers (infGrid.m:56,70): refusing beats returning results as if the option
+                # had been honoured
                 raise ValueError('opt.%s=%r is not supported by the B200 engine' % (k, v))
             else:
                 import warnings

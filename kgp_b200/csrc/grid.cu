@@ -105,7 +105,10 @@ static int grid_setup(kgp_ctx* c, GridState* g, GridDesc& G) {
     G.ng[d] = (int)a.size(); G.stride[d] = N; N *= G.ng[d];
     G.ax[d] = g->axes.d() + o; o += (long)a.size();
     const bool neq = d < (int)c->grid.neq.size() && c->grid.neq[d] != 0;
-    g->any_neq |= neq;
+    G.deg[d] = c->model.opt.deg;                                // opt.deg (apx.m:122): equispaced axes only, neqinterp ignores it
+    // the cell-sorted kernels (persistent CG, Gram accumulation, sorted Chebyshev recurrence) hard-wire the cubic stencil:
+    // every other interpolation takes the general streaming kernels, like a non-equispaced axis
+    g->any_neq |= neq || G.deg[d] != 3;
     G.s0[d] = a[0]; G.ds[d] = neq ? 0.0 : a[1] - a[0];           // ds = 0 marks a non-equispaced axis for the interpolation kernels
     G.range[d] = neq ? 1.0 : *std::max_element(a.begin(), a.end()) - *std::min_element(a.begin(), a.end());   // deriv_x.m:11-15: wi = 1
     g->ng[d] = G.ng[d]; g->koff[d] = ko; ko += (long)G.ng[d] * G.ng[d]; g->eoff_h[d] = eo; eo += G.ng[d];
@@ -1123,7 +1126,7 @@ int grid_eval(kgp_ctx* c, int slot, int want, double* nlZ_out, double* dnlZ_out)
   bool toep[GRID_MAXP] = {false}, any_toep = false;
   for (int d = 0; d < G.p; ++d) { toep[d] = d < (int)c->grid.toep.size() && c->grid.toep[d] != 0; any_toep |= toep[d]; }
   if (g->any_neq && (any_toep || m.opt.cg_precond || m.opt.pred_var != 0 || slq))
-    return c->fail(KGP_BAD_ARG, "non-equispaced grid axes (neqinterp) run with the plain CG and the Fiedler / Chebyshev log-det only");
+    return c->fail(KGP_BAD_ARG, "non-equispaced grid axes (neqinterp) and opt.deg != 3 run with the plain CG and the Fiedler / Chebyshev log-det only");
   if (any_toep && (m.opt.cg_precond || m.opt.pred_var != 0))
     return c->fail(KGP_BAD_ARG, "opt.cg_precond / opt.pred_var need the factor eigenvectors: not available for Toeplitz factors (nested xg)");
   for (int d = 0; d < G.p; ++d) {

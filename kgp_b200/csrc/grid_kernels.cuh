@@ -18,6 +18,7 @@ struct GridDesc {
   int p; int ng[GRID_MAXP]; long stride[GRID_MAXP]; long N;
   const double* ax[GRID_MAXP];           // device axis values
   double s0[GRID_MAXP], ds[GRID_MAXP], range[GRID_MAXP];
+  int deg[GRID_MAXP];                    // opt.deg on an equispaced axis: 3 cubic, 1 linear, 0 nearest node (apxGrid.m:497-500)
 };
 
 __device__ __forceinline__ double kcub(double x) {
@@ -59,10 +60,51 @@ __device__ __forceinline__ void neqinterp1(const double* __restrict__ ax, int ns
   j = jb;
 }
 
+// eqinterp with deg = 1 (linear) or 0 (nearest node), apxGrid.m:498-499 with it = -1:0, nc = 2: nodes j, j+1 with weights
+// k(w), k(w-1), k(x) = max(1-|x|,0) resp. [-0.5 < x <= 0.5]; boundary rule of apxGrid.m:515-522 on two nodes.  Returned inside the
+// 4-node stencil (two zero weights), like neqinterp1.
+template <bool DERIV>
+__device__ __forceinline__ void eqinterp_low(const double* __restrict__ ax, int ns, double s0, double ds, double t, int deg,
+                                             int& j, double c[4], double dc[4]) {
+  const double u = (t - s0) / ds;
+  double jf = floor(u) + 1.0;                         // 1-based index of the closest smaller grid point (it(nc) = 0)
+  const double w = u - jf + 1.0;
+  double c0, c1, d0 = 0.0, d1 = 0.0;
+  if (deg == 1) {
+    c0 = fmax(1.0 - fabs(w), 0.0); c1 = fmax(1.0 - fabs(w - 1.0), 0.0);
+    if (DERIV) {                                      // dk(x) = -(|x| <= 1) sign(x), times ns - 1 (apxGrid.m:512)
+      const double f = (double)(ns - 1), w1 = w - 1.0;
+      d0 = (fabs(w) <= 1.0) ? ((w > 0.0) ? -f : ((w < 0.0) ? f : 0.0)) : 0.0;
+      d1 = (fabs(w1) <= 1.0) ? ((w1 > 0.0) ? -f : ((w1 < 0.0) ? f : 0.0)) : 0.0;
+    }
+  } else {
+    c0 = (-0.5 < w && w <= 0.5) ? 1.0 : 0.0; c1 = (-0.5 < w - 1.0 && w - 1.0 <= 0.5) ? 1.0 : 0.0;
+  }
+  if (jf < 1.0) {                                     // lower boundary: weight 1 on the nearer of s(1:2) (min takes the first on a tie)
+    const bool first = fabs(ax[0] - t) <= fabs(ax[1] - t);
+    c0 = first ? 1.0 : 0.0; c1 = first ? 0.0 : 1.0; d0 = d1 = 0.0; jf = 1.0;
+  }
+  const double v = (double)(ns - 1);
+  if (jf > v) {                                       // upper boundary
+    const bool first = fabs(ax[ns - 2] - t) <= fabs(ax[ns - 1] - t);
+    c0 = first ? 1.0 : 0.0; c1 = first ? 0.0 : 1.0; d0 = d1 = 0.0; jf = v;
+  }
+  const int jn = (int)jf - 1;                         // 0-based first node of the pair
+  int jb = jn - 1; if (jb < 0) jb = 0; if (jb > ns - 4) jb = ns - 4;
+  const int sft = jn - jb;
+#pragma unroll
+  for (int q = 0; q < 4; ++q) {
+    c[q] = (q == sft) ? c0 : ((q == sft + 1) ? c1 : 0.0);
+    if (DERIV) dc[q] = (q == sft) ? d0 : ((q == sft + 1) ? d1 : 0.0);
+  }
+  j = jb;
+}
+
 template <bool DERIV>
 __device__ __forceinline__ void eqinterp1(const double* __restrict__ ax, int ns, double s0, double ds, double t,
-                                          int& j, double c[4], double dc[4]) {
+                                          int& j, double c[4], double dc[4], int deg = 3) {
   if (ds <= 0.0) { neqinterp1<DERIV>(ax, ns, t, j, c, dc); return; }       // non-equispaced axis (grid_setup sets ds = 0)
+  if (deg != 3) { eqinterp_low<DERIV>(ax, ns, s0, ds, t, deg, j, c, dc); return; }
   const double u = (t - s0) / ds;
   double jf = floor(u) + 1.0;
   const double w = u - jf + 1.0;
@@ -108,7 +150,7 @@ __global__ void interp_scatter_kernel(GridDesc G, const double* __restrict__ X, 
   for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long)gridDim.x * blockDim.x) {
     int j[P]; double c[P][4], dummy[4];
 #pragma unroll
-    for (int d = 0; d < P; ++d) eqinterp1<false>(G.ax[d], G.ng[d], G.s0[d], G.ds[d], X[i * D + d], j[d], c[d], dummy);
+    for (int d = 0; d < P; ++d) eqinterp1<false>(G.ax[d], G.ng[d], G.s0[d], G.ds[d], X[i * D + d], j[d], c[d], dummy, G.deg[d]);
     const double vi = v[i] * scale;
     if (P == 1) {
 #pragma unroll
@@ -144,7 +186,7 @@ __device__ __forceinline__ double interp_gather_point(const GridDesc& G, const d
                                                       const double* __restrict__ u, double dout[P]) {
   int j[P]; double c[P][4], dc[P][4];
 #pragma unroll
-  for (int d = 0; d < P; ++d) eqinterp1<DERIV>(G.ax[d], G.ng[d], G.s0[d], G.ds[d], xi[d], j[d], c[d], dc[d]);
+  for (int d = 0; d < P; ++d) eqinterp1<DERIV>(G.ax[d], G.ng[d], G.s0[d], G.ds[d], xi[d], j[d], c[d], dc[d], G.deg[d]);
   double acc = 0.0;
   if (DERIV) {
 #pragma unroll

@@ -111,10 +111,20 @@ def dkcub(x):
     return y
 
 
-def eqinterp(s, t):
-    """J (nt,4) 0-based node indices, C (nt,4) weights, dC (nt,4) derivative weights * (ns-1)."""
+def eqinterp(s, t, deg=3):
+    """J (nt,nc) 0-based node indices, C (nt,nc) weights, dC (nt,nc) derivative weights * (ns-1); apxGrid.m:495-523.
+    deg = 3: Keys cubic on 4 nodes (the default, apx.m:122); deg = 1: linear, deg = 0: nearest node, both on 2 nodes
+    (apxGrid.m:498-500).  The GP-interpolation branch (deg > 3, apxGrid.m:501-504) is not restated."""
     s = np.asarray(s, dtype=np.float64); t = np.asarray(t, dtype=np.float64)
-    it = np.array([-2, -1, 0, 1]); nc = 4
+    if deg == 3:
+        it = np.array([-2, -1, 0, 1]); k, dk = kcub, dkcub
+    elif deg == 1:
+        it = np.array([-1, 0]); k = lambda x: np.maximum(1.0 - np.abs(x), 0.0); dk = lambda x: -(np.abs(x) <= 1).astype(np.float64) * np.sign(x)
+    elif deg == 0:
+        it = np.array([-1, 0]); k = lambda x: ((-0.5 < x) & (x <= 0.5)).astype(np.float64); dk = lambda x: 0.0 * x
+    else:
+        raise ValueError('interpolation degree %r is not restated (0, 1, 3)' % (deg,))
+    nc = it.size
     ds = s[1] - s[0]; ns = s.size
     assert ns >= nc
     j = np.floor((t - s[0]) / ds) + 1
@@ -122,8 +132,8 @@ def eqinterp(s, t):
     j = j - it[nc - 1]
     C = np.zeros((t.size, nc)); dC = np.zeros((t.size, nc))
     for i in range(nc):
-        C[:, i] = kcub(w + it[nc - 1 - i])
-        dC[:, i] = dkcub(w + it[nc - 1 - i]) * (ns - 1)
+        C[:, i] = k(w + it[nc - 1 - i])
+        dC[:, i] = dk(w + it[nc - 1 - i]) * (ns - 1)
     idx = np.where(j < nc + it[0])[0]                     # lower boundary (:515-518)
     C[idx] = 0; dC[idx] = 0
     if idx.size:
@@ -164,8 +174,9 @@ def neqinterp(s, t):
     return J, C, dC
 
 
-def interpgrid(xg, x, want_deriv=False):
-    """Sparse Mx (n x N) and optionally dMx[i]; grid linear index has the first axis fastest."""
+def interpgrid(xg, x, want_deriv=False, deg=3):
+    """Sparse Mx (n x N) and optionally dMx[i]; grid linear index has the first axis fastest.  deg: interpolation degree of the
+    equispaced axes (opt.deg, apxGrid.m:448); non-equispaced axes ignore it (apx.m:28-32)."""
     x = np.asarray(x, dtype=np.float64)
     if x.ndim == 1:
         x = x[:, None]
@@ -175,7 +186,7 @@ def interpgrid(xg, x, want_deriv=False):
     dC = [np.ones((n, 1)) for _ in range(p)]
     s = 1
     for i in range(p):
-        Ji, Ci, dCi = eqinterp(xg[i], x[:, i]) if equi(xg[i]) else neqinterp(xg[i], x[:, i])   # apxGrid.m:453-465
+        Ji, Ci, dCi = eqinterp(xg[i], x[:, i], deg) if equi(xg[i]) else neqinterp(xg[i], x[:, i])   # apxGrid.m:453-465
         J = (J[:, :, None] + s * Ji[:, None, :]).reshape(n, -1)
         C = (C[:, :, None] * Ci[:, None, :]).reshape(n, -1)
         for jd in range(p):
@@ -587,7 +598,7 @@ def inf_grid(hyp, mean, kind, xg, x, y, opt=None, Q=0, want_grad=True, cheby=Non
         else:
             K_, dK_ = factor_cov(kind, hs[i], xg[i], Q); Ks.append(K_); dKs.append(dK_)
     xg = flat_grid(xg)
-    Mx = interpgrid(xg, x)
+    Mx = interpgrid(xg, x, deg=int(opt.get('deg', 3)))              # apx.m:122,131
     MxT = Mx.T.tocsr()
     m, dm = mean_eval(mean, hyp.get('mean', []), x)
     sn2 = np.exp(2.0 * float(hyp['lik'])); W = np.full(n, 1.0 / sn2); sW = np.sqrt(W)
@@ -640,7 +651,7 @@ def dlik_grid(hyp, mean, kind, xg, x, y, opt=None, Q=0, h=1e-5):
     post, _, _ = inf_grid(hyp, mean, kind, xg, x, y, opt, Q, want_grad=False)
     alpha = post['alpha']
     xg = flat_grid(xg)
-    _, dM = interpgrid(xg, x, want_deriv=True)
+    _, dM = interpgrid(xg, x, want_deriv=True, deg=int((opt or {}).get('deg', 3)))      # dlikGrid.m:23, deriv_x.m:7
     beta = post['Kalpha']
     cols = []
     for i in range(x.shape[1]):
@@ -669,13 +680,13 @@ def pred_var_grid(post, Rg, Rn):
     return (z * z).sum(1) / ns
 
 
-def predict_grid(hyp, mean, kind, xg, post, xs, Q=0, vg=None):
-    """[fmu fs2 ymu ys2] = post.predict(xs)  (infGrid.m:135-145; vg = 0 unless opt.pred_var)."""
+def predict_grid(hyp, mean, kind, xg, post, xs, Q=0, vg=None, deg=3):
+    """[fmu fs2 ymu ys2] = post.predict(xs)  (infGrid.m:135-145; vg = 0 unless opt.pred_var; deg = opt.deg, infGrid.m:66,131)."""
     xs = np.asarray(xs, dtype=np.float64)
     if xs.ndim == 1:
         xs = xs[:, None]
     xg = flat_grid(xg)
-    Ms = interpgrid(xg, xs)
+    Ms = interpgrid(xg, xs, deg=deg)
     ms, _ = mean_eval(mean, hyp.get('mean', []), xs)
     fmu = ms + Ms @ post['Kalpha']
     hs = split_hyp(kind, hyp['cov'], len(xg), Q)

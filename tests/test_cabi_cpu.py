@@ -96,7 +96,8 @@ def test_unsupported_opt_keys_are_refused():
     d._l = type('L', (), {'kgp_opt_default': staticmethod(_cabi.lib().kgp_opt_default), 'kgp_set_model': staticmethod(lambda *a: 0)})()
     d.set_model('infGrid', 'covSEiso', [0., 0.], 0.0, opt={'cg_tol': 1e-4, 'deg': 3})
     d.set_model('infGrid', 'covSEiso', [0., 0.], 0.0, opt={'proj': 'orth'})     # handled above the C ABI (engine.py)
-    for bad in ({'deg': 1}, {'ndcovs': 5}):
+    d.set_model('infGrid', 'covSEiso', [0., 0.], 0.0, opt={'deg': 1})           # linear / nearest-node interpolation are built
+    for bad in ({'deg': 5}, {'deg': [3, 1]}, {'ndcovs': 5}):
         with pytest.raises(ValueError):
             d.set_model('infGrid', 'covSEiso', [0., 0.], 0.0, opt=bad)
 

@@ -476,6 +476,57 @@ def test_non_equispaced_axes_vs_oracle(built_lib, shape):
     assert rel(ymu, gg.predict_grid(oh, ['meanZero'], 'covSEiso', xg, post, Xs)[2]) < 1e-7
 
 
+@pytest.mark.parametrize('deg,shape', [(1, '1d'), (1, '2d'), (0, '2d')])
+def test_interpolation_degree_vs_oracle(built_lib, deg, shape):
+    """opt.deg (apx.m:27-32,122; apxGrid.m:495-523; passed through by kgp's `opt` dict): linear and nearest-node interpolation on
+    equispaced axes -- nlZ, dnlZ, alpha, dnlZ/dX (zero for deg = 0: dk = 0) and the predictive mean against the oracle at tight CG;
+    the cubic default gives a different nlZ on the same problem; degrees the engine does not build are refused."""
+    import gpml_grid as gg
+    from kgp_b200 import B200GP
+    rng = np.random.RandomState(12)
+    opt = {'cg_maxit': 8000, 'cg_tol': 1e-12, 'deg': deg}
+    if shape == '1d':
+        n = 500; X = rng.rand(n, 1); y = np.sin(5 * X[:, 0]) + 0.1 * rng.randn(n); Xs = rng.rand(60, 1) * 1.8 - 0.4
+        hc = [[np.log(0.2)], [0.1]]; k = 40.
+    else:
+        n = 1500; X = rng.rand(n, 2); y = np.sin(4 * X[:, 0]) + X[:, 1] + 0.1 * rng.randn(n); Xs = rng.rand(90, 2) * 1.6 - 0.3
+        hc = [[np.log(0.3)], [0.0]]; k = 24.
+    D = X.shape[1]
+
+    def run(o):
+        gp = B200GP()
+        gp.configure(D, {'lik': np.log(0.1), 'mean': [], 'cov': [list(r) for r in hc]}, o, 'infGrid', 'meanZero', 'covSEiso', 'likGauss',
+                     'dlikGrid', grid_kwargs={'eq': 1, 'k': k}, verbose=0)
+        gp.update_data('tr', X, y[:, None]); gp.update_grid('tr')
+        nlZ, g = gp.eng.eval(0, 2, gp._n_hyp)
+        return gp, nlZ, g
+    gp, nlZ, g = run(opt)
+    dX = gp.get_dlik_dx('tr'); ymu = gp.predict(Xs)
+    xg = gg.creategrid(X, 1, k)
+    hv = gp._hyp_vec(); nc = gp.hyp['cov'].size
+    oh = {'cov': hv[:nc], 'lik': gp.hyp['lik'], 'mean': []}
+    post, nlZ0, d0 = gg.inf_grid(oh, ['meanZero'], 'covSEiso', xg, X, y, opt)
+    g0 = np.concatenate([d0['cov'], [d0['lik']]])
+    assert rel(nlZ, nlZ0) < 1e-8 and rel(g, g0) < 1e-7 and rel(gp.alpha(), post['alpha']) < 1e-7
+    dX0 = gg.dlik_grid(oh, ['meanZero'], 'covSEiso', xg, X, y, opt)
+    if deg == 0:
+        assert np.all(dX0 == 0) and np.all(dX == 0)
+    else:
+        assert rel(dX, dX0) < 1e-7
+    assert rel(ymu, gg.predict_grid(oh, ['meanZero'], 'covSEiso', xg, post, Xs, deg=deg)[2]) < 1e-7
+    _, nlZ3, _ = run({'cg_maxit': 8000, 'cg_tol': 1e-12})
+    assert abs(nlZ3 - nlZ) > 1e-6 * abs(nlZ)                           # not the cubic result under another name
+    with pytest.raises(ValueError):
+        run(dict(opt, deg=5))
+    with pytest.raises(_cabi_mod().KgpError):
+        run(dict(opt, cg_precond=1))                                   # the preconditioner's Gram kernel hard-wires the cubic stencil
+
+
+def _cabi_mod():
+    from kgp_b200 import _cabi
+    return _cabi
+
+
 def test_kmeans_grid_eq0_vs_oracle(built_lib):
     """SURVEY 8(f)-4, k-means grid: grid_kwargs eq = 0 -> covGrid('create', x, 0, k) (kgp/backend/gpml.py:29-31, apxGrid.m:410-415).
     Octave's randomly initialised kmeans cannot be reproduced; engine and oracle share the deterministic Lloyd stand-in, so the

@@ -403,3 +403,50 @@ def test_kmeans_grid_eq0_structure_and_host_routine():
         fd = (gg.inf_grid(hp, ['meanZero'], 'covSEiso', xg2, X, y, opt, want_grad=False)[1] -
               gg.inf_grid(hm, ['meanZero'], 'covSEiso', xg2, X, y, opt, want_grad=False)[1]) / 2e-6
         assert abs(fd - d['cov'][i]) < 1e-5 * max(1.0, abs(fd))
+
+
+@pytest.mark.parametrize('deg', [1, 0])
+def test_eqinterp_low_degrees(deg):
+    """opt.deg (apx.m:27-32,122; apxGrid.m:495-523): linear (1) and nearest-node (0) interpolation on equispaced axes -- two
+    nodes per axis, rows sum to 1, boundary rule on the two end nodes; deg = 1 reproduces linear functions exactly inside the grid and
+    its dlik_grid passes the central-difference check (deg = 0 has zero input gradient: dk = 0, apxGrid.m:498)."""
+    s = np.linspace(-1.0, 2.0, 13); h = s[1] - s[0]
+    t = np.array([-1.5, -1.0, -0.9, 0.123, 0.5, s[5], s[5] + 0.5 * h, 1.99, 2.0, 2.7])
+    J, C, dC = gg.eqinterp(s, t, deg)
+    assert J.shape == (t.size, 2) and np.allclose(C.sum(1), 1.0) and J.min() >= 0 and J.max() <= s.size - 1
+    inside = (t >= s[0]) & (t < s[-1])
+    if deg == 1:
+        assert np.allclose((C * s[J]).sum(1)[inside], t[inside])                       # exact on linear functions
+        off = inside & (np.abs((t - s[0]) / h - np.round((t - s[0]) / h)) > 1e-9)      # at a node dk(0) = -sign(0) = 0: one-sided weights
+        assert np.allclose((dC * s[J]).sum(1)[off] / (s[-1] - s[0]), 1.0)              # d/dt of the same, deriv_x's w_i scaling
+    else:
+        assert set(np.unique(C)) <= {0.0, 1.0} and np.all(dC == 0)
+        near = s[J[np.arange(t.size), np.argmax(C, axis=1)]]
+        assert np.all(np.abs(near - t)[inside] <= 0.5 * h + 1e-12)
+        assert near[6] == s[5]                                                       # a tie at w = 0.5 goes to the lower node
+    assert np.array_equal(C[0], [1.0, 0.0]) and J[0, 0] == 0                         # below the axis: first node
+    assert np.array_equal(C[-1], [0.0, 1.0]) and J[-1, 1] == s.size - 1              # above: last node
+    rng = np.random.RandomState(9)
+    n = 140; X = rng.rand(n, 2); y = np.sin(4 * X[:, 0]) + X[:, 1] + 0.1 * rng.randn(n)
+    xg = [np.linspace(-0.2, 1.2, 17), np.linspace(-0.3, 1.3, 15)]
+    hyp = {'cov': np.array([np.log(0.3), 0.0, np.log(0.4), 0.1]), 'lik': np.log(0.1), 'mean': []}
+    opt = {'cg_maxit': 3000, 'cg_tol': 1e-13, 'deg': deg}
+    Mx = gg.interpgrid(xg, X, deg=deg)
+    assert np.allclose(Mx.sum(1), 1.0) and (Mx.getnnz(axis=1) <= 4).all()
+    _, nl3, _ = gg.inf_grid(hyp, ['meanZero'], 'covSEiso', xg, X, y, dict(opt, deg=3))
+    _, nl, d = gg.inf_grid(hyp, ['meanZero'], 'covSEiso', xg, X, y, opt)
+    assert abs(nl - nl3) > 1e-6                                                      # the option is honoured
+    for i in range(4):                                                               # hyper-gradient vs central differences
+        e = np.zeros(4); e[i] = 1e-6
+        hp = dict(hyp, cov=hyp['cov'] + e); hm = dict(hyp, cov=hyp['cov'] - e)
+        fd = (gg.inf_grid(hp, ['meanZero'], 'covSEiso', xg, X, y, opt, want_grad=False)[1] -
+              gg.inf_grid(hm, ['meanZero'], 'covSEiso', xg, X, y, opt, want_grad=False)[1]) / 2e-6
+        assert abs(fd - d['cov'][i]) < 1e-5 * max(1.0, abs(fd))
+    dX = gg.dlik_grid(hyp, ['meanZero'], 'covSEiso', xg, X, y, opt)
+    if deg == 0:
+        assert np.all(dX == 0)
+    else:
+        f = lambda xx: gg.inf_grid(hyp, ['meanZero'], 'covSEiso', xg, xx, y, opt, want_grad=False)[1]
+        for (i, dd) in ((3, 0), (40, 1), (77, 0)):
+            e = np.zeros_like(X); e[i, dd] = 1e-6
+            assert abs((f(X + e) - f(X - e)) / 2e-6 - dX[i, dd]) < 1e-5 * max(1.0, abs(dX[i, dd]))
