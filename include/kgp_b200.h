@@ -65,6 +65,8 @@ typedef struct {
                               * 3 (default) Keys cubic, 1 linear, 0 nearest node; other values (GP interpolation) are refused.
                               * Non-equispaced axes ignore it.  deg != 3 runs the general CG path (no cg_precond / pred_var /
                               * SLQ / Toeplitz factors, like non-equispaced axes) */
+  int    deg_axis[4];        /* one degree per grid dimension (GPML/cov/apxGrid.m:448 "deg = deg(:).*ones(p,1)"); an entry < 0 (the
+                              * default) means "use deg" */
 } kgp_opt;
 
 /* per-call statistics of the last kgp_eval / kgp_dlik_dx / kgp_predict */

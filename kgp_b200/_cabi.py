@@ -22,7 +22,7 @@ class KgpOpt(C.Structure):
                 ('ldB2_cheby_hutch', C.c_int), ('ldB2_cheby_degree', C.c_int),
                 ('ldB2_cheby_maxit', C.c_int), ('ldB2_cheby_seed', C.c_uint64),
                 ('ard_reference_form', C.c_int), ('cg_precond', C.c_int), ('pred_var', C.c_int),
-                ('ldB2_slq', C.c_int), ('ldB2_slq_steps', C.c_int), ('cg_deterministic', C.c_int), ('deg', C.c_int)]
+                ('ldB2_slq', C.c_int), ('ldB2_slq_steps', C.c_int), ('cg_deterministic', C.c_int), ('deg', C.c_int), ('deg_axis', C.c_int * 4)]
 
 
 class KgpStats(C.Structure):
@@ -181,9 +181,17 @@ class Context(object):
         for k, v in (opt or {}).items():
             if k == 'pred_var':
                 v = int(np.ceil(abs(float(v))))                  # infGrid.m:94
-            if k == 'deg' and (np.ndim(v) != 0 or int(v) not in (0, 1, 3)):
-                # apxGrid.m:448 also takes one degree per dimension, and d > 3 selects GP interpolation (apxGrid.m:501-504): not built
-                raise ValueError('opt.deg=%r is not supported by the B200 engine (0, 1 or 3, one value for all axes)' % (v,))
+            if k == 'deg':
+                # one degree for all axes or one per grid dimension (apxGrid.m:448); d > 3 selects GP interpolation
+                # (apxGrid.m:501-504), which is not built
+                dv = [int(t) for t in np.atleast_1d(v).ravel()]
+                if not dv or len(dv) > 4 or any(t not in (0, 1, 3) for t in dv) or any(float(t) != int(t) for t in np.atleast_1d(v).ravel()):
+                    raise ValueError('opt.deg=%r is not supported by the B200 engine (degrees 0, 1 or 3)' % (v,))
+                if len(dv) > 1:
+                    for i, t in enumerate(dv):
+                        o.deg_axis[i] = t
+                    continue
+                v = dv[0]
             if hasattr(o, k):
                 setattr(o, k, type(getattr(o, k))(v))
             elif k == 'stat' and not v:

@@ -57,6 +57,7 @@ void kgp_opt_default(kgp_opt* o) {
   memset(o, 0, sizeof *o);
   o->cg_tol = 1e-6; o->cg_maxit = 0; o->ldB2_cheby = 0; o->ldB2_cheby_hutch = 10;
   o->ldB2_cheby_degree = 15; o->ldB2_cheby_maxit = 50; o->ldB2_cheby_seed = 0; o->ard_reference_form = 0; o->cg_precond = 0; o->pred_var = 0; o->ldB2_slq = 0; o->ldB2_slq_steps = 30; o->cg_deterministic = 1; o->deg = 3;
+  for (int d = 0; d < 4; ++d) o->deg_axis[d] = -1;
 }
 
 int kgp_ctx_create(int device, kgp_ctx** out) {
@@ -235,6 +236,9 @@ int kgp_set_model(kgp_ctx* c, int inf_kind, int cov_kind, int sm_Q, int mean_mas
   if (mean_mask & ~3) return c->fail(KGP_BAD_ARG, "unknown mean mask %d", mean_mask);
   if (opt && opt->deg != 0 && opt->deg != 1 && opt->deg != 3)
     return c->fail(KGP_BAD_ARG, "opt.deg = %d: interpolation degrees 0, 1 and 3 are built (GPML/cov/apxGrid.m:497-504)", opt->deg);
+  if (opt) for (int d = 0; d < 4; ++d)
+    if (opt->deg_axis[d] >= 0 && opt->deg_axis[d] != 0 && opt->deg_axis[d] != 1 && opt->deg_axis[d] != 3)
+      return c->fail(KGP_BAD_ARG, "opt.deg(%d) = %d: interpolation degrees 0, 1 and 3 are built (GPML/cov/apxGrid.m:497-504)", d + 1, opt->deg_axis[d]);
   Model& m = c->model;
   m.inf_kind = inf_kind; m.cov_kind = cov_kind; m.sm_Q = sm_Q; m.mean_mask = mean_mask;
   m.hyp_cov.assign(hyp_cov, hyp_cov + n_cov); m.hyp_mean.assign(hyp_mean, hyp_mean + n_mean); m.hyp_lik = hyp_lik;

@@ -105,7 +105,7 @@ static int grid_setup(kgp_ctx* c, GridState* g, GridDesc& G) {
     G.ng[d] = (int)a.size(); G.stride[d] = N; N *= G.ng[d];
     G.ax[d] = g->axes.d() + o; o += (long)a.size();
     const bool neq = d < (int)c->grid.neq.size() && c->grid.neq[d] != 0;
-    G.deg[d] = c->model.opt.deg;                                // opt.deg (apx.m:122): equispaced axes only, neqinterp ignores it
+    G.deg[d] = (d < 4 && c->model.opt.deg_axis[d] >= 0) ? c->model.opt.deg_axis[d] : c->model.opt.deg;   // opt.deg (apx.m:122, apxGrid.m:448): equispaced axes only, neqinterp ignores it
     // the cell-sorted kernels (persistent CG, Gram accumulation, sorted Chebyshev recurrence) hard-wire the cubic stencil:
     // every other interpolation takes the general streaming kernels, like a non-equispaced axis
     g->any_neq |= neq || G.deg[d] != 3;

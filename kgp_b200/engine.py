@@ -100,6 +100,10 @@ class B200GP(object):
         if hyp.get('proj') is not None and inf != 'infGrid':
             raise ValueError('hyp.proj belongs to infGrid (infGrid.m:56-65)')
         self.using_grid = (inf == 'infGrid')
+        if self.using_grid and np.ndim(self._opt.get('deg', 3)) > 0:          # one degree per grid dimension (apxGrid.m:448)
+            p_grid = np.atleast_2d(hyp['proj']).shape[0] if hyp.get('proj') is not None else self.input_dim
+            if np.size(self._opt['deg']) not in (1, p_grid):
+                raise ValueError('opt.deg needs one entry or one per grid dimension (%d); got %r' % (p_grid, self._opt['deg']))
         if self.using_grid:
             assert grid_kwargs is not None, (
                 "GPML: No arguments provided for grid generation for infGrid.")

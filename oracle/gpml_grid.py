@@ -186,7 +186,8 @@ def interpgrid(xg, x, want_deriv=False, deg=3):
     dC = [np.ones((n, 1)) for _ in range(p)]
     s = 1
     for i in range(p):
-        Ji, Ci, dCi = eqinterp(xg[i], x[:, i], deg) if equi(xg[i]) else neqinterp(xg[i], x[:, i])   # apxGrid.m:453-465
+        di = int(np.atleast_1d(deg)[i % np.size(deg)])                                  # deg = deg(:).*ones(p,1) (apxGrid.m:448)
+        Ji, Ci, dCi = eqinterp(xg[i], x[:, i], di) if equi(xg[i]) else neqinterp(xg[i], x[:, i])    # apxGrid.m:453-465
         J = (J[:, :, None] + s * Ji[:, None, :]).reshape(n, -1)
         C = (C[:, :, None] * Ci[:, None, :]).reshape(n, -1)
         for jd in range(p):
@@ -598,7 +599,7 @@ def inf_grid(hyp, mean, kind, xg, x, y, opt=None, Q=0, want_grad=True, cheby=Non
         else:
             K_, dK_ = factor_cov(kind, hs[i], xg[i], Q); Ks.append(K_); dKs.append(dK_)
     xg = flat_grid(xg)
-    Mx = interpgrid(xg, x, deg=int(opt.get('deg', 3)))              # apx.m:122,131
+    Mx = interpgrid(xg, x, deg=opt.get('deg', 3))                   # apx.m:122,131
     MxT = Mx.T.tocsr()
     m, dm = mean_eval(mean, hyp.get('mean', []), x)
     sn2 = np.exp(2.0 * float(hyp['lik'])); W = np.full(n, 1.0 / sn2); sW = np.sqrt(W)
@@ -651,7 +652,7 @@ def dlik_grid(hyp, mean, kind, xg, x, y, opt=None, Q=0, h=1e-5):
     post, _, _ = inf_grid(hyp, mean, kind, xg, x, y, opt, Q, want_grad=False)
     alpha = post['alpha']
     xg = flat_grid(xg)
-    _, dM = interpgrid(xg, x, want_deriv=True, deg=int((opt or {}).get('deg', 3)))      # dlikGrid.m:23, deriv_x.m:7
+    _, dM = interpgrid(xg, x, want_deriv=True, deg=(opt or {}).get('deg', 3))           # dlikGrid.m:23, deriv_x.m:7
     beta = post['Kalpha']
     cols = []
     for i in range(x.shape[1]):

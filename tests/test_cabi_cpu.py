@@ -97,7 +97,8 @@ def test_unsupported_opt_keys_are_refused():
     d.set_model('infGrid', 'covSEiso', [0., 0.], 0.0, opt={'cg_tol': 1e-4, 'deg': 3})
     d.set_model('infGrid', 'covSEiso', [0., 0.], 0.0, opt={'proj': 'orth'})     # handled above the C ABI (engine.py)
     d.set_model('infGrid', 'covSEiso', [0., 0.], 0.0, opt={'deg': 1})           # linear / nearest-node interpolation are built
-    for bad in ({'deg': 5}, {'deg': [3, 1]}, {'ndcovs': 5}):
+    d.set_model('infGrid', 'covSEiso', [0., 0.], 0.0, opt={'deg': [3, 1]})      # one degree per grid dimension (apxGrid.m:448)
+    for bad in ({'deg': 5}, {'deg': [3, 2]}, {'deg': 1.5}, {'ndcovs': 5}):
         with pytest.raises(ValueError):
             d.set_model('infGrid', 'covSEiso', [0., 0.], 0.0, opt=bad)
 

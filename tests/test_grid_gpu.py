@@ -476,7 +476,7 @@ def test_non_equispaced_axes_vs_oracle(built_lib, shape):
     assert rel(ymu, gg.predict_grid(oh, ['meanZero'], 'covSEiso', xg, post, Xs)[2]) < 1e-7
 
 
-@pytest.mark.parametrize('deg,shape', [(1, '1d'), (1, '2d'), (0, '2d')])
+@pytest.mark.parametrize('deg,shape', [(1, '1d'), (1, '2d'), (0, '2d'), ([3, 1], '2d')])
 def test_interpolation_degree_vs_oracle(built_lib, deg, shape):
     """opt.deg (apx.m:27-32,122; apxGrid.m:495-523; passed through by kgp's `opt` dict): linear and nearest-node interpolation on
     equispaced axes -- nlZ, dnlZ, alpha, dnlZ/dX (zero for deg = 0: dk = 0) and the predictive mean against the oracle at tight CG;
@@ -514,6 +514,12 @@ def test_interpolation_degree_vs_oracle(built_lib, deg, shape):
     else:
         assert rel(dX, dX0) < 1e-7
     assert rel(ymu, gg.predict_grid(oh, ['meanZero'], 'covSEiso', xg, post, Xs, deg=deg)[2]) < 1e-7
+    if isinstance(deg, list):                                          # one degree per grid dimension (apxGrid.m:448)
+        _, nlZ1, _ = run(dict(opt, deg=1))
+        assert abs(nlZ1 - nlZ) > 1e-6 * abs(nlZ)
+        with pytest.raises(ValueError):
+            run(dict(opt, deg=[3, 1, 1]))
+        return
     _, nlZ3, _ = run({'cg_maxit': 8000, 'cg_tol': 1e-12})
     assert abs(nlZ3 - nlZ) > 1e-6 * abs(nlZ)                           # not the cubic result under another name
     with pytest.raises(ValueError):

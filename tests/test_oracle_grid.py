@@ -442,6 +442,9 @@ def test_eqinterp_low_degrees(deg):
         fd = (gg.inf_grid(hp, ['meanZero'], 'covSEiso', xg, X, y, opt, want_grad=False)[1] -
               gg.inf_grid(hm, ['meanZero'], 'covSEiso', xg, X, y, opt, want_grad=False)[1]) / 2e-6
         assert abs(fd - d['cov'][i]) < 1e-5 * max(1.0, abs(fd))
+    # one degree per grid dimension (apxGrid.m:448): cubic x this degree
+    Mm = gg.interpgrid(xg, X, deg=[3, deg])
+    assert np.allclose(Mm.sum(1), 1.0) and (Mm.getnnz(axis=1) <= 8).all() and abs(Mm - Mx).max() > 1e-3
     dX = gg.dlik_grid(hyp, ['meanZero'], 'covSEiso', xg, X, y, opt)
     if deg == 0:
         assert np.all(dX == 0)
