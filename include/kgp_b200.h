@@ -90,6 +90,10 @@ int  kgp_ctx_destroy(kgp_ctx* ctx);
 const char* kgp_last_error(kgp_ctx* ctx);
 const char* kgp_version(void);
 void kgp_opt_default(kgp_opt* opt);
+/* sizeof(kgp_opt) (which = 0) / sizeof(kgp_stats) (which = 1) as the library was compiled: a binding (the ctypes stub of
+ * INTEGRATION.md, a cgo / JNI struct) checks its own layout against it before the first call.  No counterpart in the reference
+ * (oct2py marshals dictionaries); -1 for an unknown `which`. */
+long kgp_abi_sizeof(int which);
 int  kgp_set_profiling(kgp_ctx* ctx, int on);   /* on: time GEMM launches separately (adds syncs) */
 
 /* multi-GPU: one context per rank / GPU, NCCL over NVLink.  No reference counterpart (the

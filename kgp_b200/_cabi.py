@@ -53,6 +53,7 @@ SIGNATURES = {
     'kgp_last_error': (C.c_char_p, [C.c_void_p]),
     'kgp_version': (C.c_char_p, []),
     'kgp_opt_default': (None, [C.POINTER(KgpOpt)]),
+    'kgp_abi_sizeof': (C.c_long, [C.c_int]),
     'kgp_set_profiling': (C.c_int, [C.c_void_p, C.c_int]),
     'kgp_set_data_host': (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_long, C.c_int, C.c_void_p]),
     'kgp_set_data_dev': (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_long, C.c_int, C.c_void_p]),
@@ -100,6 +101,10 @@ def lib():
             fn = getattr(l, name)
             fn.restype = res
             fn.argtypes = args
+        # the ctypes mirrors must have the layout the library was compiled with (a mismatch would corrupt memory silently)
+        if l.kgp_abi_sizeof(0) != C.sizeof(KgpOpt) or l.kgp_abi_sizeof(1) != C.sizeof(KgpStats):
+            raise ImportError('libkgp_b200.so and kgp_b200/_cabi.py disagree on kgp_opt / kgp_stats (%d / %d vs %d / %d bytes): rebuild'
+                              % (l.kgp_abi_sizeof(0), l.kgp_abi_sizeof(1), C.sizeof(KgpOpt), C.sizeof(KgpStats)))
         _lib = l
     return _lib
 

@@ -53,6 +53,7 @@ extern "C" {
 
 const char* kgp_version(void) { return "kgp_b200 0.1 (sm_100a)"; }
 
+long kgp_abi_sizeof(int which) { return which == 0 ? (long)sizeof(kgp_opt) : (which == 1 ? (long)sizeof(kgp_stats) : -1L); }
 void kgp_opt_default(kgp_opt* o) {
   memset(o, 0, sizeof *o);
   o->cg_tol = 1e-6; o->cg_maxit = 0; o->ldB2_cheby = 0; o->ldB2_cheby_hutch = 10;

@@ -111,3 +111,14 @@ def test_creategrid_fractional_k():
     du = 10.0 / 12.5
     assert ax.size == 12 and abs(ax[0] - (0.0 - 5 * du)) < 1e-15 and abs(ax[-1] - (10.0 + 5 * du)) < 1e-15
     assert np.allclose(np.diff(ax), (10.0 + 10 * du) / 11)
+
+
+def test_struct_layouts_match_the_library():
+    """kgp_abi_sizeof: the ctypes mirrors of kgp_opt / kgp_stats have the size the library was compiled with (lib() refuses to load
+    otherwise), and kgp_opt_default fills the documented defaults."""
+    import ctypes as C
+    from kgp_b200 import _cabi
+    l = _cabi.lib()
+    assert l.kgp_abi_sizeof(0) == C.sizeof(_cabi.KgpOpt) and l.kgp_abi_sizeof(1) == C.sizeof(_cabi.KgpStats) and l.kgp_abi_sizeof(7) == -1
+    o = _cabi.KgpOpt(); l.kgp_opt_default(C.byref(o))
+    assert o.deg == 3 and list(o.deg_axis) == [-1, -1, -1, -1] and o.cg_deterministic == 1 and o.cg_precond == 0 and o.pred_var == 0
